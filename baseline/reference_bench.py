@@ -1,0 +1,33 @@
+"""Reference arm of bench.py: runs the UNMODIFIED reference (copied under baseline/_ref) through its own public
+C++ API (Sequential / SequentialBuilder model zoo, Adam, LogSoftmaxCrossEntropy, the train_class_epoch loop of
+include/nn/train.hpp:108-170) on synthetic data.  See baseline/README.md for how the subset build is made."""
+import json
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+BIN = os.path.join(HERE, "_ref", "bin", "ref_bench")
+
+
+def run(args):
+    if not os.path.exists(BIN):
+        print(json.dumps({"impl": "reference", "unavailable": "reference harness not built (baseline/build_ref.sh)"}))
+        return 0
+    if args.gpus != 1:
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "the reference has no data parallelism and its pipeline needs asio+TBB, absent offline; "
+                          "only the single-GPU reference arm exists"}))
+        return 0
+    cmd = [BIN, str(args.batch), str(args.steps), str(args.warmup)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    line = None
+    for l in r.stdout.splitlines():
+        if l.startswith("{"):
+            line = l
+    if r.returncode != 0 or line is None:
+        print(json.dumps({"impl": "reference", "unavailable": "reference harness failed: " +
+                          (r.stderr.strip().splitlines() or ["no output"])[-1][:200]}))
+        return 0
+    print(line)
+    return 0

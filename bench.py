@@ -1,0 +1,240 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 (Tiny-ImageNet shape, 64x64) training throughput in images/s.
+
+Contract (see the round brief): ``python bench.py --gpus N --steps K --warmup W`` (launched under torchrun for
+N>1, one rank per GPU, NCCL for the plumbing).  W untimed warm-up steps, then exactly K timed steps bracketed by
+barrier + cuda synchronize, device-timed with CUDA events, max over ranks; rank 0 prints ONE JSON line.
+``--impl reference`` runs the unmodified reference build under baseline/_ref for the same metric/config.
+Synthetic data of the named shape, random-init weights; compute dtype: fp32 storage, TF32 tensor-core MMA with
+FP32 accumulation (the reference is FP32 cuDNN/cuBLAS, which uses TF32 tensor cores for FP32 convolutions)."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MODEL = "ResNet-50-Tiny-ImageNet"
+IMG = (3, 64, 64)
+CLASSES = 200
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+
+    def __init__(self, gpu_index: int):
+        super().__init__(daemon=True)
+        self.gpu_index = gpu_index
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.proc = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.gpu_index), "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            return
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.proc.stdout:
+            if self._stop_evt.is_set():
+                break
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                self.samples.append(float(parts[0]))
+                self.max_mhz = float(parts[1])
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    self.reasons.add(n)
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.proc is not None:
+            self.proc.terminate()
+
+    def summary(self):
+        s = sorted(self.samples)
+        med = s[len(s) // 2] if s else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=int(os.environ.get("BENCH_BATCH", 256)), help="per-GPU batch")
+    ap.add_argument("--parallelism", default=os.environ.get("BENCH_PARALLELISM", "auto"))
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--microbatches", type=int, default=1)
+    return ap.parse_args()
+
+
+def reference_arm(args):
+    from baseline import reference_bench
+    return reference_bench.run(args)
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+    from dcnn_b200 import _lib, nn
+    from dcnn_b200.models import create_resnet50_tiny_imagenet
+    from dcnn_b200.train import TrainStep
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N > 1")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    torch.manual_seed(1234)
+    model = create_resnet50_tiny_imagenet()
+    model.set_seed(42)           # identical initial weights on every replica
+    model.set_device(dev)
+    model.initialize()
+    model.compute_input_gradient = False
+    opt = nn.Adam(1e-4, epsilon=1e-3, weight_decay=1e-3)   # examples/tiny_imagenet_resnet50.cpp:90
+    loss_fn = nn.LogSoftmaxCrossEntropyLoss()
+
+    parallelism = "single"
+    dp = None
+    if world > 1:
+        from dcnn_b200.parallel.dp import DataParallel
+        dp = DataParallel(model, opt, dist.group.WORLD, sync_bn=os.environ.get("BENCH_SYNC_BN", "1") == "1")
+        parallelism = f"dp{world}"
+    else:
+        opt.attach(model.parameters(), model.gradients())
+    step = TrainStep(model, opt, loss_fn, use_cuda_graph=not args.no_graph and dp is None,
+                     num_microbatches=args.microbatches, data_parallel=dp)
+
+    B = args.batch
+    g = torch.Generator().manual_seed(1000 + rank)
+    nbuf = 4
+    host_x = [torch.randn(B, *IMG, generator=g).pin_memory() for _ in range(nbuf)]
+    host_t = [torch.nn.functional.one_hot(torch.randint(0, CLASSES, (B,), generator=g), CLASSES).float()
+              .reshape(B, CLASSES, 1, 1).pin_memory() for _ in range(nbuf)]
+    dev_x = [x.to(dev) for x in host_x]
+    dev_t = [t.to(dev) for t in host_t]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- kernel-only arm: inputs already resident, no host read-back inside the timed region
+    for i in range(args.warmup):
+        step(dev_x[i % nbuf], dev_t[i % nbuf])
+    barrier()
+    sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else 0)
+    if rank == 0:
+        sampler.start()
+    _lib.reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        loss, correct = step(dev_x[i % nbuf], dev_t[i % nbuf])
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = _lib.launch_count()
+    if step._graph is not None:   # replayed graph: count the kernels captured in one step
+        launches = step_launches(step, dev_x[0], dev_t[0], _lib) * args.steps
+    final_loss = float(loss)
+
+    # ---- end-to-end arm: public API, pinned-host -> device copy of every batch + loss read-back every step
+    h2d = host_x[0].numel() * 4 + host_t[0].numel() * 4
+    d2h = 8
+    out_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+    for i in range(2):
+        step(host_x[i % nbuf].to(dev, non_blocking=True), host_t[i % nbuf].to(dev, non_blocking=True))
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for i in range(args.steps):
+        x = host_x[i % nbuf].to(dev, non_blocking=True)
+        t = host_t[i % nbuf].to(dev, non_blocking=True)
+        loss, correct = step(x, t)
+        out_host[0].copy_(loss, non_blocking=True)
+        out_host[1].copy_(correct, non_blocking=True)
+        torch.cuda.current_stream().synchronize()     # the step's result is on the host before the next step
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    if rank == 0:
+        sampler.stop()
+
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    gb = B * world
+    value = gb * args.steps / (ms / 1000.0)
+    e2e = gb * args.steps / (ms_e2e / 1000.0)
+    if rank == 0:
+        base = None
+        try:
+            with open(os.path.join(ROOT, "BASELINE.json")) as f:
+                pub = json.load(f).get("published", {})
+            base = pub.get("images_per_sec") if isinstance(pub, dict) else None
+        except (OSError, ValueError):
+            pass
+        out = {
+            "metric": "train images/sec ResNet-50 64x64 (Tiny-ImageNet shape), max over ranks",
+            "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": (value / base) if base else None,
+            "dtype": "fp32 storage, tf32 tensor-core MMA, fp32 accumulate", "data": "synthetic", "impl": "ours",
+            "config": {"model": MODEL, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
+                       "image": "3x64x64", "classes": CLASSES, "parallelism": parallelism,
+                       "optimizer": "Adam(lr 1e-4, eps 1e-3, wd 1e-3)", "loss": "LogSoftmaxCrossEntropy",
+                       "cuda_graph": step._graph is not None, "microbatches": args.microbatches,
+                       "l2": "per-step working set (activations, >10 GB at batch 256) is far larger than the 126 MB L2; "
+                             "inputs rotate over 4 distinct batches"},
+            "clocks": sampler.summary(),
+            "e2e": {"value": round(e2e, 2), "unit": "images/s", "ms_per_step": round(ms_e2e / args.steps, 4),
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(launches),
+            "final_loss": final_loss,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def step_launches(step, x, t, _lib):
+    """Kernels of one training step, counted by running it once eagerly outside the timed region."""
+    import torch
+    _lib.reset_launch_count()
+    step._eager(x, t)
+    torch.cuda.synchronize()
+    return _lib.launch_count()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,204 @@
+// CUDA-core (SIMT, exact FP32) implicit-GEMM fallbacks for shapes the tensor-core path does not take:
+// channel counts that are not a multiple of 32 (the RGB stem, the MNIST CNN, odd Dense widths).
+// One tiled gather-GEMM kernel, three instantiations: fprop, dgrad, wgrad (split-K with FP32 atomics so that
+// weight gradients accumulate, beta=1, like the reference's cudnnConvolutionBackwardFilter call).
+// Also: the weight re-layout used by the tensor-core dgrad, and the exact-FP32 Dense paths.
+#include "common.cuh"
+
+namespace dcnn {
+
+struct ConvGeom {
+  int N, H, W, C;     // input
+  int OH, OW, K;      // output (K = out channels)
+  int R, S, sh, sw, ph, pw;
+};
+
+// ---- operand functors: element (row, k) of the logical GEMM operand, 0 when masked -------------------
+struct FpropA {  // row = output pixel, k = (r,s,c)
+  const float* x; ConvGeom g;
+  __device__ __forceinline__ float operator()(int m, int k) const {
+    const int c = k % g.C; const int t = k / g.C; const int s = t % g.S; const int r = t / g.S;
+    const int ow = m % g.OW; const int oh = (m / g.OW) % g.OH; const int n = m / (g.OW * g.OH);
+    const int ih = oh * g.sh - g.ph + r, iw = ow * g.sw - g.pw + s;
+    if ((unsigned)ih >= (unsigned)g.H || (unsigned)iw >= (unsigned)g.W) return 0.f;
+    return __ldg(x + (((long long)n * g.H + ih) * g.W + iw) * g.C + c);
+  }
+};
+struct FpropB {  // row = oc, k = (r,s,c): weights are [K][R][S][C]
+  const float* w; int Ktot;
+  __device__ __forceinline__ float operator()(int n, int k) const { return __ldg(w + (long long)n * Ktot + k); }
+};
+struct DgradA {  // row = input pixel (n,h,w), k = (r,s,oc)
+  const float* dy; ConvGeom g;
+  __device__ __forceinline__ float operator()(int m, int k) const {
+    const int oc = k % g.K; const int t = k / g.K; const int s = t % g.S; const int r = t / g.S;
+    const int w_ = m % g.W; const int h = (m / g.W) % g.H; const int n = m / (g.W * g.H);
+    const int a = h + g.ph - r, b = w_ + g.pw - s;
+    if (a < 0 || b < 0 || a % g.sh || b % g.sw) return 0.f;
+    const int oh = a / g.sh, ow = b / g.sw;
+    if (oh >= g.OH || ow >= g.OW) return 0.f;
+    return __ldg(dy + (((long long)n * g.OH + oh) * g.OW + ow) * g.K + oc);
+  }
+};
+struct DgradB {  // row = c, k = (r,s,oc)
+  const float* w; ConvGeom g;
+  __device__ __forceinline__ float operator()(int c, int k) const {
+    const int oc = k % g.K; const int t = k / g.K;
+    return __ldg(w + ((long long)oc * g.R * g.S + t) * g.C + c);
+  }
+};
+struct WgradA {  // row = oc, k = output pixel
+  const float* dy; int K;
+  __device__ __forceinline__ float operator()(int oc, int pix) const { return __ldg(dy + (long long)pix * K + oc); }
+};
+struct WgradB {  // row = (r,s,c), k = output pixel
+  const float* x; ConvGeom g;
+  __device__ __forceinline__ float operator()(int j, int pix) const {
+    const int c = j % g.C; const int t = j / g.C; const int s = t % g.S; const int r = t / g.S;
+    const int ow = pix % g.OW; const int oh = (pix / g.OW) % g.OH; const int n = pix / (g.OW * g.OH);
+    const int ih = oh * g.sh - g.ph + r, iw = ow * g.sw - g.pw + s;
+    if ((unsigned)ih >= (unsigned)g.H || (unsigned)iw >= (unsigned)g.W) return 0.f;
+    return __ldg(x + (((long long)n * g.H + ih) * g.W + iw) * g.C + c);
+  }
+};
+
+// C[m][n] = sum_k A(m,k) * B(n,k); 64x64 tile, 16-deep k slices, 256 threads, 4x4 outputs per thread.
+// ATOMIC: split-K over blockIdx.z, results added with atomics (accumulates into C).
+template <class FA, class FB, bool ATOMIC>
+__global__ void __launch_bounds__(256) gather_gemm_kernel(int M, int N, int K, int k_per_split, FA fa, FB fb,
+                                                          float* __restrict__ C, long long ldc,
+                                                          const float* __restrict__ bias, int accumulate) {
+  __shared__ float sA[16][64 + 4];
+  __shared__ float sB[16][64 + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
+  const int kbeg = blockIdx.z * k_per_split;
+  const int kend = min(K, kbeg + k_per_split);
+  float acc[4][4] = {};
+  for (int k0 = kbeg; k0 < kend; k0 += 16) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = tid + i * 256;  // 0..1023
+      const int kk = idx & 15, row = idx >> 4;
+      const int k = k0 + kk;
+      sA[kk][row] = (m0 + row < M && k < kend) ? fa(m0 + row, k) : 0.f;
+      sB[kk][row] = (n0 + row < N && k < kend) ? fb(n0 + row, k) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = sA[kk][ty * 4 + i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = sB[kk][tx * 4 + j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= N) continue;
+      float* dst = C + (long long)m * ldc + n;
+      if (ATOMIC) {
+        atomicAdd(dst, acc[i][j]);
+      } else {
+        float v = acc[i][j] + (bias ? __ldg(bias + n) : 0.f);
+        if (accumulate) v += *dst;
+        *dst = v;
+      }
+    }
+  }
+}
+
+// W[K][R][S][C]  ->  Wt[C][R][S][K] with both spatial axes flipped: the weights of the stride-1 dgrad
+// expressed as a forward convolution over dY.
+__global__ void weight_dgrad_layout_kernel(const float* __restrict__ w, float* __restrict__ wt, int K, int R, int S,
+                                           int C) {
+  const long long total = (long long)K * R * S * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    // i indexes the destination [c][r'][s'][k]
+    const int k = (int)(i % K);
+    long long t = i / K;
+    const int s2 = (int)(t % S); t /= S;
+    const int r2 = (int)(t % R);
+    const int c = (int)(t / R);
+    wt[i] = __ldg(w + (((long long)k * R + (R - 1 - r2)) * S + (S - 1 - s2)) * C + c);
+  }
+}
+
+}  // namespace dcnn
+using namespace dcnn;
+
+static ConvGeom make_geom(int N, int H, int W, int C, int K, int R, int S, int sh, int sw, int ph, int pw) {
+  ConvGeom g;
+  g.N = N; g.H = H; g.W = W; g.C = C; g.K = K; g.R = R; g.S = S; g.sh = sh; g.sw = sw; g.ph = ph; g.pw = pw;
+  g.OH = (H + 2 * ph - R) / sh + 1;
+  g.OW = (W + 2 * pw - S) / sw + 1;
+  return g;
+}
+
+DCNN_API int dcnn_conv_fprop_simt(const float* x, const float* w, const float* bias, float* y, int N, int H, int W,
+                                  int C, int K, int R, int S, int sh, int sw, int ph, int pw, cudaStream_t stream) {
+  ConvGeom g = make_geom(N, H, W, C, K, R, S, sh, sw, ph, pw);
+  const long long M = (long long)N * g.OH * g.OW;
+  const int Ktot = R * S * C;
+  dim3 grid(ceil_div(M, 64), ceil_div(K, 64), 1);
+  gather_gemm_kernel<FpropA, FpropB, false><<<grid, 256, 0, stream>>>((int)M, K, Ktot, Ktot, FpropA{x, g},
+                                                                      FpropB{w, Ktot}, y, K, bias, 0);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_conv_dgrad_simt(const float* dy, const float* w, float* dx, int N, int H, int W, int C, int K, int R,
+                                  int S, int sh, int sw, int ph, int pw, int accumulate, cudaStream_t stream) {
+  ConvGeom g = make_geom(N, H, W, C, K, R, S, sh, sw, ph, pw);
+  const long long M = (long long)N * H * W;
+  const int Kred = R * S * K;
+  dim3 grid(ceil_div(M, 64), ceil_div(C, 64), 1);
+  gather_gemm_kernel<DgradA, DgradB, false><<<grid, 256, 0, stream>>>((int)M, C, Kred, Kred, DgradA{dy, g},
+                                                                      DgradB{w, g}, dx, C, nullptr, accumulate);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_conv_wgrad_simt(const float* dy, const float* x, float* dw, int N, int H, int W, int C, int K, int R,
+                                  int S, int sh, int sw, int ph, int pw, cudaStream_t stream) {
+  ConvGeom g = make_geom(N, H, W, C, K, R, S, sh, sw, ph, pw);
+  const long long P = (long long)N * g.OH * g.OW;
+  const int Ktot = R * S * C;
+  const int tiles = ceil_div(K, 64) * ceil_div(Ktot, 64);
+  int splits = ceil_div(4 * num_sms(), tiles);
+  const int max_splits = ceil_div(P, 256);
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  int per = ceil_div(P, splits);
+  per = ceil_div(per, 16) * 16;
+  splits = ceil_div(P, per);
+  dim3 grid(ceil_div(K, 64), ceil_div(Ktot, 64), splits);
+  gather_gemm_kernel<WgradA, WgradB, true><<<grid, 256, 0, stream>>>(K, Ktot, (int)P, per, WgradA{dy, K},
+                                                                     WgradB{x, g}, dw, Ktot, nullptr, 1);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_weight_dgrad_layout(const float* w, float* wt, int K, int R, int S, int C, cudaStream_t stream) {
+  const long long total = (long long)K * R * S * C;
+  weight_dgrad_layout_kernel<<<ew_grid(total, 256), 256, 0, stream>>>(w, wt, K, R, S, C);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}

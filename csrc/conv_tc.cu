@@ -1,0 +1,657 @@
+// Implicit-GEMM convolution / GEMM on the 5th-generation tensor cores (sm_100a).
+//
+//   * conv_tc_kernel   : D[pixels, oc] = sum_{tap, c} A[pixel@tap, c] * W[oc, tap, c]      (both operands K-major)
+//       used for conv fprop, conv dgrad (on dY with re-laid-out weights; strided dgrad as parity classes with an
+//       output stride), Dense forward and Dense dgrad.  Replaces cudnnConvolutionForward / BackwardData and
+//       cublasSgemm of the reference (src/nn/layers_impl/cuda/cudnn_conv2d_ops.cu:171-216, dense_ops.cu:24-137).
+//   * wgrad_tc_kernel  : dW[oc, tap, c] += sum_{pixels} dY[pixel, oc] * X[pixel@tap, c]   (both operands MN-major)
+//       replaces cudnnConvolutionBackwardFilter (beta=1 accumulate, cudnn_conv2d_ops.cu:218-232).
+//
+// Data path: activations are NHWC fp32.  One elected thread issues TMA: the A tile is a 4-D box {32 ch, bw, bh, bn}
+// (bw*bh*bn = 128 output pixels) whose start coordinate is shifted by the filter tap; out-of-image coordinates
+// (padding) are zero-filled by the TMA unit, so no im2col buffer and no padding copies exist.  Strided convolutions
+// use the tensor map's element strides.  Tiles land in shared memory in the 128-byte-swizzled canonical layout and
+// are consumed by tcgen05.mma.kind::tf32 (issued by one thread), accumulating FP32 in TMEM.  Four epilogue warps
+// read TMEM with tcgen05.ld, add bias, stage the tile in shared memory, then (a) store it coalesced (optionally
+// accumulating into the destination, which is how residual-branch gradients are summed) and (b) emit per-channel
+// BatchNorm partial statistics (sum, centred M2) for this 128-pixel tile, so BN never re-reads the conv output
+// to compute its statistics.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace dcnn {
+using namespace tc;
+
+constexpr int kMaxTaps = 49;
+constexpr int kBM = 128;       // output pixels per tile == TMEM lanes
+constexpr int kBK = 32;        // fp32 per k-block == 128 bytes == one swizzle row
+constexpr int kThreads = 192;  // warp0: TMA, warp1: MMA + TMEM alloc, warps 2-5: epilogue
+
+struct ConvTcParams {
+  int N, OH, OW;                 // loop-space extents
+  int bn, bh, bw;                // tile box (bn*bh*bw == 128)
+  int tiles_n, tiles_h, tiles_w;
+  int in_mul_h, in_mul_w;        // input coordinate = out coordinate * mul + tap offset
+  int Cin, Cout, n_tiles;
+  int num_taps;
+  int accumulate;
+  long long out_sn, out_sh, out_sw;
+  float* out;
+  const float* bias;
+  float* partials;               // [m_tiles][2][Cout] then [m_tiles] counts, or nullptr
+  int m_tiles;
+  int16_t tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_w[kMaxTaps];
+};
+
+template <int BN, int STAGES>
+struct ConvTcSmem {
+  static constexpr int kABytes = kBM * 128;
+  static constexpr int kBBytes = BN * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kPipeBytes = STAGES * kStageBytes;
+  static constexpr int kOutStride = BN + 4;  // floats; +4 keeps float4 alignment and spreads banks
+  static constexpr int kStagingBytes = kBM * kOutStride * 4;
+  static constexpr int kMainBytes = kPipeBytes > kStagingBytes ? kPipeBytes : kStagingBytes;
+  static constexpr int kTotalBytes = kMainBytes + 1024 /*align*/ + 256 /*barriers*/ + 512 /*row flags*/;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                           const __grid_constant__ CUtensorMap tmB,
+                                                           const __grid_constant__ ConvTcParams p) {
+  using S = ConvTcSmem<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kMainBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  uint8_t* row_valid = smem + S::kMainBytes + 256;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // tile coordinates: n-tile is the fastest index so CTAs that share an A tile run back to back (L2 reuse)
+  const int n_tile = blockIdx.x % p.n_tiles;
+  const int m_tile = blockIdx.x / p.n_tiles;
+  const int tw = m_tile % p.tiles_w;
+  const int th = (m_tile / p.tiles_w) % p.tiles_h;
+  const int tn = m_tile / (p.tiles_w * p.tiles_h);
+  const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
+
+  const int cchunks = p.Cin / kBK;
+  const int num_kb = p.num_taps * cchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, BN < 32 ? 32 : BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int t = kb / cchunks;
+        const int c = kb - t * cchunks;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
+        uint8_t* sA = smem + stage * S::kStageBytes;
+        tma_load_4d(sA, &tmA, &full_bar[stage], c * kBK, ow0 * p.in_mul_w + p.tap_dw[t],
+                    oh0 * p.in_mul_h + p.tap_dh[t], n0);
+        tma_load_2d(sA + S::kABytes, &tmB, &full_bar[stage], p.tap_w[t] * p.Cin + c * kBK, n_tile * BN);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t idesc = make_idesc_tf32(kBM, BN, 0, 0);
+      constexpr uint64_t desc_hi = make_smem_desc_hi(16, 1024);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+        const uint32_t b_addr = a_addr + S::kABytes;
+#pragma unroll
+        for (int k = 0; k < kBK / 8; ++k) {
+          mma_tf32_ss(tmem_base, make_smem_desc(a_addr + k * 32, desc_hi), make_smem_desc(b_addr + k * 32, desc_hi),
+                      idesc, (kb | k) != 0);
+        }
+        mma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      mma_commit(tmem_full_bar);
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;  // TMEM lane quadrant this warp may access
+    const int r = q * 32 + lane;
+    const int e = threadIdx.x - 64;  // 0..127
+    // row -> output pixel
+    const int w_l = r % p.bw;
+    const int h_l = (r / p.bw) % p.bh;
+    const int n_l = r / (p.bw * p.bh);
+    const bool valid = (n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW);
+    row_valid[r] = valid ? 1 : 0;
+
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    float* staging = reinterpret_cast<float*>(smem);
+    const int col_base = n_tile * BN;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      float* dst = staging + r * S::kOutStride + c0;
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        float4 o;
+        o.x = __uint_as_float(v[j + 0]);
+        o.y = __uint_as_float(v[j + 1]);
+        o.z = __uint_as_float(v[j + 2]);
+        o.w = __uint_as_float(v[j + 3]);
+        if (p.bias != nullptr) {
+          const int c = col_base + c0 + j;
+          o.x += (c + 0 < p.Cout) ? __ldg(p.bias + c + 0) : 0.f;
+          o.y += (c + 1 < p.Cout) ? __ldg(p.bias + c + 1) : 0.f;
+          o.z += (c + 2 < p.Cout) ? __ldg(p.bias + c + 2) : 0.f;
+          o.w += (c + 3 < p.Cout) ? __ldg(p.bias + c + 3) : 0.f;
+        }
+        st4(dst + j, o);
+      }
+    }
+    tc_fence_before();
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+
+    // ---- (a) coalesced store: one warp instruction writes one output row segment
+    const int ew = warp - 2;
+    const bool vec_ok = (p.Cout & 3) == 0;
+    for (int i = 0; i < 32; ++i) {
+      const int rr = ew * 32 + i;
+      if (!row_valid[rr]) continue;
+      const int ww = rr % p.bw, hh = (rr / p.bw) % p.bh, nn = rr / (p.bw * p.bh);
+      float* orow = p.out + (long long)(n0 + nn) * p.out_sn + (long long)(oh0 + hh) * p.out_sh +
+                    (long long)(ow0 + ww) * p.out_sw + col_base;
+      const float* srow = staging + rr * S::kOutStride;
+      if (vec_ok) {
+        for (int cj = lane * 4; cj < BN; cj += 128) {
+          if (col_base + cj < p.Cout) {
+            float4 o = ld4(srow + cj);
+            if (p.accumulate) {
+              const float4 old = ld4(orow + cj);
+              o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+            }
+            st4(orow + cj, o);
+          }
+        }
+      } else {
+        for (int cj = lane; cj < BN; cj += 32) {
+          if (col_base + cj < p.Cout) {
+            float o = srow[cj];
+            if (p.accumulate) o += orow[cj];
+            orow[cj] = o;
+          }
+        }
+      }
+    }
+
+    // ---- (b) BatchNorm partial statistics of this tile: per channel (sum, M2 about the tile mean)
+    if (p.partials != nullptr) {
+      int cnt = 0;
+      for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
+      if (e == 0 && n_tile == 0) p.partials[(long long)p.m_tiles * 2 * p.Cout + m_tile] = (float)cnt;
+      for (int j = e; j < BN; j += 128) {
+        const int c = col_base + j;
+        if (c >= p.Cout) continue;
+        float s = 0.f;
+        for (int rr = 0; rr < kBM; ++rr) s += row_valid[rr] ? staging[rr * S::kOutStride + j] : 0.f;
+        const float mean = cnt > 0 ? s / (float)cnt : 0.f;
+        float m2 = 0.f;
+        for (int rr = 0; rr < kBM; ++rr) {
+          const float d = staging[rr * S::kOutStride + j] - mean;
+          m2 += row_valid[rr] ? d * d : 0.f;
+        }
+        p.partials[((long long)m_tile * 2 + 0) * p.Cout + c] = s;
+        p.partials[((long long)m_tile * 2 + 1) * p.Cout + c] = m2;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+  }
+}
+
+// =====================================================================================================
+// wgrad
+// =====================================================================================================
+constexpr int kWPix = 64;  // reduction (pixel) rows per pipeline stage
+
+struct WgradTcParams {
+  int N, OH, OW;
+  int bn, bh, bw;  // box over dY pixels (product == kWPix)
+  int tiles_n, tiles_h, tiles_w;
+  int in_mul_h, in_mul_w;
+  int Cin, Cout, Ktot;
+  int num_taps, oc_tiles, c_tiles, splits;
+  float* dw;  // [Cout][Ktot]
+  int16_t tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_w[kMaxTaps];
+};
+
+template <int BNW, int STAGES>
+struct WgradSmem {
+  static constexpr int kABytes = 4 * kWPix * 128;          // 4 boxes of [64 pix][32 oc]
+  static constexpr int kBBytes = (BNW / 32) * kWPix * 128;  // BNW/32 boxes of [64 pix][32 c]
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kMainBytes = STAGES * kStageBytes;
+  static constexpr int kTotalBytes = kMainBytes + 1024 + 256;
+};
+
+template <int BNW, int STAGES>
+__global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY,
+                                                            const __grid_constant__ CUtensorMap tmX,
+                                                            const __grid_constant__ WgradTcParams p) {
+  using S = WgradSmem<BNW, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kMainBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // blockIdx.x -> (c_tile, oc_tile, tap); blockIdx.y -> split of the pixel-tile range
+  int b = blockIdx.x;
+  const int c_tile = b % p.c_tiles;
+  b /= p.c_tiles;
+  const int oc_tile = b % p.oc_tiles;
+  const int tap = b / p.oc_tiles;
+  const int pix_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
+  const int per = (pix_tiles + p.splits - 1) / p.splits;
+  const int pt_begin = blockIdx.y * per;
+  const int pt_end = min(pix_tiles, pt_begin + per);
+  const int num_kb = max(0, pt_end - pt_begin);
+  const int oc0 = oc_tile * 128, c0 = c_tile * BNW;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmDY);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      mbar_init(tmem_full_bar, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, BNW);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (num_kb > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        int stage = 0;
+        uint32_t phase = 0;
+        const int dh = p.tap_dh[tap], dw_ = p.tap_dw[tap];
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int pt = pt_begin + kb;
+          const int tw = pt % p.tiles_w;
+          const int th = (pt / p.tiles_w) % p.tiles_h;
+          const int tn = pt / (p.tiles_w * p.tiles_h);
+          const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
+          uint8_t* sA = smem + stage * S::kStageBytes;
+          uint8_t* sB = sA + S::kABytes;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            tma_load_4d(sA + i * kWPix * 128, &tmDY, &full_bar[stage], oc0 + i * 32, ow0, oh0, n0);
+#pragma unroll
+          for (int j = 0; j < BNW / 32; ++j)
+            tma_load_4d(sB + j * kWPix * 128, &tmX, &full_bar[stage], c0 + j * 32, ow0 * p.in_mul_w + dw_,
+                        oh0 * p.in_mul_h + dh, n0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        constexpr uint32_t idesc = make_idesc_tf32(128, BNW, 1, 1);           // both operands MN-major
+        constexpr uint64_t desc_hi = make_smem_desc_hi(kWPix * 128, 1024);     // LBO = next 32-wide MN chunk
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+          const uint32_t b_addr = a_addr + S::kABytes;
+#pragma unroll
+          for (int k = 0; k < kWPix / 8; ++k) {
+            // advancing K by 8 pixel rows == 8 * 128 B == one swizzle atom
+            mma_tf32_ss(tmem_base, make_smem_desc(a_addr + k * 1024, desc_hi),
+                        make_smem_desc(b_addr + k * 1024, desc_hi), idesc, (kb | k) != 0);
+          }
+          mma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        mma_commit(tmem_full_bar);
+      }
+    } else {
+      const int q = warp & 3;
+      const int r = q * 32 + lane;  // output row = oc
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+      const int oc = oc0 + r;
+#pragma unroll 1
+      for (int cc = 0; cc < BNW; cc += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + cc, v);
+        tmem_ld_wait();
+        if (oc < p.Cout) {
+          float* dst = p.dw + (long long)oc * p.Ktot + (long long)p.tap_w[tap] * p.Cin + c0 + cc;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            if (c0 + cc + j < p.Cin) {
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j),
+                           "f"(__uint_as_float(v[j])), "f"(__uint_as_float(v[j + 1])),
+                           "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3]))
+                           : "memory");
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BNW);
+  }
+}
+
+// =====================================================================================================
+// host side
+// =====================================================================================================
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                        CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                        CUtensorMapFloatOOBfill);
+
+static PFN_tmapEncodeTiled get_encode() {
+  static PFN_tmapEncodeTiled fn = nullptr;
+  if (!fn) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_tmapEncodeTiled>(ptr);
+  }
+  return fn;
+}
+
+// NHWC fp32 tensor [N][H][W][C] -> 4-D map, box {32, bw*mul_w, bh*mul_h, bn}, element strides {1,mul_w,mul_h,1}
+static int make_tmap_nhwc(CUtensorMap* tm, const float* base, int N, int H, int W, int C, int bn, int bh, int bw,
+                          int mul_h, int mul_w) {
+  PFN_tmapEncodeTiled enc = get_encode();
+  DCNN_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+  cuuint32_t box[4] = {32, (cuuint32_t)(bw * mul_w), (cuuint32_t)(bh * mul_h), (cuuint32_t)bn};
+  cuuint32_t estr[4] = {1, (cuuint32_t)mul_w, (cuuint32_t)mul_h, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DCNN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(NHWC %dx%dx%dx%d box %d,%d,%d mul %d,%d) failed: %d", N, H,
+               W, C, bn, bh, bw, mul_h, mul_w, (int)r);
+  return 0;
+}
+
+// row-major fp32 matrix [rows][cols] -> 2-D map, box {32, box_rows}
+static int make_tmap_2d(CUtensorMap* tm, const float* base, long long rows, long long cols, int box_rows) {
+  PFN_tmapEncodeTiled enc = get_encode();
+  DCNN_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)cols * 4};
+  cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DCNN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(2D %lldx%lld box %d) failed: %d", rows, cols, box_rows,
+               (int)r);
+  return 0;
+}
+
+// Pick the power-of-two box (bn,bh,bw) with bn*bh*bw == pixels that covers [N,OH,OW] with the fewest tiles.
+static void choose_box(int N, int OH, int OW, int pixels, int mul_h, int mul_w, int* bn, int* bh, int* bw) {
+  long long best = -1;
+  for (int w = 1; w <= pixels; w <<= 1) {
+    if (w * mul_w > 256) break;
+    for (int h = 1; w * h <= pixels; h <<= 1) {
+      if (h * mul_h > 256) break;
+      const int n = pixels / (w * h);
+      if (n > 256) continue;
+      const long long tiles = (long long)ceil_div(OW, w) * ceil_div(OH, h) * ceil_div(N, n);
+      // prefer fewer tiles, then wider rows (longer contiguous runs)
+      if (best < 0 || tiles < best || (tiles == best && w > *bw)) {
+        best = tiles;
+        *bn = n; *bh = h; *bw = w;
+      }
+    }
+  }
+}
+
+template <int BN, int STAGES>
+static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvTcParams& p, cudaStream_t stream) {
+  using S = ConvTcSmem<BN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         S::kTotalBytes));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)((long long)p.m_tiles * p.n_tiles));
+  conv_tc_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, p);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+template <int BNW, int STAGES>
+static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradTcParams& p, cudaStream_t stream) {
+  using S = WgradSmem<BNW, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DCNN_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<BNW, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         S::kTotalBytes));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)(p.num_taps * p.oc_tiles * p.c_tiles), (unsigned)p.splits);
+  wgrad_tc_kernel<BNW, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmDY, tmX, p);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+}  // namespace dcnn
+
+using namespace dcnn;
+
+// Number of 128-pixel M tiles the tensor-core conv uses for a loop space [N,OH,OW]; the BN partial-statistics
+// buffer must hold m_tiles*(2*Cout+1) floats.
+DCNN_API int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w) {
+  int bn = 1, bh = 1, bw = 1;
+  choose_box(N, OH, OW, kBM, mul_h, mul_w, &bn, &bh, &bw);
+  return ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
+}
+
+// Generic tap-list implicit GEMM (see file header).  x: NHWC [N][H][W][Cin] (Cin % 32 == 0),
+// w: [Cout][Ktot] with K index = tap_w*Cin + c.  Output pixel (n,oh,ow), channel oc is written to
+// out[n*out_sn + oh*out_sh + ow*out_sw + oc].
+DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
+                          long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h,
+                          int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w,
+                          const float* bias, int accumulate, float* partials, cudaStream_t stream) {
+  DCNN_REQUIRE(Cin % kBK == 0, "dcnn_conv_tc: Cin (%d) must be a multiple of 32", Cin);
+  DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_conv_tc: bad tap count %d", num_taps);
+  DCNN_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0,
+               "dcnn_conv_tc: operands must be 16-byte aligned");
+  ConvTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.N = N; p.OH = OH; p.OW = OW;
+  choose_box(N, OH, OW, kBM, in_mul_h, in_mul_w, &p.bn, &p.bh, &p.bw);
+  p.tiles_n = ceil_div(N, p.bn); p.tiles_h = ceil_div(OH, p.bh); p.tiles_w = ceil_div(OW, p.bw);
+  p.m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
+  p.in_mul_h = in_mul_h; p.in_mul_w = in_mul_w;
+  p.Cin = Cin; p.Cout = Cout;
+  p.num_taps = num_taps; p.accumulate = accumulate;
+  p.out_sn = out_sn; p.out_sh = out_sh; p.out_sw = out_sw;
+  p.out = out; p.bias = bias; p.partials = partials;
+  for (int t = 0; t < num_taps; ++t) {
+    p.tap_dh[t] = (int16_t)tap_dh[t]; p.tap_dw[t] = (int16_t)tap_dw[t]; p.tap_w[t] = (int16_t)tap_w[t];
+  }
+  const bool vec_ok = (Cout & 3) == 0;
+  DCNN_REQUIRE(!vec_ok || ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (out_sn & 3) == 0 && (out_sh & 3) == 0 &&
+                           (out_sw & 3) == 0),
+               "dcnn_conv_tc: output must be 16-byte aligned with strides multiple of 4");
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_nhwc(&tmA, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
+  if (rc) return rc;
+  if (Cout <= 64) {
+    p.n_tiles = ceil_div(Cout, 64);
+    rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
+    if (rc) return rc;
+    return launch_conv<64, 4>(tmA, tmB, p, stream);
+  }
+  p.n_tiles = ceil_div(Cout, 128);
+  rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
+  if (rc) return rc;
+  return launch_conv<128, 3>(tmA, tmB, p, stream);
+}
+
+// dW[oc][tap_w*Cin + c] += sum_{n,oh,ow} dY[n,oh,ow,oc] * X[n, oh*mul_h + tap_dh, ow*mul_w + tap_dw, c]
+// dy: NHWC [N][OH][OW][Cout]; x: NHWC [N][H][W][Cin] (Cin % 32 == 0, Cout % 4 == 0).
+DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin,
+                           float* dw, int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh,
+                           const int* tap_dw, const int* tap_w, cudaStream_t stream) {
+  DCNN_REQUIRE(Cin % 32 == 0, "dcnn_wgrad_tc: Cin (%d) must be a multiple of 32", Cin);
+  DCNN_REQUIRE(Cout % 4 == 0, "dcnn_wgrad_tc: Cout (%d) must be a multiple of 4", Cout);
+  DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_wgrad_tc: bad tap count %d", num_taps);
+  WgradTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.N = N; p.OH = OH; p.OW = OW;
+  choose_box(N, OH, OW, kWPix, in_mul_h, in_mul_w, &p.bn, &p.bh, &p.bw);
+  p.tiles_n = ceil_div(N, p.bn); p.tiles_h = ceil_div(OH, p.bh); p.tiles_w = ceil_div(OW, p.bw);
+  p.in_mul_h = in_mul_h; p.in_mul_w = in_mul_w;
+  p.Cin = Cin; p.Cout = Cout; p.Ktot = Ktot; p.num_taps = num_taps;
+  p.dw = dw;
+  for (int t = 0; t < num_taps; ++t) {
+    p.tap_dh[t] = (int16_t)tap_dh[t]; p.tap_dw[t] = (int16_t)tap_dw[t]; p.tap_w[t] = (int16_t)tap_w[t];
+  }
+  p.oc_tiles = ceil_div(Cout, 128);
+  const bool wide = Cin >= 128;
+  p.c_tiles = ceil_div(Cin, wide ? 128 : 64);
+  const int pix_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
+  const int base = num_taps * p.oc_tiles * p.c_tiles;
+  int splits = ceil_div(2 * num_sms(), base);
+  if (splits > pix_tiles) splits = pix_tiles;
+  if (splits < 1) splits = 1;
+  // make every split non-empty
+  const int per = ceil_div(pix_tiles, splits);
+  splits = ceil_div(pix_tiles, per);
+  p.splits = splits;
+  CUtensorMap tmDY, tmX;
+  int rc = make_tmap_nhwc(&tmDY, dy, N, OH, OW, Cout, p.bn, p.bh, p.bw, 1, 1);
+  if (rc) return rc;
+  rc = make_tmap_nhwc(&tmX, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
+  if (rc) return rc;
+  if (wide) return launch_wgrad<128, 3>(tmDY, tmX, p, stream);
+  return launch_wgrad<64, 4>(tmDY, tmX, p, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// TMA semantics probe (used by the GPU tests): loads ONE 4-D box at the given start coordinate and dumps the raw
+// shared-memory image (swizzled, bn*bh*bw rows x 128 B) to `out`.
+namespace dcnn {
+__global__ void tma_probe_kernel(const __grid_constant__ CUtensorMap tm, int c0, int c1, int c2, int c3, int bytes,
+                                 float* out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t bar;
+  float* f = reinterpret_cast<float*>(smem);
+  for (int i = threadIdx.x; i < bytes / 4; i += blockDim.x) f[i] = -12345.f;
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    fence_barrier_init();
+  }
+  fence_proxy_async();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(&bar, bytes);
+    tma_load_4d(smem, &tm, &bar, c0, c1, c2, c3);
+  }
+  mbar_wait(&bar, 0);
+  for (int i = threadIdx.x; i < bytes / 4; i += blockDim.x) out[i] = f[i];
+}
+}  // namespace dcnn
+
+DCNN_API int dcnn_tma_probe(const float* x, int N, int H, int W, int C, int bn, int bh, int bw, int mul_h, int mul_w,
+                            int c0, int c1, int c2, int c3, float* out, cudaStream_t stream) {
+  CUtensorMap tm;
+  int rc = make_tmap_nhwc(&tm, x, N, H, W, C, bn, bh, bw, mul_h, mul_w);
+  if (rc) return rc;
+  const int bytes = bn * bh * bw * 128;
+  DCNN_CHECK_CUDA(cudaFuncSetAttribute(tma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes + 1024));
+  tma_probe_kernel<<<1, 128, bytes + 1024, stream>>>(tm, c0, c1, c2, c3, bytes, out);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}

@@ -1,0 +1,691 @@
+// BatchNorm / GroupNorm kernels for NHWC fp32 activations (x viewed as [M = N*H*W rows][C channels]).
+//
+// BatchNorm forward statistics are *partials*: per 128-row tile (sum, M2 about the tile mean) per channel plus a
+// row count per tile.  The tensor-core conv epilogue (conv_tc.cu) emits exactly this format, so for conv->BN the
+// statistics cost no extra pass over the activation; bn_colstats_kernel produces it for every other producer.
+// bn_finalize merges partials with Chan's parallel-variance formula in FP64 (numerically equivalent to the
+// reference's Welford kernel, batchnorm_ops.cu:108-155), updates the running statistics (unbiased variance,
+// momentum) and precomputes scale/shift so the apply pass is one FMA per element with ReLU / residual fused.
+// Backward = one reduce pass (ReLU mask folded in) + finalize + one apply pass (dx = g*k1 + x*k2 + k3).
+#include "common.cuh"
+
+namespace dcnn {
+
+constexpr int kStatRows = 128;  // rows per partial tile of the standalone statistics kernel
+
+// grid: (row_tiles, ceil(C/128)); block (32, 8): lane -> 4 channels (float4), ty strides rows.
+__global__ void __launch_bounds__(256) bn_colstats_kernel(const float* __restrict__ x, long long M, int C,
+                                                          int rows_per_tile, int tiles, float* __restrict__ partials) {
+  __shared__ float4 s_sum[8][32];
+  __shared__ float4 s_sq[8][32];
+  const int tile = blockIdx.x;
+  const int c = (blockIdx.y * 32 + threadIdx.x) * 4;
+  const long long r0 = (long long)tile * rows_per_tile;
+  const long long r1 = min(M, r0 + rows_per_tile);
+  const bool active = c < C;
+  float4 shift = make_float4(0, 0, 0, 0), s = shift, q = shift;
+  if (active) {
+    shift = ldg4(x + r0 * C + c);  // shifted sums: robust against |mean| >> std
+#pragma unroll 4
+    for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+      const float4 v = ldcs4(x + r * C + c);
+      const float dx = v.x - shift.x, dy = v.y - shift.y, dz = v.z - shift.z, dw = v.w - shift.w;
+      s.x += dx; s.y += dy; s.z += dz; s.w += dw;
+      q.x = fmaf(dx, dx, q.x); q.y = fmaf(dy, dy, q.y); q.z = fmaf(dz, dz, q.z); q.w = fmaf(dw, dw, q.w);
+    }
+  }
+  s_sum[threadIdx.y][threadIdx.x] = s;
+  s_sq[threadIdx.y][threadIdx.x] = q;
+  __syncthreads();
+  if (threadIdx.y == 0 && active) {
+    for (int i = 1; i < 8; ++i) {
+      const float4 a = s_sum[i][threadIdx.x], b = s_sq[i][threadIdx.x];
+      s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
+      q.x += b.x; q.y += b.y; q.z += b.z; q.w += b.w;
+    }
+    const float n = (float)(r1 - r0);
+    float* ps = partials + ((long long)tile * 2 + 0) * C + c;
+    float* pm = partials + ((long long)tile * 2 + 1) * C + c;
+    // sum = sum(d) + n*shift ; M2 = sum(d^2) - sum(d)^2/n
+    st4(ps, make_float4(s.x + n * shift.x, s.y + n * shift.y, s.z + n * shift.z, s.w + n * shift.w));
+    st4(pm, make_float4(q.x - s.x * s.x / n, q.y - s.y * s.y / n, q.z - s.z * s.z / n, q.w - s.w * s.w / n));
+    if (blockIdx.y == 0 && threadIdx.x == 0) partials[(long long)tiles * 2 * C + tile] = n;
+  }
+}
+
+// Scalar-channel variant for C % 4 != 0 (tiny layers only).
+__global__ void bn_colstats_scalar_kernel(const float* __restrict__ x, long long M, int C, int rows_per_tile, int tiles,
+                                          float* __restrict__ partials) {
+  const int tile = blockIdx.x;
+  const int c = blockIdx.y * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const long long r0 = (long long)tile * rows_per_tile, r1 = min(M, r0 + rows_per_tile);
+  const float shift = x[r0 * C + c];
+  float s = 0.f, q = 0.f;
+  for (long long r = r0; r < r1; ++r) {
+    const float d = x[r * C + c] - shift;
+    s += d; q = fmaf(d, d, q);
+  }
+  const float n = (float)(r1 - r0);
+  partials[((long long)tile * 2 + 0) * C + c] = s + n * shift;
+  partials[((long long)tile * 2 + 1) * C + c] = q - s * s / n;
+  if (c == 0) partials[(long long)tiles * 2 * C + tile] = n;
+}
+
+struct Moments { double n, mean, m2; };
+__device__ __forceinline__ Moments merge(Moments a, Moments b) {
+  if (b.n == 0) return a;
+  if (a.n == 0) return b;
+  Moments r;
+  r.n = a.n + b.n;
+  const double d = b.mean - a.mean;
+  r.mean = a.mean + d * (b.n / r.n);
+  r.m2 = a.m2 + b.m2 + d * d * (a.n * b.n / r.n);
+  return r;
+}
+
+// grid: ceil(C/32); block (32 channels, 32 tile lanes).
+// peers: optional cross-replica merge (sync-BN, K27): peer_moments[r] points at replica r's exported
+// (n, mean, m2)[C] triple array (double), readable over NVLink peer mapping; n_peers == 0 => local only.
+__global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restrict__ partials, int tiles, int C,
+                                                           float eps, float momentum, float* __restrict__ running_mean,
+                                                           float* __restrict__ running_var,
+                                                           const float* __restrict__ gamma,
+                                                           const float* __restrict__ beta, float* __restrict__ mean_out,
+                                                           float* __restrict__ invstd_out, float* __restrict__ scale_out,
+                                                           float* __restrict__ shift_out,
+                                                           double* __restrict__ export_moments) {
+  __shared__ double s_n[32][33], s_mean[32][33], s_m2[32][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  Moments acc{0, 0, 0};
+  if (c < C) {
+    const float* counts = partials + (long long)tiles * 2 * C;
+    for (int t = threadIdx.y; t < tiles; t += 32) {
+      const double n = counts[t];
+      if (n <= 0) continue;
+      const double s = partials[((long long)t * 2 + 0) * C + c];
+      const double m2 = partials[((long long)t * 2 + 1) * C + c];
+      acc = merge(acc, Moments{n, s / n, m2});
+    }
+  }
+  s_n[threadIdx.y][threadIdx.x] = acc.n;
+  s_mean[threadIdx.y][threadIdx.x] = acc.mean;
+  s_m2[threadIdx.y][threadIdx.x] = acc.m2;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    for (int i = 1; i < 32; ++i)
+      acc = merge(acc, Moments{s_n[i][threadIdx.x], s_mean[i][threadIdx.x], s_m2[i][threadIdx.x]});
+    if (export_moments != nullptr) {
+      export_moments[0 * C + c] = acc.n;
+      export_moments[1 * C + c] = acc.mean;
+      export_moments[2 * C + c] = acc.m2;
+      return;  // the sync variant finishes in bn_finalize_sync_kernel after the peer exchange
+    }
+    const double var = acc.n > 0 ? acc.m2 / acc.n : 0.0;  // biased: used to normalise
+    const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+    const float mean = (float)acc.mean;
+    mean_out[c] = mean;
+    invstd_out[c] = invstd;
+    const float sc = gamma ? gamma[c] * invstd : invstd;
+    scale_out[c] = sc;
+    shift_out[c] = (beta ? beta[c] : 0.f) - mean * sc;
+    if (running_mean != nullptr) {
+      const double unbiased = acc.n > 1 ? acc.m2 / (acc.n - 1) : var;
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+  }
+}
+
+// Cross-replica finish: merge every replica's exported moments (peer pointers over NVLink / NVSwitch).
+__global__ void bn_finalize_sync_kernel(const double* const* __restrict__ peer_moments, int n_peers, int C, float eps,
+                                        float momentum, float* __restrict__ running_mean,
+                                        float* __restrict__ running_var, const float* __restrict__ gamma,
+                                        const float* __restrict__ beta, float* __restrict__ mean_out,
+                                        float* __restrict__ invstd_out, float* __restrict__ scale_out,
+                                        float* __restrict__ shift_out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  Moments acc{0, 0, 0};
+  for (int r = 0; r < n_peers; ++r) {
+    const double* pm = peer_moments[r];
+    acc = merge(acc, Moments{pm[0 * C + c], pm[1 * C + c], pm[2 * C + c]});
+  }
+  const double var = acc.n > 0 ? acc.m2 / acc.n : 0.0;
+  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float mean = (float)acc.mean;
+  mean_out[c] = mean;
+  invstd_out[c] = invstd;
+  const float sc = gamma ? gamma[c] * invstd : invstd;
+  scale_out[c] = sc;
+  shift_out[c] = (beta ? beta[c] : 0.f) - mean * sc;
+  if (running_mean != nullptr) {
+    const double unbiased = acc.n > 1 ? acc.m2 / (acc.n - 1) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+  }
+}
+
+// Eval-mode scale/shift from running statistics.
+__global__ void bn_eval_coeffs_kernel(const float* __restrict__ rm, const float* __restrict__ rv,
+                                      const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int C,
+                                      float* __restrict__ scale, float* __restrict__ shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float invstd = rsqrtf(rv[c] + eps);
+  const float sc = gamma ? gamma[c] * invstd : invstd;
+  scale[c] = sc;
+  shift[c] = (beta ? beta[c] : 0.f) - rm[c] * sc;
+}
+
+// y = x*scale[c] + shift[c] (+ residual) (ReLU).  float4 over channels; C % 4 == 0.
+template <bool RES, bool RELU>
+__global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, const float* __restrict__ scale,
+                                                       const float* __restrict__ shift, const float* __restrict__ res,
+                                                       float* __restrict__ y, long long total4, int C4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C4) * 4;
+    const float4 v = ldcs4(x + i * 4);
+    const float4 sc = ldg4(scale + c), sf = ldg4(shift + c);
+    float4 o;
+    o.x = fmaf(v.x, sc.x, sf.x); o.y = fmaf(v.y, sc.y, sf.y); o.z = fmaf(v.z, sc.z, sf.z); o.w = fmaf(v.w, sc.w, sf.w);
+    if (RES) {
+      const float4 r = ldcs4(res + i * 4);
+      o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+    }
+    if (RELU) {
+      o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+    }
+    st4(y + i * 4, o);
+  }
+}
+
+__global__ void bn_apply_scalar_kernel(const float* __restrict__ x, const float* __restrict__ scale,
+                                       const float* __restrict__ shift, const float* __restrict__ res,
+                                       float* __restrict__ y, long long total, int C, int relu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    float o = fmaf(x[i], scale[c], shift[c]);
+    if (res) o += res[i];
+    if (relu) o = fmaxf(o, 0.f);
+    y[i] = o;
+  }
+}
+
+// Backward reduce: per row tile, per channel: (sum g, sum g*xhat) with g = dout * (out > 0 if RELU).
+// Same grid/block shape as bn_colstats_kernel; partials [tiles][2][C].
+template <bool RELU>
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restrict__ dout, const float* __restrict__ x,
+                                                            const float* __restrict__ out,
+                                                            const float* __restrict__ mean,
+                                                            const float* __restrict__ invstd, long long M, int C,
+                                                            int rows_per_tile, float* __restrict__ partials) {
+  __shared__ float4 s_a[8][32];
+  __shared__ float4 s_b[8][32];
+  const int tile = blockIdx.x;
+  const int c = (blockIdx.y * 32 + threadIdx.x) * 4;
+  const long long r0 = (long long)tile * rows_per_tile, r1 = min(M, r0 + rows_per_tile);
+  const bool active = c < C;
+  float4 a = make_float4(0, 0, 0, 0), b = a;
+  if (active) {
+    const float4 mu = ldg4(mean + c), is = ldg4(invstd + c);
+#pragma unroll 4
+    for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+      float4 g = ldg4(dout + r * C + c);
+      const float4 v = ldg4(x + r * C + c);
+      if (RELU) {
+        const float4 o = ldg4(out + r * C + c);
+        g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
+        g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+      }
+      a.x += g.x; a.y += g.y; a.z += g.z; a.w += g.w;
+      b.x = fmaf(g.x, (v.x - mu.x) * is.x, b.x); b.y = fmaf(g.y, (v.y - mu.y) * is.y, b.y);
+      b.z = fmaf(g.z, (v.z - mu.z) * is.z, b.z); b.w = fmaf(g.w, (v.w - mu.w) * is.w, b.w);
+    }
+  }
+  s_a[threadIdx.y][threadIdx.x] = a;
+  s_b[threadIdx.y][threadIdx.x] = b;
+  __syncthreads();
+  if (threadIdx.y == 0 && active) {
+    for (int i = 1; i < 8; ++i) {
+      const float4 p = s_a[i][threadIdx.x], q = s_b[i][threadIdx.x];
+      a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
+      b.x += q.x; b.y += q.y; b.z += q.z; b.w += q.w;
+    }
+    st4(partials + ((long long)tile * 2 + 0) * C + c, a);
+    st4(partials + ((long long)tile * 2 + 1) * C + c, b);
+  }
+}
+
+__global__ void bn_bwd_reduce_scalar_kernel(const float* __restrict__ dout, const float* __restrict__ x,
+                                            const float* __restrict__ out, const float* __restrict__ mean,
+                                            const float* __restrict__ invstd, long long M, int C, int rows_per_tile,
+                                            float* __restrict__ partials, int relu) {
+  const int tile = blockIdx.x;
+  const int c = blockIdx.y * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const long long r0 = (long long)tile * rows_per_tile, r1 = min(M, r0 + rows_per_tile);
+  float a = 0.f, b = 0.f;
+  for (long long r = r0; r < r1; ++r) {
+    float g = dout[r * C + c];
+    if (relu && !(out[r * C + c] > 0.f)) g = 0.f;
+    a += g;
+    b = fmaf(g, (x[r * C + c] - mean[c]) * invstd[c], b);
+  }
+  partials[((long long)tile * 2 + 0) * C + c] = a;
+  partials[((long long)tile * 2 + 1) * C + c] = b;
+}
+
+// Sum backward partials (FP64), accumulate dgamma/dbeta, emit apply coefficients k1,k2,k3.
+// Optional cross-replica: export (sum_dy, sum_dy_xhat) and finish in bn_bwd_finalize_sync_kernel.
+__global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __restrict__ partials, int tiles, int C,
+                                                               double count, const float* __restrict__ mean,
+                                                               const float* __restrict__ invstd,
+                                                               const float* __restrict__ gamma,
+                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                               float* __restrict__ k1, float* __restrict__ k2,
+                                                               float* __restrict__ k3,
+                                                               double* __restrict__ export_sums) {
+  __shared__ double s_a[32][33], s_b[32][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  double a = 0, b = 0;
+  if (c < C)
+    for (int t = threadIdx.y; t < tiles; t += 32) {
+      a += partials[((long long)t * 2 + 0) * C + c];
+      b += partials[((long long)t * 2 + 1) * C + c];
+    }
+  s_a[threadIdx.y][threadIdx.x] = a;
+  s_b[threadIdx.y][threadIdx.x] = b;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    for (int i = 1; i < 32; ++i) { a += s_a[i][threadIdx.x]; b += s_b[i][threadIdx.x]; }
+    if (dgamma != nullptr) {  // local contribution; the DP all-reduce sums replicas
+      dgamma[c] += (float)b;
+      dbeta[c] += (float)a;
+    }
+    if (export_sums != nullptr) {
+      export_sums[0 * C + c] = a;
+      export_sums[1 * C + c] = b;
+      export_sums[2 * C + c] = count;
+      return;
+    }
+    const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
+    const float ma = (float)(a / count), mb = (float)(b / count);
+    // dx = (g - ma - xhat*mb) * sc,  xhat = (x - mean)*invstd
+    k1[c] = sc;
+    k2[c] = -invstd[c] * mb * sc;
+    k3[c] = (mean[c] * invstd[c] * mb - ma) * sc;
+  }
+}
+
+__global__ void bn_bwd_finalize_sync_kernel(const double* const* __restrict__ peer_sums, int n_peers, int C,
+                                            const float* __restrict__ mean, const float* __restrict__ invstd,
+                                            const float* __restrict__ gamma, float* __restrict__ k1,
+                                            float* __restrict__ k2, float* __restrict__ k3) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double a = 0, b = 0, n = 0;
+  for (int r = 0; r < n_peers; ++r) {
+    const double* p = peer_sums[r];
+    a += p[0 * C + c]; b += p[1 * C + c]; n += p[2 * C + c];
+  }
+  const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
+  const float ma = (float)(a / n), mb = (float)(b / n);
+  k1[c] = sc;
+  k2[c] = -invstd[c] * mb * sc;
+  k3[c] = (mean[c] * invstd[c] * mb - ma) * sc;
+}
+
+// dx = g*k1 + x*k2 + k3 with g = dout masked by (out > 0); optionally also writes the masked g (the gradient
+// that flows into the residual shortcut).
+template <bool RELU, bool MASKED>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ dout, const float* __restrict__ x,
+                                                           const float* __restrict__ out, const float* __restrict__ k1,
+                                                           const float* __restrict__ k2, const float* __restrict__ k3,
+                                                           float* __restrict__ dx, float* __restrict__ masked,
+                                                           long long total4, int C4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C4) * 4;
+    float4 g = ldcs4(dout + i * 4);
+    const float4 v = ldcs4(x + i * 4);
+    if (RELU) {
+      const float4 o = ldcs4(out + i * 4);
+      g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
+      g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+    }
+    const float4 a = ldg4(k1 + c), b = ldg4(k2 + c), d = ldg4(k3 + c);
+    float4 r;
+    r.x = fmaf(g.x, a.x, fmaf(v.x, b.x, d.x)); r.y = fmaf(g.y, a.y, fmaf(v.y, b.y, d.y));
+    r.z = fmaf(g.z, a.z, fmaf(v.z, b.z, d.z)); r.w = fmaf(g.w, a.w, fmaf(v.w, b.w, d.w));
+    st4(dx + i * 4, r);
+    if (MASKED) st4(masked + i * 4, g);
+  }
+}
+
+__global__ void bn_bwd_apply_scalar_kernel(const float* __restrict__ dout, const float* __restrict__ x,
+                                           const float* __restrict__ out, const float* __restrict__ k1,
+                                           const float* __restrict__ k2, const float* __restrict__ k3,
+                                           float* __restrict__ dx, float* __restrict__ masked, long long total, int C,
+                                           int relu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    float g = dout[i];
+    if (relu && !(out[i] > 0.f)) g = 0.f;
+    dx[i] = fmaf(g, k1[c], fmaf(x[i], k2[c], k3[c]));
+    if (masked) masked[i] = g;
+  }
+}
+
+// db[c] += sum over rows of dy[row][c]   (bias gradient; accumulates like cudnnConvolutionBackwardBias beta=1)
+__global__ void __launch_bounds__(256) colsum_accum_kernel(const float* __restrict__ dy, long long M, int C,
+                                                           int rows_per_block, float* __restrict__ db) {
+  __shared__ float s[8][33];
+  const int c = blockIdx.y * 32 + threadIdx.x;
+  const long long r0 = (long long)blockIdx.x * rows_per_block, r1 = min(M, r0 + rows_per_block);
+  float a = 0.f;
+  if (c < C)
+    for (long long r = r0 + threadIdx.y; r < r1; r += 8) a += __ldg(dy + r * C + c);
+  s[threadIdx.y][threadIdx.x] = a;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    for (int i = 1; i < 8; ++i) a += s[i][threadIdx.x];
+    atomicAdd(db + c, a);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ GroupNorm
+// One CTA per (n, group).  The group's HW x Cg slice is read twice (stats, then apply) - the second read hits L2.
+__global__ void __launch_bounds__(256) gn_forward_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                         const float* __restrict__ gamma,
+                                                         const float* __restrict__ beta, float* __restrict__ mean_out,
+                                                         float* __restrict__ invstd_out, int HW, int C, int G,
+                                                         float eps) {
+  __shared__ float red[2][8];
+  __shared__ float s_stat[2];
+  const int n = blockIdx.x / G, g = blockIdx.x % G;
+  const int Cg = C / G;
+  const long long base = (long long)n * HW * C + (long long)g * Cg;
+  const int cnt = HW * Cg;
+  const float shift = x[base];
+  float s = 0.f, q = 0.f;
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const int p = i / Cg, c = i - p * Cg;
+    const float d = x[base + (long long)p * C + c] - shift;
+    s += d; q = fmaf(d, d, q);
+  }
+  s = warp_sum(s); q = warp_sum(q);
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s; red[1][threadIdx.x >> 5] = q; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += red[0][i]; b += red[1][i]; }
+    const float mean_d = a / cnt;
+    const float var = fmaxf(b / cnt - mean_d * mean_d, 0.f);
+    s_stat[0] = mean_d + shift;
+    s_stat[1] = rsqrtf(var + eps);
+    mean_out[blockIdx.x] = s_stat[0];
+    invstd_out[blockIdx.x] = s_stat[1];
+  }
+  __syncthreads();
+  const float mean = s_stat[0], invstd = s_stat[1];
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const int p = i / Cg, c = i - p * Cg;
+    const long long idx = base + (long long)p * C + c;
+    float v = (x[idx] - mean) * invstd;
+    if (gamma) v = fmaf(v, gamma[g * Cg + c], beta[g * Cg + c]);
+    y[idx] = v;
+  }
+}
+
+// dgamma/dbeta accumulate (ref groupnorm_ops.cu:175-176 uses +=); dx per group.
+__global__ void __launch_bounds__(256) gn_backward_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                          const float* __restrict__ mean,
+                                                          const float* __restrict__ invstd,
+                                                          const float* __restrict__ gamma, float* __restrict__ dx,
+                                                          int HW, int C, int G) {
+  __shared__ float red[2][8];
+  __shared__ float s_stat[2];
+  const int n = blockIdx.x / G, g = blockIdx.x % G;
+  const int Cg = C / G;
+  const long long base = (long long)n * HW * C + (long long)g * Cg;
+  const int cnt = HW * Cg;
+  const float mu = mean[blockIdx.x], is = invstd[blockIdx.x];
+  float s1 = 0.f, s2 = 0.f;
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const int p = i / Cg, c = i - p * Cg;
+    const long long idx = base + (long long)p * C + c;
+    const float gy = dy[idx] * (gamma ? gamma[g * Cg + c] : 1.f);
+    s1 += gy;
+    s2 = fmaf(gy, (x[idx] - mu) * is, s2);
+  }
+  s1 = warp_sum(s1); s2 = warp_sum(s2);
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s1; red[1][threadIdx.x >> 5] = s2; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { a += red[0][i]; b += red[1][i]; }
+    s_stat[0] = a / cnt; s_stat[1] = b / cnt;
+  }
+  __syncthreads();
+  const float m1 = s_stat[0], m2 = s_stat[1];
+  for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const int p = i / Cg, c = i - p * Cg;
+    const long long idx = base + (long long)p * C + c;
+    const float gy = dy[idx] * (gamma ? gamma[g * Cg + c] : 1.f);
+    const float xh = (x[idx] - mu) * is;
+    dx[idx] = (gy - m1 - xh * m2) * is;
+  }
+}
+
+// dgamma[c] += sum dy*xhat ; dbeta[c] += sum dy   (per channel over N, HW)
+__global__ void __launch_bounds__(256) gn_param_grad_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                            const float* __restrict__ mean,
+                                                            const float* __restrict__ invstd, float* __restrict__ dgamma,
+                                                            float* __restrict__ dbeta, int N, int HW, int C, int G) {
+  __shared__ float red[2][8];
+  const int c = blockIdx.x;
+  const int g = c / (C / G);
+  float a = 0.f, b = 0.f;
+  const int total = N * HW;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int n = i / HW;
+    const long long idx = (long long)i * C + c;
+    const float d = dy[idx];
+    a += d;
+    b = fmaf(d, (x[idx] - mean[n * G + g]) * invstd[n * G + g], b);
+  }
+  a = warp_sum(a); b = warp_sum(b);
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = a; red[1][threadIdx.x >> 5] = b; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float sa = 0.f, sb = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { sa += red[0][i]; sb += red[1][i]; }
+    dbeta[c] += sa;
+    dgamma[c] += sb;
+  }
+}
+
+static int stat_rows_per_tile(long long M, int* tiles) {
+  // enough tiles to fill the machine, at least kStatRows rows each
+  long long target = (long long)num_sms() * 8;
+  long long rows = (M + target - 1) / target;
+  if (rows < kStatRows) rows = kStatRows;
+  rows = (rows + 7) / 8 * 8;
+  *tiles = (int)((M + rows - 1) / rows);
+  return (int)rows;
+}
+
+}  // namespace dcnn
+using namespace dcnn;
+
+DCNN_API int dcnn_bn_stat_tiles(long long M) {
+  int tiles;
+  stat_rows_per_tile(M, &tiles);
+  return tiles;
+}
+
+// partials must hold tiles*(2*C+1) floats with tiles = dcnn_bn_stat_tiles(M)
+DCNN_API int dcnn_bn_colstats(const float* x, long long M, int C, float* partials, cudaStream_t stream) {
+  int tiles;
+  const int rows = stat_rows_per_tile(M, &tiles);
+  if ((C & 3) == 0) {
+    dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
+    bn_colstats_kernel<<<grid, block, 0, stream>>>(x, M, C, rows, tiles, partials);
+  } else {
+    dim3 grid(tiles, ceil_div(C, 32));
+    bn_colstats_scalar_kernel<<<grid, 32, 0, stream>>>(x, M, C, rows, tiles, partials);
+  }
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
+                              float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
+                              float* scale, float* shift, double* export_moments, cudaStream_t stream) {
+  dim3 block(32, 32);
+  bn_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
+                                                           running_var, gamma, beta, mean, invstd, scale, shift,
+                                                           export_moments);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_finalize_sync(const double* const* peer_moments, int n_peers, int C, float eps, float momentum,
+                                   float* running_mean, float* running_var, const float* gamma, const float* beta,
+                                   float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream) {
+  bn_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(peer_moments, n_peers, C, eps, momentum, running_mean,
+                                                               running_var, gamma, beta, mean, invstd, scale, shift);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_eval_coeffs(const float* rm, const float* rv, const float* gamma, const float* beta, float eps,
+                                 int C, float* scale, float* shift, cudaStream_t stream) {
+  bn_eval_coeffs_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(rm, rv, gamma, beta, eps, C, scale, shift);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_apply(const float* x, const float* scale, const float* shift, const float* residual, float* y,
+                           long long M, int C, int relu, cudaStream_t stream) {
+  const long long total = M * C;
+  if ((C & 3) == 0) {
+    const long long t4 = total / 4;
+    const int grid = ew_grid(t4, 256);
+    const int C4 = C / 4;
+    if (residual && relu) bn_apply_kernel<true, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C4);
+    else if (residual) bn_apply_kernel<true, false><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C4);
+    else if (relu) bn_apply_kernel<false, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C4);
+    else bn_apply_kernel<false, false><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C4);
+  } else {
+    bn_apply_scalar_kernel<<<ew_grid(total, 256), 256, 0, stream>>>(x, scale, shift, residual, y, total, C, relu);
+  }
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean,
+                                const float* invstd, long long M, int C, int relu, float* partials,
+                                cudaStream_t stream) {
+  int tiles;
+  const int rows = stat_rows_per_tile(M, &tiles);
+  if ((C & 3) == 0) {
+    dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
+    if (relu) bn_bwd_reduce_kernel<true><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    else bn_bwd_reduce_kernel<false><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+  } else {
+    dim3 grid(tiles, ceil_div(C, 32));
+    bn_bwd_reduce_scalar_kernel<<<grid, 32, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials, relu);
+  }
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
+                                  const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1,
+                                  float* k2, float* k3, double* export_sums, cudaStream_t stream) {
+  dim3 block(32, 32);
+  bn_bwd_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma, dgamma,
+                                                               dbeta, k1, k2, k3, export_sums);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, int n_peers, int C, const float* mean,
+                                       const float* invstd, const float* gamma, float* k1, float* k2, float* k3,
+                                       cudaStream_t stream) {
+  bn_bwd_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(peer_sums, n_peers, C, mean, invstd, gamma, k1, k2,
+                                                                   k3);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* out, const float* k1, const float* k2,
+                               const float* k3, float* dx, float* masked, long long M, int C, int relu,
+                               cudaStream_t stream) {
+  const long long total = M * C;
+  if ((C & 3) == 0) {
+    const long long t4 = total / 4;
+    const int grid = ew_grid(t4, 256);
+    const int C4 = C / 4;
+    if (relu && masked)
+      bn_bwd_apply_kernel<true, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else if (relu)
+      bn_bwd_apply_kernel<true, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else if (masked)
+      bn_bwd_apply_kernel<false, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else
+      bn_bwd_apply_kernel<false, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+  } else {
+    bn_bwd_apply_scalar_kernel<<<ew_grid(total, 256), 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, total, C,
+                                                                       relu);
+  }
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, cudaStream_t stream) {
+  long long target = (long long)num_sms() * 4;
+  long long rows = (M + target - 1) / target;
+  if (rows < 64) rows = 64;
+  dim3 grid(ceil_div(M, rows), ceil_div(C, 32)), block(32, 8);
+  colsum_accum_kernel<<<grid, block, 0, stream>>>(dy, M, C, (int)rows, db);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_gn_forward(const float* x, float* y, const float* gamma, const float* beta, float* mean,
+                             float* invstd, int N, int HW, int C, int G, float eps, cudaStream_t stream) {
+  gn_forward_kernel<<<N * G, 256, 0, stream>>>(x, y, gamma, beta, mean, invstd, HW, C, G, eps);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_gn_backward(const float* dy, const float* x, const float* mean, const float* invstd,
+                              const float* gamma, float* dgamma, float* dbeta, float* dx, int N, int HW, int C, int G,
+                              cudaStream_t stream) {
+  if (dgamma != nullptr) {
+    gn_param_grad_kernel<<<C, 256, 0, stream>>>(dy, x, mean, invstd, dgamma, dbeta, N, HW, C, G);
+    DCNN_CHECK_LAUNCH();
+    DCNN_COUNT_LAUNCH(1);
+  }
+  gn_backward_kernel<<<N * G, 256, 0, stream>>>(dy, x, mean, invstd, gamma, dx, HW, C, G);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}

@@ -442,7 +442,7 @@ class BatchNormLayer(Layer):
         if stats is None:
             stats = ops.bn_stats(x)
         mean, invstd = ops.bn_finalize(stats, self.epsilon, self.momentum, self.running_mean,
-                                       self.running_var, sync=self.sync)
+                                       self.running_var, sync=self.sync, gamma=self.gamma, beta=self.beta)
         out = ops.bn_apply(x, mean, invstd, self.gamma, self.beta, residual, relu)
         self._cache[micro_batch_id] = (x, mean, invstd, out if relu else None, relu)
         return out

@@ -20,6 +20,26 @@ class Optimizer:
         self.params: List[torch.Tensor] = []
         self.grads: List[torch.Tensor] = []
         self._table = None  # backend-specific cached pointer table
+        #: optional device tensor {lr, bias_corr1, bias_corr2}: step-varying scalars read from memory so
+        #: a captured CUDA graph of the whole training step can be replayed (see train.TrainStep)
+        self.hyper = None
+        self._hyper_host = None
+
+    def enable_device_hyper(self, device):
+        import torch as _t
+        self.hyper = _t.zeros(4, device=device, dtype=_t.float32)
+        self._hyper_host = _t.zeros(4, dtype=_t.float32).pin_memory() if _t.cuda.is_available() else _t.zeros(4)
+
+    def _hyper_values(self):
+        return (self.learning_rate, 1.0, 1.0)
+
+    def push_hyper(self):
+        """Stage this step's scalars on the device (stream-ordered, outside any captured graph)."""
+        if self.hyper is None:
+            return
+        lr, b1, b2 = self._hyper_values()
+        self._hyper_host[0], self._hyper_host[1], self._hyper_host[2] = lr, b1, b2
+        self.hyper.copy_(self._hyper_host, non_blocking=True)
 
     def attach(self, params: Sequence[torch.Tensor], grads: Sequence[torch.Tensor]):
         if len(params) != len(grads):
@@ -29,6 +49,9 @@ class Optimizer:
         self.on_attach()
 
     def on_attach(self):
+        pass
+
+    def advance(self):
         pass
 
     def update(self, zero_grads: bool = False):
@@ -75,7 +98,7 @@ class SGD(Optimizer):
         if not self.params:
             return
         ops.sgd_update(self.params, self.grads, self.velocities, self.learning_rate, self.momentum,
-                       zero_grads=zero_grads)
+                       zero_grads=zero_grads, hyper=self.hyper)
 
     def name(self):
         return "SGD"
@@ -113,6 +136,14 @@ class Adam(Optimizer):
     def bias_corrections(self):
         return 1.0 - self.beta1 ** self.t, 1.0 - self.beta2 ** self.t
 
+    def _hyper_values(self):
+        bc1, bc2 = self.bias_corrections()
+        return (self.learning_rate, bc1, bc2)
+
+    def advance(self):
+        """Advance the step counter without launching (used when a captured graph is replayed)."""
+        self.t += 1
+
     def update(self, zero_grads: bool = False):
         if not self.params:
             return
@@ -120,7 +151,7 @@ class Adam(Optimizer):
         bc1, bc2 = self.bias_corrections()
         ops.adam_update(self.params, self.grads, self.m, self.v, self.learning_rate, self.beta1,
                         self.beta2, self.epsilon, bc1, bc2, self.weight_decay,
-                        self.decouple_weight_decay, zero_grads=zero_grads)
+                        self.decouple_weight_decay, zero_grads=zero_grads, hyper=self.hyper)
 
     def name(self):
         return "AdamW" if self.decouple_weight_decay else "Adam"

@@ -47,9 +47,11 @@ for _n in _OPS:
     globals()[_n] = _dispatch(_n)
 
 
-def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None):
+def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None, gamma=None, beta=None):
+    """-> (mean, invstd).  On CUDA ``invstd`` is an opaque (invstd, scale, shift) bundle: the finalize kernel
+    also precomputes the fused apply coefficients from gamma/beta."""
     be = _cpu if isinstance(stats, _cpu.CpuStats) else _cuda_backend()
-    return be.bn_finalize(stats, eps, momentum, running_mean, running_var, sync=sync)
+    return be.bn_finalize(stats, eps, momentum, running_mean, running_var, sync=sync, gamma=gamma, beta=beta)
 
 
 def loss_forward_backward(kind, pred, target, param=0.0, want_grad=True):

@@ -82,7 +82,7 @@ def bn_stats(x):
     return CpuStats(mean, var, n)
 
 
-def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None):
+def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None, gamma=None, beta=None):
     """Turn partial statistics into (mean, invstd) and update running stats.
 
     Normalisation uses the biased variance, the running variance gets the unbiased one
@@ -209,11 +209,14 @@ def avgpool_backward(dy, x_shape, k, stride, pad):
     n, c, h, w = x_shape
     ones = torch.ones(c, 1, k[0], k[1], dtype=dy.dtype, device=dy.device) / (k[0] * k[1])
     oh, ow = dy.shape[2:]
-    dx = F.conv_transpose2d(dy, ones, stride=stride, padding=pad, groups=c)
-    # conv_transpose output may be smaller than the input when the window does not tile it
-    if dx.shape[2] != h or dx.shape[3] != w:
+    nat_h = (oh - 1) * stride[0] - 2 * pad[0] + k[0]
+    nat_w = (ow - 1) * stride[1] - 2 * pad[1] + k[1]
+    op = (max(0, min(h - nat_h, stride[0] - 1)), max(0, min(w - nat_w, stride[1] - 1)))
+    dx = F.conv_transpose2d(dy, ones, stride=stride, padding=pad, output_padding=op, groups=c)
+    if dx.shape[2] != h or dx.shape[3] != w:  # rows/cols no window reaches get zero gradient
         full = torch.zeros(x_shape, dtype=dy.dtype, device=dy.device)
-        full[:, :, : dx.shape[2], : dx.shape[3]] = dx[:, :, :h, :w]
+        hh, ww = min(h, dx.shape[2]), min(w, dx.shape[3])
+        full[:, :, :hh, :ww] = dx[:, :, :hh, :ww]
         dx = full
     return dx
 
@@ -331,7 +334,7 @@ def loss_forward_backward(kind, pred, target, param=0.0, want_grad=True):
 # ----------------------------------------------------------------------------------------------
 # optimizers (multi-tensor semantics: lists of tensors updated in place)
 # ----------------------------------------------------------------------------------------------
-def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False):
+def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False, hyper=None):
     for i, (p, g) in enumerate(zip(params, grads)):
         if momentum > 0:
             v = velocities[i]
@@ -344,7 +347,7 @@ def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False):
 
 
 def adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_decay, decoupled,
-                zero_grads=False):
+                zero_grads=False, hyper=None):
     """ref adam_kernels.cu:24-60"""
     for p, g, m, v in zip(params, grads, ms, vs):
         m.mul_(beta1).add_(g, alpha=1 - beta1)

@@ -1,0 +1,560 @@
+"""CUDA backend of the functional op set: thin wrappers that allocate outputs with torch and launch the
+hand-written sm_100a kernels of libdcnn_b200.so on the current torch stream.  No cuDNN / cuBLAS / ATen compute
+kernel runs on these paths (torch is used for allocation, views and stream/graph plumbing only).
+
+Layout contract: 4-D activations are logical NCHW stored channels-last (NHWC); conv weights are logical OIHW
+stored O-H-W-I.  Tensor-core (tcgen05) kernels are used whenever the GEMM-K channel count is a multiple of 32;
+everything else takes the exact-FP32 CUDA-core kernels.  ``DCNN_DISABLE_TC=1`` forces the CUDA-core path (the
+"FP32-exact mode" for bit-tight tests)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+from .._lib import D, F, I, LL, P, ULL, check, lib
+
+NAME = "cuda"
+CL = torch.channels_last
+
+_ACT = {"relu": 0, "leaky_relu": 1, "elu": 2, "sigmoid": 3, "tanh": 4, "linear": 5}
+
+
+def _stream():
+    return P(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t: Optional[torch.Tensor]):
+    return P(t.data_ptr()) if t is not None else P(0)
+
+
+def tc_enabled() -> bool:
+    return os.environ.get("DCNN_DISABLE_TC", "0") != "1"
+
+
+def tc_strided_enabled() -> bool:
+    return os.environ.get("DCNN_DISABLE_TC_STRIDED", "0") != "1"
+
+
+def as_nhwc(x: torch.Tensor) -> torch.Tensor:
+    if x.dtype != torch.float32:
+        x = x.float()
+    return x.contiguous(memory_format=CL)
+
+
+def _empty_nhwc(n, c, h, w, device):
+    return torch.empty((n, c, h, w), device=device, dtype=torch.float32, memory_format=CL)
+
+
+_TAPS = {}
+
+
+def _taps(key, gen):
+    t = _TAPS.get(key)
+    if t is None:
+        dh, dw, wi = gen()
+        n = len(dh)
+        t = (n, (I * n)(*dh), (I * n)(*dw), (I * n)(*wi))
+        _TAPS[key] = t
+    return t
+
+
+class CudaStats:
+    """BN partial statistics: ``partials`` = [tiles][2][C] (sum, centred M2) followed by [tiles] row counts."""
+    __slots__ = ("partials", "tiles", "C", "count")
+
+    def __init__(self, partials, tiles, C_, count):
+        self.partials, self.tiles, self.C, self.count = partials, tiles, C_, count
+
+
+# ================================================================================== convolution
+def _conv_tc(x, N, H, W, Cin, w, Cout, Ktot, out, out_off, sn, sh, sw, OH, OW, mul_h, mul_w, taps, bias,
+             accumulate, partials):
+    n, dh, dw, wi = taps
+    check(lib().dcnn_conv_tc(_p(x), I(N), I(H), I(W), I(Cin), _p(w), I(Cout), I(Ktot),
+                             P(out.data_ptr() + 4 * out_off), LL(sn), LL(sh), LL(sw), I(OH), I(OW), I(mul_h),
+                             I(mul_w), I(n), dh, dw, wi, _p(bias), I(1 if accumulate else 0), _p(partials),
+                             _stream()), "dcnn_conv_tc")
+
+
+def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
+    x = as_nhwc(x)
+    N, Cin, H, W = x.shape
+    Cout, _, R, S = w.shape
+    assert w.is_contiguous(memory_format=CL), "conv weights must be stored O-H-W-I (channels_last)"
+    sh_, sw_ = stride
+    ph, pw = pad
+    OH = (H + 2 * ph - R) // sh_ + 1
+    OW = (W + 2 * pw - S) // sw_ + 1
+    y = _empty_nhwc(N, Cout, OH, OW, x.device)
+    use_tc = tc_enabled() and Cin % 32 == 0 and R * S <= 49 and \
+        ((sh_ == 1 and sw_ == 1) or (tc_strided_enabled() and sh_ <= 8 and sw_ <= 8))
+    if use_tc:
+        taps = _taps(("f", R, S, ph, pw), lambda: (
+            [r - ph for r in range(R) for s in range(S)],
+            [s - pw for r in range(R) for s in range(S)],
+            [r * S + s for r in range(R) for s in range(S)]))
+        stats = None
+        partials = None
+        if want_stats:
+            tiles = lib().dcnn_conv_tc_m_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_))
+            partials = torch.empty(tiles * (2 * Cout + 1), device=x.device, dtype=torch.float32)
+            stats = CudaStats(partials, tiles, Cout, N * OH * OW)
+        _conv_tc(x, N, H, W, Cin, w, Cout, R * S * Cin, y, 0, OH * OW * Cout, OW * Cout, Cout, OH, OW, sh_, sw_,
+                 taps, bias, False, partials)
+        return y, stats
+    check(lib().dcnn_conv_fprop_simt(_p(x), _p(w), _p(bias), _p(y), I(N), I(H), I(W), I(Cin), I(Cout), I(R), I(S),
+                                     I(sh_), I(sw_), I(ph), I(pw), _stream()), "dcnn_conv_fprop_simt")
+    return y, (bn_stats(y) if want_stats else None)
+
+
+def _dgrad_weights(w):
+    """W[K][R][S][C] -> Wt[C][R][S][K], both spatial axes flipped (K-major over the dY channels)."""
+    K, Cc, R, S = w.shape
+    wt = torch.empty(Cc * R * S * K, device=w.device, dtype=torch.float32)
+    check(lib().dcnn_weight_dgrad_layout(_p(w), _p(wt), I(K), I(R), I(S), I(Cc), _stream()), "weight_dgrad_layout")
+    return wt
+
+
+def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False):
+    dy = as_nhwc(dy)
+    N, Cin, H, W = x_shape
+    K, _, R, S = w.shape
+    _, _, OH, OW = dy.shape
+    sh_, sw_ = stride
+    ph, pw = pad
+    if out is None:
+        accumulate = False
+    dx = out if out is not None else _empty_nhwc(N, Cin, H, W, dy.device)
+    assert dx.is_contiguous(memory_format=CL)
+    use_tc = tc_enabled() and K % 32 == 0 and R * S <= 49 and R - 1 - ph >= -64
+    if use_tc and sh_ == 1 and sw_ == 1:
+        wt = _dgrad_weights(w)
+        taps = _taps(("d1", R, S, ph, pw), lambda: (
+            [r2 - (R - 1 - ph) for r2 in range(R) for s2 in range(S)],
+            [s2 - (S - 1 - pw) for r2 in range(R) for s2 in range(S)],
+            [r2 * S + s2 for r2 in range(R) for s2 in range(S)]))
+        _conv_tc(dy, N, OH, OW, K, wt, Cin, R * S * K, dx, 0, H * W * Cin, W * Cin, Cin, H, W, 1, 1, taps, None,
+                 accumulate, None)
+        return dx
+    if use_tc:
+        # strided dgrad = one stride-1 tap-subset convolution per output parity class, written with an output stride
+        wt = _dgrad_weights(w)
+        classes = []
+        empty_class = False
+        for a in range(sh_):
+            for b in range(sw_):
+                if a >= H or b >= W:
+                    continue
+                rs = [r for r in range(R) if (a + ph - r) % sh_ == 0]
+                ss = [s for s in range(S) if (b + pw - s) % sw_ == 0]
+                if not rs or not ss:
+                    empty_class = True
+                    continue
+                classes.append((a, b, rs, ss))
+        if empty_class and not accumulate:
+            dx.zero_()
+        for a, b, rs, ss in classes:
+            taps = _taps(("ds", R, S, ph, pw, sh_, sw_, a, b), lambda: (
+                [(a + ph - r) // sh_ for r in rs for s in ss],
+                [(b + pw - s) // sw_ for r in rs for s in ss],
+                [(R - 1 - r) * S + (S - 1 - s) for r in rs for s in ss]))
+            Hc = (H - a + sh_ - 1) // sh_
+            Wc = (W - b + sw_ - 1) // sw_
+            _conv_tc(dy, N, OH, OW, K, wt, Cin, R * S * K, dx, (a * W + b) * Cin, H * W * Cin, sh_ * W * Cin,
+                     sw_ * Cin, Hc, Wc, 1, 1, taps, None, accumulate, None)
+        return dx
+    check(lib().dcnn_conv_dgrad_simt(_p(dy), _p(w), _p(dx), I(N), I(H), I(W), I(Cin), I(K), I(R), I(S), I(sh_),
+                                     I(sw_), I(ph), I(pw), I(1 if accumulate else 0), _stream()), "conv_dgrad_simt")
+    return dx
+
+
+def conv2d_backward_weight(dy, x, dw, stride, pad):
+    dy = as_nhwc(dy)
+    x = as_nhwc(x)
+    N, Cin, H, W = x.shape
+    K, _, R, S = dw.shape
+    _, _, OH, OW = dy.shape
+    sh_, sw_ = stride
+    ph, pw = pad
+    assert dw.is_contiguous(memory_format=CL)
+    use_tc = tc_enabled() and Cin % 32 == 0 and K % 4 == 0 and R * S <= 49 and \
+        ((sh_ == 1 and sw_ == 1) or (tc_strided_enabled() and sh_ <= 8 and sw_ <= 8))
+    if use_tc:
+        taps = _taps(("f", R, S, ph, pw), lambda: (
+            [r - ph for r in range(R) for s in range(S)],
+            [s - pw for r in range(R) for s in range(S)],
+            [r * S + s for r in range(R) for s in range(S)]))
+        n, dh, dw_, wi = taps
+        check(lib().dcnn_wgrad_tc(_p(dy), I(N), I(OH), I(OW), I(K), _p(x), I(H), I(W), I(Cin), _p(dw),
+                                  I(R * S * Cin), I(sh_), I(sw_), I(n), dh, dw_, wi, _stream()), "dcnn_wgrad_tc")
+        return
+    check(lib().dcnn_conv_wgrad_simt(_p(dy), _p(x), _p(dw), I(N), I(H), I(W), I(Cin), I(K), I(R), I(S), I(sh_),
+                                     I(sw_), I(ph), I(pw), _stream()), "conv_wgrad_simt")
+
+
+def bias_grad(dy, db):
+    dy = as_nhwc(dy) if dy.dim() == 4 else dy.contiguous()
+    Cc = dy.shape[1]
+    M = dy.numel() // Cc
+    check(lib().dcnn_colsum_accum(_p(dy), LL(M), I(Cc), _p(db), _stream()), "colsum_accum")
+
+
+# ================================================================================== dense (1x1 conv on [B,1,1,C])
+_ONE_TAP = None
+
+
+def _one_tap():
+    global _ONE_TAP
+    if _ONE_TAP is None:
+        _ONE_TAP = (1, (I * 1)(0), (I * 1)(0), (I * 1)(0))
+    return _ONE_TAP
+
+
+def dense_forward(x2d, w2d, bias):
+    x2d = x2d.contiguous()
+    B, Fin = x2d.shape
+    Fout = w2d.shape[0]
+    y = torch.empty((B, Fout), device=x2d.device, dtype=torch.float32)
+    if tc_enabled() and Fin % 32 == 0:
+        _conv_tc(x2d, B, 1, 1, Fin, w2d, Fout, Fin, y, 0, Fout, Fout, Fout, 1, 1, 1, 1, _one_tap(), bias, False, None)
+    else:
+        check(lib().dcnn_conv_fprop_simt(_p(x2d), _p(w2d), _p(bias), _p(y), I(B), I(1), I(1), I(Fin), I(Fout), I(1),
+                                         I(1), I(1), I(1), I(0), I(0), _stream()), "dense fprop simt")
+    return y
+
+
+def dense_backward_data(dy2d, w2d):
+    dy2d = dy2d.contiguous()
+    B, Fout = dy2d.shape
+    Fin = w2d.shape[1]
+    dx = torch.empty((B, Fin), device=dy2d.device, dtype=torch.float32)
+    if tc_enabled() and Fout % 32 == 0:
+        wt = torch.empty(Fin * Fout, device=dy2d.device, dtype=torch.float32)
+        check(lib().dcnn_weight_dgrad_layout(_p(w2d), _p(wt), I(Fout), I(1), I(1), I(Fin), _stream()), "dense wt")
+        _conv_tc(dy2d, B, 1, 1, Fout, wt, Fin, Fout, dx, 0, Fin, Fin, Fin, 1, 1, 1, 1, _one_tap(), None, False, None)
+    else:
+        check(lib().dcnn_conv_dgrad_simt(_p(dy2d), _p(w2d), _p(dx), I(B), I(1), I(1), I(Fin), I(Fout), I(1), I(1),
+                                         I(1), I(1), I(0), I(0), I(0), _stream()), "dense dgrad simt")
+    return dx
+
+
+def dense_backward_weight(dy2d, x2d, dw2d):
+    dy2d = dy2d.contiguous()
+    x2d = x2d.contiguous()
+    B, Fout = dy2d.shape
+    Fin = x2d.shape[1]
+    if tc_enabled() and Fin % 32 == 0 and Fout % 4 == 0:
+        n, dh, dw_, wi = _one_tap()
+        check(lib().dcnn_wgrad_tc(_p(dy2d), I(B), I(1), I(1), I(Fout), _p(x2d), I(1), I(1), I(Fin), _p(dw2d), I(Fin),
+                                  I(1), I(1), I(n), dh, dw_, wi, _stream()), "dense wgrad tc")
+    else:
+        check(lib().dcnn_conv_wgrad_simt(_p(dy2d), _p(x2d), _p(dw2d), I(B), I(1), I(1), I(Fin), I(Fout), I(1), I(1),
+                                         I(1), I(1), I(0), I(0), _stream()), "dense wgrad simt")
+
+
+# ================================================================================== batch norm
+def bn_stats(x):
+    x = as_nhwc(x)
+    Cc = x.shape[1]
+    M = x.numel() // Cc
+    tiles = lib().dcnn_bn_stat_tiles(LL(M))
+    partials = torch.empty(tiles * (2 * Cc + 1), device=x.device, dtype=torch.float32)
+    check(lib().dcnn_bn_colstats(_p(x), LL(M), I(Cc), _p(partials), _stream()), "bn_colstats")
+    return CudaStats(partials, tiles, Cc, M)
+
+
+class _BNCoeffs:
+    """mean / invstd plus the fused scale/shift used by the apply pass."""
+    __slots__ = ("mean", "invstd", "scale", "shift")
+
+
+def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None, gamma=None, beta=None):
+    Cc = stats.C
+    dev = stats.partials.device
+    buf = torch.empty(4 * Cc, device=dev, dtype=torch.float32)
+    mean, invstd, scale, shift = buf[:Cc], buf[Cc:2 * Cc], buf[2 * Cc:3 * Cc], buf[3 * Cc:]
+    if sync is None:
+        check(lib().dcnn_bn_finalize(_p(stats.partials), I(stats.tiles), I(Cc), F(eps), F(momentum),
+                                     _p(running_mean), _p(running_var), _p(gamma), _p(beta), _p(mean), _p(invstd),
+                                     _p(scale), _p(shift), P(0), _stream()), "bn_finalize")
+    else:
+        sync.finalize_forward(stats, eps, momentum, running_mean, running_var, gamma, beta, mean, invstd, scale, shift)
+    return mean, (invstd, scale, shift)
+
+
+def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False):
+    x = as_nhwc(x)
+    if isinstance(invstd, tuple):
+        invstd, scale, shift = invstd
+    else:  # raw tensors: build the coefficients here
+        scale = invstd if gamma is None else invstd * gamma.view(-1)
+        shift = -mean * scale + (beta.view(-1) if beta is not None else 0)
+    Cc = x.shape[1]
+    M = x.numel() // Cc
+    y = torch.empty_like(x, memory_format=torch.preserve_format)
+    if residual is not None:
+        residual = as_nhwc(residual)
+    check(lib().dcnn_bn_apply(_p(x), _p(scale), _p(shift), _p(residual), _p(y), LL(M), I(Cc), I(1 if relu else 0),
+                              _stream()), "bn_apply")
+    return y
+
+
+def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, want_masked=False, sync=None):
+    dout = as_nhwc(dout)
+    if isinstance(invstd, tuple):
+        invstd = invstd[0]
+    Cc = x.shape[1]
+    M = x.numel() // Cc
+    tiles = lib().dcnn_bn_stat_tiles(LL(M))
+    partials = torch.empty(tiles * 2 * Cc, device=x.device, dtype=torch.float32)
+    check(lib().dcnn_bn_bwd_reduce(_p(dout), _p(x), _p(out), _p(mean), _p(invstd), LL(M), I(Cc),
+                                   I(1 if relu else 0), _p(partials), _stream()), "bn_bwd_reduce")
+    k = torch.empty(3 * Cc, device=x.device, dtype=torch.float32)
+    k1, k2, k3 = k[:Cc], k[Cc:2 * Cc], k[2 * Cc:]
+    if sync is None:
+        check(lib().dcnn_bn_bwd_finalize(_p(partials), I(tiles), I(Cc), D(float(M)), _p(mean), _p(invstd), _p(gamma),
+                                         _p(dgamma), _p(dbeta), _p(k1), _p(k2), _p(k3), P(0), _stream()),
+              "bn_bwd_finalize")
+    else:
+        sync.finalize_backward(partials, tiles, Cc, M, mean, invstd, gamma, dgamma, dbeta, k1, k2, k3)
+    dx = torch.empty_like(x, memory_format=torch.preserve_format)
+    masked = None
+    if want_masked:
+        masked = torch.empty_like(x, memory_format=torch.preserve_format) if relu else dout
+    check(lib().dcnn_bn_bwd_apply(_p(dout), _p(x), _p(out), _p(k1), _p(k2), _p(k3), _p(dx),
+                                  _p(masked if (want_masked and relu) else None), LL(M), I(Cc), I(1 if relu else 0),
+                                  _stream()), "bn_bwd_apply")
+    return dx, masked
+
+
+def bn_inference(x, running_mean, running_var, gamma, beta, eps, residual=None, relu=False):
+    x = as_nhwc(x)
+    Cc = x.shape[1]
+    buf = torch.empty(2 * Cc, device=x.device, dtype=torch.float32)
+    scale, shift = buf[:Cc], buf[Cc:]
+    check(lib().dcnn_bn_eval_coeffs(_p(running_mean), _p(running_var), _p(gamma), _p(beta), F(eps), I(Cc), _p(scale),
+                                    _p(shift), _stream()), "bn_eval_coeffs")
+    return bn_apply(x, None, (None, scale, shift), gamma, beta, residual, relu)
+
+
+# ================================================================================== group norm
+def groupnorm_forward(x, groups, gamma, beta, eps):
+    x = as_nhwc(x)
+    N, Cc, H, W = x.shape
+    y = torch.empty_like(x, memory_format=torch.preserve_format)
+    st = torch.empty(2 * N * groups, device=x.device, dtype=torch.float32)
+    mean, invstd = st[:N * groups], st[N * groups:]
+    check(lib().dcnn_gn_forward(_p(x), _p(y), _p(gamma), _p(beta), _p(mean), _p(invstd), I(N), I(H * W), I(Cc),
+                                I(groups), F(eps), _stream()), "gn_forward")
+    return y, mean, invstd
+
+
+def groupnorm_backward(dy, x, mean, invstd, groups, gamma, dgamma, dbeta):
+    dy = as_nhwc(dy)
+    N, Cc, H, W = x.shape
+    dx = torch.empty_like(x, memory_format=torch.preserve_format)
+    check(lib().dcnn_gn_backward(_p(dy), _p(x), _p(mean), _p(invstd), _p(gamma), _p(dgamma), _p(dbeta), _p(dx), I(N),
+                                 I(H * W), I(Cc), I(groups), _stream()), "gn_backward")
+    return dx
+
+
+# ================================================================================== pooling
+def _pool_out(H, W, k, stride, pad):
+    return (H + 2 * pad[0] - k[0]) // stride[0] + 1, (W + 2 * pad[1] - k[1]) // stride[1] + 1
+
+
+def maxpool_forward(x, k, stride, pad):
+    x = as_nhwc(x)
+    N, Cc, H, W = x.shape
+    OH, OW = _pool_out(H, W, k, stride, pad)
+    y = _empty_nhwc(N, Cc, OH, OW, x.device)
+    idx = torch.empty((N, OH, OW, Cc), device=x.device, dtype=torch.uint8)
+    check(lib().dcnn_maxpool_fwd(_p(x), _p(y), _p(idx), I(N), I(H), I(W), I(Cc), I(OH), I(OW), I(k[0]), I(k[1]),
+                                 I(stride[0]), I(stride[1]), I(pad[0]), I(pad[1]), _stream()), "maxpool_fwd")
+    return y, idx
+
+
+def maxpool_backward(dy, idx, x_shape, k, stride, pad):
+    dy = as_nhwc(dy)
+    N, Cc, H, W = x_shape
+    OH, OW = dy.shape[2:]
+    dx = _empty_nhwc(N, Cc, H, W, dy.device)
+    check(lib().dcnn_maxpool_bwd(_p(dy), _p(idx), _p(dx), I(N), I(H), I(W), I(Cc), I(OH), I(OW), I(k[0]), I(k[1]),
+                                 I(stride[0]), I(stride[1]), I(pad[0]), I(pad[1]), _stream()), "maxpool_bwd")
+    return dx
+
+
+def avgpool_forward(x, k, stride, pad):
+    x = as_nhwc(x)
+    N, Cc, H, W = x.shape
+    OH, OW = _pool_out(H, W, k, stride, pad)
+    y = _empty_nhwc(N, Cc, OH, OW, x.device)
+    check(lib().dcnn_avgpool_fwd(_p(x), _p(y), I(N), I(H), I(W), I(Cc), I(OH), I(OW), I(k[0]), I(k[1]), I(stride[0]),
+                                 I(stride[1]), I(pad[0]), I(pad[1]), _stream()), "avgpool_fwd")
+    return y
+
+
+def avgpool_backward(dy, x_shape, k, stride, pad):
+    dy = as_nhwc(dy)
+    N, Cc, H, W = x_shape
+    OH, OW = dy.shape[2:]
+    dx = _empty_nhwc(N, Cc, H, W, dy.device)
+    check(lib().dcnn_avgpool_bwd(_p(dy), _p(dx), I(N), I(H), I(W), I(Cc), I(OH), I(OW), I(k[0]), I(k[1]),
+                                 I(stride[0]), I(stride[1]), I(pad[0]), I(pad[1]), _stream()), "avgpool_bwd")
+    return dx
+
+
+# ================================================================================== activations
+def _dense(x):
+    """Make the storage dense, preserving channels-last when that is what it already is."""
+    if x.dim() == 4 and x.is_contiguous(memory_format=CL):
+        return x
+    return x.contiguous()
+
+
+def activation_forward(x, kind, alpha=0.0):
+    if kind == "softmax":
+        x = as_nhwc(x) if x.dim() == 4 else x.contiguous()
+        Cc = x.shape[1]
+        y = torch.empty_like(x, memory_format=torch.preserve_format)
+        check(lib().dcnn_softmax_fwd(_p(x), _p(y), LL(x.numel() // Cc), I(Cc), _stream()), "softmax_fwd")
+        return y
+    x = _dense(x)
+    y = torch.empty_like(x, memory_format=torch.preserve_format)
+    check(lib().dcnn_act_fwd(I(_ACT[kind]), _p(x), _p(y), LL(x.numel()), F(alpha), _stream()), "act_fwd")
+    return y
+
+
+def activation_backward(x, dy, kind, alpha=0.0):
+    if kind == "softmax":
+        x = as_nhwc(x) if x.dim() == 4 else x.contiguous()
+        dy = as_nhwc(dy) if dy.dim() == 4 else dy.contiguous()
+        Cc = x.shape[1]
+        dx = torch.empty_like(x, memory_format=torch.preserve_format)
+        check(lib().dcnn_softmax_bwd(_p(x), _p(dy), _p(dx), LL(x.numel() // Cc), I(Cc), _stream()), "softmax_bwd")
+        return dx
+    x = _dense(x)
+    dy = as_nhwc(dy) if (x.dim() == 4 and x.is_contiguous(memory_format=CL)) else dy.contiguous()
+    dx = torch.empty_like(x, memory_format=torch.preserve_format)
+    check(lib().dcnn_act_bwd(I(_ACT[kind]), _p(x), _p(dy), _p(dx), LL(x.numel()), F(alpha), _stream()), "act_bwd")
+    return dx
+
+
+def add(a, b):
+    a = _dense(a)
+    b = as_nhwc(b) if (a.dim() == 4 and a.is_contiguous(memory_format=CL)) else b.contiguous()
+    y = torch.empty_like(a, memory_format=torch.preserve_format)
+    check(lib().dcnn_add(_p(a), _p(b), _p(y), LL(a.numel()), _stream()), "add")
+    return y
+
+
+def dropout_forward(x, rate, seed, offset):
+    x = _dense(x)
+    y = torch.empty_like(x, memory_format=torch.preserve_format)
+    check(lib().dcnn_dropout(_p(x), _p(y), LL(x.numel()), F(rate), ULL(seed), ULL(offset), _stream()), "dropout")
+    return y
+
+
+def dropout_backward(dy, rate, seed, offset):
+    return dropout_forward(dy, rate, seed, offset)
+
+
+# ================================================================================== layout
+def flatten_nchw(x):
+    N = x.shape[0]
+    if x.dim() != 4 or x.shape[2] * x.shape[3] == 1 or x.shape[1] == 1:
+        return x.reshape(N, -1, 1, 1)
+    x = as_nhwc(x)
+    _, Cc, H, W = x.shape
+    out = torch.empty((N, Cc * H * W, 1, 1), device=x.device, dtype=torch.float32)
+    check(lib().dcnn_transpose_batched(_p(x), _p(out), I(N), I(H * W), I(Cc), _stream()), "flatten transpose")
+    return out
+
+
+def unflatten_nchw(g, shape):
+    N, Cc, H, W = shape
+    if H * W == 1 or Cc == 1:
+        return as_nhwc(g.reshape(shape))
+    g = g.contiguous()
+    out = _empty_nhwc(N, Cc, H, W, g.device)
+    check(lib().dcnn_transpose_batched(_p(g), _p(out), I(N), I(Cc), I(H * W), _stream()), "unflatten transpose")
+    return out
+
+
+# ================================================================================== loss
+def loss_forward_backward(kind, pred, target, param=0.0, want_grad=True):
+    B = pred.shape[0]
+    p = pred.reshape(B, -1).contiguous()
+    t = target.reshape(B, -1).to(p.device).contiguous()
+    n = p.shape[1]
+    grad = torch.empty_like(p) if want_grad else None
+    if kind in ("softmax_crossentropy", "logsoftmax_crossentropy", "crossentropy"):
+        out = torch.empty(2, device=p.device, dtype=torch.float32)
+        mode = 1 if kind == "crossentropy" else 0
+        eps = (param if param > 0 else 1e-15) if mode == 1 else 0.0
+        check(lib().dcnn_softmax_ce(_p(p), _p(t), _p(grad), _p(out), I(B), I(n), I(mode), F(eps), _stream()),
+              "softmax_ce")
+        loss, correct = out[0], out[1]
+    else:
+        code = {"mse": 0, "mae": 1, "huber": 2}[kind]
+        out = torch.empty(1, device=p.device, dtype=torch.float32)
+        check(lib().dcnn_regression_loss(_p(p), _p(t), _p(grad), _p(out), LL(p.numel()), I(code), F(param),
+                                         _stream()), "regression_loss")
+        loss, correct = out[0], None
+    if grad is not None:
+        grad = grad.reshape(B, n, 1, 1) if pred.dim() == 4 else grad.reshape(pred.shape)
+    return loss, grad, correct
+
+
+# ================================================================================== optimizers
+_MT_TABLES = {}
+
+
+def _mt_table(params, grads, s1, s2):
+    key = tuple(p.data_ptr() for p in params) + tuple(g.data_ptr() for g in grads) + \
+        tuple(s.data_ptr() for s in (s1 or [])) + tuple(s.data_ptr() for s in (s2 or []))
+    tb = _MT_TABLES.get(key)
+    if tb is None:
+        dev = params[0].device
+        chunk = lib().dcnn_mt_chunk()
+        numel = [p.numel() for p in params]
+        bt, bo = [], []
+        for i, n in enumerate(numel):
+            for off in range(0, n, chunk):
+                bt.append(i)
+                bo.append(off)
+
+        def ptrs(ts):
+            if not ts:
+                return torch.zeros(len(params), dtype=torch.int64, device=dev)
+            return torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64, device=dev)
+        for t in list(params) + list(grads) + list(s1 or []) + list(s2 or []):
+            assert t.is_contiguous() or t.is_contiguous(memory_format=CL), "optimizer tensors must be dense"
+        tb = (ptrs(params), ptrs(grads), ptrs(s1), ptrs(s2),
+              torch.tensor(numel, dtype=torch.int64, device=dev),
+              torch.tensor(bt, dtype=torch.int32, device=dev),
+              torch.tensor(bo, dtype=torch.int64, device=dev), len(bt))
+        if len(_MT_TABLES) > 64:
+            _MT_TABLES.clear()
+        _MT_TABLES[key] = tb
+    return tb
+
+
+def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False, hyper=None):
+    mode = 1 if momentum > 0 else 0
+    tb = _mt_table(params, grads, velocities if mode else None, None)
+    check(lib().dcnn_multi_tensor_update(I(mode), _p(tb[0]), _p(tb[1]), _p(tb[2]), _p(tb[3]), _p(tb[4]), _p(tb[5]),
+                                         _p(tb[6]), I(tb[7]), F(lr), F(momentum), F(0), F(0), F(1), F(1), F(0),
+                                         I(1 if zero_grads else 0), _p(hyper), _stream()), "sgd_update")
+
+
+def adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_decay, decoupled, zero_grads=False,
+                hyper=None):
+    tb = _mt_table(params, grads, ms, vs)
+    check(lib().dcnn_multi_tensor_update(I(3 if decoupled else 2), _p(tb[0]), _p(tb[1]), _p(tb[2]), _p(tb[3]),
+                                         _p(tb[4]), _p(tb[5]), _p(tb[6]), I(tb[7]), F(lr), F(beta1), F(beta2), F(eps),
+                                         F(bc1), F(bc2), F(weight_decay), I(1 if zero_grads else 0), _p(hyper),
+                                         _stream()), "adam_update")

@@ -1,0 +1,123 @@
+/* C ABI of libdcnn_b200.so -- hand-written sm_100a kernels behind plain pointers + a CUDA stream.
+ *
+ * Conventions: activations are NHWC fp32; every function returns 0 on success, otherwise a non-zero code whose
+ * text is available from dcnn_last_error().  All launches are asynchronous on `stream`; nothing here synchronises.
+ * Each declaration cites the reference code it replaces (paths relative to the reference repository). */
+#ifndef DCNN_B200_H_
+#define DCNN_B200_H_
+#include <cuda_runtime.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ---- */
+const char* dcnn_last_error(void);
+const char* dcnn_version(void);
+unsigned long long dcnn_launch_count(void);
+void dcnn_reset_launch_count(void);
+int dcnn_device_sms(void);
+
+/* ---- tensor-core implicit GEMM (tcgen05 + TMEM + TMA); replaces cudnnConvolutionForward/BackwardData/
+ *      BackwardFilter and cublasSgemm: src/nn/layers_impl/cuda/cudnn_conv2d_ops.cu:171-232, dense_ops.cu:24-137 ---- */
+int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w);
+int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
+                 long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h, int in_mul_w,
+                 int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w, const float* bias,
+                 int accumulate, float* partials, cudaStream_t stream);
+int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin, float* dw,
+                  int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw,
+                  const int* tap_w, cudaStream_t stream);
+int dcnn_tma_probe(const float* x, int N, int H, int W, int C, int bn, int bh, int bw, int mul_h, int mul_w, int c0,
+                   int c1, int c2, int c3, float* out, cudaStream_t stream);
+
+/* ---- exact-FP32 CUDA-core fallbacks (src/nn/layers_impl/cuda/conv2d_ops.cu:19-100, tensor_kernels.cu:18-119) ---- */
+int dcnn_conv_fprop_simt(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int C,
+                         int K, int R, int S, int sh, int sw, int ph, int pw, cudaStream_t stream);
+int dcnn_conv_dgrad_simt(const float* dy, const float* w, float* dx, int N, int H, int W, int C, int K, int R, int S,
+                         int sh, int sw, int ph, int pw, int accumulate, cudaStream_t stream);
+int dcnn_conv_wgrad_simt(const float* dy, const float* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                         int sh, int sw, int ph, int pw, cudaStream_t stream);
+int dcnn_weight_dgrad_layout(const float* w, float* wt, int K, int R, int S, int C, cudaStream_t stream);
+
+/* ---- BatchNorm / GroupNorm (batchnorm_ops.cu:108-295, groupnorm_ops.cu:45-252, cudnnConvolutionBackwardBias) ---- */
+int dcnn_bn_stat_tiles(long long M);
+int dcnn_bn_colstats(const float* x, long long M, int C, float* partials, cudaStream_t stream);
+int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
+                     float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
+                     float* scale, float* shift, double* export_moments, cudaStream_t stream);
+int dcnn_bn_finalize_sync(const double* const* peer_moments, int n_peers, int C, float eps, float momentum,
+                          float* running_mean, float* running_var, const float* gamma, const float* beta, float* mean,
+                          float* invstd, float* scale, float* shift, cudaStream_t stream);
+int dcnn_bn_eval_coeffs(const float* rm, const float* rv, const float* gamma, const float* beta, float eps, int C,
+                        float* scale, float* shift, cudaStream_t stream);
+int dcnn_bn_apply(const float* x, const float* scale, const float* shift, const float* residual, float* y,
+                  long long M, int C, int relu, cudaStream_t stream);
+int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean, const float* invstd,
+                       long long M, int C, int relu, float* partials, cudaStream_t stream);
+int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
+                         const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1, float* k2,
+                         float* k3, double* export_sums, cudaStream_t stream);
+int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, int n_peers, int C, const float* mean,
+                              const float* invstd, const float* gamma, float* k1, float* k2, float* k3,
+                              cudaStream_t stream);
+int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* out, const float* k1, const float* k2,
+                      const float* k3, float* dx, float* masked, long long M, int C, int relu, cudaStream_t stream);
+int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, cudaStream_t stream);
+int dcnn_gn_forward(const float* x, float* y, const float* gamma, const float* beta, float* mean, float* invstd,
+                    int N, int HW, int C, int G, float eps, cudaStream_t stream);
+int dcnn_gn_backward(const float* dy, const float* x, const float* mean, const float* invstd, const float* gamma,
+                     float* dgamma, float* dbeta, float* dx, int N, int HW, int C, int G, cudaStream_t stream);
+
+/* ---- pooling / activations / dropout / layout (maxpool_ops.cu, avgpool_ops.cu, activations_impl/cuda/*.cu,
+ *      dropout.cu, ops/cuda/kernels.cu) ---- */
+int dcnn_maxpool_fwd(const float* x, float* y, uint8_t* idx, int N, int H, int W, int C, int OH, int OW, int kh,
+                     int kw, int sh, int sw, int ph, int pw, cudaStream_t stream);
+int dcnn_maxpool_bwd(const float* dy, const uint8_t* idx, float* dx, int N, int H, int W, int C, int OH, int OW,
+                     int kh, int kw, int sh, int sw, int ph, int pw, cudaStream_t stream);
+int dcnn_avgpool_fwd(const float* x, float* y, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh,
+                     int sw, int ph, int pw, cudaStream_t stream);
+int dcnn_avgpool_bwd(const float* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int kh, int kw, int sh,
+                     int sw, int ph, int pw, cudaStream_t stream);
+int dcnn_act_fwd(int kind, const float* x, float* y, long long n, float alpha, cudaStream_t stream);
+int dcnn_act_bwd(int kind, const float* x, const float* g, float* dx, long long n, float alpha, cudaStream_t stream);
+int dcnn_softmax_fwd(const float* x, float* y, long long rows, int C, cudaStream_t stream);
+int dcnn_softmax_bwd(const float* x, const float* g, float* dx, long long rows, int C, cudaStream_t stream);
+int dcnn_add(const float* a, const float* b, float* y, long long n, cudaStream_t stream);
+int dcnn_dropout(const float* x, float* y, long long n, float rate, unsigned long long seed,
+                 unsigned long long offset, cudaStream_t stream);
+int dcnn_transpose_batched(const float* in, float* out, int batch, int rows, int cols, cudaStream_t stream);
+int dcnn_fill(float* p, long long n, float v, cudaStream_t stream);
+
+/* ---- loss + accuracy, optimizers (loss_ops.cu:18-435, accuracy.cu:15-111, adam_kernels.cu, sgd_kernels.cu) ---- */
+int dcnn_softmax_ce(const float* pred, const float* tgt, float* grad, float* out2, int B, int C, int mode, float eps,
+                    cudaStream_t stream);
+int dcnn_regression_loss(const float* pred, const float* tgt, float* grad, float* out1, long long n, int kind,
+                         float delta, cudaStream_t stream);
+int dcnn_multi_tensor_update(int mode, float* const* param, float* const* grad, float* const* s1, float* const* s2,
+                             const long long* numel, const int* block_tensor, const long long* block_off,
+                             int num_blocks, float lr, float a, float b, float eps, float bc1, float bc2, float wd,
+                             int zero_grads, const float* hyper /* device {lr,bc1,bc2} or NULL */,
+                             cudaStream_t stream);
+int dcnn_mt_chunk(void);
+
+/* ---- data-parallel peer-memory path (no counterpart in the reference: it has no data parallelism) ---- */
+int dcnn_dev_malloc(void** ptr, long long bytes);
+int dcnn_dev_free(void* ptr);
+int dcnn_ipc_get_handle(void* ptr, unsigned char* handle64);
+int dcnn_ipc_open(const unsigned char* handle64, void** ptr);
+int dcnn_ipc_close(void* ptr);
+int dcnn_enable_peer_access(int peer_device);
+int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, int world, unsigned long long epoch,
+                      cudaStream_t stream);
+int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* param_ptrs, float* s1, float* s2, long long n,
+                                long long shard_begin, long long shard_end,
+                                unsigned long long* const* start_flag_ptrs, unsigned long long* const* done_flag_ptrs,
+                                unsigned int* block_counter, int rank, int world, unsigned long long epoch, int mode,
+                                float lr, float a, float b, float eps, float bc1, float bc2, float wd, int num_blocks,
+                                cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DCNN_B200_H_ */

@@ -1,0 +1,315 @@
+"""GPU kernel tests: every CUDA op against the CPU FP32 oracle of the same op (the reference's strategy:
+unit_tests/cuda_*_ops_test.cpp compare GPU results with the CPU implementation, tol 1e-4; layer-level 1e-3).
+Tensor-core paths use TF32 inputs with FP32 accumulation, so they get a relative bound instead (documented in
+DESIGN.md); DCNN_DISABLE_TC=1 gives the FP32-exact CUDA-core path, tested with the tight bound."""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from dcnn_b200 import ops
+from dcnn_b200.ops import cpu as ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def cl(t):
+    return t.to(DEV).contiguous(memory_format=torch.channels_last)
+
+
+def rel_err(a, b):
+    a, b = a.detach().cpu().float(), b.detach().cpu().float()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+def check_close(a, b, tol, what=""):
+    e = rel_err(a, b)
+    assert e < tol, f"{what}: rel err {e:.3e} >= {tol}"
+
+
+@pytest.fixture(autouse=True)
+def _seed():
+    torch.manual_seed(1234)
+    yield
+    torch.cuda.synchronize()
+
+
+# ----------------------------------------------------------------------------------------- TMA semantics probes
+def _probe(x_nhwc, bn, bh, bw, mul, c0, c1, c2, c3):
+    from dcnn_b200._lib import I, P, check, lib
+    N, H, W, C = x_nhwc.shape
+    out = torch.empty(bn * bh * bw * 32, device=DEV)
+    check(lib().dcnn_tma_probe(P(x_nhwc.data_ptr()), I(N), I(H), I(W), I(C), I(bn), I(bh), I(bw), I(mul), I(mul),
+                               I(c0), I(c1), I(c2), I(c3), P(out.data_ptr()), P(0)), "tma_probe")
+    torch.cuda.synchronize()
+    raw = out.cpu().reshape(bn * bh * bw, 8, 4)  # rows x 16-byte chunks x 4 floats
+    rows = torch.arange(raw.shape[0])
+    unsw = torch.empty_like(raw)
+    for j in range(8):  # undo the 128B swizzle: physical chunk = logical chunk XOR (row % 8)
+        unsw[:, j] = raw[rows, (j ^ (rows % 8))]
+    return unsw.reshape(bn, bh, bw, 32)
+
+
+def test_tma_negative_coords_zero_fill():
+    x = torch.randn(2, 6, 6, 32, device=DEV)
+    got = _probe(x, 1, 8, 16, 1, 0, -1, -1, 1)
+    exp = torch.zeros(1, 8, 16, 32)
+    xc = x.cpu()
+    for h in range(8):
+        for w in range(16):
+            ih, iw = h - 1, w - 1
+            if 0 <= ih < 6 and 0 <= iw < 6:
+                exp[0, h, w] = xc[1, ih, iw]
+    assert torch.equal(got, exp)
+
+
+def test_tma_element_strides():
+    x = torch.randn(2, 16, 16, 32, device=DEV)
+    got = _probe(x, 2, 8, 8, 2, 0, -1, -1, 0)
+    exp = torch.zeros(2, 8, 8, 32)
+    xc = x.cpu()
+    for n in range(2):
+        for h in range(8):
+            for w in range(8):
+                ih, iw = 2 * h - 1, 2 * w - 1
+                if 0 <= ih < 16 and 0 <= iw < 16:
+                    exp[n, h, w] = xc[n, ih, iw]
+    assert torch.equal(got, exp)
+
+
+# ----------------------------------------------------------------------------------------- convolution
+CONV_CASES = [
+    # N, C, H, W, OC, k, s, p, bias
+    (4, 64, 16, 16, 128, 3, 1, 1, True),
+    (2, 32, 8, 8, 64, 1, 1, 0, False),
+    (8, 64, 32, 32, 64, 3, 1, 1, False),
+    (3, 128, 14, 14, 256, 3, 1, 1, True),
+    (5, 256, 7, 7, 96, 1, 1, 0, True),
+    (2, 64, 4, 4, 512, 3, 1, 1, False),
+    (4, 64, 16, 16, 128, 3, 2, 1, False),
+    (4, 128, 16, 16, 256, 1, 2, 0, False),
+    (2, 32, 30, 30, 64, 7, 2, 3, True),
+    (2, 3, 32, 32, 64, 3, 1, 1, True),       # stem: CUDA-core path
+    (2, 8, 12, 12, 16, 5, 1, 0, True),       # MNIST-like: CUDA-core path
+    (2, 16, 9, 9, 48, 5, 1, 0, True),
+]
+
+
+def _tol(C):
+    return 4e-3 if C % 32 == 0 and os.environ.get("DCNN_DISABLE_TC", "0") != "1" else 2e-5
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_conv_forward(case):
+    N, C, H, W, OC, k, s, p, bias = case
+    x = torch.randn(N, C, H, W)
+    w = torch.randn(OC, C, k, k) / (C * k * k) ** 0.5
+    b = torch.randn(OC, 1, 1, 1) if bias else None
+    y_ref, st_ref = ref.conv2d_forward(x, w, b, (s, s), (p, p), True)
+    y, st = ops.conv2d_forward(cl(x), cl(w), None if b is None else b.to(DEV), (s, s), (p, p), True)
+    check_close(y, y_ref, _tol(C), "conv fprop")
+    rm, rv = torch.zeros(OC, device=DEV), torch.ones(OC, device=DEV)
+    mean, inv = ops.bn_finalize(st, 1e-5, 0.1, rm, rv)
+    mean_ref, inv_ref = ref.bn_finalize(st_ref, 1e-5, 0.1, torch.zeros(OC), torch.ones(OC))
+    assert (mean.cpu() - mean_ref).abs().max() < 5e-3
+    check_close(inv[0], inv_ref, 1e-2, "epilogue BN invstd")
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_conv_backward_data(case):
+    N, C, H, W, OC, k, s, p, _ = case
+    w = torch.randn(OC, C, k, k) / (C * k * k) ** 0.5
+    oh = (H + 2 * p - k) // s + 1
+    dy = torch.randn(N, OC, oh, oh)
+    dx_ref = ref.conv2d_backward_data(dy, w, (N, C, H, W), (s, s), (p, p))
+    dx = ops.conv2d_backward_data(cl(dy), cl(w), (N, C, H, W), (s, s), (p, p))
+    check_close(dx, dx_ref, _tol(OC), "conv dgrad")
+    # accumulate into an existing buffer (how residual branch gradients are summed)
+    base = torch.randn(N, C, H, W)
+    out = cl(base.clone())
+    ops.conv2d_backward_data(cl(dy), cl(w), (N, C, H, W), (s, s), (p, p), out=out, accumulate=True)
+    check_close(out, dx_ref + base, _tol(OC), "conv dgrad accumulate")
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_conv_backward_weight(case):
+    N, C, H, W, OC, k, s, p, _ = case
+    x = torch.randn(N, C, H, W)
+    oh = (H + 2 * p - k) // s + 1
+    dy = torch.randn(N, OC, oh, oh)
+    dw_ref = torch.zeros(OC, C, k, k)
+    ref.conv2d_backward_weight(dy, x, dw_ref, (s, s), (p, p))
+    dw = cl(torch.zeros(OC, C, k, k))
+    ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p))
+    check_close(dw, dw_ref, _tol(C), "conv wgrad")
+    ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p))  # beta=1: second call accumulates
+    check_close(dw, 2 * dw_ref, _tol(C), "conv wgrad accumulate")
+    db_ref = torch.zeros(OC, 1, 1, 1)
+    ref.bias_grad(dy, db_ref)
+    db = torch.zeros(OC, 1, 1, 1, device=DEV)
+    ops.bias_grad(cl(dy), db)
+    check_close(db, db_ref, 1e-4, "bias grad")
+
+
+def test_conv_fp32_exact_mode(monkeypatch):
+    monkeypatch.setenv("DCNN_DISABLE_TC", "1")
+    x, w = torch.randn(2, 64, 8, 8), torch.randn(32, 64, 3, 3) / 24
+    y_ref, _ = ref.conv2d_forward(x, w, None, (1, 1), (1, 1))
+    y, _ = ops.conv2d_forward(cl(x), cl(w), None, (1, 1), (1, 1))
+    check_close(y, y_ref, 2e-5, "fp32 exact conv")
+
+
+@pytest.mark.parametrize("B,Fin,Fout", [(256, 2048, 200), (64, 512, 10), (7, 96, 33), (32, 75, 10)])
+def test_dense(B, Fin, Fout):
+    x, w, b = torch.randn(B, Fin), torch.randn(Fout, Fin) / Fin ** 0.5, torch.randn(Fout, 1, 1, 1)
+    tol = 4e-3 if Fin % 32 == 0 else 2e-5
+    check_close(ops.dense_forward(x.to(DEV), w.to(DEV), b.to(DEV)), ref.dense_forward(x, w, b), tol, "dense fwd")
+    dy = torch.randn(B, Fout)
+    tol_d = 4e-3 if Fout % 32 == 0 else 2e-5
+    check_close(ops.dense_backward_data(dy.to(DEV), w.to(DEV)), ref.dense_backward_data(dy, w), tol_d, "dense dgrad")
+    dw_ref = torch.zeros(Fout, Fin)
+    ref.dense_backward_weight(dy, x, dw_ref)
+    dw = torch.zeros(Fout, Fin, device=DEV)
+    ops.dense_backward_weight(dy.to(DEV), x.to(DEV), dw)
+    check_close(dw, dw_ref, tol, "dense wgrad")
+
+
+# ----------------------------------------------------------------------------------------- batch norm
+@pytest.mark.parametrize("N,C,H,W", [(8, 64, 16, 16), (4, 256, 8, 8), (3, 6, 5, 5), (16, 2048, 2, 2)])
+@pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
+def test_batchnorm_fwd_bwd(N, C, H, W, relu, res):
+    x = torch.randn(N, C, H, W) * 3 + 5   # large mean: exercises the shifted/centred statistics
+    gamma, beta = torch.rand(C, 1, 1, 1) + 0.5, torch.randn(C, 1, 1, 1)
+    r = torch.randn(N, C, H, W) if res else None
+    rm_ref, rv_ref = torch.zeros(C), torch.ones(C)
+    mean_ref, inv_ref = ref.bn_finalize(ref.bn_stats(x), 1e-5, 0.1, rm_ref, rv_ref)
+    y_ref = ref.bn_apply(x, mean_ref, inv_ref, gamma, beta, r, relu)
+    rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    xg, gg, bg = cl(x), gamma.to(DEV), beta.to(DEV)
+    mean, inv = ops.bn_finalize(ops.bn_stats(xg), 1e-5, 0.1, rm, rv, gamma=gg, beta=bg)
+    y = ops.bn_apply(xg, mean, inv, gg, bg, None if r is None else cl(r), relu)
+    check_close(mean, mean_ref, 1e-5, "bn mean")
+    check_close(inv[0], inv_ref, 1e-4, "bn invstd")
+    check_close(rm, rm_ref, 1e-5, "running mean")
+    check_close(rv, rv_ref, 1e-4, "running var")
+    check_close(y, y_ref, 1e-4, "bn apply")
+    dout = torch.randn(N, C, H, W)
+    dg_ref, db_ref = torch.zeros(C, 1, 1, 1), torch.zeros(C, 1, 1, 1)
+    dx_ref, m_ref = ref.bn_backward(dout, x, y_ref, mean_ref, inv_ref, gamma, dg_ref, db_ref, relu, True)
+    dg, db = torch.zeros(C, 1, 1, 1, device=DEV), torch.zeros(C, 1, 1, 1, device=DEV)
+    dx, m = ops.bn_backward(cl(dout), xg, y, mean, inv, gg, dg, db, relu, True)
+    check_close(dx, dx_ref, 2e-4, "bn dx")
+    check_close(m, m_ref, 1e-6, "masked dout")
+    check_close(dg, dg_ref, 2e-4, "dgamma")
+    check_close(db, db_ref, 2e-4, "dbeta")
+
+
+def test_batchnorm_inference():
+    x = torch.randn(4, 32, 6, 6)
+    rm, rv, g, b = torch.randn(32), torch.rand(32) + 0.5, torch.rand(32, 1, 1, 1), torch.randn(32, 1, 1, 1)
+    check_close(ops.bn_inference(cl(x), rm.to(DEV), rv.to(DEV), g.to(DEV), b.to(DEV), 1e-5, None, True),
+                ref.bn_inference(x, rm, rv, g, b, 1e-5, None, True), 1e-5, "bn eval")
+
+
+@pytest.mark.parametrize("N,C,H,W,G", [(4, 32, 8, 8, 8), (2, 6, 5, 5, 3), (3, 64, 4, 4, 32)])
+def test_groupnorm(N, C, H, W, G):
+    x = torch.randn(N, C, H, W) * 2 + 1
+    gamma, beta = torch.rand(C, 1, 1, 1) + 0.5, torch.randn(C, 1, 1, 1)
+    y_ref, mean_ref, inv_ref = ref.groupnorm_forward(x, G, gamma, beta, 1e-5)
+    y, mean, inv = ops.groupnorm_forward(cl(x), G, gamma.to(DEV), beta.to(DEV), 1e-5)
+    check_close(y, y_ref, 1e-4, "gn fwd")
+    dy = torch.randn(N, C, H, W)
+    dg_ref, db_ref = torch.zeros(C, 1, 1, 1), torch.zeros(C, 1, 1, 1)
+    dx_ref = ref.groupnorm_backward(dy, x, mean_ref, inv_ref, G, gamma, dg_ref, db_ref)
+    dg, db = torch.zeros(C, 1, 1, 1, device=DEV), torch.zeros(C, 1, 1, 1, device=DEV)
+    dx = ops.groupnorm_backward(cl(dy), cl(x), mean, inv, G, gamma.to(DEV), dg, db)
+    check_close(dx, dx_ref, 2e-4, "gn dx")
+    check_close(dg, dg_ref, 2e-4, "gn dgamma")
+    check_close(db, db_ref, 2e-4, "gn dbeta")
+
+
+# ----------------------------------------------------------------------------------------- pooling / act / misc
+@pytest.mark.parametrize("C", [64, 6])
+@pytest.mark.parametrize("k,s,p", [(2, 2, 0), (3, 2, 1), (3, 3, 0), (3, 1, 1)])
+def test_maxpool(C, k, s, p):
+    x = torch.randn(3, C, 13, 13)
+    y_ref, idx_ref = ref.maxpool_forward(x, (k, k), (s, s), (p, p))
+    y, idx = ops.maxpool_forward(cl(x), (k, k), (s, s), (p, p))
+    check_close(y, y_ref, 1e-7, "maxpool fwd")
+    dy = torch.randn_like(y_ref)
+    dx_ref = ref._maxpool_bwd_scatter(dy, idx_ref, x.shape)
+    dx = ops.maxpool_backward(cl(dy), idx, tuple(x.shape), (k, k), (s, s), (p, p))
+    check_close(dx, dx_ref, 1e-6, "maxpool bwd")
+
+
+@pytest.mark.parametrize("C", [64, 6])
+@pytest.mark.parametrize("k,s,p", [(2, 2, 0), (4, 1, 0), (3, 2, 1), (4, 4, 0)])
+def test_avgpool(C, k, s, p):
+    x = torch.randn(3, C, 12, 12)
+    y_ref = ref.avgpool_forward(x, (k, k), (s, s), (p, p))
+    check_close(ops.avgpool_forward(cl(x), (k, k), (s, s), (p, p)), y_ref, 1e-6, "avgpool fwd")
+    dy = torch.randn_like(y_ref)
+    check_close(ops.avgpool_backward(cl(dy), tuple(x.shape), (k, k), (s, s), (p, p)),
+                ref.avgpool_backward(dy, tuple(x.shape), (k, k), (s, s), (p, p)), 1e-6, "avgpool bwd")
+
+
+@pytest.mark.parametrize("kind,alpha", [("relu", 0), ("leaky_relu", 0.01), ("elu", 1.0), ("sigmoid", 0), ("tanh", 0),
+                                        ("softmax", 0), ("linear", 0)])
+def test_activations(kind, alpha):
+    x, g = torch.randn(5, 10, 3, 3), torch.randn(5, 10, 3, 3)
+    check_close(ops.activation_forward(cl(x), kind, alpha), ref.activation_forward(x, kind, alpha), 1e-5, kind)
+    check_close(ops.activation_backward(cl(x), cl(g), kind, alpha), ref.activation_backward(x, g, kind, alpha), 1e-5,
+                kind + " grad")
+
+
+def test_add_flatten_dropout():
+    a, b = torch.randn(3, 5, 7, 7), torch.randn(3, 5, 7, 7)
+    check_close(ops.add(cl(a), cl(b)), a + b, 1e-7, "add")
+    f = ops.flatten_nchw(cl(a))
+    assert torch.equal(f.cpu(), a.reshape(3, -1, 1, 1))
+    assert torch.equal(ops.unflatten_nchw(f, a.shape).cpu(), a)
+    y = ops.dropout_forward(torch.ones(1 << 16, device=DEV), 0.3, 7, 1)
+    keep = float((y > 0).float().mean())
+    assert abs(keep - 0.7) < 0.01 and abs(float(y.max()) - 1 / 0.7) < 1e-5
+    assert torch.equal(y, ops.dropout_backward(torch.ones(1 << 16, device=DEV), 0.3, 7, 1))
+    assert not torch.equal(y, ops.dropout_forward(torch.ones(1 << 16, device=DEV), 0.3, 7, 2))
+
+
+@pytest.mark.parametrize("kind,param", [("softmax_crossentropy", 0), ("logsoftmax_crossentropy", 0),
+                                        ("crossentropy", 1e-7), ("mse", 0), ("mae", 0), ("huber", 1.0)])
+def test_losses(kind, param):
+    B, C = 37, 200
+    p = torch.randn(B, C, 1, 1)
+    if kind == "crossentropy":
+        p = torch.softmax(p, 1)
+    t = F.one_hot(torch.randint(0, C, (B,)), C).float().reshape(B, C, 1, 1)
+    l_ref, g_ref, c_ref = ref.loss_forward_backward(kind, p, t, param)
+    l, g, c = ops.loss_forward_backward(kind, p.to(DEV), t.to(DEV), param)
+    assert abs(float(l) - float(l_ref)) < 1e-4 * max(1.0, abs(float(l_ref)))
+    check_close(g, g_ref, 1e-4, kind + " grad")
+    if c_ref is not None:
+        assert int(c) == int(c_ref)
+
+
+@pytest.mark.parametrize("opt", ["sgd", "momentum", "adam", "adamw"])
+def test_optimizers(opt):
+    shapes = [(64, 3, 3, 3), (64, 1, 1, 1), (200, 2048, 1, 1), (7,), (100000,)]
+    P_ = [torch.randn(s) for s in shapes]
+    G_ = [torch.randn(s) for s in shapes]
+    S1 = [torch.randn(s) * 0.1 for s in shapes]
+    S2 = [torch.rand(s) * 0.1 for s in shapes]
+    dev = [[t.clone().to(DEV) for t in L] for L in (P_, G_, S1, S2)]
+    if opt in ("sgd", "momentum"):
+        mom = 0.9 if opt == "momentum" else 0.0
+        ref.sgd_update(P_, G_, S1, 0.1, mom)
+        ops.sgd_update(dev[0], dev[1], dev[2], 0.1, mom, zero_grads=True)
+    else:
+        ref.adam_update(P_, G_, S1, S2, 1e-2, 0.9, 0.999, 1e-8, 0.1, 0.001, 5e-4, opt == "adamw")
+        ops.adam_update(dev[0], dev[1], dev[2], dev[3], 1e-2, 0.9, 0.999, 1e-8, 0.1, 0.001, 5e-4, opt == "adamw",
+                        zero_grads=True)
+    for a, b in zip(dev[0], P_):
+        check_close(a, b, 1e-5, opt + " params")
+    for g in dev[1]:
+        assert float(g.abs().max()) == 0.0
