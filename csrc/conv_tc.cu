@@ -16,6 +16,8 @@
 // accumulating into the destination, which is how residual-branch gradients are summed) and (b) emit per-channel
 // BatchNorm partial statistics (sum, centred M2) for this 128-pixel tile, so BN never re-reads the conv output
 // to compute its statistics.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -266,6 +268,10 @@ struct WgradTcParams {
   int Cin, Cout, Ktot;
   int num_taps, oc_tiles, c_tiles, splits;
   float* dw;  // [Cout][Ktot]
+  // operand descriptors are runtime values so that layout experiments do not need a rebuild
+  uint64_t desc_hi_a, desc_hi_b;
+  uint32_t idesc;
+  uint32_t k_step_bytes;
   int16_t tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_w[kMaxTaps];
 };
 
@@ -359,8 +365,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
       }
     } else if (warp == 1) {
       if (lane == 0) {
-        constexpr uint32_t idesc = make_idesc_tf32(128, BNW, 1, 1);           // both operands MN-major
-        constexpr uint64_t desc_hi = make_smem_desc_hi(kWPix * 128, 1024);     // LBO = next 32-wide MN chunk
+        const uint32_t idesc = p.idesc;  // both operands MN-major
         int stage = 0;
         uint32_t phase = 0;
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -371,8 +376,8 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
 #pragma unroll
           for (int k = 0; k < kWPix / 8; ++k) {
             // advancing K by 8 pixel rows == 8 * 128 B == one swizzle atom
-            mma_tf32_ss(tmem_base, make_smem_desc(a_addr + k * 1024, desc_hi),
-                        make_smem_desc(b_addr + k * 1024, desc_hi), idesc, (kb | k) != 0);
+            mma_tf32_ss(tmem_base, make_smem_desc(a_addr + k * p.k_step_bytes, p.desc_hi_a),
+                        make_smem_desc(b_addr + k * p.k_step_bytes, p.desc_hi_b), idesc, (kb | k) != 0);
           }
           mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) {
@@ -439,7 +444,7 @@ static PFN_tmapEncodeTiled get_encode() {
 
 // NHWC fp32 tensor [N][H][W][C] -> 4-D map, box {32, bw*mul_w, bh*mul_h, bn}, element strides {1,mul_w,mul_h,1}
 static int make_tmap_nhwc(CUtensorMap* tm, const float* base, int N, int H, int W, int C, int bn, int bh, int bw,
-                          int mul_h, int mul_w) {
+                          int mul_h, int mul_w, CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   PFN_tmapEncodeTiled enc = get_encode();
   DCNN_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
   cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
@@ -447,7 +452,7 @@ static int make_tmap_nhwc(CUtensorMap* tm, const float* base, int N, int H, int 
   cuuint32_t box[4] = {32, (cuuint32_t)(bw * mul_w), (cuuint32_t)(bh * mul_h), (cuuint32_t)bn};
   cuuint32_t estr[4] = {1, (cuuint32_t)mul_w, (cuuint32_t)mul_h, 1};
   CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstr, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   DCNN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(NHWC %dx%dx%dx%d box %d,%d,%d mul %d,%d) failed: %d", N, H,
                W, C, bn, bh, bw, mul_h, mul_w, (int)r);
@@ -598,6 +603,20 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   }
   p.oc_tiles = ceil_div(Cout, 128);
   const bool wide = Cin >= 128;
+  CUtensorMapSwizzle wgrad_swizzle = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
+  {
+    // MN-major TF32 operands must use the 128B-swizzle-with-32B-atoms layout (TMA: SWIZZLE_128B_ATOM_32B, UMMA
+    // layout type 1): rows of 128 B (32 elements along M/N), 32-byte chunks XOR-ed with (row % 4).  LBO = byte distance
+    // between 32-element MN chunks (one TMA box), SBO = byte distance between 4-row K groups, one K=8 MMA = 1024 B.
+    uint32_t lbo = kWPix * 128, sbo = 512, a_mn = 1, b_mn = 1, kstep = 1024, layout = 1, swz = 4;
+    if (const char* dbg = getenv("DCNN_WGRAD_DBG"))
+      sscanf(dbg, "%u,%u,%u,%u,%u,%u,%u", &lbo, &sbo, &a_mn, &b_mn, &kstep, &layout, &swz);
+    wgrad_swizzle = (CUtensorMapSwizzle)swz;
+    p.desc_hi_a = make_smem_desc_hi(lbo, sbo, layout);
+    p.desc_hi_b = make_smem_desc_hi(lbo, sbo, layout);
+    p.idesc = make_idesc_tf32(128, wide ? 128 : 64, a_mn, b_mn);
+    p.k_step_bytes = kstep;
+  }
   p.c_tiles = ceil_div(Cin, wide ? 128 : 64);
   const int pix_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
   const int base = num_taps * p.oc_tiles * p.c_tiles;
@@ -609,9 +628,9 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   splits = ceil_div(pix_tiles, per);
   p.splits = splits;
   CUtensorMap tmDY, tmX;
-  int rc = make_tmap_nhwc(&tmDY, dy, N, OH, OW, Cout, p.bn, p.bh, p.bw, 1, 1);
+  int rc = make_tmap_nhwc(&tmDY, dy, N, OH, OW, Cout, p.bn, p.bh, p.bw, 1, 1, wgrad_swizzle);
   if (rc) return rc;
-  rc = make_tmap_nhwc(&tmX, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
+  rc = make_tmap_nhwc(&tmX, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w, wgrad_swizzle);
   if (rc) return rc;
   if (wide) return launch_wgrad<128, 3>(tmDY, tmX, p, stream);
   return launch_wgrad<64, 4>(tmDY, tmX, p, stream);

@@ -52,7 +52,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) __trap();
+    if (++spins > (1u << 22)) __trap();
   }
 }
 
@@ -127,9 +127,11 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t* r) 
 // ---------------------------------------------------------------- descriptors
 // Shared-memory matrix descriptor (tcgen05 / "UMMA"): bits [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4,
 // [46,48) version=1, [49,52) base offset, [61,64) layout (2 = SWIZZLE_128B).
-__host__ __device__ constexpr uint64_t make_smem_desc_hi(uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// layout: 2 = SWIZZLE_128B (16-byte atoms), 1 = SWIZZLE_128B_BASE32B (32-byte atoms; the only layout the hardware
+// accepts for MN-major TF32 operands).
+__host__ __device__ constexpr uint64_t make_smem_desc_hi(uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout = 2) {
   return (uint64_t((lbo_bytes >> 4) & 0x3FFF) << 16) | (uint64_t((sbo_bytes >> 4) & 0x3FFF) << 32) |
-         (uint64_t(1) << 46) | (uint64_t(2) << 61);
+         (uint64_t(1) << 46) | (uint64_t(layout & 7) << 61);
 }
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint64_t hi_bits) {
   return hi_bits | uint64_t((smem_addr >> 4) & 0x3FFF);

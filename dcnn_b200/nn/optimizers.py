@@ -37,6 +37,9 @@ class Optimizer:
         """Stage this step's scalars on the device (stream-ordered, outside any captured graph)."""
         if self.hyper is None:
             return
+        import torch as _t
+        if self.hyper.is_cuda and _t.cuda.is_current_stream_capturing():
+            return
         lr, b1, b2 = self._hyper_values()
         self._hyper_host[0], self._hyper_host[1], self._hyper_host[2] = lr, b1, b2
         self.hyper.copy_(self._hyper_host, non_blocking=True)
@@ -97,6 +100,7 @@ class SGD(Optimizer):
     def update(self, zero_grads: bool = False):
         if not self.params:
             return
+        self.push_hyper()
         ops.sgd_update(self.params, self.grads, self.velocities, self.learning_rate, self.momentum,
                        zero_grads=zero_grads, hyper=self.hyper)
 
@@ -149,6 +153,7 @@ class Adam(Optimizer):
             return
         self.t += 1
         bc1, bc2 = self.bias_corrections()
+        self.push_hyper()
         ops.adam_update(self.params, self.grads, self.m, self.v, self.learning_rate, self.beta1,
                         self.beta2, self.epsilon, bc1, bc2, self.weight_decay,
                         self.decouple_weight_decay, zero_grads=zero_grads, hyper=self.hyper)

@@ -129,10 +129,8 @@ class TrainStep:
         self._calls += 1
         if self._graph is None:
             if self._calls <= 2:  # eager warm-up: lazy init, cudaFuncSetAttribute, pointer tables
-                self.optimizer.push_hyper()
                 return self._eager(x, t)
             self._static = (x.clone(), t.clone())
-            self.optimizer.push_hyper()
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
             with torch.cuda.graph(g):

@@ -18,15 +18,37 @@ def _clone_to(model, device):
 
 
 def _rel(a, b):
-    a, b = a.detach().cpu().float(), b.detach().cpu().float()
-    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+    """Relative L2 error (stable under TF32 rounding noise, unlike a max-norm ratio)."""
+    a, b = a.detach().cpu().double(), b.detach().cpu().double()
+    return float((a - b).norm() / (b.norm() + 1e-30))
 
 
+def _grad_err(gpu_grads, cpu_grads):
+    """Worst per-tensor relative L2 error, measured against the largest gradient norm in the model so that
+    analytically-zero gradients (a conv bias in front of BatchNorm) do not turn rounding noise into a ratio of 1."""
+    scale = max(float(g.detach().double().norm()) / max(1, g.numel()) ** 0.5 for g in cpu_grads)
+    worst = 0.0
+    for a, b in zip(gpu_grads, cpu_grads):
+        a, b = a.detach().cpu().double(), b.detach().cpu().double()
+        rms_b = float(b.norm()) / max(1, b.numel()) ** 0.5
+        err = float((a - b).norm()) / max(1, b.numel()) ** 0.5 / (rms_b + 1e-3 * scale)
+        worst = max(worst, err)
+    return worst
+
+
+# Exact mode (CUDA-core FP32 kernels) proves the layer/fusion logic with tight bounds.  TF32 mode gets statistical
+# bounds: a TF32-rounded pre-activation near zero flips its ReLU mask, so a fraction f of gradient elements differs
+# completely and the relative L2 error of dx is ~sqrt(f) per layer (the same holds for cuDNN's TF32 path).
+@pytest.mark.parametrize("exact", [True, False], ids=["fp32exact", "tf32"])
 @pytest.mark.parametrize("factory,shape,tol", [
-    (create_mnist_trainer, (8, 1, 28, 28), 5e-4),
-    (create_resnet9_cifar10, (8, 3, 32, 32), 3e-2),
+    (create_mnist_trainer, (8, 1, 28, 28), 2e-4),
+    (create_resnet9_cifar10, (8, 3, 32, 32), 2e-3),
 ])
-def test_model_forward_backward_matches_cpu(factory, shape, tol):
+def test_model_forward_backward_matches_cpu(factory, shape, tol, exact, monkeypatch):
+    if exact:
+        monkeypatch.setenv("DCNN_DISABLE_TC", "1")
+    else:
+        tol = max(tol * 30, 6e-3)
     torch.manual_seed(0)
     cpu = factory()
     cpu.set_seed(1)
@@ -39,12 +61,16 @@ def test_model_forward_backward_matches_cpu(factory, shape, tol):
     g = torch.randn_like(y_c)
     dx_c = cpu.backward(g)
     dx_g = gpu.backward(g.cuda())
-    assert _rel(dx_g, dx_c) < 10 * tol
-    worst = max(_rel(a, b) for a, b in zip(gpu.gradients(), cpu.gradients()))
-    assert worst < 20 * tol, worst
+    assert _rel(dx_g, dx_c) < 5 * tol, _rel(dx_g, dx_c)
+    worst = _grad_err(gpu.gradients(), cpu.gradients())
+    assert worst < 5 * tol, worst
 
 
-def test_resnet50_bottleneck_stage_matches_cpu():
+@pytest.mark.parametrize("exact", [True, False], ids=["fp32exact", "tf32"])
+def test_resnet50_bottleneck_stage_matches_cpu(exact, monkeypatch):
+    if exact:
+        monkeypatch.setenv("DCNN_DISABLE_TC", "1")
+    k = 1.0 if exact else 40.0
     torch.manual_seed(0)
     b = (dnn.SequentialBuilder("t").input([64, 16, 16])
          .bottleneck_residual_block(64, 64, 256, 1, "b1")
@@ -55,12 +81,12 @@ def test_resnet50_bottleneck_stage_matches_cpu():
     g = _clone_to(b, "cuda:0")
     x = torch.randn(8, 64, 16, 16)
     yc, yg = b.forward(x), g.forward(x.cuda())
-    assert _rel(yg, yc) < 2e-2
+    assert _rel(yg, yc) < 2e-4 * k, _rel(yg, yc)
     gr = torch.randn_like(yc)
     dc_, dg_ = b.backward(gr), g.backward(gr.cuda())
-    assert _rel(dg_, dc_) < 5e-2
-    worst = max(_rel(a, bb) for a, bb in zip(g.gradients(), b.gradients()))
-    assert worst < 8e-2, worst
+    assert _rel(dg_, dc_) < 4e-3 * k, _rel(dg_, dc_)
+    worst = _grad_err(g.gradients(), b.gradients())
+    assert worst < 4e-3 * k, worst
 
 
 def test_resnet50_training_step_runs_and_loss_decreases():
