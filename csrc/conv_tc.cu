@@ -255,6 +255,272 @@ __global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant
   }
 }
 
+
+// =====================================================================================================
+// conv_tc2: persistent, warp-specialised version of conv_tc_kernel.
+//   * one CTA per SM walks a static tile schedule (n-tile fastest); barriers, TMEM allocation and descriptor
+//     prefetch are paid once per CTA instead of once per tile;
+//   * the accumulator is double-buffered in TMEM (2 x BN columns): the MMA warp starts tile i+1 while the four
+//     epilogue warps drain tile i, so short-K layers (1x1 convs) are bounded by the store stream, not by a serial
+//     load -> MMA -> epilogue chain;
+//   * the epilogue stages the tile in 128B-swizzled shared memory and hands it to the TMA unit:
+//     cp.async.bulk.tensor store (or cp.reduce ... .add for the accumulate mode that sums residual-branch
+//     gradients); out-of-range rows/columns of edge tiles are clipped by the TMA unit, there is no per-row
+//     address arithmetic at all;
+//   * BatchNorm partial statistics are computed from the staged tile with conflict-free swizzled reads
+//     (shifted single pass: sum(x-k), sum((x-k)^2) with k = the tile's first row).
+// =====================================================================================================
+template <int BN, int STAGES>
+struct ConvTc2Smem {
+  static constexpr int kABytes = kBM * 128;
+  static constexpr int kBBytes = BN * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kPipeBytes = STAGES * kStageBytes;
+  static constexpr int kChunks = BN / 32;
+  static constexpr int kStagingBytes = kChunks * kBM * 128;
+  static constexpr int kRedBytes = 2 * 4 * BN * 4;  // [2][4 row groups][BN]
+  static constexpr int kBarOff = kPipeBytes + kStagingBytes;
+  static constexpr int kRedOff = kBarOff + 256;
+  static constexpr int kFlagOff = kRedOff + kRedBytes;
+  static constexpr int kTotalBytes = kFlagOff + 128 + 1024 /*align*/;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                               const __grid_constant__ CUtensorMap tmB,
+                                                               const __grid_constant__ CUtensorMap tmO,
+                                                               const __grid_constant__ ConvTcParams p) {
+  using S = ConvTc2Smem<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + S::kPipeBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  float* red = reinterpret_cast<float*>(smem + S::kRedOff);
+  uint8_t* row_valid = smem + S::kFlagOff;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int cchunks = p.Cin / kBK;
+  const int num_kb = p.num_taps * cchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full_bar[a], 1);
+        mbar_init(&tmem_empty_bar[a], 4);  // one arrival per epilogue warp
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % p.n_tiles;
+        const int m_tile = tile / p.n_tiles;
+        const int tw = m_tile % p.tiles_w;
+        const int th = (m_tile / p.tiles_w) % p.tiles_h;
+        const int tn = m_tile / (p.tiles_w * p.tiles_h);
+        const int n0 = tn * p.bn, ih0 = th * p.bh * p.in_mul_h, iw0 = tw * p.bw * p.in_mul_w;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int t = kb / cchunks;
+          const int c = kb - t * cchunks;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
+          uint8_t* sA = smem + stage * S::kStageBytes;
+          tma_load_4d(sA, &tmA, &full_bar[stage], c * kBK, iw0 + p.tap_dw[t], ih0 + p.tap_dh[t], n0);
+          tma_load_2d(sA + S::kABytes, &tmB, &full_bar[stage], p.tap_w[t] * p.Cin + c * kBK, n_tile * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===================== MMA issuer =====================
+      constexpr uint32_t idesc = make_idesc_tf32(kBM, BN, 0, 0);
+      constexpr uint64_t desc_hi = make_smem_desc_hi(16, 1024);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+          const uint32_t b_addr = a_addr + S::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 8; ++k)
+            mma_tf32_ss(tmem_d, make_smem_desc(a_addr + k * 32, desc_hi), make_smem_desc(b_addr + k * 32, desc_hi),
+                        idesc, (kb | k) != 0);
+          mma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&tmem_full_bar[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;          // TMEM lane quadrant
+    const int r = q * 32 + lane;     // tile row owned by this thread
+    const int e = threadIdx.x - 64;  // 0..127
+    const bool issuer = (e == 0);
+    const int w_l = r % p.bw, h_l = (r / p.bw) % p.bh, n_l = r / (p.bw * p.bh);
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int n_tile = tile % p.n_tiles;
+      const int m_tile = tile / p.n_tiles;
+      const int tw = m_tile % p.tiles_w;
+      const int th = (m_tile / p.tiles_w) % p.tiles_h;
+      const int tn = m_tile / (p.tiles_w * p.tiles_h);
+      const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
+      const int col_base = n_tile * BN;
+      const bool full_tile = (n0 + p.bn <= p.N) && (oh0 + p.bh <= p.OH) && (ow0 + p.bw <= p.OW);
+
+      mbar_wait(&tmem_full_bar[as], aphase);
+      tc_fence_after();
+      if (issuer) tma_store_wait_read();  // the previous tile's stores no longer read the staging buffer
+      if (p.partials != nullptr && !full_tile)
+        row_valid[r] = ((n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW)) ? 1 : 0;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+
+      const uint32_t tmem_d = tmem_base + as * BN + (uint32_t(q * 32) << 16);
+#pragma unroll 1
+      for (int ch = 0; ch < S::kChunks; ++ch) {
+        if (col_base + ch * 32 >= p.Cout) break;
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
+        tmem_ld_wait();
+        uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float4 o;
+          o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
+          o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
+          if (p.bias != nullptr) {
+            const int c = col_base + ch * 32 + 4 * j;
+            if (c < p.Cout) {  // Cout % 4 == 0 on this path
+              const float4 b = ldg4(p.bias + c);
+              o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+            }
+          }
+          *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
+        }
+      }
+      // accumulator fully read: hand the TMEM stage back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+
+      if (issuer) {
+        for (int ch = 0; ch < S::kChunks; ++ch) {
+          const int c = col_base + ch * 32;
+          if (c >= p.Cout) break;
+          if (p.accumulate) tma_reduce_add_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
+          else tma_store_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
+        }
+        tma_store_commit();
+      }
+
+      if (p.partials != nullptr) {
+        // shifted single pass over this thread's (column, 32-row group)
+        const int cl = e & 31, rg = e >> 5;
+        int cnt = kBM;
+        if (!full_tile) {
+          cnt = 0;
+          for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
+        }
+        for (int ch = 0; ch < S::kChunks; ++ch) {
+          if (col_base + ch * 32 >= p.Cout) break;
+          const uint8_t* src = staging + ch * (kBM * 128);
+          const float kshift = *reinterpret_cast<const float*>(src + (((cl >> 2) ^ 0) << 4) + ((cl & 3) << 2));  // row 0
+          float s = 0.f, qq = 0.f;
+          if (full_tile) {
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+              const int rr = rg * 32 + i;
+              const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
+                                                              ((cl & 3) << 2));
+              const float d = x - kshift;
+              s += d;
+              qq = fmaf(d, d, qq);
+            }
+          } else {
+            for (int i = 0; i < 32; ++i) {
+              const int rr = rg * 32 + i;
+              const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
+                                                              ((cl & 3) << 2));
+              const float d = row_valid[rr] ? x - kshift : 0.f;
+              s += d;
+              qq = fmaf(d, d, qq);
+            }
+          }
+          red[(0 * 4 + rg) * BN + ch * 32 + cl] = s;
+          red[(1 * 4 + rg) * BN + ch * 32 + cl] = qq;
+          if (rg == 0) red[(0 * 4 + 0) * BN + ch * 32 + cl] = s;  // (same value; keeps the compiler from hoisting)
+        }
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        for (int j = e; j < BN; j += 128) {
+          const int c = col_base + j;
+          if (c < p.Cout) {
+            const int ch = j >> 5, cl2 = j & 31;
+            const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) +
+                                                                 ((cl2 & 3) << 2));
+            const float s = red[(0 * 4 + 0) * BN + j] + red[(0 * 4 + 1) * BN + j] + red[(0 * 4 + 2) * BN + j] +
+                            red[(0 * 4 + 3) * BN + j];
+            const float qq = red[(1 * 4 + 0) * BN + j] + red[(1 * 4 + 1) * BN + j] + red[(1 * 4 + 2) * BN + j] +
+                             red[(1 * 4 + 3) * BN + j];
+            const float n = (float)cnt;
+            p.partials[((long long)m_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
+            p.partials[((long long)m_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
+          }
+        }
+        if (e == 0 && n_tile == 0) p.partials[(long long)p.m_tiles * 2 * p.Cout + m_tile] = (float)cnt;
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (issuer) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
 // =====================================================================================================
 // wgrad
 // =====================================================================================================
@@ -494,6 +760,40 @@ static void choose_box(int N, int OH, int OW, int pixels, int mul_h, int mul_w, 
   }
 }
 
+// Output view [N][OH][OW][Cout] with arbitrary element strides -> 4-D map, box {32, bw, bh, bn}
+static int make_tmap_out(CUtensorMap* tm, float* base, int N, int OH, int OW, int Cout, long long sn, long long sh,
+                         long long sw, int bn, int bh, int bw) {
+  PFN_tmapEncodeTiled enc = get_encode();
+  DCNN_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t gdim[4] = {(cuuint64_t)Cout, (cuuint64_t)OW, (cuuint64_t)OH, (cuuint64_t)N};
+  cuuint64_t gstr[3] = {(cuuint64_t)sw * 4, (cuuint64_t)sh * 4, (cuuint64_t)sn * 4};
+  cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DCNN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(out %dx%dx%dx%d strides %lld,%lld,%lld) failed: %d", N, OH,
+               OW, Cout, sn, sh, sw, (int)r);
+  return 0;
+}
+
+template <int BN, int STAGES>
+static int launch_conv2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const ConvTcParams& p,
+                        cudaStream_t stream) {
+  using S = ConvTc2Smem<BN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         S::kTotalBytes));
+    attr_set = true;
+  }
+  const long long tiles = (long long)p.m_tiles * p.n_tiles;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  conv_tc2_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, tmO, p);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
 template <int BN, int STAGES>
 static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvTcParams& p, cudaStream_t stream) {
   using S = ConvTcSmem<BN, STAGES>;
@@ -570,6 +870,23 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   CUtensorMap tmA, tmB;
   int rc = make_tmap_nhwc(&tmA, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
   if (rc) return rc;
+  static const bool use_v1 = getenv("DCNN_CONV_V1") != nullptr && atoi(getenv("DCNN_CONV_V1")) != 0;
+  if (vec_ok && !use_v1) {
+    // persistent kernel, TMA-store epilogue
+    CUtensorMap tmO;
+    rc = make_tmap_out(&tmO, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);
+    if (rc) return rc;
+    if (Cout <= 64) {
+      p.n_tiles = 1;
+      rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
+      if (rc) return rc;
+      return launch_conv2<64, 6>(tmA, tmB, tmO, p, stream);
+    }
+    p.n_tiles = ceil_div(Cout, 128);
+    rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
+    if (rc) return rc;
+    return launch_conv2<128, 4>(tmA, tmB, tmO, p, stream);
+  }
   if (Cout <= 64) {
     p.n_tiles = ceil_div(Cout, 64);
     rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);

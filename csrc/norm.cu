@@ -95,26 +95,35 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
                                                            float* __restrict__ invstd_out, float* __restrict__ scale_out,
                                                            float* __restrict__ shift_out,
                                                            double* __restrict__ export_moments) {
-  __shared__ double s_n[32][33], s_mean[32][33], s_m2[32][33];
+  __shared__ double s_n[32][33], s_s[32][33], s_q[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
-  Moments acc{0, 0, 0};
+  // Per tile we have (n, sum, M2 about the tile mean).  sum(x^2) of the tile = M2 + sum^2/n, so three plain FP64
+  // running sums per thread merge any number of tiles without a serial Chan update (no FP64 divide in the loop);
+  // the FP64 accumulation keeps the final M2 = Q - S^2/N accurate even when |mean| >> std.
+  double an = 0, as = 0, aq = 0;
   if (c < C) {
     const float* counts = partials + (long long)tiles * 2 * C;
+#pragma unroll 4
     for (int t = threadIdx.y; t < tiles; t += 32) {
-      const double n = counts[t];
-      if (n <= 0) continue;
-      const double s = partials[((long long)t * 2 + 0) * C + c];
-      const double m2 = partials[((long long)t * 2 + 1) * C + c];
-      acc = merge(acc, Moments{n, s / n, m2});
+      const float n = counts[t];
+      const float sf = partials[((long long)t * 2 + 0) * C + c];
+      const float m2 = partials[((long long)t * 2 + 1) * C + c];
+      const float rn = n > 0.f ? 1.f / n : 0.f;
+      an += (double)n;
+      as += (double)sf;
+      aq += (double)m2 + (double)sf * (double)sf * (double)rn;
     }
   }
-  s_n[threadIdx.y][threadIdx.x] = acc.n;
-  s_mean[threadIdx.y][threadIdx.x] = acc.mean;
-  s_m2[threadIdx.y][threadIdx.x] = acc.m2;
+  s_n[threadIdx.y][threadIdx.x] = an;
+  s_s[threadIdx.y][threadIdx.x] = as;
+  s_q[threadIdx.y][threadIdx.x] = aq;
   __syncthreads();
   if (threadIdx.y == 0 && c < C) {
-    for (int i = 1; i < 32; ++i)
-      acc = merge(acc, Moments{s_n[i][threadIdx.x], s_mean[i][threadIdx.x], s_m2[i][threadIdx.x]});
+    for (int i = 1; i < 32; ++i) {
+      an += s_n[i][threadIdx.x]; as += s_s[i][threadIdx.x]; aq += s_q[i][threadIdx.x];
+    }
+    Moments acc{an, an > 0 ? as / an : 0.0, 0.0};
+    acc.m2 = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
     if (export_moments != nullptr) {
       export_moments[0 * C + c] = acc.n;
       export_moments[1 * C + c] = acc.mean;
@@ -291,11 +300,13 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
   __shared__ double s_a[32][33], s_b[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   double a = 0, b = 0;
-  if (c < C)
+  if (c < C) {
+#pragma unroll 8
     for (int t = threadIdx.y; t < tiles; t += 32) {
       a += partials[((long long)t * 2 + 0) * C + c];
       b += partials[((long long)t * 2 + 1) * C + c];
     }
+  }
   s_a[threadIdx.y][threadIdx.x] = a;
   s_b[threadIdx.y][threadIdx.x] = b;
   __syncthreads();
