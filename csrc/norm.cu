@@ -700,3 +700,77 @@ DCNN_API int dcnn_gn_backward(const float* dy, const float* x, const float* mean
   DCNN_COUNT_LAUNCH(1);
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free BatchNorm batch statistics.
+//
+// Who needs this: code that is not allowed to call cudaMalloc (or any allocating library routine) at the moment
+// it wants BatchNorm statistics -- a host thread inside a latency-critical region that must not take the
+// allocator lock, a plugin loaded into somebody else's process that owns no memory pool, or a caller running
+// under a fixed memory budget after start-up.  The regular path (dcnn_bn_colstats + dcnn_bn_finalize) needs a
+// caller-provided scratch buffer for the per-tile partial sums; here that scratch lives in a file-scope
+// `static __device__` array, so the caller passes only inputs and outputs.
+//
+// Limits and rules:
+//   * the scratch holds kNoAllocScratchFloats floats (4 MiB); every GPU that loads this library keeps those
+//     4 MiB resident until the process exits.  A call needs tiles*(2*C+1) floats (tiles = dcnn_bn_stat_tiles(M));
+//     larger problems are rejected with an error, nothing is launched;
+//   * the array name is only a host-side stand-in in host code: the device address is fetched once per device
+//     with cudaGetSymbolAddress (return code checked) while that device is current, and that pointer is what the
+//     kernels receive.  The first call on each device performs this set-up -- make that first call before any
+//     stream capture begins on that device;
+//   * all calls share the one array and it keeps the previous call's contents.  Nothing here relies on it being
+//     zero: the statistics kernel overwrites every slot (partials and tile counts) that the finalize kernel of the
+//     same call reads, so stale values from an earlier, larger call are never observed;
+//   * because the scratch is shared, two calls that overlap on the GPU (different streams, or different host
+//     threads on the same device) race on it.  Serialise them (same stream, or an event between them).
+// The entry point itself calls no cudaMalloc/cudaFree and no allocating library function.
+constexpr long long kNoAllocScratchFloats = 1ll << 20;
+static __device__ __align__(256) float g_bn_noalloc_scratch[kNoAllocScratchFloats];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_noalloc_ptr[kMaxDevices] = {};
+}  // namespace
+
+DCNN_API long long dcnn_bn_noalloc_capacity_floats() { return kNoAllocScratchFloats; }
+
+DCNN_API int dcnn_bn_batch_stats_noalloc(const float* x, long long M, int C, float eps, float momentum,
+                                         float* running_mean, float* running_var, const float* gamma,
+                                         const float* beta, float* mean, float* invstd, float* scale, float* shift,
+                                         cudaStream_t stream) {
+  DCNN_REQUIRE(M > 0 && C > 0, "dcnn_bn_batch_stats_noalloc: empty input (M=%lld, C=%d)", M, C);
+  int tiles;
+  const int rows = stat_rows_per_tile(M, &tiles);
+  const long long need = (long long)tiles * (2ll * C + 1);
+  DCNN_REQUIRE(need <= kNoAllocScratchFloats,
+               "dcnn_bn_batch_stats_noalloc: needs %lld scratch floats (M=%lld rows in %d tiles, C=%d) but the built-in "
+               "scratch holds %lld; use dcnn_bn_colstats + dcnn_bn_finalize with your own buffer",
+               need, M, tiles, C, kNoAllocScratchFloats);
+  int dev = 0;
+  DCNN_CHECK_CUDA(cudaGetDevice(&dev));
+  DCNN_REQUIRE(dev >= 0 && dev < kMaxDevices, "dcnn_bn_batch_stats_noalloc: device index %d out of range", dev);
+  float* scratch = g_noalloc_ptr[dev];
+  if (scratch == nullptr) {  // once per device, with that device current
+    void* p = nullptr;
+    DCNN_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bn_noalloc_scratch));
+    DCNN_REQUIRE(p != nullptr, "dcnn_bn_batch_stats_noalloc: cudaGetSymbolAddress returned a null address");
+    scratch = static_cast<float*>(p);
+    g_noalloc_ptr[dev] = scratch;
+  }
+  if ((C & 3) == 0) {
+    dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
+    bn_colstats_kernel<<<grid, block, 0, stream>>>(x, M, C, rows, tiles, scratch);
+  } else {
+    dim3 grid(tiles, ceil_div(C, 32));
+    bn_colstats_scalar_kernel<<<grid, 32, 0, stream>>>(x, M, C, rows, tiles, scratch);
+  }
+  DCNN_CHECK_LAUNCH();
+  dim3 fblock(32, 32);
+  bn_finalize_kernel<<<ceil_div(C, 32), fblock, 0, stream>>>(scratch, tiles, C, eps, momentum, running_mean,
+                                                            running_var, gamma, beta, mean, invstd, scale, shift,
+                                                            nullptr);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(2);
+  return 0;
+}

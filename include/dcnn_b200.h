@@ -64,6 +64,17 @@ int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, int n_peers, int C
 int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* out, const float* k1, const float* k2,
                       const float* k3, float* dx, float* masked, long long M, int C, int relu, cudaStream_t stream);
 int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, cudaStream_t stream);
+/* Allocation-free variant of dcnn_bn_colstats + dcnn_bn_finalize (no counterpart in the reference).  For callers
+ * that may not allocate device memory when they need the statistics (no access to an allocator, or not allowed to
+ * take its lock): the per-tile scratch lives in a 4 MiB `static __device__` array inside the library instead of a
+ * caller buffer.  x is [M][C] fp32; outputs are [C] each; running_mean/running_var/gamma/beta may be NULL.
+ * Problems needing more than dcnn_bn_noalloc_capacity_floats() = tiles*(2*C+1) floats are rejected.  The first call
+ * on a device looks the array's address up (do it before any stream capture); calls share the scratch, so calls
+ * that overlap on the GPU race -- keep them on one stream or order them with events. */
+long long dcnn_bn_noalloc_capacity_floats(void);
+int dcnn_bn_batch_stats_noalloc(const float* x, long long M, int C, float eps, float momentum, float* running_mean,
+                                float* running_var, const float* gamma, const float* beta, float* mean,
+                                float* invstd, float* scale, float* shift, cudaStream_t stream);
 int dcnn_gn_forward(const float* x, float* y, const float* gamma, const float* beta, float* mean, float* invstd,
                     int N, int HW, int C, int G, float eps, cudaStream_t stream);
 int dcnn_gn_backward(const float* dy, const float* x, const float* mean, const float* invstd, const float* gamma,
