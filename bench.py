@@ -129,7 +129,7 @@ def main():
         parallelism = f"dp{world}"
     else:
         opt.attach(model.parameters(), model.gradients())
-    step = TrainStep(model, opt, loss_fn, use_cuda_graph=not args.no_graph and dp is None,
+    step = TrainStep(model, opt, loss_fn, use_cuda_graph=not args.no_graph,
                      num_microbatches=args.microbatches, data_parallel=dp)
 
     B = args.batch

@@ -10,49 +10,15 @@
 //     flags written with st.release.sys and polled with ld.acquire.sys;
 //   * peer_barrier_kernel: the same flag protocol as a standalone stream-ordered barrier (used by sync-BatchNorm
 //     around the exchange of per-channel moments, whose merge runs in norm.cu's *_sync kernels).
-#include "common.cuh"
+#include "peer.cuh"
 
 namespace dcnn {
 
-constexpr int kMaxPeers = 8;
+__global__ void epoch_bump_kernel(unsigned long long* counter) { *counter += 1; }
 
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-
-// peer data must never be served from this SM's L1 (it may hold last step's values): volatile == relaxed.sys
-__device__ __forceinline__ float4 ld_peer4(const float* p) {
-  float4 v;
-  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p)
-               : "memory");
-  return v;
-}
-
-struct PeerFlags {
-  unsigned long long* flags[kMaxPeers];  // flags[r] = rank r's flag array (kMaxPeers slots), mapped locally
-};
-
-// signal: write `epoch` into slot [rank] of every peer's flag array; wait: until every slot of OUR array >= epoch.
-__device__ __forceinline__ void peer_signal(const PeerFlags& pf, int rank, int world, unsigned long long epoch) {
-  __threadfence_system();
-  for (int r = 0; r < world; ++r) st_release_sys(pf.flags[r] + rank, epoch);
-}
-__device__ __forceinline__ void peer_wait(const PeerFlags& pf, int rank, int world, unsigned long long epoch) {
-  for (int r = 0; r < world; ++r) {
-    unsigned long long spins = 0;
-    while (ld_acquire_sys(pf.flags[rank] + r) < epoch) {
-      if (++spins > (1ull << 31)) __trap();  // a lost peer must not hang the GPU forever
-    }
-  }
-}
-
-__global__ void peer_barrier_kernel(PeerFlags pf, int rank, int world, unsigned long long epoch) {
+__global__ void peer_barrier_kernel(PeerFlags pf, int rank, int world, const unsigned long long* epoch_ptr) {
   if (threadIdx.x == 0) {
+    const unsigned long long epoch = *epoch_ptr;
     peer_signal(pf, rank, world, epoch);
     peer_wait(pf, rank, world, epoch);
   }
@@ -68,16 +34,20 @@ struct ArParams {
   PeerFlags start_flags, done_flags;
   unsigned int* block_counter;       // local, zero-initialised; reset by the last block
   int rank, world;
-  unsigned long long epoch;
+  const unsigned long long* epoch_ptr;  // device-resident, bumped by epoch_bump_kernel just before this kernel
+  const float* hyper;                   // optional device {lr, bc1, bc2} (CUDA-graph replay)
   float lr, a, b, eps, bc1, bc2, wd, inv_world;
   int mode;  // 0 SGD, 1 momentum, 2 Adam, 3 AdamW
 };
 
-__global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __grid_constant__ ArParams p) {
+__global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __grid_constant__ ArParams pp) {
+  ArParams p = pp;
+  const unsigned long long epoch = *p.epoch_ptr;
+  if (p.hyper != nullptr) { p.lr = p.hyper[0]; p.bc1 = p.hyper[1]; p.bc2 = p.hyper[2]; }
   // every block waits until all replicas have finished producing gradients for this epoch
   if (threadIdx.x == 0) {
-    if (blockIdx.x == 0) peer_signal(p.start_flags, p.rank, p.world, p.epoch);
-    peer_wait(p.start_flags, p.rank, p.world, p.epoch);
+    if (blockIdx.x == 0) peer_signal(p.start_flags, p.rank, p.world, epoch);
+    peer_wait(p.start_flags, p.rank, p.world, epoch);
   }
   __syncthreads();
 
@@ -141,15 +111,16 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __gri
     const unsigned int done = atomicAdd(p.block_counter, 1u);
     if (done == gridDim.x - 1) {
       *p.block_counter = 0;
-      peer_signal(p.done_flags, p.rank, p.world, p.epoch);
+      peer_signal(p.done_flags, p.rank, p.world, epoch);
     }
   }
 }
 
 // Waits for every replica's "done" signal of this epoch, then zeroes the local gradient buffer.
 __global__ void __launch_bounds__(512) wait_done_zero_kernel(PeerFlags done_flags, int rank, int world,
-                                                             unsigned long long epoch, float* grads, long long n) {
-  if (threadIdx.x == 0) peer_wait(done_flags, rank, world, epoch);
+                                                             const unsigned long long* epoch_ptr, float* grads,
+                                                             long long n) {
+  if (threadIdx.x == 0) peer_wait(done_flags, rank, world, *epoch_ptr);
   __syncthreads();
   const long long n4 = n >> 2;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
@@ -202,14 +173,15 @@ static int fill_flags(PeerFlags* pf, unsigned long long* const* ptrs, int world)
 }
 
 // flag_ptrs[r]: rank r's flag array (>= 8 u64, zero-initialised) as mapped in THIS process
-DCNN_API int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, int world, unsigned long long epoch,
-                               cudaStream_t stream) {
+DCNN_API int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, int world,
+                               unsigned long long* epoch_counter, cudaStream_t stream) {
   PeerFlags pf;
   int rc = fill_flags(&pf, flag_ptrs, world);
   if (rc) return rc;
-  peer_barrier_kernel<<<1, 32, 0, stream>>>(pf, rank, world, epoch);
+  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
+  peer_barrier_kernel<<<1, 32, 0, stream>>>(pf, rank, world, epoch_counter);
   DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(1);
+  DCNN_COUNT_LAUNCH(2);
   return 0;
 }
 
@@ -217,9 +189,9 @@ DCNN_API int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* 
                                          long long n, long long shard_begin, long long shard_end,
                                          unsigned long long* const* start_flag_ptrs,
                                          unsigned long long* const* done_flag_ptrs, unsigned int* block_counter,
-                                         int rank, int world, unsigned long long epoch, int mode, float lr, float a,
-                                         float b, float eps, float bc1, float bc2, float wd, int num_blocks,
-                                         cudaStream_t stream) {
+                                         int rank, int world, unsigned long long* epoch_counter, int mode, float lr,
+                                         float a, float b, float eps, float bc1, float bc2, float wd,
+                                         const float* hyper, int num_blocks, cudaStream_t stream) {
   DCNN_REQUIRE((shard_begin & 3) == 0 && (shard_end & 3) == 0 && (n & 3) == 0,
                "fused all-reduce needs 4-element aligned shards");
   ArParams p;
@@ -230,14 +202,15 @@ DCNN_API int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* 
   rc = fill_flags(&p.done_flags, done_flag_ptrs, world);
   if (rc) return rc;
   p.s1 = s1; p.s2 = s2; p.n = n; p.shard_begin = shard_begin; p.shard_end = shard_end;
-  p.block_counter = block_counter; p.rank = rank; p.world = world; p.epoch = epoch;
+  p.block_counter = block_counter; p.rank = rank; p.world = world; p.epoch_ptr = epoch_counter; p.hyper = hyper;
   p.lr = lr; p.a = a; p.b = b; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2; p.wd = wd; p.inv_world = 1.f / (float)world;
   p.mode = mode;
   if (num_blocks <= 0) num_blocks = num_sms();
+  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
   fused_allreduce_update_kernel<<<num_blocks, 512, 0, stream>>>(p);
   DCNN_CHECK_LAUNCH();
-  wait_done_zero_kernel<<<num_sms(), 512, 0, stream>>>(p.done_flags, rank, world, epoch, grad_ptrs[rank], n);
+  wait_done_zero_kernel<<<num_sms(), 512, 0, stream>>>(p.done_flags, rank, world, epoch_counter, grad_ptrs[rank], n);
   DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(2);
+  DCNN_COUNT_LAUNCH(3);
   return 0;
 }

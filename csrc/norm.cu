@@ -7,7 +7,7 @@
 // reference's Welford kernel, batchnorm_ops.cu:108-155), updates the running statistics (unbiased variance,
 // momentum) and precomputes scale/shift so the apply pass is one FMA per element with ReLU / residual fused.
 // Backward = one reduce pass (ReLU mask folded in) + finalize + one apply pass (dx = g*k1 + x*k2 + k3).
-#include "common.cuh"
+#include "peer.cuh"
 
 namespace dcnn {
 
@@ -146,18 +146,27 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
   }
 }
 
-// Cross-replica finish: merge every replica's exported moments (peer pointers over NVLink / NVSwitch).
-__global__ void bn_finalize_sync_kernel(const double* const* __restrict__ peer_moments, int n_peers, int C, float eps,
+// Cross-replica finish (sync-BN, K27), fused with the rendezvous: block 0 publishes "my moments are exported" to every
+// replica (st.release.sys), every block waits until all replicas have published this epoch (ld.acquire.sys), then each
+// thread merges its channel's (n, mean, M2) from every replica's symmetric buffer over NVLink peer loads.
+__global__ void bn_finalize_sync_kernel(PeerPtrs peer_moments, PeerFlags flags, int rank,
+                                        const unsigned long long* epoch_ptr, int n_peers, int C, float eps,
                                         float momentum, float* __restrict__ running_mean,
                                         float* __restrict__ running_var, const float* __restrict__ gamma,
                                         const float* __restrict__ beta, float* __restrict__ mean_out,
                                         float* __restrict__ invstd_out, float* __restrict__ scale_out,
                                         float* __restrict__ shift_out) {
+  if (threadIdx.x == 0) {
+    const unsigned long long epoch = *epoch_ptr;
+    if (blockIdx.x == 0) peer_signal(flags, rank, n_peers, epoch);
+    peer_wait(flags, rank, n_peers, epoch);
+  }
+  __syncthreads();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   Moments acc{0, 0, 0};
   for (int r = 0; r < n_peers; ++r) {
-    const double* pm = peer_moments[r];
+    const volatile double* pm = peer_moments.p[r];  // volatile: never served from a stale L1 line
     acc = merge(acc, Moments{pm[0 * C + c], pm[1 * C + c], pm[2 * C + c]});
   }
   const double var = acc.n > 0 ? acc.m2 / acc.n : 0.0;
@@ -331,15 +340,22 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
   }
 }
 
-__global__ void bn_bwd_finalize_sync_kernel(const double* const* __restrict__ peer_sums, int n_peers, int C,
+__global__ void bn_bwd_finalize_sync_kernel(PeerPtrs peer_sums, PeerFlags flags, int rank,
+                                            const unsigned long long* epoch_ptr, int n_peers, int C,
                                             const float* __restrict__ mean, const float* __restrict__ invstd,
                                             const float* __restrict__ gamma, float* __restrict__ k1,
                                             float* __restrict__ k2, float* __restrict__ k3) {
+  if (threadIdx.x == 0) {
+    const unsigned long long epoch = *epoch_ptr;
+    if (blockIdx.x == 0) peer_signal(flags, rank, n_peers, epoch);
+    peer_wait(flags, rank, n_peers, epoch);
+  }
+  __syncthreads();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   double a = 0, b = 0, n = 0;
   for (int r = 0; r < n_peers; ++r) {
-    const double* p = peer_sums[r];
+    const volatile double* p = peer_sums.p[r];
     a += p[0 * C + c]; b += p[1 * C + c]; n += p[2 * C + c];
   }
   const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
@@ -567,13 +583,32 @@ DCNN_API int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps
   return 0;
 }
 
-DCNN_API int dcnn_bn_finalize_sync(const double* const* peer_moments, int n_peers, int C, float eps, float momentum,
+static int fill_peers(PeerPtrs* pp, PeerFlags* pf, const double* const* ptrs, unsigned long long* const* flag_ptrs,
+                      int n_peers) {
+  DCNN_REQUIRE(n_peers >= 1 && n_peers <= kMaxPeers, "sync-BN: %d replicas out of range (max %d)", n_peers, kMaxPeers);
+  for (int r = 0; r < kMaxPeers; ++r) {
+    pp->p[r] = r < n_peers ? ptrs[r] : nullptr;
+    pf->flags[r] = r < n_peers ? flag_ptrs[r] : nullptr;
+  }
+  return 0;
+}
+
+// peer_moments[r] / flag_ptrs[r]: replica r's exported-moments buffer and flag array as mapped in THIS process (host
+// arrays of device pointers); epoch_counter: this rank's device-resident rendezvous counter.
+DCNN_API int dcnn_bn_finalize_sync(const double* const* peer_moments, unsigned long long* const* flag_ptrs, int rank,
+                                   unsigned long long* epoch_counter, int n_peers, int C, float eps, float momentum,
                                    float* running_mean, float* running_var, const float* gamma, const float* beta,
                                    float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream) {
-  bn_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(peer_moments, n_peers, C, eps, momentum, running_mean,
-                                                               running_var, gamma, beta, mean, invstd, scale, shift);
+  PeerPtrs pp;
+  PeerFlags pf;
+  int rc = fill_peers(&pp, &pf, peer_moments, flag_ptrs, n_peers);
+  if (rc) return rc;
+  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
+  bn_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(pp, pf, rank, epoch_counter, n_peers, C, eps, momentum,
+                                                               running_mean, running_var, gamma, beta, mean, invstd,
+                                                               scale, shift);
   DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(1);
+  DCNN_COUNT_LAUNCH(2);
   return 0;
 }
 
@@ -633,13 +668,19 @@ DCNN_API int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, doubl
   return 0;
 }
 
-DCNN_API int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, int n_peers, int C, const float* mean,
+DCNN_API int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, unsigned long long* const* flag_ptrs, int rank,
+                                       unsigned long long* epoch_counter, int n_peers, int C, const float* mean,
                                        const float* invstd, const float* gamma, float* k1, float* k2, float* k3,
                                        cudaStream_t stream) {
-  bn_bwd_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(peer_sums, n_peers, C, mean, invstd, gamma, k1, k2,
-                                                                   k3);
+  PeerPtrs pp;
+  PeerFlags pf;
+  int rc = fill_peers(&pp, &pf, peer_sums, flag_ptrs, n_peers);
+  if (rc) return rc;
+  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
+  bn_bwd_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(pp, pf, rank, epoch_counter, n_peers, C, mean,
+                                                                   invstd, gamma, k1, k2, k3);
   DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(1);
+  DCNN_COUNT_LAUNCH(2);
   return 0;
 }
 

@@ -138,6 +138,12 @@ class ResidualBlock(Layer):
     def has_parameters(self):
         return any(l.has_parameters() for l in self._all())
 
+    def rebind_parameters(self, params, grads):
+        used = 0
+        for l in self._all():
+            used += l.rebind_parameters(params[used:], grads[used:])
+        return used
+
     def clear_gradients(self):
         for l in self._all():
             l.clear_gradients()

@@ -97,6 +97,21 @@ class Layer:
     def has_parameters(self) -> bool:
         return False
 
+    #: attribute names behind parameters()/gradients(), in order (used to re-home them into flat buffers)
+    _param_attrs: tuple = ()
+    _grad_attrs: tuple = ()
+
+    def rebind_parameters(self, params, grads):
+        """Replace this layer's parameter/gradient tensors by same-shaped views (e.g. slices of a flat,
+        NVLink-shared buffer).  Values are copied into the new storage.  Returns the number consumed."""
+        live = [(a, g) for a, g in zip(self._param_attrs, self._grad_attrs) if getattr(self, a) is not None]
+        for i, (a, g) in enumerate(live):
+            params[i].copy_(getattr(self, a))
+            grads[i].copy_(getattr(self, g))
+            setattr(self, a, params[i])
+            setattr(self, g, grads[i])
+        return len(live)
+
     def clear_gradients(self):
         for g in self.gradients():
             g.zero_()
@@ -182,6 +197,8 @@ class Conv2DLayer(Layer):
     cudnn_conv2d_ops.cu:226,242)."""
 
     type_name = "conv2d"
+    _param_attrs = ("weights", "bias")
+    _grad_attrs = ("weight_grad", "bias_grad")
 
     def __init__(self, in_channels, out_channels, kernel_h, kernel_w, stride_h=1, stride_w=1,
                  pad_h=0, pad_w=0, use_bias=True, name="conv2d"):
@@ -296,6 +313,8 @@ class DenseLayer(Layer):
     ``C*H*W == input_features`` and emits ``[N,out,1,1]`` (dense_layer.tpp:64-88)."""
 
     type_name = "dense"
+    _param_attrs = ("weights", "bias")
+    _grad_attrs = ("weight_grad", "bias_grad")
 
     def __init__(self, input_features, output_features, use_bias=True, name="dense"):
         super().__init__(name)
@@ -394,6 +413,8 @@ class BatchNormLayer(Layer):
     kernel then reads every replica's partial sums over NVLink peer memory (K27)."""
 
     type_name = "batchnorm"
+    _param_attrs = ("gamma", "beta")
+    _grad_attrs = ("gamma_grad", "beta_grad")
 
     def __init__(self, num_features, epsilon=1e-5, momentum=0.1, affine=True, name="batchnorm"):
         super().__init__(name)
@@ -495,6 +516,8 @@ class GroupNormLayer(Layer):
     """Group normalisation (ref groupnorm_layer.{hpp,tpp}, groupnorm_ops.cu:45-252)."""
 
     type_name = "groupnorm"
+    _param_attrs = ("gamma", "beta")
+    _grad_attrs = ("gamma_grad", "beta_grad")
 
     def __init__(self, num_groups, num_channels, epsilon=1e-5, affine=True, name="groupnorm"):
         super().__init__(name)

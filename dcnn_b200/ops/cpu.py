@@ -127,11 +127,11 @@ def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, wa
     sum_dy = g.sum(dim=(0, 2, 3))
     sum_dy_xhat = (g * xhat).sum(dim=(0, 2, 3))
     m = x.numel() // c
-    if sync is not None:
-        sum_dy, sum_dy_xhat, m = sync.merge_bwd_cpu(sum_dy, sum_dy_xhat, m)
-    if dgamma is not None:
+    if dgamma is not None:  # local contribution; the data-parallel gradient all-reduce averages the replicas
         dgamma.add_(sum_dy_xhat.view_as(dgamma))
         dbeta.add_(sum_dy.view_as(dbeta))
+    if sync is not None:
+        sum_dy, sum_dy_xhat, m = sync.merge_bwd_cpu(sum_dy, sum_dy_xhat, m)
     scale = invstd if gamma is None else invstd * gamma.view(-1)
     dx = (g - (sum_dy / m).view(1, c, 1, 1) - xhat * (sum_dy_xhat / m).view(1, c, 1, 1)) \
         * scale.view(1, c, 1, 1)

@@ -46,7 +46,8 @@ int dcnn_bn_colstats(const float* x, long long M, int C, float* partials, cudaSt
 int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
                      float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
                      float* scale, float* shift, double* export_moments, cudaStream_t stream);
-int dcnn_bn_finalize_sync(const double* const* peer_moments, int n_peers, int C, float eps, float momentum,
+int dcnn_bn_finalize_sync(const double* const* peer_moments, unsigned long long* const* flag_ptrs, int rank,
+                          unsigned long long* epoch_counter, int n_peers, int C, float eps, float momentum,
                           float* running_mean, float* running_var, const float* gamma, const float* beta, float* mean,
                           float* invstd, float* scale, float* shift, cudaStream_t stream);
 int dcnn_bn_eval_coeffs(const float* rm, const float* rv, const float* gamma, const float* beta, float eps, int C,
@@ -58,7 +59,8 @@ int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, cons
 int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
                          const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1, float* k2,
                          float* k3, double* export_sums, cudaStream_t stream);
-int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, int n_peers, int C, const float* mean,
+int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, unsigned long long* const* flag_ptrs, int rank,
+                              unsigned long long* epoch_counter, int n_peers, int C, const float* mean,
                               const float* invstd, const float* gamma, float* k1, float* k2, float* k3,
                               cudaStream_t stream);
 int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* out, const float* k1, const float* k2,
@@ -119,14 +121,14 @@ int dcnn_ipc_get_handle(void* ptr, unsigned char* handle64);
 int dcnn_ipc_open(const unsigned char* handle64, void** ptr);
 int dcnn_ipc_close(void* ptr);
 int dcnn_enable_peer_access(int peer_device);
-int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, int world, unsigned long long epoch,
+int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, int world, unsigned long long* epoch_counter,
                       cudaStream_t stream);
 int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* param_ptrs, float* s1, float* s2, long long n,
                                 long long shard_begin, long long shard_end,
                                 unsigned long long* const* start_flag_ptrs, unsigned long long* const* done_flag_ptrs,
-                                unsigned int* block_counter, int rank, int world, unsigned long long epoch, int mode,
-                                float lr, float a, float b, float eps, float bc1, float bc2, float wd, int num_blocks,
-                                cudaStream_t stream);
+                                unsigned int* block_counter, int rank, int world, unsigned long long* epoch_counter,
+                                int mode, float lr, float a, float b, float eps, float bc1, float bc2, float wd,
+                                const float* hyper, int num_blocks, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,73 @@
+"""Data-parallel logic on CPU (gloo, world_size 2): R replicas with sync-BatchNorm and averaged gradients must take
+exactly the same optimisation step as one process on the concatenated batch (SURVEY §4 test plan item 2)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from dcnn_b200 import nn as dnn
+from dcnn_b200.train import TrainStep
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _model():
+    m = (dnn.SequentialBuilder("dp_test").input([3, 8, 8])
+         .conv2d(8, 3, 3, 1, 1, 1, 1, True, "c1").batchnorm(1e-5, 0.1, True, "bn1").activation("relu", "r1")
+         .basic_residual_block(8, 16, 2, "rb")
+         .avgpool2d(4, 4, 1, 1, 0, 0, "ap").flatten("f").dense(5, True, "fc").build())
+    m.set_seed(3)
+    m.initialize()
+    return m
+
+
+def _data():
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(8, 3, 8, 8, generator=g)
+    t = torch.nn.functional.one_hot(torch.randint(0, 5, (8,), generator=g), 5).float().reshape(8, 5, 1, 1)
+    return x, t
+
+
+def _worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from dcnn_b200.parallel.dp import DataParallel
+    torch.set_num_threads(1)
+    m = _model()
+    opt = dnn.SGD(0.05, 0.9)  # SGD: linear in the gradients (Adam would amplify the rounding noise of the analytically-zero conv-bias-before-BN gradients)
+    dp = DataParallel(m, opt, dist.group.WORLD, sync_bn=True)
+    step = TrainStep(m, opt, dnn.SoftmaxCrossEntropyLoss(), data_parallel=dp)
+    x, t = _data()
+    lo, hi = rank * 4, rank * 4 + 4
+    for _ in range(2):
+        step(x[lo:hi], t[lo:hi])
+    if rank == 0:
+        torch.save([p.clone() for p in m.parameters()] + list(m.buffers().values()), out)
+    dist.destroy_process_group()
+
+
+def test_dp2_syncbn_equals_single_process(tmp_path):
+    out = str(tmp_path / "dp.pt")
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    m = _model()
+    opt = dnn.SGD(0.05, 0.9)  # SGD: linear in the gradients (Adam would amplify the rounding noise of the analytically-zero conv-bias-before-BN gradients)
+    opt.attach(m.parameters(), m.gradients())
+    step = TrainStep(m, opt, dnn.SoftmaxCrossEntropyLoss())
+    x, t = _data()
+    for _ in range(2):
+        step(x, t)
+    ref = [p for p in m.parameters()] + list(m.buffers().values())
+    assert len(got) == len(ref)
+    for a, b in zip(got, ref):
+        assert torch.allclose(a, b, atol=2e-5, rtol=1e-4), (a - b).abs().max()
