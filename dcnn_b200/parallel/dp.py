@@ -159,6 +159,14 @@ class DataParallel:
         quantum = 4 * self.world
         self.n = (total + quantum - 1) // quantum * quantum
         self.offsets = offs
+        if self.device.type == "cuda":
+            # rendezvous state shared by the fused update and sync-BN: symmetric epoch flags + local counters
+            self.ctl = SymmetricBuffer(3 * 64, self.group, self.device)
+            self.start_flags = self.ctl.peer_array(0)
+            self.done_flags = self.ctl.peer_array(64)
+            self.bn_flags = self.ctl.peer_array(128)
+            self.local = torch.zeros(8, dtype=torch.int64, device=self.device)  # [0] block ctr, [1] epoch, [2] bn epoch
+            self.bn_epoch_ptr = self.local.data_ptr() + 16
         if self.fused:
             self._setup_fused(params)
         else:
@@ -173,8 +181,8 @@ class DataParallel:
     # ------------------------------------------------------------------------------------------------
     def _setup_fused(self, params):
         n = self.n
-        # layout: [params n floats][grads n floats][start flags 8 u64][done flags 8 u64][bn flags 8 u64]
-        self.buf = SymmetricBuffer(8 * n + 3 * 64, self.group, self.device)
+        # layout: [params n floats][grads n floats]
+        self.buf = SymmetricBuffer(8 * n, self.group, self.device)
         self.flat_param = self.buf.view(torch.float32, 0, n)
         self.flat_grad = self.buf.view(torch.float32, 4 * n, n)
         new_p, new_g = [], []
@@ -199,20 +207,16 @@ class DataParallel:
         self.s1 = torch.zeros(shard, device=self.device) if (isinstance(opt, Adam) or getattr(opt, "momentum", 0) > 0) \
             else None
         self.s2 = torch.zeros(shard, device=self.device) if isinstance(opt, Adam) else None
-        self.local = torch.zeros(8, dtype=torch.int64, device=self.device)  # [0]=block counter, [1]=epoch, [2]=bn epoch
         opt.params, opt.grads = self.model.parameters(), self.model.gradients()   # for clear_gradients()/introspection
         self.grad_ptrs = self.buf.peer_array(4 * self.n)
         self.param_ptrs = self.buf.peer_array(0)
-        self.start_flags = self.buf.peer_array(8 * self.n)
-        self.done_flags = self.buf.peer_array(8 * self.n + 64)
-        self.bn_flags = self.buf.peer_array(8 * self.n + 128)
-        self.bn_epoch_ptr = self.local.data_ptr() + 16
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
 
     def _setup_sync_bn(self):
         bns = [l for l in _all_layers(self.model) if isinstance(l, BatchNormLayer)]
-        if self.fused:
+        on_gpu = self.device.type == "cuda"
+        if on_gpu:
             total = sum(SyncBN.bytes_needed(l.num_features) for l in bns)
             self.bn_buf = SymmetricBuffer(total, self.group, self.device)
         off = 0
@@ -221,7 +225,7 @@ class DataParallel:
             off += SyncBN.bytes_needed(l.num_features)
             l.sync = s
             self.sync_objs.append(s)
-        if self.fused:
+        if on_gpu:
             torch.cuda.synchronize()
             dist.barrier(group=self.group)
 

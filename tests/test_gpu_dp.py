@@ -96,10 +96,10 @@ def test_fused_allreduce_update_matches_nccl_baseline_and_single_gpu(kind, tmp_p
         mp.spawn(_worker, args=(world, _free_port(), out, kind, baseline), nprocs=world, join=True)
         res[baseline] = torch.load(out)
     single = _single(kind, world)
-    # fused (P2P kernel) vs NCCL baseline: same arithmetic up to summation order
-    worst_fb = max(_err(a, b) for a, b in zip(res[False], res[True]))
-    # vs one GPU on the concatenated batch (sync-BN makes the statistics identical up to TF32/ordering noise)
-    worst_fs = max(_err(a, b) for a, b in zip(res[False], single))
-    tol = 2e-3 if kind == "sgd" else 5e-2   # Adam normalises near-zero gradients, amplifying rounding noise
-    assert worst_fb < tol, worst_fb
-    assert worst_fs < tol, worst_fs
+    # fused (P2P kernel) vs NCCL baseline: same arithmetic up to summation order.
+    # vs one GPU on the concatenated batch: sync-BN makes the statistics identical up to ordering noise.  Mixed
+    # abs/rel bound: BN betas start at 0 and stay tiny after 3 steps, so a pure relative error would just measure noise.
+    atol, rtol = (5e-4, 5e-3) if kind == "sgd" else (5e-3, 5e-2)   # Adam normalises near-zero gradients
+    for name, other in (("nccl-baseline", res[True]), ("single-gpu", single)):
+        for i, (a, b) in enumerate(zip(res[False], other)):
+            assert torch.allclose(a, b, rtol=rtol, atol=atol), (name, i, tuple(a.shape), float((a - b).abs().max()))
