@@ -1,0 +1,236 @@
+"""Communicators (ref include/pipeline/communicator.hpp:27-169, concurrent_message_map.hpp,
+in_process_communicator.hpp, tcp_communicator.hpp).
+
+``Communicator`` keeps one input queue per CommandType and dequeues in enum order, so FORWARD_JOB is served before
+BACKWARD_JOB -- the reference's emergent stage scheduling (communicator.hpp:100-110).
+
+Backends:
+  * ``InProcessCommunicator`` -- thread-safe direct delivery between communicators in one process (tests, and
+    single-process multi-GPU).  Includes a test-only fault-injection hook (drop / delay).
+  * ``DistCommunicator``      -- one process per participant over torch.distributed.  Control messages (and tensor
+    metadata) go through the c10d store as a per-rank mailbox; tensors go straight device-to-device with
+    ``dist.send/recv`` (NCCL p2p over NVLink on GPUs, gloo on CPU).  This replaces the reference's ASIO TCP transport
+    and its GPU->host->TCP->host->GPU path."""
+from __future__ import annotations
+
+import collections
+import pickle
+import threading
+import time
+from typing import Callable, Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .protocol import CommandType, Endpoint, Job, Message
+
+
+class Communicator:
+    def __init__(self, comm_id: str = ""):
+        self.id = comm_id
+        self._queues: Dict[CommandType, collections.deque] = {c: collections.deque() for c in CommandType}
+        self._lock = threading.Lock()
+        self._cv = threading.Condition(self._lock)
+        self._callback: Optional[Callable[[], None]] = None
+        self._recipients: Dict[str, Endpoint] = {}
+
+    # -- registry -------------------------------------------------------------------------------
+    def connect(self, recipient_id: str, endpoint: Endpoint) -> bool:
+        self._recipients[recipient_id] = endpoint
+        return True
+
+    def disconnect(self, recipient_id: str):
+        self._recipients.pop(recipient_id, None)
+
+    def get_recipient(self, recipient_id: str) -> Endpoint:
+        if recipient_id not in self._recipients:
+            raise KeyError(f"{self.id}: unknown recipient '{recipient_id}'")
+        return self._recipients[recipient_id]
+
+    def set_message_notification_callback(self, cb: Callable[[], None]):
+        self._callback = cb
+
+    # -- input side -----------------------------------------------------------------------------
+    def enqueue_input_message(self, msg: Message):
+        with self._cv:
+            self._queues[msg.command_type].append(msg)
+            self._cv.notify_all()
+        if self._callback:
+            self._callback()
+
+    def has_input_message(self) -> bool:
+        with self._lock:
+            return any(self._queues[c] for c in CommandType)
+
+    def message_count(self, ctype: CommandType) -> int:
+        with self._lock:
+            return len(self._queues[ctype])
+
+    def dequeue_input_message(self) -> Optional[Message]:
+        """Highest-priority (lowest enum value) pending message, or None."""
+        with self._lock:
+            for c in CommandType:
+                if self._queues[c]:
+                    return self._queues[c].popleft()
+        return None
+
+    def dequeue_message_by_type(self, ctype: CommandType) -> Optional[Message]:
+        with self._lock:
+            return self._queues[ctype].popleft() if self._queues[ctype] else None
+
+    def dequeue_all_messages_by_type(self, ctype: CommandType) -> List[Message]:
+        with self._lock:
+            out = list(self._queues[ctype])
+            self._queues[ctype].clear()
+            return out
+
+    def wait_for_input(self, timeout: Optional[float] = None) -> bool:
+        self.poll()
+        with self._cv:
+            if any(self._queues[c] for c in CommandType):
+                return True
+            self._cv.wait(timeout)
+            return any(self._queues[c] for c in CommandType)
+
+    def wait_for_count(self, ctype: CommandType, count: int, timeout: float) -> bool:
+        deadline = time.monotonic() + timeout
+        while True:
+            self.poll()
+            with self._cv:
+                if len(self._queues[ctype]) >= count:
+                    return True
+                left = deadline - time.monotonic()
+                if left <= 0:
+                    return False
+                self._cv.wait(min(left, 0.05))
+
+    # -- output side ----------------------------------------------------------------------------
+    def send_message(self, msg: Message):
+        raise NotImplementedError
+
+    def poll(self):
+        """Backends that pull (DistCommunicator) fetch pending messages here."""
+
+    def flush_output_messages(self):
+        pass
+
+    def close(self):
+        pass
+
+
+class InProcessCommunicator(Communicator):
+    #: test-only fault injection: callable(msg) -> "drop" | float seconds of delay | None
+    fault_hook: Optional[Callable[[Message], object]] = None
+
+    def send_message(self, msg: Message):
+        if not msg.sender_id:
+            msg.sender_id = self.id
+        ep = self.get_recipient(msg.recipient_id)
+        if ep.communicator is None:
+            raise RuntimeError(f"{self.id}: endpoint for '{msg.recipient_id}' has no in-process communicator")
+        hook = InProcessCommunicator.fault_hook
+        if hook is not None:
+            verdict = hook(msg)
+            if verdict == "drop":
+                return
+            if isinstance(verdict, (int, float)) and verdict > 0:
+                threading.Timer(float(verdict), ep.communicator.enqueue_input_message, args=(msg,)).start()
+                return
+        ep.communicator.enqueue_input_message(msg)
+
+
+class DistCommunicator(Communicator):
+    """torch.distributed backend; every participant (coordinator included) is one rank of ``control_group``.
+    ``data_group`` is the group used for tensor send/recv (NCCL between GPU stages); when the peer of a tensor
+    transfer is not a member of it (the CPU-side coordinator), the tensor goes over ``control_group`` (gloo)."""
+
+    def __init__(self, comm_id: str, rank: int, store, control_group=None, data_group=None, data_ranks=None,
+                 device: Optional[torch.device] = None):
+        super().__init__(comm_id)
+        self.rank = rank
+        self.store = store
+        self.control_group, self.data_group = control_group, data_group
+        self.data_ranks = set(data_ranks) if data_ranks is not None else None
+        self.device = device or torch.device("cpu")
+        self._send_seq: Dict[int, int] = collections.defaultdict(int)
+        self._recv_seq = 0
+
+    def _key(self, dst: int, seq: int) -> str:
+        return f"mbox/{dst}/{seq}"
+
+    def _tensor_route(self, peer: int):
+        if self.data_group is not None and self.data_ranks is not None and peer in self.data_ranks \
+                and self.rank in self.data_ranks:
+            return self.data_group, self.device
+        return self.control_group, torch.device("cpu")
+
+    def send_message(self, msg: Message):
+        if not msg.sender_id:
+            msg.sender_id = self.id
+        ep = self.get_recipient(msg.recipient_id)
+        dst = ep.rank
+        tensors = []
+        payload = msg.payload
+        if isinstance(payload, Job):
+            meta = {"mb": payload.micro_batch_id, "t": []}
+            for t in (payload.data, payload.targets):
+                if t is None:
+                    meta["t"].append(None)
+                else:
+                    nhwc = t.dim() == 4 and not t.is_contiguous() and t.is_contiguous(memory_format=torch.channels_last)
+                    meta["t"].append((tuple(t.shape), str(t.dtype).replace("torch.", ""), nhwc))
+                    tensors.append(t.permute(0, 2, 3, 1) if nhwc else t)
+            payload = ("job", meta)
+        # the store assigns the per-destination sequence number atomically (several senders may target one rank)
+        seq = self.store.add(f"mbox/{dst}/tail", 1) - 1
+        blob = pickle.dumps((msg.recipient_id, msg.sender_id, int(msg.command_type), payload, self.rank))
+        self.store.set(self._key(dst, seq), blob)
+        group, dev = self._tensor_route(dst)
+        for t in tensors:
+            buf = t.contiguous().to(dev)   # NHWC views are already dense: no copy on the GPU->GPU path
+            dist.send(buf, dst=dist.get_global_rank(group, dist.get_group_rank(group, dst)) if group else dst,
+                      group=group)
+
+    def poll(self):
+        while True:
+            key = self._key(self.rank, self._recv_seq)
+            try:
+                if not self.store.check([key]):
+                    return
+            except RuntimeError:
+                return
+            blob = self.store.get(key)
+            try:
+                self.store.delete_key(key)
+            except Exception:
+                pass
+            self._recv_seq += 1
+            recipient, sender, ctype, payload, src = pickle.loads(blob)
+            if isinstance(payload, tuple) and payload and payload[0] == "job":
+                meta = payload[1]
+                group, dev = self._tensor_route(src)
+                got = []
+                for spec in meta["t"]:
+                    if spec is None:
+                        got.append(None)
+                        continue
+                    shape, dtype, nhwc = spec
+                    wire_shape = (shape[0], shape[2], shape[3], shape[1]) if nhwc else shape
+                    buf = torch.empty(wire_shape, dtype=getattr(torch, dtype), device=dev)
+                    dist.recv(buf, src=src, group=group)
+                    buf = buf.to(self.device)
+                    got.append(buf.permute(0, 3, 1, 2) if nhwc else buf)
+                payload = Job(got[0], meta["mb"], got[1])
+            self.enqueue_input_message(Message(recipient, CommandType(ctype), payload, sender))
+
+    def wait_for_input(self, timeout: Optional[float] = None) -> bool:
+        deadline = None if timeout is None else time.monotonic() + timeout
+        while True:
+            self.poll()
+            if self.has_input_message():
+                return True
+            if deadline is not None and time.monotonic() >= deadline:
+                return False
+            time.sleep(0.0002)
+
+

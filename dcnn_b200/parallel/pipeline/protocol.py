@@ -1,0 +1,143 @@
+"""Pipeline control protocol (ref include/pipeline/command_type.hpp:20-68, message.hpp:21-166, job.hpp:14-35,
+stage_config.hpp:8-35, endpoint.hpp:17-95, load_tracker.hpp:9-22).
+
+Same command vocabulary and the same JSON stage-config schema as the reference.  Differences by design: tensors
+never travel inside control messages on the distributed backend (activations/gradients go GPU->GPU over NCCL p2p;
+the message only carries shape metadata), and endpoints are ``{rank, device}`` instead of host:port."""
+from __future__ import annotations
+
+import enum
+import json
+from dataclasses import dataclass, field
+from typing import Any, Dict, Optional
+
+import torch
+
+
+class CommandType(enum.IntEnum):
+    _START = 0
+    # core commands
+    FORWARD_JOB = 1
+    BACKWARD_JOB = 2
+    UPDATE_PARAMETERS = 3
+    # mode switching
+    TRAIN_MODE = 4
+    EVAL_MODE = 5
+    SHUTDOWN = 6
+    # configuration
+    CONFIG_TRANSFER = 7
+    CONFIG_RECEIVED = 8
+    LOAD_PARAMS = 9
+    PARAMS_LOADED = 10
+    SEND_PARAMS = 11
+    PARAMS_TRANSFER = 12
+    # status and monitoring
+    STATUS_REQUEST = 13
+    STATUS_RESPONSE = 14
+    PARAMETERS_UPDATED = 15
+    HEALTH_CHECK = 16
+    # error handling
+    ERROR_REPORT = 17
+    JOB_FAILURE = 18
+    # advanced features
+    BARRIER_SYNC = 19
+    CHECKPOINT_REQUEST = 20
+    CHECKPOINT_COMPLETE = 21
+    # load balancing and resource management
+    UPDATE_LOAD = 22
+    REPORT_LOAD = 23
+    LOAD_REPORT = 24
+    # profiling and debugging
+    PRINT_PROFILING = 25
+    PROFILING_PRINTED = 26
+    CLEAR_PROFILING = 27
+    PROFILING_CLEARED = 28
+    _COUNT = 29
+
+
+@dataclass
+class Job:
+    """A tensor plus the microbatch it belongs to.  ``targets`` (optional) rides along with forward jobs so the
+    LAST stage can compute loss + gradient locally instead of shipping logits back to the coordinator."""
+    data: Optional[torch.Tensor]
+    micro_batch_id: int = 0
+    targets: Optional[torch.Tensor] = None
+
+
+@dataclass
+class LoadTracker:
+    avg_forward_time_ms: float = 0.0
+    avg_backward_time_ms: float = 0.0
+    avg_cpu_utilization: float = 0.0
+    max_memory_usage_mb: float = 0.0
+
+
+@dataclass
+class Message:
+    recipient_id: str
+    command_type: CommandType
+    payload: Any = None          # None | Job | str | bool | float | LoadTracker | dict
+    sender_id: str = ""
+
+    def has_job(self) -> bool:
+        return isinstance(self.payload, Job)
+
+
+@dataclass
+class Endpoint:
+    """Where a pipeline participant lives.  ``in_process`` endpoints carry the communicator object itself (ref
+    Endpoint::in_process); ``rank`` endpoints name a torch.distributed rank (replaces host:port)."""
+    kind: str = "rank"                 # "rank" | "in_process"
+    rank: int = -1
+    device: str = "cpu"
+    communicator: Any = field(default=None, repr=False, compare=False)
+
+    @staticmethod
+    def network(rank: int, device: str = "cpu") -> "Endpoint":
+        return Endpoint("rank", int(rank), device)
+
+    @staticmethod
+    def in_process(communicator) -> "Endpoint":
+        return Endpoint("in_process", -1, "cpu", communicator)
+
+    def to_json(self) -> dict:
+        return {"communication_type": self.kind, "rank": self.rank, "device": self.device}
+
+    @staticmethod
+    def from_json(j: dict) -> "Endpoint":
+        return Endpoint(j.get("communication_type", "rank"), int(j.get("rank", -1)), j.get("device", "cpu"))
+
+
+@dataclass
+class StageConfig:
+    """JSON-serialisable stage description (ref stage_config.hpp:16-23)."""
+    stage_id: str
+    model_config: dict
+    optimizer_config: dict
+    next_stage_endpoint: Endpoint
+    prev_stage_endpoint: Endpoint
+    coordinator_endpoint: Endpoint
+    loss_config: Optional[dict] = None     # extension: the last stage owns the loss
+    is_first: bool = False
+    is_last: bool = False
+
+    def to_json(self) -> dict:
+        return {"stage_id": self.stage_id, "model_config": self.model_config,
+                "optimizer_config": self.optimizer_config,
+                "next_stage_endpoint": self.next_stage_endpoint.to_json(),
+                "prev_stage_endpoint": self.prev_stage_endpoint.to_json(),
+                "coordinator_endpoint": self.coordinator_endpoint.to_json(),
+                "loss_config": self.loss_config, "is_first": self.is_first, "is_last": self.is_last}
+
+    def dumps(self) -> str:
+        return json.dumps(self.to_json())
+
+    @staticmethod
+    def from_json(j) -> "StageConfig":
+        if isinstance(j, str):
+            j = json.loads(j)
+        return StageConfig(j["stage_id"], j["model_config"], j["optimizer_config"],
+                           Endpoint.from_json(j["next_stage_endpoint"]),
+                           Endpoint.from_json(j["prev_stage_endpoint"]),
+                           Endpoint.from_json(j["coordinator_endpoint"]), j.get("loss_config"),
+                           bool(j.get("is_first", False)), bool(j.get("is_last", False)))
