@@ -115,25 +115,62 @@ def main():
     torch.manual_seed(1234)
     model = create_resnet50_tiny_imagenet()
     model.set_seed(42)           # identical initial weights on every replica
-    model.set_device(dev)
-    model.initialize()
-    model.compute_input_gradient = False
     opt = nn.Adam(1e-4, epsilon=1e-3, weight_decay=1e-3)   # examples/tiny_imagenet_resnet50.cpp:90
     loss_fn = nn.LogSoftmaxCrossEntropyLoss()
 
-    parallelism = "single"
+    # ---- parallelism: single | dpR | ppS | ppSxdpR   (rank = replica * S + stage)
+    par = args.parallelism
+    if par == "auto":
+        par = "single" if world == 1 else f"dp{world}"
+    S, R = 1, world
+    if par.startswith("pp"):
+        S = int(par[2:].split("x")[0])
+        R = int(par.split("xdp")[1]) if "xdp" in par else 1
+    elif par.startswith("dp"):
+        S, R = 1, int(par[2:])
+    elif par == "single":
+        S, R = 1, 1
+    if S * R != world:
+        raise SystemExit(f"--parallelism {par} needs {S * R} GPUs, got {world}")
+    parallelism = par
+    engine = None
     dp = None
-    if world > 1:
-        from dcnn_b200.parallel.dp import DataParallel
-        dp = DataParallel(model, opt, dist.group.WORLD, sync_bn=os.environ.get("BENCH_SYNC_BN", "1") == "1")
-        parallelism = f"dp{world}"
-    else:
-        opt.attach(model.parameters(), model.gradients())
-    step = TrainStep(model, opt, loss_fn, use_cuda_graph=not args.no_graph,
-                     num_microbatches=args.microbatches, data_parallel=dp)
+    sync_bn = os.environ.get("BENCH_SYNC_BN", "1") == "1"
+    if S > 1:
+        from dcnn_b200.parallel.pipeline import PipelineEngine, make_pipeline_groups
+        from dcnn_b200.partitioner import BalancedPartitioner
+        stage, rep, links, dp_g = make_pipeline_groups(S, R)
+        mb = args.microbatches if args.microbatches > 1 else 2 * S
+        parts = BalancedPartitioner(input_shape=[args.batch, *IMG]).get_partitions(model.get_layers(), S)
+        engine = PipelineEngine(model, parts, stage, opt, loss_fn, mb, links, dev,
+                                schedule=os.environ.get("SCHEDULE", "semi_async"), dp_group=dp_g if R > 1 else None,
+                                sync_bn=sync_bn, seed=42)
+        args.microbatches = mb
 
-    B = args.batch
-    g = torch.Generator().manual_seed(1000 + rank)
+        class _Step:
+            _graph = None
+
+            def __call__(self, x, t):
+                return engine.train_step(x, t)
+
+            def _eager(self, x, t):
+                return engine.train_step(x, t)
+        step = _Step()
+    else:
+        model.set_device(dev)
+        model.initialize()
+        model.compute_input_gradient = False
+        if world > 1:
+            from dcnn_b200.parallel.dp import DataParallel
+            dp = DataParallel(model, opt, dist.group.WORLD, sync_bn=sync_bn,
+                              nccl_baseline=os.environ.get("BENCH_NCCL_BASELINE", "0") == "1")
+        else:
+            opt.attach(model.parameters(), model.gradients())
+        step = TrainStep(model, opt, loss_fn, use_cuda_graph=not args.no_graph,
+                         num_microbatches=args.microbatches, data_parallel=dp)
+
+    B = args.batch * S          # batch fed to one pipeline replica: per-GPU work stays fixed
+    g = torch.Generator().manual_seed(1000 + rank // S)
     nbuf = 4
     host_x = [torch.randn(B, *IMG, generator=g).pin_memory() for _ in range(nbuf)]
     host_t = [torch.nn.functional.one_hot(torch.randint(0, CLASSES, (B,), generator=g), CLASSES).float()
@@ -165,7 +202,8 @@ def main():
     launches = _lib.launch_count()
     if step._graph is not None:   # replayed graph: count the kernels captured in one step
         launches = step_launches(step, dev_x[0], dev_t[0], _lib) * args.steps
-    final_loss = float(loss)
+    final_loss = float(loss) if loss is not None else float('nan')
+    stage_stats = engine.stats() if engine is not None else None
 
     # ---- end-to-end arm: public API, pinned-host -> device copy of every batch + loss read-back every step
     h2d = host_x[0].numel() * 4 + host_t[0].numel() * 4
@@ -180,8 +218,9 @@ def main():
         x = host_x[i % nbuf].to(dev, non_blocking=True)
         t = host_t[i % nbuf].to(dev, non_blocking=True)
         loss, correct = step(x, t)
-        out_host[0].copy_(loss, non_blocking=True)
-        out_host[1].copy_(correct, non_blocking=True)
+        if loss is not None:
+            out_host[0].copy_(loss, non_blocking=True)
+            out_host[1].copy_(correct, non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the step's result is on the host before the next step
     f1.record()
     barrier()
@@ -189,11 +228,20 @@ def main():
     if rank == 0:
         sampler.stop()
 
-    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    t = torch.tensor([ms, ms_e2e, final_loss if final_loss == final_loss else -1e30, float(launches)], device=dev,
+                     dtype=torch.float64)
+    bubble = None
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
-    gb = B * world
+        if stage_stats is not None:
+            b = torch.tensor([stage_stats["busy_ms"], stage_stats["step_ms"]], device=dev, dtype=torch.float64)
+            allb = [torch.zeros_like(b) for _ in range(world)]
+            dist.all_gather(allb, b)
+            busy = sum(float(v[0]) for v in allb)
+            stepm = max(float(v[1]) for v in allb)
+            bubble = 1.0 - busy / (world * stepm)
+    ms, ms_e2e, final_loss, launches = float(t[0]), float(t[1]), float(t[2]), int(t[3])
+    gb = B * R
     value = gb * args.steps / (ms / 1000.0)
     e2e = gb * args.steps / (ms_e2e / 1000.0)
     if rank == 0:
@@ -214,12 +262,14 @@ def main():
                        "image": "3x64x64", "classes": CLASSES, "parallelism": parallelism,
                        "optimizer": "Adam(lr 1e-4, eps 1e-3, wd 1e-3)", "loss": "LogSoftmaxCrossEntropy",
                        "cuda_graph": step._graph is not None, "microbatches": args.microbatches,
+                       "pipeline_stages": S, "dp_replicas": R, "sync_bn": sync_bn and R > 1,
+                       "pipeline_bubble_fraction": bubble,
                        "l2": "per-step working set (activations, >10 GB at batch 256) is far larger than the 126 MB L2; "
                              "inputs rotate over 4 distinct batches"},
             "clocks": sampler.summary(),
             "e2e": {"value": round(e2e, 2), "unit": "images/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(launches),  # per rank, max over ranks
             "final_loss": final_loss,
         }
         print(json.dumps(out), flush=True)

@@ -152,8 +152,9 @@ class DistCommunicator(Communicator):
         self.control_group, self.data_group = control_group, data_group
         self.data_ranks = set(data_ranks) if data_ranks is not None else None
         self.device = device or torch.device("cpu")
-        self._send_seq: Dict[int, int] = collections.defaultdict(int)
         self._recv_seq = 0
+        self._pending = []   # (work, tensor) of in-flight isends: sends never block the event loop (two stages
+        #                      sending to each other with blocking sends would deadlock)
 
     def _key(self, dst: int, seq: int) -> str:
         return f"mbox/{dst}/{seq}"
@@ -186,10 +187,10 @@ class DistCommunicator(Communicator):
         blob = pickle.dumps((msg.recipient_id, msg.sender_id, int(msg.command_type), payload, self.rank))
         self.store.set(self._key(dst, seq), blob)
         group, dev = self._tensor_route(dst)
+        self._pending = [(w, b) for (w, b) in self._pending if not w.is_completed()]
         for t in tensors:
             buf = t.contiguous().to(dev)   # NHWC views are already dense: no copy on the GPU->GPU path
-            dist.send(buf, dst=dist.get_global_rank(group, dist.get_group_rank(group, dst)) if group else dst,
-                      group=group)
+            self._pending.append((dist.isend(buf, dst=dst, group=group), buf))
 
     def poll(self):
         while True:
@@ -222,6 +223,14 @@ class DistCommunicator(Communicator):
                     got.append(buf.permute(0, 3, 1, 2) if nhwc else buf)
                 payload = Job(got[0], meta["mb"], got[1])
             self.enqueue_input_message(Message(recipient, CommandType(ctype), payload, sender))
+
+    def flush_output_messages(self):
+        for w, _ in self._pending:
+            w.wait()
+        self._pending = []
+
+    def close(self):
+        self.flush_output_messages()
 
     def wait_for_input(self, timeout: Optional[float] = None) -> bool:
         deadline = None if timeout is None else time.monotonic() + timeout

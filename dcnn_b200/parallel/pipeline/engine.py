@@ -1,0 +1,273 @@
+"""SPMD pipeline engine: the performance path of pipeline parallelism on one 8xB200 box.
+
+Every rank owns one stage (one GPU) and executes a *static schedule table* instead of reacting to message priority
+(the reference's effective schedule is emergent, communicator.hpp:100-110):
+
+  * ``sync``        GPipe: all forwards, then all backwards (examples/sync_pipeline_coordinator.cpp:122-180)
+  * ``semi_async``  backward of a microbatch starts as soon as its forward leaves the last stage -> 1F1B steady state
+                    (coordinator.hpp:273-326), which also bounds live activations to (S - stage) microbatches.
+
+Activations and gradients move GPU->GPU with NCCL p2p (NVLink 5) as dense NHWC buffers.  Every stage-to-stage link has
+its own pair of 2-rank communicators (one per direction): NCCL executes the ops of one communicator in issue order,
+so a receive that is posted early on a shared communicator would block every later send of that rank behind it and
+the 1F1B schedule dead-locks (seen on hardware with one 4-rank group per direction).  With per-link, per-direction
+communicators each communicator carries one ordered stream of transfers whose order is identical on both ends.
+Receives for the next op are posted before the current op computes, so transfers overlap compute.  The loss lives on the last stage; dL/dinput of the first stage is never computed or shipped.
+With ``dp_group`` each stage is replicated and its update is the fused P2P all-reduce+optimizer kernel
+(parallel/dp.py); BatchNorm statistics then span the replicas of the stage.
+
+Numerics match the reference: BN statistics per microbatch, weight gradients accumulated over microbatches, each
+microbatch gradient scaled by 1/microbatch_size, reported loss = mean over microbatches."""
+from __future__ import annotations
+
+import time
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ...nn.loss import Loss
+from ...nn.optimizers import Optimizer
+from ...nn.sequential import Partition, Sequential
+from ...train import split_microbatches
+
+
+def build_schedule(kind: str, stage: int, num_stages: int, num_microbatches: int) -> List[Tuple[str, int]]:
+    m = num_microbatches
+    if kind == "sync":
+        return [("F", i) for i in range(m)] + [("B", i) for i in range(m)]
+    if kind != "semi_async":
+        raise ValueError(f"unknown schedule '{kind}' (sync | semi_async)")
+    warm = min(num_stages - 1 - stage, m)
+    ops = [("F", i) for i in range(warm)]
+    for i in range(m - warm):
+        ops.append(("F", warm + i))
+        ops.append(("B", i))
+    ops += [("B", i) for i in range(m - warm, m)]
+    return ops
+
+
+class PipelineEngine:
+    def __init__(self, full_model: Sequential, partitions: Sequence[Partition], stage: int, optimizer: Optimizer,
+                 loss_fn: Loss, num_microbatches: int, links: "PipelineLinks", device, schedule: str = "semi_async",
+                 dp_group=None, sync_bn: bool = True, seed: Optional[int] = None, nccl_baseline: bool = False):
+        self.S, self.stage, self.M = len(partitions), stage, int(num_microbatches)
+        self.links = links
+        self.device = torch.device(device)
+        self.loss_fn, self.optimizer = loss_fn, optimizer
+        self.is_first, self.is_last = stage == 0, stage == len(partitions) - 1
+        self.partitions = list(partitions)
+        self.full_model = full_model
+        sub = full_model.split(partitions)[stage]
+        if seed is not None:
+            sub.set_seed(seed + 1000003 * partitions[stage].start_layer)
+        sub.set_device(self.device)
+        sub.initialize()
+        sub.compute_input_gradient = not self.is_first
+        self.model = sub
+        self.schedule = build_schedule(schedule, stage, self.S, self.M)
+        self.dp = None
+        if dp_group is not None and dist.get_world_size(dp_group) > 1:
+            from ..dp import DataParallel
+            self.dp = DataParallel(sub, optimizer, dp_group, sync_bn=sync_bn, nccl_baseline=nccl_baseline)
+        else:
+            optimizer.attach(sub.parameters(), sub.gradients())
+        self.prev_rank = links.ranks[stage - 1] if not self.is_first else None
+        self.next_rank = links.ranks[stage + 1] if not self.is_last else None
+        # communicators of this stage's four transfer streams
+        self.g_recv_act = links.fwd[stage - 1] if not self.is_first else None   # activations from prev
+        self.g_send_act = links.fwd[stage] if not self.is_last else None        # activations to next
+        self.g_recv_grad = links.bwd[stage] if not self.is_last else None       # gradients from next
+        self.g_send_grad = links.bwd[stage - 1] if not self.is_first else None  # gradients to prev
+        self._pending_sends = []
+        self.last_stats = {}
+
+    # -- shapes ------------------------------------------------------------------------------------------
+    def _boundary_shapes(self, mb_input_shape):
+        """Input shape of this stage and of the next stage for one microbatch."""
+        s = list(mb_input_shape)
+        shapes = [s]
+        for part in self.partitions:
+            for l in self.full_model.layers[part.start_layer:part.end_layer]:
+                s = l.compute_output_shape(s)
+            shapes.append(list(s))
+        return shapes[self.stage], shapes[self.stage + 1]
+
+    # -- wire --------------------------------------------------------------------------------------------
+    def _wire(self, t):
+        if t.dim() == 4 and not t.is_contiguous() and t.is_contiguous(memory_format=torch.channels_last):
+            return t.permute(0, 2, 3, 1)
+        return t.contiguous()
+
+    def _alloc(self, shape):
+        if self.device.type == "cuda" and len(shape) == 4:
+            n, c, h, w = shape
+            buf = torch.empty((n, h, w, c), device=self.device, dtype=torch.float32)
+            return buf, buf.permute(0, 3, 1, 2)
+        buf = torch.empty(shape, device=self.device, dtype=torch.float32)
+        return buf, buf
+
+    def _isend(self, t, dst, group):
+        buf = self._wire(t)
+        if self.device.type != "cuda" and buf.dim() == 4 and tuple(buf.shape) != tuple(t.shape):
+            buf = t.contiguous()
+        self._pending_sends.append((dist.isend(buf, dst=dst, group=group), buf))
+
+    def _irecv(self, shape, src, group):
+        buf, view = self._alloc(shape)
+        return dist.irecv(buf, src=src, group=group), view
+
+    # -- one optimisation step -------------------------------------------------------------------------------
+    def train_step(self, x: Optional[torch.Tensor] = None, targets: Optional[torch.Tensor] = None):
+        """x: this replica's batch (needed on the first stage), targets: needed on the last stage.
+        Returns (mean loss tensor | None, correct-count tensor | None) -- non-None on the last stage."""
+        M = self.M
+        timing = self.device.type == "cuda"
+        xs = split_microbatches(x.to(self.device, non_blocking=True), M) if self.is_first else None
+        ts = split_microbatches(targets.to(self.device, non_blocking=True), M) if self.is_last else None
+        if self.is_first:
+            mb_shapes = [list(t.shape) for t in xs]
+            meta = torch.tensor([s[0] for s in mb_shapes] + list(mb_shapes[0][1:]), dtype=torch.int64)
+        else:
+            meta = None
+        mb_batch, sample_shape = self._microbatch_layout(meta, M)
+        in_shapes, out_shapes = [], []
+        for b in mb_batch:
+            i, o = self._boundary_shapes([b] + sample_shape)
+            in_shapes.append(i)
+            out_shapes.append(o)
+
+        sched = self.schedule
+        recv_slot = {}
+
+        def post_recv(k):
+            if k >= len(sched):
+                return
+            op, mb = sched[k]
+            if op == "F" and not self.is_first:
+                recv_slot[k] = self._irecv(in_shapes[mb], self.prev_rank, self.g_recv_act)
+            elif op == "B" and not self.is_last:
+                recv_slot[k] = self._irecv(out_shapes[mb], self.next_rank, self.g_recv_grad)
+
+        loss_acc = correct_acc = None
+        grads = {}
+        busy = []
+        t_begin = time.perf_counter()
+        if timing:
+            ev_begin = torch.cuda.Event(enable_timing=True)
+            ev_begin.record()
+        post_recv(0)
+        for k, (op, mb) in enumerate(sched):
+            post_recv(k + 1)       # overlap the next transfer with this op's compute
+            if k in recv_slot:
+                work, view = recv_slot.pop(k)
+                work.wait()
+            if timing:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            else:
+                c0 = time.perf_counter()
+            if op == "F":
+                inp = xs[mb] if self.is_first else view
+                y = self.model.forward(inp, mb)
+                if self.is_last:
+                    loss, g, correct = self.loss_fn.forward_backward(y, ts[mb])
+                    grads[mb] = g
+                    loss_acc = loss if loss_acc is None else loss_acc + loss
+                    if correct is not None:
+                        correct_acc = correct if correct_acc is None else correct_acc + correct
+                else:
+                    self._isend(y, self.next_rank, self.g_send_act)
+            else:
+                g = grads.pop(mb) if self.is_last else view
+                dx = self.model.backward(g, mb)
+                if not self.is_first:
+                    self._isend(dx, self.prev_rank, self.g_send_grad)
+            if timing:
+                e1.record()
+                busy.append((e0, e1))
+            else:
+                busy.append(time.perf_counter() - c0)
+        if self.dp is not None:
+            self.dp.reduce_and_update(self.optimizer)
+        else:
+            self.optimizer.update(zero_grads=True)
+        for w, _ in self._pending_sends:
+            w.wait()
+        self._pending_sends = []
+        if timing:
+            ev_end = torch.cuda.Event(enable_timing=True)
+            ev_end.record()
+            self._events = (ev_begin, ev_end, busy)
+        else:
+            self.last_stats = {"busy_ms": sum(busy) * 1000, "step_ms": (time.perf_counter() - t_begin) * 1000}
+        if self.is_last and loss_acc is not None and M > 1:
+            loss_acc = loss_acc / M
+        return loss_acc, correct_acc
+
+    def stats(self):
+        """(busy_ms, step_ms) of the last step on this stage; synchronises."""
+        if self.device.type == "cuda" and getattr(self, "_events", None):
+            torch.cuda.synchronize(self.device)
+            b, e, busy = self._events
+            self.last_stats = {"busy_ms": sum(a.elapsed_time(z) for a, z in busy), "step_ms": b.elapsed_time(e)}
+        return self.last_stats
+
+    def _microbatch_layout(self, meta, M):
+        """Every stage needs the microbatch sizes and the sample shape; stage 0 knows them, the rest learn them once
+        (cached) through the forward group."""
+        key = "_layout"
+        if self.is_first:
+            vals = meta.tolist()
+            layout = (vals[:M], vals[M:])
+            if getattr(self, key, None) != layout:
+                setattr(self, key, layout)
+                obj = [layout]
+            else:
+                obj = [None]
+        else:
+            obj = [None]
+        if self.S > 1 and not getattr(self, "_layout_synced", False):
+            # one-time exchange (batch geometry is static afterwards; call reset_layout() if it changes)
+            dist.broadcast_object_list(obj, src=self.links.ranks[0], group=self.links.ctl)
+            self._layout_synced = True
+        if obj[0] is not None:
+            setattr(self, key, (list(obj[0][0]), list(obj[0][1])))
+        layout = getattr(self, key)
+        return list(layout[0]), list(layout[1])
+
+
+class PipelineLinks:
+    """Communicators of one pipeline replica: ``fwd[s]`` / ``bwd[s]`` are 2-rank groups for the link between stage s
+    and s+1 (one per direction), ``ctl`` spans all stages (set-up only), ``ranks[s]`` is stage s's global rank."""
+
+    def __init__(self, ranks, fwd, bwd, ctl):
+        self.ranks, self.fwd, self.bwd, self.ctl = list(ranks), fwd, bwd, ctl
+
+    def reset(self):
+        pass
+
+
+def make_pipeline_groups(num_stages: int, dp_replicas: int, backend: Optional[str] = None):
+    """Rank layout: rank = replica * S + stage.  Returns (stage, replica, links, dp_group).
+    Every rank must call this (group creation is collective over the whole job)."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    if num_stages * dp_replicas != world:
+        raise ValueError(f"stages ({num_stages}) x replicas ({dp_replicas}) != world size ({world})")
+    my_stage, my_rep = rank % num_stages, rank // num_stages
+    links = dpg = None
+    for r in range(dp_replicas):
+        ranks = [r * num_stages + s for s in range(num_stages)]
+        ctl = dist.new_group(ranks=ranks, backend=backend)
+        fwd, bwd = {}, {}
+        for s in range(num_stages - 1):
+            fwd[s] = dist.new_group(ranks=[ranks[s], ranks[s + 1]], backend=backend)
+            bwd[s] = dist.new_group(ranks=[ranks[s], ranks[s + 1]], backend=backend)
+        if r == my_rep:
+            links = PipelineLinks(ranks, fwd, bwd, ctl)
+    for s in range(num_stages):
+        ranks = [r * num_stages + s for r in range(dp_replicas)]
+        g = dist.new_group(ranks=ranks, backend=backend)
+        if s == my_stage:
+            dpg = g
+    return my_stage, my_rep, links, dpg

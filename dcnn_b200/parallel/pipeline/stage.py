@@ -76,6 +76,7 @@ class PipelineStage:
                                f"{self.name}: {type(e).__name__}: {e}\n{traceback.format_exc()}")
                 if self.should_stop:
                     break
+        self.comm.flush_output_messages()
 
     # -- helpers -----------------------------------------------------------------------------------------
     def _send(self, recipient: str, ctype: CommandType, payload=None):

@@ -1,0 +1,120 @@
+"""SPMD PipelineEngine on CPU (gloo): stages x microbatches (x data-parallel replicas) == single device."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from dcnn_b200 import nn as dnn
+from dcnn_b200.parallel.pipeline import build_schedule
+from dcnn_b200.partitioner import NaivePartitioner
+from tests.test_pipeline_inprocess import _data, _model, _reference_run
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_schedules():
+    assert build_schedule("sync", 0, 2, 3) == [("F", 0), ("F", 1), ("F", 2), ("B", 0), ("B", 1), ("B", 2)]
+    # last stage alternates immediately; first stage warms up with S-1 forwards (1F1B)
+    assert build_schedule("semi_async", 2, 3, 4) == [("F", 0), ("B", 0), ("F", 1), ("B", 1), ("F", 2), ("B", 2),
+                                                     ("F", 3), ("B", 3)]
+    assert build_schedule("semi_async", 0, 3, 4) == [("F", 0), ("F", 1), ("F", 2), ("B", 0), ("F", 3), ("B", 1),
+                                                     ("B", 2), ("B", 3)]
+    for st in range(4):
+        ops = build_schedule("semi_async", st, 4, 2)
+        assert sorted(ops) == sorted([("F", 0), ("F", 1), ("B", 0), ("B", 1)])
+        assert all(ops.index(("F", i)) < ops.index(("B", i)) for i in range(2))
+
+
+def _proc(rank, world, port, out, stages, reps, micro, schedule):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from dcnn_b200.parallel.pipeline import PipelineEngine, make_pipeline_groups
+    stage, rep, links, dpg = make_pipeline_groups(stages, reps)
+    full = _model()
+    parts = NaivePartitioner().get_partitions(full.get_layers(), stages)
+    eng = PipelineEngine(full, parts, stage, dnn.SGD(0.05, 0.9), dnn.SoftmaxCrossEntropyLoss(), micro, links, "cpu",
+                         schedule=schedule, dp_group=dpg, seed=77)
+    x, t = _data(8)
+    per = 8 // reps
+    xs, ts = x[rep * per:(rep + 1) * per], t[rep * per:(rep + 1) * per]
+    losses = []
+    for _ in range(3):
+        loss, _ = eng.train_step(xs, ts)
+        if loss is not None:
+            losses.append(float(loss))
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (stage, rep, [p.clone() for p in eng.model.parameters()], losses))
+    if rank == 0:
+        torch.save(gathered, out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("stages,reps,micro,schedule", [(2, 1, 2, "semi_async"), (3, 1, 4, "sync"),
+                                                        (2, 2, 2, "semi_async")])
+def test_engine_equals_single_device(tmp_path, stages, reps, micro, schedule):
+    out = str(tmp_path / "eng.pt")
+    world = stages * reps
+    mp.spawn(_proc, args=(world, _free_port(), out, stages, reps, micro, schedule), nprocs=world, join=True)
+    got = torch.load(out)
+    if reps == 1:
+        ref, ref_losses = _reference_run(stages, micro, 3)
+    else:
+        # replicas with sync-BN and averaged gradients == one device, where every pipeline microbatch is the
+        # concatenation of the replicas' microbatches.  Build that reference explicitly.
+        ref, ref_losses = _reference_dp(stages, micro, reps, 3)
+    params = []
+    for s in range(stages):
+        entry = [g for g in got if g[0] == s and g[1] == 0][0]
+        params.extend(entry[2])
+    for p, q in zip(params, ref.parameters()):
+        assert torch.allclose(p, q, atol=2e-5, rtol=1e-4), (p - q).abs().max()
+    if reps == 1:
+        losses = [g for g in got if g[0] == stages - 1][0][3]
+        for a, b in zip(losses, ref_losses):
+            assert abs(a - b) < 1e-4
+
+
+def _reference_dp(stages, micro, reps, steps):
+    import dcnn_b200 as dc
+    from dcnn_b200.train import split_microbatches
+    full = _model()
+    parts = NaivePartitioner().get_partitions(full.get_layers(), stages)
+    subs = full.split(parts)
+    for i, s in enumerate(subs):
+        s.set_seed(77 + 1000003 * parts[i].start_layer)
+        s.initialize()
+    seq = dc.Sequential("ref")
+    for s in subs:
+        for l in s.layers:
+            seq.add(l)
+    opt = dnn.SGD(0.05, 0.9)
+    opt.attach(seq.parameters(), seq.gradients())
+    loss_fn = dnn.SoftmaxCrossEntropyLoss()
+    x, t = _data(8)
+    per = 8 // reps
+    losses = []
+    for _ in range(steps):
+        xr = [split_microbatches(x[r * per:(r + 1) * per], micro) for r in range(reps)]
+        tr = [split_microbatches(t[r * per:(r + 1) * per], micro) for r in range(reps)]
+        gs = []
+        for m in range(micro):
+            xm = torch.cat([xr[r][m] for r in range(reps)])
+            tm = torch.cat([tr[r][m] for r in range(reps)])
+            y = seq.forward(xm, m)
+            loss, g, _ = loss_fn.forward_backward(y, tm)
+            gs.append(g)
+        for m in reversed(range(micro)):
+            seq.backward(gs[m], m)
+        opt.update(zero_grads=True)
+    return seq, losses
