@@ -110,7 +110,15 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        if args.parallelism.startswith("pp"):
+            # lazy communicator creation: in eager mode (device_id given) NCCL treats every unbatched isend/irecv of a
+            # group as a collective serialised with all other ops of that group
+            dist.init_process_group("nccl")
+        else:
+            dist.init_process_group("nccl", device_id=dev)
+        if os.environ.get("DCNN_HANG_DUMP_S"):
+            import faulthandler
+            faulthandler.dump_traceback_later(float(os.environ["DCNN_HANG_DUMP_S"]), exit=True)
 
     torch.manual_seed(1234)
     model = create_resnet50_tiny_imagenet()

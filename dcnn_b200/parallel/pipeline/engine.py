@@ -32,6 +32,11 @@ from ...nn.sequential import Partition, Sequential
 from ...train import split_microbatches
 
 
+import os as _os
+
+_PIPE_DEBUG = _os.environ.get("DCNN_PIPE_DEBUG", "0") == "1"
+
+
 def build_schedule(kind: str, stage: int, num_stages: int, num_microbatches: int) -> List[Tuple[str, int]]:
     m = num_microbatches
     if kind == "sync":
@@ -157,7 +162,10 @@ class PipelineEngine:
             ev_begin = torch.cuda.Event(enable_timing=True)
             ev_begin.record()
         post_recv(0)
+        debug = _PIPE_DEBUG
         for k, (op, mb) in enumerate(sched):
+            if debug:
+                print(f"[pipe s{self.stage}] op {k}: {op}{mb}", flush=True)
             post_recv(k + 1)       # overlap the next transfer with this op's compute
             if k in recv_slot:
                 work, view = recv_slot.pop(k)
