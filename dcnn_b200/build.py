@@ -72,5 +72,29 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+HOST_LIB = os.path.join(LIBDIR, "libdcnn_host.so")
+
+
+def build_host(force: bool = False) -> str:
+    """CPU-side native runtime (csrc/host/*.cpp -> libdcnn_host.so): g++ -O3 -fopenmp, no CUDA needed."""
+    os.makedirs(LIBDIR, exist_ok=True)
+    hdir = os.path.join(CSRC, "host")
+    srcs = sorted(os.path.join(hdir, f) for f in os.listdir(hdir) if f.endswith(".cpp"))
+    hdrs = [os.path.join(hdir, f) for f in os.listdir(hdir) if f.endswith(".h")]
+    stamp = os.path.join(LIBDIR, "build_host.sha256")
+    digest = _digest(srcs + hdrs)
+    if not force and os.path.exists(HOST_LIB) and os.path.exists(stamp) and open(stamp).read().strip() == digest:
+        return HOST_LIB
+    cmd = ["g++", "-O3", "-std=c++17", "-fPIC", "-shared", "-fopenmp", "-fvisibility=hidden", "-march=x86-64-v3",
+           "-I", hdir, "-o", HOST_LIB, *srcs]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"host library build failed:\n{r.stdout}\n{r.stderr}")
+    with open(stamp, "w") as f:
+        f.write(digest)
+    return HOST_LIB
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))
