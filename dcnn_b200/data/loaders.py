@@ -490,3 +490,8 @@ def create_tiny_imagenet_data_loaders(data_dir: str):
     if not tr.load_data(data_dir, True) or not te.load_data(data_dir, False):
         raise RuntimeError("Failed to load Tiny ImageNet data")
     return tr, te
+
+
+def create_mnist_data_loaders_dir(data_dir: str):
+    """``<dir>/train.csv`` + ``<dir>/test.csv`` (the reference examples read ./data/mnist/{train,test}.csv)."""
+    return create_mnist_data_loaders(os.path.join(data_dir, "train.csv"), os.path.join(data_dir, "test.csv"))

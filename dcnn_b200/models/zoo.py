@@ -58,6 +58,11 @@ def create_cifar10_trainer_v2() -> Sequential:
     return _vgg_like("cifar10_cnn_classifier", 32, 512, 10)
 
 
+def create_cifar100_trainer() -> Sequential:
+    """CIFAR-100 CNN of examples/cifar100_cnn_trainer.cpp: the v2 VGG-style stack with a 100-way head."""
+    return _vgg_like("cifar100_cnn_classifier", 32, 512, 100)
+
+
 def create_cnn_tiny_imagenet() -> Sequential:
     return _vgg_like("", 64, 1024, 200)
 
@@ -180,6 +185,7 @@ MODEL_ZOO = {
     "mnist_cnn": create_mnist_trainer,
     "cifar10_cnn_v1": create_cifar10_trainer_v1,
     "cifar10_cnn_v2": create_cifar10_trainer_v2,
+    "cifar100_cnn": create_cifar100_trainer,
     "resnet9_cifar10": create_resnet9_cifar10,
     "resnet18_cifar10": create_resnet18_cifar10,
     "resnet20_cifar10": create_resnet20_cifar10,

@@ -182,6 +182,16 @@ class DistCommunicator(Communicator):
                     meta["t"].append((tuple(t.shape), str(t.dtype).replace("torch.", ""), nhwc))
                     tensors.append(t.permute(0, 2, 3, 1) if nhwc else t)
             payload = ("job", meta)
+        elif isinstance(payload, (dict, list, tuple)):
+            # parameter bundles (SEND_PARAMS / LOAD_PARAMS): tensors are pulled out, concatenated into one flat float32
+            # buffer and sent over the tensor transport; the store only carries the structure
+            found: List[torch.Tensor] = []
+            skeleton = _strip_tensors(payload, found)
+            if found:
+                flat = torch.cat([t.detach().to(torch.float32).reshape(-1).cpu() for t in found]) \
+                    if found else torch.empty(0)
+                tensors.append(flat)
+                payload = ("bundle", skeleton, [(tuple(t.shape), t.numel()) for t in found])
         # the store assigns the per-destination sequence number atomically (several senders may target one rank)
         seq = self.store.add(f"mbox/{dst}/tail", 1) - 1
         blob = pickle.dumps((msg.recipient_id, msg.sender_id, int(msg.command_type), payload, self.rank))
@@ -222,6 +232,18 @@ class DistCommunicator(Communicator):
                     buf = buf.to(self.device)
                     got.append(buf.permute(0, 3, 1, 2) if nhwc else buf)
                 payload = Job(got[0], meta["mb"], got[1])
+            elif isinstance(payload, tuple) and payload and payload[0] == "bundle":
+                _, skeleton, specs = payload
+                group, dev = self._tensor_route(src)
+                total = sum(n for _, n in specs)
+                flat = torch.empty(total, dtype=torch.float32, device=dev)
+                dist.recv(flat, src=src, group=group)
+                flat = flat.cpu()
+                parts, o = [], 0
+                for shape, n in specs:
+                    parts.append(flat[o:o + n].reshape(shape).clone())
+                    o += n
+                payload = _restore_tensors(skeleton, parts)
             self.enqueue_input_message(Message(recipient, CommandType(ctype), payload, sender))
 
     def flush_output_messages(self):
@@ -243,3 +265,24 @@ class DistCommunicator(Communicator):
             time.sleep(0.0002)
 
 
+
+
+def _strip_tensors(obj, found):
+    if isinstance(obj, torch.Tensor):
+        found.append(obj)
+        return ("__tensor__", len(found) - 1)
+    if isinstance(obj, dict):
+        return {k: _strip_tensors(v, found) for k, v in obj.items()}
+    if isinstance(obj, (list, tuple)):
+        return [_strip_tensors(v, found) for v in obj]
+    return obj
+
+
+def _restore_tensors(obj, parts):
+    if isinstance(obj, (list, tuple)) and len(obj) == 2 and obj[0] == "__tensor__":
+        return parts[obj[1]]
+    if isinstance(obj, dict):
+        return {k: _restore_tensors(v, parts) for k, v in obj.items()}
+    if isinstance(obj, list):
+        return [_restore_tensors(v, parts) for v in obj]
+    return obj

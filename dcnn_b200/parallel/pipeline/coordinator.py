@@ -238,6 +238,18 @@ class Coordinator:
         self.join(CommandType.PROFILING_CLEARED, self.num_stages, 30.0)
         self.comm.dequeue_all_messages_by_type(CommandType.PROFILING_CLEARED)
 
+    def fetch_loss_stats(self, timeout: float = 30.0) -> dict:
+        """Loss / correct-count accumulated on the last stage since the last fetch or update (used by validation,
+        where no optimizer step must happen)."""
+        self._broadcast(CommandType.STATUS_REQUEST, "reset_stats")
+        self.join(CommandType.STATUS_RESPONSE, self.num_stages, timeout)
+        out = {"loss": float("nan"), "correct": 0.0}
+        for m in self.comm.dequeue_all_messages_by_type(CommandType.STATUS_RESPONSE):
+            p = m.payload or {}
+            if p.get("count", 0) > 0:
+                out = {"loss": p["loss_sum"] / p["count"], "correct": p["correct_sum"]}
+        return out
+
     def request_status_from_all_stages(self, timeout: float = 30.0):
         self._broadcast(CommandType.STATUS_REQUEST)
         self.join(CommandType.STATUS_RESPONSE, self.num_stages, timeout)

@@ -140,7 +140,11 @@ class PipelineStage:
         elif c == CommandType.STATUS_REQUEST:
             self._send("coordinator", CommandType.STATUS_RESPONSE,
                        {"stage": self.name, "layers": self.model.layer_size() if self.model else 0,
-                        "training": self.model.is_training() if self.model else None})
+                        "training": self.model.is_training() if self.model else None,
+                        "loss_sum": self.loss_sum, "correct_sum": self.correct_sum, "count": self.loss_count})
+            if msg.payload == "reset_stats":
+                self.loss_sum = self.correct_sum = 0.0
+                self.loss_count = 0
         elif c == CommandType.HEALTH_CHECK:
             self._send("coordinator", CommandType.HEALTH_CHECK, self.name)
         elif c == CommandType.BARRIER_SYNC:

@@ -1,0 +1,41 @@
+"""Shared scaffolding of the example entrypoints (the reference's examples/*.cpp): .env + environment configuration,
+device selection, dataset-or-synthetic loaders.  ``SYNTHETIC=1`` (or a missing dataset directory) substitutes synthetic
+data of the dataset's shape, which is what the benchmark configs in BASELINE.json use."""
+from __future__ import annotations
+
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch  # noqa: E402
+
+from dcnn_b200.data import SyntheticDataLoader  # noqa: E402
+from dcnn_b200.train import TrainingConfig  # noqa: E402
+from dcnn_b200.utils.env import get_env, load_env_file  # noqa: E402
+
+
+def setup():
+    print("Loading environment variables...")
+    if not (os.path.exists("./.env") and load_env_file("./.env")):
+        print("No .env file found, using default training parameters.")
+    cfg = TrainingConfig().load_from_env()
+    if cfg.device_type == "GPU" and not torch.cuda.is_available():
+        raise SystemExit("DEVICE_TYPE=GPU but no CUDA device is visible")
+    print(f"Using device type: {cfg.device_type}")
+    cfg.print_config()
+    return cfg
+
+
+def loaders(real_factory, data_dir, shape, classes, cfg, n_train=None, n_test=None):
+    """Real dataset if present (and SYNTHETIC != 1), else synthetic tensors of the same shape."""
+    synthetic = get_env("SYNTHETIC", False) or not os.path.exists(data_dir)
+    if not synthetic:
+        try:
+            return real_factory(data_dir)
+        except Exception as e:  # missing/corrupt files: fall back, loudly
+            print(f"Could not load dataset from {data_dir} ({e}); using synthetic data")
+    n_train = n_train or get_env("SYNTHETIC_TRAIN_SAMPLES", cfg.batch_size * 8)
+    n_test = n_test or get_env("SYNTHETIC_TEST_SAMPLES", cfg.batch_size * 2)
+    print(f"Using synthetic data: {n_train} train / {n_test} test samples of shape {tuple(shape)}, {classes} classes")
+    return SyntheticDataLoader(n_train, shape, classes, seed=0), SyntheticDataLoader(n_test, shape, classes, seed=1)

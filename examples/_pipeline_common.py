@@ -1,0 +1,51 @@
+"""Bring-up shared by the pipeline coordinator examples.
+
+Launch modes:
+  * single process  (``python examples/<coordinator>.py``): every stage is a thread of this process
+    (InProcessCoordinator), stage i on GPU i when GPUs are visible and DEVICE_TYPE=GPU, else on the CPU;
+  * one process per participant (``torchrun --nproc-per-node S+1 examples/<coordinator>.py``): rank 0 is the
+    coordinator (owns the data loader, CPU side), ranks 1..S run a NetworkStageWorker on GPU rank-1.  This is the
+    counterpart of starting ``network_worker <port> --gpu`` S times plus a coordinator binary in the reference."""
+from __future__ import annotations
+
+import os
+
+import torch
+
+from _common import get_env
+
+from dcnn_b200.parallel.pipeline import DistributedCoordinator, InProcessCoordinator, NetworkStageWorker
+from dcnn_b200.parallel.pipeline.launch import init_distributed, pipeline_groups
+
+
+def make_coordinator(model, optimizer, loss, num_stages, cfg, partitioner=None, seed=1234):
+    """Returns (coordinator | None, is_coordinator).  Worker ranks serve until SHUTDOWN and return (None, False)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    use_gpu = cfg.device_type == "GPU"
+    if world == 1:
+        ngpu = torch.cuda.device_count() if use_gpu else 0
+        devs = [f"cuda:{i % ngpu}" if ngpu else "cpu" for i in range(num_stages)]
+        coord = InProcessCoordinator(model, optimizer, devs)
+    else:
+        rank, world = init_distributed(use_gpu=use_gpu)
+        num_stages = world - 1
+        stage_ranks = list(range(1, world))
+        if rank != 0 and use_gpu:
+            torch.cuda.set_device((rank - 1) % torch.cuda.device_count())
+        store, control, data = pipeline_groups(stage_ranks, use_gpu)
+        if rank != 0:
+            NetworkStageWorker(rank, store, control, data, stage_ranks, use_gpu,
+                               (rank - 1) % max(1, torch.cuda.device_count())).start(threaded=False)
+            return None, False
+        devs = [f"cuda:{(r - 1)}" if use_gpu else "cpu" for r in stage_ranks]
+        coord = DistributedCoordinator(model, optimizer, store, control, 0, stage_ranks, devs)
+    coord.seed = seed
+    coord.set_loss_function(loss)
+    if partitioner is not None:
+        coord.set_partitioner(partitioner)
+    coord.set_num_microbatches(cfg.num_microbatches)
+    coord.initialize()
+    if not coord.deploy_stages():
+        raise SystemExit("Failed to deploy stages")
+    coord.start()
+    return coord, True

@@ -1,0 +1,35 @@
+#!/usr/bin/env python
+"""Semi-async pipeline coordinator, ResNet-18 Tiny-ImageNet -- counterpart of the reference's examples/coordinator_tiny_imagenet.cpp.
+Single process: stages are threads (one per GPU when DEVICE_TYPE=GPU).  Multi-process:
+torchrun --nproc-per-node <S+1> examples/coordinator_tiny_imagenet.py (rank 0 = coordinator, ranks 1..S = stage workers)."""
+from _common import get_env, loaders, setup
+from _pipeline_common import make_coordinator
+
+from dcnn_b200 import nn
+from dcnn_b200.data import create_tiny_imagenet_data_loaders
+from dcnn_b200.models import create_resnet18_tiny_imagenet
+from dcnn_b200.parallel.pipeline.train import train_model, validate_semi_async_epoch
+from dcnn_b200.partitioner import NaivePartitioner
+
+
+def main():
+    cfg = setup()
+    model = create_resnet18_tiny_imagenet()                      # NOT initialised on the coordinator: stages build their own shards
+    optimizer = nn.Adam(get_env('LR_INITIAL', 0.0001), 0.9, 0.999, 1e-7)
+    loss = nn.LossFactory.create_logsoftmax_crossentropy()
+    coord, is_coord = make_coordinator(model, optimizer, loss, get_env("NUM_STAGES", 2), cfg, NaivePartitioner())
+    if not is_coord:
+        return
+    train_loader, test_loader = loaders(create_tiny_imagenet_data_loaders, "./data/tiny-imagenet-200", (3, 64, 64), 200, cfg)
+    history = train_model(coord, train_loader, test_loader, cfg, schedule="semi_async")
+    val_loss, val_acc = validate_semi_async_epoch(coord, test_loader) if coord.loss_on_last_stage else (float("nan"), float("nan"))
+    print(f"Validation - Loss: {val_loss:.4f}, Accuracy: {100 * val_acc:.2f}%")
+    coord.print_profiling_on_all_stages()
+    if coord.save_checkpoint("model_snapshots/" + model.name()):
+        print("Model saved to model_snapshots/" + model.name())
+    coord.stop()
+    return history
+
+
+if __name__ == "__main__":
+    main()

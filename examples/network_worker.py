@@ -1,0 +1,52 @@
+#!/usr/bin/env python
+"""Pipeline stage worker -- counterpart of the reference's ``network_worker <port> [--gpu] ...``
+(examples/network_worker.cpp:155-195).  Ports/hosts are replaced by torch.distributed ranks:
+
+    RANK=<1..S> WORLD_SIZE=<S+1> MASTER_ADDR=127.0.0.1 MASTER_PORT=29500 python examples/network_worker.py --gpu
+
+The process joins the job, waits for CONFIG_TRANSFER from the coordinator (rank 0), builds its stage and serves
+FORWARD/BACKWARD/UPDATE jobs until SHUTDOWN."""
+import argparse
+import os
+
+from _common import sys  # noqa: F401  (path setup)
+
+import torch
+
+from dcnn_b200.parallel.pipeline import NetworkStageWorker
+from dcnn_b200.parallel.pipeline.launch import init_distributed, pipeline_groups
+from dcnn_b200.utils.hardware import HardwareInfo, ThreadAffinity
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpu", action="store_true", help="run the stage on a GPU (index = rank-1 unless --device)")
+    ap.add_argument("--device", type=int, default=None)
+    ap.add_argument("--num-threads", type=int, default=0, help="CPU threads for a CPU stage")
+    ap.add_argument("--pin-numa", action="store_true", help="pin this process to the NUMA node of its GPU")
+    ap.add_argument("--show-cores", action="store_true")
+    args = ap.parse_args()
+    hw = HardwareInfo()
+    hw.initialize()
+    if args.show_cores:
+        hw.print_info()
+        ThreadAffinity(hw).print_affinity_info()
+    rank, world = init_distributed(use_gpu=args.gpu)
+    if rank == 0:
+        raise SystemExit("rank 0 is the coordinator; start a coordinator example there")
+    dev = args.device if args.device is not None else (rank - 1) % max(1, torch.cuda.device_count())
+    if args.gpu:
+        torch.cuda.set_device(dev)
+        if args.pin_numa:
+            ThreadAffinity(hw).pin_to_gpu_node(dev)
+    elif args.num_threads:
+        torch.set_num_threads(args.num_threads)
+    stage_ranks = list(range(1, world))
+    store, control, data = pipeline_groups(stage_ranks, args.gpu)
+    print(f"Network stage worker rank {rank} listening ({'GPU ' + str(dev) if args.gpu else 'CPU'})")
+    NetworkStageWorker(rank, store, control, data, stage_ranks, args.gpu, dev).start(threaded=False)
+    print(f"worker {rank}: shutdown")
+
+
+if __name__ == "__main__":
+    main()
