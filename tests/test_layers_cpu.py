@@ -187,7 +187,7 @@ def test_zoo_builds_and_shapes(name):
     first = cfg["layers"][0]["parameters"]
     hw = {"mnist_cnn": 28, "resnet50_imagenet": 224}.get(name, 64 if "tiny" in name else 32)
     out = m.compute_output_shape([2, first["in_channels"], hw, hw])
-    classes = {"mnist_cnn": 10, "resnet50_imagenet": 1000}.get(name, 200 if "tiny" in name else 10)
+    classes = {"mnist_cnn": 10, "resnet50_imagenet": 1000, "cifar100_cnn": 100}.get(name, 200 if "tiny" in name else 10)
     assert out == [2, classes, 1, 1]
     m2 = dc.Sequential.load_from_config(json.loads(json.dumps(cfg)))
     assert m2.get_config() == cfg
