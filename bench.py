@@ -93,6 +93,9 @@ def main():
     args = parse()
     if args.impl == "reference":
         return reference_arm(args)
+    if args.parallelism.startswith("pp"):
+        # no lazy kernel loading in the middle of a pipeline schedule (see PipelineEngine._warm_kernels)
+        os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
 
     import torch
     import torch.distributed as dist

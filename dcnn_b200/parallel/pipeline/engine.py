@@ -86,6 +86,54 @@ class PipelineEngine:
         self.g_send_grad = links.bwd[stage - 1] if not self.is_first else None  # gradients to prev
         self._pending_sends = []
         self.last_stats = {}
+        self._kernels_warm = False
+        self._warm_links()
+
+    # -- start-up hygiene ------------------------------------------------------------------------------------
+    # Two things may block the HOST in the middle of a schedule and, together with a pre-posted receive that is
+    # spinning on the GPU, close a cross-rank wait cycle (CUDA documents the first one for lazy module loading):
+    #   (a) the first launch of a kernel (lazy module load synchronises the context, i.e. waits for the spinning receive),
+    #   (b) the first use of a communicator (connection set-up is a host-side handshake with the peer).
+    # Both are therefore done up front, in an order that cannot cycle.
+    def _warm_links(self):
+        if self.S == 1:
+            return
+        token = torch.zeros(4, device=self.device)
+        for s in range(self.S - 1):          # links in global order: every rank walks the same list
+            if self.stage == s:
+                dist.send(token, dst=self.links.ranks[s + 1], group=self.links.fwd[s])
+                dist.recv(token, src=self.links.ranks[s + 1], group=self.links.bwd[s])
+            elif self.stage == s + 1:
+                dist.recv(token, src=self.links.ranks[s], group=self.links.fwd[s])
+                dist.send(token, dst=self.links.ranks[s], group=self.links.bwd[s])
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+
+    def _warm_kernels(self, in_shape, targets_shape):
+        """One local forward+backward(+loss) on zeros so that every kernel of this stage is loaded and the caching
+        allocator has its blocks before any transfer is posted.  Model state is restored afterwards."""
+        if self._kernels_warm:
+            return
+        self._kernels_warm = True
+        if self.device.type != "cuda":
+            return
+        bufs = {k: v.clone() for k, v in self.model.buffers().items()}
+        scratch_mb = self.M + 7
+        x = torch.zeros(in_shape, device=self.device)
+        y = self.model.forward(x, scratch_mb)
+        if self.is_last and targets_shape is not None:
+            t = torch.zeros(targets_shape, device=self.device)
+            t.view(targets_shape[0], -1)[:, 0] = 1
+            _, g, _ = self.loss_fn.forward_backward(y, t)
+        else:
+            g = torch.zeros_like(y)
+        self.model.backward(g, scratch_mb)
+        for gr in self.model.gradients():
+            gr.zero_()
+        for k, v in self.model.buffers().items():
+            v.copy_(bufs[k])
+        self.model.clear_cache()
+        torch.cuda.synchronize(self.device)
 
     # -- shapes ------------------------------------------------------------------------------------------
     def _boundary_shapes(self, mb_input_shape):
@@ -142,6 +190,7 @@ class PipelineEngine:
             in_shapes.append(i)
             out_shapes.append(o)
 
+        self._warm_kernels(in_shapes[0], list(ts[0].shape) if self.is_last else None)
         sched = self.schedule
         recv_slot = {}
 

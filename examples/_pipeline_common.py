@@ -10,6 +10,8 @@ from __future__ import annotations
 
 import os
 
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")   # stage workers must not lazy-load kernels mid-schedule
+
 import torch
 
 from _common import get_env

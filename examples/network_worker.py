@@ -9,6 +9,8 @@ FORWARD/BACKWARD/UPDATE jobs until SHUTDOWN."""
 import argparse
 import os
 
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
+
 from _common import sys  # noqa: F401  (path setup)
 
 import torch
