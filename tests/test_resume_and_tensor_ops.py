@@ -1,0 +1,74 @@
+import torch
+import torch.nn.functional as F
+
+from dcnn_b200 import nn as dnn
+from dcnn_b200.io import load_training_state, save_training_state
+from dcnn_b200.models import create_mnist_trainer
+from dcnn_b200.ops import tensor_ops as T
+from dcnn_b200.train import TrainStep
+
+
+def _data():
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(8, 1, 28, 28, generator=g)
+    t = F.one_hot(torch.randint(0, 10, (8,), generator=g), 10).float().reshape(8, 10, 1, 1)
+    return x, t
+
+
+def test_resume_continues_bit_identically(tmp_path):
+    x, t = _data()
+
+    def fresh():
+        m = create_mnist_trainer()
+        m.set_seed(1)
+        m.initialize()
+        o = dnn.Adam(1e-2)
+        o.attach(m.parameters(), m.gradients())
+        return m, o, TrainStep(m, o, dnn.SoftmaxCrossEntropyLoss())
+    m, o, step = fresh()
+    for _ in range(3):
+        step(x, t)
+    path = str(tmp_path / "ck" / "mnist")
+    save_training_state(path, m, o, epoch=2, extra={"note": "hi"})
+    for _ in range(2):
+        step(x, t)
+    want = [p.clone() for p in m.parameters()] + list(m.buffers().values())
+    m2, o2, step2 = fresh()
+    blob = load_training_state(path, m2, o2)
+    assert blob["epoch"] == 2 and blob["extra"]["note"] == "hi" and o2.t == 3
+    for _ in range(2):
+        step2(x, t)
+    got = [p for p in m2.parameters()] + list(m2.buffers().values())
+    for a, b in zip(got, want):
+        assert torch.equal(a, b)
+
+
+def test_tensor_ops_match_reference_semantics():
+    x = torch.randn(2, 3, 6, 5)
+    cols = T.im2col(x, 3, 3, 1, 1, 1, 1)
+    assert cols.shape == (27, 2 * 6 * 5)
+    w = torch.randn(4, 3, 3, 3)
+    y = (w.reshape(4, 27) @ cols).reshape(4, 2, 6, 5).permute(1, 0, 2, 3)
+    assert torch.allclose(y, F.conv2d(x, w, padding=1), atol=1e-5)
+    back = T.col2im(cols, 2, 3, 6, 5, 3, 3, 1, 1, 1, 1)
+    ones = T.col2im(torch.ones_like(cols), 2, 3, 6, 5, 3, 3, 1, 1, 1, 1)
+    assert torch.allclose(back / ones, x, atol=1e-5)
+    p = T.pad(x, 2, 1)
+    assert p.shape == (2, 3, 10, 7) and torch.equal(T.unpad(p, 2, 1), x)
+    assert T.crop(x, 1, 1, 3, 2).shape == (2, 3, 3, 2)
+    assert T.slice_channels(x, 1, 2).shape == (2, 2, 6, 5) and T.slice_batch(x, 1, 2).shape == (1, 3, 6, 5)
+    parts = T.split(torch.arange(10).reshape(10, 1, 1, 1), 3)
+    assert [q.shape[0] for q in parts] == [3, 3, 4]
+    s = T.apply_softmax(x.clone())
+    assert torch.allclose(s.sum(1), torch.ones(2, 6, 5), atol=1e-6)
+    a, b = torch.randn(4, 6), torch.randn(6, 5)
+    assert torch.allclose(T.gemm(a, b), a @ b, atol=1e-6)
+    assert torch.allclose(T.gemm(a, b.t().contiguous(), trans_b=True, alpha=2.0), 2 * a @ b, atol=1e-5)
+    c = torch.ones(4, 5)
+    T.gemm(a, b, beta=0.5, c=c)
+    assert torch.allclose(c, a @ b + 0.5, atol=1e-5)
+    yv = torch.ones(3)
+    T.axpy(2.0, torch.tensor([1.0, 2.0, 3.0]), yv)
+    assert torch.equal(yv, torch.tensor([3.0, 5.0, 7.0]))
+    assert float(T.dot_product(torch.ones(4), torch.arange(4.0))) == 6.0
+    assert torch.equal(T.cnhw_to_nchw(T.nchw_to_cnhw(x)), x)
