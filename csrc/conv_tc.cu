@@ -522,6 +522,289 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
 }
 
 // =====================================================================================================
+// conv_tc3: conv_tc2 with a 256-pixel M tile (two M=128 MMAs per k-step that share one B tile in shared memory).
+//
+// Why: the ncu capture of conv_tc2 (profiles/03) shows the TF32 mainloop pinned at the L2->SM operand feed
+// (~12.5 TB/s chip-wide, 42.6 B/clk/SM), not at the tensor pipe (40 % active) or DRAM (14 %).  A 128x128 tile moves
+// (128+128)*128 B per 128x128x32 MAC block = 32 FLOP/B; 256x128 moves (256+128)*128 B for twice the math = 42.7
+// FLOP/B, i.e. a 1.33x higher ceiling for every layer regardless of Cout.  The accumulators (2 halves x 2 buffers x BN
+// columns) fill TMEM exactly at BN = 128.
+//
+// The epilogue treats each 128-row half as conv_tc2 treats a tile (own TMA store box, own BN-statistics tile), so
+// the partial-statistics buffer has 2 * m_tiles entries.  Selected with DCNN_CONV_V3=1 (off by default until its
+// hardware validation run; see dcnn_conv_tc / dcnn_conv_tc_stat_tiles).
+// =====================================================================================================
+struct ConvTc3Params {
+  ConvTcParams b;     // bn/bh/bw, tiles_* and m_tiles describe the 256-pixel LOAD box
+  int obn, obh, obw;  // store / statistics box: one half (128 pixels) of the load box
+  int hdn, hdh, hdw;  // coordinate offset of half 1 inside the load box
+};
+
+template <int BN, int STAGES>
+struct ConvTc3Smem {
+  static constexpr int kABytes = 2 * kBM * 128;
+  static constexpr int kBBytes = BN * 128;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kPipeBytes = STAGES * kStageBytes;
+  static constexpr int kChunks = BN / 32;
+  static constexpr int kStagingBytes = kChunks * kBM * 128;
+  static constexpr int kRedBytes = 2 * 4 * BN * 4;
+  static constexpr int kBarOff = kPipeBytes + kStagingBytes;
+  static constexpr int kRedOff = kBarOff + 256;
+  static constexpr int kFlagOff = kRedOff + kRedBytes;
+  static constexpr int kTotalBytes = kFlagOff + 128 + 1024 /*align*/;
+  static_assert(kTotalBytes <= 232448, "conv_tc3 shared memory exceeds 227 KB");
+  static_assert(4 * BN <= 512, "conv_tc3 accumulators exceed TMEM");
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                               const __grid_constant__ CUtensorMap tmB,
+                                                               const __grid_constant__ CUtensorMap tmO,
+                                                               const __grid_constant__ ConvTc3Params pp) {
+  using S = ConvTc3Smem<BN, STAGES>;
+  const ConvTcParams& p = pp.b;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + S::kPipeBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  float* red = reinterpret_cast<float*>(smem + S::kRedOff);
+  uint8_t* row_valid = smem + S::kFlagOff;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int cchunks = p.Cin / kBK;
+  const int num_kb = p.num_taps * cchunks;
+  constexpr uint32_t kTmemCols = 4 * BN;  // 2 buffers x 2 halves (power of two: 256 or 512)
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 1);
+        mbar_init(&empty_bar[s], 1);
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full_bar[a], 1);
+        mbar_init(&tmem_empty_bar[a], 4);  // one arrival per epilogue warp
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer: one 256-pixel A box + one B box per stage =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % p.n_tiles;
+        const int m_tile = tile / p.n_tiles;
+        const int tw = m_tile % p.tiles_w;
+        const int th = (m_tile / p.tiles_w) % p.tiles_h;
+        const int tn = m_tile / (p.tiles_w * p.tiles_h);
+        const int n0 = tn * p.bn, ih0 = th * p.bh * p.in_mul_h, iw0 = tw * p.bw * p.in_mul_w;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int t = kb / cchunks;
+          const int c = kb - t * cchunks;
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
+          uint8_t* sA = smem + stage * S::kStageBytes;
+          tma_load_4d(sA, &tmA, &full_bar[stage], c * kBK, iw0 + p.tap_dw[t], ih0 + p.tap_dh[t], n0);
+          tma_load_2d(sA + S::kABytes, &tmB, &full_bar[stage], p.tap_w[t] * p.Cin + c * kBK, n_tile * BN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===================== MMA issuer: rows 0-127 -> columns [0,BN), rows 128-255 -> [BN,2BN) =====================
+      constexpr uint32_t idesc = make_idesc_tf32(kBM, BN, 0, 0);
+      constexpr uint64_t desc_hi = make_smem_desc_hi(16, 1024);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * (2 * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+          const uint32_t b_addr = a_addr + S::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 8; ++k) {
+            const uint64_t bdesc = make_smem_desc(b_addr + k * 32, desc_hi);
+            mma_tf32_ss(tmem_d, make_smem_desc(a_addr + k * 32, desc_hi), bdesc, idesc, (kb | k) != 0);
+            mma_tf32_ss(tmem_d + BN, make_smem_desc(a_addr + kBM * 128 + k * 32, desc_hi), bdesc, idesc,
+                        (kb | k) != 0);
+          }
+          mma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit(&tmem_full_bar[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5), one 128-row half at a time =====================
+    const int q = warp & 3;
+    const int r = q * 32 + lane;     // row inside the half
+    const int e = threadIdx.x - 64;  // 0..127
+    const bool issuer = (e == 0);
+    const int w_l = r % pp.obw, h_l = (r / pp.obw) % pp.obh, n_l = r / (pp.obw * pp.obh);
+    const int stat_tiles = 2 * p.m_tiles;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int n_tile = tile % p.n_tiles;
+      const int m_tile = tile / p.n_tiles;
+      const int tw = m_tile % p.tiles_w;
+      const int th = (m_tile / p.tiles_w) % p.tiles_h;
+      const int tn = m_tile / (p.tiles_w * p.tiles_h);
+      const int col_base = n_tile * BN;
+
+      mbar_wait(&tmem_full_bar[as], aphase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        const int n0 = tn * p.bn + half * pp.hdn, oh0 = th * p.bh + half * pp.hdh, ow0 = tw * p.bw + half * pp.hdw;
+        const bool full_tile = (n0 + pp.obn <= p.N) && (oh0 + pp.obh <= p.OH) && (ow0 + pp.obw <= p.OW);
+        const int st = m_tile * 2 + half;  // statistics tile
+
+        if (issuer) tma_store_wait_read();  // earlier stores no longer read the staging buffer
+        if (p.partials != nullptr && !full_tile)
+          row_valid[r] = ((n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW)) ? 1 : 0;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+
+        const uint32_t tmem_d = tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16);
+#pragma unroll 1
+        for (int ch = 0; ch < S::kChunks; ++ch) {
+          if (col_base + ch * 32 >= p.Cout) break;
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
+          tmem_ld_wait();
+          uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 o;
+            o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
+            o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
+            if (p.bias != nullptr) {
+              const int c = col_base + ch * 32 + 4 * j;
+              if (c < p.Cout) {
+                const float4 b = ldg4(p.bias + c);
+                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+              }
+            }
+            *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
+          }
+        }
+        if (half == 1) {
+          // both halves read: hand the accumulator buffer back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+        }
+        fence_proxy_async();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+
+        if (issuer) {
+          for (int ch = 0; ch < S::kChunks; ++ch) {
+            const int c = col_base + ch * 32;
+            if (c >= p.Cout) break;
+            if (p.accumulate) tma_reduce_add_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
+            else tma_store_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
+          }
+          tma_store_commit();
+        }
+
+        if (p.partials != nullptr) {
+          const int cl = e & 31, rg = e >> 5;
+          int cnt = kBM;
+          if (!full_tile) {
+            cnt = 0;
+            for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
+          }
+          for (int ch = 0; ch < S::kChunks; ++ch) {
+            if (col_base + ch * 32 >= p.Cout) break;
+            const uint8_t* src = staging + ch * (kBM * 128);
+            const float kshift = *reinterpret_cast<const float*>(src + ((cl >> 2) << 4) + ((cl & 3) << 2));  // row 0
+            float s = 0.f, qq = 0.f;
+            if (full_tile) {
+#pragma unroll 8
+              for (int i = 0; i < 32; ++i) {
+                const int rr = rg * 32 + i;
+                const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
+                                                                ((cl & 3) << 2));
+                const float d = x - kshift;
+                s += d;
+                qq = fmaf(d, d, qq);
+              }
+            } else {
+              for (int i = 0; i < 32; ++i) {
+                const int rr = rg * 32 + i;
+                const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
+                                                                ((cl & 3) << 2));
+                const float d = row_valid[rr] ? x - kshift : 0.f;
+                s += d;
+                qq = fmaf(d, d, qq);
+              }
+            }
+            red[(0 * 4 + rg) * BN + ch * 32 + cl] = s;
+            red[(1 * 4 + rg) * BN + ch * 32 + cl] = qq;
+          }
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          for (int j = e; j < BN; j += 128) {
+            const int c = col_base + j;
+            if (c < p.Cout) {
+              const int ch = j >> 5, cl2 = j & 31;
+              const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) +
+                                                                   ((cl2 & 3) << 2));
+              const float s = red[(0 * 4 + 0) * BN + j] + red[(0 * 4 + 1) * BN + j] + red[(0 * 4 + 2) * BN + j] +
+                              red[(0 * 4 + 3) * BN + j];
+              const float qq = red[(1 * 4 + 0) * BN + j] + red[(1 * 4 + 1) * BN + j] + red[(1 * 4 + 2) * BN + j] +
+                               red[(1 * 4 + 3) * BN + j];
+              const float n = (float)cnt;
+              p.partials[((long long)st * 2 + 0) * p.Cout + c] = s + n * kshift;
+              p.partials[((long long)st * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
+            }
+          }
+          if (e == 0 && n_tile == 0) p.partials[(long long)stat_tiles * 2 * p.Cout + st] = (float)cnt;
+        }
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (issuer) tma_store_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// =====================================================================================================
 // wgrad
 // =====================================================================================================
 constexpr int kWPix = 64;  // reduction (pixel) rows per pipeline stage
@@ -795,6 +1078,39 @@ static int launch_conv2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 }
 
 template <int BN, int STAGES>
+static int launch_conv3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
+                        const ConvTc3Params& p, cudaStream_t stream) {
+  using S = ConvTc3Smem<BN, STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         S::kTotalBytes));
+    attr_set = true;
+  }
+  const long long tiles = (long long)p.b.m_tiles * p.b.n_tiles;
+  const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+  conv_tc3_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, tmO, p);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+// conv_tc3 is used when it is switched on (DCNN_CONV_V3=1), the vectorised epilogue applies (Cout % 4 == 0) and the
+// loop space has at least one 256-pixel tile per SM; smaller problems keep the 128-pixel tiles of conv_tc2.
+static bool conv_v3_enabled() {
+  static const bool on = getenv("DCNN_CONV_V3") != nullptr && atoi(getenv("DCNN_CONV_V3")) != 0 &&
+                         !(getenv("DCNN_CONV_V1") != nullptr && atoi(getenv("DCNN_CONV_V1")) != 0);
+  return on;
+}
+static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int* bn, int* bh, int* bw) {
+  if (!conv_v3_enabled() || (Cout & 3) != 0) return false;
+  *bn = *bh = *bw = 1;
+  choose_box(N, OH, OW, 2 * kBM, mul_h, mul_w, bn, bh, bw);
+  const long long m_tiles = (long long)ceil_div(OW, *bw) * ceil_div(OH, *bh) * ceil_div(N, *bn);
+  return m_tiles >= num_sms();
+}
+
+template <int BN, int STAGES>
 static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvTcParams& p, cudaStream_t stream) {
   using S = ConvTcSmem<BN, STAGES>;
   static bool attr_set = false;
@@ -838,6 +1154,16 @@ DCNN_API int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w) {
   return ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
 }
 
+// Number of BatchNorm partial-statistics tiles dcnn_conv_tc will emit for this problem (the partials buffer holds
+// tiles*(2*Cout+1) floats).  Equals dcnn_conv_tc_m_tiles unless the 256-pixel kernel is selected, which emits two
+// 128-row statistics tiles per M tile.
+DCNN_API int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout) {
+  int bn, bh, bw;
+  if (conv_v3_applies(N, OH, OW, mul_h, mul_w, Cout, &bn, &bh, &bw))
+    return 2 * ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
+  return dcnn_conv_tc_m_tiles(N, OH, OW, mul_h, mul_w);
+}
+
 // Generic tap-list implicit GEMM (see file header).  x: NHWC [N][H][W][Cin] (Cin % 32 == 0),
 // w: [Cout][Ktot] with K index = tap_w*Cin + c.  Output pixel (n,oh,ow), channel oc is written to
 // out[n*out_sn + oh*out_sh + ow*out_sw + oc].
@@ -871,6 +1197,37 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   int rc = make_tmap_nhwc(&tmA, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
   if (rc) return rc;
   static const bool use_v1 = getenv("DCNN_CONV_V1") != nullptr && atoi(getenv("DCNN_CONV_V1")) != 0;
+  {
+    int bn3, bh3, bw3;
+    if (vec_ok && conv_v3_applies(N, OH, OW, in_mul_h, in_mul_w, Cout, &bn3, &bh3, &bw3)) {
+      ConvTc3Params q;
+      q.b = p;
+      q.b.bn = bn3; q.b.bh = bh3; q.b.bw = bw3;
+      q.b.tiles_n = ceil_div(N, bn3); q.b.tiles_h = ceil_div(OH, bh3); q.b.tiles_w = ceil_div(OW, bw3);
+      q.b.m_tiles = q.b.tiles_n * q.b.tiles_h * q.b.tiles_w;
+      // the second 128 rows of the box (row order n, h, w) start half-way along its slowest dimension of extent >= 2
+      q.obn = bn3; q.obh = bh3; q.obw = bw3;
+      q.hdn = q.hdh = q.hdw = 0;
+      if (bn3 >= 2) { q.obn = bn3 / 2; q.hdn = bn3 / 2; }
+      else if (bh3 >= 2) { q.obh = bh3 / 2; q.hdh = bh3 / 2; }
+      else { q.obw = bw3 / 2; q.hdw = bw3 / 2; }
+      CUtensorMap tmA3, tmO3;
+      rc = make_tmap_nhwc(&tmA3, x, N, H, W, Cin, bn3, bh3, bw3, in_mul_h, in_mul_w);
+      if (rc) return rc;
+      rc = make_tmap_out(&tmO3, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, q.obn, q.obh, q.obw);
+      if (rc) return rc;
+      if (Cout <= 64) {
+        q.b.n_tiles = 1;
+        rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
+        if (rc) return rc;
+        return launch_conv3<64, 4>(tmA3, tmB, tmO3, q, stream);
+      }
+      q.b.n_tiles = ceil_div(Cout, 128);
+      rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
+      if (rc) return rc;
+      return launch_conv3<128, 3>(tmA3, tmB, tmO3, q, stream);
+    }
+  }
   if (vec_ok && !use_v1) {
     // persistent kernel, TMA-store epilogue
     CUtensorMap tmO;

@@ -234,7 +234,10 @@ __global__ void bn_apply_scalar_kernel(const float* __restrict__ x, const float*
 
 // Backward reduce: per row tile, per channel: (sum g, sum g*xhat) with g = dout * (out > 0 if RELU).
 // Same grid/block shape as bn_colstats_kernel; partials [tiles][2][C].
-template <bool RELU>
+// RELU: 0 = no mask, 1 = mask from the saved activation output (needed when a residual was added before the ReLU),
+// 2 = mask recomputed as fmaf(x, scale, shift) > 0 -- bit-identical to what bn_apply_kernel evaluated in the forward
+// pass, and one activation-sized read cheaper (`out` then carries scale[C] followed by shift[C]).
+template <int RELU>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restrict__ dout, const float* __restrict__ x,
                                                             const float* __restrict__ out,
                                                             const float* __restrict__ mean,
@@ -249,14 +252,19 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
   float4 a = make_float4(0, 0, 0, 0), b = a;
   if (active) {
     const float4 mu = ldg4(mean + c), is = ldg4(invstd + c);
+    float4 sc = make_float4(0, 0, 0, 0), sf = sc;
+    if (RELU == 2) { sc = ldg4(out + c); sf = ldg4(out + C + c); }
 #pragma unroll 4
     for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
       float4 g = ldg4(dout + r * C + c);
       const float4 v = ldg4(x + r * C + c);
-      if (RELU) {
+      if (RELU == 1) {
         const float4 o = ldg4(out + r * C + c);
         g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
         g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+      } else if (RELU == 2) {
+        g.x = fmaf(v.x, sc.x, sf.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, sc.y, sf.y) > 0.f ? g.y : 0.f;
+        g.z = fmaf(v.z, sc.z, sf.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, sc.w, sf.w) > 0.f ? g.w : 0.f;
       }
       a.x += g.x; a.y += g.y; a.z += g.z; a.w += g.w;
       b.x = fmaf(g.x, (v.x - mu.x) * is.x, b.x); b.y = fmaf(g.y, (v.y - mu.y) * is.y, b.y);
@@ -288,7 +296,8 @@ __global__ void bn_bwd_reduce_scalar_kernel(const float* __restrict__ dout, cons
   float a = 0.f, b = 0.f;
   for (long long r = r0; r < r1; ++r) {
     float g = dout[r * C + c];
-    if (relu && !(out[r * C + c] > 0.f)) g = 0.f;
+    if (relu == 1 && !(out[r * C + c] > 0.f)) g = 0.f;
+    if (relu == 2 && !(fmaf(x[r * C + c], out[c], out[C + c]) > 0.f)) g = 0.f;
     a += g;
     b = fmaf(g, (x[r * C + c] - mean[c]) * invstd[c], b);
   }
@@ -367,7 +376,7 @@ __global__ void bn_bwd_finalize_sync_kernel(PeerPtrs peer_sums, PeerFlags flags,
 
 // dx = g*k1 + x*k2 + k3 with g = dout masked by (out > 0); optionally also writes the masked g (the gradient
 // that flows into the residual shortcut).
-template <bool RELU, bool MASKED>
+template <int RELU, bool MASKED>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ dout, const float* __restrict__ x,
                                                            const float* __restrict__ out, const float* __restrict__ k1,
                                                            const float* __restrict__ k2, const float* __restrict__ k3,
@@ -378,10 +387,14 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restri
     const int c = (int)(i % C4) * 4;
     float4 g = ldcs4(dout + i * 4);
     const float4 v = ldcs4(x + i * 4);
-    if (RELU) {
+    if (RELU == 1) {
       const float4 o = ldcs4(out + i * 4);
       g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
       g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+    } else if (RELU == 2) {
+      const float4 sc = ldg4(out + c), sf = ldg4(out + C4 * 4 + c);
+      g.x = fmaf(v.x, sc.x, sf.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, sc.y, sf.y) > 0.f ? g.y : 0.f;
+      g.z = fmaf(v.z, sc.z, sf.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, sc.w, sf.w) > 0.f ? g.w : 0.f;
     }
     const float4 a = ldg4(k1 + c), b = ldg4(k2 + c), d = ldg4(k3 + c);
     float4 r;
@@ -401,7 +414,8 @@ __global__ void bn_bwd_apply_scalar_kernel(const float* __restrict__ dout, const
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
     float g = dout[i];
-    if (relu && !(out[i] > 0.f)) g = 0.f;
+    if (relu == 1 && !(out[i] > 0.f)) g = 0.f;
+    if (relu == 2 && !(fmaf(x[i], out[c], out[C + c]) > 0.f)) g = 0.f;
     dx[i] = fmaf(g, k1[c], fmaf(x[i], k2[c], k3[c]));
     if (masked) masked[i] = g;
   }
@@ -646,8 +660,9 @@ DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* 
   const int rows = stat_rows_per_tile(M, &tiles);
   if ((C & 3) == 0) {
     dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
-    if (relu) bn_bwd_reduce_kernel<true><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
-    else bn_bwd_reduce_kernel<false><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    if (relu == 2) bn_bwd_reduce_kernel<2><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    else if (relu) bn_bwd_reduce_kernel<1><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    else bn_bwd_reduce_kernel<0><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
   } else {
     dim3 grid(tiles, ceil_div(C, 32));
     bn_bwd_reduce_scalar_kernel<<<grid, 32, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials, relu);
@@ -692,14 +707,18 @@ DCNN_API int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* o
     const long long t4 = total / 4;
     const int grid = ew_grid(t4, 256);
     const int C4 = C / 4;
-    if (relu && masked)
-      bn_bwd_apply_kernel<true, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    if (relu == 2 && masked)
+      bn_bwd_apply_kernel<2, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else if (relu == 2)
+      bn_bwd_apply_kernel<2, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else if (relu && masked)
+      bn_bwd_apply_kernel<1, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
     else if (relu)
-      bn_bwd_apply_kernel<true, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+      bn_bwd_apply_kernel<1, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
     else if (masked)
-      bn_bwd_apply_kernel<false, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+      bn_bwd_apply_kernel<0, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
     else
-      bn_bwd_apply_kernel<false, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+      bn_bwd_apply_kernel<0, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
   } else {
     bn_bwd_apply_scalar_kernel<<<ew_grid(total, 256), 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, total, C,
                                                                        relu);

@@ -465,7 +465,7 @@ class BatchNormLayer(Layer):
         mean, invstd = ops.bn_finalize(stats, self.epsilon, self.momentum, self.running_mean,
                                        self.running_var, sync=self.sync, gamma=self.gamma, beta=self.beta)
         out = ops.bn_apply(x, mean, invstd, self.gamma, self.beta, residual, relu)
-        self._cache[micro_batch_id] = (x, mean, invstd, out if relu else None, relu)
+        self._cache[micro_batch_id] = (x, mean, invstd, out if relu else None, relu, relu and residual is None)
         return out
 
     def backward(self, grad, micro_batch_id=0):
@@ -473,10 +473,12 @@ class BatchNormLayer(Layer):
         return dx
 
     def backward_fused(self, grad, micro_batch_id=0, want_masked=False):
-        x, mean, invstd, out, relu = self._cache[micro_batch_id]
+        x, mean, invstd, out, relu, plain_relu = self._cache[micro_batch_id]
         grad = ops.to_activation_layout(grad)
+        # plain_relu: no residual between BN and ReLU, so the mask can be recomputed from x (CUDA backend)
         return ops.bn_backward(grad, x, out, mean, invstd, self.gamma, self.gamma_grad,
-                               self.beta_grad, relu=relu, want_masked=want_masked, sync=self.sync)
+                               self.beta_grad, relu=relu, want_masked=want_masked, sync=self.sync,
+                               recompute_mask=plain_relu)
 
     def parameters(self):
         return [self.gamma, self.beta] if self.affine else []

@@ -30,6 +30,10 @@ def _p(t: Optional[torch.Tensor]):
     return P(t.data_ptr()) if t is not None else P(0)
 
 
+# DCNN_BN_RECOMPUTE_MASK=0 restores the read-the-saved-output ReLU mask in BatchNorm backward
+RECOMPUTE_RELU_MASK = os.environ.get("DCNN_BN_RECOMPUTE_MASK", "1") != "0"
+
+
 def tc_enabled() -> bool:
     return os.environ.get("DCNN_DISABLE_TC", "0") != "1"
 
@@ -99,7 +103,7 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
         stats = None
         partials = None
         if want_stats:
-            tiles = lib().dcnn_conv_tc_m_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_))
+            tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_), I(Cout))
             partials = torch.empty(tiles * (2 * Cout + 1), device=x.device, dtype=torch.float32)
             stats = CudaStats(partials, tiles, Cout, N * OH * OW)
         _conv_tc(x, N, H, W, Cin, w, Cout, R * S * Cin, y, 0, OH * OW * Cout, OW * Cout, Cout, OH, OW, sh_, sw_,
@@ -302,16 +306,24 @@ def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False):
     return y
 
 
-def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, want_masked=False, sync=None):
+def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, want_masked=False, sync=None,
+                recompute_mask=False):
+    """``recompute_mask`` (BN -> ReLU with no residual in between): the ReLU mask is re-evaluated from ``x`` with the
+    forward pass's scale/shift instead of reading the saved output -- two activation-sized reads fewer."""
     dout = as_nhwc(dout)
+    relu_mode = 1 if relu else 0
     if isinstance(invstd, tuple):
+        if relu and recompute_mask and RECOMPUTE_RELU_MASK:
+            scale, shift = invstd[1], invstd[2]
+            if scale.data_ptr() + 4 * scale.numel() == shift.data_ptr():
+                relu_mode, out = 2, scale       # kernels read scale[C] then shift[C] through this pointer
         invstd = invstd[0]
     Cc = x.shape[1]
     M = x.numel() // Cc
     tiles = lib().dcnn_bn_stat_tiles(LL(M))
     partials = torch.empty(tiles * 2 * Cc, device=x.device, dtype=torch.float32)
     check(lib().dcnn_bn_bwd_reduce(_p(dout), _p(x), _p(out), _p(mean), _p(invstd), LL(M), I(Cc),
-                                   I(1 if relu else 0), _p(partials), _stream()), "bn_bwd_reduce")
+                                   I(relu_mode), _p(partials), _stream()), "bn_bwd_reduce")
     k = torch.empty(3 * Cc, device=x.device, dtype=torch.float32)
     k1, k2, k3 = k[:Cc], k[Cc:2 * Cc], k[2 * Cc:]
     if sync is None:
@@ -325,7 +337,7 @@ def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, wa
     if want_masked:
         masked = torch.empty_like(x, memory_format=torch.preserve_format) if relu else dout
     check(lib().dcnn_bn_bwd_apply(_p(dout), _p(x), _p(out), _p(k1), _p(k2), _p(k3), _p(dx),
-                                  _p(masked if (want_masked and relu) else None), LL(M), I(Cc), I(1 if relu else 0),
+                                  _p(masked if (want_masked and relu) else None), LL(M), I(Cc), I(relu_mode),
                                   _stream()), "bn_bwd_apply")
     return dx, masked
 

@@ -6,7 +6,7 @@ import socket
 import pytest
 import torch
 import torch.distributed as dist
-import torch.multiprocessing as mp
+from dcnn_b200.utils.spawn import spawn_bounded
 
 from dcnn_b200 import nn as dnn
 from dcnn_b200.train import TrainStep
@@ -58,7 +58,7 @@ def _worker(rank, world, port, out):
 
 def test_dp2_syncbn_equals_single_process(tmp_path):
     out = str(tmp_path / "dp.pt")
-    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    spawn_bounded(_worker, args=(2, _free_port(), out), nprocs=2, timeout_s=300)
     got = torch.load(out)
     m = _model()
     opt = dnn.SGD(0.05, 0.9)  # SGD: linear in the gradients (Adam would amplify the rounding noise of the analytically-zero conv-bias-before-BN gradients)

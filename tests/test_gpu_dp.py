@@ -7,7 +7,7 @@ import socket
 import pytest
 import torch
 import torch.distributed as dist
-import torch.multiprocessing as mp
+from dcnn_b200.utils.spawn import spawn_bounded
 
 from dcnn_b200 import nn as dnn
 from dcnn_b200.train import TrainStep
@@ -93,7 +93,7 @@ def test_fused_allreduce_update_matches_nccl_baseline_and_single_gpu(kind, tmp_p
     res = {}
     for baseline in (False, True):
         out = str(tmp_path / f"dp_{kind}_{int(baseline)}.pt")
-        mp.spawn(_worker, args=(world, _free_port(), out, kind, baseline), nprocs=world, join=True)
+        spawn_bounded(_worker, args=(world, _free_port(), out, kind, baseline), nprocs=world, timeout_s=240)
         res[baseline] = torch.load(out)
     single = _single(kind, world)
     # fused (P2P kernel) vs NCCL baseline: same arithmetic up to summation order.

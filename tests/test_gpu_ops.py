@@ -204,6 +204,13 @@ def test_batchnorm_fwd_bwd(N, C, H, W, relu, res):
     check_close(m, m_ref, 1e-6, "masked dout")
     check_close(dg, dg_ref, 2e-4, "dgamma")
     check_close(db, db_ref, 2e-4, "dbeta")
+    if relu and not res:
+        # ReLU mask recomputed from x with the forward scale/shift: the saved output is not read at all
+        dg2, db2 = torch.zeros(C, 1, 1, 1, device=DEV), torch.zeros(C, 1, 1, 1, device=DEV)
+        dx2, m2 = ops.bn_backward(cl(dout), xg, None, mean, inv, gg, dg2, db2, relu, True, recompute_mask=True)
+        check_close(m2, m, 1e-7, "masked dout (recomputed mask)")
+        check_close(dx2, dx, 1e-6, "bn dx (recomputed mask)")
+        check_close(dg2, dg, 1e-6, "dgamma (recomputed mask)")
 
 
 def test_batchnorm_inference():

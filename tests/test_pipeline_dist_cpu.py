@@ -5,7 +5,7 @@ import socket
 
 import torch
 import torch.distributed as dist
-import torch.multiprocessing as mp
+from dcnn_b200.utils.spawn import spawn_bounded
 
 import dcnn_b200 as dc
 from dcnn_b200 import nn as dnn
@@ -54,7 +54,7 @@ def _proc(rank, world, port, out):
 
 def test_distributed_coordinator_two_workers(tmp_path):
     out = str(tmp_path / "pipe.pt")
-    mp.spawn(_proc, args=(3, _free_port(), out), nprocs=3, join=True)
+    spawn_bounded(_proc, args=(3, _free_port(), out), nprocs=3, timeout_s=300)
     got = torch.load(out)
     ref, ref_losses = _reference_run(2, 2, 3)
     for a, b in zip(got["losses"], ref_losses):

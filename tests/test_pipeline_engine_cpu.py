@@ -5,7 +5,7 @@ import socket
 import pytest
 import torch
 import torch.distributed as dist
-import torch.multiprocessing as mp
+from dcnn_b200.utils.spawn import spawn_bounded
 
 from dcnn_b200 import nn as dnn
 from dcnn_b200.parallel.pipeline import build_schedule
@@ -65,7 +65,7 @@ def _proc(rank, world, port, out, stages, reps, micro, schedule):
 def test_engine_equals_single_device(tmp_path, stages, reps, micro, schedule):
     out = str(tmp_path / "eng.pt")
     world = stages * reps
-    mp.spawn(_proc, args=(world, _free_port(), out, stages, reps, micro, schedule), nprocs=world, join=True)
+    spawn_bounded(_proc, args=(world, _free_port(), out, stages, reps, micro, schedule), nprocs=world, timeout_s=300)
     got = torch.load(out)
     if reps == 1:
         ref, ref_losses = _reference_run(stages, micro, 3)
