@@ -21,7 +21,7 @@ int dcnn_device_sms(void);
 /* ---- tensor-core implicit GEMM (tcgen05 + TMEM + TMA); replaces cudnnConvolutionForward/BackwardData/
  *      BackwardFilter and cublasSgemm: src/nn/layers_impl/cuda/cudnn_conv2d_ops.cu:171-232, dense_ops.cu:24-137 ---- */
 int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w);
-/* statistics tiles dcnn_conv_tc emits for this problem (== m_tiles unless the 256-pixel kernel, DCNN_CONV_V3=1, is selected) */
+/* statistics tiles dcnn_conv_tc emits for this problem (== m_tiles unless the 256-pixel kernel is selected; DCNN_CONV_V3=0 disables it) */
 int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout);
 int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
                  long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h, int in_mul_w,

@@ -320,3 +320,17 @@ def test_optimizers(opt):
         check_close(a, b, 1e-5, opt + " params")
     for g in dev[1]:
         assert float(g.abs().max()) == 0.0
+
+
+# ----------------------------------------------------------------------------------------- 256-pixel-tile conv kernel
+def test_conv_tc3_large_problems():
+    """conv_tc3 is only selected for loop spaces with >= 1 tile per SM; scripts/check_conv_v3.py runs such shapes
+    (partial tiles, partial N tiles, strided boxes, accumulate mode) against cuDNN FP32 in a fresh process."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, DCNN_CONV_V3="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "check_conv_v3.py")], env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ALL PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "FAIL" not in r.stdout
