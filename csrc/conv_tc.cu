@@ -1277,6 +1277,11 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   }
   p.oc_tiles = ceil_div(Cout, 128);
   const bool wide = Cin >= 128;
+  // N = 256 tiles (128 oc x 256 c): 42.7 instead of 32 FLOP per operand byte on the L2-feed-bound mainloop (same
+  // argument as conv_tc3).  Two 96 KB stages.  Opt-in (DCNN_WGRAD_N256=1) until it has had its hardware run.
+  const char* n256_env = getenv("DCNN_WGRAD_N256");
+  const bool n256 = n256_env != nullptr && atoi(n256_env) != 0 && Cin % 256 == 0;
+  const int bnw = n256 ? 256 : (wide ? 128 : 64);
   CUtensorMapSwizzle wgrad_swizzle = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
   {
     // MN-major TF32 operands must use the 128B-swizzle-with-32B-atoms layout (TMA: SWIZZLE_128B_ATOM_32B, UMMA
@@ -1288,10 +1293,10 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
     wgrad_swizzle = (CUtensorMapSwizzle)swz;
     p.desc_hi_a = make_smem_desc_hi(lbo, sbo, layout);
     p.desc_hi_b = make_smem_desc_hi(lbo, sbo, layout);
-    p.idesc = make_idesc_tf32(128, wide ? 128 : 64, a_mn, b_mn);
+    p.idesc = make_idesc_tf32(128, bnw, a_mn, b_mn);
     p.k_step_bytes = kstep;
   }
-  p.c_tiles = ceil_div(Cin, wide ? 128 : 64);
+  p.c_tiles = ceil_div(Cin, bnw);
   const int pix_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
   const int base = num_taps * p.oc_tiles * p.c_tiles;
   int splits = ceil_div(2 * num_sms(), base);
@@ -1306,6 +1311,7 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   if (rc) return rc;
   rc = make_tmap_nhwc(&tmX, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w, wgrad_swizzle);
   if (rc) return rc;
+  if (n256) return launch_wgrad<256, 2>(tmDY, tmX, p, stream);
   if (wide) return launch_wgrad<128, 3>(tmDY, tmX, p, stream);
   return launch_wgrad<64, 4>(tmDY, tmX, p, stream);
 }

@@ -197,10 +197,13 @@ __global__ void bn_eval_coeffs_kernel(const float* __restrict__ rm, const float*
 }
 
 // y = x*scale[c] + shift[c] (+ residual) (ReLU).  float4 over channels; C % 4 == 0.
+// `mask` (optional, RELU only): one byte per float4, bit j set iff lane j of the float4 passed the ReLU -- 1/16 of
+// the tensor instead of the whole output when BatchNorm backward needs the mask of a (BN + residual -> ReLU) unit.
 template <bool RES, bool RELU>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, const float* __restrict__ scale,
                                                        const float* __restrict__ shift, const float* __restrict__ res,
-                                                       float* __restrict__ y, long long total4, int C4) {
+                                                       float* __restrict__ y, long long total4, int C4,
+                                                       uint8_t* __restrict__ mask = nullptr) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % C4) * 4;
@@ -213,6 +216,8 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__
       o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
     }
     if (RELU) {
+      if (mask != nullptr)
+        mask[i] = (uint8_t)((o.x > 0.f ? 1 : 0) | (o.y > 0.f ? 2 : 0) | (o.z > 0.f ? 4 : 0) | (o.w > 0.f ? 8 : 0));
       o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
     }
     st4(y + i * 4, o);
@@ -265,6 +270,10 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
       } else if (RELU == 2) {
         g.x = fmaf(v.x, sc.x, sf.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, sc.y, sf.y) > 0.f ? g.y : 0.f;
         g.z = fmaf(v.z, sc.z, sf.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, sc.w, sf.w) > 0.f ? g.w : 0.f;
+      } else if (RELU == 3) {
+        const unsigned mk = reinterpret_cast<const uint8_t*>(out)[(r * C + c) >> 2];
+        g.x = (mk & 1u) ? g.x : 0.f; g.y = (mk & 2u) ? g.y : 0.f;
+        g.z = (mk & 4u) ? g.z : 0.f; g.w = (mk & 8u) ? g.w : 0.f;
       }
       a.x += g.x; a.y += g.y; a.z += g.z; a.w += g.w;
       b.x = fmaf(g.x, (v.x - mu.x) * is.x, b.x); b.y = fmaf(g.y, (v.y - mu.y) * is.y, b.y);
@@ -395,6 +404,10 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restri
       const float4 sc = ldg4(out + c), sf = ldg4(out + C4 * 4 + c);
       g.x = fmaf(v.x, sc.x, sf.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, sc.y, sf.y) > 0.f ? g.y : 0.f;
       g.z = fmaf(v.z, sc.z, sf.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, sc.w, sf.w) > 0.f ? g.w : 0.f;
+    } else if (RELU == 3) {
+      const unsigned mk = reinterpret_cast<const uint8_t*>(out)[i];
+      g.x = (mk & 1u) ? g.x : 0.f; g.y = (mk & 2u) ? g.y : 0.f;
+      g.z = (mk & 4u) ? g.z : 0.f; g.w = (mk & 8u) ? g.w : 0.f;
     }
     const float4 a = ldg4(k1 + c), b = ldg4(k2 + c), d = ldg4(k3 + c);
     float4 r;
@@ -653,6 +666,20 @@ DCNN_API int dcnn_bn_apply(const float* x, const float* scale, const float* shif
   return 0;
 }
 
+// BN apply + residual/ReLU that also emits the 4-bit-per-float4 ReLU mask (M*C/4 bytes; C % 4 == 0, relu != 0).
+// BatchNorm backward then takes the mask through its `out` pointer with relu mode 3.
+DCNN_API int dcnn_bn_apply_mask(const float* x, const float* scale, const float* shift, const float* residual,
+                                float* y, unsigned char* mask, long long M, int C, cudaStream_t stream) {
+  DCNN_REQUIRE((C & 3) == 0, "dcnn_bn_apply_mask: C (%d) must be a multiple of 4", C);
+  const long long t4 = M * C / 4;
+  const int grid = ew_grid(t4, 256);
+  if (residual) bn_apply_kernel<true, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C / 4, mask);
+  else bn_apply_kernel<false, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C / 4, mask);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
 DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean,
                                 const float* invstd, long long M, int C, int relu, float* partials,
                                 cudaStream_t stream) {
@@ -660,7 +687,8 @@ DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* 
   const int rows = stat_rows_per_tile(M, &tiles);
   if ((C & 3) == 0) {
     dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
-    if (relu == 2) bn_bwd_reduce_kernel<2><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    if (relu == 3) bn_bwd_reduce_kernel<3><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    else if (relu == 2) bn_bwd_reduce_kernel<2><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
     else if (relu) bn_bwd_reduce_kernel<1><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
     else bn_bwd_reduce_kernel<0><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
   } else {
@@ -707,7 +735,11 @@ DCNN_API int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* o
     const long long t4 = total / 4;
     const int grid = ew_grid(t4, 256);
     const int C4 = C / 4;
-    if (relu == 2 && masked)
+    if (relu == 3 && masked)
+      bn_bwd_apply_kernel<3, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else if (relu == 3)
+      bn_bwd_apply_kernel<3, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
+    else if (relu == 2 && masked)
       bn_bwd_apply_kernel<2, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
     else if (relu == 2)
       bn_bwd_apply_kernel<2, false><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);

@@ -464,8 +464,15 @@ class BatchNormLayer(Layer):
             stats = ops.bn_stats(x)
         mean, invstd = ops.bn_finalize(stats, self.epsilon, self.momentum, self.running_mean,
                                        self.running_var, sync=self.sync, gamma=self.gamma, beta=self.beta)
-        out = ops.bn_apply(x, mean, invstd, self.gamma, self.beta, residual, relu)
-        self._cache[micro_batch_id] = (x, mean, invstd, out if relu else None, relu, relu and residual is None)
+        mask = None
+        if relu and residual is not None and x.is_cuda and x.shape[1] % 4 == 0 and ops._cuda_backend().RELU_BITMASK:
+            # compact ReLU mask (1/16 of the tensor) so backward does not re-read `out` twice
+            mask = torch.empty(x.numel() // 4, dtype=torch.uint8, device=x.device)
+            out = ops.bn_apply(x, mean, invstd, self.gamma, self.beta, residual, relu, mask_out=mask)
+        else:
+            out = ops.bn_apply(x, mean, invstd, self.gamma, self.beta, residual, relu)
+        keep_out = out if (relu and mask is None) else None
+        self._cache[micro_batch_id] = (x, mean, invstd, keep_out, relu, relu and residual is None, mask)
         return out
 
     def backward(self, grad, micro_batch_id=0):
@@ -473,12 +480,12 @@ class BatchNormLayer(Layer):
         return dx
 
     def backward_fused(self, grad, micro_batch_id=0, want_masked=False):
-        x, mean, invstd, out, relu, plain_relu = self._cache[micro_batch_id]
+        x, mean, invstd, out, relu, plain_relu, mask = self._cache[micro_batch_id]
         grad = ops.to_activation_layout(grad)
         # plain_relu: no residual between BN and ReLU, so the mask can be recomputed from x (CUDA backend)
         return ops.bn_backward(grad, x, out, mean, invstd, self.gamma, self.gamma_grad,
                                self.beta_grad, relu=relu, want_masked=want_masked, sync=self.sync,
-                               recompute_mask=plain_relu)
+                               recompute_mask=plain_relu, relu_mask=mask)
 
     def parameters(self):
         return [self.gamma, self.beta] if self.affine else []

@@ -113,7 +113,7 @@ def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False):
 
 
 def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, want_masked=False,
-                sync=None, recompute_mask=False):
+                sync=None, recompute_mask=False, relu_mask=None):
     """Backward of (BN -> [+residual] -> [ReLU]).
 
     ``out`` is the forward output (needed for the ReLU mask).  Returns (dx, masked_dout|None).

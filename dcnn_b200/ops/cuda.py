@@ -32,6 +32,9 @@ def _p(t: Optional[torch.Tensor]):
 
 # DCNN_BN_RECOMPUTE_MASK=0 restores the read-the-saved-output ReLU mask in BatchNorm backward
 RECOMPUTE_RELU_MASK = os.environ.get("DCNN_BN_RECOMPUTE_MASK", "1") != "0"
+# DCNN_BN_BITMASK=1: (BN + residual -> ReLU) units keep a 4-bit-per-float4 mask instead of re-reading their output in
+# backward (opt-in until its hardware validation run)
+RELU_BITMASK = os.environ.get("DCNN_BN_BITMASK", "0") == "1"
 
 
 def tc_enabled() -> bool:
@@ -289,7 +292,8 @@ def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None, gamm
     return mean, (invstd, scale, shift)
 
 
-def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False):
+def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False, mask_out=None):
+    """``mask_out`` (uint8, numel/4, ReLU only): also emit the compact ReLU mask for :func:`bn_backward`."""
     x = as_nhwc(x)
     if isinstance(invstd, tuple):
         invstd, scale, shift = invstd
@@ -301,13 +305,18 @@ def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False):
     y = torch.empty_like(x, memory_format=torch.preserve_format)
     if residual is not None:
         residual = as_nhwc(residual)
+    if mask_out is not None:
+        assert relu and Cc % 4 == 0 and mask_out.dtype == torch.uint8 and mask_out.numel() * 4 == x.numel()
+        check(lib().dcnn_bn_apply_mask(_p(x), _p(scale), _p(shift), _p(residual), _p(y), _p(mask_out), LL(M), I(Cc),
+                                       _stream()), "bn_apply_mask")
+        return y
     check(lib().dcnn_bn_apply(_p(x), _p(scale), _p(shift), _p(residual), _p(y), LL(M), I(Cc), I(1 if relu else 0),
                               _stream()), "bn_apply")
     return y
 
 
 def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, want_masked=False, sync=None,
-                recompute_mask=False):
+                recompute_mask=False, relu_mask=None):
     """``recompute_mask`` (BN -> ReLU with no residual in between): the ReLU mask is re-evaluated from ``x`` with the
     forward pass's scale/shift instead of reading the saved output -- two activation-sized reads fewer."""
     dout = as_nhwc(dout)
@@ -318,6 +327,8 @@ def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, wa
             if scale.data_ptr() + 4 * scale.numel() == shift.data_ptr():
                 relu_mode, out = 2, scale       # kernels read scale[C] then shift[C] through this pointer
         invstd = invstd[0]
+    if relu and relu_mask is not None and relu_mode == 1:
+        relu_mode, out = 3, relu_mask          # 4 bits per float4 written by bn_apply(mask_out=...)
     Cc = x.shape[1]
     M = x.numel() // Cc
     tiles = lib().dcnn_bn_stat_tiles(LL(M))

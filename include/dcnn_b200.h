@@ -56,6 +56,11 @@ int dcnn_bn_eval_coeffs(const float* rm, const float* rv, const float* gamma, co
                         float* scale, float* shift, cudaStream_t stream);
 int dcnn_bn_apply(const float* x, const float* scale, const float* shift, const float* residual, float* y,
                   long long M, int C, int relu, cudaStream_t stream);
+/* BN apply (+residual) + ReLU that also writes a 4-bit-per-float4 ReLU mask (M*C/4 bytes); pass the mask as `out`
+ * with relu = 3 to dcnn_bn_bwd_reduce / dcnn_bn_bwd_apply.  relu modes there: 0 none, 1 mask = out > 0,
+ * 2 mask recomputed from x (out -> scale[C] | shift[C]), 3 mask bytes. */
+int dcnn_bn_apply_mask(const float* x, const float* scale, const float* shift, const float* residual, float* y,
+                       unsigned char* mask, long long M, int C, cudaStream_t stream);
 int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean, const float* invstd,
                        long long M, int C, int relu, float* partials, cudaStream_t stream);
 int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,

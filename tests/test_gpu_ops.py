@@ -13,6 +13,10 @@ from dcnn_b200.ops import cpu as ref
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda"
+# opt-in features that have not had their first hardware run yet (no GPU minutes left in the round that wrote them);
+# DCNN_TEST_PENDING=1 runs them -- the first GPU call of the next session does.
+pending_hw = pytest.mark.skipif(os.environ.get("DCNN_TEST_PENDING") != "1",
+                                reason="awaiting first hardware validation (set DCNN_TEST_PENDING=1)")
 
 
 def cl(t):
@@ -334,3 +338,46 @@ def test_conv_tc3_large_problems():
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ALL PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
     assert "FAIL" not in r.stdout
+
+
+# ----------------------------------------------------------------------------------------- pending hardware validation
+@pending_hw
+@pytest.mark.parametrize("N,C,H,W", [(8, 64, 16, 16), (4, 256, 8, 8), (16, 2048, 2, 2)])
+def test_batchnorm_relu_bitmask(N, C, H, W):
+    """(BN + residual -> ReLU): the 4-bit-per-float4 mask written by the forward apply drives backward."""
+    x = torch.randn(N, C, H, W) * 2 + 1
+    gamma, beta = torch.rand(C, 1, 1, 1) + 0.5, torch.randn(C, 1, 1, 1)
+    r = torch.randn(N, C, H, W)
+    xg, gg, bg, rg = cl(x), gamma.to(DEV), beta.to(DEV), cl(r)
+    rm, rv = torch.zeros(C, device=DEV), torch.ones(C, device=DEV)
+    mean, inv = ops.bn_finalize(ops.bn_stats(xg), 1e-5, 0.1, rm, rv, gamma=gg, beta=bg)
+    y = ops.bn_apply(xg, mean, inv, gg, bg, rg, True)
+    mask = torch.zeros(x.numel() // 4, dtype=torch.uint8, device=DEV)
+    y2 = ops.bn_apply(xg, mean, inv, gg, bg, rg, True, mask_out=mask)
+    assert torch.equal(y, y2)
+    bits = (y.permute(0, 2, 3, 1).reshape(-1, 4) > 0).to(torch.uint8)
+    want = bits[:, 0] | (bits[:, 1] << 1) | (bits[:, 2] << 2) | (bits[:, 3] << 3)
+    assert torch.equal(mask, want)
+    dout = cl(torch.randn(N, C, H, W))
+    dg, db = torch.zeros(C, 1, 1, 1, device=DEV), torch.zeros(C, 1, 1, 1, device=DEV)
+    dx, m = ops.bn_backward(dout, xg, y, mean, inv, gg, dg, db, True, True)
+    dg2, db2 = torch.zeros_like(dg), torch.zeros_like(db)
+    dx2, m2 = ops.bn_backward(dout, xg, None, mean, inv, gg, dg2, db2, True, True, relu_mask=mask)
+    assert torch.equal(m, m2) and torch.equal(dx, dx2) and torch.equal(dg, dg2) and torch.equal(db, db2)
+
+
+@pending_hw
+@pytest.mark.parametrize("case", [(4, 256, 16, 16, 128, 3, 1, 1), (2, 512, 8, 8, 256, 1, 1, 0),
+                                  (3, 256, 9, 9, 96, 3, 2, 1)], ids=lambda c: "x".join(map(str, c)))
+def test_wgrad_n256(case, monkeypatch):
+    """128 x 256 weight-gradient tiles (DCNN_WGRAD_N256=1) against the CPU oracle."""
+    monkeypatch.setenv("DCNN_WGRAD_N256", "1")
+    N, C, H, W, OC, k, s, p = case
+    x = torch.randn(N, C, H, W)
+    oh = (H + 2 * p - k) // s + 1
+    dy = torch.randn(N, OC, oh, oh)
+    dw_ref = torch.zeros(OC, C, k, k)
+    ref.conv2d_backward_weight(dy, x, dw_ref, (s, s), (p, p))
+    dw = cl(torch.zeros(OC, C, k, k))
+    ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p))
+    check_close(dw, dw_ref, 4e-3, "conv wgrad N256")
