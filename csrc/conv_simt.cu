@@ -202,3 +202,46 @@ DCNN_API int dcnn_weight_dgrad_layout(const float* w, float* wt, int K, int R, i
   DCNN_COUNT_LAUNCH(1);
   return 0;
 }
+
+namespace dcnn {
+// Packed-tap im2col for small-Cin ("stem") convolutions: P[n,oh,ow,k] = x[n, oh*sh-ph+r, ow*sw-pw+s, c] with
+// k = (r*S+s)*Cin + c for k < R*S*Cin, zero for the padding channels up to Kp (a multiple of 32) and for taps that fall
+// outside the image.  The stem then runs as a 1x1 convolution with Cin = Kp on the tensor-core kernels instead of on
+// CUDA cores (a 3x3x3 stem is K = 27 -> 32: no wasted MMA work to speak of).  k is the fastest index: stores are
+// full 128-byte rows; the reads hit L1/L2 (every input element is read R*S times).
+__global__ void __launch_bounds__(256) pack_taps_kernel(const float* __restrict__ x, float* __restrict__ P, int N, int H,
+                                                        int W, int Cin, int OH, int OW, int R, int S, int sh, int sw,
+                                                        int ph, int pw, int Kp) {
+  const int K = R * S * Cin;
+  const long long total = (long long)N * OH * OW * Kp;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % Kp);
+    long long t = i / Kp;
+    const int ow = (int)(t % OW); t /= OW;
+    const int oh = (int)(t % OH);
+    const int n = (int)(t / OH);
+    float v = 0.f;
+    if (k < K) {
+      const int tap = k / Cin, c = k - tap * Cin;
+      const int r = tap / S, s2 = tap - r * S;
+      const int ih = oh * sh - ph + r, iw = ow * sw - pw + s2;
+      if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W)
+        v = __ldg(x + (((long long)n * H + ih) * W + iw) * Cin + c);
+    }
+    P[i] = v;
+  }
+}
+}  // namespace dcnn
+
+DCNN_API int dcnn_pack_taps(const float* x, float* P, int N, int H, int W, int Cin, int OH, int OW, int R, int S,
+                            int sh, int sw, int ph, int pw, int Kp, cudaStream_t stream) {
+  DCNN_REQUIRE(Kp % 32 == 0 && Kp >= R * S * Cin, "dcnn_pack_taps: Kp (%d) must be a multiple of 32 >= R*S*Cin (%d)", Kp,
+               R * S * Cin);
+  const long long total = (long long)N * OH * OW * Kp;
+  dcnn::pack_taps_kernel<<<dcnn::ew_grid(total, 256, 4), 256, 0, stream>>>(x, P, N, H, W, Cin, OH, OW, R, S, sh, sw, ph,
+                                                                          pw, Kp);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}

@@ -77,6 +77,36 @@ class CudaStats:
 
 
 # ================================================================================== convolution
+# DCNN_STEM_TC=1: small-Cin convolutions (R*S*Cin <= 64, e.g. the 3x3x3 ResNet stem or a 5x5x1 MNIST conv) are run as
+# packed-tap im2col + a 1x1 tensor-core convolution instead of on CUDA cores (opt-in until validated on hardware).
+STEM_TC = os.environ.get("DCNN_STEM_TC", "0") == "1"
+
+
+def _stem_kp(Cin, R, S):
+    """Padded reduction length if this convolution qualifies for the packed-tap path, else 0."""
+    if not (STEM_TC and tc_enabled()) or Cin % 32 == 0:
+        return 0
+    K = R * S * Cin
+    return (K + 31) // 32 * 32 if K <= 64 else 0
+
+
+def _pack_taps(x, R, S, stride, pad, OH, OW, Kp):
+    N, Cin, H, W = x.shape
+    P_ = _empty_nhwc(N, Kp, OH, OW, x.device)
+    check(lib().dcnn_pack_taps(_p(x), _p(P_), I(N), I(H), I(W), I(Cin), I(OH), I(OW), I(R), I(S), I(stride[0]),
+                               I(stride[1]), I(pad[0]), I(pad[1]), I(Kp), _stream()), "pack_taps")
+    return P_
+
+
+def _packed_weights(w, Kp):
+    """[Cout][R][S][Cin] (the stored O-H-W-I layout) -> [Cout][Kp] zero padded, as a 1x1 O-H-W-I weight."""
+    Cout, Cin, R, S = w.shape
+    flat = w.permute(0, 2, 3, 1).reshape(Cout, R * S * Cin)
+    wp = torch.zeros(Cout, Kp, device=w.device, dtype=torch.float32)
+    wp[:, :R * S * Cin] = flat
+    return wp.view(Cout, Kp, 1, 1).contiguous(memory_format=CL)
+
+
 def _conv_tc(x, N, H, W, Cin, w, Cout, Ktot, out, out_off, sn, sh, sw, OH, OW, mul_h, mul_w, taps, bias,
              accumulate, partials):
     n, dh, dw, wi = taps
@@ -95,6 +125,10 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
     ph, pw = pad
     OH = (H + 2 * ph - R) // sh_ + 1
     OW = (W + 2 * pw - S) // sw_ + 1
+    kp = _stem_kp(Cin, R, S)
+    if kp:
+        return conv2d_forward(_pack_taps(x, R, S, stride, pad, OH, OW, kp), _packed_weights(w, kp), bias, (1, 1),
+                              (0, 0), want_stats)
     y = _empty_nhwc(N, Cout, OH, OW, x.device)
     use_tc = tc_enabled() and Cin % 32 == 0 and R * S <= 49 and \
         ((sh_ == 1 and sw_ == 1) or (tc_strided_enabled() and sh_ <= 8 and sw_ <= 8))
@@ -187,6 +221,14 @@ def conv2d_backward_weight(dy, x, dw, stride, pad):
     sh_, sw_ = stride
     ph, pw = pad
     assert dw.is_contiguous(memory_format=CL)
+    kp = _stem_kp(Cin, R, S)
+    if kp and K % 4 == 0:
+        # the packed activations are rebuilt here rather than kept from the forward pass (134 MB for the ResNet stem at
+        # batch 256 against a 30 us kernel)
+        dwp = torch.zeros(K, kp, 1, 1, device=dw.device, dtype=torch.float32).contiguous(memory_format=CL)
+        conv2d_backward_weight(dy, _pack_taps(x, R, S, stride, pad, OH, OW, kp), dwp, (1, 1), (0, 0))
+        dw.permute(0, 2, 3, 1).reshape(K, R * S * Cin).add_(dwp.reshape(K, kp)[:, :R * S * Cin])
+        return
     use_tc = tc_enabled() and Cin % 32 == 0 and K % 4 == 0 and R * S <= 49 and \
         ((sh_ == 1 and sw_ == 1) or (tc_strided_enabled() and sh_ <= 8 and sw_ <= 8))
     if use_tc:

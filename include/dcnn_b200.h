@@ -106,6 +106,9 @@ int dcnn_softmax_bwd(const float* x, const float* g, float* dx, long long rows, 
 int dcnn_add(const float* a, const float* b, float* y, long long n, cudaStream_t stream);
 int dcnn_dropout(const float* x, float* y, long long n, float rate, unsigned long long seed,
                  unsigned long long offset, cudaStream_t stream);
+/* packed-tap im2col for small-Cin convolutions: P[n,oh,ow,Kp], k = (r*S+s)*Cin + c, zero padded to Kp (multiple of 32) */
+int dcnn_pack_taps(const float* x, float* P, int N, int H, int W, int Cin, int OH, int OW, int R, int S, int sh, int sw,
+                   int ph, int pw, int Kp, cudaStream_t stream);
 int dcnn_transpose_batched(const float* in, float* out, int batch, int rows, int cols, cudaStream_t stream);
 int dcnn_fill(float* p, long long n, float v, cudaStream_t stream);
 

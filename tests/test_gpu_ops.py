@@ -381,3 +381,34 @@ def test_wgrad_n256(case, monkeypatch):
     dw = cl(torch.zeros(OC, C, k, k))
     ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p))
     check_close(dw, dw_ref, 4e-3, "conv wgrad N256")
+
+
+@pending_hw
+@pytest.mark.parametrize("case", [(4, 3, 32, 32, 64, 3, 1, 1, True), (2, 1, 28, 28, 8, 5, 1, 0, False),
+                                  (3, 3, 17, 15, 32, 3, 2, 1, True)], ids=lambda c: "x".join(map(str, c)))
+def test_stem_packed_taps(case):
+    """Small-Cin convolutions as packed-tap im2col + 1x1 tensor-core conv (DCNN_STEM_TC=1) against the CPU oracle."""
+    from dcnn_b200.ops import cuda as K
+    N, C, H, W, OC, k, s, p, bias = case
+    x = torch.randn(N, C, H, W)
+    w = torch.randn(OC, C, k, k) / (C * k * k) ** 0.5
+    b = torch.randn(OC, 1, 1, 1) if bias else None
+    y_ref, _ = ref.conv2d_forward(x, w, b, (s, s), (p, p), False)
+    oh, ow = y_ref.shape[2:]
+    dy = torch.randn(N, OC, oh, ow)
+    dw_ref = torch.zeros(OC, C, k, k)
+    ref.conv2d_backward_weight(dy, x, dw_ref, (s, s), (p, p))
+    old = K.STEM_TC
+    K.STEM_TC = True
+    try:
+        assert K._stem_kp(C, k, k) == 32
+        y, st = ops.conv2d_forward(cl(x), cl(w), None if b is None else b.to(DEV), (s, s), (p, p), True)
+        check_close(y, y_ref, 4e-3, "stem fprop (packed taps)")
+        mean, _ = ops.bn_finalize(st, 1e-5, 0.1, torch.zeros(OC, device=DEV), torch.ones(OC, device=DEV))
+        assert (mean.cpu() - y_ref.mean((0, 2, 3))).abs().max() < 5e-3
+        dw = cl(torch.zeros(OC, C, k, k))
+        ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p))
+        ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p))
+        check_close(dw, 2 * dw_ref, 4e-3, "stem wgrad (packed taps, accumulates)")
+    finally:
+        K.STEM_TC = old

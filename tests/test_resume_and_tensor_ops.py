@@ -72,3 +72,31 @@ def test_tensor_ops_match_reference_semantics():
     assert torch.equal(yv, torch.tensor([3.0, 5.0, 7.0]))
     assert float(T.dot_product(torch.ones(4), torch.arange(4.0))) == 6.0
     assert torch.equal(T.cnhw_to_nchw(T.nchw_to_cnhw(x)), x)
+
+
+def test_packed_tap_stem_formulation():
+    """Index convention of the packed-tap stem path (csrc/conv_simt.cu pack_taps_kernel, ops/cuda.py _packed_weights):
+    P[n,oh,ow,(r*S+s)*Cin+c] against the O-H-W-I weight flattening reproduces conv2d, and P^T dY reproduces dW."""
+    N, Cin, H, W, Cout, R, S, st, pd = 2, 3, 9, 8, 8, 3, 3, 2, 1
+    x = torch.randn(N, Cin, H, W)
+    w = torch.randn(Cout, Cin, R, S)
+    OH, OW = (H + 2 * pd - R) // st + 1, (W + 2 * pd - S) // st + 1
+    Kp = 32
+    P = torch.zeros(N, OH, OW, Kp)
+    for n in range(N):
+        for oh in range(OH):
+            for ow in range(OW):
+                for r in range(R):
+                    for s in range(S):
+                        ih, iw = oh * st - pd + r, ow * st - pd + s
+                        if 0 <= ih < H and 0 <= iw < W:
+                            P[n, oh, ow, (r * S + s) * Cin:(r * S + s + 1) * Cin] = x[n, :, ih, iw]
+    wp = torch.zeros(Cout, Kp)
+    wp[:, :R * S * Cin] = w.permute(0, 2, 3, 1).reshape(Cout, -1)
+    y = (P.reshape(-1, Kp) @ wp.t()).reshape(N, OH, OW, Cout).permute(0, 3, 1, 2)
+    assert torch.allclose(y, F.conv2d(x, w, stride=st, padding=pd), atol=1e-5)
+    dy = torch.randn(N, Cout, OH, OW)
+    dwp = dy.permute(0, 2, 3, 1).reshape(-1, Cout).t() @ P.reshape(-1, Kp)
+    dw = dwp[:, :R * S * Cin].reshape(Cout, R, S, Cin).permute(0, 3, 1, 2)
+    want = torch.nn.grad.conv2d_weight(x, w.shape, dy, stride=st, padding=pd)
+    assert torch.allclose(dw, want, atol=1e-4)
