@@ -30,13 +30,27 @@ class CpuStats:
         self.mean, self.var, self.count = mean, var, count
 
 
+def _native():
+    """The hand-written AVX2 GEMM path (ops/cpu_native.py) when DCNN_CPU_BACKEND=native, else None (ATen)."""
+    from . import cpu_native
+    return cpu_native if cpu_native.enabled() else None
+
+
 def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
+    nat = _native()
+    if nat is not None and x.dtype == torch.float32:
+        y = nat.conv2d_forward(x, w, bias, stride, pad)
+        return y, (bn_stats(y) if want_stats else None)
     y = F.conv2d(x, w, None if bias is None else bias.reshape(-1), stride=stride, padding=pad)
     return y, (bn_stats(y) if want_stats else None)
 
 
 def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False):
-    dx = torch.nn.grad.conv2d_input(list(x_shape), w, dy, stride=stride, padding=pad)
+    nat = _native()
+    if nat is not None and dy.dtype == torch.float32:
+        dx = nat.conv2d_backward_data(dy, w, tuple(x_shape), stride, pad)
+    else:
+        dx = torch.nn.grad.conv2d_input(list(x_shape), w, dy, stride=stride, padding=pad)
     if out is not None:
         if accumulate:
             out.add_(dx)
@@ -48,6 +62,9 @@ def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False
 
 def conv2d_backward_weight(dy, x, dw, stride, pad):
     """dw += dL/dW  (beta=1 accumulation across microbatches, ref cudnn_conv2d_ops.cu:226)."""
+    nat = _native()
+    if nat is not None and dy.dtype == torch.float32:
+        return nat.conv2d_backward_weight(dy, x, dw, stride, pad)
     g = torch.nn.grad.conv2d_weight(x, list(dw.shape), dy, stride=stride, padding=pad)
     dw.add_(g)
 
@@ -58,6 +75,9 @@ def bias_grad(dy, db):
 
 
 def dense_forward(x2d, w2d, bias):
+    nat = _native()
+    if nat is not None and x2d.dtype == torch.float32:
+        return nat.dense_forward(x2d, w2d, bias)
     y = x2d @ w2d.t()
     if bias is not None:
         y = y + bias.view(1, -1)
@@ -65,10 +85,16 @@ def dense_forward(x2d, w2d, bias):
 
 
 def dense_backward_data(dy2d, w2d):
+    nat = _native()
+    if nat is not None and dy2d.dtype == torch.float32:
+        return nat.dense_backward_data(dy2d, w2d)
     return dy2d @ w2d
 
 
 def dense_backward_weight(dy2d, x2d, dw2d):
+    nat = _native()
+    if nat is not None and dy2d.dtype == torch.float32:
+        return nat.dense_backward_weight(dy2d, x2d, dw2d)
     dw2d.add_(dy2d.t() @ x2d)
 
 

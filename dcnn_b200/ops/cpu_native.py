@@ -1,0 +1,227 @@
+"""Native CPU math (libdcnn_host.so, csrc/host/cpu_math.cpp): blocked AVX2/FMA sgemm/dgemm, vectorised elementwise
+primitives, reductions, dot product, im2col/col2im -- the counterpart of the reference's hand-written CPU backend
+(ref src/math/cpu/sgemm.cpp, dgemm.cpp; src/ops/cpu/skernels.cpp, dkernels.cpp; src/utils/simd_dot_product.S;
+include/threading/thread_handler.hpp; include/tensor/cpu/tensor_ops.hpp:22-330).
+
+``DCNN_CPU_BACKEND=native`` routes the CPU path's convolution (im2col + GEMM, as the reference's CPU Conv2D does:
+src/nn/layers_impl/cpu/conv2d_ops.cpp:19-67) and Dense layers through these kernels instead of ATen; the default stays
+ATen (oneDNN/MKL are faster on most hosts; the native path exists for parity and for hosts without them)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from .._hostlib import lib as _hostlib
+
+BIN = {"add": 0, "sub": 1, "mul": 2, "div": 3, "max": 4, "min": 5}
+UN = {"neg": 0, "abs": 1, "sqrt": 2, "rsqrt": 3, "rcp": 4, "exp": 5, "log": 6, "square": 7, "relu": 8}
+_SETUP = False
+
+
+def _lib():
+    global _SETUP
+    l = _hostlib()
+    if not _SETUP:
+        l.dcnn_cpu_sdot.restype = C.c_float
+        l.dcnn_cpu_ddot.restype = C.c_double
+        l.dcnn_cpu_ssum.restype = C.c_double
+        l.dcnn_cpu_ssum_squared_diff.restype = C.c_double
+        l.dcnn_cpu_get_threads.restype = C.c_int
+        _SETUP = True
+    return l
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def _chk(*ts):
+    for t in ts:
+        if t.is_cuda or not t.is_contiguous() or t.dtype not in (torch.float32, torch.float64):
+            raise ValueError("cpu_native ops take contiguous float32/float64 CPU tensors")
+    if len({t.dtype for t in ts}) != 1:
+        raise ValueError("mixed dtypes")
+    return ts[0].dtype == torch.float64
+
+
+def set_num_threads(n: int):
+    """ref ThreadWrapper (include/threading/thread_wrapper.hpp:18-47): bound the worker count of the native kernels."""
+    _lib().dcnn_cpu_set_threads(C.c_int(int(n)))
+
+
+def get_num_threads() -> int:
+    return int(_lib().dcnn_cpu_get_threads())
+
+
+def gemm(a, b, trans_a=False, trans_b=False, alpha=1.0, beta=0.0, c=None):
+    """C = alpha * op(A) @ op(B) + beta * C, row-major 2-D float32/float64 (ref include/math/cpu/gemm.hpp:14-32)."""
+    dbl = _chk(a, b)
+    M, K = (a.shape[1], a.shape[0]) if trans_a else a.shape
+    K2, N = (b.shape[1], b.shape[0]) if trans_b else b.shape
+    if K != K2:
+        raise ValueError(f"gemm: inner dimensions differ ({K} vs {K2})")
+    if c is None:
+        c = torch.empty(M, N, dtype=a.dtype)
+        beta = 0.0
+    else:
+        _chk(a, c)
+        if tuple(c.shape) != (M, N):
+            raise ValueError("gemm: bad output shape")
+    fn = _lib().dcnn_cpu_dgemm if dbl else _lib().dcnn_cpu_sgemm
+    sc = C.c_double if dbl else C.c_float
+    fn(C.c_int(int(trans_a)), C.c_int(int(trans_b)), C.c_int(M), C.c_int(N), C.c_int(K), sc(alpha), _ptr(a),
+       C.c_int(a.shape[1]), _ptr(b), C.c_int(b.shape[1]), sc(beta), _ptr(c), C.c_int(N))
+    return c
+
+
+def dot(a, b) -> float:
+    dbl = _chk(a, b)
+    n = C.c_longlong(a.numel())
+    return float((_lib().dcnn_cpu_ddot if dbl else _lib().dcnn_cpu_sdot)(_ptr(a), _ptr(b), n))
+
+
+def sum(a) -> float:  # noqa: A001 - reference name
+    if _chk(a):
+        return float(a.sum())
+    return float(_lib().dcnn_cpu_ssum(_ptr(a), C.c_longlong(a.numel())))
+
+
+def sum_squared_diff(a, mean: float) -> float:
+    if _chk(a):
+        return float(((a - mean) ** 2).sum())
+    return float(_lib().dcnn_cpu_ssum_squared_diff(_ptr(a), C.c_float(mean), C.c_longlong(a.numel())))
+
+
+def binary(op: str, a, b, out=None):
+    """add / sub / mul / div / max / min; ``b`` may be a Python scalar."""
+    scalar = not torch.is_tensor(b)
+    dbl = _chk(a) if scalar else _chk(a, b)
+    out = torch.empty_like(a) if out is None else out
+    n = C.c_longlong(a.numel())
+    l = _lib()
+    if scalar:
+        (l.dcnn_cpu_dbinary_scalar if dbl else l.dcnn_cpu_sbinary_scalar)(
+            C.c_int(BIN[op]), _ptr(a), (C.c_double if dbl else C.c_float)(b), _ptr(out), n)
+    else:
+        if a.shape != b.shape:
+            raise ValueError("binary: shapes differ")
+        (l.dcnn_cpu_dbinary if dbl else l.dcnn_cpu_sbinary)(C.c_int(BIN[op]), _ptr(a), _ptr(b), _ptr(out), n)
+    return out
+
+
+def unary(op: str, a, out=None):
+    dbl = _chk(a)
+    out = torch.empty_like(a) if out is None else out
+    (_lib().dcnn_cpu_dunary if dbl else _lib().dcnn_cpu_sunary)(C.c_int(UN[op]), _ptr(a), _ptr(out),
+                                                                C.c_longlong(a.numel()))
+    return out
+
+
+def fma(a, b, c, mode="fmadd", out=None):
+    """fmadd: a*b+c, fmsub: a*b-c, fnmadd: c-a*b (float32)."""
+    _chk(a, b, c)
+    out = torch.empty_like(a) if out is None else out
+    _lib().dcnn_cpu_sfma(C.c_int({"fmadd": 0, "fmsub": 1, "fnmadd": 2}[mode]), _ptr(a), _ptr(b), _ptr(c), _ptr(out),
+                         C.c_longlong(a.numel()))
+    return out
+
+
+def axpy(alpha, x, y):
+    _chk(x, y)
+    _lib().dcnn_cpu_saxpy(C.c_float(alpha), _ptr(x), _ptr(y), C.c_longlong(x.numel()))
+    return y
+
+
+def fill(y, value):
+    _chk(y)
+    _lib().dcnn_cpu_sset(_ptr(y), C.c_float(value), C.c_longlong(y.numel()))
+    return y
+
+
+def transpose_2d(a):
+    _chk(a)
+    out = torch.empty(a.shape[1], a.shape[0], dtype=a.dtype)
+    _lib().dcnn_cpu_stranspose(_ptr(a), _ptr(out), C.c_int(a.shape[0]), C.c_int(a.shape[1]))
+    return out
+
+
+def _out_hw(H, W, kh, kw, stride, pad):
+    return (H + 2 * pad[0] - kh) // stride[0] + 1, (W + 2 * pad[1] - kw) // stride[1] + 1
+
+
+def im2col(x, kh, kw, stride=(1, 1), pad=(0, 0)):
+    """[N,C,H,W] -> [C*kh*kw, N*OH*OW]"""
+    x = x.contiguous()
+    _chk(x)
+    N, Cc, H, W = x.shape
+    OH, OW = _out_hw(H, W, kh, kw, stride, pad)
+    col = torch.empty(Cc * kh * kw, N * OH * OW, dtype=torch.float32)
+    _lib().dcnn_cpu_im2col(_ptr(x), _ptr(col), *(C.c_int(v) for v in (N, Cc, H, W, kh, kw, stride[0], stride[1],
+                                                                       pad[0], pad[1], OH, OW)))
+    return col
+
+
+def col2im(col, x_shape, kh, kw, stride=(1, 1), pad=(0, 0)):
+    col = col.contiguous()
+    _chk(col)
+    N, Cc, H, W = x_shape
+    OH, OW = _out_hw(H, W, kh, kw, stride, pad)
+    x = torch.empty(N, Cc, H, W, dtype=torch.float32)
+    _lib().dcnn_cpu_col2im(_ptr(col), _ptr(x), *(C.c_int(v) for v in (N, Cc, H, W, kh, kw, stride[0], stride[1],
+                                                                       pad[0], pad[1], OH, OW)))
+    return x
+
+
+# ---------------------------------------------------------------------------------------------- layer ops on the native GEMM
+def enabled() -> bool:
+    return os.environ.get("DCNN_CPU_BACKEND", "aten").lower() == "native"
+
+
+def conv2d_forward(x, w, bias, stride, pad):
+    """y[n,oc,:,:] = W[oc, C*kh*kw] @ im2col(x) (+bias): one GEMM for the whole batch."""
+    N, Cc, H, W = x.shape
+    OC, _, kh, kw = w.shape
+    OH, OW = _out_hw(H, W, kh, kw, stride, pad)
+    col = im2col(x.float(), kh, kw, stride, pad)
+    y = gemm(w.contiguous().reshape(OC, -1), col)                     # [OC, N*OH*OW]
+    y = y.reshape(OC, N, OH, OW).permute(1, 0, 2, 3).contiguous()
+    if bias is not None:
+        y += bias.reshape(1, -1, 1, 1)
+    return y
+
+
+def conv2d_backward_data(dy, w, x_shape, stride, pad):
+    OC, _, kh, kw = w.shape
+    g = dy.permute(1, 0, 2, 3).contiguous().reshape(OC, -1)           # [OC, N*OH*OW]
+    col = gemm(w.contiguous().reshape(OC, -1), g, trans_a=True)       # [C*kh*kw, N*OH*OW]
+    return col2im(col, x_shape, kh, kw, stride, pad)
+
+
+def conv2d_backward_weight(dy, x, dw, stride, pad):
+    OC, _, kh, kw = dw.shape
+    g = dy.permute(1, 0, 2, 3).contiguous().reshape(OC, -1)
+    col = im2col(x.float(), kh, kw, stride, pad)
+    if dw.is_contiguous():
+        gemm(g, col, trans_b=True, beta=1.0, c=dw.view(OC, -1))       # accumulate in place (beta = 1)
+    else:
+        dw.add_(gemm(g, col, trans_b=True).reshape(dw.shape))
+
+
+def dense_forward(x2d, w2d, bias):
+    y = gemm(x2d.contiguous(), w2d.contiguous(), trans_b=True)
+    if bias is not None:
+        y += bias.view(1, -1)
+    return y
+
+
+def dense_backward_data(dy2d, w2d):
+    return gemm(dy2d.contiguous(), w2d.contiguous())
+
+
+def dense_backward_weight(dy2d, x2d, dw2d):
+    if dw2d.is_contiguous():
+        gemm(dy2d.contiguous(), x2d.contiguous(), trans_a=True, beta=1.0, c=dw2d)
+    else:
+        dw2d.add_(gemm(dy2d.contiguous(), x2d.contiguous(), trans_a=True))

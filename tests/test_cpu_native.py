@@ -1,0 +1,135 @@
+"""Native CPU math (csrc/host/cpu_math.cpp) against ATen: GEMM in all transpose modes with ragged sizes, dgemm,
+elementwise / reduction primitives, im2col/col2im, and the DCNN_CPU_BACKEND=native layer path end to end.
+Mirrors the reference's unit_tests/math/sgemm_test.cpp / dgemm_test.cpp and ops tests (tol 1e-4 relative)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from dcnn_b200.ops import cpu_native as N
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).abs().max() / (b.double().abs().max() + 1e-30))
+
+
+@pytest.mark.parametrize("M,N_,K", [(1, 1, 1), (5, 7, 3), (6, 16, 8), (97, 33, 129), (128, 128, 128), (200, 17, 300),
+                                    (13, 2100, 40), (300, 70, 513)])
+@pytest.mark.parametrize("ta,tb", [(False, False), (False, True), (True, False), (True, True)])
+def test_sgemm(M, N_, K, ta, tb):
+    torch.manual_seed(M * 1000 + N_ * 10 + K)
+    a = torch.randn((K, M) if ta else (M, K))
+    b = torch.randn((N_, K) if tb else (K, N_))
+    want = (a.t() if ta else a) @ (b.t() if tb else b)
+    assert _rel(N.gemm(a, b, ta, tb), want) < 1e-5
+    c = torch.randn(M, N_)
+    want2 = 0.5 * want - 2.0 * c
+    N.gemm(a, b, ta, tb, alpha=0.5, beta=-2.0, c=c)
+    assert _rel(c, want2) < 1e-5
+
+
+def test_gemm_beta_zero_ignores_nan_and_dgemm():
+    a, b = torch.randn(20, 30), torch.randn(30, 10)
+    c = torch.full((20, 10), float("nan"))
+    N.gemm(a, b, beta=0.0, c=c)
+    assert torch.isfinite(c).all() and _rel(c, a @ b) < 1e-5
+    ad, bd = torch.randn(70, 45, dtype=torch.float64), torch.randn(33, 45, dtype=torch.float64)
+    assert _rel(N.gemm(ad, bd, trans_b=True), ad @ bd.t()) < 1e-12
+    with pytest.raises(ValueError):
+        N.gemm(torch.randn(3, 4), torch.randn(5, 6))
+
+
+def test_elementwise_and_reductions():
+    torch.manual_seed(0)
+    a, b, c = torch.randn(100003), torch.randn(100003), torch.randn(100003)
+    assert torch.equal(N.binary("add", a, b), a + b)
+    assert torch.equal(N.binary("sub", a, b), a - b)
+    assert torch.equal(N.binary("mul", a, b), a * b)
+    assert torch.allclose(N.binary("div", a, b), a / b, rtol=1e-6)
+    assert torch.equal(N.binary("max", a, b), torch.maximum(a, b))
+    assert torch.equal(N.binary("mul", a, 3.0), a * 3.0)
+    assert torch.equal(N.unary("relu", a), torch.relu(a))
+    assert torch.equal(N.unary("abs", a), a.abs())
+    assert torch.allclose(N.unary("sqrt", a.abs()), a.abs().sqrt(), rtol=1e-6)
+    assert torch.allclose(N.unary("exp", a), a.exp(), rtol=1e-5)
+    assert torch.allclose(N.fma(a, b, c), a * b + c, atol=1e-6)
+    assert torch.allclose(N.fma(a, b, c, "fnmadd"), c - a * b, atol=1e-6)
+    y = b.clone()
+    N.axpy(0.25, a, y)
+    assert torch.allclose(y, b + 0.25 * a, atol=1e-6)
+    assert abs(N.dot(a, b) - float(a.double() @ b.double())) < 2e-2
+    assert abs(N.sum(a) - float(a.double().sum())) < 1e-3
+    m = float(a.mean())
+    assert abs(N.sum_squared_diff(a, m) - float(((a.double() - m) ** 2).sum())) < 1e-1
+    d = torch.randn(1000, dtype=torch.float64)
+    assert abs(N.dot(d, d) - float(d @ d)) < 1e-9
+    assert torch.equal(N.fill(torch.empty(77), 1.5), torch.full((77,), 1.5))
+    t = torch.randn(70, 45)
+    assert torch.equal(N.transpose_2d(t), t.t().contiguous())
+    N.set_num_threads(2)
+    assert N.get_num_threads() == 2
+    assert _rel(N.gemm(torch.ones(64, 64), torch.ones(64, 64)), torch.full((64, 64), 64.0)) < 1e-6
+
+
+@pytest.mark.parametrize("k,s,p", [(3, 1, 1), (5, 2, 2), (1, 1, 0), (3, 2, 0)])
+def test_im2col_col2im(k, s, p):
+    x = torch.randn(3, 4, 11, 9)
+    col = N.im2col(x, k, k, (s, s), (p, p))
+    want = F.unfold(x, k, padding=p, stride=s).permute(1, 0, 2).reshape(col.shape[0], -1)
+    assert torch.equal(col, want)
+    back = N.col2im(col, tuple(x.shape), k, k, (s, s), (p, p))
+    L = col.shape[1] // 3
+    want_back = F.fold(col.reshape(col.shape[0], 3, L).permute(1, 0, 2), (11, 9), k, padding=p, stride=s)
+    assert torch.allclose(back, want_back, atol=1e-5)
+
+
+def test_native_backend_layers_match_aten(monkeypatch):
+    from dcnn_b200.ops import cpu
+    x, w, b = torch.randn(4, 3, 12, 10), torch.randn(8, 3, 3, 3), torch.randn(8, 1, 1, 1)
+    dy = torch.randn(4, 8, 6, 5)
+    ref_y, _ = cpu.conv2d_forward(x, w, b, (2, 2), (1, 1))
+    ref_dx = cpu.conv2d_backward_data(dy, w, x.shape, (2, 2), (1, 1))
+    ref_dw = torch.ones(8, 3, 3, 3)
+    cpu.conv2d_backward_weight(dy, x, ref_dw, (2, 2), (1, 1))
+    x2, w2, b2, dy2 = torch.randn(9, 20), torch.randn(7, 20), torch.randn(7), torch.randn(9, 7)
+    ref_d = cpu.dense_forward(x2, w2, b2)
+    ref_ddx = cpu.dense_backward_data(dy2, w2)
+    ref_ddw = torch.ones(7, 20)
+    cpu.dense_backward_weight(dy2, x2, ref_ddw)
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    y, st = cpu.conv2d_forward(x, w, b, (2, 2), (1, 1), want_stats=True)
+    assert st is not None and torch.allclose(y, ref_y, atol=1e-5)
+    assert torch.allclose(cpu.conv2d_backward_data(dy, w, x.shape, (2, 2), (1, 1)), ref_dx, atol=1e-5)
+    dw = torch.ones(8, 3, 3, 3)
+    cpu.conv2d_backward_weight(dy, x, dw, (2, 2), (1, 1))
+    assert torch.allclose(dw, ref_dw, atol=1e-4)
+    assert torch.allclose(cpu.dense_forward(x2, w2, b2), ref_d, atol=1e-5)
+    assert torch.allclose(cpu.dense_backward_data(dy2, w2), ref_ddx, atol=1e-5)
+    ddw = torch.ones(7, 20)
+    cpu.dense_backward_weight(dy2, x2, ddw)
+    assert torch.allclose(ddw, ref_ddw, atol=1e-5)
+
+
+def test_native_backend_trains_mnist_cnn(monkeypatch):
+    """The MNIST CNN takes identical steps (to rounding) on the native GEMM path and on ATen."""
+    from dcnn_b200 import nn as dnn
+    from dcnn_b200.models import create_mnist_trainer
+    from dcnn_b200.train import TrainStep
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(8, 1, 28, 28, generator=g)
+    t = F.one_hot(torch.randint(0, 10, (8,), generator=g), 10).float().reshape(8, 10, 1, 1)
+
+    def run():
+        m = create_mnist_trainer()
+        m.set_seed(5)
+        m.initialize()
+        o = dnn.SGD(0.05, 0.9)
+        o.attach(m.parameters(), m.gradients())
+        step = TrainStep(m, o, dnn.SoftmaxCrossEntropyLoss())
+        losses = [float(step(x, t)[0]) for _ in range(3)]
+        return losses, [p.clone() for p in m.parameters()]
+    l0, p0 = run()
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    l1, p1 = run()
+    assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-4
+    for a, b in zip(p0, p1):
+        assert torch.allclose(a, b, atol=1e-4)
