@@ -21,6 +21,8 @@ from typing import Dict, List, Optional, Sequence
 
 import torch
 
+from ..utils import runtime as _rt
+
 from ..io.tensor_codec import read_tensor, write_tensor
 from .blocks import ResidualBlock
 from .factory import LayerBuilder, LayerFactory
@@ -175,6 +177,13 @@ class Sequential:
         return dict(self.backward_times_us)
 
     def _timed(self, table, name, fn, *a, **k):
+        if _rt.NVTX and self.device.type == "cuda":   # DCNN_NVTX=1: one range per fusion unit and direction
+            tag = ("fwd " if table is self.forward_times_us else "bwd ") + name
+            with _rt.nvtx_range(tag):
+                return self._timed_inner(table, name, fn, *a, **k)
+        return self._timed_inner(table, name, fn, *a, **k)
+
+    def _timed_inner(self, table, name, fn, *a, **k):
         if not self.enable_profiling_:
             return fn(*a, **k)
         if self.device.type == "cuda":

@@ -30,6 +30,7 @@ from ...nn.loss import Loss
 from ...nn.optimizers import Optimizer
 from ...nn.sequential import Partition, Sequential
 from ...train import split_microbatches
+from ...utils import runtime as _runtime
 
 
 import os as _os
@@ -175,6 +176,7 @@ class PipelineEngine:
         """x: this replica's batch (needed on the first stage), targets: needed on the last stage.
         Returns (mean loss tensor | None, correct-count tensor | None) -- non-None on the last stage."""
         M = self.M
+        _runtime.kick()                   # feeds any running StepWatchdog (STEP_TIMEOUT_S)
         timing = self.device.type == "cuda"
         xs = split_microbatches(x.to(self.device, non_blocking=True), M) if self.is_first else None
         ts = split_microbatches(targets.to(self.device, non_blocking=True), M) if self.is_last else None

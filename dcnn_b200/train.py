@@ -18,7 +18,9 @@ import torch
 from .nn.loss import Loss
 from .nn.optimizers import Optimizer
 from .nn.sequential import Sequential
+from .utils import runtime as _runtime
 from .utils.env import get_env
+from .utils.runtime import checkpoint_on_signal, metrics_from_env, watchdog_from_env
 
 
 @dataclass
@@ -124,6 +126,7 @@ class TrainStep:
         return loss_acc, correct_acc
 
     def __call__(self, x: torch.Tensor, t: torch.Tensor):
+        _runtime.kick()                   # feeds any running StepWatchdog (STEP_TIMEOUT_S)
         if not self.use_cuda_graph:
             return self._eager(x, t)
         self._calls += 1
@@ -254,7 +257,21 @@ def train_classification_model(model, train_loader, test_loader, optimizer, loss
     step = TrainStep(model, optimizer, loss_function, config.use_cuda_graph)
     best_val_accuracy = 0.0
     history = []
+    metrics = metrics_from_env()
+    epoch_box = [0]
+    ckpt = os.path.join(config.snapshot_dir, model.name() + ".interrupted")
+    with watchdog_from_env("train step") as wd, checkpoint_on_signal(ckpt, model, optimizer, lambda: epoch_box[0]):
+        history = _classification_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step,
+                                         metrics, wd, epoch_box)
+    return history
+
+
+def _classification_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step, metrics, wd,
+                           epoch_box):
+    best_val_accuracy = 0.0
+    history = []
     for epoch in range(config.epochs):
+        epoch_box[0] = epoch
         print(f"Epoch {epoch + 1}/{config.epochs}")
         t0 = time.perf_counter()
         tl, ta = train_class_epoch(model, train_loader, optimizer, loss_function, config, step)
@@ -278,6 +295,10 @@ def train_classification_model(model, train_loader, test_loader, optimizer, loss
         print("=" * 60)
         history.append({"epoch": epoch + 1, "train_loss": tl, "train_acc": ta, "val_loss": vl, "val_acc": va,
                         "train_ms": train_ms})
+        n_img = train_loader.num_batches() * config.batch_size
+        metrics.log(kind="epoch", images_per_s=n_img / max(train_ms, 1e-9) * 1000.0, rss_kb=get_memory_usage_kb(),
+                    lr=optimizer.get_learning_rate(), **history[-1])
+        wd.kick()
         if model.is_profiling_enabled():
             model.clear_profiling_data()
         if (epoch + 1) % config.lr_decay_interval == 0:

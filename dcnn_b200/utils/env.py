@@ -62,6 +62,12 @@ def get_env(key: str, default: T) -> T:
         return default
 
 
+def override(key: str, value) -> None:
+    """Highest-priority setting (command-line flags): beats both the .env file and the inherited environment."""
+    _loaded[key] = str(value)
+    os.environ[key] = str(value)
+
+
 def ensure_env_loaded(file_path: str = "./.env"):
     if not _file_loaded and os.path.exists(file_path):
         load_env_file(file_path)

@@ -12,13 +12,40 @@ import torch  # noqa: E402
 
 from dcnn_b200.data import SyntheticDataLoader  # noqa: E402
 from dcnn_b200.train import TrainingConfig  # noqa: E402
-from dcnn_b200.utils.env import get_env, load_env_file  # noqa: E402
+from dcnn_b200.utils.env import get_env, load_env_file, override  # noqa: E402
+
+
+def apply_flag_overrides(argv=None):
+    """``--epochs 3 --batch-size=64 --device-type GPU`` -> EPOCHS / BATCH_SIZE / DEVICE_TYPE in the environment: a flag
+    layer over the reference's .env keys.  Flags win over the .env file and the inherited environment.
+    Returns the positional arguments that were not consumed."""
+    argv = list(sys.argv[1:] if argv is None else argv)
+    rest, i = [], 0
+    while i < len(argv):
+        a = argv[i]
+        if a.startswith("--") and len(a) > 2:
+            key, eq, val = a[2:].partition("=")
+            if not eq:
+                if i + 1 < len(argv) and not argv[i + 1].startswith("--"):
+                    val, i = argv[i + 1], i + 1
+                else:
+                    val = "1"            # bare switch
+            os.environ[key.upper().replace("-", "_")] = val
+        else:
+            rest.append(a)
+        i += 1
+    return rest
 
 
 def setup():
+    overrides = {k: v for k, v in os.environ.items()}
+    apply_flag_overrides()
+    flagged = {k: v for k, v in os.environ.items() if overrides.get(k) != v}
     print("Loading environment variables...")
     if not (os.path.exists("./.env") and load_env_file("./.env")):
         print("No .env file found, using default training parameters.")
+    for k, v in flagged.items():         # command-line flags beat the .env file
+        override(k, v)
     cfg = TrainingConfig().load_from_env()
     if cfg.device_type == "GPU" and not torch.cuda.is_available():
         raise SystemExit("DEVICE_TYPE=GPU but no CUDA device is visible")

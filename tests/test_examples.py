@@ -23,6 +23,9 @@ def _run(args, cwd, timeout=600, **env):
     ("uji_ips_trainer.py", "Validation - Loss"),
     ("sync_pipeline_coordinator.py", "Stopped all pipeline stages"),
     ("hardware_info_example.py", "Available devices"),
+    ("tiny_imagenet_visual_check.py", "PNG files"),
+    ("device_ptr_example.py", "grow-only"),
+    ("cuda_vs_avx2_comparison.py", "native AVX2"),
 ])
 def test_example_runs(tmp_path, script, expect):
     out = _run([sys.executable, os.path.join(ROOT, "examples", script)], cwd=str(tmp_path))
@@ -43,3 +46,9 @@ def test_multiprocess_pipeline_launch(tmp_path):
                 "--master-addr", "127.0.0.1", "--master-port", "29641",
                 os.path.join(ROOT, "examples", "semi_async_pipeline_coordinator.py")], cwd=str(tmp_path), timeout=900)
     assert "Deployed 2 pipeline stages" in out and "Stopped all pipeline stages" in out
+
+
+def test_flag_overrides_reach_an_example(tmp_path):
+    out = _run([sys.executable, os.path.join(ROOT, "examples", "mnist_cnn_trainer.py"), "--epochs", "2",
+                "--batch-size=4"], cwd=str(tmp_path))
+    assert "Epoch 2/2" in out
