@@ -1354,3 +1354,88 @@ DCNN_API int dcnn_tma_probe(const float* x, int N, int H, int W, int C, int bn, 
   DCNN_COUNT_LAUNCH(1);
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// TMA ingest probe (measurement tool, scripts/tma_ingest_probe.py): one persistent CTA per SM streams operand
+// tiles through the same mbarrier ring as the convolution kernels but issues no MMA -- the consumer just hands
+// the stage back.  It answers the question the conv_tc2 capture raised (profiles/03): is the 43 B/clk/SM operand
+// feed a per-SM ingest limit or the chip-wide L2 limit, and how much of it disappears when all CTAs read the SAME
+// B tile (what a cluster multicast would exploit)?  Each iteration loads an A box {32, a_rows} that is unique to the
+// CTA and a B box {32, b_rows} that is either shared by all CTAs (b_shared = 1) or unique as well.
+namespace dcnn {
+__global__ void __launch_bounds__(64, 1) tma_stream_probe_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                 const __grid_constant__ CUtensorMap tmB, int iters,
+                                                                 int stages, int a_rows, int b_rows, int a_row_blocks,
+                                                                 int a_col_blocks, int b_row_blocks, int b_col_blocks,
+                                                                 int b_shared) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t full_bar[8], empty_bar[8];
+  const int stage_bytes = (a_rows + b_rows) * 128;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (warp == 0 && lane == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < iters; ++it) {
+      // walk the matrices so that consecutive loads of one CTA touch new lines and different CTAs touch different
+      // A tiles: tile id = it * gridDim.x + blockIdx.x
+      const long long ta = (long long)it * gridDim.x + blockIdx.x;
+      const int a_cb = (int)(ta % a_col_blocks), a_rb = (int)((ta / a_col_blocks) % a_row_blocks);
+      const long long tb = b_shared ? (long long)it : ta;
+      const int b_cb = (int)(tb % b_col_blocks), b_rb = (int)((tb / b_col_blocks) % b_row_blocks);
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+      uint8_t* s = smem + (size_t)stage * stage_bytes;
+      tma_load_2d(s, &tmA, &full_bar[stage], a_cb * 32, a_rb * a_rows);
+      if (b_rows > 0) tma_load_2d(s + a_rows * 128, &tmB, &full_bar[stage], b_cb * 32, b_rb * b_rows);
+      if (++stage == stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1 && lane == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < iters; ++it) {
+      mbar_wait(&full_bar[stage], phase);
+      mbar_arrive(&empty_bar[stage]);
+      if (++stage == stages) { stage = 0; phase ^= 1; }
+    }
+  }
+}
+}  // namespace dcnn
+
+// A: [a_total_rows][a_cols], B: [b_total_rows][b_cols] row-major fp32 (cols % 32 == 0); boxes of a_rows / b_rows rows
+// x 32 columns (rows <= 256; b_rows = 0 skips B).  `ctas` <= 0 means one per SM.  Returns the bytes each CTA loaded
+// per iteration through *bytes_per_iter (may be NULL).
+DCNN_API int dcnn_tma_stream_probe(const float* A, long long a_total_rows, long long a_cols, int a_rows, const float* B,
+                                   long long b_total_rows, long long b_cols, int b_rows, int iters, int stages,
+                                   int b_shared, int ctas, long long* bytes_per_iter, cudaStream_t stream) {
+  DCNN_REQUIRE(a_rows >= 8 && a_rows <= 256 && b_rows >= 0 && b_rows <= 256 && a_rows % 8 == 0 && b_rows % 8 == 0,
+               "tma_stream_probe: box rows must be multiples of 8 in [8,256] (a %d, b %d)", a_rows, b_rows);
+  DCNN_REQUIRE(stages >= 1 && stages <= 8, "tma_stream_probe: stages %d out of range", stages);
+  const int stage_bytes = (a_rows + b_rows) * 128;
+  const int smem = stages * stage_bytes + 1024;
+  DCNN_REQUIRE(smem <= 227 * 1024, "tma_stream_probe: %d bytes of shared memory requested", smem);
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_2d(&tmA, A, a_total_rows, a_cols, a_rows);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmB, b_rows > 0 ? B : A, b_rows > 0 ? b_total_rows : a_total_rows, b_rows > 0 ? b_cols : a_cols,
+                    b_rows > 0 ? b_rows : a_rows);
+  if (rc) return rc;
+  DCNN_CHECK_CUDA(cudaFuncSetAttribute(tma_stream_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  if (ctas <= 0) ctas = num_sms();
+  tma_stream_probe_kernel<<<ctas, 64, smem, stream>>>(tmA, tmB, iters, stages, a_rows, b_rows,
+                                                      (int)(a_total_rows / a_rows), (int)(a_cols / 32),
+                                                      b_rows > 0 ? (int)(b_total_rows / b_rows) : 1,
+                                                      b_rows > 0 ? (int)(b_cols / 32) : 1, b_shared);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  if (bytes_per_iter) *bytes_per_iter = stage_bytes;
+  return 0;
+}

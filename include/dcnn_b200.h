@@ -30,6 +30,11 @@ int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, i
 int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin, float* dw,
                   int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw,
                   const int* tap_w, cudaStream_t stream);
+/* measurement tool: persistent CTAs stream TMA operand tiles with no MMA (per-SM / chip-wide ingest rate, effect of a
+ * shared B tile); see scripts/tma_ingest_probe.py */
+int dcnn_tma_stream_probe(const float* A, long long a_total_rows, long long a_cols, int a_rows, const float* B,
+                          long long b_total_rows, long long b_cols, int b_rows, int iters, int stages, int b_shared,
+                          int ctas, long long* bytes_per_iter, cudaStream_t stream);
 int dcnn_tma_probe(const float* x, int N, int H, int W, int C, int bn, int bh, int bw, int mul_h, int mul_w, int c0,
                    int c1, int c2, int c3, float* out, cudaStream_t stream);
 
