@@ -28,19 +28,56 @@ CLASSES = 200
 class ClockSampler(threading.Thread):
     """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, uuid=None):
         super().__init__(daemon=True)
-        self.gpu_index = gpu_index
+        self.gpu_index, self.uuid, self.source = gpu_index, (str(uuid) if uuid else None), "nvidia-smi"
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._stop_evt = threading.Event()
         self.proc = None
 
     def run(self):
+        try:
+            if self._run_nvml():
+                return
+        except Exception:      # any NVML problem: fall back to the nvidia-smi loop below
+            pass
+        self._run_smi()
+
+    def _run_nvml(self) -> bool:
+        """In-process NVML polling every 20 ms (nvidia-smi takes a few hundred ms just to start, which is most of a
+        short timed region).  Returns False if NVML cannot be used."""
+        import pynvml
+        pynvml.nvmlInit()
+        h = None
+        if self.uuid:
+            for cand in (self.uuid, "GPU-" + self.uuid):
+                try:
+                    h = pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if hasattr(cand, "encode") else cand)
+                    break
+                except Exception:
+                    h = None
+        if h is None:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index)
+        self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+            getattr(pynvml, "nvmlDeviceGetCurrentClocksThrottleReasons")
+        bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
+        self.source = "nvml"
+        while not self._stop_evt.is_set():
+            self.samples.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+            r = int(get_reasons(h))
+            for b, n in bits.items():
+                if r & b:
+                    self.reasons.add(n)
+            self._stop_evt.wait(0.02)
+        return True
+
+    def _run_smi(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.gpu_index), "-lms", "200"],
+                                          "-i", str(self.gpu_index), "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             return
@@ -68,7 +105,8 @@ class ClockSampler(threading.Thread):
     def summary(self):
         s = sorted(self.samples)
         med = s[len(s) // 2] if s else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s),
+                "source": self.source}
 
 
 def parse():
@@ -198,7 +236,8 @@ def main():
     for i in range(args.warmup):
         step(dev_x[i % nbuf], dev_t[i % nbuf])
     barrier()
-    sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else 0)
+    sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else 0,
+                           getattr(torch.cuda.get_device_properties(dev), "uuid", None))
     if rank == 0:
         sampler.start()
     _lib.reset_launch_count()
@@ -238,6 +277,7 @@ def main():
     ms_e2e = f0.elapsed_time(f1)
     if rank == 0:
         sampler.stop()
+        sampler.join(timeout=2)
 
     t = torch.tensor([ms, ms_e2e, final_loss if final_loss == final_loss else -1e30, float(launches)], device=dev,
                      dtype=torch.float64)
