@@ -1,0 +1,22 @@
+#!/usr/bin/env bash
+# First single-GPU call of the next hardware session: validates every opt-in feature written after the previous
+# session's GPU minutes ran out, then measures what each is worth.  ~3-4 minutes of box time.
+#   gpurun --timeout 420 -- 'bash scripts/gpu_next_session.sh'
+mkdir -p gpurun_out
+export PYTHONUNBUFFERED=1
+run() { name=$1; shift; echo "== $name"; timeout 240 "$@" > "gpurun_out/$name.log" 2>&1; echo "exit $?"; }
+DCNN_TEST_PENDING=1 run t_pending python -m pytest tests/test_gpu_ops.py -m gpu -q --timeout 240 -p no:cacheprovider \
+    -k "bitmask or n256 or stem_packed or tc3 or batchnorm"
+tail -3 gpurun_out/t_pending.log | cut -c1-300
+run t_all python -m pytest tests -m gpu -x -q --timeout 300 -p no:cacheprovider
+tail -3 gpurun_out/t_all.log | cut -c1-300
+for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1"; do
+  tag=$(echo "$cfg" | tr ' =' '__')
+  if [ "$cfg" = "base" ]; then run "bench_$tag" python bench.py --steps 30 --warmup 5
+  else run "bench_$tag" env $cfg python bench.py --steps 30 --warmup 5; fi
+  tail -1 "gpurun_out/bench_$tag.log" | cut -c1-260
+done
+run tma_ingest python scripts/tma_ingest_probe.py; cat gpurun_out/tma_ingest.log | cut -c1-200
+run conv_vs_cudnn python benchmarks/conv_vs_cudnn.py; tail -25 gpurun_out/conv_vs_cudnn.log | cut -c1-200
+DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 run kernels_all python scripts/prof_kernels.py
+head -30 gpurun_out/kernels_all.log | cut -c1-170

@@ -1,0 +1,14 @@
+#!/usr/bin/env bash
+# First multi-GPU call of the next hardware session (every command under its own short timeout -- a hang costs N x):
+#   gpurun --gpus 4 --timeout 300 -- 'bash scripts/gpu_next_session_multi.sh 4'
+N=${1:-2}
+mkdir -p gpurun_out
+export PYTHONUNBUFFERED=1
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533"
+echo "== allreduce roofline"; timeout 90 $TR benchmarks/allreduce_roofline.py > gpurun_out/ar_$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/ar_$N.log | cut -c1-400
+echo "== dp$N"; timeout 90 $TR bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_dp$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_dp$N.log | cut -c1-300
+echo "== pp$N"; timeout 90 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp$N --microbatches $((2*N)) > gpurun_out/bench_pp$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp$N.log | cut -c1-300
+if [ "$N" -ge 4 ]; then
+  echo "== pp2xdp$((N/2))"; timeout 90 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp2xdp$((N/2)) --microbatches 4 > gpurun_out/bench_pp2xdp.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp2xdp.log | cut -c1-300
+fi
+echo "== dp tests"; timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_$N.log | cut -c1-300
