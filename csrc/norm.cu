@@ -146,6 +146,110 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
   }
 }
 
+// Narrow variants of the two finalize kernels: 8 channels x 128 tile lanes per CTA, i.e. 4x as many CTAs.  The wide
+// kernels put a 4 MB partials array (2048 tiles x 256 channels) on 8 SMs and take ~12 us; the work is the same, only
+// the mapping changes.  32-byte row segments keep every DRAM sector fully used.  Opt-in: DCNN_BN_FINALIZE_NARROW=1.
+__global__ void __launch_bounds__(1024) bn_finalize_narrow_kernel(const float* __restrict__ partials, int tiles, int C,
+                                                                  float eps, float momentum,
+                                                                  float* __restrict__ running_mean,
+                                                                  float* __restrict__ running_var,
+                                                                  const float* __restrict__ gamma,
+                                                                  const float* __restrict__ beta,
+                                                                  float* __restrict__ mean_out,
+                                                                  float* __restrict__ invstd_out,
+                                                                  float* __restrict__ scale_out,
+                                                                  float* __restrict__ shift_out,
+                                                                  double* __restrict__ export_moments) {
+  __shared__ double s_n[128][9], s_s[128][9], s_q[128][9];
+  const int c = blockIdx.x * 8 + threadIdx.x;
+  double an = 0, as = 0, aq = 0;
+  if (c < C) {
+    const float* counts = partials + (long long)tiles * 2 * C;
+#pragma unroll 4
+    for (int t = threadIdx.y; t < tiles; t += 128) {
+      const float n = counts[t];
+      const float sf = partials[((long long)t * 2 + 0) * C + c];
+      const float m2 = partials[((long long)t * 2 + 1) * C + c];
+      const float rn = n > 0.f ? 1.f / n : 0.f;
+      an += (double)n;
+      as += (double)sf;
+      aq += (double)m2 + (double)sf * (double)sf * (double)rn;
+    }
+  }
+  s_n[threadIdx.y][threadIdx.x] = an;
+  s_s[threadIdx.y][threadIdx.x] = as;
+  s_q[threadIdx.y][threadIdx.x] = aq;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    for (int i = 1; i < 128; ++i) {
+      an += s_n[i][threadIdx.x]; as += s_s[i][threadIdx.x]; aq += s_q[i][threadIdx.x];
+    }
+    const double mean_d = an > 0 ? as / an : 0.0;
+    const double m2_d = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
+    if (export_moments != nullptr) {
+      export_moments[0 * C + c] = an;
+      export_moments[1 * C + c] = mean_d;
+      export_moments[2 * C + c] = m2_d;
+      return;
+    }
+    const double var = an > 0 ? m2_d / an : 0.0;
+    const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+    const float mean = (float)mean_d;
+    mean_out[c] = mean;
+    invstd_out[c] = invstd;
+    const float sc = gamma ? gamma[c] * invstd : invstd;
+    scale_out[c] = sc;
+    shift_out[c] = (beta ? beta[c] : 0.f) - mean * sc;
+    if (running_mean != nullptr) {
+      const double unbiased = an > 1 ? m2_d / (an - 1) : var;
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024) bn_bwd_finalize_narrow_kernel(const float* __restrict__ partials, int tiles,
+                                                                      int C, double count,
+                                                                      const float* __restrict__ mean,
+                                                                      const float* __restrict__ invstd,
+                                                                      const float* __restrict__ gamma,
+                                                                      float* __restrict__ dgamma,
+                                                                      float* __restrict__ dbeta, float* __restrict__ k1,
+                                                                      float* __restrict__ k2, float* __restrict__ k3,
+                                                                      double* __restrict__ export_sums) {
+  __shared__ double s_a[128][9], s_b[128][9];
+  const int c = blockIdx.x * 8 + threadIdx.x;
+  double a = 0, b = 0;
+  if (c < C) {
+#pragma unroll 8
+    for (int t = threadIdx.y; t < tiles; t += 128) {
+      a += partials[((long long)t * 2 + 0) * C + c];
+      b += partials[((long long)t * 2 + 1) * C + c];
+    }
+  }
+  s_a[threadIdx.y][threadIdx.x] = a;
+  s_b[threadIdx.y][threadIdx.x] = b;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    for (int i = 1; i < 128; ++i) { a += s_a[i][threadIdx.x]; b += s_b[i][threadIdx.x]; }
+    if (dgamma != nullptr) {
+      dgamma[c] += (float)b;
+      dbeta[c] += (float)a;
+    }
+    if (export_sums != nullptr) {
+      export_sums[0 * C + c] = a;
+      export_sums[1 * C + c] = b;
+      export_sums[2 * C + c] = count;
+      return;
+    }
+    const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
+    const float ma = (float)(a / count), mb = (float)(b / count);
+    k1[c] = sc;
+    k2[c] = -invstd[c] * mb * sc;
+    k3[c] = (mean[c] * invstd[c] * mb - ma) * sc;
+  }
+}
+
 // Cross-replica finish (sync-BN, K27), fused with the rendezvous: block 0 publishes "my moments are exported" to every
 // replica (st.release.sys), every block waits until all replicas have published this epoch (ld.acquire.sys), then each
 // thread merges its channel's (n, mean, M2) from every replica's symmetric buffer over NVLink peer loads.
@@ -598,9 +702,24 @@ DCNN_API int dcnn_bn_colstats(const float* x, long long M, int C, float* partial
   return 0;
 }
 
+// read per call (cheap) so that a test can toggle it
+static bool finalize_narrow() {
+  const char* e = getenv("DCNN_BN_FINALIZE_NARROW");
+  return e != nullptr && atoi(e) != 0;
+}
+
 DCNN_API int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
                               float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
                               float* scale, float* shift, double* export_moments, cudaStream_t stream) {
+  if (finalize_narrow() && tiles >= 256) {
+    dim3 nblock(8, 128);
+    bn_finalize_narrow_kernel<<<ceil_div(C, 8), nblock, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
+                                                                    running_var, gamma, beta, mean, invstd, scale,
+                                                                    shift, export_moments);
+    DCNN_CHECK_LAUNCH();
+    DCNN_COUNT_LAUNCH(1);
+    return 0;
+  }
   dim3 block(32, 32);
   bn_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
                                                            running_var, gamma, beta, mean, invstd, scale, shift,
@@ -703,6 +822,14 @@ DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* 
 DCNN_API int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
                                   const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1,
                                   float* k2, float* k3, double* export_sums, cudaStream_t stream) {
+  if (finalize_narrow() && tiles >= 256) {
+    dim3 nblock(8, 128);
+    bn_bwd_finalize_narrow_kernel<<<ceil_div(C, 8), nblock, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma,
+                                                                        dgamma, dbeta, k1, k2, k3, export_sums);
+    DCNN_CHECK_LAUNCH();
+    DCNN_COUNT_LAUNCH(1);
+    return 0;
+  }
   dim3 block(32, 32);
   bn_bwd_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma, dgamma,
                                                                dbeta, k1, k2, k3, export_sums);

@@ -6,11 +6,11 @@ mkdir -p gpurun_out
 export PYTHONUNBUFFERED=1
 run() { name=$1; shift; echo "== $name"; timeout 240 "$@" > "gpurun_out/$name.log" 2>&1; echo "exit $?"; }
 DCNN_TEST_PENDING=1 run t_pending python -m pytest tests/test_gpu_ops.py -m gpu -q --timeout 240 -p no:cacheprovider \
-    -k "bitmask or n256 or stem_packed or tc3 or batchnorm"
+    -k "bitmask or n256 or stem_packed or tc3 or batchnorm or narrow"
 tail -3 gpurun_out/t_pending.log | cut -c1-300
 run t_all python -m pytest tests -m gpu -x -q --timeout 300 -p no:cacheprovider
 tail -3 gpurun_out/t_all.log | cut -c1-300
-for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1"; do
+for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN_BN_FINALIZE_NARROW=1" "DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 DCNN_BN_FINALIZE_NARROW=1"; do
   tag=$(echo "$cfg" | tr ' =' '__')
   if [ "$cfg" = "base" ]; then run "bench_$tag" python bench.py --steps 30 --warmup 5
   else run "bench_$tag" env $cfg python bench.py --steps 30 --warmup 5; fi
@@ -18,5 +18,5 @@ for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN
 done
 run tma_ingest python scripts/tma_ingest_probe.py; cat gpurun_out/tma_ingest.log | cut -c1-200
 run conv_vs_cudnn python benchmarks/conv_vs_cudnn.py; tail -25 gpurun_out/conv_vs_cudnn.log | cut -c1-200
-DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 run kernels_all python scripts/prof_kernels.py
+DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 DCNN_BN_FINALIZE_NARROW=1 run kernels_all python scripts/prof_kernels.py
 head -30 gpurun_out/kernels_all.log | cut -c1-170

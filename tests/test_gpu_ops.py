@@ -412,3 +412,26 @@ def test_stem_packed_taps(case):
         check_close(dw, 2 * dw_ref, 4e-3, "stem wgrad (packed taps, accumulates)")
     finally:
         K.STEM_TC = old
+
+
+@pending_hw
+def test_bn_finalize_narrow(monkeypatch):
+    """8-channel x 128-lane finalize kernels (DCNN_BN_FINALIZE_NARROW=1) == the wide ones, on a conv large enough to
+    produce >= 256 statistics tiles."""
+    x = torch.randn(40, 64, 32, 32) * 2 + 3
+    w = torch.randn(96, 64, 1, 1) / 8
+    xg, wg = cl(x), cl(w)
+    gamma, beta = (torch.rand(96, 1, 1, 1) + 0.5).to(DEV), torch.randn(96, 1, 1, 1).to(DEV)
+    res = {}
+    for narrow in ("0", "1"):
+        monkeypatch.setenv("DCNN_BN_FINALIZE_NARROW", narrow)
+        y, st = ops.conv2d_forward(xg, wg, None, (1, 1), (0, 0), True)
+        assert st.tiles >= 256
+        rm, rv = torch.zeros(96, device=DEV), torch.ones(96, device=DEV)
+        mean, inv = ops.bn_finalize(st, 1e-5, 0.1, rm, rv, gamma=gamma, beta=beta)
+        out = ops.bn_apply(y, mean, inv, gamma, beta, None, True)
+        dg, db = torch.zeros(96, 1, 1, 1, device=DEV), torch.zeros(96, 1, 1, 1, device=DEV)
+        dx, _ = ops.bn_backward(cl(torch.ones(40, 96, 32, 32)) * 0.5, y, out, mean, inv, gamma, dg, db, True, False)
+        res[narrow] = [mean.clone(), inv[0].clone(), inv[1].clone(), inv[2].clone(), rm, rv, dg, db, dx]
+    for a, b in zip(res["0"], res["1"]):
+        check_close(b, a, 1e-6, "narrow finalize")
