@@ -15,12 +15,11 @@ from dcnn_b200.train import TrainingConfig  # noqa: E402
 from dcnn_b200.utils.env import get_env, load_env_file, override  # noqa: E402
 
 
-def apply_flag_overrides(argv=None):
-    """``--epochs 3 --batch-size=64 --device-type GPU`` -> EPOCHS / BATCH_SIZE / DEVICE_TYPE in the environment: a flag
-    layer over the reference's .env keys.  Flags win over the .env file and the inherited environment.
-    Returns the positional arguments that were not consumed."""
+def parse_flags(argv=None):
+    """``--epochs 3 --batch-size=64 --device-type GPU --synthetic`` -> ({"EPOCHS": "3", "BATCH_SIZE": "64",
+    "DEVICE_TYPE": "GPU", "SYNTHETIC": "1"}, [positional arguments])."""
     argv = list(sys.argv[1:] if argv is None else argv)
-    rest, i = [], 0
+    flags, rest, i = {}, [], 0
     while i < len(argv):
         a = argv[i]
         if a.startswith("--") and len(a) > 2:
@@ -30,22 +29,27 @@ def apply_flag_overrides(argv=None):
                     val, i = argv[i + 1], i + 1
                 else:
                     val = "1"            # bare switch
-            os.environ[key.upper().replace("-", "_")] = val
+            flags[key.upper().replace("-", "_")] = val
         else:
             rest.append(a)
         i += 1
+    return flags, rest
+
+
+def apply_flag_overrides(argv=None):
+    """A flag layer over the reference's .env keys: flags beat the .env file and the inherited
+    environment.  Returns the positional arguments that were not consumed."""
+    flags, rest = parse_flags(argv)
+    for k, v in flags.items():
+        override(k, v)
     return rest
 
 
 def setup():
-    overrides = {k: v for k, v in os.environ.items()}
-    apply_flag_overrides()
-    flagged = {k: v for k, v in os.environ.items() if overrides.get(k) != v}
     print("Loading environment variables...")
     if not (os.path.exists("./.env") and load_env_file("./.env")):
         print("No .env file found, using default training parameters.")
-    for k, v in flagged.items():         # command-line flags beat the .env file
-        override(k, v)
+    apply_flag_overrides()               # after the .env file so that command-line flags win
     cfg = TrainingConfig().load_from_env()
     if cfg.device_type == "GPU" and not torch.cuda.is_available():
         raise SystemExit("DEVICE_TYPE=GPU but no CUDA device is visible")
