@@ -1,0 +1,55 @@
+"""DeviceManager / hardware / misc utility tests (the reference's device_manager_test.cpp kind) plus env parsing."""
+import os
+
+import pytest
+import torch
+
+from dcnn_b200.utils import env
+from dcnn_b200.utils.device import DeviceManager, DeviceType, getCPU, initializeDefaultDevices
+from dcnn_b200.utils.misc import MetricsLogger, benchmark, get_memory_usage_kb
+
+
+def test_device_manager_discovers_cpu_and_is_a_singleton():
+    initializeDefaultDevices()
+    dm = DeviceManager.get_instance()
+    assert dm is DeviceManager.get_instance()
+    ids = dm.get_available_device_ids()
+    assert "CPU:0" in ids and dm.has_device("CPU:0") and not dm.has_device("GPU:99")
+    assert dm.get_device("CPU:0") == torch.device("cpu") == getCPU()
+    n_gpu = sum(1 for i in ids if i.startswith("GPU:"))
+    assert n_gpu == (torch.cuda.device_count() if torch.cuda.is_available() else 0)
+    with pytest.raises(Exception):
+        dm.get_device("GPU:99")
+    assert DeviceType.CPU.name == "CPU" and DeviceType.GPU.name == "GPU"
+    flow = dm.get_flow(torch.device("cpu"), "default")
+    assert flow is None or flow is not False              # CPU flows are no-ops
+
+
+def test_env_file_parsing_types_and_precedence(tmp_path):
+    f = tmp_path / "cfg.env"
+    f.write_text('# comment\nEPOCHS=7\nLR_INITIAL=0.25\nNAME="quoted value"\nFLAG=true\nBROKEN LINE\nEMPTY=\n')
+    env.clear_loaded()
+    try:
+        assert env.load_env_file(str(f))
+        assert env.get_env("EPOCHS", 1) == 7 and env.get_env("LR_INITIAL", 0.0) == 0.25
+        assert env.get_env("NAME", "") == "quoted value" and env.get_env("FLAG", False) is True
+        assert env.get_env("MISSING_KEY_XYZ", 42) == 42
+        assert env.get_env("NAME", 3) == 3                 # unparsable as int -> default
+        env.override("EPOCHS", 9)
+        assert env.get_env("EPOCHS", 1) == 9 and os.environ["EPOCHS"] == "9"
+        assert not env.load_env_file(str(tmp_path / "nope.env"))
+    finally:
+        env.clear_loaded()
+        for k in ("EPOCHS", "LR_INITIAL", "NAME", "FLAG", "EMPTY"):
+            os.environ.pop(k, None)
+
+
+def test_misc_helpers(tmp_path, capsys):
+    assert get_memory_usage_kb() > 0
+    calls = []
+    ms = benchmark("noop", lambda: calls.append(1), runs=3)
+    assert len(calls) == 4 and ms >= 0 and "noop" in capsys.readouterr().out
+    log = MetricsLogger(str(tmp_path / "a" / "m.jsonl"), rank=2)
+    rec = log.log(step=1, loss=0.5)
+    assert rec["rank"] == 2 and rec["step"] == 1 and (tmp_path / "a" / "m.jsonl").read_text().count("\n") == 1
+    assert MetricsLogger(None).log(x=1)["x"] == 1         # no file: still returns the record
