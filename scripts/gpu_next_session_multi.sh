@@ -12,3 +12,9 @@ if [ "$N" -ge 4 ]; then
   echo "== pp2xdp$((N/2))"; timeout 90 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp2xdp$((N/2)) --microbatches 4 > gpurun_out/bench_pp2xdp.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp2xdp.log | cut -c1-300
 fi
 echo "== dp tests"; timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_$N.log | cut -c1-300
+# message-driven pipeline (coordinator rank + N-1 stage ranks) on NCCL: the reference's deployment shape
+echo "== message-driven semi-async pipeline, $N ranks"
+SYNTHETIC=1 DEVICE_TYPE=GPU EPOCHS=1 BATCH_SIZE=128 NUM_MICROBATCHES=4 SYNTHETIC_TRAIN_SAMPLES=1024 SYNTHETIC_TEST_SAMPLES=256 \
+  CUDA_MODULE_LOADING=EAGER STEP_TIMEOUT_S=60 timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N \
+  --master-addr 127.0.0.1 --master-port 29544 examples/semi_async_pipeline_coordinator.py > gpurun_out/msg_pipeline_$N.log 2>&1
+echo "exit $?"; grep -E "Epoch|Validation|Stopped|images|Error|error" gpurun_out/msg_pipeline_$N.log | tail -8 | cut -c1-200
