@@ -1,0 +1,109 @@
+"""Layer-level device agnosticity (the reference's layer_device_agnosticity_test.cpp): the same layer object type on
+the CPU and on cuda:0 with identical parameters must agree to 1e-3 in FP32-exact mode, including the Conv->MaxPool and
+Conv->Dense mini-pipelines and a residual block.
+
+Written after the last GPU minutes of its session were spent, so it is opt-in until its first hardware run:
+DCNN_TEST_PENDING=1 python -m pytest tests/test_gpu_layers.py -m gpu"""
+import os
+
+import pytest
+import torch
+
+import dcnn_b200 as dc
+from dcnn_b200 import nn as dnn
+from dcnn_b200.nn.blocks import ResidualBlock
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("DCNN_TEST_PENDING") != "1",
+                                 reason="awaiting first hardware validation (set DCNN_TEST_PENDING=1)")]
+
+
+@pytest.fixture(autouse=True)
+def _exact(monkeypatch):
+    monkeypatch.setenv("DCNN_DISABLE_TC", "1")          # FP32-exact CUDA-core GEMMs: tight tolerances apply
+    torch.manual_seed(7)
+    yield
+    torch.cuda.synchronize()
+
+
+def _pair(make):
+    cpu, gpu = make(), make()
+    cpu.set_seed(3)
+    cpu.initialize()
+    gpu.set_seed(3)
+    gpu.initialize()
+    gpu.set_device("cuda:0")
+    for p, q in zip(gpu.parameters(), cpu.parameters()):
+        p.copy_(q)
+    return cpu, gpu
+
+
+def _close(a, b, tol=1e-3):
+    a, b = a.detach().cpu().float(), b.detach().cpu().float()
+    assert a.shape == b.shape
+    assert float((a - b).abs().max()) <= tol * max(1.0, float(b.abs().max())), float((a - b).abs().max())
+
+
+LAYERS = [
+    (lambda: dnn.Conv2DLayer(8, 16, 3, 3, 1, 1, 1, 1, True, "c"), (4, 8, 12, 12)),
+    (lambda: dnn.Conv2DLayer(3, 8, 5, 5, 2, 2, 2, 2, False, "c"), (2, 3, 17, 17)),
+    (lambda: dnn.Conv2DLayer(32, 64, 1, 1, 1, 1, 0, 0, True, "c"), (2, 32, 8, 8)),
+    (lambda: dnn.DenseLayer(48, 10, True, "d"), (5, 48, 1, 1)),
+    (lambda: dnn.BatchNormLayer(8, 1e-5, 0.1, True, "bn"), (6, 8, 5, 5)),
+    (lambda: dnn.GroupNormLayer(2, 8, 1e-5, True, "gn"), (3, 8, 6, 6)),
+    (lambda: dnn.MaxPool2DLayer(3, 3, 2, 2, 1, 1, "mp"), (2, 8, 9, 9)),
+    (lambda: dnn.AvgPool2DLayer(2, 2, 2, 2, 0, 0, "ap"), (2, 8, 8, 8)),
+    (lambda: dnn.ActivationLayer(dnn.create_activation("elu"), "a"), (2, 8, 4, 4)),
+    (lambda: dnn.FlattenLayer("f"), (2, 8, 3, 3)),
+]
+
+
+@pytest.mark.parametrize("make,shape", LAYERS, ids=lambda v: v().type() if callable(v) else "x".join(map(str, v)))
+def test_layer_same_on_cpu_and_gpu(make, shape):
+    cpu, gpu = _pair(make)
+    x = torch.randn(*shape)
+    yc, yg = cpu.forward(x, 0), gpu.forward(x.cuda(), 0)
+    _close(yg, yc)
+    g = torch.randn_like(yc)
+    dc_, dg = cpu.backward(g, 0), gpu.backward(g.cuda(), 0)
+    _close(dg, dc_)
+    for a, b in zip(gpu.gradients(), cpu.gradients()):
+        _close(a, b)
+    for (k, a), (_, b) in zip(gpu.buffers().items(), cpu.buffers().items()):
+        _close(a, b)
+
+
+@pytest.mark.parametrize("tail", ["maxpool", "dense"])
+def test_mini_pipelines(tail):
+    def make():
+        b = dnn.SequentialBuilder("mini").input([4, 10, 10]).conv2d(8, 3, 3, 1, 1, 1, 1, True, "c").activation("relu", "r")
+        if tail == "maxpool":
+            b.maxpool2d(2, 2, 2, 2, 0, 0, "mp")
+        else:
+            b.flatten("f").dense(6, True, "fc")
+        return b.build()
+    cpu, gpu = _pair(make)
+    x = torch.randn(3, 4, 10, 10)
+    yc, yg = cpu.forward(x, 0), gpu.forward(x.cuda(), 0)
+    _close(yg, yc)
+    g = torch.randn_like(yc)
+    _close(gpu.backward(g.cuda(), 0), cpu.backward(g, 0))
+    for a, b in zip(gpu.gradients(), cpu.gradients()):
+        _close(a, b)
+
+
+def test_residual_block_projection():
+    def make():
+        return ResidualBlock([dnn.Conv2DLayer(8, 16, 3, 3, 2, 2, 1, 1, False, "c1"), dnn.BatchNormLayer(16, 1e-5, 0.1, True, "b1"),
+                              dnn.ActivationLayer(dnn.create_activation("relu"), "r"),
+                              dnn.Conv2DLayer(16, 16, 3, 3, 1, 1, 1, 1, False, "c2"), dnn.BatchNormLayer(16, 1e-5, 0.1, True, "b2")],
+                             [dnn.Conv2DLayer(8, 16, 1, 1, 2, 2, 0, 0, False, "p"), dnn.BatchNormLayer(16, 1e-5, 0.1, True, "pb")],
+                             "relu", "rb")
+    cpu, gpu = _pair(make)
+    x = torch.randn(4, 8, 12, 12)
+    yc, yg = cpu.forward(x, 0), gpu.forward(x.cuda(), 0)
+    _close(yg, yc)
+    g = torch.randn_like(yc)
+    _close(gpu.backward(g.cuda(), 0), cpu.backward(g, 0), 2e-3)
+    for a, b in zip(gpu.gradients(), cpu.gradients()):
+        _close(a, b, 2e-3)
