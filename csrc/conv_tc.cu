@@ -1385,12 +1385,15 @@ __global__ void __launch_bounds__(64, 1) tma_stream_probe_kernel(const __grid_co
     int stage = 0;
     uint32_t phase = 0;
     for (int it = 0; it < iters; ++it) {
-      // walk the matrices so that consecutive loads of one CTA touch new lines and different CTAs touch different
-      // A tiles: tile id = it * gridDim.x + blockIdx.x
-      const long long ta = (long long)it * gridDim.x + blockIdx.x;
-      const int a_cb = (int)(ta % a_col_blocks), a_rb = (int)((ta / a_col_blocks) % a_row_blocks);
-      const long long tb = b_shared ? (long long)it : ta;
-      const int b_cb = (int)(tb % b_col_blocks), b_rb = (int)((tb / b_col_blocks) % b_row_blocks);
+      // walk memory the way the convolution does: a CTA owns a block of consecutive rows (pixels) and visits its
+      // 32-column chunks on consecutive iterations (the k-steps), then moves to its next row block.  (The first version
+      // of this probe used 4096-column matrices and jumped to a new 2 MB region every iteration; its timings were
+      // dominated by that, see profiles/04.)
+      const int kc = it % a_col_blocks;
+      const long long tile = (long long)(it / a_col_blocks) * gridDim.x + blockIdx.x;
+      const int a_cb = kc, a_rb = (int)(tile % a_row_blocks);
+      const int b_cb = it % b_col_blocks;
+      const int b_rb = b_shared ? 0 : (int)(tile % b_row_blocks);
       mbar_wait(&empty_bar[stage], phase ^ 1);
       mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
       uint8_t* s = smem + (size_t)stage * stage_bytes;

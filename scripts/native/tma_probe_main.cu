@@ -7,7 +7,8 @@ extern "C" const char* dcnn_last_error(void);
 
 static float* A = nullptr;
 static float* B = nullptr;
-static const long long kARows = 1 << 16, kBRows = 1 << 14, kCols = 4096;
+// A: activations-like [2M pixels][128 channels] (1 GiB); B: weights-like [16384 rows][128] (8 MiB, L2 resident)
+static const long long kARows = 1 << 21, kBRows = 1 << 14, kCols = 128;
 static FILE* out = nullptr;
 
 static void run(int a_rows, int b_rows, int stages, int shared, int ctas, int iters = 1500) {

@@ -14,8 +14,8 @@ dev = "cuda:0"
 props = torch.cuda.get_device_properties(0)
 sms = props.multi_processor_count
 clk = 1.965e9
-A = torch.randn(1 << 16, 4096, device=dev)      # 1 GiB
-B = torch.randn(1 << 14, 4096, device=dev)      # 256 MiB
+A = torch.randn(1 << 21, 128, device=dev)       # activations-like: 2M pixels x 128 channels (1 GiB)
+B = torch.randn(1 << 14, 128, device=dev)       # weights-like: 8 MiB, L2 resident
 
 
 def run(a_rows, b_rows, stages, shared, ctas, iters=2000):
