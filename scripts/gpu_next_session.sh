@@ -18,7 +18,8 @@ for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN
   else run "bench_$tag" env $cfg python bench.py --steps 30 --warmup 5; fi
   tail -1 "gpurun_out/bench_$tag.log" | cut -c1-260
 done
-run tma_ingest python scripts/tma_ingest_probe.py; cat gpurun_out/tma_ingest.log | cut -c1-200
+echo '== tma probe (native)'; [ -x scripts/native/tma_probe ] || nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Icsrc scripts/native/tma_probe_main.cu csrc/core.cu -o scripts/native/tma_probe -lcuda
+timeout 30 scripts/native/tma_probe gpurun_out/tma_probe2.txt; cat gpurun_out/tma_probe2.txt | cut -c1-200
 run conv_vs_cudnn python benchmarks/conv_vs_cudnn.py; tail -25 gpurun_out/conv_vs_cudnn.log | cut -c1-200
 DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 DCNN_BN_FINALIZE_NARROW=1 run kernels_all python scripts/prof_kernels.py
 head -30 gpurun_out/kernels_all.log | cut -c1-170
