@@ -805,6 +805,278 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
 }
 
 // =====================================================================================================
+// conv_tc5: CTA-pair version (tcgen05 cta_group::2) for wide layers (Cout >= 256).
+//
+// Two CTAs of a cluster (one TPC) compute a 256-pixel x 256-channel tile with M = 256 MMAs issued by the leader:
+// each CTA loads ITS 128 pixels of A and ITS 128 of the 256 weight rows of B, and owns the accumulator rows of its
+// pixels (128 TMEM lanes x 256 columns, double buffered = all 512 columns).  Per CTA that is 128 + 128 operand rows
+// per k-step for a 128x256 output slice -- half the TMA traffic per MAC of conv_tc2 and 2/3 of conv_tc3's -- with the
+// epilogue of tile i still overlapping the mainloop of tile i+1.
+//
+// Protocol (after the DeepGEMM / CUTLASS 2-SM pattern): full[s] lives in the leader, count 2 = the leader producer's
+// arrive.expect_tx(bytes of both CTAs) + the peer producer's remote arrive; both producers' TMA loads count their
+// bytes on it.  The leader's MMA thread frees stage s in BOTH CTAs and signals the accumulator to BOTH epilogues
+// with multicast commits.  The epilogue warps of both CTAs (2 x 4) arrive on the leader's tmem_empty[a].
+// Opt-in (DCNN_CONV_2CTA=1): written after the last GPU minutes of its session; not yet run on hardware.
+// =====================================================================================================
+template <int STAGES>
+struct ConvTc5Smem {
+  static constexpr int kBN = 256;                  // tile width (channels) of the pair
+  static constexpr int kABytes = kBM * 128;        // this CTA's 128 pixels
+  static constexpr int kBBytes = (kBN / 2) * 128;  // this CTA's half of the weight rows
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kPipeBytes = STAGES * kStageBytes;
+  static constexpr int kHalfCols = 128;            // the epilogue drains 128 columns at a time
+  static constexpr int kChunks = kHalfCols / 32;
+  static constexpr int kStagingBytes = kChunks * kBM * 128;
+  static constexpr int kRedBytes = 2 * 4 * kHalfCols * 4;
+  static constexpr int kBarOff = kPipeBytes + kStagingBytes;
+  static constexpr int kRedOff = kBarOff + 256;
+  static constexpr int kFlagOff = kRedOff + kRedBytes;
+  static constexpr int kTotalBytes = kFlagOff + 128 + 1024 /*align*/;
+  static_assert(kTotalBytes <= 232448, "conv_tc5 shared memory exceeds 227 KB");
+};
+
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+    conv_tc5_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvTcParams p) {
+  using S = ConvTc5Smem<STAGES>;
+  constexpr int BN = S::kBN, HC = S::kHalfCols;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + S::kPipeBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  float* red = reinterpret_cast<float*>(smem + S::kRedOff);
+  uint8_t* row_valid = smem + S::kFlagOff;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = cluster_ctarank();   // 0 = leader
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int m_pairs = (p.m_tiles + 1) >> 1;
+  const int total_tiles = m_pairs * p.n_tiles;   // pair tiles
+  const int cchunks = p.Cin / kBK;
+  const int num_kb = p.num_taps * cchunks;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < STAGES; ++s) {
+        mbar_init(&full_bar[s], 2);    // (used in the leader) leader producer + peer producer
+        mbar_init(&empty_bar[s], 1);   // one multicast commit
+      }
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(&tmem_full_bar[a], 1);   // one multicast commit
+        mbar_init(&tmem_empty_bar[a], 8);  // (used in the leader) 4 epilogue warps of each CTA
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc_pair(tmem_slot, 2 * BN);    // executed by warp 1 of BOTH CTAs
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();   // barriers of both CTAs are initialised before any remote arrive / remote complete_tx
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer (both CTAs) =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        const int n_tile = tile % p.n_tiles;
+        const int m_tile = (tile / p.n_tiles) * 2 + (int)cta_rank;   // may be == m_tiles (odd count): all out of range
+        const int tw = m_tile % p.tiles_w;
+        const int th = (m_tile / p.tiles_w) % p.tiles_h;
+        const int tn = m_tile / (p.tiles_w * p.tiles_h);
+        const int n0 = tn * p.bn, ih0 = th * p.bh * p.in_mul_h, iw0 = tw * p.bw * p.in_mul_w;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int t = kb / cchunks;
+          const int c = kb - t * cchunks;
+          mbar_wait(&empty_bar[stage], phase ^ 1);   // own slot free (the leader's commit reaches both CTAs)
+          const uint32_t leader_full = map_to_cta(smem_u32(&full_bar[stage]), 0);
+          uint8_t* sA = smem + stage * S::kStageBytes;
+          tma_load_4d_pair(sA, &tmA, leader_full, c * kBK, iw0 + p.tap_dw[t], ih0 + p.tap_dh[t], n0);
+          tma_load_2d_pair(sA + S::kABytes, &tmB, leader_full, p.tap_w[t] * p.Cin + c * kBK,
+                           n_tile * BN + (int)cta_rank * (BN / 2));
+          if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * S::kStageBytes);
+          else mbar_arrive_cluster(leader_full);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && cta_rank == 0) {
+      // ===================== MMA issuer (leader CTA only) =====================
+      constexpr uint32_t idesc = make_idesc_tf32(2 * kBM, BN, 0, 0);   // M = 256 over the pair
+      constexpr uint64_t desc_hi = make_smem_desc_hi(16, 1024);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        mbar_wait(&tmem_empty_bar[as], aphase ^ 1);   // both epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+          const uint32_t b_addr = a_addr + S::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 8; ++k)
+            mma_tf32_ss_pair(tmem_d, make_smem_desc(a_addr + k * 32, desc_hi), make_smem_desc(b_addr + k * 32, desc_hi),
+                             idesc, (kb | k) != 0);
+          mma_commit_pair(&empty_bar[stage], 0b11);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        mma_commit_pair(&tmem_full_bar[as], 0b11);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5 of both CTAs): own 128 pixels, 256 channels in two halves ==========
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const int e = threadIdx.x - 64;
+    const bool issuer = (e == 0);
+    const int w_l = r % p.bw, h_l = (r / p.bw) % p.bh, n_l = r / (p.bw * p.bh);
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      const int n_tile = tile % p.n_tiles;
+      const int m_tile = (tile / p.n_tiles) * 2 + (int)cta_rank;
+      const bool live = m_tile < p.m_tiles;   // the odd tile out has no pixels: drain the accumulator, write nothing
+      const int tw = m_tile % p.tiles_w;
+      const int th = (m_tile / p.tiles_w) % p.tiles_h;
+      const int tn = m_tile / (p.tiles_w * p.tiles_h);
+      const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
+      const bool full_tile = (n0 + p.bn <= p.N) && (oh0 + p.bh <= p.OH) && (ow0 + p.bw <= p.OW);
+
+      mbar_wait(&tmem_full_bar[as], aphase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int half = 0; half < 2; ++half) {
+        const int col_base = n_tile * BN + half * HC;
+        const bool cols_live = live && col_base < p.Cout;
+        if (issuer) tma_store_wait_read();
+        if (p.partials != nullptr && !full_tile)
+          row_valid[r] = ((n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW)) ? 1 : 0;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+
+        const uint32_t tmem_d = tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16);
+        if (cols_live) {
+#pragma unroll 1
+          for (int ch = 0; ch < S::kChunks; ++ch) {
+            if (col_base + ch * 32 >= p.Cout) break;
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
+            tmem_ld_wait();
+            uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              float4 o;
+              o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
+              o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
+              if (p.bias != nullptr) {
+                const int c = col_base + ch * 32 + 4 * j;
+                if (c < p.Cout) {
+                  const float4 b = ldg4(p.bias + c);
+                  o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+                }
+              }
+              *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
+            }
+          }
+        }
+        if (half == 1) {
+          // accumulator fully read by this warp: tell the leader's MMA thread (one arrival per epilogue warp per CTA)
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&tmem_empty_bar[as]), 0));
+        }
+        fence_proxy_async();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (!cols_live) continue;
+
+        if (issuer) {
+          for (int ch = 0; ch < S::kChunks; ++ch) {
+            const int c = col_base + ch * 32;
+            if (c >= p.Cout) break;
+            if (p.accumulate) tma_reduce_add_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
+            else tma_store_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
+          }
+          tma_store_commit();
+        }
+
+        if (p.partials != nullptr) {
+          const int cl = e & 31, rg = e >> 5;
+          int cnt = kBM;
+          if (!full_tile) {
+            cnt = 0;
+            for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
+          }
+          for (int ch = 0; ch < S::kChunks; ++ch) {
+            if (col_base + ch * 32 >= p.Cout) break;
+            const uint8_t* src = staging + ch * (kBM * 128);
+            const float kshift = *reinterpret_cast<const float*>(src + ((cl >> 2) << 4) + ((cl & 3) << 2));  // row 0
+            float s = 0.f, qq = 0.f;
+            for (int i = 0; i < 32; ++i) {
+              const int rr = rg * 32 + i;
+              const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
+                                                              ((cl & 3) << 2));
+              const float d = (full_tile || row_valid[rr]) ? x - kshift : 0.f;
+              s += d;
+              qq = fmaf(d, d, qq);
+            }
+            red[(0 * 4 + rg) * HC + ch * 32 + cl] = s;
+            red[(1 * 4 + rg) * HC + ch * 32 + cl] = qq;
+          }
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          for (int j = e; j < HC; j += 128) {
+            const int c = col_base + j;
+            if (c < p.Cout) {
+              const int ch = j >> 5, cl2 = j & 31;
+              const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) +
+                                                                   ((cl2 & 3) << 2));
+              const float s = red[(0 * 4 + 0) * HC + j] + red[(0 * 4 + 1) * HC + j] + red[(0 * 4 + 2) * HC + j] +
+                              red[(0 * 4 + 3) * HC + j];
+              const float qq = red[(1 * 4 + 0) * HC + j] + red[(1 * 4 + 1) * HC + j] + red[(1 * 4 + 2) * HC + j] +
+                               red[(1 * 4 + 3) * HC + j];
+              const float n = (float)cnt;
+              p.partials[((long long)m_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
+              p.partials[((long long)m_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
+            }
+          }
+          if (e == 0 && n_tile == 0 && half == 0) p.partials[(long long)p.m_tiles * 2 * p.Cout + m_tile] = (float)cnt;
+        }
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (issuer) tma_store_wait_all();
+  }
+
+  // both CTAs are done with each other's barriers, shared memory and the paired tensor memory
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 2 * BN);
+  }
+}
+
+// =====================================================================================================
 // wgrad
 // =====================================================================================================
 constexpr int kWPix = 64;  // reduction (pixel) rows per pipeline stage
@@ -1095,6 +1367,36 @@ static int launch_conv3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   return 0;
 }
 
+template <int STAGES>
+static int launch_conv5(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const ConvTcParams& p,
+                        cudaStream_t stream) {
+  using S = ConvTc5Smem<STAGES>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc5_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         S::kTotalBytes));
+    attr_set = true;
+  }
+  const long long pair_tiles = (long long)((p.m_tiles + 1) / 2) * p.n_tiles;
+  const int max_pairs = num_sms() / 2;
+  const int pairs = (int)(pair_tiles < max_pairs ? pair_tiles : max_pairs);
+  conv_tc5_kernel<STAGES><<<2 * pairs, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, tmO, p);  // clusters of 2
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+// conv_tc5 (CTA pairs, 256 x 256 tiles): opt-in with DCNN_CONV_2CTA=1, for Cout >= 256 (Cout % 4 == 0) when there is at
+// least one pair tile per CTA pair.  Uses conv_tc2's 128-pixel boxes, so the statistics-tile count is unchanged.
+static bool conv_2cta_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout) {
+  const char* e = getenv("DCNN_CONV_2CTA");
+  if (e == nullptr || atoi(e) == 0 || (Cout & 3) != 0 || Cout < 256) return false;
+  int bn = 1, bh = 1, bw = 1;
+  choose_box(N, OH, OW, kBM, mul_h, mul_w, &bn, &bh, &bw);
+  const long long m_tiles = (long long)ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
+  return ((m_tiles + 1) / 2) * ceil_div(Cout, 256) >= num_sms() / 2;
+}
+
 // conv_tc3 is used unless it is switched off (DCNN_CONV_V3=0), when the vectorised epilogue applies (Cout % 4 == 0) and the
 // loop space has at least one 256-pixel tile per SM; smaller problems keep the 128-pixel tiles of conv_tc2.
 static bool conv_v3_enabled() {
@@ -1159,6 +1461,7 @@ DCNN_API int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w) {
 // 128-row statistics tiles per M tile.
 DCNN_API int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout) {
   int bn, bh, bw;
+  if (conv_2cta_applies(N, OH, OW, mul_h, mul_w, Cout)) return dcnn_conv_tc_m_tiles(N, OH, OW, mul_h, mul_w);
   if (conv_v3_applies(N, OH, OW, mul_h, mul_w, Cout, &bn, &bh, &bw))
     return 2 * ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
   return dcnn_conv_tc_m_tiles(N, OH, OW, mul_h, mul_w);
@@ -1197,6 +1500,15 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   int rc = make_tmap_nhwc(&tmA, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
   if (rc) return rc;
   static const bool use_v1 = getenv("DCNN_CONV_V1") != nullptr && atoi(getenv("DCNN_CONV_V1")) != 0;
+  if (vec_ok && conv_2cta_applies(N, OH, OW, in_mul_h, in_mul_w, Cout)) {
+    CUtensorMap tmO5;
+    rc = make_tmap_out(&tmO5, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);
+    if (rc) return rc;
+    p.n_tiles = ceil_div(Cout, 256);
+    rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);   // each CTA of the pair loads 128 of the tile's 256 weight rows
+    if (rc) return rc;
+    return launch_conv5<4>(tmA, tmB, tmO5, p, stream);
+  }
   {
     int bn3, bh3, bw3;
     if (vec_ok && conv_v3_applies(N, OH, OW, in_mul_h, in_mul_w, Cout, &bn3, &bh3, &bw3)) {

@@ -1,5 +1,5 @@
-"""Numerics + timing check of the 256-pixel-tile convolution kernel (conv_tc3).  Run with DCNN_CONV_V3=1 (a fresh
-process: the switch is read once).  Compares fprop (+ epilogue BN statistics), dgrad and dgrad-accumulate against
+"""Numerics + timing check of the 256-pixel-tile convolution kernel (conv_tc3; DCNN_CONV_V3=1) or, with ``--pair`` and
+DCNN_CONV_2CTA=1, of the CTA-pair kernel (conv_tc5).  Run in a fresh process: the switches are read once.  Compares fprop (+ epilogue BN statistics), dgrad and dgrad-accumulate against
 cuDNN FP32 (allow_tf32 off) on shapes large enough to select the kernel, including partial tiles; prints PASS/FAIL and
 CUDA-event timings with an L2 flush between launches.  Exit code 0 only if everything passed."""
 import os
@@ -49,7 +49,11 @@ def timed(fn, iters=10, warm=3):
 
 
 # (N, Cin, H, W, Cout, k, stride, pad, bias)
-cases = [(64, 64, 32, 32, 128, 3, 1, 1, True),     # 256 full tiles, two N tiles? no: Cout 128 -> one
+PAIR_CASES = [(64, 64, 32, 32, 256, 1, 1, 0, True),      # DCNN_CONV_2CTA=1: CTA-pair kernel, one 256-wide N tile
+              (37, 32, 15, 15, 320, 3, 1, 1, False),     # partial pixel tiles, partial second N tile (320 = 256 + 64)
+              (149, 64, 8, 8, 512, 3, 1, 1, True),       # odd number of 128-pixel tiles: the last pair has an empty half
+              (32, 256, 16, 16, 1024, 1, 1, 0, False)]   # ResNet-50 stage-2 expand shape, four N tiles
+cases = PAIR_CASES if "--pair" in sys.argv else [(64, 64, 32, 32, 128, 3, 1, 1, True),     # 256 full tiles, two N tiles? no: Cout 128 -> one
          (40, 32, 33, 31, 64, 3, 1, 1, False),      # partial tiles in h and w, BN=64 variant
          (48, 64, 32, 32, 320, 1, 1, 0, True),      # three N tiles, the last one partial (320 = 2.5 x 128)
          (602, 32, 16, 16, 128, 3, 2, 1, False),    # strided: element-stride box, 8x8 outputs, box spans 4 images (last partial)
@@ -83,8 +87,13 @@ for (N, Ci, H, W, Co, k, s, p, bias) in cases:
     torch.cuda.synchronize()
 
 N = 256
-for name, ci, co, h, r, p in [("3x3 128->128 @32x32", 128, 128, 32, 3, 1), ("1x1 256->1024 @16x16", 256, 1024, 16, 1, 0),
-                              ("3x3 256->256 @16x16", 256, 256, 16, 3, 1), ("1x1 512->128 @32x32", 512, 128, 32, 1, 0)]:
+TIMED = [("3x3 128->128 @32x32", 128, 128, 32, 3, 1), ("1x1 256->1024 @16x16", 256, 1024, 16, 1, 0),
+         ("3x3 256->256 @16x16", 256, 256, 16, 3, 1), ("1x1 512->128 @32x32", 512, 128, 32, 1, 0)]
+if "--pair" in sys.argv:
+    TIMED = [("1x1 256->1024 @16x16", 256, 1024, 16, 1, 0), ("3x3 256->256 @16x16", 256, 256, 16, 3, 1),
+             ("1x1 128->512 @16x16", 128, 512, 16, 1, 0), ("1x1 64->256 @32x32", 64, 256, 32, 1, 0),
+             ("1x1 512->2048 @4x4", 512, 2048, 4, 1, 0)]
+for name, ci, co, h, r, p in TIMED:
     x = torch.randn(N, ci, h, h, device=dev).contiguous(memory_format=CL)
     w = (torch.randn(co, ci, r, r, device=dev) * 0.05).contiguous(memory_format=CL)
     us = timed(lambda: K.conv2d_forward(x, w, None, (1, 1), (p, p), want_stats=True))

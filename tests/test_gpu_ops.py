@@ -435,3 +435,15 @@ def test_bn_finalize_narrow(monkeypatch):
         res[narrow] = [mean.clone(), inv[0].clone(), inv[1].clone(), inv[2].clone(), rm, rv, dg, db, dx]
     for a, b in zip(res["0"], res["1"]):
         check_close(b, a, 1e-6, "narrow finalize")
+
+
+@pending_hw
+def test_conv_tc5_cta_pairs():
+    """CTA-pair (tcgen05 cta_group::2) convolution kernel against cuDNN FP32 in a fresh process (DCNN_CONV_2CTA=1)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, DCNN_CONV_2CTA="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "check_conv_v3.py"), "--pair"], env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ALL PASS" in r.stdout and "FAIL" not in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
