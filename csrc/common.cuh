@@ -38,6 +38,20 @@ const char* last_error();
 extern unsigned long long g_launch_count;
 #define DCNN_COUNT_LAUNCH(n) (::dcnn::g_launch_count += (n))
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute of a kernel: set it once on every device the
+// kernel is launched on (a single process may drive one pipeline stage per GPU).  Usage:
+//   DCNN_SET_MAX_SMEM_ONCE(bytes, kernel<TEMPLATE, ARGS>);
+#define DCNN_SET_MAX_SMEM_ONCE(bytes, ...)                                                                        \
+  do {                                                                                                            \
+    static bool dcnn_done_[64] = {};                                                                              \
+    int dcnn_dev_ = 0;                                                                                            \
+    cudaGetDevice(&dcnn_dev_);                                                                                    \
+    if (dcnn_dev_ < 0 || dcnn_dev_ >= 64 || !dcnn_done_[dcnn_dev_]) {                                             \
+      DCNN_CHECK_CUDA(cudaFuncSetAttribute(__VA_ARGS__, cudaFuncAttributeMaxDynamicSharedMemorySize, (bytes)));   \
+      if (dcnn_dev_ >= 0 && dcnn_dev_ < 64) dcnn_done_[dcnn_dev_] = true;                                         \
+    }                                                                                                             \
+  } while (0)
+
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline int num_sms() {
   static int n = 0;

@@ -1335,12 +1335,7 @@ template <int BN, int STAGES>
 static int launch_conv2(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const ConvTcParams& p,
                         cudaStream_t stream) {
   using S = ConvTc2Smem<BN, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc2_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         S::kTotalBytes));
-    attr_set = true;
-  }
+  DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, conv_tc2_kernel<BN, STAGES>);
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   conv_tc2_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, tmO, p);
@@ -1353,12 +1348,7 @@ template <int BN, int STAGES>
 static int launch_conv3(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO,
                         const ConvTc3Params& p, cudaStream_t stream) {
   using S = ConvTc3Smem<BN, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc3_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         S::kTotalBytes));
-    attr_set = true;
-  }
+  DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, conv_tc3_kernel<BN, STAGES>);
   const long long tiles = (long long)p.b.m_tiles * p.b.n_tiles;
   const int grid = (int)(tiles < num_sms() ? tiles : num_sms());
   conv_tc3_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, tmO, p);
@@ -1371,12 +1361,7 @@ template <int STAGES>
 static int launch_conv5(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const ConvTcParams& p,
                         cudaStream_t stream) {
   using S = ConvTc5Smem<STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc5_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         S::kTotalBytes));
-    attr_set = true;
-  }
+  DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, conv_tc5_kernel<STAGES>);
   const long long pair_tiles = (long long)((p.m_tiles + 1) / 2) * p.n_tiles;
   const int max_pairs = num_sms() / 2;
   const int pairs = (int)(pair_tiles < max_pairs ? pair_tiles : max_pairs);
@@ -1415,12 +1400,7 @@ static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cou
 template <int BN, int STAGES>
 static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvTcParams& p, cudaStream_t stream) {
   using S = ConvTcSmem<BN, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DCNN_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         S::kTotalBytes));
-    attr_set = true;
-  }
+  DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, conv_tc_kernel<BN, STAGES>);
   dim3 grid((unsigned)((long long)p.m_tiles * p.n_tiles));
   conv_tc_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, p);
   DCNN_CHECK_LAUNCH();
@@ -1431,12 +1411,7 @@ static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const Con
 template <int BNW, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradTcParams& p, cudaStream_t stream) {
   using S = WgradSmem<BNW, STAGES>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DCNN_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel<BNW, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         S::kTotalBytes));
-    attr_set = true;
-  }
+  DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, wgrad_tc_kernel<BNW, STAGES>);
   dim3 grid((unsigned)(p.num_taps * p.oc_tiles * p.c_tiles), (unsigned)p.splits);
   wgrad_tc_kernel<BNW, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmDY, tmX, p);
   DCNN_CHECK_LAUNCH();
