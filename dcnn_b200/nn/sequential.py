@@ -242,9 +242,18 @@ class Sequential:
             self._units = build_units(self.layers, self.fuse)
         return self._units
 
+    def _foreign_device(self) -> bool:
+        """True when this model lives on a CUDA device that is not the calling thread's current device (kernels are
+        launched on the current device's stream, so the call has to switch first)."""
+        d = self.device
+        return d.type == "cuda" and d.index is not None and torch.cuda.current_device() != d.index
+
     def forward(self, x: torch.Tensor, micro_batch_id: int = 0) -> torch.Tensor:
         if not self.layers:
             raise RuntimeError("Cannot forward through empty sequential model")
+        if self._foreign_device():
+            with torch.cuda.device(self.device):
+                return self.forward(x, micro_batch_id)
         if x.device != self.device:
             x = x.to(self.device, non_blocking=True)
         for u in self._get_units():
@@ -257,6 +266,9 @@ class Sequential:
     def backward(self, grad: torch.Tensor, micro_batch_id: int = 0) -> Optional[torch.Tensor]:
         if not self.layers:
             raise RuntimeError("Cannot backward through empty sequential model")
+        if self._foreign_device():
+            with torch.cuda.device(self.device):
+                return self.backward(grad, micro_batch_id)
         if grad.device != self.device:
             grad = grad.to(self.device, non_blocking=True)
         units = self._get_units()

@@ -62,6 +62,10 @@ class PipelineStage:
             self._thread.join(timeout=10)
 
     def message_loop(self):
+        # the CUDA current device is per thread: a stage thread of a single-process multi-GPU pipeline must select its
+        # own GPU, or its kernels would be launched on device 0 with another device's pointers
+        if self.device is not None and torch.device(self.device).type == "cuda":
+            torch.cuda.set_device(torch.device(self.device))
         while not self.should_stop:
             if not self.comm.wait_for_input(timeout=0.05):
                 continue
