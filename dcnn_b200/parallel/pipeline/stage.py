@@ -44,6 +44,7 @@ class PipelineStage:
         self.loss_sum = 0.0
         self.correct_sum = 0.0
         self.loss_count = 0
+        self._hw = None
         if model is not None and optimizer is not None:
             optimizer.attach(model.parameters(), model.gradients())
 
@@ -126,6 +127,16 @@ class PipelineStage:
             self.load.avg_backward_time_ms = self._bwd_ms / max(1, self._bwd_n)
             if torch.cuda.is_available() and self.device is not None and self.device.type == "cuda":
                 self.load.max_memory_usage_mb = torch.cuda.max_memory_allocated(self.device) / 1048576.0
+            else:
+                from ...utils.misc import get_memory_usage_kb
+                self.load.max_memory_usage_mb = get_memory_usage_kb() / 1024.0
+            # CPU utilisation since the previous UPDATE_LOAD (ref pipeline_stage.hpp:199-229 folds HardwareInfo's
+            # dynamic info into the LoadTracker the same way)
+            if self._hw is None:
+                from ...utils.hardware import HardwareInfo
+                self._hw = HardwareInfo()
+                self._hw.initialize()
+            self.load.avg_cpu_utilization = float(self._hw.update_dynamic_info()["cpu_utilization_percent"])
             if c == CommandType.REPORT_LOAD:
                 self._send("coordinator", CommandType.LOAD_REPORT, self.load)
         elif c == CommandType.SEND_PARAMS:

@@ -27,12 +27,22 @@ def main():
     ap.add_argument("--num-threads", type=int, default=0, help="CPU threads for a CPU stage")
     ap.add_argument("--pin-numa", action="store_true", help="pin this process to the NUMA node of its GPU")
     ap.add_argument("--show-cores", action="store_true")
+    ap.add_argument("--ecore", action="store_true", help="pin a CPU stage to the efficiency cores (ref --ecore)")
+    ap.add_argument("--max-ecores", type=int, default=0, help="use at most N efficiency cores (ref --max-ecores)")
+    ap.add_argument("--io-threads", type=int, default=0,
+                    help="accepted for command-line compatibility: the reference sizes its ASIO pool with it; here "
+                         "transport threads belong to gloo / NCCL")
     args = ap.parse_args()
     hw = HardwareInfo()
     hw.initialize()
+    affinity = ThreadAffinity(hw)
+    if args.ecore and not args.gpu:
+        ok = affinity.set_efficiency_cores(args.max_ecores)
+        print(f"Efficiency-core affinity {'set' if ok else 'NOT set'}")
     if args.show_cores:
         hw.print_info()
-        ThreadAffinity(hw).print_affinity_info()
+        print(f"performance cores: {hw.get_performance_cores()}  efficiency cores: {hw.get_efficiency_cores()}")
+        affinity.print_affinity_info()
     rank, world = init_distributed(use_gpu=args.gpu)
     if rank == 0:
         raise SystemExit("rank 0 is the coordinator; start a coordinator example there")
@@ -40,7 +50,7 @@ def main():
     if args.gpu:
         torch.cuda.set_device(dev)
         if args.pin_numa:
-            ThreadAffinity(hw).pin_to_gpu_node(dev)
+            affinity.pin_to_gpu_node(dev)
     elif args.num_threads:
         torch.set_num_threads(args.num_threads)
     stage_ranks = list(range(1, world))

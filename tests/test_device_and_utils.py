@@ -53,3 +53,31 @@ def test_misc_helpers(tmp_path, capsys):
     rec = log.log(step=1, loss=0.5)
     assert rec["rank"] == 2 and rec["step"] == 1 and (tmp_path / "a" / "m.jsonl").read_text().count("\n") == 1
     assert MetricsLogger(None).log(x=1)["x"] == 1         # no file: still returns the record
+
+
+def test_hardware_info_topology_dynamic_and_affinity():
+    import json
+    import time
+    from dcnn_b200.utils.hardware import HardwareInfo, ThreadAffinity, _parse_cpulist
+    hw = HardwareInfo()
+    assert hw.initialize()
+    t = hw.info["topology"]
+    assert t["logical"] >= t["physical"] >= 1 and t["sockets"] >= 1 and t["threads_per_core"] >= 1
+    assert sorted(hw.get_performance_cores() + hw.get_efficiency_cores()) == sorted(t["per_cpu"]) or not t["per_cpu"]
+    assert hw.get_usable_cores() >= 1 and "MemTotal" in hw.info["memory"]
+    time.sleep(0.05)
+    dyn = hw.update_dynamic_info()
+    assert 0.0 <= dyn["cpu_utilization_percent"] <= 100.0 and 0.0 <= dyn["memory_used_percent"] <= 100.0
+    blob = json.loads(hw.to_json())
+    assert "per_cpu" not in blob["topology"] and "dynamic" in blob
+    assert _parse_cpulist("0-2,5, 7-8") == [0, 1, 2, 5, 7, 8]
+    if hasattr(os, "sched_getaffinity"):
+        before = os.sched_getaffinity(0)
+        try:
+            ta = ThreadAffinity(hw)
+            assert ta.set_efficiency_cores(1) and len(os.sched_getaffinity(0)) == 1
+            os.sched_setaffinity(0, before)
+            assert ta.set_performance_cores() and os.sched_getaffinity(0) <= before
+            assert not ta.set_cores([])
+        finally:
+            os.sched_setaffinity(0, before)
