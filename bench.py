@@ -190,7 +190,24 @@ def main():
         from dcnn_b200.partitioner import BalancedPartitioner
         stage, rep, links, dp_g = make_pipeline_groups(S, R)
         mb = args.microbatches if args.microbatches > 1 else 2 * S
-        parts = BalancedPartitioner(input_shape=[args.batch, *IMG]).get_partitions(model.get_layers(), S)
+        if os.environ.get("BENCH_PARTITION", "flops") == "measured":
+            # balance the stages on measured per-layer GPU time of one microbatch (rank 0 measures, everyone uses its
+            # numbers) instead of on FLOP counts -- BatchNorm / pooling layers cost time, not FLOPs
+            from dcnn_b200.partitioner import measure_layer_costs
+            costs = [None]
+            if rank == 0:
+                probe = create_resnet50_tiny_imagenet()
+                probe.set_seed(42)
+                probe.set_device(dev)
+                probe.initialize()
+                costs = [measure_layer_costs(probe, [max(1, args.batch * S // mb), *IMG])]
+                del probe
+                torch.cuda.empty_cache()
+            dist.broadcast_object_list(costs, src=0)
+            partitioner = BalancedPartitioner(costs=costs[0])
+        else:
+            partitioner = BalancedPartitioner(input_shape=[args.batch, *IMG])
+        parts = partitioner.get_partitions(model.get_layers(), S)
         engine = PipelineEngine(model, parts, stage, opt, loss_fn, mb, links, dev,
                                 schedule=os.environ.get("SCHEDULE", "semi_async"), dp_group=dp_g if R > 1 else None,
                                 sync_bn=sync_bn, seed=42)

@@ -78,3 +78,46 @@ class BalancedPartitioner(Partitioner):
             parts.append(Partition(i, j))
             j = i
         return parts[::-1]
+
+
+def measure_layer_costs(model, input_shape: Sequence[int], warmup: int = 1, iters: int = 2) -> List[float]:
+    """Measured forward+backward time (ms) per top-level layer of an initialised ``model`` on its device, for
+    ``BalancedPartitioner(costs=...)``: what the reference's "load balancing (coming soon)" note asks for.
+
+    One synthetic batch of ``input_shape`` is pushed through the whole model with the Sequential's own per-unit timers
+    (CUDA events on a GPU, wall clock on the CPU).  A fusion unit (Conv -> BN -> ReLU ...) is timed as one piece; its time
+    is spread over its layers so that the partitioner sees a cost for every layer."""
+    import torch
+    was_profiling, was_training = model.is_profiling_enabled(), model.is_training()
+    model.set_training(True)
+    model.enable_profiling(True)
+    dev = model.get_device()
+    x = torch.randn(*input_shape, device=dev)
+    acc = {}
+    saved_buffers = {k: v.clone() for k, v in model.buffers().items()}   # BatchNorm running statistics
+    try:
+        for it in range(warmup + iters):
+            model.clear_profiling_data()
+            y = model.forward(x, 0)
+            model.backward(torch.ones_like(y) / max(1, y.numel()), 0)
+            if dev.type == "cuda":
+                torch.cuda.synchronize(dev)
+            if it >= warmup:
+                f, b = model.get_forward_times(), model.get_backward_times()
+                for k in set(f) | set(b):
+                    acc[k] = acc.get(k, 0.0) + (f.get(k, 0.0) + b.get(k, 0.0)) / 1000.0 / iters
+    finally:
+        model.clear_profiling_data()
+        model.enable_profiling(was_profiling)
+        model.set_training(was_training)
+        model.clear_gradients()
+        model.clear_cache()
+        for k, v in model.buffers().items():
+            v.copy_(saved_buffers[k])
+    costs = []
+    for u in model._get_units():
+        t = acc.get(u.name, 0.0)
+        costs.extend([max(t, 1e-6) / len(u.layers)] * len(u.layers))
+    if len(costs) != model.layer_size():
+        raise RuntimeError("fusion units do not cover the model's layers")
+    return costs

@@ -8,6 +8,7 @@ TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr
 echo "== allreduce roofline"; timeout 90 $TR benchmarks/allreduce_roofline.py > gpurun_out/ar_$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/ar_$N.log | cut -c1-400
 echo "== dp$N"; timeout 90 $TR bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_dp$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_dp$N.log | cut -c1-300
 echo "== pp$N"; timeout 90 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp$N --microbatches $((2*N)) > gpurun_out/bench_pp$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp$N.log | cut -c1-300
+echo "== pp$N measured partition"; BENCH_PARTITION=measured timeout 120 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp$N --microbatches $((2*N)) > gpurun_out/bench_pp${N}_measured.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp${N}_measured.log | cut -c1-300
 if [ "$N" -ge 4 ]; then
   echo "== pp2xdp$((N/2))"; timeout 90 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp2xdp$((N/2)) --microbatches 4 > gpurun_out/bench_pp2xdp.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp2xdp.log | cut -c1-300
 fi

@@ -176,3 +176,25 @@ def test_profiling_summary_and_cache_accounting(capsys):
     assert sum(l.cached_memory_bytes() for l in m.layers) == 0
     m.print_summary([4, 1, 28, 28])
     assert "Model Summary" in capsys.readouterr().out
+
+
+def test_measured_layer_costs_drive_the_balanced_partitioner():
+    import torch
+    from dcnn_b200.models import create_resnet9_cifar10
+    from dcnn_b200.partitioner import BalancedPartitioner, measure_layer_costs
+    m = create_resnet9_cifar10()
+    m.set_seed(0)
+    m.initialize()
+    before = {k: v.clone() for k, v in m.buffers().items()}
+    costs = measure_layer_costs(m, [4, 3, 32, 32], warmup=0, iters=1)
+    assert len(costs) == m.layer_size() and all(c > 0 for c in costs)
+    for k, v in m.buffers().items():
+        assert torch.equal(v, before[k])                      # running statistics untouched by the probe passes
+    assert all(float(g.abs().sum()) == 0 for g in m.gradients()) and not m.is_profiling_enabled()
+    parts = BalancedPartitioner(costs=costs).get_partitions(m.get_layers(), 3)
+    assert parts[0].start_layer == 0 and parts[-1].end_layer == m.layer_size()
+    loads = [sum(costs[p.start_layer:p.end_layer]) for p in parts]
+    # min-max optimality against brute force over all contiguous 3-way splits
+    n = len(costs)
+    best = min(max(sum(costs[:i]), sum(costs[i:j]), sum(costs[j:])) for i in range(1, n - 1) for j in range(i + 1, n))
+    assert abs(max(loads) - best) < 1e-9
