@@ -4,7 +4,6 @@ include/nn/train.hpp:108-170) on synthetic data.  See baseline/README.md for how
 import json
 import os
 import subprocess
-import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 BIN = os.path.join(HERE, "_ref", "bin", "ref_bench")

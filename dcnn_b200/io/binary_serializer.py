@@ -16,7 +16,6 @@ from __future__ import annotations
 import ctypes as C
 import struct
 import sys
-from typing import Optional
 
 import numpy as np
 import torch

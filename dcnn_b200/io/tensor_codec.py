@@ -10,7 +10,6 @@ library is present; the pure-Python path is the definition.
 from __future__ import annotations
 
 import struct
-import sys
 from typing import BinaryIO, Sequence
 
 import numpy as np

@@ -4,7 +4,6 @@ rate, epoch nor RNG state -- SURVEY §5.4).  ``save_training_state`` writes the 
 step counters, schedule position, epoch, RNG states); the reference's loader ignores the extra files."""
 from __future__ import annotations
 
-import os
 from typing import Optional
 
 import torch

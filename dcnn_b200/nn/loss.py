@@ -7,7 +7,6 @@ the scalars on the device (no host synchronisation per call, unlike loss_ops.cu:
 API and synchronise only when the Python float is requested."""
 from __future__ import annotations
 
-from typing import Optional, Tuple
 
 import torch
 

@@ -6,8 +6,7 @@ per parameter tensor) and can zero the gradients in the same pass (``update(zero
 Optimizer state can be exported/imported (``state_dict``) -- the reference never serialises it."""
 from __future__ import annotations
 
-import math
-from typing import Dict, List, Optional, Sequence
+from typing import List, Sequence
 
 import torch
 

@@ -5,7 +5,7 @@ so Python is the right level -- there is nothing to put on the GPU."""
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Optional, Sequence
 
 
 class Scheduler:

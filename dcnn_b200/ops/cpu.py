@@ -9,8 +9,6 @@ All activation tensors are logical ``[N, C, H, W]``.
 """
 from __future__ import annotations
 
-import math
-from typing import Optional, Tuple
 
 import torch
 import torch.nn.functional as F

@@ -8,7 +8,6 @@ everything else takes the exact-FP32 CUDA-core kernels.  ``DCNN_DISABLE_TC=1`` f
 "FP32-exact mode" for bit-tight tests)."""
 from __future__ import annotations
 
-import ctypes as C
 import os
 from typing import Optional
 

@@ -7,7 +7,7 @@ implicit GEMM, padding by TMA out-of-bounds fill, residual adds / ReLU by conv a
 ``gemm`` routes to the tcgen05 kernels when the operands qualify."""
 from __future__ import annotations
 
-from typing import List, Sequence
+from typing import List
 
 import torch
 import torch.nn.functional as F

@@ -14,7 +14,6 @@ transfers and discards it); timeouts raise ``PipelineTimeout`` (fail-fast) inste
 on with a hung pipeline (coordinator.hpp:180-183)."""
 from __future__ import annotations
 
-import threading
 import time
 from typing import List, Optional, Sequence
 

@@ -6,7 +6,7 @@ activations/gradients use an NCCL group over the stage ranks (p2p over NVLink 5)
 from __future__ import annotations
 
 import os
-from typing import Optional, Sequence, Tuple
+from typing import Optional, Sequence
 
 import torch
 import torch.distributed as dist

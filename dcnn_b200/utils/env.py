@@ -6,7 +6,7 @@ from __future__ import annotations
 
 import os
 import sys
-from typing import Any, Dict, TypeVar
+from typing import Dict, TypeVar
 
 T = TypeVar("T")
 _loaded: Dict[str, str] = {}

@@ -14,7 +14,6 @@ os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")   # stage workers must not
 
 import torch
 
-from _common import get_env
 
 from dcnn_b200.parallel.pipeline import DistributedCoordinator, InProcessCoordinator, NetworkStageWorker
 from dcnn_b200.parallel.pipeline.launch import init_distributed, pipeline_groups

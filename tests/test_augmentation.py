@@ -1,9 +1,6 @@
 """Augmentation tests: native (libdcnn_host.so) vs torch implementations agree given the same seed; semantics
 match the reference formulas (rotation bilinear + zero fill, crop = zero-pad + window, clamp to [0,1])."""
-import copy
-import math
 
-import numpy as np
 import pytest
 import torch
 

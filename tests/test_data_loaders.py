@@ -1,6 +1,5 @@
 """Loader tests on generated fixture files in the reference's on-disk formats (the reference only tests its
 Tiny-ImageNet loader and needs the real dataset for it)."""
-import os
 
 import numpy as np
 import pytest

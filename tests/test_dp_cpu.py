@@ -3,7 +3,6 @@ exactly the same optimisation step as one process on the concatenated batch (SUR
 import os
 import socket
 
-import pytest
 import torch
 import torch.distributed as dist
 from dcnn_b200.utils.spawn import spawn_bounded

@@ -9,7 +9,6 @@ import os
 import pytest
 import torch
 
-import dcnn_b200 as dc
 from dcnn_b200 import nn as dnn
 from dcnn_b200.nn.blocks import ResidualBlock
 

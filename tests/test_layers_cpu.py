@@ -8,7 +8,7 @@ import torch.nn.functional as F
 
 import dcnn_b200 as dc
 from dcnn_b200 import nn as dnn
-from dcnn_b200.models import MODEL_ZOO, create_mnist_trainer, create_resnet9_cifar10, create_resnet50_tiny_imagenet
+from dcnn_b200.models import MODEL_ZOO, create_mnist_trainer, create_resnet9_cifar10
 
 torch.manual_seed(0)
 

@@ -7,9 +7,8 @@ import torch
 import torch.distributed as dist
 from dcnn_b200.utils.spawn import spawn_bounded
 
-import dcnn_b200 as dc
 from dcnn_b200 import nn as dnn
-from dcnn_b200.train import TrainStep, split_microbatches
+from dcnn_b200.train import split_microbatches
 from tests.test_pipeline_inprocess import _data, _model, _reference_run
 
 

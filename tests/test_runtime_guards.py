@@ -7,8 +7,6 @@ import sys
 import textwrap
 import time
 
-import torch
-import torch.nn.functional as F
 
 from dcnn_b200.utils import runtime
 
