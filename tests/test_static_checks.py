@@ -1,0 +1,17 @@
+"""Static hygiene: no unused imports / duplicate definitions / undefined names anywhere in the Python tree -- the
+undefined-name pass matters for CUDA-only branches that the CPU suite cannot execute."""
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_no_unused_imports_or_redefinitions():
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "lint_unused.py")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
+
+
+def test_no_undefined_names():
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "lint_undefined.py")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
