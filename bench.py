@@ -271,6 +271,9 @@ def main():
     launches = _lib.launch_count()
     if step._graph is not None:   # replayed graph: count the kernels captured in one step
         launches = step_launches(step, dev_x[0], dev_t[0], _lib) * args.steps
+    elif engine is not None and getattr(engine, "_graphs", None) is not None:
+        # pipeline graph mode: the per-op graphs' kernels (counted at capture) + what still runs eagerly each step
+        launches += engine.graph_launches * args.steps
     final_loss = float(loss) if loss is not None else float('nan')
     stage_stats = engine.stats() if engine is not None else None
 
@@ -331,7 +334,9 @@ def main():
             "config": {"model": MODEL, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
                        "image": "3x64x64", "classes": CLASSES, "parallelism": parallelism,
                        "optimizer": "Adam(lr 1e-4, eps 1e-3, wd 1e-3)", "loss": "LogSoftmaxCrossEntropy",
-                       "cuda_graph": step._graph is not None, "microbatches": args.microbatches,
+                       "cuda_graph": (step._graph is not None) or
+                                     (engine is not None and getattr(engine, "_graphs", None) is not None),
+                       "microbatches": args.microbatches,
                        "pipeline_stages": S, "dp_replicas": R, "sync_bn": sync_bn and R > 1,
                        "pipeline_bubble_fraction": bubble,
                        "l2": "per-step working set (activations, >10 GB at batch 256) is far larger than the 126 MB L2; "

@@ -88,6 +88,12 @@ class PipelineEngine:
         self._pending_sends = []
         self.last_stats = {}
         self._kernels_warm = False
+        # DCNN_PIPE_GRAPH=1 (CUDA only): after two eager steps every (op, microbatch) of this stage's schedule is
+        # captured as its own CUDA graph and replayed from then on; transfers stay outside the graphs.  Opt-in until its
+        # first hardware run.
+        self.use_graphs = self.device.type == "cuda" and _os.environ.get("DCNN_PIPE_GRAPH", "0") == "1"
+        self._graphs = None
+        self._steps = 0
         self._warm_links()
 
     # -- start-up hygiene ------------------------------------------------------------------------------------
@@ -194,6 +200,12 @@ class PipelineEngine:
 
         self._warm_kernels(in_shapes[0], list(ts[0].shape) if self.is_last else None)
         sched = self.schedule
+        if self.use_graphs:
+            self._steps += 1
+            if self._graphs is None and self._steps > 2:       # every rank reaches this on the same step
+                self._capture_graphs(in_shapes, out_shapes, [list(t.shape) for t in ts] if self.is_last else None)
+            if self._graphs is not None:
+                return self._train_step_graphs(xs, ts, in_shapes, out_shapes)
         recv_slot = {}
 
         def post_recv(k):
@@ -262,6 +274,95 @@ class PipelineEngine:
             self.last_stats = {"busy_ms": sum(busy) * 1000, "step_ms": (time.perf_counter() - t_begin) * 1000}
         if self.is_last and loss_acc is not None and M > 1:
             loss_acc = loss_acc / M
+        return loss_acc, correct_acc
+
+    # -- CUDA-graph mode ---------------------------------------------------------------------------------------
+    def _capture_graphs(self, in_shapes, out_shapes, target_shapes):
+        """One CUDA graph per schedule entry, captured in schedule order into one memory pool (graphs that share a pool
+        must be replayed in capture order, which is the schedule order).  Inputs live in static buffers: the activation
+        / gradient a transfer delivers, the first stage's microbatch, the last stage's targets.  Nothing executes and
+        nothing is communicated during capture; the calling step is then run through the replay path."""
+        torch.cuda.synchronize(self.device)
+        M = self.M
+        st = {"in": [self._alloc(in_shapes[m]) for m in range(M)],
+              "gin": [self._alloc(out_shapes[m]) if not self.is_last else None for m in range(M)],
+              "t": [torch.zeros(target_shapes[m], device=self.device) for m in range(M)] if self.is_last else None,
+              "y": {}, "dx": {}, "g": {}, "loss": {}, "correct": {}, "graph": {}}
+        if self.is_last:
+            for t in st["t"]:
+                t.view(t.shape[0], -1)[:, 0] = 1          # a valid one-hot target while capturing
+        pool = torch.cuda.graph_pool_handle()
+        from ... import _lib
+        launches_before = _lib.launch_count()
+        for (op, mb) in self.schedule:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, pool=pool):
+                if op == "F":
+                    y = self.model.forward(st["in"][mb][1], mb)
+                    st["y"][mb] = y
+                    if self.is_last:
+                        loss, gr, correct = self.loss_fn.forward_backward(y, st["t"][mb])
+                        st["loss"][mb], st["g"][mb], st["correct"][mb] = loss, gr, correct
+                else:
+                    gin = st["g"][mb] if self.is_last else st["gin"][mb][1]
+                    st["dx"][mb] = self.model.backward(gin, mb)
+            st["graph"][(op, mb)] = g
+        torch.cuda.synchronize(self.device)
+        self.graph_launches = _lib.launch_count() - launches_before    # kernels one replayed step runs from the graphs
+        self._graphs = st
+
+    def _train_step_graphs(self, xs, ts, in_shapes, out_shapes):
+        st, sched, M = self._graphs, self.schedule, self.M
+        recv_slot = {}
+
+        def post_recv(k):
+            if k >= len(sched):
+                return
+            op, mb = sched[k]
+            if op == "F" and not self.is_first:
+                recv_slot[k] = dist.irecv(st["in"][mb][0], src=self.prev_rank, group=self.g_recv_act)
+            elif op == "B" and not self.is_last:
+                recv_slot[k] = dist.irecv(st["gin"][mb][0], src=self.next_rank, group=self.g_recv_grad)
+
+        busy = []
+        ev_begin = torch.cuda.Event(enable_timing=True)
+        ev_begin.record()
+        post_recv(0)
+        for k, (op, mb) in enumerate(sched):
+            post_recv(k + 1)
+            if k in recv_slot:
+                recv_slot.pop(k).wait()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if op == "F":
+                if self.is_first:
+                    st["in"][mb][1].copy_(xs[mb], non_blocking=True)
+                if self.is_last:
+                    st["t"][mb].copy_(ts[mb], non_blocking=True)
+                st["graph"][(op, mb)].replay()
+                if not self.is_last:
+                    self._isend(st["y"][mb], self.next_rank, self.g_send_act)
+            else:
+                st["graph"][(op, mb)].replay()
+                if not self.is_first:
+                    self._isend(st["dx"][mb], self.prev_rank, self.g_send_grad)
+            e1.record()
+            busy.append((e0, e1))
+        if self.dp is not None:
+            self.dp.reduce_and_update(self.optimizer)
+        else:
+            self.optimizer.update(zero_grads=True)
+        for w, _ in self._pending_sends:       # the static output buffers are rewritten by the next step's replays
+            w.wait()
+        self._pending_sends = []
+        ev_end = torch.cuda.Event(enable_timing=True)
+        ev_end.record()
+        self._events = (ev_begin, ev_end, busy)
+        loss_acc = correct_acc = None
+        if self.is_last:
+            loss_acc = torch.stack([st["loss"][m] for m in range(M)]).sum() / M
+            if all(st["correct"][m] is not None for m in range(M)):
+                correct_acc = torch.stack([st["correct"][m] for m in range(M)]).sum()
         return loss_acc, correct_acc
 
     def stats(self):

@@ -19,3 +19,4 @@ SYNTHETIC=1 DEVICE_TYPE=GPU EPOCHS=1 BATCH_SIZE=128 NUM_MICROBATCHES=4 SYNTHETIC
   CUDA_MODULE_LOADING=EAGER STEP_TIMEOUT_S=60 timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N \
   --master-addr 127.0.0.1 --master-port 29544 examples/semi_async_pipeline_coordinator.py > gpurun_out/msg_pipeline_$N.log 2>&1
 echo "exit $?"; grep -E "Epoch|Validation|Stopped|images|Error|error" gpurun_out/msg_pipeline_$N.log | tail -8 | cut -c1-200
+echo "== pp$N with per-op CUDA graphs"; DCNN_PIPE_GRAPH=1 timeout 120 $TR bench.py --gpus $N --steps 10 --warmup 4 --parallelism pp$N --microbatches $((2*N)) > gpurun_out/bench_pp${N}_graph.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp${N}_graph.log | cut -c1-300
