@@ -39,6 +39,20 @@ class BaseDataLoader:
         self.batched_data: List[torch.Tensor] = []
         self.batched_labels: List[torch.Tensor] = []
         self._order: Optional[np.ndarray] = None
+        self._shard: Optional[Tuple[int, int]] = None
+
+    def set_shard(self, rank: int, world: int):
+        """Data-parallel sharding: this loader serves samples ``rank, rank + world, ...`` of the (shuffled) order,
+        truncated so that every replica sees the same number of samples (collectives need equal step counts).  All
+        replicas must use the same seed (``set_seed``) so that they shuffle identically."""
+        if not 0 <= int(rank) < int(world):
+            raise ValueError(f"shard rank {rank} out of range for world size {world}")
+        self._shard = (int(rank), int(world)) if int(world) > 1 else None
+        self.batches_prepared = False
+        self.current_index = self.current_batch_index = 0
+
+    def shard_size(self) -> int:
+        return self.size() // self._shard[1] if self._shard else self.size()
 
     # -- interface (ref data_loader.hpp:25-187) ----------------------------------------------------------
     def load_data(self, source: str) -> bool:
@@ -76,6 +90,9 @@ class BaseDataLoader:
     def _indices(self) -> np.ndarray:
         if self._order is None or len(self._order) != self.size():
             self._order = np.arange(self.size())
+        if self._shard is not None:
+            r, w = self._shard
+            return self._order[r::w][:self.size() // w]
         return self._order
 
     def prepare_batches(self, batch_size: int):

@@ -240,11 +240,39 @@ def validate_class_model(model, test_loader, loss_function):
     return float(val_loss) / max(1, batches), float(val_corrects) / max(1, samples)
 
 
+def _mean_over_replicas(values, group, device):
+    """Average a list of Python floats over the replicas of ``group`` (one small all-reduce)."""
+    import torch.distributed as dist
+    t = torch.tensor(values, dtype=torch.float64, device=device if device.type == "cuda" else "cpu")
+    dist.all_reduce(t, group=group)
+    return (t / dist.get_world_size(group)).tolist()
+
+
 def train_classification_model(model, train_loader, test_loader, optimizer, loss_function,
-                               config: Optional[TrainingConfig] = None):
+                               config: Optional[TrainingConfig] = None, data_parallel=None):
+    """``data_parallel``: a :class:`dcnn_b200.parallel.dp.DataParallel` built on this model/optimizer (one process per
+    replica).  Every replica then trains on its shard of the data (``config.batch_size`` is the per-replica batch), the
+    reported losses / accuracies are averages over replicas, and only replica 0 prints and writes snapshots.  The
+    reference has no data parallelism; without ``data_parallel`` this is the reference's loop."""
     config = config or TrainingConfig()
     model.compute_input_gradient = False
-    optimizer.attach(model.parameters(), model.gradients())
+    dp = data_parallel
+    main = dp is None or dp.rank == 0
+    if dp is None:
+        optimizer.attach(model.parameters(), model.gradients())
+    else:
+        for ld in (train_loader, test_loader):
+            ld.set_seed(1234)                 # identical shuffles on every replica, disjoint shards
+            ld.set_shard(dp.rank, dp.world)
+    if not main:
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):      # replicas other than 0 stay quiet
+            return _train_classification(model, train_loader, test_loader, optimizer, loss_function, config, dp, main)
+    return _train_classification(model, train_loader, test_loader, optimizer, loss_function, config, dp, main)
+
+
+def _train_classification(model, train_loader, test_loader, optimizer, loss_function, config, dp, main):
     train_loader.prepare_batches(config.batch_size)
     test_loader.prepare_batches(config.batch_size)
     model.enable_profiling(config.profiler_type in ("NORMAL", "CUMULATIVE"))
@@ -254,7 +282,7 @@ def train_classification_model(model, train_loader, test_loader, optimizer, loss
     model.print_summary([config.batch_size, c, h, w])
     if config.device_type == "CPU":
         torch.set_num_threads(max(1, config.num_threads))
-    step = TrainStep(model, optimizer, loss_function, config.use_cuda_graph)
+    step = TrainStep(model, optimizer, loss_function, config.use_cuda_graph, data_parallel=dp)
     best_val_accuracy = 0.0
     history = []
     metrics = metrics_from_env()
@@ -262,12 +290,12 @@ def train_classification_model(model, train_loader, test_loader, optimizer, loss
     ckpt = os.path.join(config.snapshot_dir, model.name() + ".interrupted")
     with watchdog_from_env("train step") as wd, checkpoint_on_signal(ckpt, model, optimizer, lambda: epoch_box[0]):
         history = _classification_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step,
-                                         metrics, wd, epoch_box)
+                                         metrics, wd, epoch_box, dp, main)
     return history
 
 
 def _classification_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step, metrics, wd,
-                           epoch_box):
+                           epoch_box, dp=None, main=True):
     best_val_accuracy = 0.0
     history = []
     for epoch in range(config.epochs):
@@ -279,7 +307,11 @@ def _classification_epochs(model, train_loader, test_loader, optimizer, loss_fun
             torch.cuda.synchronize()
         train_ms = (time.perf_counter() - t0) * 1000
         vl, va = validate_class_model(model, test_loader, loss_function)
-        if va > best_val_accuracy:
+        if dp is not None:      # equal shard sizes: the mean of the replicas' means is the global mean
+            tl, ta, vl, va = _mean_over_replicas([tl, ta, vl, va], dp.group, model.get_device())
+        if va > best_val_accuracy and not main:
+            best_val_accuracy = va
+        elif va > best_val_accuracy:
             best_val_accuracy = va
             print(f"New best validation accuracy: {best_val_accuracy * 100:.2f}%")
             try:
@@ -295,7 +327,7 @@ def _classification_epochs(model, train_loader, test_loader, optimizer, loss_fun
         print("=" * 60)
         history.append({"epoch": epoch + 1, "train_loss": tl, "train_acc": ta, "val_loss": vl, "val_acc": va,
                         "train_ms": train_ms})
-        n_img = train_loader.num_batches() * config.batch_size
+        n_img = train_loader.num_batches() * config.batch_size * (dp.world if dp is not None else 1)
         metrics.log(kind="epoch", images_per_s=n_img / max(train_ms, 1e-9) * 1000.0, rss_kb=get_memory_usage_kb(),
                     lr=optimizer.get_learning_rate(), **history[-1])
         wd.kick()

@@ -135,3 +135,32 @@ def test_synthetic_loader_is_deterministic():
     b.prepare_batches(32)
     (d1, l1), (d2, l2) = a.get_next_batch(), b.get_next_batch()
     assert torch.equal(d1, d2) and torch.equal(l1, l2) and l1.shape == (32, 200, 1, 1)
+
+
+def test_shards_are_disjoint_equal_and_cover_the_data():
+    import numpy as np
+    from dcnn_b200.data import SyntheticDataLoader
+    world, n = 3, 50
+    seen, sizes = [], []
+    for r in range(world):
+        ld = SyntheticDataLoader(n, (1, 4, 4), 5, seed=0)
+        ld.set_seed(99)                      # same seed on every replica -> same permutation
+        ld.shuffle()
+        ld.set_shard(r, world)
+        assert ld.shard_size() == n // world
+        idx = ld._indices()
+        sizes.append(len(idx))
+        seen.append(set(int(i) for i in idx))
+        ld.prepare_batches(4)
+        assert ld.num_batches() == -(-(n // world) // 4)
+        total = sum(b[0].shape[0] for b in ld)
+        assert total == n // world
+    assert len(set(sizes)) == 1                                   # equal step counts on every replica
+    assert all(not (a & b) for i, a in enumerate(seen) for b in seen[i + 1:])
+    assert len(set().union(*seen)) == (n // world) * world        # all but the n % world remainder
+    ld.set_shard(0, 1)                                            # world 1: sharding off
+    assert len(ld._indices()) == n
+    import pytest
+    with pytest.raises(ValueError):
+        ld.set_shard(3, 3)
+    assert isinstance(np.asarray(ld._indices()), np.ndarray)

@@ -52,3 +52,13 @@ def test_flag_overrides_reach_an_example(tmp_path):
     out = _run([sys.executable, os.path.join(ROOT, "examples", "mnist_cnn_trainer.py"), "--epochs", "2",
                 "--batch-size=4"], cwd=str(tmp_path))
     assert "Epoch 2/2" in out
+
+
+def test_data_parallel_trainer_two_replicas(tmp_path):
+    out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                "--master-addr", "127.0.0.1", "--master-port", "29643",
+                os.path.join(ROOT, "examples", "data_parallel_trainer.py"), "--model", "mnist_cnn"],
+               cwd=str(tmp_path), timeout=900, EPOCHS="2", SYNTHETIC_TRAIN_SAMPLES="64", SYNTHETIC_TEST_SAMPLES="32")
+    assert "Data parallel: 2 replica(s), per-replica batch 8, global batch 16" in out
+    assert out.count("Validation - Loss") == 2          # replica 0 only
+    assert "Training batches: 4" in out and "Final: train loss" in out
