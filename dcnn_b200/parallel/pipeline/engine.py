@@ -276,6 +276,49 @@ class PipelineEngine:
             loss_acc = loss_acc / M
         return loss_acc, correct_acc
 
+    # -- forward-only pass (validation) ------------------------------------------------------------------------
+    def eval_step(self, x: Optional[torch.Tensor] = None, targets: Optional[torch.Tensor] = None):
+        """Forward the batch through the pipeline in evaluation mode (BatchNorm running statistics, no dropout), loss and
+        correct count on the last stage.  Returns (mean loss | None, correct count | None) like ``train_step``."""
+        M = self.M
+        xs = split_microbatches(x.to(self.device, non_blocking=True), M) if self.is_first else None
+        ts = split_microbatches(targets.to(self.device, non_blocking=True), M) if self.is_last else None
+        meta = None
+        if self.is_first:
+            shapes = [list(t.shape) for t in xs]
+            meta = torch.tensor([s[0] for s in shapes] + list(shapes[0][1:]), dtype=torch.int64)
+        mb_batch, sample_shape = self._microbatch_layout(meta, M)
+        in_shapes = [self._boundary_shapes([b] + sample_shape)[0] for b in mb_batch]
+        self._warm_kernels(in_shapes[0], list(ts[0].shape) if self.is_last else None)
+        was_training = self.model.is_training()
+        self.model.set_training(False)
+        loss_acc = correct_acc = None
+        try:
+            nxt = self._irecv(in_shapes[0], self.prev_rank, self.g_recv_act) if not self.is_first else None
+            for mb in range(len(mb_batch)):
+                cur = nxt
+                if not self.is_first and mb + 1 < len(mb_batch):
+                    nxt = self._irecv(in_shapes[mb + 1], self.prev_rank, self.g_recv_act)
+                if cur is not None:
+                    cur[0].wait()
+                y = self.model.forward(xs[mb] if self.is_first else cur[1], mb)
+                if self.is_last:
+                    loss, _, correct = self.loss_fn.forward_backward(y, ts[mb], want_grad=False)
+                    loss_acc = loss if loss_acc is None else loss_acc + loss
+                    if correct is not None:
+                        correct_acc = correct if correct_acc is None else correct_acc + correct
+                else:
+                    self._isend(y, self.next_rank, self.g_send_act)
+            for w, _ in self._pending_sends:
+                w.wait()
+            self._pending_sends = []
+        finally:
+            self.model.set_training(was_training)
+            self.model.clear_cache()
+        if self.is_last and loss_acc is not None:
+            loss_acc = loss_acc / len(mb_batch)
+        return loss_acc, correct_acc
+
     # -- CUDA-graph mode ---------------------------------------------------------------------------------------
     def _capture_graphs(self, in_shapes, out_shapes, target_shapes):
         """One CUDA graph per schedule entry, captured in schedule order into one memory pool (graphs that share a pool

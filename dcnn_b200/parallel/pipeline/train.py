@@ -107,3 +107,62 @@ def train_model(coordinator: Coordinator, train_loader, test_loader, config: Opt
         history.append({"epoch": epoch + 1, "loss": loss, "accuracy": acc})
         train_loader.prepare_batches(config.batch_size)
     return history
+
+
+# ------------------------------------------------------------------------------------------------ SPMD engine driver
+def train_engine_model(engine, train_loader, test_loader, config: Optional[TrainingConfig] = None, replica: int = 0,
+                       num_replicas: int = 1, snapshot: bool = False):
+    """Epoch loop for the SPMD :class:`PipelineEngine` (one process per stage x replica, ``torchrun``).
+
+    Every rank iterates the same batches as the other stages of its replica (same seed; replicas take disjoint shards):
+    the first stage uses the images, the last stage the labels.  Loss / accuracy live on the last stages; one small
+    all-reduce over the whole job per epoch turns them into global means that every rank returns.  Rank 0 prints."""
+    import torch
+    import torch.distributed as dist
+    config = config or TrainingConfig()
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    say = print if rank == 0 else (lambda *a, **k: None)
+    for ld in (train_loader, test_loader):
+        ld.set_seed(1234)
+        ld.set_shard(replica, num_replicas)
+        ld.prepare_batches(config.batch_size)
+    dev = engine.device
+    red_dev = dev if dev.type == "cuda" else torch.device("cpu")
+
+    def run(loader, step_fn):
+        loader.reset()
+        acc = torch.zeros(4, dtype=torch.float64, device=red_dev)       # loss sum, correct, samples, batches
+        for data, labels in loader:
+            loss, correct = step_fn(data, labels)
+            if engine.is_last:
+                acc[0] += loss.double().to(red_dev)
+                if correct is not None:
+                    acc[1] += correct.double().to(red_dev)
+                acc[2] += data.shape[0]
+                acc[3] += 1
+        if dist.is_initialized():
+            dist.all_reduce(acc)
+        return float(acc[0] / acc[3].clamp(min=1)), float(acc[1] / acc[2].clamp(min=1))
+
+    history = []
+    for epoch in range(config.epochs):
+        say(f"Epoch {epoch + 1}/{config.epochs}")
+        t0 = time.perf_counter()
+        train_loader.shuffle()
+        tl, ta = run(train_loader, engine.train_step)
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+        train_ms = (time.perf_counter() - t0) * 1000
+        vl, va = run(test_loader, engine.eval_step)
+        say("-" * 60)
+        say(f"Epoch {epoch + 1}/{config.epochs} completed in {train_ms:.0f}ms")
+        say(f"Training   - Loss: {tl:.4f}, Accuracy: {ta * 100:.2f}%")
+        say(f"Validation - Loss: {vl:.4f}, Accuracy: {va * 100:.2f}%")
+        say("=" * 60)
+        history.append({"epoch": epoch + 1, "train_loss": tl, "train_acc": ta, "val_loss": vl, "val_acc": va,
+                        "train_ms": train_ms})
+        if (epoch + 1) % config.lr_decay_interval == 0:
+            cur = engine.optimizer.get_learning_rate()
+            engine.optimizer.set_learning_rate(cur * config.lr_decay_factor)
+        train_loader.prepare_batches(config.batch_size)      # re-apply augmentation, like the single-device loop
+    return history

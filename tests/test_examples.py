@@ -62,3 +62,17 @@ def test_data_parallel_trainer_two_replicas(tmp_path):
     assert "Data parallel: 2 replica(s), per-replica batch 8, global batch 16" in out
     assert out.count("Validation - Loss") == 2          # replica 0 only
     assert "Training batches: 4" in out and "Final: train loss" in out
+
+
+@pytest.mark.parametrize("procs,stages", [(2, 2), (4, 2)])
+def test_spmd_pipeline_trainer(tmp_path, procs, stages):
+    out = _run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(procs),
+                "--master-addr", "127.0.0.1", "--master-port", str(29650 + procs),
+                os.path.join(ROOT, "examples", "spmd_pipeline_trainer.py"), "--model", "mnist_cnn",
+                "--num-stages", str(stages)], cwd=str(tmp_path), timeout=900, EPOCHS="2",
+               SYNTHETIC_TRAIN_SAMPLES="64", SYNTHETIC_TEST_SAMPLES="32", NUM_THREADS="1")
+    assert f"Pipeline: {stages} stage(s) x {procs // stages} replica(s)" in out
+    assert out.count("Validation - Loss") == 2 and "Final: train loss" in out
+    # training loss decreases from epoch 1 to epoch 2 on the 64 synthetic samples
+    losses = [float(l.split("Loss:")[1].split(",")[0]) for l in out.splitlines() if l.startswith("Training   - Loss")]
+    assert len(losses) == 2 and losses[1] < losses[0]
