@@ -20,3 +20,7 @@ SYNTHETIC=1 DEVICE_TYPE=GPU EPOCHS=1 BATCH_SIZE=128 NUM_MICROBATCHES=4 SYNTHETIC
   --master-addr 127.0.0.1 --master-port 29544 examples/semi_async_pipeline_coordinator.py > gpurun_out/msg_pipeline_$N.log 2>&1
 echo "exit $?"; grep -E "Epoch|Validation|Stopped|images|Error|error" gpurun_out/msg_pipeline_$N.log | tail -8 | cut -c1-200
 echo "== pp$N with per-op CUDA graphs"; DCNN_PIPE_GRAPH=1 timeout 120 $TR bench.py --gpus $N --steps 10 --warmup 4 --parallelism pp$N --microbatches $((2*N)) > gpurun_out/bench_pp${N}_graph.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp${N}_graph.log | cut -c1-300
+# public training loops on GPUs (synthetic data): data-parallel trainer and SPMD pipeline trainer
+COMMON="SYNTHETIC=1 DEVICE_TYPE=GPU EPOCHS=1 BATCH_SIZE=128 SYNTHETIC_TRAIN_SAMPLES=$((1024*N)) SYNTHETIC_TEST_SAMPLES=$((256*N)) PROGRESS_PRINT_INTERVAL=1000 STEP_TIMEOUT_S=60"
+echo "== data_parallel_trainer x$N"; env $COMMON timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29555 examples/data_parallel_trainer.py --model resnet50_tiny_imagenet > gpurun_out/dp_trainer_$N.log 2>&1; echo "exit $?"; grep -E "Data parallel|Training   -|Validation -|Final|Error" gpurun_out/dp_trainer_$N.log | tail -5 | cut -c1-200
+echo "== spmd_pipeline_trainer pp$N"; env $COMMON NUM_MICROBATCHES=4 timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29556 examples/spmd_pipeline_trainer.py --model resnet50_tiny_imagenet --num-stages $N > gpurun_out/spmd_trainer_$N.log 2>&1; echo "exit $?"; grep -E "Pipeline:|Training   -|Validation -|Final|Error" gpurun_out/spmd_trainer_$N.log | tail -5 | cut -c1-200
