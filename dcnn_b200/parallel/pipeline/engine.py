@@ -276,6 +276,34 @@ class PipelineEngine:
             loss_acc = loss_acc / M
         return loss_acc, correct_acc
 
+    # -- checkpoint of a pipelined run ---------------------------------------------------------------------------
+    def gather_full_model(self, dst_stage: int = 0) -> Optional[Sequential]:
+        """Collective over the stages of this replica: returns, on stage ``dst_stage``, a CPU :class:`Sequential` with
+        the whole model's structure and the parameters / BatchNorm statistics currently held by the stages (None on the
+        other stages).  ``model.save_to_file(path)`` on it writes the reference-compatible ``.json`` + ``.bin`` -- the
+        reference itself can never gather weights trained through its pipeline."""
+        mine = {"stage": self.stage,
+                "params": [p.detach().to("cpu").contiguous() for p in self.model.parameters()],
+                "buffers": [v.detach().to("cpu") for v in self.model.buffers().values()]}
+        if self.S == 1:
+            shards = [mine]
+        else:
+            shards = [None] * self.S
+            dist.all_gather_object(shards, mine, group=self.links.ctl)
+        if self.stage != dst_stage:
+            return None
+        full = Sequential.load_from_config(self.full_model.get_config())
+        full.initialize()
+        shards.sort(key=lambda d: d["stage"])
+        full.load_parameters([p for d in shards for p in d["params"]])
+        bufs = [b for d in shards for b in d["buffers"]]
+        own = list(full.buffers().values())
+        if len(own) != len(bufs):
+            raise RuntimeError("buffer count mismatch while gathering the pipelined model")
+        for dst, src in zip(own, bufs):
+            dst.copy_(src)
+        return full
+
     # -- forward-only pass (validation) ------------------------------------------------------------------------
     def eval_step(self, x: Optional[torch.Tensor] = None, targets: Optional[torch.Tensor] = None):
         """Forward the batch through the pipeline in evaluation mode (BatchNorm running statistics, no dropout), loss and

@@ -145,6 +145,7 @@ def train_engine_model(engine, train_loader, test_loader, config: Optional[Train
         return float(acc[0] / acc[3].clamp(min=1)), float(acc[1] / acc[2].clamp(min=1))
 
     history = []
+    best_val_accuracy = 0.0
     for epoch in range(config.epochs):
         say(f"Epoch {epoch + 1}/{config.epochs}")
         t0 = time.perf_counter()
@@ -161,6 +162,16 @@ def train_engine_model(engine, train_loader, test_loader, config: Optional[Train
         say("=" * 60)
         history.append({"epoch": epoch + 1, "train_loss": tl, "train_acc": ta, "val_loss": vl, "val_acc": va,
                         "train_ms": train_ms})
+        if snapshot and va > best_val_accuracy:
+            # every stage takes part in the gather; replica 0's first stage writes <snapshot_dir>/<model name>.json/.bin
+            # (+ .state.* with the BatchNorm statistics) -- loadable by Sequential.from_file and by the reference
+            full = engine.gather_full_model(0)
+            if full is not None and replica == 0:
+                import os
+                path = os.path.join(config.snapshot_dir, engine.full_model.name())
+                full.save_to_file(path, save_state=True)
+                say(f"New best validation accuracy: {va * 100:.2f}% -- model saved to {path}")
+        best_val_accuracy = max(best_val_accuracy, va)
         if (epoch + 1) % config.lr_decay_interval == 0:
             cur = engine.optimizer.get_learning_rate()
             engine.optimizer.set_learning_rate(cur * config.lr_decay_factor)

@@ -67,7 +67,7 @@ def main():
     engine = PipelineEngine(model, parts, stage, optimizer, nn.LossFactory.create_logsoftmax_crossentropy(),
                             cfg.num_microbatches, links, torch.device("cuda", local) if gpu else torch.device("cpu"),
                             schedule=get_env("SCHEDULE", "semi_async"), dp_group=dp_group if R > 1 else None, seed=42)
-    history = train_engine_model(engine, train_loader, test_loader, cfg, replica, R)
+    history = train_engine_model(engine, train_loader, test_loader, cfg, replica, R, snapshot=get_env("SNAPSHOT", True))
     if rank == 0 and history:
         print(f"Final: train loss {history[-1]['train_loss']:.4f}, validation accuracy {history[-1]['val_acc'] * 100:.2f}%")
     dist.barrier()

@@ -76,3 +76,6 @@ def test_spmd_pipeline_trainer(tmp_path, procs, stages):
     # training loss decreases from epoch 1 to epoch 2 on the 64 synthetic samples
     losses = [float(l.split("Loss:")[1].split(",")[0]) for l in out.splitlines() if l.startswith("Training   - Loss")]
     assert len(losses) == 2 and losses[1] < losses[0]
+    if "model saved to" in out:          # written whenever validation accuracy improved on 0
+        assert os.path.exists(tmp_path / "model_snapshots" / "mnist_cnn_model.bin")
+        assert os.path.exists(tmp_path / "model_snapshots" / "mnist_cnn_model.state.bin")

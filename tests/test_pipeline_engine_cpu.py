@@ -118,3 +118,45 @@ def _reference_dp(stages, micro, reps, steps):
             seq.backward(gs[m], m)
         opt.update(zero_grads=True)
     return seq, losses
+
+
+def _proc_eval_gather(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from dcnn_b200.parallel.pipeline import PipelineEngine, make_pipeline_groups
+    stage, rep, links, dpg = make_pipeline_groups(world, 1)
+    full = _model()
+    parts = NaivePartitioner().get_partitions(full.get_layers(), world)
+    eng = PipelineEngine(full, parts, stage, dnn.SGD(0.05, 0.9), dnn.SoftmaxCrossEntropyLoss(), 2, links, "cpu", seed=77)
+    x, t = _data(8)
+    for _ in range(2):
+        eng.train_step(x, t)
+    ev = eng.eval_step(x, t)
+    again = eng.eval_step(x, t)                          # evaluation must not change any state
+    gathered = eng.gather_full_model(0)
+    if rank == 0:
+        gathered.save_to_file(out + "_model", save_state=True)     # + BatchNorm running statistics sidecar
+    if eng.is_last:
+        torch.save({"loss": float(ev[0]), "correct": float(ev[1]), "loss2": float(again[0])}, out + "_eval.pt")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_eval_step_and_gathered_checkpoint_match_single_device(tmp_path):
+    import dcnn_b200 as dc
+    out = str(tmp_path / "eg")
+    spawn_bounded(_proc_eval_gather, args=(2, _free_port(), out), nprocs=2, timeout_s=300)
+    ev = torch.load(out + "_eval.pt")
+    assert abs(ev["loss"] - ev["loss2"]) < 1e-7
+    # the checkpoint written from the pipelined run is a plain single-device model that evaluates identically
+    m = dc.Sequential.from_file(out + "_model")
+    m.set_training(False)
+    x, t = _data(8)
+    y = m.forward(x, 0)
+    loss, _, correct = dnn.SoftmaxCrossEntropyLoss().forward_backward(y, t, want_grad=False)
+    # eval_step averages the per-microbatch mean losses (2 equal microbatches here == the batch mean)
+    assert abs(float(loss) - ev["loss"]) < 1e-5 and float(correct) == ev["correct"]
+    ref, _ = _reference_run(2, 2, 2)
+    for p, q in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, atol=2e-5, rtol=1e-4)
