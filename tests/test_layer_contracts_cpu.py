@@ -282,3 +282,49 @@ def test_dropout_train_vs_eval_scaling():
     assert torch.equal(g != 0, y != 0)                            # backward uses the forward mask
     do.set_training(False)
     assert torch.equal(do.forward(x, 0), x)
+
+
+# ------------------------------------------------------------------------------------------------ SURVEY appendix A.3
+def test_reference_semantics_init_ties_dense_shapes_and_loss_scaling():
+    # init: weights AND biases ~ U(-1/sqrt(fan_in), +1/sqrt(fan_in)); BN gamma 1 / beta 0 / mean 0 / var 1
+    conv = dnn.Conv2DLayer(16, 32, 3, 3, 1, 1, 1, 1, True, "c")
+    conv.set_seed(1)
+    conv.initialize()
+    bound = 1.0 / (16 * 9) ** 0.5
+    w, b = conv.parameters()
+    assert float(w.abs().max()) <= bound and float(b.abs().max()) <= bound
+    assert float(w.abs().max()) > 0.9 * bound and abs(float(w.mean())) < 0.1 * bound       # fills the interval, centred
+    fc = dnn.DenseLayer(100, 10, True, "d")
+    fc.set_seed(1)
+    fc.initialize()
+    assert float(fc.parameters()[0].abs().max()) <= 0.1 and float(fc.parameters()[1].abs().max()) <= 0.1
+    bn = dnn.BatchNormLayer(4)
+    bn.initialize()
+    assert torch.equal(bn.parameters()[0].reshape(-1), torch.ones(4)) and torch.equal(bn.parameters()[1].reshape(-1), torch.zeros(4))
+    assert torch.equal(bn.buffers()["running_mean"], torch.zeros(4)) and torch.equal(bn.buffers()["running_var"], torch.ones(4))
+    # max-pool ties -> the first maximum in scan order receives the gradient
+    mp = dnn.MaxPool2DLayer(2, 2, 2, 2, 0, 0, "mp")
+    x = torch.zeros(1, 1, 2, 2)
+    mp.forward(x, 0)
+    dx = mp.backward(torch.ones(1, 1, 1, 1), 0)
+    assert torch.equal(dx, torch.tensor([[[[1.0, 0.0], [0.0, 0.0]]]]))
+    # Dense takes any [N, C, H, W] with C*H*W == input_features and emits [N, out, 1, 1]
+    y = fc.forward(torch.randn(3, 4, 5, 5), 0)
+    assert tuple(y.shape) == (3, 10, 1, 1)
+    assert tuple(fc.backward(torch.ones_like(y), 0).shape) == (3, 4, 5, 5)
+    # loss = mean over the batch, gradient already scaled by 1/batch
+    loss_fn = dnn.SoftmaxCrossEntropyLoss()
+    logits = torch.randn(6, 5, 1, 1)
+    tgt = torch.nn.functional.one_hot(torch.arange(6) % 5, 5).float().reshape(6, 5, 1, 1)
+    loss, g, _ = loss_fn.forward_backward(logits, tgt)
+    lr = logits.clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(lr.reshape(6, 5), tgt.reshape(6, 5).argmax(1), reduction="mean")
+    ref.backward()
+    assert abs(float(loss) - float(ref.detach())) < 1e-6 and torch.allclose(g, lr.grad, atol=1e-6)
+    # builder auto-names (appendix B.1): every auto-named layer is "<type>_0", residual helper BNs are "bn0"
+    m = dnn.SequentialBuilder("n").input([3, 8, 8]).conv2d(4, 3, 3, 1, 1, 1, 1, True).batchnorm().activation("relu") \
+        .basic_residual_block(4, 4, 1).build()
+    names = [l.name for l in m.get_layers()]
+    assert names[0] == "conv2d_0" and names[1] == "batchnorm_0" and names[2] == "activation_0"
+    block = m.get_layers()[3]
+    assert [l.name for l in block.get_main_path() if l.type() == "batchnorm"] == ["bn0", "bn0"]
