@@ -50,6 +50,7 @@ class Sequential:
         self.training = True
         self.device = torch.device("cpu")
         self.enable_profiling_ = False
+        self.after_unit_backward = None       # optional callable(unit_index), called after each unit's backward
         self.forward_times_us: Dict[str, float] = {}
         self.backward_times_us: Dict[str, float] = {}
         self._pending_events: List[tuple] = []
@@ -275,8 +276,12 @@ class Sequential:
         first = units[0].layers[0]
         if hasattr(first, "need_input_grad"):
             first.need_input_grad = self.compute_input_gradient
-        for u in reversed(units):
+        hook = self.after_unit_backward
+        for idx in range(len(units) - 1, -1, -1):
+            u = units[idx]
             grad, _ = self._timed(self.backward_times_us, u.name, u.backward, grad, micro_batch_id)
+            if hook is not None:
+                hook(idx)          # e.g. DataParallel: the gradients of units >= idx are final for this pass
             if grad is None:
                 break
         return grad

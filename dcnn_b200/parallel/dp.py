@@ -140,6 +140,52 @@ class SyncBN:
         return a, b, m * self.dp.world
 
 
+def plan_buckets(unit_params, numels, offsets, n, k, rank, world):
+    """Cut the flat gradient buffer ``[0, n)`` into at most ``k`` contiguous buckets at fusion-unit boundaries, balanced
+    by parameter count.  ``unit_params[u] = (lo, hi)`` is unit u's parameter-index range, ``offsets[i]`` the flat offset
+    of parameter i (multiples of 4), ``numels[i]`` its size.  Returns one dict per bucket, in unit order:
+    ``first_unit`` (the unit whose backward completes the bucket), ``a`` / ``n`` (flat start / length, multiple of 4),
+    ``sb`` / ``se`` (this rank's shard inside the bucket, bucket-relative, multiples of 4) and ``state_off`` (offset of
+    that shard in this rank's optimizer-state arrays)."""
+    total = sum(numels)
+    target, groups, cur, acc = total / max(1, k), [], [], 0
+    for ui, (lo, hi) in enumerate(unit_params):
+        cur.append(ui)
+        acc += sum(numels[lo:hi])
+        if acc >= target * (len(groups) + 1) and len(groups) < k - 1 and hi < len(offsets):
+            groups.append(cur)
+            cur = []
+    if cur:
+        groups.append(cur)
+    # a group without parameters (pooling, flatten ...) joins its predecessor
+    merged = []
+    for g in groups:
+        if merged and not any(unit_params[u][1] > unit_params[u][0] for u in g):
+            merged[-1].extend(g)
+        else:
+            merged.append(list(g))
+    if merged and not any(unit_params[u][1] > unit_params[u][0] for u in merged[0]) and len(merged) > 1:
+        merged[1] = merged[0] + merged[1]
+        merged = merged[1:]
+    buckets, state_off = [], 0
+    for gi, g in enumerate(merged):
+        first_param = next((unit_params[u][0] for u in g if unit_params[u][1] > unit_params[u][0]), None)
+        a = 0 if gi == 0 else offsets[first_param]
+        if gi + 1 < len(merged):
+            nxt = next(unit_params[u][0] for u in merged[gi + 1] if unit_params[u][1] > unit_params[u][0])
+            b = offsets[nxt]
+        else:
+            b = n
+        length = b - a
+        if length <= 0 or length % 4:
+            raise ValueError(f"bad bucket [{a}, {b})")
+        q = length // 4
+        sb, se = (q * rank // world) * 4, (q * (rank + 1) // world) * 4
+        buckets.append({"first_unit": g[0], "a": a, "n": length, "sb": sb, "se": se, "state_off": state_off})
+        state_off += se - sb
+    return buckets
+
+
 class DataParallel:
     def __init__(self, model: Sequential, optimizer: Optimizer, group=None, sync_bn: bool = True,
                  nccl_baseline: bool = False, num_blocks: int = 0):
@@ -167,8 +213,14 @@ class DataParallel:
             self.bn_flags = self.ctl.peer_array(128)
             self.local = torch.zeros(8, dtype=torch.int64, device=self.device)  # [0] block ctr, [1] epoch, [2] bn epoch
             self.bn_epoch_ptr = self.local.data_ptr() + 16
+        self.buckets = None           # DCNN_DP_BUCKETS=K: K fused all-reduce launches overlapped with backward
+        self.final_backward = False   # set by the training step before the last backward pass of an optimisation step
         if self.fused:
             self._setup_fused(params)
+            import os
+            k = int(os.environ.get("DCNN_DP_BUCKETS", "0") or 0)
+            if k > 1 and self.world > 1:
+                self._setup_buckets(k)
         else:
             self.flat_grad = None
             optimizer.attach(params, grads)
@@ -213,6 +265,86 @@ class DataParallel:
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
 
+    # ------------------------------------------------------------------------------------------------
+    # Bucketed, overlapped variant (opt-in, DCNN_DP_BUCKETS=K; written after the last GPU minutes of its session, not yet
+    # run on hardware).  The flat gradient buffer is cut at fusion-unit boundaries into K contiguous buckets.  Backward
+    # visits units from last to first, so a bucket's gradients are final once its FIRST unit has run its backward; at
+    # that moment the same fused kernel is launched for just that range on a side stream (event-ordered after the
+    # compute stream), so reduce-scatter + update + all-gather of the late layers run under the backward of the early
+    # ones.  Every bucket is sharded over the replicas on its own; the optimizer state of this rank is the
+    # concatenation of its bucket shards.
+    def _setup_buckets(self, k: int):
+        units = self.model._get_units()
+        unit_params, i = [], 0          # parameter index range of every unit (model.parameters() is unit order)
+        for u in units:
+            cnt = sum(len(l.parameters()) for l in u.layers)
+            unit_params.append((i, i + cnt))
+            i += cnt
+        assert i == len(self.offsets), "fusion units do not cover the model parameters"
+        self.buckets = plan_buckets(unit_params, self.numels, self.offsets, self.n, k, self.rank, self.world)
+        for bk in self.buckets:
+            bk["grad_ptrs"] = self.buf.peer_array(4 * self.n + 4 * bk["a"])
+            bk["param_ptrs"] = self.buf.peer_array(4 * bk["a"])
+        state = max(4, sum(bk["se"] - bk["sb"] for bk in self.buckets))
+        opt = self.optimizer
+        self.s1 = torch.zeros(state, device=self.device) \
+            if (isinstance(opt, Adam) or getattr(opt, "momentum", 0) > 0) else None
+        self.s2 = torch.zeros(state, device=self.device) if isinstance(opt, Adam) else None
+        self.comm_stream = torch.cuda.Stream(device=self.device)
+        self._trigger = {bk["first_unit"]: bi for bi, bk in enumerate(self.buckets)}
+        self._launched = set()
+        self._step_args = None
+        self.model.after_unit_backward = self._on_unit_backward
+
+    def _on_unit_backward(self, unit_index: int):
+        if self.final_backward and unit_index in self._trigger:
+            self._launch_bucket(self._trigger[unit_index])
+
+    def _begin_step(self, opt):
+        """Once per optimisation step, before its first bucket launch: step count and bias corrections."""
+        if isinstance(opt, Adam):
+            opt.t += 1
+            bc1, bc2 = opt.bias_corrections()
+            args = (3 if opt.decouple_weight_decay else 2, opt.beta1, opt.beta2, opt.epsilon, bc1, bc2, opt.weight_decay)
+        elif isinstance(opt, SGD):
+            args = (1 if opt.momentum > 0 else 0, opt.momentum, 0.0, 0.0, 1.0, 1.0, 0.0)
+        else:
+            raise TypeError(f"fused all-reduce+update does not know optimizer {type(opt).__name__}")
+        opt.push_hyper()
+        self._step_args = args
+
+    def _launch_bucket(self, bi: int):
+        from .._lib import F, I, LL, P, check, lib
+        from ..ops.cuda import _p
+        if bi in self._launched:
+            return
+        opt = self.optimizer
+        if self._step_args is None:
+            self._begin_step(opt)
+        mode, a, b, eps, bc1, bc2, wd = self._step_args
+        bk = self.buckets[bi]
+        ready = torch.cuda.Event()
+        ready.record()                                   # the bucket's gradients are complete at this point
+        self.comm_stream.wait_event(ready)
+        s1 = self.s1[bk["state_off"]:] if self.s1 is not None else None
+        s2 = self.s2[bk["state_off"]:] if self.s2 is not None else None
+        with torch.cuda.stream(self.comm_stream):
+            check(lib().dcnn_fused_allreduce_update(
+                bk["grad_ptrs"], bk["param_ptrs"], _p(s1), _p(s2), LL(bk["n"]), LL(bk["sb"]), LL(bk["se"]),
+                self.start_flags, self.done_flags, P(self.local.data_ptr()), I(self.rank), I(self.world),
+                P(self.local.data_ptr() + 8), I(mode), F(opt.learning_rate), F(a), F(b), F(eps), F(bc1), F(bc2), F(wd),
+                _p(opt.hyper), I(self.num_blocks if self.num_blocks > 0 else 32),
+                P(self.comm_stream.cuda_stream)), "dcnn_fused_allreduce_update (bucket)")
+        self._launched.add(bi)
+
+    def _finish_buckets(self):
+        for bi in range(len(self.buckets) - 1, -1, -1):   # whatever the hooks did not launch (e.g. no final-pass flag)
+            self._launch_bucket(bi)
+        torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self._launched = set()
+        self._step_args = None
+        self.final_backward = False
+
     def _setup_sync_bn(self):
         bns = [l for l in _all_layers(self.model) if isinstance(l, BatchNormLayer)]
         on_gpu = self.device.type == "cuda"
@@ -246,6 +378,8 @@ class DataParallel:
         opt = optimizer or self.optimizer
         if not self.fused:
             return self._baseline(opt)
+        if self.buckets is not None:
+            return self._finish_buckets()
         from .._lib import F, I, LL, P, check, lib
         from ..ops.cuda import _p, _stream
         if isinstance(opt, Adam):

@@ -251,6 +251,8 @@ class PipelineEngine:
                     self._isend(y, self.next_rank, self.g_send_act)
             else:
                 g = grads.pop(mb) if self.is_last else view
+                if self.dp is not None:      # last backward of the step: bucketed DP may start reducing early
+                    self.dp.final_backward = all(o != "B" for o, _ in sched[k + 1:])
                 dx = self.model.backward(g, mb)
                 if not self.is_first:
                     self._isend(dx, self.prev_rank, self.g_send_grad)

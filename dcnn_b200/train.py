@@ -116,6 +116,8 @@ class TrainStep:
             if correct is not None:
                 correct_acc = correct if correct_acc is None else correct_acc + correct
         for i in reversed(range(len(xs))):
+            if self.dp is not None:
+                self.dp.final_backward = (i == 0)     # bucketed DP may start reducing finished buckets during this pass
             self.model.backward(grads[i], i)
         if self.dp is not None:
             self.dp.reduce_and_update(self.optimizer)

@@ -24,3 +24,5 @@ echo "== pp$N with per-op CUDA graphs"; DCNN_PIPE_GRAPH=1 timeout 120 $TR bench.
 COMMON="SYNTHETIC=1 DEVICE_TYPE=GPU EPOCHS=1 BATCH_SIZE=128 SYNTHETIC_TRAIN_SAMPLES=$((1024*N)) SYNTHETIC_TEST_SAMPLES=$((256*N)) PROGRESS_PRINT_INTERVAL=1000 STEP_TIMEOUT_S=60"
 echo "== data_parallel_trainer x$N"; env $COMMON timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29555 examples/data_parallel_trainer.py --model resnet50_tiny_imagenet > gpurun_out/dp_trainer_$N.log 2>&1; echo "exit $?"; grep -E "Data parallel|Training   -|Validation -|Final|Error" gpurun_out/dp_trainer_$N.log | tail -5 | cut -c1-200
 echo "== spmd_pipeline_trainer pp$N"; env $COMMON NUM_MICROBATCHES=4 timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29556 examples/spmd_pipeline_trainer.py --model resnet50_tiny_imagenet --num-stages $N > gpurun_out/spmd_trainer_$N.log 2>&1; echo "exit $?"; grep -E "Pipeline:|Training   -|Validation -|Final|Error" gpurun_out/spmd_trainer_$N.log | tail -5 | cut -c1-200
+echo "== dp$N with bucketed overlapped all-reduce"; DCNN_DP_BUCKETS=4 timeout 90 $TR bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_dp${N}_buckets.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_dp${N}_buckets.log | cut -c1-300
+echo "== dp tests with buckets"; DCNN_DP_BUCKETS=3 timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_buckets_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_buckets_$N.log | cut -c1-300

@@ -70,3 +70,48 @@ def test_dp2_syncbn_equals_single_process(tmp_path):
     assert len(got) == len(ref)
     for a, b in zip(got, ref):
         assert torch.allclose(a, b, atol=2e-5, rtol=1e-4), (a - b).abs().max()
+
+
+def test_bucket_plan_covers_the_buffer_and_shards_evenly():
+    """plan_buckets (the DCNN_DP_BUCKETS planner): buckets are contiguous, start at unit boundaries, cover [0, n), and the
+    per-rank shards of every bucket partition it in multiples of 4 with consistent optimizer-state offsets."""
+    from dcnn_b200.models import create_resnet9_cifar10
+    from dcnn_b200.parallel.dp import plan_buckets
+    m = create_resnet9_cifar10()
+    m.set_seed(0)
+    m.initialize()
+    numels = [p.numel() for p in m.parameters()]
+    offsets, total = [], 0
+    for nn_ in numels:
+        offsets.append(total)
+        total += (nn_ + 3) // 4 * 4
+    units = m._get_units()
+    unit_params, i = [], 0
+    for u in units:
+        c = sum(len(l.parameters()) for l in u.layers)
+        unit_params.append((i, i + c))
+        i += c
+    assert i == len(numels)
+    for world in (2, 3, 8):
+        n = (total + 4 * world - 1) // (4 * world) * (4 * world)
+        for k in (1, 2, 4, 7, 100):
+            per_rank = [plan_buckets(unit_params, numels, offsets, n, k, r, world) for r in range(world)]
+            b0 = per_rank[0]
+            assert 1 <= len(b0) <= max(1, k)
+            assert b0[0]["a"] == 0 and b0[-1]["a"] + b0[-1]["n"] == n
+            assert all(x["a"] + x["n"] == y["a"] for x, y in zip(b0, b0[1:]))
+            assert [b["first_unit"] for b in b0] == sorted({b["first_unit"] for b in b0})
+            for bi, bk in enumerate(b0):
+                assert bk["n"] % 4 == 0
+                if bi > 0:       # a bucket starts where the first parameter of its first unit starts
+                    lo = next(unit_params[u][0] for u in range(bk["first_unit"], len(units))
+                              if unit_params[u][1] > unit_params[u][0])
+                    assert bk["a"] == offsets[lo]
+                cuts = [per_rank[r][bi]["sb"] for r in range(world)] + [per_rank[-1][bi]["se"]]
+                assert cuts[0] == 0 and cuts[-1] == bk["n"] and cuts == sorted(cuts) and all(c % 4 == 0 for c in cuts)
+                assert all(per_rank[r][bi]["se"] == per_rank[r + 1][bi]["sb"] for r in range(world - 1))
+            for r in range(world):
+                off = 0
+                for bk in per_rank[r]:
+                    assert bk["state_off"] == off
+                    off += bk["se"] - bk["sb"]
