@@ -76,6 +76,100 @@ class SymmetricBuffer:
         return (C.c_void_p * self.world)(*[p + offset_bytes for p in self.peer_ptrs])
 
 
+def send_fd_to_ranks(tag: str, ranks, fd: int, timeout_s: float = 60.0):
+    """Hand a file descriptor to other local processes: each receiver listens on the abstract-namespace UNIX socket
+    ``\\0<tag>-<rank>`` (see :func:`recv_fd`); the descriptor travels as SCM_RIGHTS ancillary data."""
+    import socket
+    import time
+    for r in ranks:
+        addr = "\0" + f"{tag}-{r}"
+        deadline = time.monotonic() + timeout_s
+        while True:
+            s_ = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            try:
+                s_.connect(addr)
+                break
+            except OSError:
+                s_.close()
+                if time.monotonic() > deadline:
+                    raise
+                time.sleep(0.02)
+        try:
+            socket.send_fds(s_, [b"fd"], [fd])
+        finally:
+            s_.close()
+
+
+def recv_fd(tag: str, rank: int, timeout_s: float = 60.0) -> int:
+    import socket
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    try:
+        srv.bind("\0" + f"{tag}-{rank}")
+        srv.listen(1)
+        srv.settimeout(timeout_s)
+        conn, _ = srv.accept()
+        try:
+            _msg, fds, _flags, _addr = socket.recv_fds(conn, 16, 1)
+        finally:
+            conn.close()
+    finally:
+        srv.close()
+    if not fds:
+        raise RuntimeError("no file descriptor received")
+    return fds[0]
+
+
+class NvlsBuffer:
+    """Flat device buffer whose memory is bound to an NVSwitch MULTICAST object spanning the replicas of ``group``
+    (csrc/nvls.cu): ``ptr`` is this replica's ordinary (unicast) mapping, ``mc_ptr`` the multicast mapping on which
+    ``multimem.ld_reduce`` sums all replicas' copies inside the switch and ``multimem.st`` writes all of them.
+
+    Set-up is collective: rank 0 creates the object and exports a POSIX file descriptor, which reaches the other ranks
+    over abstract UNIX sockets (SCM_RIGHTS); every rank adds its device, then (after a barrier) allocates, binds and
+    maps.  Opt-in, not yet run on hardware (DCNN_DP_NVLS=1)."""
+
+    def __init__(self, nbytes: int, group, device: torch.device):
+        import time
+        from .._lib import check, lib
+        l = lib()
+        l.dcnn_nvls_padded_size.restype = C.c_longlong
+        self.group, self.device = group, device
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        dev = device.index if device.index is not None else torch.cuda.current_device()
+        self.nbytes = int(l.dcnn_nvls_padded_size(C.c_int(self.world), C.c_longlong(int(nbytes)), C.c_int(dev)))
+        if self.nbytes <= 0:
+            raise RuntimeError("dcnn_nvls_padded_size failed: " + l.dcnn_last_error().decode())
+        handle = C.c_ulonglong(0)
+        tag = [None]
+        if self.rank == 0:
+            import os
+            tag[0] = f"dcnn-nvls-{os.getpid()}-{time.monotonic_ns()}"
+        dist.broadcast_object_list(tag, src=dist.get_global_rank(group, 0), group=group)
+        if self.rank == 0:
+            fd = C.c_int(-1)
+            check(l.dcnn_nvls_create(C.c_int(self.world), C.c_longlong(self.nbytes), C.byref(handle), C.byref(fd)),
+                  "dcnn_nvls_create")
+            import os
+            send_fd_to_ranks(tag[0], range(1, self.world), fd.value)
+            os.close(fd.value)
+        else:
+            check(l.dcnn_nvls_import(C.c_int(recv_fd(tag[0], self.rank)), C.byref(handle)), "dcnn_nvls_import")
+        self.handle = handle.value
+        check(l.dcnn_nvls_add_device(C.c_ulonglong(self.handle), C.c_int(dev)), "dcnn_nvls_add_device")
+        dist.barrier(group=group)                      # every device is part of the object before anyone binds
+        uc, mc = C.c_void_p(), C.c_void_p()
+        check(l.dcnn_nvls_bind(C.c_ulonglong(self.handle), C.c_int(dev), C.c_longlong(self.nbytes), C.byref(uc),
+                               C.byref(mc)), "dcnn_nvls_bind")
+        self.ptr, self.mc_ptr = uc.value, mc.value
+        self._bytes = torch.as_tensor(_RawCuda(self.ptr, self.nbytes), device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)                      # all bindings exist before the first multimem access
+
+    def view(self, dtype, offset_bytes: int, numel: int) -> torch.Tensor:
+        size = torch.empty((), dtype=dtype).element_size()
+        return self._bytes[offset_bytes:offset_bytes + numel * size].view(dtype)
+
+
 class SyncBN:
     """Cross-replica BatchNorm statistics for one BN layer (forward moments and backward sums)."""
 
@@ -219,7 +313,7 @@ class DataParallel:
             self._setup_fused(params)
             import os
             k = int(os.environ.get("DCNN_DP_BUCKETS", "0") or 0)
-            if k > 1 and self.world > 1:
+            if k > 1 and self.world > 1 and not self.nvls:
                 self._setup_buckets(k)
         else:
             self.flat_grad = None
@@ -234,7 +328,18 @@ class DataParallel:
     def _setup_fused(self, params):
         n = self.n
         # layout: [params n floats][grads n floats]
-        self.buf = SymmetricBuffer(8 * n, self.group, self.device)
+        import os
+        self.nvls = False
+        if os.environ.get("DCNN_DP_NVLS", "0") == "1" and self.world > 1:
+            from .._lib import lib
+            dev = self.device.index if self.device.index is not None else torch.cuda.current_device()
+            ok = torch.tensor([int(lib().dcnn_nvls_supported(C.c_int(dev)))], device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)     # all replicas or none
+            self.nvls = bool(int(ok.item()))
+            if not self.nvls and self.rank == 0:
+                print("DCNN_DP_NVLS=1 but multicast objects are not supported here: using the P2P kernel")
+        self.buf = NvlsBuffer(8 * n, self.group, self.device) if self.nvls \
+            else SymmetricBuffer(8 * n, self.group, self.device)
         self.flat_param = self.buf.view(torch.float32, 0, n)
         self.flat_grad = self.buf.view(torch.float32, 4 * n, n)
         new_p, new_g = [], []
@@ -260,8 +365,9 @@ class DataParallel:
             else None
         self.s2 = torch.zeros(shard, device=self.device) if isinstance(opt, Adam) else None
         opt.params, opt.grads = self.model.parameters(), self.model.gradients()   # for clear_gradients()/introspection
-        self.grad_ptrs = self.buf.peer_array(4 * self.n)
-        self.param_ptrs = self.buf.peer_array(0)
+        if not self.nvls:
+            self.grad_ptrs = self.buf.peer_array(4 * self.n)
+            self.param_ptrs = self.buf.peer_array(0)
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
 
@@ -394,6 +500,15 @@ class DataParallel:
         else:
             raise TypeError(f"fused all-reduce+update does not know optimizer {type(opt).__name__}")
         opt.push_hyper()
+        if self.nvls:
+            # reduction inside the NVSwitch (multimem.ld_reduce) and one multicast store per parameter slice
+            check(lib().dcnn_fused_allreduce_update_nvls(
+                P(self.buf.mc_ptr + 4 * self.n), P(self.buf.mc_ptr), P(self.buf.ptr), P(self.buf.ptr + 4 * self.n),
+                _p(self.s1), _p(self.s2), LL(self.n), LL(self.shard_begin), LL(self.shard_end), self.start_flags,
+                self.done_flags, P(self.local.data_ptr()), I(self.rank), I(self.world), P(self.local.data_ptr() + 8),
+                I(mode), F(opt.learning_rate), F(a), F(b), F(eps), F(bc1), F(bc2), F(wd), _p(opt.hyper),
+                I(self.num_blocks), _stream()), "dcnn_fused_allreduce_update_nvls")
+            return
         check(lib().dcnn_fused_allreduce_update(
             self.grad_ptrs, self.param_ptrs, _p(self.s1), _p(self.s2), LL(self.n), LL(self.shard_begin),
             LL(self.shard_end), self.start_flags, self.done_flags, P(self.local.data_ptr()), I(self.rank),
@@ -422,6 +537,10 @@ class DataParallel:
         opt.update(zero_grads=True)
 
     def bytes_over_nvlink_per_step(self) -> int:
-        """Per-GPU one-direction NVLink traffic of the fused kernel: (R-1)/R of the gradients in, the same amount of
-        parameters out."""
-        return int(self.n * 4 * (self.world - 1) / self.world)
+        """Per-GPU NVLink traffic in ONE direction per step.  P2P kernel: (R-1)/R of the gradients are loaded from the
+        peers and (R-1)/R of the parameters arrive from them: 2 * 4n * (R-1)/R bytes inbound (and the same outbound).
+        NVLS kernel: 1/R of the gradients arrives already reduced by the switch and (R-1)/R of the parameters arrive by
+        multicast: 4n bytes inbound."""
+        if getattr(self, "nvls", False):
+            return int(self.n * 4)
+        return int(2 * self.n * 4 * (self.world - 1) / self.world)

@@ -130,6 +130,20 @@ int dcnn_multi_tensor_update(int mode, float* const* param, float* const* grad, 
 int dcnn_mt_chunk(void);
 
 /* ---- data-parallel peer-memory path (no counterpart in the reference: it has no data parallelism) ---- */
+/* ---- NVLS (NVSwitch multicast) variant of the data-parallel update: csrc/nvls.cu.  Opt-in, see parallel/dp.py ---- */
+int dcnn_nvls_supported(int device);
+long long dcnn_nvls_padded_size(int world, long long bytes, int device);
+int dcnn_nvls_create(int world, long long bytes, unsigned long long* handle_out, int* fd_out);   /* rank 0 */
+int dcnn_nvls_import(int fd, unsigned long long* handle_out);                                    /* other ranks */
+int dcnn_nvls_add_device(unsigned long long handle, int device);   /* every rank, before any rank binds */
+int dcnn_nvls_bind(unsigned long long handle, int device, long long bytes, void** uc_ptr, void** mc_ptr);
+int dcnn_fused_allreduce_update_nvls(const float* mc_grads, float* mc_params, const float* params, float* grads,
+                                     float* s1, float* s2, long long n, long long shard_begin, long long shard_end,
+                                     unsigned long long* const* start_flag_ptrs,
+                                     unsigned long long* const* done_flag_ptrs, unsigned int* block_counter, int rank,
+                                     int world, unsigned long long* epoch_counter, int mode, float lr, float a, float b,
+                                     float eps, float bc1, float bc2, float wd, const float* hyper, int num_blocks,
+                                     cudaStream_t stream);
 int dcnn_dev_malloc(void** ptr, long long bytes);
 int dcnn_dev_free(void* ptr);
 int dcnn_ipc_get_handle(void* ptr, unsigned char* handle64);

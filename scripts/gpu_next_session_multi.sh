@@ -26,3 +26,5 @@ echo "== data_parallel_trainer x$N"; env $COMMON timeout 150 python -m torch.dis
 echo "== spmd_pipeline_trainer pp$N"; env $COMMON NUM_MICROBATCHES=4 timeout 150 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29556 examples/spmd_pipeline_trainer.py --model resnet50_tiny_imagenet --num-stages $N > gpurun_out/spmd_trainer_$N.log 2>&1; echo "exit $?"; grep -E "Pipeline:|Training   -|Validation -|Final|Error" gpurun_out/spmd_trainer_$N.log | tail -5 | cut -c1-200
 echo "== dp$N with bucketed overlapped all-reduce"; DCNN_DP_BUCKETS=4 timeout 90 $TR bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_dp${N}_buckets.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_dp${N}_buckets.log | cut -c1-300
 echo "== dp tests with buckets"; DCNN_DP_BUCKETS=3 timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_buckets_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_buckets_$N.log | cut -c1-300
+echo "== NVLS all-reduce (multimem)"; DCNN_DP_NVLS=1 timeout 90 $TR benchmarks/allreduce_roofline.py > gpurun_out/ar_nvls_$N.log 2>&1; echo "exit $?"; tail -2 gpurun_out/ar_nvls_$N.log | cut -c1-400
+DCNN_DP_NVLS=1 timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_nvls_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_nvls_$N.log | cut -c1-300

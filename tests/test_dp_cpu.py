@@ -115,3 +115,35 @@ def test_bucket_plan_covers_the_buffer_and_shards_evenly():
                 for bk in per_rank[r]:
                     assert bk["state_off"] == off
                     off += bk["se"] - bk["sb"]
+
+
+def _fd_receiver(rank, tag, out):
+    from dcnn_b200.parallel.dp import recv_fd
+    fd = recv_fd(tag, rank + 1, timeout_s=30)
+    data = os.pread(fd, 1 << 16, 0)       # the duplicates share one file offset: read positionally
+    os.close(fd)
+    with open(out + f".{rank + 1}", "wb") as f:
+        f.write(data)
+
+
+def test_fd_passing_between_processes(tmp_path):
+    """The descriptor hand-off NvlsBuffer uses for the multicast object (SCM_RIGHTS over abstract UNIX sockets): two
+    receiver processes each get a working duplicate of a descriptor opened by the sender."""
+    import time
+    import torch.multiprocessing as mp
+    from dcnn_b200.parallel.dp import send_fd_to_ranks
+    src = tmp_path / "payload.bin"
+    src.write_bytes(b"multicast-handle-stand-in" * 10)
+    tag = f"dcnn-test-{os.getpid()}-{time.monotonic_ns()}"
+    out = str(tmp_path / "got")
+    ctx = mp.spawn(_fd_receiver, args=(tag, out), nprocs=2, join=False)
+    fd = os.open(str(src), os.O_RDONLY)
+    try:
+        send_fd_to_ranks(tag, [1, 2], fd, timeout_s=30)
+    finally:
+        os.close(fd)
+    deadline = time.monotonic() + 60
+    while not ctx.join(timeout=1.0):
+        assert time.monotonic() < deadline
+    for r in (1, 2):
+        assert open(out + f".{r}", "rb").read() == src.read_bytes()
