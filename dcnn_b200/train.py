@@ -138,8 +138,16 @@ class TrainStep:
             self._static = (x.clone(), t.clone())
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
-            with torch.cuda.graph(g):
-                out = self._eager(*self._static)
+            try:
+                with torch.cuda.graph(g):
+                    out = self._eager(*self._static)
+            except Exception as e:      # keep training: a failed capture costs launch overhead, not the run
+                import sys
+                print(f"[dcnn] CUDA graph capture failed ({type(e).__name__}: {e}); continuing without graphs",
+                      file=sys.stderr)
+                self.use_cuda_graph, self._static = False, None
+                torch.cuda.synchronize()
+                return self._eager(x, t)
             self._graph, self._out = g, out
             # the capture itself did not execute: fall through to replay with this batch
             if hasattr(self.optimizer, "t"):
