@@ -1,0 +1,205 @@
+// Native CPU layer kernels (NCHW fp32, OpenMP): BatchNorm statistics / apply / backward, max- and average pooling
+// forward / backward.  Together with cpu_math.cpp (GEMM-based conv and Dense) they are the counterpart of the
+// reference's CPU layer ops (src/nn/layers_impl/cpu/batchnorm_ops.cpp, maxpool_ops.cpp, avgpool_ops.cpp) for the
+// DCNN_CPU_BACKEND=native path; semantics follow SURVEY appendix A.3 (biased variance for normalisation, avg-pool
+// divisor always kh*kw, max-pool ties -> first maximum in scan order, gradients accumulate).
+#include <math.h>
+#include <string.h>
+
+#include <vector>
+
+#include "host_common.h"
+
+// per-channel mean and biased variance over (N, H, W); FP64 accumulation, two passes
+DCNN_HOST_API void dcnn_cpu_bn_stats(const float* x, int N, int C, int HW, float* mean, float* var) {
+#pragma omp parallel for schedule(static)
+  for (int c = 0; c < C; ++c) {
+    double s = 0;
+    for (int n = 0; n < N; ++n) {
+      const float* p = x + ((size_t)n * C + c) * HW;
+      double t = 0;
+#pragma omp simd reduction(+ : t)
+      for (int i = 0; i < HW; ++i) t += p[i];
+      s += t;
+    }
+    const double m = s / ((double)N * HW);
+    double q = 0;
+    for (int n = 0; n < N; ++n) {
+      const float* p = x + ((size_t)n * C + c) * HW;
+      double t = 0;
+#pragma omp simd reduction(+ : t)
+      for (int i = 0; i < HW; ++i) t += ((double)p[i] - m) * ((double)p[i] - m);
+      q += t;
+    }
+    mean[c] = (float)m;
+    var[c] = (float)(q / ((double)N * HW));
+  }
+}
+
+// y = x * scale[c] + shift[c] (+ residual) (ReLU)
+DCNN_HOST_API void dcnn_cpu_bn_apply(const float* x, const float* scale, const float* shift, const float* residual,
+                                     float* y, int N, int C, int HW, int relu) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int c = 0; c < C; ++c) {
+      const size_t o = ((size_t)n * C + c) * HW;
+      const float sc = scale[c], sh = shift[c];
+      const float* r = residual ? residual + o : nullptr;
+#pragma omp simd
+      for (int i = 0; i < HW; ++i) {
+        float v = x[o + i] * sc + sh;
+        if (r) v += r[i];
+        y[o + i] = (relu && v < 0.f) ? 0.f : v;
+      }
+    }
+  }
+}
+
+// Backward of (BN -> [+residual] -> [ReLU]).  g = dout masked by (out > 0) when relu.  Emits the per-channel sums
+// (sum_dy, sum_dy_xhat) and, in a second call (phase 1) after the caller merged them across replicas if it needs to,
+// dx = (g - sum_dy/m - xhat * sum_dy_xhat/m) * scale.  `masked` (optional) receives g.
+DCNN_HOST_API void dcnn_cpu_bn_bwd_sums(const float* dout, const float* x, const float* out, const float* mean,
+                                        const float* invstd, int N, int C, int HW, int relu, double* sum_dy,
+                                        double* sum_dy_xhat) {
+#pragma omp parallel for schedule(static)
+  for (int c = 0; c < C; ++c) {
+    double a = 0, b = 0;
+    const float mu = mean[c], is = invstd[c];
+    for (int n = 0; n < N; ++n) {
+      const size_t o = ((size_t)n * C + c) * HW;
+      double ta = 0, tb = 0;
+#pragma omp simd reduction(+ : ta, tb)
+      for (int i = 0; i < HW; ++i) {
+        const float g = (relu && !(out[o + i] > 0.f)) ? 0.f : dout[o + i];
+        ta += g;
+        tb += (double)g * (double)((x[o + i] - mu) * is);
+      }
+      a += ta;
+      b += tb;
+    }
+    sum_dy[c] = a;
+    sum_dy_xhat[c] = b;
+  }
+}
+
+DCNN_HOST_API void dcnn_cpu_bn_bwd_dx(const float* dout, const float* x, const float* out, const float* mean,
+                                      const float* invstd, const float* scale, const double* sum_dy,
+                                      const double* sum_dy_xhat, double count, int N, int C, int HW, int relu, float* dx,
+                                      float* masked) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int c = 0; c < C; ++c) {
+      const size_t o = ((size_t)n * C + c) * HW;
+      const float mu = mean[c], is = invstd[c], sc = scale[c];
+      const float ma = (float)(sum_dy[c] / count), mb = (float)(sum_dy_xhat[c] / count);
+#pragma omp simd
+      for (int i = 0; i < HW; ++i) {
+        const float g = (relu && !(out[o + i] > 0.f)) ? 0.f : dout[o + i];
+        const float xhat = (x[o + i] - mu) * is;
+        dx[o + i] = (g - ma - xhat * mb) * sc;
+        if (masked) masked[o + i] = g;
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ pooling
+// idx[n,c,oh,ow] = flat input index (ih*W + iw) of the first maximum in scan order (torch.max_pool2d's convention too)
+DCNN_HOST_API void dcnn_cpu_maxpool_fwd(const float* x, float* y, long long* idx, int N, int C, int H, int W, int OH,
+                                        int OW, int kh, int kw, int sh, int sw, int ph, int pw) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int c = 0; c < C; ++c) {
+      const float* p = x + ((size_t)n * C + c) * H * W;
+      float* q = y + ((size_t)n * C + c) * OH * OW;
+      long long* qi = idx + ((size_t)n * C + c) * OH * OW;
+      for (int oh = 0; oh < OH; ++oh) {
+        for (int ow = 0; ow < OW; ++ow) {
+          float best = -INFINITY;
+          long long bi = -1;
+          for (int r = 0; r < kh; ++r) {
+            const int ih = oh * sh - ph + r;
+            if (ih < 0 || ih >= H) continue;
+            for (int s = 0; s < kw; ++s) {
+              const int iw = ow * sw - pw + s;
+              if (iw < 0 || iw >= W) continue;
+              const float v = p[(size_t)ih * W + iw];
+              if (bi < 0 || v > best || (v != v && best == best)) {   // NaN propagates like ATen
+                best = v;
+                bi = (long long)ih * W + iw;
+              }
+            }
+          }
+          q[oh * OW + ow] = best;
+          qi[oh * OW + ow] = bi;
+        }
+      }
+    }
+  }
+}
+
+DCNN_HOST_API void dcnn_cpu_maxpool_bwd(const float* dy, const long long* idx, float* dx, int N, int C, int HW,
+                                        int OHW) {
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int c = 0; c < C; ++c) {
+      float* d = dx + ((size_t)n * C + c) * HW;
+      memset(d, 0, sizeof(float) * HW);
+      const float* g = dy + ((size_t)n * C + c) * OHW;
+      const long long* qi = idx + ((size_t)n * C + c) * OHW;
+      for (int i = 0; i < OHW; ++i)
+        if (qi[i] >= 0) d[qi[i]] += g[i];
+    }
+  }
+}
+
+// divisor is always kh*kw (zero padding counts)
+DCNN_HOST_API void dcnn_cpu_avgpool_fwd(const float* x, float* y, int N, int C, int H, int W, int OH, int OW, int kh,
+                                        int kw, int sh, int sw, int ph, int pw) {
+  const float inv = 1.f / (float)(kh * kw);
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int c = 0; c < C; ++c) {
+      const float* p = x + ((size_t)n * C + c) * H * W;
+      float* q = y + ((size_t)n * C + c) * OH * OW;
+      for (int oh = 0; oh < OH; ++oh)
+        for (int ow = 0; ow < OW; ++ow) {
+          float acc = 0.f;
+          for (int r = 0; r < kh; ++r) {
+            const int ih = oh * sh - ph + r;
+            if (ih < 0 || ih >= H) continue;
+            for (int s = 0; s < kw; ++s) {
+              const int iw = ow * sw - pw + s;
+              if (iw >= 0 && iw < W) acc += p[(size_t)ih * W + iw];
+            }
+          }
+          q[oh * OW + ow] = acc * inv;
+        }
+    }
+  }
+}
+
+DCNN_HOST_API void dcnn_cpu_avgpool_bwd(const float* dy, float* dx, int N, int C, int H, int W, int OH, int OW, int kh,
+                                        int kw, int sh, int sw, int ph, int pw) {
+  const float inv = 1.f / (float)(kh * kw);
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int n = 0; n < N; ++n) {
+    for (int c = 0; c < C; ++c) {
+      float* d = dx + ((size_t)n * C + c) * H * W;
+      memset(d, 0, sizeof(float) * H * W);
+      const float* g = dy + ((size_t)n * C + c) * OH * OW;
+      for (int oh = 0; oh < OH; ++oh)
+        for (int ow = 0; ow < OW; ++ow) {
+          const float v = g[oh * OW + ow] * inv;
+          for (int r = 0; r < kh; ++r) {
+            const int ih = oh * sh - ph + r;
+            if (ih < 0 || ih >= H) continue;
+            for (int s = 0; s < kw; ++s) {
+              const int iw = ow * sw - pw + s;
+              if (iw >= 0 && iw < W) d[(size_t)ih * W + iw] += v;
+            }
+          }
+        }
+    }
+  }
+}

@@ -33,6 +33,12 @@ int dcnn_decode_message(const uint8_t*, size_t, uint64_t*, uint64_t*, uint64_t*,
                         uint64_t*, uint64_t*, uint64_t*, uint64_t*, uint64_t*, uint64_t*, uint8_t*);
 long long dcnn_encode_tensor_record(uint8_t*, size_t, const uint64_t*, const float*);
 long long dcnn_load_mnist_csv(const char*, float*, int*, long long, int);
+void dcnn_cpu_bn_stats(const float*, int, int, int, float*, float*);
+void dcnn_cpu_bn_apply(const float*, const float*, const float*, const float*, float*, int, int, int, int);
+void dcnn_cpu_maxpool_fwd(const float*, float*, long long*, int, int, int, int, int, int, int, int, int, int, int, int);
+void dcnn_cpu_maxpool_bwd(const float*, const long long*, float*, int, int, int, int);
+void dcnn_cpu_avgpool_fwd(const float*, float*, int, int, int, int, int, int, int, int, int, int, int, int);
+void dcnn_cpu_avgpool_bwd(const float*, float*, int, int, int, int, int, int, int, int, int, int, int, int);
 }
 
 static int failures = 0;
@@ -204,7 +210,31 @@ static void test_loader(const char* tmpdir) {
   remove(path.c_str());
 }
 
+static void test_layers() {
+  const int N = 2, C = 3, H = 7, W = 5, HW = H * W;
+  std::vector<float> x = randv((size_t)N * C * HW), mean(C), var(C), y(x.size()), sc(C, 2.f), sh(C, -1.f);
+  dcnn_cpu_bn_stats(x.data(), N, C, HW, mean.data(), var.data());
+  for (int c = 0; c < C; ++c) {
+    double s = 0;
+    for (int n = 0; n < N; ++n)
+      for (int i = 0; i < HW; ++i) s += x[((size_t)n * C + c) * HW + i];
+    CHECK(fabs(mean[c] - s / (N * HW)) < 1e-5, "bn mean");
+    CHECK(var[c] >= 0.f, "bn var");
+  }
+  dcnn_cpu_bn_apply(x.data(), sc.data(), sh.data(), nullptr, y.data(), N, C, HW, 1);
+  for (size_t i = 0; i < y.size(); ++i) CHECK(y[i] == fmaxf(x[i] * 2.f - 1.f, 0.f), "bn apply");
+  const int k = 3, st = 2, p = 1, OH = (H + 2 * p - k) / st + 1, OW = (W + 2 * p - k) / st + 1;
+  std::vector<float> py((size_t)N * C * OH * OW), dx(x.size());
+  std::vector<long long> idx(py.size());
+  dcnn_cpu_maxpool_fwd(x.data(), py.data(), idx.data(), N, C, H, W, OH, OW, k, k, st, st, p, p);
+  for (size_t i = 0; i < idx.size(); ++i) CHECK(idx[i] >= 0 && idx[i] < HW, "maxpool index in range");
+  dcnn_cpu_maxpool_bwd(py.data(), idx.data(), dx.data(), N, C, HW, OH * OW);
+  dcnn_cpu_avgpool_fwd(x.data(), py.data(), N, C, H, W, OH, OW, k, k, st, st, p, p);
+  dcnn_cpu_avgpool_bwd(py.data(), dx.data(), N, C, H, W, OH, OW, k, k, st, st, p, p);
+}
+
 int main(int argc, char** argv) {
+  test_layers();
   test_gemm();
   test_elementwise();
   test_im2col();

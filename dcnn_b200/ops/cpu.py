@@ -101,6 +101,10 @@ def dense_backward_weight(dy2d, x2d, dw2d):
 # ----------------------------------------------------------------------------------------------
 def bn_stats(x):
     n = x.numel() // x.shape[1]
+    nat = _native()
+    if nat is not None and x.dtype == torch.float32 and x.dim() == 4:
+        mean, var = nat.bn_stats(x)
+        return CpuStats(mean, var, n)
     mean = x.mean(dim=(0, 2, 3))
     var = x.var(dim=(0, 2, 3), unbiased=False)
     return CpuStats(mean, var, n)
@@ -128,6 +132,9 @@ def bn_apply(x, mean, invstd, gamma, beta, residual=None, relu=False):
     shift = -mean * scale
     if beta is not None:
         shift = shift + beta.view(-1)
+    nat = _native()
+    if nat is not None and x.dtype == torch.float32 and x.dim() == 4:
+        return nat.bn_apply(x, scale, shift, residual, relu)
     y = x * scale.view(1, c, 1, 1) + shift.view(1, c, 1, 1)
     if residual is not None:
         y = y + residual
@@ -144,6 +151,18 @@ def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, wa
     dgamma/dbeta are accumulated (deviation from ref batchnorm_ops.cu:218-219, which overwrites;
     see SURVEY appendix B.2)."""
     c = x.shape[1]
+    nat = _native()
+    if nat is not None and x.dtype == torch.float32 and x.dim() == 4:
+        m = x.numel() // c
+        a, b = nat.bn_backward_sums(dout, x, out, mean, invstd, relu)
+        if dgamma is not None:
+            dgamma.add_(b.float().view_as(dgamma))
+            dbeta.add_(a.float().view_as(dbeta))
+        if sync is not None:
+            a32, b32, m = sync.merge_bwd_cpu(a.float(), b.float(), m)
+            a, b = a32.double(), b32.double()
+        scale = invstd if gamma is None else invstd * gamma.view(-1)
+        return nat.bn_backward_dx(dout, x, out, mean, invstd, scale, a, b, m, relu, want_masked)
     g = dout
     if relu:
         g = dout * (out > 0).to(dout.dtype)
@@ -204,11 +223,17 @@ def groupnorm_backward(dy, x, mean, invstd, groups, gamma, dgamma, dbeta):
 # pooling
 # ----------------------------------------------------------------------------------------------
 def maxpool_forward(x, k, stride, pad):
+    nat = _native()
+    if nat is not None and x.dtype == torch.float32:
+        return nat.maxpool_forward(x, k, stride, pad)
     y, idx = F.max_pool2d(x, k, stride, pad, return_indices=True)
     return y, idx
 
 
 def maxpool_backward(dy, idx, x_shape, k, stride, pad):
+    nat = _native()
+    if nat is not None and dy.dtype == torch.float32:
+        return nat.maxpool_backward(dy, idx, tuple(x_shape))
     return F.max_unpool2d(dy, idx, k, stride, pad, output_size=list(x_shape[2:])) \
         if _non_overlapping(k, stride) else _maxpool_bwd_scatter(dy, idx, x_shape)
 
@@ -226,10 +251,16 @@ def _maxpool_bwd_scatter(dy, idx, x_shape):
 
 def avgpool_forward(x, k, stride, pad):
     # divisor is always pool_h*pool_w (ref avgpool_ops.cu:106,122)
+    nat = _native()
+    if nat is not None and x.dtype == torch.float32:
+        return nat.avgpool_forward(x, k, stride, pad)
     return F.avg_pool2d(x, k, stride, pad, count_include_pad=True)
 
 
 def avgpool_backward(dy, x_shape, k, stride, pad):
+    nat = _native()
+    if nat is not None and dy.dtype == torch.float32:
+        return nat.avgpool_backward(dy, tuple(x_shape), k, stride, pad)
     n, c, h, w = x_shape
     ones = torch.ones(c, 1, k[0], k[1], dtype=dy.dtype, device=dy.device) / (k[0] * k[1])
     oh, ow = dy.shape[2:]

@@ -4,7 +4,8 @@ primitives, reductions, dot product, im2col/col2im -- the counterpart of the ref
 include/threading/thread_handler.hpp; include/tensor/cpu/tensor_ops.hpp:22-330).
 
 ``DCNN_CPU_BACKEND=native`` routes the CPU path's convolution (im2col + GEMM, as the reference's CPU Conv2D does:
-src/nn/layers_impl/cpu/conv2d_ops.cpp:19-67) and Dense layers through these kernels instead of ATen; the default stays
+src/nn/layers_impl/cpu/conv2d_ops.cpp:19-67), Dense, BatchNorm and pooling layers (csrc/host/cpu_layers.cpp; ref
+batchnorm_ops.cpp, maxpool_ops.cpp, avgpool_ops.cpp) through these kernels instead of ATen; the default stays
 ATen (oneDNN/MKL are faster on most hosts; the native path exists for parity and for hosts without them)."""
 from __future__ import annotations
 
@@ -225,3 +226,93 @@ def dense_backward_weight(dy2d, x2d, dw2d):
         gemm(dy2d.contiguous(), x2d.contiguous(), trans_a=True, beta=1.0, c=dw2d)
     else:
         dw2d.add_(gemm(dy2d.contiguous(), x2d.contiguous(), trans_a=True))
+
+
+# ---------------------------------------------------------------------------------------------- native layer kernels
+def _ci(*v):
+    return [C.c_int(int(a)) for a in v]
+
+
+def bn_stats(x):
+    """-> (mean[C], biased var[C]) over (N, H, W)."""
+    x = x.contiguous()
+    n, c = x.shape[:2]
+    hw = x.numel() // (n * c)
+    mean, var = torch.empty(c), torch.empty(c)
+    _lib().dcnn_cpu_bn_stats(_ptr(x), *_ci(n, c, hw), _ptr(mean), _ptr(var))
+    return mean, var
+
+
+def bn_apply(x, scale, shift, residual=None, relu=False):
+    x = x.contiguous()
+    n, c = x.shape[:2]
+    hw = x.numel() // (n * c)
+    y = torch.empty_like(x)
+    r = residual.contiguous() if residual is not None else None
+    _lib().dcnn_cpu_bn_apply(_ptr(x), _ptr(scale.contiguous()), _ptr(shift.contiguous()),
+                             _ptr(r) if r is not None else C.c_void_p(0), _ptr(y), *_ci(n, c, hw, 1 if relu else 0))
+    return y
+
+
+def bn_backward_sums(dout, x, out, mean, invstd, relu):
+    dout, x = dout.contiguous(), x.contiguous()
+    n, c = x.shape[:2]
+    hw = x.numel() // (n * c)
+    a, b = torch.empty(c, dtype=torch.float64), torch.empty(c, dtype=torch.float64)
+    o = out.contiguous() if (relu and out is not None) else None
+    _lib().dcnn_cpu_bn_bwd_sums(_ptr(dout), _ptr(x), _ptr(o) if o is not None else C.c_void_p(0), _ptr(mean.contiguous()),
+                                _ptr(invstd.contiguous()), *_ci(n, c, hw, 1 if o is not None else 0), _ptr(a), _ptr(b))
+    return a, b
+
+
+def bn_backward_dx(dout, x, out, mean, invstd, scale, sum_dy, sum_dy_xhat, count, relu, want_masked):
+    dout, x = dout.contiguous(), x.contiguous()
+    n, c = x.shape[:2]
+    hw = x.numel() // (n * c)
+    dx = torch.empty_like(x)
+    o = out.contiguous() if (relu and out is not None) else None
+    masked = torch.empty_like(x) if want_masked else None
+    _lib().dcnn_cpu_bn_bwd_dx(_ptr(dout), _ptr(x), _ptr(o) if o is not None else C.c_void_p(0), _ptr(mean.contiguous()),
+                              _ptr(invstd.contiguous()), _ptr(scale.contiguous()), _ptr(sum_dy.contiguous()),
+                              _ptr(sum_dy_xhat.contiguous()), C.c_double(float(count)),
+                              *_ci(n, c, hw, 1 if o is not None else 0), _ptr(dx),
+                              _ptr(masked) if masked is not None else C.c_void_p(0))
+    return dx, masked
+
+
+def maxpool_forward(x, k, stride, pad):
+    x = x.contiguous()
+    n, c, h, w = x.shape
+    oh, ow = _out_hw(h, w, k[0], k[1], stride, pad)
+    y = torch.empty(n, c, oh, ow)
+    idx = torch.empty(n, c, oh, ow, dtype=torch.int64)
+    _lib().dcnn_cpu_maxpool_fwd(_ptr(x), _ptr(y), _ptr(idx),
+                                *_ci(n, c, h, w, oh, ow, k[0], k[1], stride[0], stride[1], pad[0], pad[1]))
+    return y, idx
+
+
+def maxpool_backward(dy, idx, x_shape):
+    dy, idx = dy.contiguous(), idx.contiguous()
+    n, c, h, w = x_shape
+    dx = torch.empty(n, c, h, w)
+    _lib().dcnn_cpu_maxpool_bwd(_ptr(dy), _ptr(idx), _ptr(dx), *_ci(n, c, h * w, dy.shape[2] * dy.shape[3]))
+    return dx
+
+
+def avgpool_forward(x, k, stride, pad):
+    x = x.contiguous()
+    n, c, h, w = x.shape
+    oh, ow = _out_hw(h, w, k[0], k[1], stride, pad)
+    y = torch.empty(n, c, oh, ow)
+    _lib().dcnn_cpu_avgpool_fwd(_ptr(x), _ptr(y), *_ci(n, c, h, w, oh, ow, k[0], k[1], stride[0], stride[1], pad[0],
+                                                     pad[1]))
+    return y
+
+
+def avgpool_backward(dy, x_shape, k, stride, pad):
+    dy = dy.contiguous()
+    n, c, h, w = x_shape
+    dx = torch.empty(n, c, h, w)
+    _lib().dcnn_cpu_avgpool_bwd(_ptr(dy), _ptr(dx), *_ci(n, c, h, w, dy.shape[2], dy.shape[3], k[0], k[1], stride[0],
+                                                       stride[1], pad[0], pad[1]))
+    return dx

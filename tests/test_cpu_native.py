@@ -133,3 +133,76 @@ def test_native_backend_trains_mnist_cnn(monkeypatch):
     assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-4
     for a, b in zip(p0, p1):
         assert torch.allclose(a, b, atol=1e-4)
+
+
+@pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
+def test_native_batchnorm_matches_aten(monkeypatch, relu, res):
+    from dcnn_b200.ops import cpu
+    torch.manual_seed(3)
+    x = torch.randn(6, 5, 7, 4) * 2 + 1
+    gamma, beta = torch.rand(5, 1, 1, 1) + 0.5, torch.randn(5, 1, 1, 1)
+    r = torch.randn_like(x) if res else None
+    dout = torch.randn_like(x)
+
+    def run():
+        rm, rv = torch.zeros(5), torch.ones(5)
+        mean, inv = cpu.bn_finalize(cpu.bn_stats(x), 1e-5, 0.1, rm, rv)
+        y = cpu.bn_apply(x, mean, inv, gamma, beta, r, relu)
+        dg, db = torch.zeros(5, 1, 1, 1), torch.zeros(5, 1, 1, 1)
+        dx, m = cpu.bn_backward(dout, x, y, mean, inv, gamma, dg, db, relu, True)
+        return [mean, inv, rm, rv, y, dx, m, dg, db]
+    want = run()
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    got = run()
+    for a, b in zip(got, want):
+        assert torch.allclose(a, b, atol=2e-5, rtol=1e-4), (a - b).abs().max()
+
+
+@pytest.mark.parametrize("k,s,p", [((2, 2), (2, 2), (0, 0)), ((3, 3), (2, 2), (1, 1)), ((3, 2), (1, 2), (1, 0)),
+                                   ((3, 3), (1, 1), (1, 1))])
+def test_native_pools_match_aten(monkeypatch, k, s, p):
+    from dcnn_b200.ops import cpu
+    torch.manual_seed(4)
+    x = torch.randn(3, 4, 9, 8)
+
+    def run():
+        y, idx = cpu.maxpool_forward(x, k, s, p)
+        g = torch.arange(y.numel(), dtype=torch.float32).reshape(y.shape) / 10
+        dx = cpu.maxpool_backward(g, idx, x.shape, k, s, p)
+        ya = cpu.avgpool_forward(x, k, s, p)
+        da = cpu.avgpool_backward(torch.ones_like(ya) * 0.5, x.shape, k, s, p)
+        return [y, idx, dx, ya, da]
+    want = run()
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    got = run()
+    for a, b in zip(got, want):
+        assert torch.allclose(a.double(), b.double(), atol=1e-5), (a.double() - b.double()).abs().max()
+    # ties: the first maximum in scan order gets the gradient
+    y, idx = cpu.maxpool_forward(torch.zeros(1, 1, 2, 2), (2, 2), (2, 2), (0, 0))
+    assert int(idx.reshape(-1)[0]) == 0
+
+
+def test_native_backend_trains_resnet9_like_aten(monkeypatch):
+    """Conv + BN + ReLU + residual blocks + pools + Dense through the native kernels == through ATen."""
+    from dcnn_b200 import nn as dnn
+    from dcnn_b200.models import create_resnet9_cifar10
+    from dcnn_b200.train import TrainStep
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(4, 3, 32, 32, generator=g)
+    t = F.one_hot(torch.randint(0, 10, (4,), generator=g), 10).float().reshape(4, 10, 1, 1)
+
+    def run():
+        m = create_resnet9_cifar10()
+        m.set_seed(5)
+        m.initialize()
+        o = dnn.SGD(0.01, 0.9)
+        o.attach(m.parameters(), m.gradients())
+        step = TrainStep(m, o, dnn.SoftmaxCrossEntropyLoss())
+        losses = [float(step(x, t)[0]) for _ in range(2)]
+        return losses, [p.clone() for p in m.parameters()], [b.clone() for b in m.buffers().values()]
+    l0, p0, b0 = run()
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    l1, p1, b1 = run()
+    assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-3
+    for a, b in zip(p0 + b0, p1 + b1):
+        assert torch.allclose(a, b, atol=2e-3, rtol=1e-2), (a - b).abs().max()
