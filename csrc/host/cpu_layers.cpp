@@ -203,3 +203,69 @@ DCNN_HOST_API void dcnn_cpu_avgpool_bwd(const float* dy, float* dx, int N, int C
     }
   }
 }
+
+// ------------------------------------------------------------------------------------------------ optimizers
+// One pass per tensor (ref src/nn/optimizers_impl/cpu: sgd / adam kernels; maths as adam_kernels.cu:24-60).
+// v = mu*v - lr*g; p += v   (mu == 0: p -= lr*g, `vel` may be NULL)
+DCNN_HOST_API void dcnn_cpu_sgd_update(float* p, float* g, float* vel, long long n, float lr, float mu, int zero_grads) {
+#pragma omp parallel for simd schedule(static) if (n > 32768)
+  for (long long i = 0; i < n; ++i) {
+    if (vel != nullptr && mu > 0.f) {
+      const float v = mu * vel[i] - lr * g[i];
+      vel[i] = v;
+      p[i] += v;
+    } else {
+      p[i] -= lr * g[i];
+    }
+    if (zero_grads) g[i] = 0.f;
+  }
+}
+
+// Adam (L2 weight decay folded into the update) / AdamW (decoupled), bias corrections passed in
+DCNN_HOST_API void dcnn_cpu_adam_update(float* p, float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                                        float eps, float bc1, float bc2, float wd, int decoupled, int zero_grads) {
+#pragma omp parallel for simd schedule(static) if (n > 32768)
+  for (long long i = 0; i < n; ++i) {
+    const float gi = g[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    float pi = p[i];
+    float upd = lr * (mi / bc1) / (sqrtf(vi / bc2) + eps);
+    if (wd > 0.f) {
+      if (decoupled) pi -= wd * lr * pi;
+      else upd += wd * lr * pi;
+    }
+    p[i] = pi - upd;
+    if (zero_grads) g[i] = 0.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ softmax cross-entropy
+// pred / target: [B][C] (targets one-hot).  out[0] = mean loss, out[1] = number of rows whose argmax matches the target's.
+// grad (optional) = (softmax(pred) - target) / B.
+DCNN_HOST_API void dcnn_cpu_softmax_ce(const float* pred, const float* target, float* grad, double* out, int B, int C) {
+  double loss = 0, correct = 0;
+#pragma omp parallel for schedule(static) reduction(+ : loss, correct) if ((long long)B * C > 16384)
+  for (int b = 0; b < B; ++b) {
+    const float* p = pred + (size_t)b * C;
+    const float* t = target + (size_t)b * C;
+    int pi = 0, ti = 0;
+    for (int c = 1; c < C; ++c) {
+      if (p[c] > p[pi]) pi = c;
+      if (t[c] > t[ti]) ti = c;
+    }
+    double s = 0;
+    for (int c = 0; c < C; ++c) s += exp((double)p[c] - (double)p[pi]);
+    loss += log(s) + (double)p[pi] - (double)p[ti];
+    correct += pi == ti ? 1.0 : 0.0;
+    if (grad != nullptr) {
+      float* g = grad + (size_t)b * C;
+      const double inv = 1.0 / s;
+      for (int c = 0; c < C; ++c) g[c] = (float)((exp((double)p[c] - (double)p[pi]) * inv - (double)t[c]) / B);
+    }
+  }
+  out[0] = loss / B;
+  out[1] = correct;
+}

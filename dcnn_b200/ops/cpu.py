@@ -351,6 +351,10 @@ def loss_forward_backward(kind, pred, target, param=0.0, want_grad=True):
     t = target.reshape(b, -1)
     n = p.shape[1]
     correct = None
+    nat = _native()
+    if nat is not None and p.dtype == torch.float32 and kind in ("softmax_crossentropy", "logsoftmax_crossentropy"):
+        loss, grad, correct = nat.softmax_ce(p, t, want_grad)
+        return loss, (grad.reshape(pred.shape) if grad is not None else None), correct
     if kind in ("softmax_crossentropy", "logsoftmax_crossentropy"):
         lse = torch.logsumexp(p.double(), dim=1)
         tgt = t.argmax(dim=1)
@@ -389,7 +393,14 @@ def loss_forward_backward(kind, pred, target, param=0.0, want_grad=True):
 # ----------------------------------------------------------------------------------------------
 # optimizers (multi-tensor semantics: lists of tensors updated in place)
 # ----------------------------------------------------------------------------------------------
+def _native_ok(tensors):
+    return all(t.dtype == torch.float32 and t.is_contiguous() for t in tensors)
+
+
 def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False, hyper=None):
+    nat = _native()
+    if nat is not None and _native_ok(list(params) + list(grads)):
+        return nat.sgd_update(params, grads, velocities, lr, momentum, zero_grads)
     for i, (p, g) in enumerate(zip(params, grads)):
         if momentum > 0:
             v = velocities[i]
@@ -404,6 +415,10 @@ def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False, hyper=
 def adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_decay, decoupled,
                 zero_grads=False, hyper=None):
     """ref adam_kernels.cu:24-60"""
+    nat = _native()
+    if nat is not None and _native_ok(list(params) + list(grads)):
+        return nat.adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_decay, decoupled,
+                               zero_grads)
     for p, g, m, v in zip(params, grads, ms, vs):
         m.mul_(beta1).add_(g, alpha=1 - beta1)
         v.mul_(beta2).addcmul_(g, g, value=1 - beta2)

@@ -316,3 +316,30 @@ def avgpool_backward(dy, x_shape, k, stride, pad):
     _lib().dcnn_cpu_avgpool_bwd(_ptr(dy), _ptr(dx), *_ci(n, c, h, w, dy.shape[2], dy.shape[3], k[0], k[1], stride[0],
                                                        stride[1], pad[0], pad[1]))
     return dx
+
+
+def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False):
+    for i, (p, g) in enumerate(zip(params, grads)):
+        v = velocities[i] if (velocities is not None and momentum > 0) else None
+        _lib().dcnn_cpu_sgd_update(_ptr(p), _ptr(g), _ptr(v) if v is not None else C.c_void_p(0),
+                                   C.c_longlong(p.numel()), C.c_float(lr), C.c_float(momentum),
+                                   C.c_int(1 if zero_grads else 0))
+
+
+def adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_decay, decoupled, zero_grads=False):
+    for p, g, m, v in zip(params, grads, ms, vs):
+        _lib().dcnn_cpu_adam_update(_ptr(p), _ptr(g), _ptr(m), _ptr(v), C.c_longlong(p.numel()), C.c_float(lr),
+                                    C.c_float(beta1), C.c_float(beta2), C.c_float(eps), C.c_float(bc1), C.c_float(bc2),
+                                    C.c_float(weight_decay), C.c_int(1 if decoupled else 0),
+                                    C.c_int(1 if zero_grads else 0))
+
+
+def softmax_ce(pred2d, target2d, want_grad=True):
+    """-> (loss tensor, grad [B, C] | None, correct-count tensor)."""
+    p, t = pred2d.contiguous(), target2d.contiguous()
+    b, c = p.shape
+    grad = torch.empty_like(p) if want_grad else None
+    out = torch.empty(2, dtype=torch.float64)
+    _lib().dcnn_cpu_softmax_ce(_ptr(p), _ptr(t), _ptr(grad) if grad is not None else C.c_void_p(0), _ptr(out),
+                               C.c_int(b), C.c_int(c))
+    return out[0].to(torch.float32), grad, out[1].to(torch.int64)

@@ -206,3 +206,42 @@ def test_native_backend_trains_resnet9_like_aten(monkeypatch):
     assert max(abs(a - b) for a, b in zip(l0, l1)) < 1e-3
     for a, b in zip(p0 + b0, p1 + b1):
         assert torch.allclose(a, b, atol=2e-3, rtol=1e-2), (a - b).abs().max()
+
+
+def test_native_optimizers_and_loss_match_aten(monkeypatch):
+    from dcnn_b200.ops import cpu
+    torch.manual_seed(5)
+
+    def tensors():
+        g = torch.Generator().manual_seed(9)
+        p = [torch.randn(33, 7, generator=g), torch.randn(100003, generator=g)]
+        gr = [torch.randn(33, 7, generator=g), torch.randn(100003, generator=g)]
+        return p, gr, [torch.zeros_like(t) for t in p], [torch.zeros_like(t) for t in p]
+
+    def run():
+        out = []
+        p, g, v, _ = tensors()
+        cpu.sgd_update(p, [t.clone() for t in g], v, 0.1, 0.9)
+        cpu.sgd_update(p, g, v, 0.1, 0.9, zero_grads=True)
+        out += p + v + g
+        p, g, _, _ = tensors()
+        cpu.sgd_update(p, g, None, 0.05, 0.0)
+        out += p
+        for decoupled in (False, True):
+            p, g, m, v = tensors()
+            cpu.adam_update(p, [t.clone() for t in g], m, v, 1e-2, 0.9, 0.999, 1e-8, 0.1, 0.001, 1e-2, decoupled)
+            cpu.adam_update(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, 0.19, 0.002, 1e-2, decoupled, zero_grads=True)
+            out += p + m + v + g
+        logits = torch.randn(9, 11, 1, 1, generator=torch.Generator().manual_seed(21))
+        tgt = F.one_hot(torch.arange(9) % 11, 11).float().reshape(9, 11, 1, 1)
+        loss, grad, correct = cpu.loss_forward_backward("softmax_crossentropy", logits, tgt)
+        loss2, none, _ = cpu.loss_forward_backward("logsoftmax_crossentropy", logits, tgt, want_grad=False)
+        assert none is None
+        out += [loss.reshape(1), grad, correct.reshape(1).float(), loss2.reshape(1)]
+        return out
+    want = run()
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    got = run()
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert torch.allclose(a.float(), b.float(), atol=1e-6, rtol=1e-5), (a.float() - b.float()).abs().max()
