@@ -53,4 +53,10 @@ g++ "${CXXFLAGS[@]}" -c "$HERE/ref_bench.cpp" -o "$OUT/obj/ref_bench.o"
 # initialisation, which is only safe when the runtime library is already loaded
 "$NVCC" --cudart shared -o "$OUT/bin/ref_bench" "$OUT/obj/ref_bench.o" "${OBJS[@]}" -gencode arch=compute_100,code=sm_100 \
    -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
-echo "built $OUT/bin/ref_bench"
+# BASELINE config 1 (MNIST CNN on the CPU): same objects, second harness
+g++ "${CXXFLAGS[@]}" -c "$HERE/ref_mnist_cpu.cpp" -o "$OUT/obj/ref_mnist_cpu.o"
+OBJS_NOBENCH=()
+for o in "${OBJS[@]}"; do OBJS_NOBENCH+=("$o"); done
+"$NVCC" --cudart shared -o "$OUT/bin/ref_mnist_cpu" "$OUT/obj/ref_mnist_cpu.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
+   -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
+echo "built $OUT/bin/ref_bench and $OUT/bin/ref_mnist_cpu"

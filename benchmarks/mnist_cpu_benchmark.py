@@ -1,0 +1,51 @@
+#!/usr/bin/env python
+"""BASELINE config 1: MNIST CNN (mnist_cnn_trainer's model), CPU, synthetic 28x28, batch 64, single process.
+Reports training images/s for the ATen CPU path and for this library's native CPU kernels (DCNN_CPU_BACKEND=native).
+Wall clock, 5 warm-up + 30 timed steps."""
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+from dcnn_b200 import nn  # noqa: E402
+from dcnn_b200.models import create_mnist_trainer  # noqa: E402
+from dcnn_b200.ops import cpu_native  # noqa: E402
+from dcnn_b200.train import TrainStep  # noqa: E402
+
+
+def run(batch=64, steps=30, warm=5):
+    m = create_mnist_trainer()
+    m.set_seed(1)
+    m.initialize()
+    m.compute_input_gradient = False
+    opt = nn.Adam(0.01, epsilon=1e-8)
+    opt.attach(m.parameters(), m.gradients())
+    step = TrainStep(m, opt, nn.LogSoftmaxCrossEntropyLoss())
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(batch, 1, 28, 28, generator=g)
+    t = torch.nn.functional.one_hot(torch.randint(0, 10, (batch,), generator=g), 10).float().reshape(batch, 10, 1, 1)
+    for _ in range(warm):
+        step(x, t)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss, _ = step(x, t)
+    dt = time.perf_counter() - t0
+    return batch * steps / dt, float(loss)
+
+
+def main():
+    threads = int(os.environ.get("NUM_THREADS", torch.get_num_threads()))
+    torch.set_num_threads(threads)
+    cpu_native.set_num_threads(threads)
+    os.environ["DCNN_CPU_BACKEND"] = "aten"
+    a, la = run()
+    os.environ["DCNN_CPU_BACKEND"] = "native"
+    n, ln = run()
+    print(f"MNIST CNN, CPU, batch 64, {threads} threads: ATen path {a:,.0f} images/s (loss {la:.4f}); "
+          f"native kernels {n:,.0f} images/s (loss {ln:.4f})")
+
+
+if __name__ == "__main__":
+    main()
