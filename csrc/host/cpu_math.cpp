@@ -9,6 +9,7 @@
 // -- rather than the reference's 32^3 blocked loops.  Everything is row-major with explicit leading dimensions.
 #include <immintrin.h>
 #include <omp.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -46,7 +47,73 @@ struct Micro<float> {
       _mm256_storeu_ps(acc + i * NR + 8, c[i][1]);
     }
   }
+  // C[i][0..NR) += alpha * (A-strip x B-strip)[i], straight into the output rows
+  static inline void run_direct(int kc, const float* a, const float* b, float* C, long long ldc, float alpha) {
+    __m256 c[MR][2];
+    for (int i = 0; i < MR; ++i) c[i][0] = c[i][1] = _mm256_setzero_ps();
+    for (int k = 0; k < kc; ++k) {
+      const __m256 b0 = _mm256_loadu_ps(b), b1 = _mm256_loadu_ps(b + 8);
+#pragma GCC unroll 6
+      for (int i = 0; i < MR; ++i) {
+        const __m256 ai = _mm256_broadcast_ss(a + i);
+        c[i][0] = _mm256_fmadd_ps(ai, b0, c[i][0]);
+        c[i][1] = _mm256_fmadd_ps(ai, b1, c[i][1]);
+      }
+      a += MR;
+      b += NR;
+    }
+    const __m256 va = _mm256_set1_ps(alpha);
+    for (int i = 0; i < MR; ++i) {
+      float* r = C + i * ldc;
+      _mm256_storeu_ps(r, _mm256_fmadd_ps(va, c[i][0], _mm256_loadu_ps(r)));
+      _mm256_storeu_ps(r + 8, _mm256_fmadd_ps(va, c[i][1], _mm256_loadu_ps(r + 8)));
+    }
+  }
 };
+
+// AVX-512 variant (12 x 32 tile: 24 zmm accumulators), selected at run time when the CPU has avx512f.  The functions
+// carry their own target attribute so the rest of the library keeps the portable x86-64-v3 baseline.
+#define DCNN_AVX512 __attribute__((target("avx512f,fma")))
+struct MicroF512 {
+  static constexpr int MR = 12, NR = 32;
+  DCNN_AVX512 static inline void mac(int kc, const float* a, const float* b, __m512 (&c)[MR][2]) {
+    for (int i = 0; i < MR; ++i) c[i][0] = c[i][1] = _mm512_setzero_ps();
+    for (int k = 0; k < kc; ++k) {
+      const __m512 b0 = _mm512_loadu_ps(b), b1 = _mm512_loadu_ps(b + 16);
+#pragma GCC unroll 12
+      for (int i = 0; i < MR; ++i) {
+        const __m512 ai = _mm512_set1_ps(a[i]);
+        c[i][0] = _mm512_fmadd_ps(ai, b0, c[i][0]);
+        c[i][1] = _mm512_fmadd_ps(ai, b1, c[i][1]);
+      }
+      a += MR;
+      b += NR;
+    }
+  }
+  DCNN_AVX512 static void run(int kc, const float* a, const float* b, float* acc) {
+    __m512 c[MR][2];
+    mac(kc, a, b, c);
+    for (int i = 0; i < MR; ++i) {
+      _mm512_storeu_ps(acc + i * NR, c[i][0]);
+      _mm512_storeu_ps(acc + i * NR + 16, c[i][1]);
+    }
+  }
+  DCNN_AVX512 static void run_direct(int kc, const float* a, const float* b, float* C, long long ldc, float alpha) {
+    __m512 c[MR][2];
+    mac(kc, a, b, c);
+    const __m512 va = _mm512_set1_ps(alpha);
+    for (int i = 0; i < MR; ++i) {
+      float* r = C + i * ldc;
+      _mm512_storeu_ps(r, _mm512_fmadd_ps(va, c[i][0], _mm512_loadu_ps(r)));
+      _mm512_storeu_ps(r + 16, _mm512_fmadd_ps(va, c[i][1], _mm512_loadu_ps(r + 16)));
+    }
+  }
+};
+
+static bool has_avx512() {
+  static const bool v = __builtin_cpu_supports("avx512f") && getenv("DCNN_CPU_NO_AVX512") == nullptr;
+  return v;
+}
 
 template <>
 struct Micro<double> {
@@ -70,13 +137,18 @@ struct Micro<double> {
       _mm256_storeu_pd(acc + i * NR + 4, c[i][1]);
     }
   }
+  static inline void run_direct(int kc, const double* a, const double* b, double* C, long long ldc, double alpha) {
+    alignas(32) double acc[MR * NR];
+    run(kc, a, b, acc);
+    for (int i = 0; i < MR; ++i)
+      for (int j = 0; j < NR; ++j) C[i * ldc + j] += alpha * acc[i * NR + j];
+  }
 };
 
 // ------------------------------------------------------------------------------------------------ packing
 // op(A)(i,k) = A[i*rs + k*cs]; strips of MR rows, zero padded: dst[strip][k][MR]
-template <typename T>
+template <typename T, int MR>
 void pack_a(const T* A, long long rs, long long cs, int mc, int kc, T* dst) {
-  constexpr int MR = Micro<T>::MR;
   for (int i0 = 0; i0 < mc; i0 += MR) {
     const int mr = std::min(MR, mc - i0);
     for (int k = 0; k < kc; ++k) {
@@ -88,9 +160,8 @@ void pack_a(const T* A, long long rs, long long cs, int mc, int kc, T* dst) {
 }
 
 // op(B)(k,j) = B[k*rs + j*cs]; one strip of NR columns: dst[k][NR]
-template <typename T>
+template <typename T, int NR>
 void pack_b_strip(const T* B, long long rs, long long cs, int kc, int nr, T* dst) {
-  constexpr int NR = Micro<T>::NR;
   if (cs == 1 && nr == NR) {
     for (int k = 0; k < kc; ++k) memcpy(dst + (long long)k * NR, B + (long long)k * rs, NR * sizeof(T));
     return;
@@ -102,11 +173,11 @@ void pack_b_strip(const T* B, long long rs, long long cs, int kc, int nr, T* dst
   }
 }
 
-template <typename T>
+template <typename KERNEL, typename T>
 void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A, int lda, const T* B, int ldb, T beta,
                T* C, int ldc) {
-  constexpr int MR = Micro<T>::MR, NR = Micro<T>::NR;
-  constexpr int MC = 96, KC = 256, NC = 2048;
+  constexpr int MR = KERNEL::MR, NR = KERNEL::NR;
+  constexpr int MC = 96, KC = 256, NC = 2048;   // MC is a multiple of both MR = 6 and MR = 12
   if (M <= 0 || N <= 0) return;
   // C *= beta once, up front (beta == 0 overwrites: NaNs in C must not propagate)
 #pragma omp parallel for schedule(static) if ((long long)M * N > 16384)
@@ -123,7 +194,7 @@ void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A,
 #pragma omp parallel if (par)
   {
     std::vector<T> apack((size_t)(MC + MR) * KC);
-    alignas(32) T acc[MR * NR];
+    alignas(64) T acc[MR * NR];
     for (int jc = 0; jc < N; jc += NC) {
       const int nc = std::min(NC, N - jc);
       const int strips = (nc + NR - 1) / NR;
@@ -132,7 +203,7 @@ void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A,
 #pragma omp for schedule(static)
         for (int s = 0; s < strips; ++s) {
           const int j0 = jc + s * NR;
-          pack_b_strip(B + (long long)pc * b_rs + (long long)j0 * b_cs, b_rs, b_cs, kc, std::min(NR, N - j0),
+          pack_b_strip<T, NR>(B + (long long)pc * b_rs + (long long)j0 * b_cs, b_rs, b_cs, kc, std::min(NR, N - j0),
                        bpack.data() + (size_t)s * kc * NR);
         }  // implicit barrier: the panel is complete before anyone multiplies
         // tasks = (MC block) x (group of B strips): when M is small the strip groups supply the parallelism (each
@@ -147,19 +218,17 @@ void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A,
             const int ic = ib * MC, mc = std::min(MC, M - ic);
             const int s_lo = g * per_group, s_hi = std::min(strips, s_lo + per_group);
             if (s_lo >= s_hi) continue;
-            pack_a(A + (long long)ic * a_rs + (long long)pc * a_cs, a_rs, a_cs, mc, kc, apack.data());
+            pack_a<T, MR>(A + (long long)ic * a_rs + (long long)pc * a_cs, a_rs, a_cs, mc, kc, apack.data());
             for (int s = s_lo; s < s_hi; ++s) {
               const int j0 = jc + s * NR, nr = std::min(NR, N - j0);
               const T* bp = bpack.data() + (size_t)s * kc * NR;
               for (int i0 = 0; i0 < mc; i0 += MR) {
                 const int mr = std::min(MR, mc - i0);
-                Micro<T>::run(kc, apack.data() + (size_t)(i0 / MR) * kc * MR, bp, acc);
                 T* c = C + (long long)(ic + i0) * ldc + j0;
-                if (mr == MR && nr == NR) {
-                  for (int i = 0; i < MR; ++i)
-#pragma omp simd
-                    for (int j = 0; j < NR; ++j) c[(long long)i * ldc + j] += alpha * acc[i * NR + j];
+                if (mr == MR && nr == NR) {   // full tile: accumulate straight into C
+                  KERNEL::run_direct(kc, apack.data() + (size_t)(i0 / MR) * kc * MR, bp, c, ldc, alpha);
                 } else {
+                  KERNEL::run(kc, apack.data() + (size_t)(i0 / MR) * kc * MR, bp, acc);
                   for (int i = 0; i < mr; ++i)
                     for (int j = 0; j < nr; ++j) c[(long long)i * ldc + j] += alpha * acc[i * NR + j];
                 }
@@ -351,11 +420,14 @@ DCNN_HOST_API int dcnn_cpu_get_threads() { return omp_get_max_threads(); }
 // (A is stored K x M when transA, B is stored N x K when transB).
 DCNN_HOST_API void dcnn_cpu_sgemm(int transA, int transB, int M, int N, int K, float alpha, const float* A, int lda,
                                   const float* B, int ldb, float beta, float* C, int ldc) {
-  gemm_impl<float>(transA, transB, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+  // the 12 x 32 tile only pays off when the problem has enough full tiles; skinny products (a conv with 8 output
+  // channels is an 8 x N GEMM) stay on the 6 x 16 kernel
+  if (has_avx512() && M >= 48 && N >= 64) gemm_impl<MicroF512, float>(transA, transB, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+  else gemm_impl<Micro<float>, float>(transA, transB, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
 }
 DCNN_HOST_API void dcnn_cpu_dgemm(int transA, int transB, int M, int N, int K, double alpha, const double* A, int lda,
                                   const double* B, int ldb, double beta, double* C, int ldc) {
-  gemm_impl<double>(transA, transB, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+  gemm_impl<Micro<double>, double>(transA, transB, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
 }
 
 DCNN_HOST_API float dcnn_cpu_sdot(const float* a, const float* b, long long n) {
