@@ -64,7 +64,7 @@ static std::vector<float> randv(size_t n) {
 }
 
 static void test_gemm() {
-  const int sizes[][3] = {{1, 1, 1}, {5, 7, 3}, {6, 16, 8}, {7, 17, 9}, {97, 33, 129}, {13, 100, 300}, {130, 5, 257}};
+  const int sizes[][3] = {{1, 1, 1}, {5, 7, 3}, {6, 16, 8}, {7, 17, 9}, {97, 33, 129}, {13, 100, 300}, {130, 5, 257}, {100, 130, 70}, {61, 97, 300}};
   for (auto& s : sizes) {
     const int M = s[0], N = s[1], K = s[2];
     for (int ta = 0; ta < 2; ++ta)
