@@ -19,6 +19,9 @@ def run(args):
                           "only the single-GPU reference arm exists"}))
         return 0
     cmd = [BIN, str(args.batch), str(args.steps), str(args.warmup)]
+    model = getattr(args, "model", "resnet50_tiny_imagenet")
+    if model != "resnet50_tiny_imagenet":      # other BASELINE.json configs: same harness, another zoo model
+        cmd.append(model)
     r = subprocess.run(cmd, capture_output=True, text=True)
     line = None
     for l in r.stdout.splitlines():

@@ -118,8 +118,26 @@ def parse():
     ap.add_argument("--batch", type=int, default=int(os.environ.get("BENCH_BATCH", 256)), help="per-GPU batch")
     ap.add_argument("--parallelism", default=os.environ.get("BENCH_PARALLELISM", "auto"))
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--model", default=os.environ.get("BENCH_MODEL", "resnet50_tiny_imagenet"),
+                    help="dcnn_b200.models.MODEL_ZOO key; the headline benchmark is the default (BASELINE.json)")
     ap.add_argument("--microbatches", type=int, default=1)
     return ap.parse_args()
+
+
+def model_spec(name):
+    """(display name, image shape, classes, optimizer constructor arguments as in the reference's example for that model,
+    optimizer description) -- the other BASELINE.json configs use the same harness with another --model."""
+    if name == "resnet50_tiny_imagenet":
+        return MODEL, IMG, CLASSES, dict(lr=1e-4, epsilon=1e-3, weight_decay=1e-3), "Adam(lr 1e-4, eps 1e-3, wd 1e-3)"
+    if "tiny_imagenet" in name:      # examples/tiny_imagenet_resnet18.cpp / resnet34.cpp
+        return name, (3, 64, 64), 200, dict(lr=1e-4, epsilon=1e-7), "Adam(lr 1e-4, eps 1e-7)"
+    if "cifar100" in name:
+        return name, (3, 32, 32), 100, dict(lr=1e-3, epsilon=1e-8), "Adam(lr 1e-3, eps 1e-8)"
+    if "cifar10" in name:            # examples/cifar10_resnet9.cpp
+        return name, (3, 32, 32), 10, dict(lr=1e-3, epsilon=1e-8, weight_decay=5e-4), "Adam(lr 1e-3, eps 1e-8, wd 5e-4)"
+    if "mnist" in name:
+        return name, (1, 28, 28), 10, dict(lr=1e-2, epsilon=1e-8), "Adam(lr 1e-2, eps 1e-8)"
+    raise SystemExit(f"--model {name}: no input shape is associated with this model")
 
 
 def reference_arm(args):
@@ -138,7 +156,7 @@ def main():
     import torch
     import torch.distributed as dist
     from dcnn_b200 import _lib, nn
-    from dcnn_b200.models import create_resnet50_tiny_imagenet
+    from dcnn_b200.models import MODEL_ZOO
     from dcnn_b200.train import TrainStep
 
     rank = int(os.environ.get("RANK", 0))
@@ -162,9 +180,13 @@ def main():
             faulthandler.dump_traceback_later(float(os.environ["DCNN_HANG_DUMP_S"]), exit=True)
 
     torch.manual_seed(1234)
-    model = create_resnet50_tiny_imagenet()
+    if args.model not in MODEL_ZOO:
+        raise SystemExit(f"--model {args.model}: not in MODEL_ZOO ({sorted(MODEL_ZOO)})")
+    model_name, img, classes, opt_args, opt_desc = model_spec(args.model)
+    headline = args.model == "resnet50_tiny_imagenet"
+    model = MODEL_ZOO[args.model]()
     model.set_seed(42)           # identical initial weights on every replica
-    opt = nn.Adam(1e-4, epsilon=1e-3, weight_decay=1e-3)   # examples/tiny_imagenet_resnet50.cpp:90
+    opt = nn.Adam(opt_args.pop("lr"), **opt_args)   # headline: examples/tiny_imagenet_resnet50.cpp:90
     loss_fn = nn.LogSoftmaxCrossEntropyLoss()
 
     # ---- parallelism: single | dpR | ppS | ppSxdpR   (rank = replica * S + stage)
@@ -196,17 +218,17 @@ def main():
             from dcnn_b200.partitioner import measure_layer_costs
             costs = [None]
             if rank == 0:
-                probe = create_resnet50_tiny_imagenet()
+                probe = MODEL_ZOO[args.model]()
                 probe.set_seed(42)
                 probe.set_device(dev)
                 probe.initialize()
-                costs = [measure_layer_costs(probe, [max(1, args.batch * S // mb), *IMG])]
+                costs = [measure_layer_costs(probe, [max(1, args.batch * S // mb), *img])]
                 del probe
                 torch.cuda.empty_cache()
             dist.broadcast_object_list(costs, src=0)
             partitioner = BalancedPartitioner(costs=costs[0])
         else:
-            partitioner = BalancedPartitioner(input_shape=[args.batch, *IMG])
+            partitioner = BalancedPartitioner(input_shape=[args.batch, *img])
         parts = partitioner.get_partitions(model.get_layers(), S)
         engine = PipelineEngine(model, parts, stage, opt, loss_fn, mb, links, dev,
                                 schedule=os.environ.get("SCHEDULE", "semi_async"), dp_group=dp_g if R > 1 else None,
@@ -238,9 +260,9 @@ def main():
     B = args.batch * S          # batch fed to one pipeline replica: per-GPU work stays fixed
     g = torch.Generator().manual_seed(1000 + rank // S)
     nbuf = 4
-    host_x = [torch.randn(B, *IMG, generator=g).pin_memory() for _ in range(nbuf)]
-    host_t = [torch.nn.functional.one_hot(torch.randint(0, CLASSES, (B,), generator=g), CLASSES).float()
-              .reshape(B, CLASSES, 1, 1).pin_memory() for _ in range(nbuf)]
+    host_x = [torch.randn(B, *img, generator=g).pin_memory() for _ in range(nbuf)]
+    host_t = [torch.nn.functional.one_hot(torch.randint(0, classes, (B,), generator=g), classes).float()
+              .reshape(B, classes, 1, 1).pin_memory() for _ in range(nbuf)]
     dev_x = [x.to(dev) for x in host_x]
     dev_t = [t.to(dev) for t in host_t]
 
@@ -326,14 +348,15 @@ def main():
         except (OSError, ValueError):
             pass
         out = {
-            "metric": "train images/sec ResNet-50 64x64 (Tiny-ImageNet shape), max over ranks",
+            "metric": "train images/sec ResNet-50 64x64 (Tiny-ImageNet shape), max over ranks" if headline
+            else f"train images/sec {model_name} {img[1]}x{img[2]}, max over ranks",
             "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": (value / base) if base else None,
             "dtype": "fp32 storage, tf32 tensor-core MMA, fp32 accumulate", "data": "synthetic", "impl": "ours",
-            "config": {"model": MODEL, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
-                       "image": "3x64x64", "classes": CLASSES, "parallelism": parallelism,
-                       "optimizer": "Adam(lr 1e-4, eps 1e-3, wd 1e-3)", "loss": "LogSoftmaxCrossEntropy",
+            "config": {"model": model_name, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
+                       "image": "x".join(map(str, img)), "classes": classes, "parallelism": parallelism,
+                       "optimizer": opt_desc, "loss": "LogSoftmaxCrossEntropy",
                        "cuda_graph": (step._graph is not None) or
                                      (engine is not None and getattr(engine, "_graphs", None) is not None),
                        "microbatches": args.microbatches,
