@@ -281,6 +281,37 @@ double dot_impl<double>(const double* a, const double* b, long long n) {
   return r;
 }
 
+// C[M,N] = alpha * A[M,K] * B[N,K]^T + beta * C for SMALL M and N and a LONG K (both operands contiguous along K): the
+// weight gradient of a convolution with few channels is exactly this (8 x 25 outputs, K = N*OH*OW = 36 864 for the first
+// MNIST layer).  The blocked kernel would spend its time packing and synchronising per 256-deep panel; here every
+// thread takes a slice of K, forms its M x N partial with the FMA dot product, and the partials are summed in thread
+// order (deterministic for a given thread count).
+template <typename T>
+void gemm_nt_long_k(int M, int N, int K, T alpha, const T* A, int lda, const T* B, int ldb, T beta, T* C, int ldc) {
+  constexpr int kChunk = 2048;
+  const int chunks = (K + kChunk - 1) / kChunk;
+  const int nt = std::max(1, std::min(omp_get_max_threads(), chunks));
+  std::vector<T> part((size_t)nt * M * N, T(0));
+#pragma omp parallel num_threads(nt)
+  {
+    T* mine = part.data() + (size_t)omp_get_thread_num() * M * N;
+#pragma omp for schedule(static)
+    for (int c = 0; c < chunks; ++c) {
+      const int k0 = c * kChunk, len = std::min(kChunk, K - k0);
+      for (int i = 0; i < M; ++i)
+        for (int j = 0; j < N; ++j)
+          mine[i * N + j] += dot_impl<T>(A + (long long)i * lda + k0, B + (long long)j * ldb + k0, len);
+    }
+  }
+  for (int i = 0; i < M; ++i)
+    for (int j = 0; j < N; ++j) {
+      T s = T(0);
+      for (int t = 0; t < nt; ++t) s += part[(size_t)t * M * N + i * N + j];
+      T& c = C[(long long)i * ldc + j];
+      c = (beta == T(0) ? T(0) : beta * c) + alpha * s;
+    }
+}
+
 // Parallel reduction of per-chunk results in a fixed order (deterministic for a given thread count-independent
 // chunking: the chunk size does not depend on the number of threads).
 template <typename T, typename F>
@@ -420,6 +451,10 @@ DCNN_HOST_API int dcnn_cpu_get_threads() { return omp_get_max_threads(); }
 // (A is stored K x M when transA, B is stored N x K when transB).
 DCNN_HOST_API void dcnn_cpu_sgemm(int transA, int transB, int M, int N, int K, float alpha, const float* A, int lda,
                                   const float* B, int ldb, float beta, float* C, int ldc) {
+  if (!transA && transB && M <= 64 && N <= 512 && (long long)M * N <= 4096 && K >= 4096 && alpha != 0.f) {
+    gemm_nt_long_k<float>(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+    return;
+  }
   // the 12 x 32 tile only pays off when the problem has enough full tiles; skinny products (a conv with 8 output
   // channels is an 8 x N GEMM) stay on the 6 x 16 kernel
   if (has_avx512() && M >= 48 && N >= 64) gemm_impl<MicroF512, float>(transA, transB, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);

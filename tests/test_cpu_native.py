@@ -245,3 +245,20 @@ def test_native_optimizers_and_loss_match_aten(monkeypatch):
     assert len(got) == len(want)
     for a, b in zip(got, want):
         assert torch.allclose(a.float(), b.float(), atol=1e-6, rtol=1e-5), (a.float() - b.float()).abs().max()
+
+
+@pytest.mark.parametrize("M,N_,K", [(8, 25, 36864), (1, 1, 4096), (48, 80, 5000), (64, 64, 4097)])
+def test_sgemm_long_k_nt_path(M, N_, K):
+    """Small M x N with a long K and both operands K-contiguous (a conv weight gradient) takes the split-K dot path."""
+    torch.manual_seed(K)
+    a, b = torch.randn(M, K), torch.randn(N_, K)
+    want = (a.double() @ b.double().t()).float()
+    got = N.gemm(a, b, trans_b=True)
+    assert _rel(got, want) < 1e-5
+    c = torch.randn(M, N_)
+    want2 = (0.5 * want.double() + 2.0 * c.double()).float()
+    N.gemm(a, b, trans_b=True, alpha=0.5, beta=2.0, c=c)
+    assert _rel(c, want2) < 1e-5
+    nanc = torch.full((M, N_), float("nan"))
+    N.gemm(a, b, trans_b=True, beta=0.0, c=nanc)
+    assert torch.isfinite(nanc).all()
