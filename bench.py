@@ -165,11 +165,37 @@ def main():
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N > 1")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
+    # BENCH_DEVICE=cpu: plumbing check of THIS SCRIPT on a machine without a GPU (tests/test_bench_contract.py).  Every
+    # number it prints is meaningless and marked as such; the benchmark proper always runs on CUDA.
+    cpu_mode = os.environ.get("BENCH_DEVICE", "cuda") == "cpu"
+
+    class _CpuEvent:
+        def record(self):
+            self.t = time.perf_counter()
+
+        def elapsed_time(self, other):
+            return (other.t - self.t) * 1000.0
+
+    def new_event():
+        return _CpuEvent() if cpu_mode else torch.cuda.Event(enable_timing=True)
+
+    def pin(t):
+        return t if cpu_mode else t.pin_memory()
+
+    def device_sync():
+        if not cpu_mode:
+            torch.cuda.synchronize()
+
+    if cpu_mode:
+        dev = torch.device("cpu")
+    else:
+        torch.cuda.set_device(local_rank)
+        dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if args.parallelism.startswith("pp"):
+        if cpu_mode:
+            dist.init_process_group("gloo")
+        elif args.parallelism.startswith("pp"):
             # lazy communicator creation: in eager mode (device_id given) NCCL treats every unbatched isend/irecv of a
             # group as a collective serialised with all other ops of that group
             dist.init_process_group("nccl")
@@ -224,7 +250,8 @@ def main():
                 probe.initialize()
                 costs = [measure_layer_costs(probe, [max(1, args.batch * S // mb), *img])]
                 del probe
-                torch.cuda.empty_cache()
+                if not cpu_mode:
+                    torch.cuda.empty_cache()
             dist.broadcast_object_list(costs, src=0)
             partitioner = BalancedPartitioner(costs=costs[0])
         else:
@@ -260,16 +287,16 @@ def main():
     B = args.batch * S          # batch fed to one pipeline replica: per-GPU work stays fixed
     g = torch.Generator().manual_seed(1000 + rank // S)
     nbuf = 4
-    host_x = [torch.randn(B, *img, generator=g).pin_memory() for _ in range(nbuf)]
-    host_t = [torch.nn.functional.one_hot(torch.randint(0, classes, (B,), generator=g), classes).float()
-              .reshape(B, classes, 1, 1).pin_memory() for _ in range(nbuf)]
+    host_x = [pin(torch.randn(B, *img, generator=g)) for _ in range(nbuf)]
+    host_t = [pin(torch.nn.functional.one_hot(torch.randint(0, classes, (B,), generator=g), classes).float()
+                  .reshape(B, classes, 1, 1)) for _ in range(nbuf)]
     dev_x = [x.to(dev) for x in host_x]
     dev_t = [t.to(dev) for t in host_t]
 
     def barrier():
         if world > 1:
             dist.barrier()
-        torch.cuda.synchronize()
+        device_sync()
 
     # ---- kernel-only arm: inputs already resident, no host read-back inside the timed region
     # at least 3 untimed steps whatever --warmup says: the first two run eagerly (lazy init, pointer tables) and the
@@ -278,11 +305,11 @@ def main():
         step(dev_x[i % nbuf], dev_t[i % nbuf])
     barrier()
     sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else 0,
-                           getattr(torch.cuda.get_device_properties(dev), "uuid", None))
+                           None if cpu_mode else getattr(torch.cuda.get_device_properties(dev), "uuid", None))
     if rank == 0:
         sampler.start()
     _lib.reset_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0, e1 = new_event(), new_event()
     barrier()
     e0.record()
     for i in range(args.steps):
@@ -302,11 +329,11 @@ def main():
     # ---- end-to-end arm: public API, pinned-host -> device copy of every batch + loss read-back every step
     h2d = host_x[0].numel() * 4 + host_t[0].numel() * 4
     d2h = 8
-    out_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+    out_host = pin(torch.zeros(2, dtype=torch.float32))
     for i in range(2):
         step(host_x[i % nbuf].to(dev, non_blocking=True), host_t[i % nbuf].to(dev, non_blocking=True))
     barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0, f1 = new_event(), new_event()
     f0.record()
     for i in range(args.steps):
         x = host_x[i % nbuf].to(dev, non_blocking=True)
@@ -315,7 +342,8 @@ def main():
         if loss is not None:
             out_host[0].copy_(loss, non_blocking=True)
             out_host[1].copy_(correct, non_blocking=True)
-        torch.cuda.current_stream().synchronize()     # the step's result is on the host before the next step
+        if not cpu_mode:
+            torch.cuda.current_stream().synchronize()     # the step's result is on the host before the next step
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
@@ -353,7 +381,8 @@ def main():
             "value": round(value, 2), "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": (value / base) if base else None,
-            "dtype": "fp32 storage, tf32 tensor-core MMA, fp32 accumulate", "data": "synthetic", "impl": "ours",
+            "dtype": "fp32 storage, tf32 tensor-core MMA, fp32 accumulate" if not cpu_mode
+            else "CPU DRY RUN OF THE SCRIPT -- not a measurement", "data": "synthetic", "impl": "ours",
             "config": {"model": model_name, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
                        "image": "x".join(map(str, img)), "classes": classes, "parallelism": parallelism,
                        "optimizer": opt_desc, "loss": "LogSoftmaxCrossEntropy",
