@@ -1373,7 +1373,12 @@ static int launch_conv5(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
 
 // conv_tc5 (CTA pairs, 256 x 256 tiles): opt-in with DCNN_CONV_2CTA=1, for Cout >= 256 (Cout % 4 == 0) when there is at
 // least one pair tile per CTA pair.  Uses conv_tc2's 128-pixel boxes, so the statistics-tile count is unchanged.
+// Per-thread override of the variant choice, used by the autotuner (ops/cuda.py): 0 = the rules below, 2 = conv_tc2,
+// 3 = conv_tc3 wherever it is structurally possible, 5 = conv_tc5 wherever it is structurally possible.
+static thread_local int g_conv_variant = 0;
+
 static bool conv_2cta_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout) {
+  if (g_conv_variant != 0) return g_conv_variant == 5 && (Cout & 3) == 0 && Cout >= 256;
   const char* e = getenv("DCNN_CONV_2CTA");
   if (e == nullptr || atoi(e) == 0 || (Cout & 3) != 0 || Cout < 256) return false;
   int bn = 1, bh = 1, bw = 1;
@@ -1390,9 +1395,11 @@ static bool conv_v3_enabled() {
   return on;
 }
 static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int* bn, int* bh, int* bw) {
-  if (!conv_v3_enabled() || (Cout & 3) != 0) return false;
+  if (g_conv_variant != 0 && g_conv_variant != 3) return false;
+  if ((g_conv_variant == 0 && !conv_v3_enabled()) || (Cout & 3) != 0) return false;
   *bn = *bh = *bw = 1;
   choose_box(N, OH, OW, 2 * kBM, mul_h, mul_w, bn, bh, bw);
+  if (g_conv_variant == 3) return true;
   const long long m_tiles = (long long)ceil_div(OW, *bw) * ceil_div(OH, *bh) * ceil_div(N, *bn);
   return m_tiles >= num_sms();
 }
@@ -1429,6 +1436,13 @@ DCNN_API int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w) {
   int bn = 1, bh = 1, bw = 1;
   choose_box(N, OH, OW, kBM, mul_h, mul_w, &bn, &bh, &bw);
   return ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
+}
+
+// Autotuner hook: force a convolution kernel variant for the calls this thread makes next (0 restores the rules).
+DCNN_API int dcnn_conv_tc_set_variant(int variant) {
+  DCNN_REQUIRE(variant == 0 || variant == 2 || variant == 3 || variant == 5, "unknown conv variant %d", variant);
+  g_conv_variant = variant;
+  return 0;
 }
 
 // Number of BatchNorm partial-statistics tiles dcnn_conv_tc will emit for this problem (the partials buffer holds

@@ -106,6 +106,46 @@ def _packed_weights(w, Kp):
     return wp.view(Cout, Kp, 1, 1).contiguous(memory_format=CL)
 
 
+# DCNN_AUTOTUNE=1: the first time a convolution shape is seen (outside CUDA-graph capture) every structurally possible
+# kernel variant -- conv_tc2 (128-pixel tiles), conv_tc3 (256-pixel tiles), conv_tc5 (CTA pairs, Cout >= 256) -- is timed
+# with CUDA events on that very call's operands and the fastest is used from then on, instead of the built-in size
+# rules.  Opt-in until its first hardware run.
+AUTOTUNE = os.environ.get("DCNN_AUTOTUNE", "0") == "1"
+_TUNED = {}
+
+
+def _autotuned(key, cout, fn, tunable=True):
+    """Run ``fn()`` (one convolution launch sequence, idempotent when ``tunable``) under the variant chosen for ``key``."""
+    if not AUTOTUNE:
+        return fn()
+    v = _TUNED.get(key)
+    if v is None:
+        if not tunable or torch.cuda.is_current_stream_capturing():
+            return fn()
+        best_t = None
+        for cand in (2, 3, 5) if cout >= 256 else (2, 3):
+            check(lib().dcnn_conv_tc_set_variant(I(cand)), "conv_tc_set_variant")
+            try:
+                fn()                                                 # warm (attribute set-up, descriptor caches)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3):
+                    fn()
+                e1.record()
+                e1.synchronize()
+                t = e0.elapsed_time(e1)
+            finally:
+                check(lib().dcnn_conv_tc_set_variant(I(0)), "conv_tc_set_variant")
+            if best_t is None or t < best_t:
+                best_t, v = t, cand
+        _TUNED[key] = v
+    check(lib().dcnn_conv_tc_set_variant(I(v)), "conv_tc_set_variant")
+    try:
+        return fn()
+    finally:
+        check(lib().dcnn_conv_tc_set_variant(I(0)), "conv_tc_set_variant")
+
+
 def _conv_tc(x, N, H, W, Cin, w, Cout, Ktot, out, out_off, sn, sh, sw, OH, OW, mul_h, mul_w, taps, bias,
              accumulate, partials):
     n, dh, dw, wi = taps
@@ -136,15 +176,17 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
             [r - ph for r in range(R) for s in range(S)],
             [s - pw for r in range(R) for s in range(S)],
             [r * S + s for r in range(R) for s in range(S)]))
-        stats = None
-        partials = None
-        if want_stats:
-            tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_), I(Cout))
-            partials = torch.empty(tiles * (2 * Cout + 1), device=x.device, dtype=torch.float32)
-            stats = CudaStats(partials, tiles, Cout, N * OH * OW)
-        _conv_tc(x, N, H, W, Cin, w, Cout, R * S * Cin, y, 0, OH * OW * Cout, OW * Cout, Cout, OH, OW, sh_, sw_,
-                 taps, bias, False, partials)
-        return y, stats
+        def run():
+            stats = None
+            partials = None
+            if want_stats:      # the statistics-tile count depends on the kernel variant in force
+                tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_), I(Cout))
+                partials = torch.empty(tiles * (2 * Cout + 1), device=x.device, dtype=torch.float32)
+                stats = CudaStats(partials, tiles, Cout, N * OH * OW)
+            _conv_tc(x, N, H, W, Cin, w, Cout, R * S * Cin, y, 0, OH * OW * Cout, OW * Cout, Cout, OH, OW, sh_, sw_,
+                     taps, bias, False, partials)
+            return y, stats
+        return _autotuned(("f", N, H, W, Cin, Cout, R, S, sh_, sw_), Cout, run)
     check(lib().dcnn_conv_fprop_simt(_p(x), _p(w), _p(bias), _p(y), I(N), I(H), I(W), I(Cin), I(Cout), I(R), I(S),
                                      I(sh_), I(sw_), I(ph), I(pw), _stream()), "dcnn_conv_fprop_simt")
     return y, (bn_stats(y) if want_stats else None)
@@ -176,9 +218,12 @@ def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False
             [r2 - (R - 1 - ph) for r2 in range(R) for s2 in range(S)],
             [s2 - (S - 1 - pw) for r2 in range(R) for s2 in range(S)],
             [r2 * S + s2 for r2 in range(R) for s2 in range(S)]))
-        _conv_tc(dy, N, OH, OW, K, wt, Cin, R * S * K, dx, 0, H * W * Cin, W * Cin, Cin, H, W, 1, 1, taps, None,
-                 accumulate, None)
-        return dx
+        def run():
+            _conv_tc(dy, N, OH, OW, K, wt, Cin, R * S * K, dx, 0, H * W * Cin, W * Cin, Cin, H, W, 1, 1, taps, None,
+                     accumulate, None)
+            return dx
+        # an accumulating call is not idempotent: it uses the variant tuned by a plain call of the same shape, if any
+        return _autotuned(("d", N, H, W, Cin, K, R, S), Cin, run, tunable=not accumulate)
     if use_tc:
         # strided dgrad = one stride-1 tap-subset convolution per output parity class, written with an output stride
         wt = _dgrad_weights(w)

@@ -22,6 +22,8 @@ int dcnn_device_sms(void);
  *      BackwardFilter and cublasSgemm: src/nn/layers_impl/cuda/cudnn_conv2d_ops.cu:171-232, dense_ops.cu:24-137 ---- */
 int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w);
 /* statistics tiles dcnn_conv_tc emits for this problem (== m_tiles unless the 256-pixel kernel is selected; DCNN_CONV_V3=0 disables it) */
+/* autotuner hook: force conv_tc2 (2), conv_tc3 (3) or conv_tc5 (5) for this thread's next calls; 0 = built-in rules */
+int dcnn_conv_tc_set_variant(int variant);
 int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout);
 int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
                  long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h, int in_mul_w,

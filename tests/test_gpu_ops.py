@@ -447,3 +447,33 @@ def test_conv_tc5_cta_pairs():
     r = subprocess.run([sys.executable, os.path.join(root, "scripts", "check_conv_v3.py"), "--pair"], env=env,
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "ALL PASS" in r.stdout and "FAIL" not in r.stdout, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+@pending_hw
+def test_conv_autotuner_picks_a_variant_and_stays_correct():
+    """DCNN_AUTOTUNE: every structurally possible conv kernel variant is timed on first sight of a shape; results stay
+    equal to the CPU oracle whichever wins, and the choice is cached."""
+    from dcnn_b200.ops import cuda as K
+    old = K.AUTOTUNE
+    K.AUTOTUNE = True
+    K._TUNED.clear()
+    try:
+        for (N, C, H, OC, k, p) in [(32, 64, 32, 128, 3, 1), (16, 128, 16, 256, 1, 0)]:
+            x = torch.randn(N, C, H, H)
+            w = torch.randn(OC, C, k, k) / (C * k * k) ** 0.5
+            y_ref, st_ref = ref.conv2d_forward(x, w, None, (1, 1), (p, p), True)
+            y, st = ops.conv2d_forward(cl(x), cl(w), None, (1, 1), (p, p), True)
+            check_close(y, y_ref, 4e-3, "autotuned fprop")
+            mean, _ = ops.bn_finalize(st, 1e-5, 0.1, torch.zeros(OC, device=DEV), torch.ones(OC, device=DEV))
+            assert (mean.cpu() - y_ref.mean((0, 2, 3))).abs().max() < 5e-3
+            key = ("f", N, H, H, C, OC, k, k, 1, 1)
+            assert K._TUNED.get(key) in (2, 3, 5)
+            y2, _ = ops.conv2d_forward(cl(x), cl(w), None, (1, 1), (p, p), True)      # cached choice, same answer
+            check_close(y2, y_ref, 4e-3, "autotuned fprop (cached)")
+            dy = torch.randn_like(y_ref)
+            dx_ref = ref.conv2d_backward_data(dy, w, (N, C, H, H), (1, 1), (p, p))
+            dx = ops.conv2d_backward_data(cl(dy), cl(w), (N, C, H, H), (1, 1), (p, p))
+            check_close(dx, dx_ref, 4e-3, "autotuned dgrad")
+    finally:
+        K.AUTOTUNE = old
+        K._TUNED.clear()
