@@ -51,6 +51,22 @@ class BaseDataLoader:
         self.batches_prepared = False
         self.current_index = self.current_batch_index = 0
 
+    def get_rng_state(self) -> dict:
+        """Everything that determines the next ``shuffle()`` / ``prepare_batches()``: the loader's generator, the sample
+        order and the generators of the attached augmentations (for resumable training)."""
+        aug = self.augmentation
+        return {"rng": self.rng.bit_generator.state,
+                "order": None if self._order is None else self._order.copy(),
+                "aug": [a.rng.bit_generator.state for a in aug.augmentations] if aug is not None else []}
+
+    def set_rng_state(self, state: dict):
+        self.rng.bit_generator.state = state["rng"]
+        self._order = None if state["order"] is None else np.asarray(state["order"]).copy()
+        if self.augmentation is not None:
+            for a, st in zip(self.augmentation.augmentations, state["aug"]):
+                a.rng.bit_generator.state = st
+        self.batches_prepared = False
+
     def shard_size(self) -> int:
         return self.size() // self._shard[1] if self._shard else self.size()
 

@@ -283,6 +283,18 @@ def train_classification_model(model, train_loader, test_loader, optimizer, loss
 
 
 def _train_classification(model, train_loader, test_loader, optimizer, loss_function, config, dp, main):
+    # RESUME_FROM=<path written by CHECKPOINT_EVERY / checkpoint_on_signal>: continue where that run stopped -- weights,
+    # BatchNorm statistics, optimizer moments and step, learning rate, epoch counter, RNG and data-order state
+    resume = get_env("RESUME_FROM", "")
+    state = None
+    if resume:
+        from .io import load_training_state
+        state = load_training_state(resume, model, optimizer)
+        ls = state.get("extra", {}).get("loaders")
+        if ls:
+            train_loader.set_rng_state(ls[0])
+            test_loader.set_rng_state(ls[1])
+        print(f"Resumed from {resume}: epoch {state['epoch']}, lr {optimizer.get_learning_rate():.6g}")
     train_loader.prepare_batches(config.batch_size)
     test_loader.prepare_batches(config.batch_size)
     model.enable_profiling(config.profiler_type in ("NORMAL", "CUMULATIVE"))
@@ -300,15 +312,20 @@ def _train_classification(model, train_loader, test_loader, optimizer, loss_func
     ckpt = os.path.join(config.snapshot_dir, model.name() + ".interrupted")
     with watchdog_from_env("train step") as wd, checkpoint_on_signal(ckpt, model, optimizer, lambda: epoch_box[0]):
         history = _classification_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step,
-                                         metrics, wd, epoch_box, dp, main)
+                                         metrics, wd, epoch_box, dp, main, state)
     return history
 
 
 def _classification_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step, metrics, wd,
-                           epoch_box, dp=None, main=True):
+                           epoch_box, dp=None, main=True, resumed=None):
     best_val_accuracy = 0.0
     history = []
-    for epoch in range(config.epochs):
+    start_epoch = 0
+    if resumed is not None:
+        start_epoch = int(resumed.get("epoch", 0))
+        best_val_accuracy = float(resumed.get("extra", {}).get("best_val_accuracy", 0.0))
+    every = get_env("CHECKPOINT_EVERY", 0)          # epochs between resumable checkpoints (0 = off)
+    for epoch in range(start_epoch, config.epochs):
         epoch_box[0] = epoch
         print(f"Epoch {epoch + 1}/{config.epochs}")
         t0 = time.perf_counter()
@@ -347,6 +364,14 @@ def _classification_epochs(model, train_loader, test_loader, optimizer, loss_fun
             cur = optimizer.get_learning_rate()
             optimizer.set_learning_rate(cur * config.lr_decay_factor)
             print(f"Learning rate decayed: {cur:.6f} -> {cur * config.lr_decay_factor:.6f}")
+        if every > 0 and (epoch + 1) % every == 0 and main:
+            # written BEFORE the next epoch's batches are drawn, so that a resumed run re-draws exactly the same batches
+            from .io import save_training_state
+            path = os.path.join(config.snapshot_dir, model.name() + ".checkpoint")
+            save_training_state(path, model, optimizer, epoch=epoch + 1,
+                                extra={"best_val_accuracy": best_val_accuracy,
+                                       "loaders": [train_loader.get_rng_state(), test_loader.get_rng_state()]})
+            print(f"Checkpoint written to {path} (resume with RESUME_FROM={path})")
         train_loader.prepare_batches(config.batch_size)  # re-apply augmentation
         test_loader.prepare_batches(config.batch_size)
         print(f"{get_memory_usage_kb() // 1024} MB of memory used.")

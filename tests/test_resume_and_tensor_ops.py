@@ -100,3 +100,41 @@ def test_packed_tap_stem_formulation():
     dw = dwp[:, :R * S * Cin].reshape(Cout, R, S, Cin).permute(0, 3, 1, 2)
     want = torch.nn.grad.conv2d_weight(x, w.shape, dy, stride=st, padding=pd)
     assert torch.allclose(dw, want, atol=1e-4)
+
+
+def test_training_loop_resumes_bit_identically(tmp_path, monkeypatch):
+    """3 epochs in one go == 2 epochs (CHECKPOINT_EVERY=1) + a fresh process state resumed for the third: same weights,
+    same statistics, same history -- shuffling and augmentation draws included."""
+    from dcnn_b200.data import AugmentationBuilder, SyntheticDataLoader
+    from dcnn_b200.train import TrainingConfig, train_classification_model
+
+    def setup(epochs, snap):
+        cfg = TrainingConfig()
+        cfg.epochs, cfg.batch_size, cfg.snapshot_dir, cfg.progress_print_interval = epochs, 8, str(snap), 1000
+        cfg.lr_decay_interval, cfg.lr_decay_factor = 1, 0.5
+        tr, te = SyntheticDataLoader(32, (1, 28, 28), 10, seed=0), SyntheticDataLoader(16, (1, 28, 28), 10, seed=1)
+        tr.set_seed(5)
+        te.set_seed(6)
+        tr.set_augmentation(AugmentationBuilder().horizontal_flip(0.5).brightness(0.5, 0.2).build())
+        tr.augmentation.set_seed(7)
+        m = create_mnist_trainer()
+        m.set_seed(1)
+        m.initialize()
+        return cfg, tr, te, m, dnn.Adam(1e-2)
+    torch.manual_seed(0)
+    cfg, tr, te, m_full, o = setup(3, tmp_path / "a")
+    h_full = train_classification_model(m_full, tr, te, o, dnn.SoftmaxCrossEntropyLoss(), cfg)
+    monkeypatch.setenv("CHECKPOINT_EVERY", "1")
+    torch.manual_seed(0)
+    cfg, tr, te, m1, o = setup(2, tmp_path / "b")
+    h1 = train_classification_model(m1, tr, te, o, dnn.SoftmaxCrossEntropyLoss(), cfg)
+    ck = str(tmp_path / "b" / (m1.name() + ".checkpoint"))
+    monkeypatch.delenv("CHECKPOINT_EVERY")
+    monkeypatch.setenv("RESUME_FROM", ck)
+    cfg, tr, te, m2, o = setup(3, tmp_path / "c")          # brand-new objects, as after a restart
+    h2 = train_classification_model(m2, tr, te, o, dnn.SoftmaxCrossEntropyLoss(), cfg)
+    assert [h["epoch"] for h in h1] == [1, 2] and [h["epoch"] for h in h2] == [3]
+    assert abs(h2[0]["train_loss"] - h_full[2]["train_loss"]) < 1e-7 and h2[0]["val_acc"] == h_full[2]["val_acc"]
+    for a, b in zip(list(m2.parameters()) + list(m2.buffers().values()),
+                    list(m_full.parameters()) + list(m_full.buffers().values())):
+        assert torch.equal(a, b)
