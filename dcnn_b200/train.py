@@ -432,7 +432,18 @@ def train_regression_model(model, train_loader, test_loader, optimizer, loss_fun
     step = TrainStep(model, optimizer, loss_function, config.use_cuda_graph)
     best = float("inf")
     history = []
+    metrics = metrics_from_env()
+    epoch_box = [0]
+    ckpt = os.path.join(config.snapshot_dir, model.name() + ".interrupted")
+    with watchdog_from_env("train step"), checkpoint_on_signal(ckpt, model, optimizer, lambda: epoch_box[0]):
+        return _regression_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step, best, history,
+                                  metrics, epoch_box)
+
+
+def _regression_epochs(model, train_loader, test_loader, optimizer, loss_function, config, step, best, history, metrics,
+                       epoch_box):
     for epoch in range(config.epochs):
+        epoch_box[0] = epoch
         print(f"Epoch {epoch + 1}/{config.epochs}")
         t0 = time.perf_counter()
         tl = train_reg_epoch(model, train_loader, optimizer, loss_function, config, step)
@@ -449,6 +460,7 @@ def train_regression_model(model, train_loader, test_loader, optimizer, loss_fun
         print(f"Training   - Loss: {tl:.6f}")
         print(f"Validation - Loss: {vl:.6f}, Mean abs error: {ve:.6f}")
         history.append({"epoch": epoch + 1, "train_loss": tl, "val_loss": vl, "val_err": ve, "train_ms": ms})
+        metrics.log(kind="epoch", lr=optimizer.get_learning_rate(), rss_kb=get_memory_usage_kb(), **history[-1])
         if (epoch + 1) % config.lr_decay_interval == 0:
             optimizer.set_learning_rate(optimizer.get_learning_rate() * config.lr_decay_factor)
         train_loader.prepare_batches(config.batch_size)
