@@ -28,3 +28,4 @@ echo "== dp$N with bucketed overlapped all-reduce"; DCNN_DP_BUCKETS=4 timeout 90
 echo "== dp tests with buckets"; DCNN_DP_BUCKETS=3 timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_buckets_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_buckets_$N.log | cut -c1-300
 echo "== NVLS all-reduce (multimem)"; DCNN_DP_NVLS=1 timeout 90 $TR benchmarks/allreduce_roofline.py > gpurun_out/ar_nvls_$N.log 2>&1; echo "exit $?"; tail -2 gpurun_out/ar_nvls_$N.log | cut -c1-400
 DCNN_DP_NVLS=1 timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_nvls_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_nvls_$N.log | cut -c1-300
+echo "== gpu pipeline tests"; DCNN_TEST_PENDING=1 timeout 400 python -m pytest tests/test_gpu_pipeline.py -m gpu -x -q --timeout 300 -p no:cacheprovider > gpurun_out/t_gpu_pipeline_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_gpu_pipeline_$N.log | cut -c1-300
