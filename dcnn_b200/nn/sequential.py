@@ -178,6 +178,10 @@ class Sequential:
         return dict(self.backward_times_us)
 
     def _timed(self, table, name, fn, *a, **k):
+        rec = _rt.ACTIVE_TRACE
+        if rec is not None:        # Chrome-trace recording (utils/trace.py)
+            return rec.timed(self.device, name, "forward" if table is self.forward_times_us else "backward",
+                             lambda: self._timed_inner(table, name, fn, *a, **k))
         if _rt.NVTX and self.device.type == "cuda":   # DCNN_NVTX=1: one range per fusion unit and direction
             tag = ("fwd " if table is self.forward_times_us else "bwd ") + name
             with _rt.nvtx_range(tag):

@@ -100,6 +100,9 @@ class TrainStep:
         self._graph = None
         self._static = None
         self._calls = 0
+        self._trace_path = os.environ.get("DCNN_TRACE_FILE", "")
+        self._trace_total = self._trace_left = int(os.environ.get("DCNN_TRACE_STEPS", "3") or 3) if self._trace_path else 0
+        self._trace = None
         if self.use_cuda_graph:
             optimizer.enable_device_hyper(model.get_device())
 
@@ -129,6 +132,30 @@ class TrainStep:
 
     def __call__(self, x: torch.Tensor, t: torch.Tensor):
         _runtime.kick()                   # feeds any running StepWatchdog (STEP_TIMEOUT_S)
+        if self._trace_path and self._trace_left > 0:
+            return self._traced_call(x, t)
+        return self._call(x, t)
+
+    def _traced_call(self, x, t):
+        """DCNN_TRACE_FILE: Chrome trace of the first DCNN_TRACE_STEPS steps (eager steps only -- a replayed CUDA graph
+        does not pass through the per-unit hooks)."""
+        from .utils.trace import TraceRecorder
+        if self._trace is None:
+            root, ext = os.path.splitext(self._trace_path)
+            rank = int(os.environ.get("RANK", "0"))
+            self._trace = TraceRecorder(self._trace_path if rank == 0 else f"{root}.rank{rank}{ext or '.json'}")
+            self._trace.__enter__()
+        self._trace.mark(f"step {self._calls if self.use_cuda_graph else self._trace_total - self._trace_left}")
+        try:
+            return self._call(x, t)
+        finally:
+            self._trace_left -= 1
+            if self._trace_left == 0 or self._graph is not None:
+                self._trace_left = 0
+                self._trace.__exit__(None, None, None)
+                print(f"[dcnn] trace written to {self._trace.path}")
+
+    def _call(self, x: torch.Tensor, t: torch.Tensor):
         if not self.use_cuda_graph:
             return self._eager(x, t)
         self._calls += 1

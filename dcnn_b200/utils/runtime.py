@@ -22,6 +22,7 @@ from typing import Callable, Optional
 from .misc import MetricsLogger
 
 NVTX = os.environ.get("DCNN_NVTX", "0") == "1"
+ACTIVE_TRACE = None   # a utils.trace.TraceRecorder while one is recording (Sequential._timed feeds it)
 _ACTIVE = []      # running watchdogs; kick() from anywhere (TrainStep, the pipeline engine) feeds all of them
 
 

@@ -123,3 +123,59 @@ def test_flag_override_layer(tmp_path, monkeypatch):
         env.clear_loaded()
         for k in ("EPOCHS", "BATCH_SIZE", "DEVICE_TYPE", "SYNTHETIC", "X_Y"):
             os.environ.pop(k, None)
+
+
+def test_chrome_trace_of_training_steps(tmp_path):
+    from dcnn_b200 import nn as dnn
+    from dcnn_b200.models import create_mnist_trainer
+    from dcnn_b200.train import TrainStep
+    from dcnn_b200.utils.trace import TraceRecorder
+    m = create_mnist_trainer()
+    m.set_seed(0)
+    m.initialize()
+    o = dnn.SGD(0.01)
+    o.attach(m.parameters(), m.gradients())
+    step = TrainStep(m, o, dnn.SoftmaxCrossEntropyLoss())
+    import torch
+    x = torch.randn(4, 1, 28, 28)
+    t = torch.zeros(4, 10, 1, 1)
+    t[:, 1] = 1
+    path = str(tmp_path / "t" / "trace.json")
+    with TraceRecorder(path) as rec:
+        for i in range(2):
+            rec.mark(f"step {i}")
+            step(x, t)
+    assert runtime.ACTIVE_TRACE is None
+    blob = json.load(open(path))
+    ev = [e for e in blob["traceEvents"] if e.get("ph") == "X"]
+    units = len(m._get_units())
+    assert len(ev) == 2 * 2 * units                                # 2 steps x (forward + backward) x units
+    assert {e["cat"] for e in ev} == {"forward", "backward"} and all(e["dur"] >= 0 for e in ev)
+    assert [e["ts"] for e in ev] == sorted(e["ts"] for e in ev)
+    assert sum(1 for e in blob["traceEvents"] if e.get("ph") == "i") == 2
+    # forward of a step precedes its backward; the last unit's backward comes first in the backward sweep
+    first_step = ev[:2 * units]
+    assert [e["cat"] for e in first_step] == ["forward"] * units + ["backward"] * units
+    assert first_step[units]["name"] == first_step[units - 1]["name"]
+
+
+def test_trace_file_env_records_first_steps(tmp_path, monkeypatch):
+    import torch
+    from dcnn_b200 import nn as dnn
+    from dcnn_b200.models import create_mnist_trainer
+    from dcnn_b200.train import TrainStep
+    path = tmp_path / "run.json"
+    monkeypatch.setenv("DCNN_TRACE_FILE", str(path))
+    monkeypatch.setenv("DCNN_TRACE_STEPS", "2")
+    m = create_mnist_trainer()
+    m.initialize()
+    o = dnn.SGD(0.01)
+    o.attach(m.parameters(), m.gradients())
+    step = TrainStep(m, o, dnn.SoftmaxCrossEntropyLoss())
+    x, t = torch.randn(2, 1, 28, 28), torch.zeros(2, 10, 1, 1)
+    t[:, 0] = 1
+    for _ in range(4):
+        step(x, t)
+    assert runtime.ACTIVE_TRACE is None and path.exists()
+    ev = [e for e in json.load(open(path))["traceEvents"] if e.get("ph") == "X"]
+    assert len(ev) == 2 * 2 * len(m._get_units())            # only the first two steps
