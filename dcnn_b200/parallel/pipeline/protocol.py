@@ -86,25 +86,39 @@ class Message:
 @dataclass
 class Endpoint:
     """Where a pipeline participant lives.  ``in_process`` endpoints carry the communicator object itself (ref
-    Endpoint::in_process); ``rank`` endpoints name a torch.distributed rank (replaces host:port)."""
-    kind: str = "rank"                 # "rank" | "in_process"
+    Endpoint::in_process); ``rank`` endpoints name a torch.distributed rank; ``tcp`` endpoints are the reference's
+    ``Endpoint::network(host, port)`` (endpoint.hpp:46-51), served by the native TCP transport."""
+    kind: str = "rank"                 # "rank" | "in_process" | "tcp"
     rank: int = -1
     device: str = "cpu"
     communicator: Any = field(default=None, repr=False, compare=False)
+    host: str = ""
+    port: int = 0
 
     @staticmethod
     def network(rank: int, device: str = "cpu") -> "Endpoint":
         return Endpoint("rank", int(rank), device)
 
     @staticmethod
+    def tcp(host: str, port: int, device: str = "cpu") -> "Endpoint":
+        return Endpoint("tcp", -1, device, None, host, int(port))
+
+    @staticmethod
     def in_process(communicator) -> "Endpoint":
         return Endpoint("in_process", -1, "cpu", communicator)
 
     def to_json(self) -> dict:
+        if self.kind == "tcp":     # the reference's schema (endpoint.hpp:59-83): parameters are strings
+            return {"communication_type_": "tcp",
+                    "parameters_": {"host": self.host, "port": str(self.port), "device": self.device}}
         return {"communication_type": self.kind, "rank": self.rank, "device": self.device}
 
     @staticmethod
     def from_json(j: dict) -> "Endpoint":
+        if "communication_type_" in j:
+            p = j.get("parameters_", {})
+            return Endpoint(j["communication_type_"], -1, p.get("device", "cpu"), None, p.get("host", ""),
+                            int(p.get("port", 0)))
         return Endpoint(j.get("communication_type", "rank"), int(j.get("rank", -1)), j.get("device", "cpu"))
 
 

@@ -5,10 +5,14 @@ Launch modes:
     (InProcessCoordinator), stage i on GPU i when GPUs are visible and DEVICE_TYPE=GPU, else on the CPU;
   * one process per participant (``torchrun --nproc-per-node S+1 examples/<coordinator>.py``): rank 0 is the
     coordinator (owns the data loader, CPU side), ranks 1..S run a NetworkStageWorker on GPU rank-1.  This is the
-    counterpart of starting ``network_worker <port> --gpu`` S times plus a coordinator binary in the reference."""
+    counterpart of starting ``network_worker <port> --gpu`` S times plus a coordinator binary in the reference;
+  * host:port, exactly like the reference (``PIPELINE_WORKERS=host:8001,host:8002 python examples/<coordinator>.py`` or
+    ``--workers host:8001,host:8002``): the stages are ``python examples/network_worker.py <port>`` processes reached
+    over the native TCP transport; ``COORDINATOR_HOST`` is the address they use to call back (default 127.0.0.1)."""
 from __future__ import annotations
 
 import os
+import sys
 
 os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")   # stage workers must not lazy-load kernels mid-schedule
 
@@ -23,7 +27,18 @@ def make_coordinator(model, optimizer, loss, num_stages, cfg, partitioner=None, 
     """Returns (coordinator | None, is_coordinator).  Worker ranks serve until SHUTDOWN and return (None, False)."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     use_gpu = cfg.device_type == "GPU"
-    if world == 1:
+    workers = os.environ.get("PIPELINE_WORKERS", "")
+    for i, a in enumerate(sys.argv):
+        if a == "--workers" and i + 1 < len(sys.argv):
+            workers = sys.argv[i + 1]
+        elif a.startswith("--workers="):
+            workers = a.split("=", 1)[1]
+    if workers:
+        from dcnn_b200.parallel.pipeline import TcpCoordinator
+        addrs = [w for w in workers.split(",") if w]
+        coord = TcpCoordinator(model, optimizer, addrs, os.environ.get("COORDINATOR_HOST", "127.0.0.1"),
+                               stage_devices=["cuda:0" if use_gpu else "cpu"] * len(addrs))
+    elif world == 1:
         ngpu = torch.cuda.device_count() if use_gpu else 0
         devs = [f"cuda:{i % ngpu}" if ngpu else "cpu" for i in range(num_stages)]
         coord = InProcessCoordinator(model, optimizer, devs)
