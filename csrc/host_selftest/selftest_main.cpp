@@ -41,6 +41,8 @@ void dcnn_cpu_avgpool_fwd(const float*, float*, int, int, int, int, int, int, in
 void dcnn_cpu_avgpool_bwd(const float*, float*, int, int, int, int, int, int, int, int, int, int, int, int);
 }
 
+int run_tcp_selftest();   // selftest_tcp.cpp
+
 static int failures = 0;
 #define CHECK(cond, ...)                                  \
   do {                                                    \
@@ -241,6 +243,7 @@ int main(int argc, char** argv) {
   test_augment();
   test_codec();
   test_loader(argc > 1 ? argv[1] : ".");
+  failures += run_tcp_selftest();
   if (failures) {
     fprintf(stderr, "%d check(s) failed\n", failures);
     return 1;
