@@ -141,6 +141,8 @@ def model_spec(name):
 
 
 def reference_arm(args):
+    if int(os.environ.get("RANK", "0")) != 0:      # launched with torchrun for N > 1: one line, from rank 0
+        return 0
     from baseline import reference_bench
     return reference_bench.run(args)
 

@@ -1068,6 +1068,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   }
 
   // both CTAs are done with each other's barriers, shared memory and the paired tensor memory
+  __syncwarp();   // the cluster barrier is .aligned: lanes that skipped the single-lane roles wait for their lane 0 here
   tc_fence_before();
   cluster_sync_all();
   if (warp == 1) {

@@ -48,6 +48,20 @@ def test_multiprocess_pipeline_launch(tmp_path):
     assert "Deployed 2 pipeline stages" in out and "Stopped all pipeline stages" in out
 
 
+def test_host_port_pipeline_launch(tmp_path):
+    """scripts/local_tcp_pipeline.sh: two `network_worker <port>` processes + a coordinator naming them host:port."""
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    out = _run(["bash", os.path.join(ROOT, "scripts", "local_tcp_pipeline.sh"),
+                os.path.join(ROOT, "examples", "semi_async_pipeline_coordinator.py"), "2", str(port)],
+               cwd=str(tmp_path), timeout=900, PYTHONPATH=ROOT)
+    assert "Deployed 2 pipeline stages" in out and "Stopped all pipeline stages" in out
+    assert out.count(": shutdown") == 2
+
+
 def test_flag_overrides_reach_an_example(tmp_path):
     out = _run([sys.executable, os.path.join(ROOT, "examples", "mnist_cnn_trainer.py"), "--epochs", "2",
                 "--batch-size=4"], cwd=str(tmp_path))
