@@ -67,15 +67,30 @@ DCNN_HOST_API void dcnn_cpu_bn_bwd_sums(const float* dout, const float* x, const
     const float mu = mean[c], is = invstd[c];
     for (int n = 0; n < N; ++n) {
       const size_t o = ((size_t)n * C + c) * HW;
-      double ta = 0, tb = 0;
+      // one (n, c) plane at a time in float lanes (a plane is at most a few thousand elements), planes summed in FP64
+      for (int i0 = 0; i0 < HW; i0 += 4096) {
+        const int len = HW - i0 < 4096 ? HW - i0 : 4096;
+        const float* pd = dout + o + i0;
+        const float* px = x + o + i0;
+        float ta = 0.f, tb = 0.f;
+        if (relu) {
+          const float* po = out + o + i0;
 #pragma omp simd reduction(+ : ta, tb)
-      for (int i = 0; i < HW; ++i) {
-        const float g = (relu && !(out[o + i] > 0.f)) ? 0.f : dout[o + i];
-        ta += g;
-        tb += (double)g * (double)((x[o + i] - mu) * is);
+          for (int i = 0; i < len; ++i) {
+            const float g = po[i] > 0.f ? pd[i] : 0.f;
+            ta += g;
+            tb += g * ((px[i] - mu) * is);
+          }
+        } else {
+#pragma omp simd reduction(+ : ta, tb)
+          for (int i = 0; i < len; ++i) {
+            ta += pd[i];
+            tb += pd[i] * ((px[i] - mu) * is);
+          }
+        }
+        a += ta;
+        b += tb;
       }
-      a += ta;
-      b += tb;
     }
     sum_dy[c] = a;
     sum_dy_xhat[c] = b;
@@ -104,15 +119,62 @@ DCNN_HOST_API void dcnn_cpu_bn_bwd_dx(const float* dout, const float* x, const f
 }
 
 // ------------------------------------------------------------------------------------------------ pooling
+namespace {
+// One (n, c) plane whose windows all lie inside the image.  KH/KW > 0 fix the window at compile time (the loops unroll
+// into compare/select chains without branches); 0 takes the run-time size.  First maximum in scan order wins; a NaN in
+// the window makes the output NaN at the first NaN's position (ATen's convention), handled off the fast path.
+template <int KH, int KW>
+inline void pool_plane_inside(const float* p, float* q, long long* qi, int W, int OH, int OW, int kh_rt, int kw_rt, int sh,
+                              int sw) {
+  const int kh = KH ? KH : kh_rt, kw = KW ? KW : kw_rt;
+  for (int oh = 0; oh < OH; ++oh) {
+    for (int ow = 0; ow < OW; ++ow) {
+      const float* win = p + (size_t)oh * sh * W + (size_t)ow * sw;
+      float best = win[0];
+      int off = 0;
+      bool nan = false;
+      for (int r = 0; r < kh; ++r)
+        for (int s = 0; s < kw; ++s) {
+          const float v = win[r * W + s];
+          const bool take = v > best;
+          nan |= v != v;
+          best = take ? v : best;
+          off = take ? r * W + s : off;
+        }
+      if (nan) {
+        for (int r = 0, found = 0; r < kh && !found; ++r)
+          for (int s = 0; s < kw; ++s)
+            if (win[r * W + s] != win[r * W + s]) {
+              best = win[r * W + s];
+              off = r * W + s;
+              found = 1;
+              break;
+            }
+      }
+      q[oh * OW + ow] = best;
+      qi[oh * OW + ow] = (long long)(win - p) + off;
+    }
+  }
+}
+}  // namespace
+
 // idx[n,c,oh,ow] = flat input index (ih*W + iw) of the first maximum in scan order (torch.max_pool2d's convention too)
 DCNN_HOST_API void dcnn_cpu_maxpool_fwd(const float* x, float* y, long long* idx, int N, int C, int H, int W, int OH,
                                         int OW, int kh, int kw, int sh, int sw, int ph, int pw) {
+  // windows that never leave the image (no padding, complete windows): no bounds tests in the inner loops
+  const bool inside = ph == 0 && pw == 0 && (OH - 1) * sh + kh <= H && (OW - 1) * sw + kw <= W;
 #pragma omp parallel for collapse(2) schedule(static)
   for (int n = 0; n < N; ++n) {
     for (int c = 0; c < C; ++c) {
       const float* p = x + ((size_t)n * C + c) * H * W;
       float* q = y + ((size_t)n * C + c) * OH * OW;
       long long* qi = idx + ((size_t)n * C + c) * OH * OW;
+      if (inside) {
+        if (kh == 2 && kw == 2) pool_plane_inside<2, 2>(p, q, qi, W, OH, OW, kh, kw, sh, sw);
+        else if (kh == 3 && kw == 3) pool_plane_inside<3, 3>(p, q, qi, W, OH, OW, kh, kw, sh, sw);
+        else pool_plane_inside<0, 0>(p, q, qi, W, OH, OW, kh, kw, sh, sw);
+        continue;
+      }
       for (int oh = 0; oh < OH; ++oh) {
         for (int ow = 0; ow < OW; ++ow) {
           float best = -INFINITY;

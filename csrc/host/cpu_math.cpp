@@ -189,11 +189,17 @@ void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A,
   if (K <= 0 || alpha == T(0)) return;
   const long long a_rs = transA ? 1 : lda, a_cs = transA ? lda : 1;
   const long long b_rs = transB ? 1 : ldb, b_cs = transB ? ldb : 1;
-  std::vector<T> bpack((size_t)KC * (NC + NR));
+  // packing buffers live for the life of the thread: a convolution issues thousands of small products and must not pay
+  // an allocation plus a 2 MB clear for each
+  static thread_local std::vector<T> bpack_tls;
+  const size_t bneed = (size_t)std::min(KC, K) * ((size_t)std::min(NC, N) + NR);
+  if (bpack_tls.size() < bneed) bpack_tls.resize(bneed);
+  T* const bpack_data = bpack_tls.data();
   const bool par = (2.0 * M * N * K) > 2e6;
 #pragma omp parallel if (par)
   {
-    std::vector<T> apack((size_t)(MC + MR) * KC);
+    static thread_local std::vector<T> apack;
+    if (apack.size() < (size_t)(MC + MR) * KC) apack.resize((size_t)(MC + MR) * KC);
     alignas(64) T acc[MR * NR];
     for (int jc = 0; jc < N; jc += NC) {
       const int nc = std::min(NC, N - jc);
@@ -204,7 +210,7 @@ void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A,
         for (int s = 0; s < strips; ++s) {
           const int j0 = jc + s * NR;
           pack_b_strip<T, NR>(B + (long long)pc * b_rs + (long long)j0 * b_cs, b_rs, b_cs, kc, std::min(NR, N - j0),
-                       bpack.data() + (size_t)s * kc * NR);
+                       bpack_data + (size_t)s * kc * NR);
         }  // implicit barrier: the panel is complete before anyone multiplies
         // tasks = (MC block) x (group of B strips): when M is small the strip groups supply the parallelism (each
         // task re-packs its A block, which is cheap next to the kc * group-width multiply it feeds)
@@ -221,7 +227,7 @@ void gemm_impl(int transA, int transB, int M, int N, int K, T alpha, const T* A,
             pack_a<T, MR>(A + (long long)ic * a_rs + (long long)pc * a_cs, a_rs, a_cs, mc, kc, apack.data());
             for (int s = s_lo; s < s_hi; ++s) {
               const int j0 = jc + s * NR, nr = std::min(NR, N - j0);
-              const T* bp = bpack.data() + (size_t)s * kc * NR;
+              const T* bp = bpack_data + (size_t)s * kc * NR;
               for (int i0 = 0; i0 < mc; i0 += MR) {
                 const int mr = std::min(MR, mc - i0);
                 T* c = C + (long long)(ic + i0) * ldc + j0;

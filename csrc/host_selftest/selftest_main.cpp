@@ -39,6 +39,10 @@ void dcnn_cpu_maxpool_fwd(const float*, float*, long long*, int, int, int, int, 
 void dcnn_cpu_maxpool_bwd(const float*, const long long*, float*, int, int, int, int);
 void dcnn_cpu_avgpool_fwd(const float*, float*, int, int, int, int, int, int, int, int, int, int, int, int);
 void dcnn_cpu_avgpool_bwd(const float*, float*, int, int, int, int, int, int, int, int, int, int, int, int);
+void dcnn_cpu_conv2d_fwd(const float*, const float*, const float*, float*, int, int, int, int, int, int, int, int, int, int,
+                         int, int, int);
+void dcnn_cpu_conv2d_bwd(const float*, const float*, const float*, float*, float*, int, int, int, int, int, int, int, int,
+                         int, int, int, int, int);
 }
 
 int run_tcp_selftest();   // selftest_tcp.cpp
@@ -235,8 +239,50 @@ static void test_layers() {
   dcnn_cpu_avgpool_bwd(py.data(), dx.data(), N, C, H, W, OH, OW, k, k, st, st, p, p);
 }
 
+// blocked convolution against a naive loop nest, over shapes whose taps fall on padding, strides that skip pixels,
+// kernels as large as the image and ragged last blocks
+static void test_conv() {
+  const int cases[][8] = {{5, 3, 9, 11, 7, 3, 2, 1}, {3, 4, 6, 6, 5, 3, 1, 2}, {2, 2, 5, 5, 3, 5, 1, 2}, {9, 3, 7, 7, 4, 3, 3, 0},
+                          {2, 1, 1, 1, 2, 5, 2, 2}, {70, 2, 40, 40, 4, 3, 1, 1}, {33, 1, 28, 28, 8, 5, 1, 0}};
+  for (const auto& cs : cases) {
+    const int N = cs[0], C = cs[1], H = cs[2], W = cs[3], OC = cs[4], k = cs[5], st = cs[6], pd = cs[7];
+    const int OH = (H + 2 * pd - k) / st + 1, OW = (W + 2 * pd - k) / st + 1;
+    auto x = randv((size_t)N * C * H * W), w = randv((size_t)OC * C * k * k), b = randv(OC);
+    auto dy = randv((size_t)N * OC * OH * OW);
+    std::vector<float> y((size_t)N * OC * OH * OW), dx((size_t)N * C * H * W, 7.f), dw((size_t)OC * C * k * k, 0.25f);
+    std::vector<double> yr(y.size()), dxr(dx.size(), 0.0), dwr(dw.size(), 0.25);
+    for (int n = 0; n < N; ++n)
+      for (int oc = 0; oc < OC; ++oc)
+        for (int oh = 0; oh < OH; ++oh)
+          for (int ow = 0; ow < OW; ++ow) {
+            const size_t yo = (((size_t)n * OC + oc) * OH + oh) * OW + ow;
+            double acc = b[oc];
+            for (int c = 0; c < C; ++c)
+              for (int r = 0; r < k; ++r)
+                for (int s = 0; s < k; ++s) {
+                  const int ih = oh * st - pd + r, iw = ow * st - pd + s;
+                  if (ih < 0 || ih >= H || iw < 0 || iw >= W) continue;
+                  const size_t xo = (((size_t)n * C + c) * H + ih) * W + iw, wo = (((size_t)oc * C + c) * k + r) * k + s;
+                  acc += (double)x[xo] * w[wo];
+                  dxr[xo] += (double)dy[yo] * w[wo];
+                  dwr[wo] += (double)dy[yo] * x[xo];
+                }
+            yr[yo] = acc;
+          }
+    dcnn_cpu_conv2d_fwd(x.data(), w.data(), b.data(), y.data(), N, C, H, W, OC, k, k, st, st, pd, pd, OH, OW);
+    dcnn_cpu_conv2d_bwd(x.data(), w.data(), dy.data(), dw.data(), dx.data(), N, C, H, W, OC, k, k, st, st, pd, pd, OH, OW);
+    double ey = 0, ex = 0, ew = 0;
+    for (size_t i = 0; i < y.size(); ++i) ey = fmax(ey, fabs(y[i] - yr[i]));
+    for (size_t i = 0; i < dx.size(); ++i) ex = fmax(ex, fabs(dx[i] - dxr[i]));
+    for (size_t i = 0; i < dw.size(); ++i) ew = fmax(ew, fabs(dw[i] - dwr[i]) / (1.0 + fabs(dwr[i])));
+    CHECK(ey < 1e-4 && ex < 1e-4 && ew < 1e-4, "conv %dx%dx%dx%d oc%d k%d s%d p%d: %g %g %g", N, C, H, W, OC, k, st, pd, ey,
+          ex, ew);
+  }
+}
+
 int main(int argc, char** argv) {
   test_layers();
+  test_conv();
   test_gemm();
   test_elementwise();
   test_im2col();

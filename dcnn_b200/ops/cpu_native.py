@@ -180,34 +180,39 @@ def enabled() -> bool:
     return os.environ.get("DCNN_CPU_BACKEND", "aten").lower() == "native"
 
 
-def conv2d_forward(x, w, bias, stride, pad):
-    """y[n,oc,:,:] = W[oc, C*kh*kw] @ im2col(x) (+bias): one GEMM for the whole batch."""
-    N, Cc, H, W = x.shape
-    OC, _, kh, kw = w.shape
+def _conv_geometry(x_shape, w_shape, stride, pad):
+    N, Cc, H, W = x_shape
+    OC, _, kh, kw = w_shape
     OH, OW = _out_hw(H, W, kh, kw, stride, pad)
-    col = im2col(x.float(), kh, kw, stride, pad)
-    y = gemm(w.contiguous().reshape(OC, -1), col)                     # [OC, N*OH*OW]
-    y = y.reshape(OC, N, OH, OW).permute(1, 0, 2, 3).contiguous()
-    if bias is not None:
-        y += bias.reshape(1, -1, 1, 1)
+    return [C.c_int(int(v)) for v in (N, Cc, H, W, OC, kh, kw, stride[0], stride[1], pad[0], pad[1], OH, OW)], OH, OW
+
+
+def conv2d_forward(x, w, bias, stride, pad):
+    """Blocked im2col + GEMM, the output written straight into NCHW (csrc/host/cpu_conv.cpp)."""
+    x, w = x.float().contiguous(), w.contiguous()
+    geo, OH, OW = _conv_geometry(x.shape, w.shape, stride, pad)
+    y = torch.empty(x.shape[0], w.shape[0], OH, OW)
+    b = bias.contiguous() if bias is not None else None
+    _lib().dcnn_cpu_conv2d_fwd(_ptr(x), _ptr(w), _ptr(b) if b is not None else C.c_void_p(0), _ptr(y), *geo)
     return y
 
 
 def conv2d_backward_data(dy, w, x_shape, stride, pad):
-    OC, _, kh, kw = w.shape
-    g = dy.permute(1, 0, 2, 3).contiguous().reshape(OC, -1)           # [OC, N*OH*OW]
-    col = gemm(w.contiguous().reshape(OC, -1), g, trans_a=True)       # [C*kh*kw, N*OH*OW]
-    return col2im(col, x_shape, kh, kw, stride, pad)
+    dy, w = dy.float().contiguous(), w.contiguous()
+    geo, _, _ = _conv_geometry(x_shape, w.shape, stride, pad)
+    dx = torch.empty(*x_shape)
+    _lib().dcnn_cpu_conv2d_bwd(C.c_void_p(0), _ptr(w), _ptr(dy), C.c_void_p(0), _ptr(dx), *geo)
+    return dx
 
 
 def conv2d_backward_weight(dy, x, dw, stride, pad):
-    OC, _, kh, kw = dw.shape
-    g = dy.permute(1, 0, 2, 3).contiguous().reshape(OC, -1)
-    col = im2col(x.float(), kh, kw, stride, pad)
-    if dw.is_contiguous():
-        gemm(g, col, trans_b=True, beta=1.0, c=dw.view(OC, -1))       # accumulate in place (beta = 1)
-    else:
-        dw.add_(gemm(g, col, trans_b=True).reshape(dw.shape))
+    """dw += dy (*) x, accumulated in place when ``dw`` is contiguous."""
+    dy, x = dy.float().contiguous(), x.float().contiguous()
+    geo, _, _ = _conv_geometry(x.shape, dw.shape, stride, pad)
+    acc = dw if dw.is_contiguous() else torch.zeros(dw.shape)
+    _lib().dcnn_cpu_conv2d_bwd(_ptr(x), C.c_void_p(0), _ptr(dy), _ptr(acc), C.c_void_p(0), *geo)
+    if acc is not dw:
+        dw.add_(acc)
 
 
 def dense_forward(x2d, w2d, bias):

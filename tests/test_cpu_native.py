@@ -262,3 +262,42 @@ def test_sgemm_long_k_nt_path(M, N_, K):
     nanc = torch.full((M, N_), float("nan"))
     N.gemm(a, b, trans_b=True, beta=0.0, c=nanc)
     assert torch.isfinite(nanc).all()
+
+
+@pytest.mark.parametrize("shape", [
+    # N, C, H, W, OC, k, stride, pad
+    (64, 1, 28, 28, 8, 5, 1, 0),      # one image per block (OH*OW = 576): GEMM writes NCHW in place
+    (64, 16, 8, 8, 48, 5, 1, 0),      # 64 images per block, AVX-512 tile path
+    (37, 3, 9, 11, 7, 3, 2, 1),       # strided, padded, ragged last block
+    (70, 2, 40, 40, 4, 3, 1, 1),      # two images per block, odd block count
+    (3, 4, 6, 6, 5, 3, 1, 2),         # padding wider than half the kernel
+    (2, 2, 5, 5, 3, 5, 1, 2),         # kernel as large as the image
+    (9, 3, 7, 7, 4, 3, 3, 0),         # stride == kernel
+    (2, 1, 1, 1, 2, 5, 2, 2),         # 1x1 input living entirely on padding taps
+])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_blocked_native_convolution_matches_aten(shape, threads):
+    """csrc/host/cpu_conv.cpp: forward, data gradient and (accumulating) weight gradient against ATen."""
+    B, C, H, W, OC, k, st, pd = shape
+    old = N.get_num_threads()
+    N.set_num_threads(threads)
+    try:
+        g = torch.Generator().manual_seed(B * 131 + k)
+        x, w, b = torch.randn(B, C, H, W, generator=g), torch.randn(OC, C, k, k, generator=g), torch.randn(OC, generator=g)
+        y = N.conv2d_forward(x, w, b, (st, st), (pd, pd))
+        y_ref = F.conv2d(x, w, b, st, pd)
+        assert y.shape == y_ref.shape and torch.allclose(y, y_ref, atol=2e-4, rtol=1e-4)
+        assert torch.allclose(N.conv2d_forward(x, w, None, (st, st), (pd, pd)), F.conv2d(x, w, None, st, pd),
+                              atol=2e-4, rtol=1e-4)
+        dy = torch.randn(y_ref.shape, generator=g)
+        dx = N.conv2d_backward_data(dy, w, x.shape, (st, st), (pd, pd))
+        assert torch.allclose(dx, torch.nn.grad.conv2d_input(x.shape, w, dy, st, pd), atol=3e-4, rtol=1e-4)
+        dw = torch.full_like(w, 0.5)
+        N.conv2d_backward_weight(dy, x, dw, (st, st), (pd, pd))          # accumulates
+        dw_ref = 0.5 + torch.nn.grad.conv2d_weight(x, w.shape, dy, st, pd)
+        assert torch.allclose(dw, dw_ref, atol=1e-3 * float(dw_ref.abs().max()), rtol=1e-4)
+        dwt = torch.zeros(C, OC, k, k).permute(1, 0, 2, 3)                       # non-contiguous gradient tensor
+        N.conv2d_backward_weight(dy, x, dwt, (st, st), (pd, pd))
+        assert torch.allclose(dwt, dw_ref - 0.5, atol=1e-3 * float(dw_ref.abs().max()), rtol=1e-4)
+    finally:
+        N.set_num_threads(old)
