@@ -4,3 +4,4 @@ from .loaders import (BaseDataLoader, CIFAR10DataLoader, CIFAR100DataLoader, Ima
                       RegressionDataLoader, SyntheticDataLoader, TinyImageNetDataLoader, WiFiDataLoader,
                       create_cifar10_data_loaders, create_cifar100_data_loaders, create_mnist_data_loaders, create_mnist_data_loaders_dir,
                       create_tiny_imagenet_data_loaders)
+from .prefetch import PrefetchLoader  # noqa: F401

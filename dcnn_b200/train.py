@@ -322,6 +322,14 @@ def _train_classification(model, train_loader, test_loader, optimizer, loss_func
             train_loader.set_rng_state(ls[0])
             test_loader.set_rng_state(ls[1])
         print(f"Resumed from {resume}: epoch {state['epoch']}, lr {optimizer.get_learning_rate():.6g}")
+    # PREFETCH_DEPTH=k: stream the training set instead of materialising every batch -- batches are built k ahead on a
+    # worker thread (fresh augmentation every epoch, sample-level reshuffle) and copied to the GPU on a side stream
+    depth = get_env("PREFETCH_DEPTH", 0)
+    if depth > 0:
+        from .data import PrefetchLoader
+        dev = model.get_device()
+        train_loader = PrefetchLoader(train_loader, config.batch_size, depth,
+                                      dev if getattr(dev, "type", "cpu") == "cuda" else None)
     train_loader.prepare_batches(config.batch_size)
     test_loader.prepare_batches(config.batch_size)
     model.enable_profiling(config.profiler_type in ("NORMAL", "CUMULATIVE"))

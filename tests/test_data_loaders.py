@@ -164,3 +164,66 @@ def test_shards_are_disjoint_equal_and_cover_the_data():
     with pytest.raises(ValueError):
         ld.set_shard(3, 3)
     assert isinstance(np.asarray(ld._indices()), np.ndarray)
+
+
+def test_prefetch_loader_streams_the_same_batches_with_fresh_augmentation_per_epoch():
+    """PrefetchLoader == the sequence of loader.get_batch() calls (order, sharding, augmentation draws), ends epochs
+    cleanly, restarts after an early shuffle(), and re-draws the augmentation every epoch."""
+    from dcnn_b200.data import AugmentationBuilder, PrefetchLoader, SyntheticDataLoader
+
+    def make():
+        ld = SyntheticDataLoader(50, (3, 8, 8), 5, seed=3)
+        ld.set_augmentation(AugmentationBuilder().horizontal_flip(0.5).brightness(0.5, 0.2).random_crop(0.5, 2).build())
+        ld.set_seed(11)
+        return ld
+    ref, ld = make(), make()
+    pf = PrefetchLoader(ld, 16, depth=2)
+    assert pf.num_batches() == 4 and pf.size() == 50 and pf.get_image_shape() == [3, 8, 8]
+    epochs = []
+    for _ in range(2):
+        ref.shuffle(); ref.reset()
+        pf.shuffle(); pf.reset()
+        got = []
+        while True:
+            want = ref.get_batch(16)
+            have = pf.get_next_batch()
+            if want is None:
+                assert have is None
+                break
+            assert torch.equal(want[0], have[0]) and torch.equal(want[1], have[1])
+            got.append(have[0].clone())
+        assert [g.shape[0] for g in got] == [16, 16, 16, 2]
+        epochs.append(torch.cat(got))
+    assert not torch.equal(epochs[0], epochs[1])
+    # abandoning an epoch half way: the next one starts from the top
+    pf.shuffle(); pf.reset()
+    first = pf.get_next_batch()[0].clone()
+    pf.reset()
+    assert pf.get_next_batch()[0].shape == first.shape
+    n = 1
+    while pf.get_next_batch() is not None:
+        n += 1
+    assert n == 4
+    # sharding and drop_last
+    pf2 = PrefetchLoader(make(), 8, depth=1, drop_last=True)
+    pf2.set_shard(1, 2)
+    assert pf2.num_batches() == 3
+    assert sum(1 for _ in pf2) == 3
+    pf.close(); pf2.close()
+
+
+def test_prefetch_loader_surfaces_producer_errors():
+    from dcnn_b200.data import PrefetchLoader, SyntheticDataLoader
+
+    class Broken(SyntheticDataLoader):
+        def get_batch(self, bs):
+            if self.current_index >= 8:
+                raise RuntimeError("disk on fire")
+            return super().get_batch(bs)
+    pf = PrefetchLoader(Broken(32, (1, 4, 4), 2), 8)
+    pf.reset()
+    assert pf.get_next_batch() is not None
+    import pytest as _pytest
+    with _pytest.raises(RuntimeError, match="disk on fire"):
+        while pf.get_next_batch() is not None:
+            pass

@@ -62,6 +62,12 @@ def test_host_port_pipeline_launch(tmp_path):
     assert out.count(": shutdown") == 2
 
 
+def test_streaming_loader_in_the_stock_training_loop(tmp_path):
+    out = _run([sys.executable, os.path.join(ROOT, "examples", "cifar10_resnet9.py")], cwd=str(tmp_path),
+               PREFETCH_DEPTH="2", EPOCHS="2")
+    assert out.count("Validation - Loss") == 2 and "Training batches: 2" in out
+
+
 def test_flag_overrides_reach_an_example(tmp_path):
     out = _run([sys.executable, os.path.join(ROOT, "examples", "mnist_cnn_trainer.py"), "--epochs", "2",
                 "--batch-size=4"], cwd=str(tmp_path))
