@@ -3,4 +3,4 @@ from .coordinator import Coordinator, DistributedCoordinator, InProcessCoordinat
 from .protocol import CommandType, Endpoint, Job, LoadTracker, Message, StageConfig  # noqa: F401
 from .stage import NetworkStageWorker, PipelineStage  # noqa: F401
 from .engine import PipelineEngine, PipelineLinks, build_schedule, make_pipeline_groups  # noqa: F401
-from .tcp import TcpCommunicator, TcpCoordinator, TcpStageWorker  # noqa: F401
+from .tcp import PipelineStageLost, TcpCommunicator, TcpCoordinator, TcpStageWorker  # noqa: F401

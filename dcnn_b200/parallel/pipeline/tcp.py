@@ -25,6 +25,7 @@ import json
 import struct
 import sys
 import threading
+import time
 import warnings
 from typing import List, Optional, Sequence, Tuple
 
@@ -32,7 +33,7 @@ import torch
 
 from ... import _hostlib
 from .communicator import Communicator, _restore_tensors, _strip_tensors
-from .coordinator import Coordinator
+from .coordinator import Coordinator, PipelineTimeout
 from .protocol import CommandType, Endpoint, Job, LoadTracker, Message
 from .stage import PipelineStage
 
@@ -330,6 +331,10 @@ class TcpCommunicator(Communicator):
 
 
 # ---- coordinator and worker -----------------------------------------------------------------------------------
+class PipelineStageLost(PipelineTimeout):
+    """A stage's connection closed while the coordinator was waiting for it."""
+
+
 def parse_host_port(s: str, default_host: str = "127.0.0.1") -> Tuple[str, int]:
     """'host:port' or 'port'."""
     if ":" in s:
@@ -352,6 +357,23 @@ class TcpCoordinator(Coordinator):
         self.coordinator_endpoint = Endpoint.tcp(advertise_host, self.comm.port)
         devs = stage_devices or ["cpu"] * len(addrs)
         self.remote_endpoints = [Endpoint.tcp(h, p, d) for (h, p), d in zip(addrs, devs)]
+
+    def join(self, ctype: CommandType, expected: int, timeout: float = 60.0, raise_on_timeout: bool = True) -> bool:
+        """Like Coordinator.join, but a stage whose connection dropped fails the wait at once (``PipelineStageLost``)
+        instead of running into the timeout: the transport notices end-of-stream within one io-loop wake-up."""
+        deadline = time.monotonic() + timeout
+        while True:
+            left = deadline - time.monotonic()
+            if self.comm.wait_for_count(ctype, expected, max(0.0, min(0.25, left))):
+                break
+            lost = [n for n in self.stage_names if n in self.comm._recipients and not self.comm.peer_alive(n)]
+            if lost and self.is_deployed and ctype != CommandType.CONFIG_RECEIVED:
+                self._drain_errors()
+                raise PipelineStageLost(f"lost the connection to {', '.join(lost)} while waiting for "
+                                        f"{expected} x {ctype.name} (got {self.comm.message_count(ctype)})")
+            if left <= 0:
+                break
+        return super().join(ctype, expected, 0.0, raise_on_timeout)
 
     def stop(self):
         super().stop()

@@ -221,3 +221,35 @@ def test_tcp_coordinator_with_two_network_worker_processes_matches_single_device
         assert abs(a - b) < 1e-4
     for p, q in zip(coord.model.parameters(), ref.parameters()):
         assert torch.allclose(p, q, atol=1e-5, rtol=1e-4)
+
+
+def test_tcp_coordinator_notices_a_killed_worker_long_before_the_timeout():
+    from dcnn_b200.parallel.pipeline import PipelineStageLost
+    workers = [_start_worker(), _start_worker()]
+    coord = None
+    try:
+        coord = TcpCoordinator(_model(), dnn.SGD(0.05, 0.9), [("127.0.0.1", port) for _, port in workers])
+        coord.seed = 77
+        coord.set_loss_function(dnn.SoftmaxCrossEntropyLoss())
+        coord.set_num_microbatches(2)
+        coord.initialize()
+        assert coord.deploy_stages(timeout=120)
+        coord.start()
+        x, t = _data()
+        coord.async_process_batch(split_microbatches(x, 2), split_microbatches(t, 2))
+        coord.update_parameters()
+        workers[1][0].kill()                      # the last stage dies
+        workers[1][0].wait(timeout=30)
+        t0 = time.time()
+        # whichever notices first: the coordinator's own dead connection (PipelineStageLost), a send into it
+        # (ConnectionError), or stage 0 reporting that its neighbour is gone (ERROR_REPORT -> RuntimeError)
+        with pytest.raises((PipelineStageLost, ConnectionError, RuntimeError)):
+            coord.async_process_batch(split_microbatches(x, 2), split_microbatches(t, 2), timeout=120.0)
+            coord.update_parameters(timeout=120.0)
+        assert time.time() - t0 < 30
+    finally:
+        for p, _ in workers:
+            if p.poll() is None:
+                p.kill()
+        if coord is not None:
+            coord.close()
