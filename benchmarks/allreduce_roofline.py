@@ -27,13 +27,13 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = f"cuda:{local}"
 
-    def build(baseline):
+    def build(baseline, num_blocks=0):
         m = create_resnet50_tiny_imagenet()
         m.set_seed(1)
         m.set_device(dev)
         m.initialize()
         opt = nn.Adam(1e-4, epsilon=1e-3, weight_decay=1e-3)
-        return m, opt, DataParallel(m, opt, dist.group.WORLD, sync_bn=False, nccl_baseline=baseline)
+        return m, opt, DataParallel(m, opt, dist.group.WORLD, sync_bn=False, nccl_baseline=baseline, num_blocks=num_blocks)
 
     def bench(dp, m, iters=20, warm=5):
         for g in m.gradients():
@@ -58,6 +58,14 @@ def main():
     total_params = dp.n
     del dp, m, opt
     torch.cuda.empty_cache()
+    # CTAs of the fused kernel: the default is one per SM; more resident CTAs keep more NVLink loads in flight
+    sweep = {}
+    sms = torch.cuda.get_device_properties(local).multi_processor_count
+    for mult in (2, 4):
+        m, opt, dp = build(False, num_blocks=mult * sms)
+        sweep[f"{mult}x_sms"] = round(bench(dp, m), 4)
+        del dp, m, opt
+        torch.cuda.empty_cache()
     m2, opt2, dp2 = build(True)
     nccl_ms = bench(dp2, m2)
     if rank == 0:
@@ -75,7 +83,7 @@ def main():
         floor_ms = nbytes / bw * 1e3
         hbm_ms = 7 * 4 * total_params / world / 6.5e12 * 1e3
         print(json.dumps({"world": world, "params": total_params, "nvlink_bytes_per_dir": nbytes,
-                          "fused_ms": round(fused_ms, 4), "nccl_allreduce_plus_update_ms": round(nccl_ms, 4),
+                          "fused_ms": round(fused_ms, 4), "fused_ms_by_ctas": sweep, "nccl_allreduce_plus_update_ms": round(nccl_ms, 4),
                           "nvlink_floor_ms": round(floor_ms, 4), "hbm_floor_ms": round(hbm_ms, 4),
                           "fraction_of_nvlink_roofline": round(floor_ms / fused_ms, 3),
                           "speedup_vs_nccl_path": round(nccl_ms / fused_ms, 2), "nvlink_GBps_assumed": bw / 1e9}))

@@ -40,6 +40,21 @@ struct ArParams {
   int mode;  // 0 SGD, 1 momentum, 2 Adam, 3 AdamW
 };
 
+// Own slice plus the W-1 peers' slices.  All peer loads are issued before the first one is consumed: an NVLink load
+// takes microseconds, and a load-add-load-add chain would keep only one of them in flight per thread.  The summation
+// order (own, rank+1, rank+2, ...) is the same as the generic loop's, so the result is bit-identical to it.
+template <int W>
+__device__ __forceinline__ float4 gather_sum(const ArParams& p, long long e) {
+  float4 v[W];
+  v[0] = *reinterpret_cast<const float4*>(p.grads[p.rank] + e);
+#pragma unroll
+  for (int r = 1; r < W; ++r) v[r] = ld_peer4(p.grads[(p.rank + r) & (W - 1)] + e);
+  float4 g = v[0];
+#pragma unroll
+  for (int r = 1; r < W; ++r) { g.x += v[r].x; g.y += v[r].y; g.z += v[r].z; g.w += v[r].w; }
+  return g;
+}
+
 __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __grid_constant__ ArParams pp) {
   ArParams p = pp;
   const unsigned long long epoch = *p.epoch_ptr;
@@ -56,15 +71,23 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __gri
        i += (long long)gridDim.x * blockDim.x) {
     const long long e = p.shard_begin + i * 4;
     // reduce-scatter: sum this 16-byte slice over all replicas (own copy first, peers over NVLink)
-    float4 g = *reinterpret_cast<const float4*>(p.grads[p.rank] + e);
+    float4 g;
+    switch (p.world) {
+      case 2: g = gather_sum<2>(pp, e); break;
+      case 4: g = gather_sum<4>(pp, e); break;
+      case 8: g = gather_sum<8>(pp, e); break;
+      default: {
+        g = *reinterpret_cast<const float4*>(pp.grads[p.rank] + e);
 #pragma unroll 1
-    for (int r = 1; r < p.world; ++r) {
-      const int src = (p.rank + r) % p.world;
-      const float4 v = ld_peer4(p.grads[src] + e);
-      g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        for (int r = 1; r < p.world; ++r) {
+          const int src = (p.rank + r) % p.world;
+          const float4 v = ld_peer4(pp.grads[src] + e);
+          g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+      }
     }
     g.x *= p.inv_world; g.y *= p.inv_world; g.z *= p.inv_world; g.w *= p.inv_world;
-    float4 w = *reinterpret_cast<const float4*>(p.params[p.rank] + e);
+    float4 w = *reinterpret_cast<const float4*>(pp.params[p.rank] + e);
     float gg[4] = {g.x, g.y, g.z, g.w};
     float ww[4] = {w.x, w.y, w.z, w.w};
     const long long s = e - p.shard_begin;
@@ -99,7 +122,7 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __gri
 #pragma unroll 1
     for (int r = 0; r < p.world; ++r) {
       const int dst = (p.rank + r) % p.world;
-      *reinterpret_cast<float4*>(p.params[dst] + e) = out;
+      *reinterpret_cast<float4*>(pp.params[dst] + e) = out;   // pointer tables are read from the parameter bank
     }
   }
   // this rank may only zero ITS OWN gradient buffer once every peer has read it: that is guaranteed after the
