@@ -13,3 +13,4 @@ from .schedulers import (CosineAnnealingLR, CosineAnnealingWarmRestarts, Exponen
                          LinearWarmup, MultiStepLR, OneCycleLR, PolynomialLR, ReduceLROnPlateau,
                          Scheduler, SchedulerFactory, StepLR, WarmupCosineAnnealing)
 from .sequential import Partition, Sequential, SequentialBuilder  # noqa: F401
+from .mem_pool import MemPool, TempBuffer  # noqa: F401

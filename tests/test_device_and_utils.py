@@ -81,3 +81,70 @@ def test_hardware_info_topology_dynamic_and_affinity():
             assert not ta.set_cores([])
         finally:
             os.sched_setaffinity(0, before)
+
+
+def test_mem_pool_best_fit_and_temp_buffer():
+    """ref include/nn/mem_pool.hpp: free blocks keyed by capacity, smallest sufficient block wins, TempBuffer returns
+    its block on scope exit."""
+    import torch
+    from dcnn_b200.nn import MemPool, TempBuffer
+    pool = MemPool()
+    a, b = pool.get([4, 8]), pool.get([100])
+    assert a.shape == (4, 8) and b.shape == (100,) and pool.misses == 2
+    pa, pb = a.data_ptr(), b.data_ptr()
+    pool.release(a)
+    pool.release(b)
+    assert pool.free_blocks() == 2 and pool.free_bytes() == (32 + 100) * 4
+    c = pool.get([5, 5])                  # 25 elements: the 32-element block, not the 100-element one
+    assert c.data_ptr() == pa and c.shape == (5, 5) and pool.hits == 1
+    d = pool.get([64])
+    assert d.data_ptr() == pb
+    e = pool.get([1000])                  # nothing fits any more
+    assert pool.misses == 3 and e.numel() == 1000
+    pool.release(c)
+    with TempBuffer(pool, [2, 3]) as t:
+        assert t.data_ptr() == pa and pool.free_blocks() == 0
+        t.fill_(1.0)
+    assert pool.free_blocks() == 1
+    buf = TempBuffer(pool, [8])
+    buf.release()
+    buf.release()                         # idempotent
+    assert pool.free_blocks() == 1
+    pool.release(torch.zeros(3, 3))       # foreign contiguous tensors of the pool's dtype are accepted
+    assert pool.free_blocks() == 2
+    pool.clear()
+    assert pool.free_blocks() == 0
+
+
+def test_matrix_container():
+    """ref include/matrix/matrix.hpp: value semantics, element-wise operators, matrix product, shape errors."""
+    import pytest
+    import torch
+    from dcnn_b200.utils.matrix import Matrix
+    a = Matrix(2, 3, [1, 2, 3, 4, 5, 6])
+    b = Matrix(2, 3)
+    b.fill(1.0)
+    c = a + b
+    assert c(1, 2) == 7.0 and a(1, 2) == 6.0 and (c - b).data().equal(a.data())
+    c -= b
+    c += b
+    c *= 2.0
+    c /= 4.0
+    assert torch.allclose(c.data(), (a.data() + 1) / 2)
+    p = a * Matrix(3, 2, [1, 0, 0, 1, 1, 1])
+    assert p.rows() == 2 and p.cols() == 2 and torch.allclose(p.data(), torch.tensor([[4., 5.], [10., 11.]]))
+    assert torch.allclose((a * 2.0).data(), (a / 0.5).data())
+    r = a.reshape(3, 2)
+    r[0, 0] = 9.0
+    assert a(0, 0) == 1.0 and r.size() == 6          # reshape and clone copy
+    with pytest.raises(ValueError):
+        a + Matrix(3, 2)
+    with pytest.raises(ValueError):
+        a * Matrix(2, 2)
+    with pytest.raises(ZeroDivisionError):
+        a / 0.0
+    m = Matrix(4, 4)
+    m.fill_random_uniform(0.5, seed=1)
+    assert float(m.data().abs().max()) <= 0.5
+    m.resize(2, 8)
+    assert m.rows() == 2 and float(m.data().abs().sum()) == 0.0
