@@ -21,6 +21,9 @@ for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN
 done
 echo '== tma probe (native)'; [ -x scripts/native/tma_probe ] || nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -Icsrc scripts/native/tma_probe_main.cu csrc/core.cu -o scripts/native/tma_probe -lcuda
 timeout 30 scripts/native/tma_probe gpurun_out/tma_probe2.txt; cat gpurun_out/tma_probe2.txt | cut -c1-200
+for v in "--tf32 1 --channels-last 1 --graph 1" "--tf32 0 --channels-last 0 --graph 0"; do
+  run "torch_baseline_$(echo $v | tr -d ' -')" python benchmarks/torch_baseline.py $v; tail -1 "gpurun_out/torch_baseline_$(echo $v | tr -d ' -').log" | cut -c1-400
+done
 run conv_vs_cudnn python benchmarks/conv_vs_cudnn.py; tail -25 gpurun_out/conv_vs_cudnn.log | cut -c1-200
 DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 DCNN_BN_FINALIZE_NARROW=1 run kernels_all python scripts/prof_kernels.py
 head -30 gpurun_out/kernels_all.log | cut -c1-170
