@@ -1,7 +1,7 @@
 // Native CPU convolution, NCHW fp32: blocked im2col + GEMM with the output written in place.
 // The reference's CPU Conv2D (src/nn/layers_impl/cpu/conv2d_ops.cpp:19-67) materialises im2col for the whole batch,
 // runs one GEMM into a [OC][N*OH*OW] matrix and transposes that back to NCHW.  Here the batch is cut into blocks of
-// images whose column matrix (K x ~4096 floats) stays cache-resident: a block is expanded, multiplied and written to
+// images whose column matrix (K x 256..4096 floats, about 4 MB) stays cache-resident: a block is expanded, multiplied and written to
 // its NCHW destination before the next one is touched, so neither the full column matrix nor the transposed output
 // ever goes through memory.  Forward, data gradient and weight gradient share the block walk; the weight gradient
 // re-expands the block instead of keeping the forward's columns (cheaper than reading them back from DRAM).
@@ -36,8 +36,11 @@ struct Scratch {
 thread_local Scratch tls;
 
 int images_per_block(const Geo& g) {
-  const int target = 4096;   // columns per block: K x 4096 floats is L2-sized for the K's of small CNNs
-  return std::max(1, std::min(g.N, target / std::max(1, g.P())));
+  // columns per block: as many as keep the K x columns expansion around 4 MB (L2-resident), between 256 (enough width
+  // for the GEMM's register tiles to amortise packing) and 4096
+  const long long budget_floats = 1 << 20;
+  const int cols = (int)std::max<long long>(256, std::min<long long>(4096, budget_floats / std::max(1, g.K())));
+  return std::max(1, std::min(g.N, cols / std::max(1, g.P())));
 }
 
 // output columns ow with 0 <= ow*sw - pw + s < W form the range [first_valid, end_valid)
