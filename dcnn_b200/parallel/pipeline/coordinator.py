@@ -322,6 +322,66 @@ class Coordinator:
     def send_all_params(self) -> bool:
         return all(self.send_params(i) for i in range(self.num_stages))
 
+    # -- recovery ----------------------------------------------------------------------------------------
+    def replace_stage(self, stage_index: int, endpoint: Endpoint, timeout: float = 60.0,
+                      restore_parameters: bool = True) -> bool:
+        """Bring a fresh worker at ``endpoint`` into the pipeline in place of stage ``stage_index`` (which crashed or
+        was lost): deploy the stage's configuration to it, make its neighbours re-dial it, discard whatever the
+        surviving stages kept of the batch that was in flight, and -- with ``restore_parameters`` -- load EVERY stage
+        with the coordinator's copy of the parameters (the last ``collect_current_parameters`` / ``save_checkpoint``),
+        so that all stages continue from the same snapshot.  Optimizer moments of the replaced stage start from zero.
+        The reference has no recovery path (a lost worker ends the run)."""
+        if not 0 <= stage_index < self.num_stages:
+            raise IndexError("stage index out of range")
+        name = self.stage_names[stage_index]
+        self.errors.clear()
+        for c in CommandType:                       # answers and error reports of the failed batch are void
+            if c != CommandType._START and c != CommandType._COUNT:
+                self.comm.dequeue_all_messages_by_type(c)
+        self.remote_endpoints[stage_index] = endpoint
+        self._initialize_topology()
+        try:
+            self.comm.disconnect(name)
+        except Exception:
+            pass
+        if not self.comm.connect(name, endpoint):
+            return False
+        self._deliver_config(name, self.stage_configs[stage_index])
+        if not self.join(CommandType.CONFIG_RECEIVED, 1, timeout, raise_on_timeout=False):
+            print(f"Replacement for {name} did not report ready")
+            return False
+        self.comm.dequeue_all_messages_by_type(CommandType.CONFIG_RECEIVED)
+        survivors = 0
+        for i, other in enumerate(self.stage_names):
+            if i == stage_index:
+                continue
+            rewire = {}
+            if i == stage_index - 1:
+                rewire["next_stage"] = self._endpoint_payload(endpoint)
+            if i == stage_index + 1:
+                rewire["prev_stage"] = self._endpoint_payload(endpoint)
+            self.comm.send_message(Message(other, CommandType.CONFIG_TRANSFER, {"rewire": rewire, "reset": True},
+                                           "coordinator"))
+            survivors += 1
+        if survivors and not self.join(CommandType.CONFIG_RECEIVED, survivors, timeout, raise_on_timeout=False):
+            print("Not all surviving stages acknowledged the new topology")
+            return False
+        self.comm.dequeue_all_messages_by_type(CommandType.CONFIG_RECEIVED)
+        if restore_parameters:
+            have = bool(self.model.layers) and all(p is not None for p in self.model.parameters())
+            if not have:
+                print("Warning: no parameter snapshot on the coordinator (collect_current_parameters was never "
+                      "called): the replacement starts from its initialisation, the other stages keep their weights")
+            elif not self.send_all_params():
+                return False
+        self.set_training(True)
+        print(f"Replaced {name}")
+        return True
+
+    def _endpoint_payload(self, endpoint: Endpoint):
+        """In-process endpoints carry live objects and travel as they are; the others as JSON."""
+        return endpoint if endpoint.kind == "in_process" else endpoint.to_json()
+
     def save_checkpoint(self, path: str) -> bool:
         if not self.collect_current_parameters():
             return False

@@ -206,7 +206,29 @@ class PipelineStage:
         else:
             self._send("prev_stage", CommandType.BACKWARD_JOB, Job(grad, job.micro_batch_id))
 
+    def _rewire(self, req: dict):
+        """Recovery message from the coordinator (``Coordinator.replace_stage``): re-dial the named neighbours and, with
+        ``reset``, drop everything that belongs to the batch that was in flight when a stage was lost -- cached
+        activations, partially accumulated gradients, loss counters."""
+        from .protocol import Endpoint
+        for role, ep in (req.get("rewire") or {}).items():
+            ep = ep if isinstance(ep, Endpoint) else Endpoint.from_json(ep)
+            try:
+                self.comm.disconnect(role)
+            except Exception:
+                pass
+            if not self.comm.connect(role, ep):
+                raise ConnectionError(f"{self.name}: cannot reach the new {role}")
+        if req.get("reset") and self.model is not None:
+            self.model.clear_gradients()
+            self.model.clear_cache()
+            self.loss_sum = self.correct_sum = 0.0
+            self.loss_count = 0
+        self._send("coordinator", CommandType.CONFIG_RECEIVED, True)
+
     def handle_configuration(self, payload):
+        if isinstance(payload, dict) and ("rewire" in payload or "reset" in payload):
+            return self._rewire(payload)
         cfg = payload if isinstance(payload, StageConfig) else StageConfig.from_json(payload)
         self.name = cfg.stage_id
         self.is_first, self.is_last = cfg.is_first, cfg.is_last

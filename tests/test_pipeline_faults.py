@@ -75,3 +75,42 @@ def test_delayed_messages_are_tolerated_and_lost_updates_time_out():
     finally:
         InProcessCommunicator.fault_hook = None
         c.stop()
+
+
+def test_replace_stage_in_process_middle_of_three():
+    """Coordinator.replace_stage with in-process endpoints: the middle stage of three is stopped and replaced; both
+    neighbours re-dial, every stage reloads the snapshot, and training continues with finite, decreasing loss."""
+    from dcnn_b200.parallel.pipeline import Endpoint, PipelineStage
+    c = InProcessCoordinator(_model(), dnn.SGD(0.05, 0.0), ["cpu"] * 3)
+    c.seed = 3
+    c.set_loss_function(dnn.SoftmaxCrossEntropyLoss())
+    c.set_num_microbatches(2)
+    c.initialize()
+    assert c.deploy_stages()
+    c.start()
+    try:
+        x, t = _data(8)
+        xs, ts = split_microbatches(x, 2), split_microbatches(t, 2)
+        c.async_process_batch(xs, ts)
+        first = c.update_parameters()["loss"]
+        assert c.collect_current_parameters()
+        snapshot = [p.clone() for p in c.model.parameters()]
+        c.stages[1].stop()                                    # the stage thread ends: its queue is never served again
+        with pytest.raises(PipelineTimeout):
+            c.async_process_batch(xs, ts, timeout=1.0)
+        comm = InProcessCommunicator("stage_1b")
+        fresh = PipelineStage(comm, "stage_1b", device="cpu")
+        fresh.start(threaded=True)
+        c.stages[1] = fresh
+        assert c.replace_stage(1, Endpoint.in_process(comm), timeout=30.0)
+        # every stage holds the snapshot again
+        assert c.collect_current_parameters()
+        for p, q in zip(c.model.parameters(), snapshot):
+            assert torch.equal(p, q)
+        losses = []
+        for _ in range(3):
+            c.async_process_batch(xs, ts)
+            losses.append(c.update_parameters()["loss"])
+        assert all(l == l for l in losses) and losses[-1] < first
+    finally:
+        c.stop()

@@ -253,3 +253,72 @@ def test_tcp_coordinator_notices_a_killed_worker_long_before_the_timeout():
                 p.kill()
         if coord is not None:
             coord.close()
+
+
+def _plain_sgd_reference(steps):
+    """Single device, SGD without momentum (a replaced stage loses its optimizer moments; plain SGD has none)."""
+    import dcnn_b200 as dc
+    from dcnn_b200.partitioner import NaivePartitioner
+    from dcnn_b200.train import TrainStep
+    full = _model()
+    parts = NaivePartitioner().get_partitions(full.get_layers(), 2)
+    subs = full.split(parts)
+    for i, s in enumerate(subs):
+        s.set_seed(77 + 1000003 * parts[i].start_layer)
+        s.initialize()
+    seq = dc.Sequential("ref")
+    for s in subs:
+        for l in s.layers:
+            seq.add(l)
+    opt = dnn.SGD(0.05, 0.0)
+    opt.attach(seq.parameters(), seq.gradients())
+    step = TrainStep(seq, opt, dnn.SoftmaxCrossEntropyLoss(), num_microbatches=2)
+    x, t = _data()
+    return seq, [float(step(x, t)[0]) for _ in range(steps)]
+
+
+def test_replacing_a_killed_worker_continues_from_the_snapshot_exactly(tmp_path):
+    """Elastic recovery: stage 1 is killed after two steps, a new worker process takes its place
+    (Coordinator.replace_stage), every stage is reloaded from the coordinator's snapshot, and steps 3-4 come out exactly
+    as in an uninterrupted single-device run."""
+    workers = [_start_worker(), _start_worker()]
+    coord = None
+    try:
+        coord = TcpCoordinator(_model(), dnn.SGD(0.05, 0.0), [("127.0.0.1", port) for _, port in workers])
+        coord.seed = 77
+        coord.set_loss_function(dnn.SoftmaxCrossEntropyLoss())
+        coord.set_num_microbatches(2)
+        coord.initialize()
+        assert coord.deploy_stages(timeout=120)
+        coord.start()
+        x, t = _data()
+        xs, ts = split_microbatches(x, 2), split_microbatches(t, 2)
+        losses = []
+        for _ in range(2):
+            coord.async_process_batch(xs, ts)
+            losses.append(coord.update_parameters()["loss"])
+        assert coord.collect_current_parameters()            # the snapshot recovery starts from
+        workers[1][0].kill()
+        workers[1][0].wait(timeout=30)
+        with pytest.raises(Exception):
+            coord.async_process_batch(xs, ts, timeout=60.0)
+            coord.update_parameters(timeout=60.0)
+        workers.append(_start_worker())
+        assert coord.replace_stage(1, Endpoint.tcp("127.0.0.1", workers[2][1]), timeout=120)
+        for _ in range(2):
+            coord.async_process_batch(xs, ts)
+            losses.append(coord.update_parameters()["loss"])
+        assert coord.collect_current_parameters()
+        coord.stop()
+        assert workers[0][0].wait(timeout=60) == 0 and workers[2][0].wait(timeout=60) == 0
+    finally:
+        for p, _ in workers:
+            if p.poll() is None:
+                p.kill()
+        if coord is not None:
+            coord.close()
+    ref, ref_losses = _plain_sgd_reference(4)
+    for a, b in zip(losses, ref_losses):
+        assert abs(a - b) < 1e-4
+    for p, q in zip(coord.model.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, atol=1e-5, rtol=1e-4)
