@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Compression benchmark (counterpart of benchmarks/compression_benchmark.cpp: zstd level 3 on a 32x3x1028x1028 FP32
-tensor; default here 32x3x256x256).  Uses the optional checkpoint-compression hook (zstd if installed, else zlib)."""
+tensor; default here 32x3x256x256).  Uses io/compression.py: zstd and LZ4-HC from the system libraries through ctypes, zlib for comparison."""
 import os
 import sys
 import time

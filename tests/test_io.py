@@ -104,3 +104,27 @@ def test_compression_round_trip():
         blob = compression.compress(data, codec)
         assert compression.decompress(blob) == data
     assert len(compression.compress(data, "zstd")) < len(data)
+    assert compression.compress(b"", "zstd")[4:] == b"" and compression.decompress(compression.compress(b"", "lz4hc")) == b""
+
+
+def test_zstd_frames_are_plain_zstd_like_the_reference_and_lz4hc_is_real():
+    """ZstdCompressor writes / reads raw zstd frames (magic 0xFD2FB528, content size in the frame header) as the
+    reference's ZSTD_compress / ZSTD_getFrameContentSize path does; corrupt input is rejected; LZ4-HC round-trips."""
+    import pytest
+    if not compression.ZstdCompressor.available():
+        pytest.skip("no zstd library")
+    data = (np.arange(50000, dtype=np.float32) % 17).tobytes()
+    frame = compression.ZstdCompressor.compress(data, 3)
+    assert frame[:4] == b"\x28\xb5\x2f\xfd" and len(frame) < len(data) // 4
+    assert compression.ZstdCompressor.decompress(frame) == data
+    assert len(compression.ZstdCompressor.compress(data, 19)) <= len(frame)
+    with pytest.raises(ValueError):
+        compression.ZstdCompressor.decompress(b"not a zstd frame at all")
+    with pytest.raises(ValueError):
+        compression.ZstdCompressor.decompress(frame[:-5])
+    if compression.Lz4hcCompressor.available():
+        blob = compression.Lz4hcCompressor.compress(data)
+        assert len(blob) < len(data) // 4 and compression.Lz4hcCompressor.decompress(blob) == data
+        with pytest.raises(ValueError):
+            compression.Lz4hcCompressor.decompress(blob[:20])
+    assert "zstd" in compression.available_codecs()
