@@ -302,6 +302,10 @@ class AugmentationStrategy:
     def clear_augmentations(self):
         self.augmentations.clear()
 
+    def set_augmentations(self, augmentations):
+        """Replace the whole chain (clones are stored, like the reference's copy semantics)."""
+        self.augmentations = [a.clone() for a in augmentations]
+
     def set_seed(self, seed: int):
         for i, a in enumerate(self.augmentations):
             a.set_seed(seed + i)

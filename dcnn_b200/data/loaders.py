@@ -160,6 +160,12 @@ class BaseDataLoader:
     def set_augmentation(self, aug: AugmentationStrategy):
         self.augmentation = aug
 
+    def set_augmentation_strategy(self, aug: AugmentationStrategy):      # the reference's second spelling
+        self.set_augmentation(aug)
+
+    def generate_shuffled_indices(self, data_size: int) -> np.ndarray:
+        return self.rng.permutation(int(data_size))
+
     def clear_augmentation(self):
         self.augmentation = None
 
@@ -528,3 +534,29 @@ def create_tiny_imagenet_data_loaders(data_dir: str):
 def create_mnist_data_loaders_dir(data_dir: str):
     """``<dir>/train.csv`` + ``<dir>/test.csv`` (the reference examples read ./data/mnist/{train,test}.csv)."""
     return create_mnist_data_loaders(os.path.join(data_dir, "train.csv"), os.path.join(data_dir, "test.csv"))
+
+
+def create_data_loader(dataset_type: str):
+    """An empty loader for a dataset name (the reference declares this factory and returns nullptr from it,
+    data_loader.hpp:192-196; here it works): mnist | cifar10 | cifar100 | tiny_imagenet | wifi | regression."""
+    kinds = {"mnist": MNISTDataLoader, "cifar10": CIFAR10DataLoader, "cifar100": CIFAR100DataLoader,
+             "tiny_imagenet": TinyImageNetDataLoader, "tinyimagenet": TinyImageNetDataLoader,
+             "wifi": WiFiDataLoader, "uji": WiFiDataLoader, "regression": RegressionDataLoader}
+    key = dataset_type.strip().lower().replace("-", "_")
+    if key not in kinds:
+        raise ValueError(f"unknown dataset type '{dataset_type}' (known: {sorted(kinds)})")
+    return kinds[key]()
+
+
+def train_val_split(dataset_size: int, val_ratio: float = 0.2, seed: int = 42):
+    """(train indices, validation indices) of a shuffled split (ref data_loader.hpp:205-222: the last
+    ``int(size * val_ratio)`` shuffled indices form the validation set)."""
+    idx = np.random.default_rng(int(seed)).permutation(int(dataset_size))
+    val = int(dataset_size * val_ratio)
+    return idx[:dataset_size - val].copy(), idx[dataset_size - val:].copy()
+
+
+def normalize_to_unit_range(data, max_value: float = 255.0):
+    """In place ``data /= max_value`` for tensors and arrays (ref data_loader.hpp:182-186)."""
+    data /= max_value
+    return data

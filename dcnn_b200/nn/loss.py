@@ -21,6 +21,10 @@ class Loss:
     def name(self) -> str:
         return self.display
 
+    def num_parameters(self) -> int:
+        """Tunable scalars of the loss (Huber's delta); 0 for the others (ref loss.hpp)."""
+        return 1 if self.kind == "huber" else 0
+
     def forward_backward(self, predictions, targets, want_grad=True):
         """-> (loss scalar tensor on device, grad | None, correct-count tensor | None)."""
         return ops.loss_forward_backward(self.kind, predictions, targets, self.param, want_grad)
@@ -75,6 +79,12 @@ class HuberLoss(Loss):
 
     def get_config(self):
         return {"type": self.kind, "name": self.display, "parameters": {"delta": self.param}}
+
+    def set_delta(self, delta: float):
+        self.param = float(delta)
+
+    def get_delta(self) -> float:
+        return self.param
 
 
 class LossFactory:

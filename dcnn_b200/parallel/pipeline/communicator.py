@@ -50,6 +50,27 @@ class Communicator:
     def set_message_notification_callback(self, cb: Callable[[], None]):
         self._callback = cb
 
+    # the reference's spellings (communicator.hpp:60-98)
+    def register_recipient(self, recipient_id: str, endpoint: Endpoint):
+        self._recipients[recipient_id] = endpoint
+
+    def unregister_recipient(self, recipient_id: str):
+        self._recipients.pop(recipient_id, None)
+
+    def connect_to_endpoint(self, recipient_id: str, endpoint: Endpoint) -> bool:
+        return self.connect(recipient_id, endpoint)
+
+    def disconnect_from_endpoint(self, recipient_id: str):
+        self.disconnect(recipient_id)
+
+    def enqueue_output_message(self, msg: Message):
+        """The reference queues outgoing messages for a sender thread; here sending is immediate (the TCP backend
+        queues inside the native transport), so this is ``send_message``."""
+        self.send_message(msg)
+
+    def has_output_message(self) -> bool:
+        return False
+
     # -- input side -----------------------------------------------------------------------------
     def enqueue_input_message(self, msg: Message):
         with self._cv:

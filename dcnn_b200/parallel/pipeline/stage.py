@@ -48,6 +48,12 @@ class PipelineStage:
         if model is not None and optimizer is not None:
             optimizer.attach(model.parameters(), model.gradients())
 
+    def get_stage_id(self) -> str:
+        return self.name
+
+    def is_configured(self) -> bool:
+        return self.model is not None and self.optimizer is not None
+
     # -- lifecycle ---------------------------------------------------------------------------------------
     def start(self, threaded: bool = True):
         self.should_stop = False

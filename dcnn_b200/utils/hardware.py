@@ -144,6 +144,185 @@ class HardwareInfo:
             pass
         return out
 
+    # ---- the reference's accessors (include/utils/hardware_info.hpp) -------------------------------------------------
+    def _need(self):
+        if not self.initialized:
+            self.initialize()
+        return self.info
+
+    def is_initialized(self) -> bool:
+        return self.initialized
+
+    def _cpuinfo_field(self, *names) -> str:
+        try:
+            with open("/proc/cpuinfo") as f:
+                for line in f:
+                    k, _, v = line.partition(":")
+                    if k.strip() in names:
+                        return v.strip()
+        except OSError:
+            pass
+        return ""
+
+    def get_vendor(self) -> str:
+        return self._cpuinfo_field("vendor_id") or platform.machine()
+
+    def get_model_name(self) -> str:
+        return str(self._need()["cpu"]["vendor_model"])
+
+    def get_architecture(self) -> str:
+        return platform.machine()
+
+    def get_family(self) -> int:
+        v = self._cpuinfo_field("cpu family")
+        return int(v) if v.isdigit() else 0
+
+    def get_model(self) -> int:
+        v = self._cpuinfo_field("model")
+        return int(v) if v.isdigit() else 0
+
+    def get_stepping(self) -> int:
+        v = self._cpuinfo_field("stepping")
+        return int(v) if v.isdigit() else 0
+
+    def get_physical_cores(self) -> int:
+        return int(self._need()["topology"]["physical"])
+
+    def get_logical_cores(self) -> int:
+        return int(self._need()["topology"]["logical"])
+
+    def get_sockets(self) -> int:
+        return int(self._need()["topology"]["sockets"])
+
+    def supports_hyperthreading(self) -> bool:
+        return int(self._need()["topology"]["threads_per_core"]) > 1
+
+    def _flag(self, name: str) -> bool:
+        return name in self._cpuinfo_field("flags").split()
+
+    def supports_avx(self) -> bool:
+        return self._flag("avx")
+
+    def supports_avx2(self) -> bool:
+        return bool(self._need()["cpu"]["avx2"])
+
+    def supports_avx512(self) -> bool:
+        return bool(self._need()["cpu"]["avx512f"])
+
+    def supports_fma(self) -> bool:
+        return bool(self._need()["cpu"]["fma"])
+
+    def supports_sse4_2(self) -> bool:
+        return self._flag("sse4_2")
+
+    def supports_aes(self) -> bool:
+        return self._flag("aes")
+
+    def supports_sha(self) -> bool:
+        return self._flag("sha_ni")
+
+    def supports_bmi1(self) -> bool:
+        return self._flag("bmi1")
+
+    def supports_bmi2(self) -> bool:
+        return self._flag("bmi2")
+
+    def _khz(self, which: str) -> List[int]:
+        per = self._need()["topology"]["per_cpu"]
+        if which == "max":
+            return [c["max_khz"] for c in per.values() if c["max_khz"] > 0]
+        out = []
+        for cpu in per:
+            v = self._read(f"/sys/devices/system/cpu/cpu{cpu}/cpufreq/{which}")
+            if v and v.isdigit():
+                out.append(int(v))
+        return out
+
+    def get_max_frequency_mhz(self) -> float:
+        v = self._khz("max")
+        return max(v) / 1000.0 if v else float(self._need()["cpu"]["mhz"])
+
+    def get_min_frequency_mhz(self) -> float:
+        v = self._khz("cpuinfo_min_freq")
+        return min(v) / 1000.0 if v else float(self._need()["cpu"]["mhz"])
+
+    def get_base_frequency_mhz(self) -> float:
+        v = self._khz("base_frequency")
+        return max(v) / 1000.0 if v else float(self._need()["cpu"]["mhz"])
+
+    def get_cache_line_size(self) -> int:
+        v = self._read("/sys/devices/system/cpu/cpu0/cache/index0/coherency_line_size")
+        return int(v) if v and v.isdigit() else 64
+
+    def get_memory_hierarchy(self) -> Dict[str, object]:
+        return dict(self._need()["caches"])
+
+    def get_total_memory_bytes(self) -> int:
+        return int(self._memory().get("MemTotal", 0))
+
+    def get_available_memory_bytes(self) -> int:
+        return int(self._memory().get("MemAvailable", 0))
+
+    def get_used_memory_bytes(self) -> int:
+        m = self._memory()
+        return int(m.get("MemTotal", 0) - m.get("MemAvailable", 0))
+
+    def get_memory_utilization_percent(self) -> float:
+        m = self._memory()
+        return 100.0 * (1.0 - m.get("MemAvailable", 0) / m["MemTotal"]) if m.get("MemTotal") else 0.0
+
+    def get_load_averages(self) -> List[float]:
+        return list(os.getloadavg()) if hasattr(os, "getloadavg") else []
+
+    def update_utilization(self) -> float:
+        return float(self.update_dynamic_info()["cpu_utilization_percent"])
+
+    def get_overall_utilization(self) -> float:
+        dyn = self.info.get("dynamic") or self.update_dynamic_info()
+        return float(dyn["cpu_utilization_percent"])
+
+    def get_thermal_info(self) -> Dict[str, float]:
+        return self._thermal()
+
+    def is_containerized(self) -> bool:
+        if os.path.exists("/.dockerenv") or os.environ.get("KUBERNETES_SERVICE_HOST"):
+            return True
+        cg = self._read("/proc/1/cgroup", "") or ""
+        return any(w in cg for w in ("docker", "kubepods", "containerd", "lxc")) or bool(self._need()["cgroup"])
+
+    def is_virtualized(self) -> bool:
+        return self._flag("hypervisor")
+
+    def get_container_cpu_limit(self) -> float:
+        """CPUs granted by the cgroup quota (0 = unlimited)."""
+        return float(self._need()["cgroup"].get("cpu_limit_cores", 0.0) or 0.0)
+
+    def get_optimal_thread_count(self) -> int:
+        """Physical cores that this process may use (affinity mask and cgroup quota respected)."""
+        usable = self.get_usable_cores()
+        per_core = max(1, int(self._need()["topology"]["threads_per_core"]))
+        n = max(1, usable // per_core if usable >= per_core else usable)
+        limit = self.get_container_cpu_limit()
+        return max(1, min(n, int(limit))) if limit >= 1 else n
+
+    def get_recommended_cpu_affinity(self, num_threads: int = 0) -> List[int]:
+        """One logical CPU per physical core, performance cores first."""
+        topo = self._need()["topology"]
+        allowed = set(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else set(topo["per_cpu"])
+        seen, out = set(), []
+        for cpu in topo["performance_cores"] + topo["efficiency_cores"]:
+            c = topo["per_cpu"].get(cpu)
+            if c is None or cpu not in allowed:
+                continue
+            key = (c["package"], c["core"])
+            if key not in seen:
+                seen.add(key)
+                out.append(cpu)
+        return out[:num_threads] if num_threads > 0 else out
+
+    def is_suitable_for_heavy_workload(self) -> bool:
+        return self.get_physical_cores() >= 4 and self.get_total_memory_bytes() >= 8 * 2**30
+
     def get_performance_cores(self) -> List[int]:
         return list(self.info.get("topology", {}).get("performance_cores", []))
 
@@ -304,6 +483,24 @@ class ThreadAffinity:
         if max_cores > 0:
             cores = cores[:max_cores]
         return self.set_cores(cores)
+
+    def has_efficiency_cores(self) -> bool:
+        return bool(self.hw.get_efficiency_cores())
+
+    def get_performance_core_count(self) -> int:
+        return len(self.hw.get_performance_cores())
+
+    def get_efficiency_core_count(self) -> int:
+        return len(self.hw.get_efficiency_cores())
+
+    def set_current_thread_affinity(self, cores: List[int]) -> bool:
+        """Pin the CALLING thread only (``set_cores`` pins the process)."""
+        try:
+            import threading
+            os.sched_setaffinity(threading.get_native_id(), set(cores))
+            return True
+        except (AttributeError, OSError, ValueError):
+            return False
 
     def pin_to_gpu_node(self, gpu_index: int) -> bool:
         node = self.gpu_numa_node(gpu_index)

@@ -148,3 +148,55 @@ def test_matrix_container():
     assert float(m.data().abs().max()) <= 0.5
     m.resize(2, 8)
     assert m.rows() == 2 and float(m.data().abs().sum()) == 0.0
+
+
+def test_reference_style_device_and_hardware_accessors():
+    """The reference's spellings: DeviceManager::getInstance / getDevice / addDevice ..., Device::getName /
+    getTotalMemory / allocateAlignedMemory / copyToDevice / getFlow, HardwareInfo getters, ThreadAffinity counts."""
+    import torch
+    from dcnn_b200.utils.device import Device, DeviceManager, DeviceType
+    from dcnn_b200.utils.hardware import HardwareInfo, ThreadAffinity
+    dm = DeviceManager.getInstance()
+    dm.discoverDevices()
+    assert dm.hasDevice("CPU:0") and "CPU:0" in dm.getAvailableDeviceIDs()
+    cpu = dm.getDevice("CPU:0")
+    assert isinstance(cpu, Device) and cpu.getID() == 0 and cpu.device_type() == DeviceType.CPU and cpu.getName()
+    assert cpu == torch.device("cpu") and cpu == dm.getDevice(DeviceType.CPU)
+    assert cpu.getTotalMemory() >= cpu.getAvailableMemory() > 0
+    buf = cpu.allocateAlignedMemory(1000, 256)
+    assert buf.numel() == 1000 and buf.data_ptr() % 256 == 0
+    src = torch.arange(100, dtype=torch.uint8)
+    cpu.copyToDevice(buf, src, 100)
+    back = torch.zeros(100, dtype=torch.uint8)
+    cpu.copyToHost(back, buf, 100)
+    assert torch.equal(back, src) and cpu.getFlow("default") is None
+    cpu.deallocateAlignedMemory(buf)
+    dm.addDevice(torch.device("cpu"), "CPU:7")
+    assert dm.hasDevice("CPU:7")
+    dm.setDefaultDevice("CPU:7")
+    dm.removeDevice("CPU:7")
+    assert not dm.hasDevice("CPU:7") and dm.default_device_id == "CPU:0"
+    dm.clearDevices()
+    assert dm.getAvailableDeviceIDs() == []
+    dm.discoverDevices()
+
+    hw = HardwareInfo()
+    assert not hw.is_initialized()
+    assert hw.get_logical_cores() >= hw.get_physical_cores() >= 1 and hw.is_initialized()
+    assert hw.get_sockets() >= 1 and hw.get_model_name() and hw.get_architecture()
+    assert hw.get_total_memory_bytes() >= hw.get_used_memory_bytes() >= 0
+    assert 0.0 <= hw.get_memory_utilization_percent() <= 100.0
+    assert hw.get_cache_line_size() in (32, 64, 128, 256)
+    assert isinstance(hw.supports_avx2(), bool) and (not hw.supports_avx512() or hw.supports_avx2())
+    assert hw.get_max_frequency_mhz() >= 0 and hw.get_optimal_thread_count() >= 1
+    rec = hw.get_recommended_cpu_affinity()
+    assert len(rec) == len(set(rec)) and 1 <= len(rec) <= hw.get_logical_cores()
+    assert len(hw.get_recommended_cpu_affinity(1)) == 1
+    assert 0.0 <= hw.update_utilization() <= 100.0 and 0.0 <= hw.get_overall_utilization() <= 100.0
+    assert isinstance(hw.is_containerized(), bool) and isinstance(hw.is_virtualized(), bool)
+    ta = ThreadAffinity(hw)
+    assert ta.get_performance_core_count() + ta.get_efficiency_core_count() >= 1
+    assert ta.has_efficiency_cores() == (ta.get_efficiency_core_count() > 0)
+    import os
+    before = os.sched_getaffinity(0)
+    assert ta.set_current_thread_affinity(sorted(before))

@@ -198,3 +198,44 @@ def test_measured_layer_costs_drive_the_balanced_partitioner():
     n = len(costs)
     best = min(max(sum(costs[:i]), sum(costs[i:j]), sum(costs[j:])) for i in range(1, n - 1) for j in range(i + 1, n))
     assert abs(max(loads) - best) < 1e-9
+
+
+def test_reference_named_helpers_exist_and_work():
+    """Small API-parity items: data_loader.hpp factory / split / normalise, AugmentationStrategy.set_augmentations,
+    HuberLoss delta accessors, Communicator recipient registry spellings, PipelineStage identity."""
+    import numpy as np
+    import torch
+    from dcnn_b200 import nn
+    from dcnn_b200.data import (AugmentationBuilder, AugmentationStrategy, MNISTDataLoader, create_data_loader,
+                                normalize_to_unit_range, train_val_split)
+    from dcnn_b200.parallel.pipeline import CommandType, Endpoint, InProcessCommunicator, Message, PipelineStage
+    assert isinstance(create_data_loader("MNIST"), MNISTDataLoader) and create_data_loader("tiny-imagenet").size() == 0
+    try:
+        create_data_loader("imagenet21k")
+        raise AssertionError("unknown dataset accepted")
+    except ValueError:
+        pass
+    tr, va = train_val_split(103, 0.2, seed=1)
+    assert len(va) == 20 and len(tr) == 83 and sorted(np.concatenate([tr, va]).tolist()) == list(range(103))
+    assert np.array_equal(train_val_split(103, 0.2, seed=1)[1], va)
+    assert float(normalize_to_unit_range(torch.full((3,), 255.0)).max()) == 1.0
+    src = AugmentationBuilder().horizontal_flip(1.0).cutout(1.0, 2).build()
+    dst = AugmentationStrategy()
+    dst.set_augmentations(src.get_augmentations())
+    assert dst.size() == 2 and dst.get_augmentations()[0] is not src.get_augmentations()[0]
+    h = nn.HuberLoss(1.0)
+    h.set_delta(0.5)
+    assert h.get_delta() == 0.5 and h.get_config()["parameters"]["delta"] == 0.5 and h.num_parameters() == 1
+    assert nn.MSELoss().num_parameters() == 0
+    a, b = InProcessCommunicator("a"), InProcessCommunicator("b")
+    a.register_recipient("b", Endpoint.in_process(b))
+    a.enqueue_output_message(Message("b", CommandType.HEALTH_CHECK, "x"))
+    assert b.message_count(CommandType.HEALTH_CHECK) == 1 and not a.has_output_message()
+    a.unregister_recipient("b")
+    try:
+        a.send_message(Message("b", CommandType.HEALTH_CHECK))
+        raise AssertionError("send to an unregistered recipient succeeded")
+    except KeyError:
+        pass
+    st = PipelineStage(b, "stage_x")
+    assert st.get_stage_id() == "stage_x" and not st.is_configured()
