@@ -265,6 +265,12 @@ class NormalizationAugmentation(Augmentation):
         super().__init__()
         self.mean, self.std = [float(v) for v in mean], [float(v) for v in std]
 
+    def get_mean(self):
+        return list(self.mean)
+
+    def get_std(self):
+        return list(self.std)
+
     def apply(self, data, labels=None):
         if data.dim() != 4:
             return

@@ -205,6 +205,10 @@ class ImageDataLoader(BaseDataLoader):
     def get_class_names(self):
         return list(self.class_names)
 
+    def get_label_counts(self):
+        """Samples per class (the reference prints these in print_data_stats)."""
+        return np.bincount(self.labels, minlength=self.num_classes).tolist() if self.size() else [0] * self.num_classes
+
     def get_data_shape(self):
         return list(self.image_shape)
 
@@ -317,9 +321,38 @@ class CIFAR10DataLoader(_CIFARBase):
 
 
 class CIFAR100DataLoader(_CIFARBase):
-    """Records are <coarse label><fine label><3072 pixels>; the fine label is the target (cifar100_data_loader.hpp)."""
+    """Records are <coarse label><fine label><3072 pixels>; the fine label is the target unless
+    ``set_use_coarse_labels(True)`` selects the 20 superclasses (cifar100_data_loader.hpp)."""
     num_classes, label_bytes = 100, 2
     class_names = [f"class_{i}" for i in range(100)]
+
+    def __init__(self, use_coarse_labels: bool = False):
+        super().__init__()
+        self.fine_labels = np.zeros((0,), np.int32)
+        self._coarse = False
+        self._want_coarse = bool(use_coarse_labels)
+
+    def load_multiple_files(self, filenames):
+        self._coarse = False
+        self.num_classes = 100
+        ok = super().load_multiple_files(filenames)
+        if ok:
+            self.fine_labels = self.labels
+            self.set_use_coarse_labels(self._want_coarse)
+        return ok
+
+    def set_use_coarse_labels(self, use_coarse: bool):
+        """Targets become the 20 coarse superclasses (True) or the 100 fine classes (False)."""
+        self._want_coarse = self._coarse = bool(use_coarse)
+        if self.fine_labels.shape[0] == 0:
+            self.fine_labels = self.labels
+        self.labels = np.ascontiguousarray(self.coarse_labels if self._coarse else self.fine_labels)
+        self.num_classes = 20 if self._coarse else 100
+        self.class_names = [f"{'superclass' if self._coarse else 'class'}_{i}" for i in range(self.num_classes)]
+        self.batches_prepared = False
+
+    def is_using_coarse_labels(self) -> bool:
+        return self._coarse
 
 
 class TinyImageNetDataLoader(ImageDataLoader):
@@ -491,6 +524,25 @@ class WiFiDataLoader(RegressionDataLoader):
             self.target_means, self.target_stds = other.target_means, other.target_stds
             self.targets = ((self.targets - self.target_means) / self.target_stds).astype(np.float32)
         self.is_normalized = True
+
+    def get_feature_means(self):
+        return None if self.feature_means is None else self.feature_means.copy()
+
+    def get_feature_stds(self):
+        return None if self.feature_stds is None else self.feature_stds.copy()
+
+    def get_target_means(self):
+        return None if self.target_means is None else self.target_means.copy()
+
+    def get_target_stds(self):
+        return None if self.target_stds is None else self.target_stds.copy()
+
+    def print_statistics(self):
+        print(f"WiFi dataset: {self.size()} samples, {self.get_num_features()} features, "
+              f"{self.get_num_outputs()} outputs, normalized: {self.is_normalized}")
+        if self.size():
+            print(f"  feature range [{float(self.features.min()):.4g}, {float(self.features.max()):.4g}], "
+                  f"target range [{float(self.targets.min()):.4g}, {float(self.targets.max()):.4g}]")
 
     def denormalize_targets(self, t: torch.Tensor) -> torch.Tensor:
         if not self.is_normalized or self.target_means is None:

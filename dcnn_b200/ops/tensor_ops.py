@@ -142,6 +142,107 @@ def apply_softmax(x):
     return x
 
 
+# ---- scalar / comparison primitives and tensor helpers (tnn::ops::*, Tensor<T> members) -----------------------------
+def add_scalar(a, scalar):
+    return a + scalar
+
+
+def sub_scalar(a, scalar):
+    return a - scalar
+
+
+def mul_scalar(a, scalar):
+    return a * scalar
+
+
+def div_scalar(a, scalar):
+    if scalar == 0:
+        raise ZeroDivisionError("Division by zero")
+    return a / scalar
+
+
+def set_scalar(t, scalar):
+    t.fill_(scalar)
+    return t
+
+
+def mul_add_scalar(a, mul, add_):
+    """a * mul + add"""
+    return torch.add(a * mul, add_)
+
+
+def sub_mul_scalar(a, sub_, mul):
+    """(a - sub) * mul"""
+    return (a - sub_) * mul
+
+
+def scalar_max(a, scalar):
+    return torch.clamp_min(a, scalar)
+
+
+def clamp(a, min_val, max_val):
+    return torch.clamp(a, min_val, max_val)
+
+
+def equal(a, b):
+    """1.0 where a == b else 0.0 (the reference's comparison ops produce masks of the value type)."""
+    return (a == b).to(a.dtype)
+
+
+def greater(a, b):
+    return (a > b).to(a.dtype)
+
+
+def rsqrt(a):
+    return torch.rsqrt(a)
+
+
+def norm_squared(t) -> float:
+    return float((t.double() * t.double()).sum())
+
+
+def mean(t) -> float:
+    return float(t.double().mean())
+
+
+def variance(t) -> float:
+    """Biased variance of all elements (Tensor::variance)."""
+    return float(t.double().var(unbiased=False))
+
+
+def same_shape(a, b) -> bool:
+    return tuple(a.shape) == tuple(b.shape)
+
+
+def shape_str(t) -> str:
+    return "(" + ", ".join(str(int(d)) for d in t.shape) + ")"
+
+
+def check_nan_and_inf(t, name: str = "tensor") -> bool:
+    """True (and a diagnostic line) if the tensor holds a NaN or an infinity (Tensor::check_nan_and_inf)."""
+    bad = ~torch.isfinite(t)
+    if bool(bad.any()):
+        idx = torch.nonzero(bad.reshape(-1))[0].item()
+        print(f"{name}: non-finite value {float(t.reshape(-1)[idx])} at flat index {idx} "
+              f"({int(bad.sum())} of {t.numel()} elements)")
+        return True
+    return False
+
+
+def copy_batch(src, src_batch: int, dst, dst_batch: int):
+    """dst[dst_batch] = src[src_batch] (Tensor::copy_batch)."""
+    if tuple(src.shape[1:]) != tuple(dst.shape[1:]):
+        raise ValueError("copy_batch: per-sample shapes differ")
+    dst[dst_batch].copy_(src[src_batch])
+    return dst
+
+
+def print_data(t, max_elements: int = 64):
+    flat = t.detach().reshape(-1)[:max_elements].tolist()
+    more = " ..." if t.numel() > max_elements else ""
+    print(f"Tensor{shape_str(t)} on {t.device}: " + " ".join(f"{v:.6g}" for v in flat) + more)
+
+
 # ---- GEMM ------------------------------------------------------------------------------------------------------------
 def gemm(a, b, trans_a=False, trans_b=False, alpha=1.0, beta=0.0, c=None):
     """C = alpha * op(A) op(B) + beta * C for row-major 2-D tensors (ref math/gemm.hpp).  On CUDA, fp32 ``A @ B^T`` with K a

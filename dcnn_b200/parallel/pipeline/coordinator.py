@@ -59,6 +59,11 @@ class Coordinator:
             raise ValueError("Loss function cannot be null")
         self.loss_function = loss
 
+    def add_message_callback(self, callback=None):
+        """Call ``callback()`` whenever a message reaches the coordinator (the reference wires its condition variable
+        this way, coordinator.hpp:95-101; waits here already block on the communicator's own condition)."""
+        self.comm.set_message_notification_callback(callback)
+
     def set_num_microbatches(self, n: int) -> bool:
         if n <= 0:
             print("Number of microbatches must be positive")
@@ -402,6 +407,9 @@ class InProcessCoordinator(Coordinator):
             c = InProcessCommunicator(f"stage_{i}")
             self.stages.append(PipelineStage(c, f"stage_{i}", device=dev))
             self.remote_endpoints.append(Endpoint.in_process(c))
+
+    def get_stages(self) -> List[PipelineStage]:
+        return list(self.stages)
 
     def _deliver_config(self, name, cfg):
         # in-process endpoints hold live communicator objects: hand the config object over as is

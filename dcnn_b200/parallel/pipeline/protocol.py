@@ -82,6 +82,12 @@ class Message:
     def has_job(self) -> bool:
         return isinstance(self.payload, Job)
 
+    def has_type(self, kind) -> bool:
+        """``msg.has_type(Job)`` / ``has_type(str)`` / ``has_type(bool)`` (ref Message::has_type<T>())."""
+        if isinstance(self.payload, bool):          # bool is an int subclass: only has_type(bool) matches it
+            return kind is bool
+        return isinstance(self.payload, kind)
+
 
 @dataclass
 class Endpoint:
@@ -106,6 +112,21 @@ class Endpoint:
     @staticmethod
     def in_process(communicator) -> "Endpoint":
         return Endpoint("in_process", -1, "cpu", communicator)
+
+    # the reference's generic accessors (endpoint.hpp:28-44)
+    def communication_type(self) -> str:
+        return self.kind
+
+    def get_parameter(self, key: str):
+        if key in ("host", "port", "rank", "device", "communicator"):
+            v = getattr(self, key)
+            return str(v) if key == "port" else v
+        raise KeyError(f"Parameter {key} not found")
+
+    def set_parameter(self, key: str, value):
+        if key not in ("host", "port", "rank", "device", "communicator"):
+            raise KeyError(f"Parameter {key} not found")
+        setattr(self, key, int(value) if key in ("port", "rank") else value)
 
     def to_json(self) -> dict:
         if self.kind == "tcp":     # the reference's schema (endpoint.hpp:59-83): parameters are strings

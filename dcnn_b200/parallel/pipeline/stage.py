@@ -51,6 +51,14 @@ class PipelineStage:
     def get_stage_id(self) -> str:
         return self.name
 
+    def get_hardware_info(self):
+        """This worker's HardwareInfo (ref NetworkStageWorker::get_hardware_info)."""
+        if self._hw is None:
+            from ...utils.hardware import HardwareInfo
+            self._hw = HardwareInfo()
+            self._hw.initialize()
+        return self._hw
+
     def is_configured(self) -> bool:
         return self.model is not None and self.optimizer is not None
 

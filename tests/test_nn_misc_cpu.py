@@ -239,3 +239,60 @@ def test_reference_named_helpers_exist_and_work():
         pass
     st = PipelineStage(b, "stage_x")
     assert st.get_stage_id() == "stage_x" and not st.is_configured()
+
+
+def test_more_reference_named_helpers(tmp_path, capsys):
+    import numpy as np
+    import torch
+    from dcnn_b200.data import CIFAR100DataLoader, NormalizationAugmentation, WiFiDataLoader
+    from dcnn_b200.ops import tensor_ops as T
+    from dcnn_b200.parallel.pipeline import CommandType, Endpoint, InProcessCoordinator, Job, Message
+    a = torch.tensor([[1.0, -2.0], [3.0, 4.0]])
+    assert torch.equal(T.mul_add_scalar(a, 2.0, 1.0), a * 2 + 1) and torch.equal(T.sub_mul_scalar(a, 1.0, 3.0), (a - 1) * 3)
+    assert torch.equal(T.scalar_max(a, 0.0), a.clamp_min(0)) and torch.equal(T.clamp(a, -1.0, 3.0), a.clamp(-1, 3))
+    assert T.equal(a, a.clone()).sum() == 4 and T.greater(a, torch.zeros(2, 2)).sum() == 3
+    assert abs(T.norm_squared(a) - 30.0) < 1e-9 and abs(T.mean(a) - 1.5) < 1e-9 and abs(T.variance(a) - 5.25) < 1e-9
+    assert T.same_shape(a, a) and T.shape_str(a) == "(2, 2)" and not T.check_nan_and_inf(a)
+    b = a.clone()
+    b[1, 0] = float("inf")
+    assert T.check_nan_and_inf(b, "b") and "non-finite" in capsys.readouterr().out
+    dst = torch.zeros(3, 2)
+    T.copy_batch(a, 1, dst, 2)
+    assert torch.equal(dst[2], a[1]) and float(T.set_scalar(dst, 7.0).sum()) == 42.0
+    T.print_data(a)
+    assert "Tensor(2, 2)" in capsys.readouterr().out
+    with __import__("pytest").raises(ZeroDivisionError):
+        T.div_scalar(a, 0)
+    # CIFAR-100 coarse / fine targets from a synthetic binary file: <coarse><fine><3072 bytes>
+    rec = np.zeros((6, 3074), np.uint8)
+    rec[:, 0] = [0, 1, 2, 3, 19, 19]
+    rec[:, 1] = [5, 15, 25, 35, 99, 98]
+    f = tmp_path / "train.bin"
+    rec.tofile(f)
+    ld = CIFAR100DataLoader()
+    assert ld.load_data(str(f)) and not ld.is_using_coarse_labels() and ld.get_num_classes() == 100
+    assert ld.labels.tolist() == [5, 15, 25, 35, 99, 98] and ld.get_label_counts()[99] == 1
+    ld.set_use_coarse_labels(True)
+    assert ld.is_using_coarse_labels() and ld.get_num_classes() == 20 and ld.labels.tolist() == [0, 1, 2, 3, 19, 19]
+    ld.prepare_batches(6)
+    _, t = ld.get_next_batch()
+    assert t.shape == (6, 20, 1, 1) and t[4, 19, 0, 0] == 1
+    ld.set_use_coarse_labels(False)
+    assert ld.labels.tolist() == [5, 15, 25, 35, 99, 98]
+    n = NormalizationAugmentation((0.1, 0.2, 0.3), (1, 2, 3))
+    assert n.get_mean() == [0.1, 0.2, 0.3] and n.get_std() == [1.0, 2.0, 3.0]
+    w = WiFiDataLoader()
+    assert w.get_feature_means() is None
+    w.print_statistics()
+    ep = Endpoint.tcp("h", 9)
+    assert ep.communication_type() == "tcp" and ep.get_parameter("host") == "h" and ep.get_parameter("port") == "9"
+    ep.set_parameter("port", "10")
+    assert ep.port == 10
+    m = Message("x", CommandType.FORWARD_JOB, Job(a, 1))
+    assert m.has_type(Job) and not m.has_type(str) and Message("x", CommandType.TRAIN_MODE, True).has_type(bool)
+    from dcnn_b200 import nn
+    from tests.test_pipeline_inprocess import _model
+    c = InProcessCoordinator(_model(), nn.SGD(0.1), ["cpu", "cpu"])
+    hits = []
+    c.add_message_callback(lambda: hits.append(1))
+    assert len(c.get_stages()) == 2 and c.get_stages()[0].get_hardware_info().get_logical_cores() >= 1
