@@ -7,7 +7,7 @@ from .nn import *  # noqa: F401,F403
 from .nn import Sequential, SequentialBuilder, Partition  # noqa: F401
 
 
-_LAZY = ("models", "train", "io", "data", "partitioner", "parallel", "utils")
+_LAZY = ("models", "train", "io", "data", "partitioner", "parallel", "utils", "serve")
 
 
 def __getattr__(name):

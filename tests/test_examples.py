@@ -26,6 +26,7 @@ def _run(args, cwd, timeout=600, **env):
     ("tiny_imagenet_visual_check.py", "PNG files"),
     ("device_ptr_example.py", "grow-only"),
     ("cuda_vs_avx2_comparison.py", "native AVX2"),
+    ("serve_example.py", "Served 20 requests"),
 ])
 def test_example_runs(tmp_path, script, expect):
     out = _run([sys.executable, os.path.join(ROOT, "examples", script)], cwd=str(tmp_path))

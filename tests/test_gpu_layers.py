@@ -106,3 +106,33 @@ def test_residual_block_projection():
     _close(gpu.backward(g.cuda(), 0), cpu.backward(g, 0), 2e-3)
     for a, b in zip(gpu.gradients(), cpu.gradients()):
         _close(a, b, 2e-3)
+
+
+def test_predictor_on_gpu_matches_cpu_eval_and_replays_a_graph():
+    """dcnn_b200.serve: folded network + CUDA-graph replay on cuda:0 against the CPU eval-mode network."""
+    from dcnn_b200.models import MODEL_ZOO
+    from dcnn_b200.serve import Predictor
+    cpu = MODEL_ZOO["resnet9_cifar10"]()
+    cpu.set_seed(3)
+    cpu.initialize()
+    cpu.set_training(True)
+    for _ in range(2):                                   # move the BatchNorm statistics off their initial values
+        cpu.forward(torch.randn(8, 3, 32, 32) * 2 + 0.3)
+    cpu.set_training(False)
+    gpu = MODEL_ZOO["resnet9_cifar10"]()
+    gpu.set_seed(3)
+    gpu.initialize()
+    gpu.set_device("cuda:0")
+    for p, q in zip(gpu.parameters(), cpu.parameters()):
+        p.copy_(q)
+    for (k, b), (_, c) in zip(sorted(gpu.buffers().items()), sorted(cpu.buffers().items())):
+        b.copy_(c)
+    p = Predictor(gpu, (3, 32, 32), batch_size=16)
+    x = torch.randn(37, 3, 32, 32)
+    ref = cpu.forward(x)
+    for _ in range(3):                                   # first call warms up and captures, later calls replay
+        got = p.predict(x.cuda())
+    _close(got.cpu(), ref, 2e-3)
+    assert "cuda_graph=True" in p.summary() and "batchnorm 0" in p.summary()
+    outs = list(p.stream_batches([x[:16], x[16:32], x[32:]]))
+    _close(torch.cat(outs).cpu(), ref, 2e-3)
