@@ -14,7 +14,7 @@ For serving:
     (pinned staging, side stream)."""
 from __future__ import annotations
 
-from typing import Iterable, Iterator, List, Optional, Sequence
+from typing import Iterable, Iterator, List, Sequence
 
 import torch
 
