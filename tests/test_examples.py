@@ -27,6 +27,8 @@ def _run(args, cwd, timeout=600, **env):
     ("device_ptr_example.py", "grow-only"),
     ("cuda_vs_avx2_comparison.py", "native AVX2"),
     ("serve_example.py", "Served 20 requests"),
+    ("microbatching_test.py", "Microbatching test PASSED"),
+    ("torch_trainer.py", "Validation - Loss"),
 ])
 def test_example_runs(tmp_path, script, expect):
     out = _run([sys.executable, os.path.join(ROOT, "examples", script)], cwd=str(tmp_path))
