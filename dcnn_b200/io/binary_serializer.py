@@ -41,8 +41,15 @@ def _payload_type(payload) -> int:
     raise TypeError(f"Unsupported payload type in MessageData: {type(payload).__name__}")
 
 
+def _wire_tensor(t: torch.Tensor) -> torch.Tensor:
+    """float32 CPU tensor as it goes on the wire.  In the reference's format ``ndims == 0`` is the EMPTY tensor (a
+    default-constructed Tensor, binary_serializer.hpp:96-107), so a 0-dim torch scalar travels as shape [1]."""
+    t = t.detach().to("cpu", torch.float32).contiguous()
+    return t.reshape(1) if t.dim() == 0 else t
+
+
 def serialize_tensor(t: torch.Tensor) -> bytes:
-    a = t.detach().to("cpu", torch.float32).contiguous().numpy()
+    a = _wire_tensor(t).numpy()
     return struct.pack(_E + "Q", a.ndim) + struct.pack(_E + f"{a.ndim}Q", *a.shape) + a.tobytes()
 
 
@@ -70,7 +77,7 @@ def serialize(msg: Message, use_native: bool = True) -> bytes:
     ndims, tptr, sptr, slen, flag, mb = 0, None, None, 0, 0, 0
     keep = None
     if pt == 1:
-        keep = msg.payload.data.detach().to("cpu", torch.float32).contiguous()
+        keep = _wire_tensor(msg.payload.data)
         ndims = keep.dim()
         for i, d in enumerate(keep.shape):
             dims[i] = d
@@ -121,10 +128,10 @@ def deserialize(buf: bytes) -> Message:
         mb = rd("Q")
         nd = rd("Q")
         shape = [rd("Q") for _ in range(nd)]
-        n = int(np.prod(shape)) if nd else 0
+        n = int(np.prod(shape)) if nd else 0          # ndims == 0: the reference's empty tensor
         arr = np.frombuffer(buf, dtype=np.dtype("float32").newbyteorder(e), count=n, offset=off).astype(np.float32)
         off += 4 * n
-        payload = Job(torch.from_numpy(arr.reshape(shape).copy()), mb)
+        payload = Job(torch.from_numpy(arr.reshape(shape).copy()) if nd else torch.empty(0), mb)
     elif pt == 2:
         payload = rstr()
     elif pt == 3:

@@ -60,6 +60,8 @@ def _u64(v: int) -> bytes:
 def _tensor_parts(t: torch.Tensor) -> list:
     """Reference tensor record: u64 ndims, u64 dims[], raw float32."""
     t = t.detach().to("cpu", torch.float32).contiguous()
+    if t.dim() == 0:          # ndims == 0 means "empty tensor" in the reference's format: a scalar travels as [1]
+        t = t.reshape(1)
     return [_u64(t.dim()) + struct.pack(_E + f"{t.dim()}Q", *t.shape), t]
 
 
@@ -171,6 +173,8 @@ class _Reader:
         n = 1
         for d in shape:
             n *= d
+        if not typed and len(shape) == 0:       # reference record with ndims == 0: its empty tensor
+            return torch.empty(0, dtype=dtype)
         size = torch.empty(0, dtype=dtype).element_size()
         if typed and self.u64() != n * size:
             raise ValueError("tensor record size does not match its shape")
