@@ -1,4 +1,4 @@
-"""Property tests (hypothesis) of the byte-level codecs: whatever message is generated, encode -> decode is the
+"""Property tests (hypothesis).  Byte-level codecs: whatever message is generated, encode -> decode is the
 identity; the native and the pure-Python reference encoders agree byte for byte; truncated or bit-flipped frames are
 rejected or decoded without crashing; compression round-trips arbitrary bytes."""
 import struct
@@ -104,3 +104,56 @@ def test_damaged_frames_never_crash_the_decoder(msg, data):
 @given(st.binary(max_size=5000), st.sampled_from(compression.available_codecs()), st.integers(1, 9))
 def test_compression_round_trips_arbitrary_bytes(data, codec, level):
     assert compression.decompress(compression.compress(data, codec, level)) == data
+
+
+@settings(max_examples=120, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(st.integers(1, 5), st.integers(1, 4), st.integers(1, 9), st.integers(1, 9), st.integers(1, 5),
+       st.integers(1, 5), st.integers(1, 5), st.integers(1, 3), st.integers(1, 3), st.integers(0, 3), st.integers(0, 3),
+       st.booleans())
+def test_native_blocked_convolution_matches_aten_for_any_geometry(n, c, h, w, oc, kh, kw, sh, sw, ph, pw, bias):
+    """csrc/host/cpu_conv.cpp over random (also degenerate) geometries: kernels wider than the image, padding larger
+    than the kernel, strides that skip the last columns."""
+    import torch.nn.functional as F
+    from dcnn_b200.ops import cpu_native
+    if h + 2 * ph < kh or w + 2 * pw < kw:
+        return
+    g = torch.Generator().manual_seed(n * 1000 + h * 31 + w)
+    x, wt = torch.randn(n, c, h, w, generator=g), torch.randn(oc, c, kh, kw, generator=g)
+    b = torch.randn(oc, generator=g) if bias else None
+    y_ref = F.conv2d(x, wt, b, (sh, sw), (ph, pw))
+    y = cpu_native.conv2d_forward(x, wt, b, (sh, sw), (ph, pw))
+    assert y.shape == y_ref.shape and torch.allclose(y, y_ref, atol=1e-4, rtol=1e-4)
+    dy = torch.randn(y_ref.shape, generator=g)
+    dx = cpu_native.conv2d_backward_data(dy, wt, x.shape, (sh, sw), (ph, pw))
+    assert torch.allclose(dx, torch.nn.grad.conv2d_input(x.shape, wt, dy, (sh, sw), (ph, pw)), atol=1e-4, rtol=1e-4)
+    dw = torch.zeros_like(wt)
+    cpu_native.conv2d_backward_weight(dy, x, dw, (sh, sw), (ph, pw))
+    assert torch.allclose(dw, torch.nn.grad.conv2d_weight(x, wt.shape, dy, (sh, sw), (ph, pw)), atol=1e-3, rtol=1e-3)
+
+
+@settings(max_examples=120, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(st.integers(1, 3), st.integers(1, 3), st.integers(1, 11), st.integers(1, 11), st.integers(1, 4), st.integers(1, 4),
+       st.integers(1, 4), st.integers(1, 4), st.integers(0, 2), st.integers(0, 2), st.booleans())
+def test_native_pooling_matches_aten_for_any_geometry(n, c, h, w, kh, kw, sh, sw, ph, pw, with_nan):
+    """csrc/host/cpu_layers.cpp max / average pooling (both the bounds-checked and the in-image fast path), indices and
+    backward included; a NaN in a window propagates like ATen's."""
+    import torch.nn.functional as F
+    from dcnn_b200.ops import cpu_native
+    ph, pw = min(ph, kh // 2), min(pw, kw // 2)
+    if h + 2 * ph < kh or w + 2 * pw < kw:
+        return
+    g = torch.Generator().manual_seed(h * 100 + w)
+    x = torch.randn(n, c, h, w, generator=g)
+    if with_nan:
+        x[0, 0, h // 2, w // 2] = float("nan")
+    y, idx = cpu_native.maxpool_forward(x, (kh, kw), (sh, sw), (ph, pw))
+    y_ref, idx_ref = F.max_pool2d(x, (kh, kw), (sh, sw), (ph, pw), return_indices=True)
+    assert torch.equal(torch.isnan(y), torch.isnan(y_ref)) and torch.equal(torch.nan_to_num(y), torch.nan_to_num(y_ref))
+    assert torch.equal(idx, idx_ref)
+    dy = torch.randn(y_ref.shape, generator=g)
+    dx = cpu_native.maxpool_backward(dy, idx, x.shape)
+    dx_ref = torch.zeros(n, c, h * w).scatter_add_(2, idx_ref.reshape(n, c, -1), dy.reshape(n, c, -1)).reshape(x.shape)
+    assert torch.allclose(dx, dx_ref, atol=1e-6)
+    if not with_nan:
+        ya = cpu_native.avgpool_forward(x, (kh, kw), (sh, sw), (ph, pw))
+        assert torch.allclose(ya, F.avg_pool2d(x, (kh, kw), (sh, sw), (ph, pw), count_include_pad=True), atol=1e-5)
