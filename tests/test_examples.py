@@ -102,3 +102,19 @@ def test_spmd_pipeline_trainer(tmp_path, procs, stages):
     if "model saved to" in out:          # written whenever validation accuracy improved on 0
         assert os.path.exists(tmp_path / "model_snapshots" / "mnist_cnn_model.bin")
         assert os.path.exists(tmp_path / "model_snapshots" / "mnist_cnn_model.state.bin")
+
+
+def test_package_command_line(tmp_path):
+    """python -m dcnn_b200 info | models | summary | train --snapshot | predict."""
+    def run(*a):
+        return _run([sys.executable, "-m", "dcnn_b200", *a], cwd=str(tmp_path), PYTHONPATH=ROOT)
+    out = run("info")
+    assert "dcnn_b200" in out and "devices: CPU:0" in out
+    assert "resnet50_tiny_imagenet" in run("models")
+    assert "Model Summary" in run("summary", "--model", "resnet9_cifar10", "--batch", "2")
+    snap = str(tmp_path / "snap" / "mnist")
+    os.makedirs(os.path.dirname(snap))
+    out = run("train", "--model", "mnist_cnn", "--synthetic", "--batch-size", "8", "--snapshot", snap)
+    assert "Snapshot written" in out and os.path.exists(snap + ".bin")
+    out = run("predict", "--snapshot", snap, "--input", "4,1,28,28", "--repeat", "2")
+    assert "batchnorm 0" in out and "images/s" in out
