@@ -136,3 +136,41 @@ def test_predictor_on_gpu_matches_cpu_eval_and_replays_a_graph():
     assert "cuda_graph=True" in p.summary() and "batchnorm 0" in p.summary()
     outs = list(p.stream_batches([x[:16], x[16:32], x[32:]]))
     _close(torch.cat(outs).cpu(), ref, 2e-3)
+
+
+def _sweep_cases():
+    """The CPU sweep tables (tests/test_layer_sweeps_cpu.py) as (constructor, input shape) pairs for the GPU."""
+    from tests.test_layer_sweeps_cpu import ACT, BN, CONV, DENSE, GN, POOL
+    out = []
+    for (N, Cin, H, W, Cout, kh, kw, sh, sw, ph, pw, bias) in CONV:
+        out.append((f"conv_{Cin}x{H}x{W}_k{kh}x{kw}_s{sh}{sw}_p{ph}{pw}_oc{Cout}",
+                    lambda a=(Cin, Cout, kh, kw, sh, sw, ph, pw, bias): dnn.Conv2DLayer(*a, "c"), (N, Cin, H, W)))
+    for (N, fin, fout, bias) in DENSE:
+        out.append((f"dense_{fin}_{fout}", lambda a=(fin, fout, bias): dnn.DenseLayer(*a, "d"), (N, fin, 1, 1)))
+    for (N, C, H, W, kh, kw, sh, sw, ph, pw) in POOL:
+        out.append((f"maxpool_{H}x{W}_k{kh}x{kw}", lambda a=(kh, kw, sh, sw, ph, pw): dnn.MaxPool2DLayer(*a, "p"), (N, C, H, W)))
+        out.append((f"avgpool_{H}x{W}_k{kh}x{kw}", lambda a=(kh, kw, sh, sw, ph, pw): dnn.AvgPool2DLayer(*a, "p"), (N, C, H, W)))
+    for (N, C, H, W, affine) in BN:
+        out.append((f"bn_{C}_{N}x{H}x{W}", lambda a=(C, affine): dnn.BatchNormLayer(a[0], 1e-5, 0.1, a[1], "bn"), (N, C, H, W)))
+    for (N, C, G, H, W, affine) in GN:
+        out.append((f"gn_{C}_{G}", lambda a=(G, C, affine): dnn.GroupNormLayer(a[0], a[1], 1e-5, a[2], "gn"), (N, C, H, W)))
+    for name, _ in ACT:
+        out.append((f"act_{name}", lambda a=name: dnn.ActivationLayer(a, "a"), (3, 8, 5, 5)))
+    return out
+
+
+@pytest.mark.parametrize("name,make,shape", _sweep_cases(), ids=[c[0] for c in _sweep_cases()])
+def test_layer_sweep_same_on_cpu_and_gpu(name, make, shape):
+    """Every case of the CPU sweep, CPU layer vs the same layer on cuda:0 (FP32-exact mode): forward, input gradient,
+    parameter gradients, BatchNorm running statistics."""
+    cpu, gpu = _pair(make)
+    x = torch.randn(*shape) * 1.5 + 0.2
+    yc, yg = cpu.forward(x, 0), gpu.forward(x.cuda(), 0)
+    _close(yg, yc)
+    g = torch.randn_like(yc)
+    dc_, dg = cpu.backward(g, 0), gpu.backward(g.cuda(), 0)
+    _close(dg, dc_, 2e-3)
+    for a, b in zip(gpu.gradients(), cpu.gradients()):
+        _close(a, b, 2e-3)
+    for (k, a), (_, b) in zip(gpu.buffers().items(), cpu.buffers().items()):
+        _close(a, b)
