@@ -46,4 +46,45 @@ class MetricsLogger:
         if self.path:
             with open(self.path, "a") as f:
                 f.write(json.dumps(rec) + "\n")
+        if self.exporter is not None:
+            self.exporter.observe(rec)
         return rec
+
+    exporter = None          # optional PrometheusExporter (METRICS_PORT)
+
+
+class PrometheusExporter:
+    """Scrape endpoint for the numeric fields that pass through a ``MetricsLogger``: every field becomes the gauge
+    ``dcnn_<field>{rank=..., kind=...}`` holding its latest value, plus the counter ``dcnn_records_total``.
+    ``METRICS_PORT=<port>`` starts one in the stock training loops (rank r listens on port + r); the endpoint is served
+    by prometheus_client's background thread, so it stays answerable while a step is running.  The reference has no
+    metrics endpoint (stdout only)."""
+
+    def __init__(self, port: int, addr: str = "0.0.0.0", rank: int = 0):
+        import prometheus_client as pc
+        self._pc = pc
+        self.registry = pc.CollectorRegistry()
+        self.rank = rank
+        self._gauges = {}
+        self._records = pc.Counter("dcnn_records", "metric records logged", ["rank", "kind"], registry=self.registry)
+        self._server = pc.start_http_server(int(port), addr=addr, registry=self.registry)
+        self.port = int(port)
+
+    def observe(self, rec: dict):
+        kind = str(rec.get("kind", "step"))
+        self._records.labels(rank=str(self.rank), kind=kind).inc()
+        for k, v in rec.items():
+            if k in ("rank", "kind") or isinstance(v, bool) or not isinstance(v, (int, float)):
+                continue
+            name = "dcnn_" + "".join(c if c.isalnum() else "_" for c in k)
+            g = self._gauges.get(name)
+            if g is None:
+                g = self._gauges[name] = self._pc.Gauge(name, f"latest value of '{k}'", ["rank", "kind"],
+                                                        registry=self.registry)
+            g.labels(rank=str(self.rank), kind=kind).set(float(v))
+
+    def close(self):
+        srv = self._server
+        if isinstance(srv, tuple):          # prometheus_client >= 0.17 returns (server, thread)
+            srv[0].shutdown()
+            srv[0].server_close()

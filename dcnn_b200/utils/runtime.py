@@ -132,4 +132,12 @@ def metrics_from_env(rank: Optional[int] = None) -> MetricsLogger:
     if path and r != 0:
         root, ext = os.path.splitext(path)
         path = f"{root}.rank{r}{ext}"
-    return MetricsLogger(path, r)
+    m = MetricsLogger(path, r)
+    port = os.environ.get("METRICS_PORT")
+    if port:                      # Prometheus scrape endpoint next to (or instead of) the JSONL file; rank r -> port + r
+        try:
+            from .misc import PrometheusExporter
+            m.exporter = PrometheusExporter(int(port) + r, rank=r)
+        except Exception as e:    # a busy port must not stop a training run
+            print(f"[dcnn] METRICS_PORT={port}: exporter not started ({type(e).__name__}: {e})")
+    return m

@@ -179,3 +179,30 @@ def test_trace_file_env_records_first_steps(tmp_path, monkeypatch):
     assert runtime.ACTIVE_TRACE is None and path.exists()
     ev = [e for e in json.load(open(path))["traceEvents"] if e.get("ph") == "X"]
     assert len(ev) == 2 * 2 * len(m._get_units())            # only the first two steps
+
+
+def test_prometheus_exporter_serves_logged_metrics(monkeypatch):
+    """METRICS_PORT: numeric fields of every MetricsLogger record are scrapeable as dcnn_<field>{rank, kind}."""
+    import socket
+    import urllib.request
+    pytest = __import__("pytest")
+    pytest.importorskip("prometheus_client")
+    from dcnn_b200.utils.runtime import metrics_from_env
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    monkeypatch.setenv("METRICS_PORT", str(port))
+    monkeypatch.delenv("METRICS_FILE", raising=False)
+    m = metrics_from_env(rank=0)
+    assert m.exporter is not None
+    try:
+        m.log(kind="epoch", images_per_s=1234.5, train_loss=0.25, note="text is skipped", ok=True)
+        m.log(kind="epoch", images_per_s=2000.0, train_loss=0.125)
+        body = urllib.request.urlopen(f"http://127.0.0.1:{port}/metrics", timeout=10).read().decode()
+        assert 'dcnn_images_per_s{kind="epoch",rank="0"} 2000.0' in body
+        assert 'dcnn_train_loss{kind="epoch",rank="0"} 0.125' in body
+        assert 'dcnn_records_total{kind="epoch",rank="0"} 2.0' in body
+        assert "dcnn_note" not in body and "dcnn_ok" not in body
+    finally:
+        m.exporter.close()
