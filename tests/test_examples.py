@@ -17,7 +17,7 @@ def _run(args, cwd, timeout=600, **env):
     return r.stdout
 
 
-@pytest.mark.parametrize("script,expect", [
+SIMPLE_EXAMPLES = [
     ("mnist_cnn_trainer.py", "Validation - Loss"),
     ("cifar10_resnet9.py", "Validation - Loss"),
     ("uji_ips_trainer.py", "Validation - Loss"),
@@ -29,10 +29,31 @@ def _run(args, cwd, timeout=600, **env):
     ("serve_example.py", "Served 20 requests"),
     ("microbatching_test.py", "Microbatching test PASSED"),
     ("torch_trainer.py", "Validation - Loss"),
-])
-def test_example_runs(tmp_path, script, expect):
-    out = _run([sys.executable, os.path.join(ROOT, "examples", script)], cwd=str(tmp_path))
-    assert expect in out
+]
+
+
+@pytest.fixture(scope="module")
+def simple_example_outputs(tmp_path_factory):
+    """The independent single-process examples, started four at a time (each is mostly interpreter start-up and import
+    time); the parametrised test below only inspects what they printed."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    dirs = {s: tmp_path_factory.mktemp(s.replace(".py", "")) for s, _ in SIMPLE_EXAMPLES}    # not thread-safe: up front
+
+    def one(script):
+        cwd = dirs[script]
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", script)], cwd=str(cwd), env=dict(ENV),
+                           capture_output=True, text=True, timeout=900)
+        return script, r
+    with ThreadPoolExecutor(max_workers=4) as ex:
+        return dict(ex.map(one, [s for s, _ in SIMPLE_EXAMPLES]))
+
+
+@pytest.mark.parametrize("script,expect", SIMPLE_EXAMPLES)
+def test_example_runs(simple_example_outputs, script, expect):
+    r = simple_example_outputs[script]
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert expect in r.stdout
 
 
 def test_mnist_snapshot_then_test_binary(tmp_path):
@@ -104,12 +125,19 @@ def test_spmd_pipeline_trainer(tmp_path, procs, stages):
         assert os.path.exists(tmp_path / "model_snapshots" / "mnist_cnn_model.state.bin")
 
 
-def test_package_command_line(tmp_path):
-    """python -m dcnn_b200 info | models | summary | train --snapshot | predict."""
-    def run(*a):
-        return _run([sys.executable, "-m", "dcnn_b200", *a], cwd=str(tmp_path), PYTHONPATH=ROOT)
-    out = run("info")
+def test_package_command_line(tmp_path, capsys, monkeypatch):
+    """python -m dcnn_b200 info | models | summary | train --snapshot | predict (one real `-m` launch, the rest through
+    the same main() in this process)."""
+    from dcnn_b200.__main__ import main
+    monkeypatch.chdir(tmp_path)
+    for k, v in ENV.items():
+        monkeypatch.setenv(k, v)
+    out = _run([sys.executable, "-m", "dcnn_b200", "info"], cwd=str(tmp_path), PYTHONPATH=ROOT)
     assert "dcnn_b200" in out and "devices: CPU:0" in out
+
+    def run(*a):
+        assert main(list(a)) == 0
+        return capsys.readouterr().out
     assert "resnet50_tiny_imagenet" in run("models")
     assert "Model Summary" in run("summary", "--model", "resnet9_cifar10", "--batch", "2")
     snap = str(tmp_path / "snap" / "mnist")
