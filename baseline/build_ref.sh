@@ -59,4 +59,8 @@ OBJS_NOBENCH=()
 for o in "${OBJS[@]}"; do OBJS_NOBENCH+=("$o"); done
 "$NVCC" --cudart shared -o "$OUT/bin/ref_mnist_cpu" "$OUT/obj/ref_mnist_cpu.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
    -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
-echo "built $OUT/bin/ref_bench and $OUT/bin/ref_mnist_cpu"
+# snapshot interoperability harness (tests/test_reference_interop.py)
+g++ "${CXXFLAGS[@]}" -c "$HERE/ref_snapshot.cpp" -o "$OUT/obj/ref_snapshot.o"
+"$NVCC" --cudart shared -o "$OUT/bin/ref_snapshot" "$OUT/obj/ref_snapshot.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
+   -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
+echo "built $OUT/bin/ref_bench, $OUT/bin/ref_mnist_cpu and $OUT/bin/ref_snapshot"

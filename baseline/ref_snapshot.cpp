@@ -1,0 +1,111 @@
+// Snapshot interoperability harness over the UNMODIFIED reference (tests/test_reference_interop.py):
+//
+//   ref_snapshot write <model> <prefix> [train steps]
+//       builds the zoo model with the reference's own builder (example_models.hpp), optionally takes a few SGD steps on
+//       deterministic data (so that weights, BatchNorm parameters and running statistics are not at their initial
+//       values), saves <prefix>.json + <prefix>.bin with Sequential::save_to_file, and writes <prefix>.io.bin =
+//       { u64 in_shape[4], float in[], u64 out_shape[4], float out_train[], float out_eval[] } where out_train is the
+//       training-mode forward (batch statistics) and out_eval the evaluation-mode forward of a fixed input.
+//   ref_snapshot read <prefix> <input io.bin> <output file>
+//       loads <prefix>.json/.bin with Sequential::from_file (a snapshot written by dcnn_b200), runs the training-mode
+//       forward of the input stored in the io file and writes { u64 out_shape[4], float out[] }.
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <fstream>
+#include <string>
+#include <vector>
+
+#include "nn/example_models.hpp"
+#include "nn/loss.hpp"
+#include "nn/optimizers.hpp"
+#include "nn/sequential.hpp"
+
+using namespace tnn;
+
+static Sequential<float> make(const std::string &name, std::vector<size_t> *shape, size_t *classes) {
+  if (name == "mnist_cnn") { *shape = {4, 1, 28, 28}; *classes = 10; return create_mnist_trainer(); }
+  if (name == "cifar10_cnn_v1") { *shape = {4, 3, 32, 32}; *classes = 10; return create_cifar10_trainer_v1(); }
+  if (name == "resnet9_cifar10") { *shape = {4, 3, 32, 32}; *classes = 10; return create_resnet9_cifar10(); }
+  if (name == "resnet18_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_resnet18_tiny_imagenet(); }
+  std::fprintf(stderr, "unknown model %s\n", name.c_str());
+  std::exit(2);
+}
+
+static void fill_input(Tensor<float> &x) {
+  for (size_t i = 0; i < x.size(); ++i) x.data()[i] = 0.5f + 0.5f * std::sin(0.37f * (float)i) * std::cos(0.011f * (float)i);
+}
+
+static void put_shape(std::ofstream &f, const Tensor<float> &t) {
+  auto s = t.shape();
+  for (int i = 0; i < 4; ++i) {
+    uint64_t d = i < (int)s.size() ? s[i] : 1;
+    f.write(reinterpret_cast<const char *>(&d), 8);
+  }
+}
+
+int main(int argc, char **argv) {
+  if (argc < 4) return 2;
+  const std::string mode = argv[1];
+  if (mode == "write") {
+    const std::string prefix = argv[3];
+    const int steps = argc > 4 ? std::atoi(argv[4]) : 2;
+    std::vector<size_t> shape;
+    size_t classes = 0;
+    auto model = make(argv[2], &shape, &classes);
+    model.set_device(DeviceType::CPU);
+    model.initialize();
+    Tensor<float> x(shape);
+    fill_input(x);
+    if (steps > 0) {
+      auto opt = std::make_unique<SGD<float>>(0.05f, 0.9f);
+      auto loss = LossFactory<float>::create_softmax_crossentropy();
+      opt->attach(model.parameters(), model.gradients());
+      model.set_training(true);
+      Tensor<float> t({shape[0], classes, 1, 1});
+      t.fill(0.f);
+      for (size_t n = 0; n < shape[0]; ++n) t.data()[n * classes + (n * 3) % classes] = 1.f;
+      Tensor<float> g;
+      for (int i = 0; i < steps; ++i) {
+        Tensor<float> y = model.forward(x);
+        loss->compute_gradient(y, t, g);
+        model.backward(g);
+        opt->update();
+        opt->clear_gradients();
+      }
+    }
+    model.save_to_file(prefix);
+    model.set_training(true);
+    Tensor<float> y_train = model.forward(x);
+    // NOTE: that forward moved the BatchNorm running statistics once more; they are not part of the reference's
+    // snapshot, so the evaluation-mode output is only comparable through the sidecar below.
+    model.set_training(false);
+    Tensor<float> y_eval = model.forward(x);
+    std::ofstream f(prefix + ".io.bin", std::ios::binary);
+    put_shape(f, x);
+    f.write(reinterpret_cast<const char *>(x.data()), x.size() * 4);
+    put_shape(f, y_train);
+    f.write(reinterpret_cast<const char *>(y_train.data()), y_train.size() * 4);
+    f.write(reinterpret_cast<const char *>(y_eval.data()), y_eval.size() * 4);
+    std::printf("wrote %s.{json,bin,io.bin}: %zu outputs\n", prefix.c_str(), y_train.size());
+    return 0;
+  }
+  if (mode == "read") {
+    auto model = Sequential<float>::from_file(argv[2]);
+    model.set_device(DeviceType::CPU);
+    std::ifstream in(argv[3], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> x({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(x.data()), x.size() * 4);
+    model.set_training(true);
+    Tensor<float> y = model.forward(x);
+    std::ofstream f(argv[4], std::ios::binary);
+    put_shape(f, y);
+    f.write(reinterpret_cast<const char *>(y.data()), y.size() * 4);
+    std::printf("read %s: %zu outputs\n", argv[2], y.size());
+    return 0;
+  }
+  return 2;
+}

@@ -1,0 +1,113 @@
+"""Snapshot interoperability against the UNMODIFIED reference, both ways, through its own code
+(baseline/ref_snapshot.cpp, built by baseline/build_ref.sh from /root/reference):
+
+  * the reference builds a zoo model with its own builder, trains a few steps, saves <name>.json + <name>.bin and records
+    its forward pass of a fixed input -> this library loads the pair and must reproduce that output;
+  * this library trains and saves a model -> the reference loads the pair and its forward pass must equal ours.
+
+That exercises, with the reference as the oracle: the JSON schema (layer types, parameter names, residual blocks), the
+.bin tensor records and their order, and the forward semantics of Conv2D / BatchNorm (batch statistics) / pooling /
+residual blocks / Dense.  Skipped when the reference subset build is not present (it is git-ignored)."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+from dcnn_b200 import nn
+from dcnn_b200.models import MODEL_ZOO
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "baseline", "_ref", "bin", "ref_snapshot")
+pytestmark = pytest.mark.skipif(not os.path.exists(BIN), reason="reference subset build absent (bash baseline/build_ref.sh)")
+
+
+def _read_io(path):
+    raw = open(path, "rb").read()
+    off = 0
+
+    def tensor(shape=None):
+        nonlocal off
+        if shape is None:
+            shape = struct.unpack_from("<4Q", raw, off)
+            off += 32
+        n = int(np.prod(shape))
+        t = torch.from_numpy(np.frombuffer(raw, np.float32, n, off).copy()).reshape(tuple(shape))
+        off += 4 * n
+        return t
+    x = tensor()
+    y_train = tensor()
+    y_eval = tensor(tuple(y_train.shape)) if off < len(raw) else None
+    return x, y_train, y_eval
+
+
+def _ref(*args):
+    r = subprocess.run([BIN, *args], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("name,steps", [("mnist_cnn", 2), ("cifar10_cnn_v1", 1), ("resnet9_cifar10", 1),
+                                        ("resnet18_tiny_imagenet", 1)])
+def test_snapshot_written_by_the_reference_loads_and_computes_the_same(tmp_path, name, steps):
+    prefix = str(tmp_path / name)
+    _ref("write", name, prefix, str(steps))
+    x, y_ref, _ = _read_io(prefix + ".io.bin")
+    model = nn.Sequential.from_file(prefix, device="CPU")
+    ours = MODEL_ZOO[name]()
+    assert model.layer_size() == ours.layer_size()                      # same architecture as our own zoo entry
+    assert [l.type() for l in model.get_layers()] == [l.type() for l in ours.get_layers()]
+    model.set_training(True)
+    y = model.forward(x)
+    assert y.shape == y_ref.shape
+    assert float((y - y_ref).abs().max()) < 2e-4 * max(1.0, float(y_ref.abs().max()))
+    # and our re-serialisation of what we loaded is byte-identical to the reference's files
+    again = str(tmp_path / (name + "_again"))
+    model.save_to_file(again)
+    assert open(again + ".bin", "rb").read() == open(prefix + ".bin", "rb").read()
+    import json
+
+    def normalised(path):
+        """Everything but the informational ``optimized`` tag of conv layers (the reference always writes "cudnn",
+        this library names its own kernel family)."""
+        def walk(o):
+            if isinstance(o, dict):
+                return {k: walk(v) for k, v in o.items() if k != "optimized"}
+            if isinstance(o, list):
+                return [walk(v) for v in o]
+            if isinstance(o, str) and o[:1] in "[{":       # residual blocks embed their paths as JSON text
+                return walk(json.loads(o))
+            return o
+        return walk(json.load(open(path)))
+    assert normalised(again + ".json") == normalised(prefix + ".json")
+
+
+@pytest.mark.parametrize("name,shape", [("mnist_cnn", (4, 1, 28, 28)), ("resnet9_cifar10", (4, 3, 32, 32))])
+def test_snapshot_written_here_is_read_by_the_reference(tmp_path, name, shape):
+    torch.manual_seed(0)
+    model = MODEL_ZOO[name]()
+    model.set_seed(11)
+    model.initialize()
+    opt = nn.SGD(0.05, 0.9)
+    opt.attach(model.parameters(), model.gradients())
+    x = torch.rand(*shape)
+    for _ in range(2):
+        y = model.forward(x)
+        model.backward(torch.randn_like(y))
+        opt.update(zero_grads=True)
+    prefix = str(tmp_path / name)
+    model.save_to_file(prefix)
+    io_path = str(tmp_path / "in.io.bin")
+    with open(io_path, "wb") as f:
+        f.write(struct.pack("<4Q", *shape))
+        f.write(x.numpy().tobytes())
+    out_path = str(tmp_path / "out.bin")
+    _ref("read", prefix, io_path, out_path)
+    raw = open(out_path, "rb").read()
+    oshape = struct.unpack_from("<4Q", raw, 0)
+    y_ref = torch.from_numpy(np.frombuffer(raw, np.float32, int(np.prod(oshape)), 32).copy()).reshape(oshape)
+    model.set_training(True)
+    y = model.forward(x)
+    assert tuple(y.shape) == tuple(y_ref.shape)
+    assert float((y - y_ref).abs().max()) < 2e-4 * max(1.0, float(y_ref.abs().max()))
