@@ -6,6 +6,10 @@
 //       values), saves <prefix>.json + <prefix>.bin with Sequential::save_to_file, and writes <prefix>.io.bin =
 //       { u64 in_shape[4], float in[], u64 out_shape[4], float out_train[], float out_eval[] } where out_train is the
 //       training-mode forward (batch statistics) and out_eval the evaluation-mode forward of a fixed input.
+//   ref_snapshot train <prefix> <input io.bin> <out prefix> <steps> <sgd|sgdm|adam|adamw> <softmax_ce|logsoftmax_ce>
+//       loads <prefix>, takes <steps> optimisation steps on the io file's input with one-hot targets (class of sample
+//       n = (3n) mod classes), prints one loss per step (train.hpp's sequence: forward, compute_loss, compute_gradient,
+//       backward, update, clear_gradients) and saves the result as <out prefix>.json/.bin.
 //   ref_snapshot read <prefix> <input io.bin> <output file>
 //       loads <prefix>.json/.bin with Sequential::from_file (a snapshot written by dcnn_b200), runs the training-mode
 //       forward of the input stored in the io file and writes { u64 out_shape[4], float out[] }.
@@ -89,6 +93,45 @@ int main(int argc, char **argv) {
     f.write(reinterpret_cast<const char *>(y_train.data()), y_train.size() * 4);
     f.write(reinterpret_cast<const char *>(y_eval.data()), y_eval.size() * 4);
     std::printf("wrote %s.{json,bin,io.bin}: %zu outputs\n", prefix.c_str(), y_train.size());
+    return 0;
+  }
+  if (mode == "train") {
+    if (argc < 8) return 2;
+    auto model = Sequential<float>::from_file(argv[2]);
+    model.set_device(DeviceType::CPU);
+    std::ifstream in(argv[3], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> x({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(x.data()), x.size() * 4);
+    const int steps = std::atoi(argv[5]);
+    const std::string on = argv[6], ln = argv[7];
+    std::unique_ptr<Optimizer<float>> opt;
+    if (on == "sgd") opt = std::make_unique<SGD<float>>(0.05f, 0.0f);
+    else if (on == "sgdm") opt = std::make_unique<SGD<float>>(0.05f, 0.9f);
+    else if (on == "adam") opt = std::make_unique<Adam<float>>(0.01f, 0.9f, 0.999f, 1e-8f, 1e-3f, false);
+    else opt = std::make_unique<Adam<float>>(0.01f, 0.9f, 0.999f, 1e-8f, 1e-2f, true);
+    auto loss = ln == "softmax_ce" ? LossFactory<float>::create_softmax_crossentropy()
+                                   : LossFactory<float>::create_logsoftmax_crossentropy();
+    opt->attach(model.parameters(), model.gradients());
+    model.set_training(true);
+    Tensor<float> y0 = model.forward(x);
+    const size_t classes = y0.size() / s[0];
+    Tensor<float> t({(size_t)s[0], classes, 1, 1});
+    t.fill(0.f);
+    for (size_t n = 0; n < s[0]; ++n) t.data()[n * classes + (n * 3) % classes] = 1.f;
+    Tensor<float> g;
+    for (int i = 0; i < steps; ++i) {
+      Tensor<float> y = model.forward(x);
+      float l = 0.f;
+      loss->compute_loss(y, t, l);
+      loss->compute_gradient(y, t, g);
+      model.backward(g);
+      opt->update();
+      opt->clear_gradients();
+      std::printf("loss %.9g\n", l);
+    }
+    model.save_to_file(argv[4]);
     return 0;
   }
   if (mode == "read") {

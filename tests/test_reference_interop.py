@@ -111,3 +111,62 @@ def test_snapshot_written_here_is_read_by_the_reference(tmp_path, name, shape):
     y = model.forward(x)
     assert tuple(y.shape) == tuple(y_ref.shape)
     assert float((y - y_ref).abs().max()) < 2e-4 * max(1.0, float(y_ref.abs().max()))
+
+
+@pytest.mark.parametrize("optimizer,loss_name", [("sgd", "softmax_ce"), ("sgdm", "logsoftmax_ce"), ("adam", "softmax_ce"),
+                                                 ("adamw", "logsoftmax_ce")])
+def test_training_steps_match_the_reference_step_for_step(tmp_path, optimizer, loss_name):
+    """Backward passes, loss scaling, BatchNorm statistics and the optimizers (SGD, momentum, Adam with L2 weight decay,
+    AdamW) against the reference itself: both sides start from the same snapshot and take the same steps; the loss
+    sequences and the final weights must agree."""
+    torch.manual_seed(1)
+    shape = (8, 1, 28, 28)
+    model = MODEL_ZOO["mnist_cnn"]()
+    model.set_seed(21)
+    model.initialize()
+    prefix = str(tmp_path / "start")
+    model.save_to_file(prefix)
+    x = torch.rand(*shape)
+    io_path = str(tmp_path / "in.io.bin")
+    with open(io_path, "wb") as f:
+        f.write(struct.pack("<4Q", *shape))
+        f.write(x.numpy().tobytes())
+    steps = 6
+    out_prefix = str(tmp_path / "ref_trained")
+    r = subprocess.run([BIN, "train", prefix, io_path, out_prefix, str(steps), optimizer, loss_name],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-2000:]
+    ref_losses = [float(l.split()[1]) for l in r.stdout.splitlines() if l.startswith("loss ")]
+    assert len(ref_losses) == steps
+    opt = {"sgd": lambda: nn.SGD(0.05, 0.0), "sgdm": lambda: nn.SGD(0.05, 0.9),
+           "adam": lambda: nn.Adam(0.01, 0.9, 0.999, 1e-8, 1e-3, False),
+           "adamw": lambda: nn.Adam(0.01, 0.9, 0.999, 1e-8, 1e-2, True)}[optimizer]()
+    loss = nn.SoftmaxCrossEntropyLoss() if loss_name == "softmax_ce" else nn.LogSoftmaxCrossEntropyLoss()
+    opt.attach(model.parameters(), model.gradients())
+    model.set_training(True)
+    t = torch.zeros(shape[0], 10, 1, 1)
+    for n in range(shape[0]):
+        t[n, (3 * n) % 10] = 1.0
+    ours = []
+    for _ in range(steps):
+        y = model.forward(x)
+        ours.append(float(loss.compute_loss(y, t)))
+        model.backward(loss.compute_gradient(y, t))
+        opt.update()
+        model.clear_gradients()
+    for a, b in zip(ours, ref_losses):
+        assert abs(a - b) < 2e-4 * max(1.0, abs(b)), (ours, ref_losses)
+    trained = nn.Sequential.from_file(out_prefix, device="CPU")
+    if optimizer.startswith("sgd"):
+        for p, q in zip(model.parameters(), trained.parameters()):
+            assert float((p - q).abs().max()) < 5e-4 * max(1.0, float(q.abs().max()))
+    else:
+        # a convolution bias that feeds a BatchNorm has an exactly-zero gradient; Adam divides that rounding noise by its
+        # own magnitude, so such biases take arbitrary O(lr) steps on both sides (and cancel in the BatchNorm).  Compare
+        # the parameters that matter -- the weights -- and the function the two networks compute.
+        for p, q in zip(model.parameters(), trained.parameters()):
+            if p.numel() > p.shape[0]:
+                assert float((p - q).abs().max()) < 2e-3 * max(1.0, float(q.abs().max()))
+        trained.set_training(True)
+        ya, yb = model.forward(x), trained.forward(x)
+        assert float((ya - yb).abs().max()) < 2e-3 * max(1.0, float(yb.abs().max()))
