@@ -63,4 +63,8 @@ for o in "${OBJS[@]}"; do OBJS_NOBENCH+=("$o"); done
 g++ "${CXXFLAGS[@]}" -c "$HERE/ref_snapshot.cpp" -o "$OUT/obj/ref_snapshot.o"
 "$NVCC" --cudart shared -o "$OUT/bin/ref_snapshot" "$OUT/obj/ref_snapshot.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
    -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
-echo "built $OUT/bin/ref_bench, $OUT/bin/ref_mnist_cpu and $OUT/bin/ref_snapshot"
+# wire-format harness: the reference's BinarySerializer / Message / TBuffer (header-only, no asio or TBB needed)
+g++ "${CXXFLAGS[@]}" -c "$HERE/ref_wire.cpp" -o "$OUT/obj/ref_wire.o"
+"$NVCC" --cudart shared -o "$OUT/bin/ref_wire" "$OUT/obj/ref_wire.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
+   -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
+echo "built $OUT/bin/ref_bench, $OUT/bin/ref_mnist_cpu, $OUT/bin/ref_snapshot and $OUT/bin/ref_wire"

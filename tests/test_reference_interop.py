@@ -170,3 +170,53 @@ def test_training_steps_match_the_reference_step_for_step(tmp_path, optimizer, l
         trained.set_training(True)
         ya, yb = model.forward(x), trained.forward(x)
         assert float((ya - yb).abs().max()) < 2e-3 * max(1.0, float(yb.abs().max()))
+
+
+WIRE = os.path.join(ROOT, "baseline", "_ref", "bin", "ref_wire")
+
+
+@pytest.mark.skipif(not os.path.exists(WIRE), reason="reference wire harness absent (bash baseline/build_ref.sh)")
+def test_wire_frames_interoperate_with_the_reference_serializer(tmp_path):
+    """Frames built by the reference's own BinarySerializer (as its TcpCommunicator frames them) are decoded here and
+    re-encoded byte for byte by all three encoders; frames built here are parsed by the reference's deserializer."""
+    from dcnn_b200.io import binary_serializer
+    from dcnn_b200.parallel.pipeline import CommandType, Job, Message
+    from dcnn_b200.parallel.pipeline.tcp import decode_frame, encode_frame
+    r = subprocess.run([WIRE, "write", str(tmp_path)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    want = {"none": ("stage_0", "coordinator", CommandType.TRAIN_MODE, None),
+            "bool": ("coordinator", "stage_1", CommandType.CONFIG_RECEIVED, True),
+            "string": ("stage_1", "coordinator", CommandType.CONFIG_TRANSFER, '{"stage_id": "stage_1"}'),
+            "job": ("stage_1", "stage_0", CommandType.FORWARD_JOB, None)}
+    for name, (rcpt, sender, cmd, payload) in want.items():
+        raw = open(tmp_path / f"{name}.frame", "rb").read()
+        for decode in (decode_frame, binary_serializer.deserialize):
+            m = decode(raw)
+            assert (m.recipient_id, m.sender_id, m.command_type) == (rcpt, sender, cmd)
+            if name == "job":
+                assert m.payload.micro_batch_id == 7 and tuple(m.payload.data.shape) == (2, 3, 4, 5)
+                assert torch.equal(m.payload.data.reshape(-1), torch.arange(120) * 0.25 - 3.0)
+            else:
+                assert m.payload == payload and type(m.payload) is type(payload)
+        assert encode_frame(m) == raw == binary_serializer.serialize_py(m) == binary_serializer.serialize(m)
+
+    def ref_read(msg):
+        p = tmp_path / "ours.frame"
+        p.write_bytes(encode_frame(msg))
+        r = subprocess.run([WIRE, "read", str(p)], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stdout + r.stderr[-2000:]
+        return dict(l.split(" ", 1) for l in r.stdout.splitlines() if " " in l and not l.startswith(("Discovered", "No CUDA", "Default")))
+    t = torch.randn(3, 2, 5, 4)
+    got = ref_read(Message("stage_9", CommandType.BACKWARD_JOB, Job(t, 42), "stage_10"))
+    assert got["recipient"] == "stage_9" and got["sender"] == "stage_10" and got["command"] == str(int(CommandType.BACKWARD_JOB))
+    assert got["payload_type"] == "1" and got["micro_batch"] == "42" and got["shape"] == "3 2 5 4"
+    checksum = float((t.reshape(-1).double() * (torch.arange(t.numel()) % 7 + 1).double()).sum())
+    assert abs(float(got["checksum"]) - checksum) < 1e-6 * max(1.0, abs(checksum))
+    frame_len = len(encode_frame(Message("stage_9", CommandType.BACKWARD_JOB, Job(t, 42), "stage_10")))
+    assert int(got["length"]) == frame_len - 10 and int(got["consumed"]) == frame_len
+    got = ref_read(Message("coordinator", CommandType.ERROR_REPORT, "stage_2: boom", "stage_2"))
+    assert got["string"] == "stage_2: boom" and got["payload_type"] == "2"
+    got = ref_read(Message("coordinator", CommandType.PARAMETERS_UPDATED, False, "stage_0"))
+    assert got["bool"] == "0" and got["payload_type"] == "3"
+    got = ref_read(Message("stage_0", CommandType.SHUTDOWN, None, "coordinator"))
+    assert got["payload_type"] == "0" and got["command"] == str(int(CommandType.SHUTDOWN))
