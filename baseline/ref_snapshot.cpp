@@ -10,6 +10,9 @@
 //       loads <prefix>, takes <steps> optimisation steps on the io file's input with one-hot targets (class of sample
 //       n = (3n) mod classes), prints one loss per step (train.hpp's sequence: forward, compute_loss, compute_gradient,
 //       backward, update, clear_gradients) and saves the result as <out prefix>.json/.bin.
+//   ref_snapshot schedulers <steps> <unused>
+//       every learning-rate scheduler of nn/schedulers.hpp on an SGD optimizer with base lr 0.1: prints
+//       "<name> lr0 lr1 ... lr<steps>" (ReduceLROnPlateau is fed the metric 1 / (1 + step / 7), floor-quantised to 0.05).
 //   ref_snapshot read <prefix> <input io.bin> <output file>
 //       loads <prefix>.json/.bin with Sequential::from_file (a snapshot written by dcnn_b200), runs the training-mode
 //       forward of the input stored in the io file and writes { u64 out_shape[4], float out[] }.
@@ -24,6 +27,7 @@
 #include "nn/example_models.hpp"
 #include "nn/loss.hpp"
 #include "nn/optimizers.hpp"
+#include "nn/schedulers.hpp"
 #include "nn/sequential.hpp"
 
 using namespace tnn;
@@ -93,6 +97,40 @@ int main(int argc, char **argv) {
     f.write(reinterpret_cast<const char *>(y_train.data()), y_train.size() * 4);
     f.write(reinterpret_cast<const char *>(y_eval.data()), y_eval.size() * 4);
     std::printf("wrote %s.{json,bin,io.bin}: %zu outputs\n", prefix.c_str(), y_train.size());
+    return 0;
+  }
+  if (mode == "schedulers") {
+    const int steps = std::atoi(argv[2]);
+    auto run = [&](const char *name, auto make) {
+      SGD<float> opt(0.1f, 0.0f);
+      auto sch = make(&opt);
+      std::printf("%s %.9g", name, opt.get_learning_rate());
+      for (int i = 0; i < steps; ++i) {
+        sch->step();
+        std::printf(" %.9g", opt.get_learning_rate());
+      }
+      std::printf("\n");
+    };
+    run("step", [](Optimizer<float> *o) { return std::make_unique<StepLR<float>>(o, 4, 0.5f); });
+    run("multistep", [](Optimizer<float> *o) { return std::make_unique<MultiStepLR<float>>(o, std::vector<size_t>{3, 7, 8}, 0.3f); });
+    run("exponential", [](Optimizer<float> *o) { return std::make_unique<ExponentialLR<float>>(o, 0.9f); });
+    run("cosine", [](Optimizer<float> *o) { return std::make_unique<CosineAnnealingLR<float>>(o, 10, 0.001f); });
+    run("cosine_restarts", [](Optimizer<float> *o) { return std::make_unique<CosineAnnealingWarmRestarts<float>>(o, 3, 2, 0.001f); });
+    run("linear_warmup", [](Optimizer<float> *o) { return std::make_unique<LinearWarmup<float>>(o, 5, 0.01f); });
+    run("warmup_cosine", [](Optimizer<float> *o) { return std::make_unique<WarmupCosineAnnealing<float>>(o, 4, 16, 0.01f, 0.002f); });
+    run("polynomial", [](Optimizer<float> *o) { return std::make_unique<PolynomialLR<float>>(o, 12, 2.0f, 0.005f); });
+    run("onecycle", [](Optimizer<float> *o) { return std::make_unique<OneCycleLR<float>>(o, 0.5f, 16, 0.25f, 10.0f, 100.0f); });
+    {
+      SGD<float> opt(0.1f, 0.0f);
+      ReduceLROnPlateau<float> sch(&opt, ReduceLROnPlateau<float>::Mode::MIN, 0.5f, 2, 1e-4f, 0.01f);
+      std::printf("plateau %.9g", opt.get_learning_rate());
+      for (int i = 0; i < steps; ++i) {
+        const float metric = std::floor(20.f / (1.f + (float)i / 7.f)) * 0.05f;
+        sch.step(metric);
+        std::printf(" %.9g", opt.get_learning_rate());
+      }
+      std::printf("\n");
+    }
     return 0;
   }
   if (mode == "train") {

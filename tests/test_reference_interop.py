@@ -220,3 +220,41 @@ def test_wire_frames_interoperate_with_the_reference_serializer(tmp_path):
     assert got["bool"] == "0" and got["payload_type"] == "3"
     got = ref_read(Message("stage_0", CommandType.SHUTDOWN, None, "coordinator"))
     assert got["payload_type"] == "0" and got["command"] == str(int(CommandType.SHUTDOWN))
+
+
+def test_every_scheduler_follows_the_reference_sequence():
+    """The ten learning-rate schedulers of nn/schedulers.hpp, stepped 24 times by the reference itself, against ours."""
+    import math
+    steps = 24
+    r = subprocess.run([BIN, "schedulers", str(steps), "x"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ref = {}
+    for line in r.stdout.splitlines():
+        parts = line.split()
+        if len(parts) == steps + 2:
+            ref[parts[0]] = [float(v) for v in parts[1:]]
+    makers = {
+        "step": lambda o: nn.StepLR(o, 4, 0.5), "multistep": lambda o: nn.MultiStepLR(o, [3, 7, 8], 0.3),
+        "exponential": lambda o: nn.ExponentialLR(o, 0.9), "cosine": lambda o: nn.CosineAnnealingLR(o, 10, 0.001),
+        "cosine_restarts": lambda o: nn.CosineAnnealingWarmRestarts(o, 3, 2, 0.001),
+        "linear_warmup": lambda o: nn.LinearWarmup(o, 5, 0.01),
+        "warmup_cosine": lambda o: nn.WarmupCosineAnnealing(o, 4, 16, 0.01, 0.002),
+        "polynomial": lambda o: nn.PolynomialLR(o, 12, 2.0, 0.005),
+        "onecycle": lambda o: nn.OneCycleLR(o, 0.5, 16, 0.25, 10.0, 100.0),
+    }
+    assert set(makers) | {"plateau"} == set(ref)
+    for name, make in makers.items():
+        opt = nn.SGD(0.1, 0.0)
+        sch = make(opt)
+        ours = [opt.get_learning_rate()]
+        for _ in range(steps):
+            sch.step()
+            ours.append(opt.get_learning_rate())
+        assert all(abs(a - b) <= 2e-6 * max(1.0, abs(b)) + 1e-8 for a, b in zip(ours, ref[name])), (name, ours, ref[name])
+    opt = nn.SGD(0.1, 0.0)
+    sch = nn.ReduceLROnPlateau(opt, "min", 0.5, 2, 1e-4, 0.01)
+    ours = [opt.get_learning_rate()]
+    for i in range(steps):
+        sch.step(math.floor(20.0 / (1.0 + i / 7.0)) * 0.05)
+        ours.append(opt.get_learning_rate())
+    assert all(abs(a - b) <= 2e-6 for a, b in zip(ours, ref["plateau"])), (ours, ref["plateau"])
