@@ -13,6 +13,8 @@
 //   ref_snapshot schedulers <steps> <unused>
 //       every learning-rate scheduler of nn/schedulers.hpp on an SGD optimizer with base lr 0.1: prints
 //       "<name> lr0 lr1 ... lr<steps>" (ReduceLROnPlateau is fed the metric 1 / (1 + step / 7), floor-quantised to 0.05).
+//   ref_snapshot losses <io file with predictions and targets> <prob|logits>
+//       value and gradient of every loss of nn/loss.hpp (plain cross-entropy only for probability inputs).
 //   ref_snapshot read <prefix> <input io.bin> <output file>
 //       loads <prefix>.json/.bin with Sequential::from_file (a snapshot written by dcnn_b200), runs the training-mode
 //       forward of the input stored in the io file and writes { u64 out_shape[4], float out[] }.
@@ -131,6 +133,33 @@ int main(int argc, char **argv) {
       }
       std::printf("\n");
     }
+    return 0;
+  }
+  if (mode == "losses") {
+    // argv[2] = io file {shape, predictions, shape, targets(as "out_train")}; prints "<loss> value g0 g1 ... g(n-1)"
+    std::ifstream in(argv[2], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> pred({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(pred.data()), pred.size() * 4);
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> tgt({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(tgt.data()), tgt.size() * 4);
+    auto run = [&](const char *name, std::unique_ptr<Loss<float>> loss) {
+      float l = 0.f;
+      Tensor<float> g;
+      loss->compute_loss(pred, tgt, l);
+      loss->compute_gradient(pred, tgt, g);
+      std::printf("%s %.9g", name, l);
+      for (size_t i = 0; i < g.size(); ++i) std::printf(" %.9g", g.data()[i]);
+      std::printf("\n");
+    };
+    run("softmax_ce", LossFactory<float>::create_softmax_crossentropy());
+    run("logsoftmax_ce", LossFactory<float>::create_logsoftmax_crossentropy());
+    run("mse", LossFactory<float>::create_mse());
+    run("mae", LossFactory<float>::create_mae());
+    run("huber", LossFactory<float>::create_huber(0.7f));
+    if (std::string(argv[3]) == "prob") run("crossentropy", LossFactory<float>::create_crossentropy());
     return 0;
   }
   if (mode == "train") {

@@ -258,3 +258,39 @@ def test_every_scheduler_follows_the_reference_sequence():
         sch.step(math.floor(20.0 / (1.0 + i / 7.0)) * 0.05)
         ours.append(opt.get_learning_rate())
     assert all(abs(a - b) <= 2e-6 for a, b in zip(ours, ref["plateau"])), (ours, ref["plateau"])
+
+
+@pytest.mark.parametrize("kind", ["logits", "prob"])
+def test_every_loss_value_and_gradient_matches_the_reference(tmp_path, kind):
+    """nn/loss.hpp evaluated by the reference itself: softmax / log-softmax cross-entropy, MSE, MAE, Huber(0.7), and plain
+    cross-entropy on probabilities -- loss value and the full gradient tensor."""
+    g = torch.Generator().manual_seed(5)
+    n, c = 6, 5
+    pred = torch.randn(n, c, 1, 1, generator=g) * 2
+    if kind == "prob":
+        pred = torch.softmax(pred, dim=1)
+    tgt = torch.zeros(n, c, 1, 1)
+    for i in range(n):
+        tgt[i, (2 * i + 1) % c] = 1.0
+    path = str(tmp_path / "loss.io.bin")
+    with open(path, "wb") as f:
+        for t in (pred, tgt):
+            f.write(struct.pack("<4Q", *t.shape))
+            f.write(t.numpy().tobytes())
+    r = subprocess.run([BIN, "losses", path, kind], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ref = {}
+    for line in r.stdout.splitlines():
+        parts = line.split()
+        if len(parts) == 2 + n * c:
+            ref[parts[0]] = (float(parts[1]), torch.tensor([float(v) for v in parts[2:]]).reshape(n, c, 1, 1))
+    ours = {"softmax_ce": nn.SoftmaxCrossEntropyLoss(), "logsoftmax_ce": nn.LogSoftmaxCrossEntropyLoss(),
+            "mse": nn.MSELoss(), "mae": nn.MAELoss(), "huber": nn.HuberLoss(0.7)}
+    if kind == "prob":
+        ours["crossentropy"] = nn.CrossEntropyLoss()
+    assert set(ours) == set(ref)
+    for name, loss in ours.items():
+        value, grad = ref[name]
+        assert abs(float(loss.compute_loss(pred, tgt)) - value) < 1e-5 * max(1.0, abs(value)), name
+        got = loss.compute_gradient(pred, tgt)
+        assert float((got - grad).abs().max()) < 1e-5 * max(1.0, float(grad.abs().max())), name
