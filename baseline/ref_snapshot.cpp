@@ -39,6 +39,27 @@ static Sequential<float> make(const std::string &name, std::vector<size_t> *shap
   if (name == "cifar10_cnn_v1") { *shape = {4, 3, 32, 32}; *classes = 10; return create_cifar10_trainer_v1(); }
   if (name == "resnet9_cifar10") { *shape = {4, 3, 32, 32}; *classes = 10; return create_resnet9_cifar10(); }
   if (name == "resnet18_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_resnet18_tiny_imagenet(); }
+  if (name == "all_layers") {   // every layer kind the zoo models do not cover: GroupNorm, average pooling with padding,
+    *shape = {3, 3, 12, 12};    // strided / asymmetric convolution, the smooth activations, dropout (identity in eval)
+    *classes = 6;
+    return SequentialBuilder<float>("all_layers")
+        .input({3, 12, 12})
+        .conv2d(8, 3, 5, 1, 2, 1, 2, true, "c_asym")
+        .groupnorm(4, 1e-5f, true, "gn")
+        .activation("elu", "a_elu")
+        .avgpool2d(3, 3, 2, 2, 1, 1, "ap_pad")
+        .conv2d(12, 1, 1, 1, 1, 0, 0, false, "c_1x1")
+        .batchnorm(1e-3f, 0.2f, true, "bn")
+        .activation("leaky_relu", "a_leaky")
+        .basic_residual_block(12, 12, 1, "rb_id")
+        .maxpool2d(2, 2, 1, 1, 0, 0, "mp_overlap")
+        .activation("tanh", "a_tanh")
+        .flatten("fl")
+        .dense(16, true, "d1")
+        .activation("sigmoid", "a_sig")
+        .dense(6, false, "d2")
+        .build();
+  }
   std::fprintf(stderr, "unknown model %s\n", name.c_str());
   std::exit(2);
 }
