@@ -31,6 +31,7 @@
 #include "nn/optimizers.hpp"
 #include "nn/schedulers.hpp"
 #include "nn/sequential.hpp"
+#include "partitioner/naive_partitioner.hpp"
 
 using namespace tnn;
 
@@ -154,6 +155,24 @@ int main(int argc, char **argv) {
       }
       std::printf("\n");
     }
+    return 0;
+  }
+  if (mode == "partition") {
+    // ref_snapshot partition <model> <stages>: NaivePartitioner ranges, then Sequential::split -> one config per line
+    std::vector<size_t> shape;
+    size_t classes = 0;
+    auto model = make(argv[2], &shape, &classes);
+    NaivePartitioner<float> part;
+    auto parts = part.get_partitions(model.get_layers(), (size_t)std::atoi(argv[3]));
+    std::printf("partitions");
+    for (auto &p : parts) std::printf(" %zu:%zu", p.start_layer, p.end_layer);
+    std::printf("\n");
+    auto stages = model.split(parts);
+    for (auto &st : stages) std::printf("stage %s\n", st.get_config().dump().c_str());
+    std::vector<size_t> in = shape;
+    std::printf("output_shape");
+    for (size_t d : model.compute_output_shape(in)) std::printf(" %zu", d);
+    std::printf("\n");
     return 0;
   }
   if (mode == "losses") {

@@ -311,3 +311,46 @@ def test_every_loss_value_and_gradient_matches_the_reference(tmp_path, kind):
         assert abs(float(loss.compute_loss(pred, tgt)) - value) < 1e-5 * max(1.0, abs(value)), name
         got = loss.compute_gradient(pred, tgt)
         assert float((got - grad).abs().max()) < 1e-5 * max(1.0, float(grad.abs().max())), name
+
+
+def _normalised_config(o):
+    import json
+    if isinstance(o, dict):
+        return {k: _normalised_config(v) for k, v in o.items() if k != "optimized"}
+    if isinstance(o, list):
+        return [_normalised_config(v) for v in o]
+    if isinstance(o, str) and o[:1] in "[{":
+        return _normalised_config(json.loads(o))
+    return o
+
+
+@pytest.mark.parametrize("name,stages,shape", [("resnet9_cifar10", 3, [4, 3, 32, 32]), ("mnist_cnn", 4, [4, 1, 28, 28]),
+                                               ("resnet18_tiny_imagenet", 5, [2, 3, 64, 64]), ("cifar10_cnn_v1", 2, [4, 3, 32, 32])])
+def test_partitions_stage_configs_and_shapes_match_the_reference(name, stages, shape):
+    """NaivePartitioner ranges, Sequential::split stage configs (what the coordinator ships to workers) and output-shape
+    inference, from the reference's own code."""
+    import json
+    from dcnn_b200.partitioner import NaivePartitioner
+    r = subprocess.run([BIN, "partition", name, str(stages)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = r.stdout.splitlines()
+    ref_parts = [tuple(int(v) for v in p.split(":")) for l in lines if l.startswith("partitions ") for p in l.split()[1:]]
+    ref_stages = [json.loads(l[len("stage "):]) for l in lines if l.startswith("stage ")]
+    ref_shape = [int(v) for l in lines if l.startswith("output_shape ") for v in l.split()[1:]]
+    model = MODEL_ZOO[name]()
+    parts = NaivePartitioner().get_partitions(model.get_layers(), stages)
+    assert [(p.start_layer, p.end_layer) for p in parts] == ref_parts
+    ours = model.split(parts)
+    assert len(ours) == len(ref_stages) == stages
+    def same(x, y):
+        """Equal up to float32 rounding of the hyper-parameters (the reference stores 1e-5f as 9.99999975e-06)."""
+        if isinstance(x, dict):
+            return isinstance(y, dict) and x.keys() == y.keys() and all(same(x[k], y[k]) for k in x)
+        if isinstance(x, list):
+            return isinstance(y, list) and len(x) == len(y) and all(same(u, v) for u, v in zip(x, y))
+        if isinstance(x, float) or isinstance(y, float):
+            return abs(float(x) - float(y)) <= 1e-6 * max(abs(float(x)), abs(float(y)))
+        return x == y
+    for a, b in zip(ours, ref_stages):
+        assert same(_normalised_config(a.get_config()), _normalised_config(b))
+    assert list(model.compute_output_shape(shape)) == ref_shape
