@@ -67,4 +67,8 @@ g++ "${CXXFLAGS[@]}" -c "$HERE/ref_snapshot.cpp" -o "$OUT/obj/ref_snapshot.o"
 g++ "${CXXFLAGS[@]}" -c "$HERE/ref_wire.cpp" -o "$OUT/obj/ref_wire.o"
 "$NVCC" --cudart shared -o "$OUT/bin/ref_wire" "$OUT/obj/ref_wire.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
    -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
-echo "built $OUT/bin/ref_bench, $OUT/bin/ref_mnist_cpu, $OUT/bin/ref_snapshot and $OUT/bin/ref_wire"
+# data-path harness: the reference's loaders and NormalizationAugmentation
+g++ "${CXXFLAGS[@]}" -c "$HERE/ref_data.cpp" -o "$OUT/obj/ref_data.o"
+"$NVCC" --cudart shared -o "$OUT/bin/ref_data" "$OUT/obj/ref_data.o" "${OBJS_NOBENCH[@]}" -gencode arch=compute_100,code=sm_100 \
+   -L/usr/lib/x86_64-linux-gnu -lcudnn -lcublas -lcurand -Xlinker -rpath,/usr/lib/x86_64-linux-gnu -Xlinker -rpath,/usr/local/cuda/lib64
+echo "built $OUT/bin/ref_bench, $OUT/bin/ref_mnist_cpu, $OUT/bin/ref_snapshot, $OUT/bin/ref_wire and $OUT/bin/ref_data"

@@ -486,18 +486,48 @@ class WiFiDataLoader(RegressionDataLoader):
         self.is_normalized = False
         self.feature_means = self.feature_stds = self.target_means = self.target_stds = None
 
-    def load_data(self, filename: str, feature_start_col: int = 0, feature_end_col: int = 520,
-                  target_start_col: int = 520, target_end_col: int = 522, has_header: bool = True) -> bool:
+    def load_data(self, filename: str, feature_start_col: int = 0, feature_end_col: int = 0,
+                  target_start_col: int = 0, target_end_col: int = 0, has_header: bool = True) -> bool:
+        """CSV of RSSI features followed by the targets, parsed like the reference (wifi_data_loader.hpp:56-125):
+        ``feature_end_col == 0`` means "the last two columns are the targets" (the last one for classification);
+        a feature that reads 100 (the UJI "access point not seen" marker), 0 or is not a number becomes -100; a target
+        that is not a number becomes 0; rows are never dropped."""
         if not os.path.exists(filename):
             print(f"Error: Could not open file {filename}")
             return False
-        raw = np.genfromtxt(filename, delimiter=",", skip_header=1 if has_header else 0, dtype=np.float64)
-        raw = np.atleast_2d(raw)
-        raw = raw[~np.isnan(raw[:, target_start_col:target_end_col]).any(axis=1)]
-        f = np.nan_to_num(raw[:, feature_start_col:feature_end_col])
-        f = np.where(f == 100, -110.0, f)   # UJI "no signal" marker -> a weak RSSI
-        self.features = np.ascontiguousarray(f.astype(np.float32))
-        self.targets = np.ascontiguousarray(raw[:, target_start_col:target_end_col].astype(np.float32))
+        feats, tgts = [], []
+
+        def num(cell):
+            try:
+                return float(cell)
+            except ValueError:
+                return None
+        with open(filename) as f:
+            for k, line in enumerate(f):
+                if k == 0 and has_header:
+                    continue
+                row = line.rstrip("\n").rstrip("\r").split(",")
+                if not line.strip():
+                    continue
+                if feature_end_col == 0:
+                    tail = 2 if self.is_regression else 1
+                    feature_end_col, target_start_col, target_end_col = len(row) - tail, len(row) - tail, len(row)
+                fr = []
+                for cell in row[feature_start_col:min(feature_end_col, len(row))]:
+                    v = num(cell)
+                    fr.append(-100.0 if v is None or v == 100.0 or v == 0.0 or v != v else v)
+                tr = []
+                for cell in row[target_start_col:min(target_end_col, len(row))]:
+                    v = num(cell)
+                    tr.append(0.0 if v is None else v)
+                if fr and tr:
+                    feats.append(fr)
+                    tgts.append(tr)
+        if not feats:
+            print(f"Error: No valid data loaded from {filename}")
+            return False
+        self.features = np.ascontiguousarray(np.asarray(feats, dtype=np.float32))
+        self.targets = np.ascontiguousarray(np.asarray(tgts, dtype=np.float32))
         print(f"Loaded {self.size()} samples from {filename}")
         print(f"Features: {self.get_num_features()}, Outputs: {self.get_num_outputs()}")
         return self.size() > 0

@@ -27,8 +27,8 @@ def main():
     train_csv, val_csv = "./data/uji/trainingData.csv", "./data/uji/validationData.csv"
     if os.path.exists(train_csv) and not get_env("SYNTHETIC", False):
         train, val = WiFiDataLoader(), WiFiDataLoader()
-        train.load_data(train_csv)
-        val.load_data(val_csv)
+        train.load_data(train_csv, 0, 520, 520, 522, True)      # examples/uji_ips_trainer.cpp:455
+        val.load_data(val_csv, 0, 520, 520, 522, True)
     else:
         print("UJI dataset not found: using synthetic regression data of the same shape")
         train, val = _synthetic(cfg.batch_size * 16, 0), _synthetic(cfg.batch_size * 4, 0)

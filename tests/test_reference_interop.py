@@ -354,3 +354,90 @@ def test_partitions_stage_configs_and_shapes_match_the_reference(name, stages, s
     for a, b in zip(ours, ref_stages):
         assert same(_normalised_config(a.get_config()), _normalised_config(b))
     assert list(model.compute_output_shape(shape)) == ref_shape
+
+
+DATA = os.path.join(ROOT, "baseline", "_ref", "bin", "ref_data")
+
+
+def _read_pair(path):
+    raw = open(path, "rb").read()
+    off, out = 0, []
+    while off < len(raw):
+        shape = struct.unpack_from("<4Q", raw, off)
+        off += 32
+        n = int(np.prod(shape))
+        out.append(torch.from_numpy(np.frombuffer(raw, np.float32, n, off).copy()).reshape(tuple(shape)))
+        off += 4 * n
+    return out
+
+
+@pytest.mark.skipif(not os.path.exists(DATA), reason="reference data harness absent (bash baseline/build_ref.sh)")
+def test_dataset_parsers_and_normalisation_match_the_reference(tmp_path):
+    """MNIST CSV, CIFAR-10 / CIFAR-100 binary batches, the WiFi regression CSV (with the reference's normalisation) and
+    NormalizationAugmentation: the same files through the reference's loaders and through ours give the same batch."""
+    from dcnn_b200.data import (CIFAR10DataLoader, CIFAR100DataLoader, MNISTDataLoader, NormalizationAugmentation,
+                                WiFiDataLoader)
+    rng = np.random.default_rng(3)
+
+    def ref(*args):
+        r = subprocess.run([DATA, *[str(a) for a in args]], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stdout[-1000:] + r.stderr[-2000:]
+
+    def first_batch(loader):
+        loader.prepare_batches(loader.size())
+        return loader.get_next_batch()
+
+    # MNIST: header line, then label + 784 pixel values 0..255
+    n = 7
+    labels, pix = rng.integers(0, 10, n), rng.integers(0, 256, (n, 784))
+    csv = tmp_path / "mnist.csv"
+    csv.write_text("label," + ",".join(f"p{i}" for i in range(784)) + "\n" +
+                   "\n".join(f"{labels[i]}," + ",".join(map(str, pix[i])) for i in range(n)) + "\n")
+    ref("mnist", csv, tmp_path / "mnist.out")
+    x_ref, t_ref = _read_pair(tmp_path / "mnist.out")
+    ld = MNISTDataLoader()
+    assert ld.load_data(str(csv))
+    x, t = first_batch(ld)
+    assert x.shape == x_ref.shape and torch.allclose(x, x_ref, atol=1e-7) and torch.equal(t, t_ref)
+
+    # CIFAR-10: <label><3072 bytes>;  CIFAR-100: <coarse><fine><3072 bytes>
+    for kind, cls, nlab, classes in (("cifar10", CIFAR10DataLoader, 1, 10), ("cifar100", CIFAR100DataLoader, 2, 100)):
+        rec = rng.integers(0, 256, (5, nlab + 3072), dtype=np.uint8)
+        rec[:, 0] = rng.integers(0, 10 if nlab == 1 else 20, 5)
+        if nlab == 2:
+            rec[:, 1] = rng.integers(0, 100, 5)
+        path = tmp_path / f"{kind}.bin"
+        rec.tofile(path)
+        ref(kind, path, tmp_path / f"{kind}.out")
+        x_ref, t_ref = _read_pair(tmp_path / f"{kind}.out")
+        ld = cls()
+        assert ld.load_data(str(path))
+        x, t = first_batch(ld)
+        assert x.shape == x_ref.shape and torch.allclose(x, x_ref, atol=1e-7)
+        assert t.shape == t_ref.shape == (5, classes, 1, 1) and torch.equal(t, t_ref)
+
+    # WiFi: header, 6 feature columns (100 = "no signal"), 2 target columns; z-score normalisation of both
+    rows = rng.integers(-100, 0, (9, 6)).astype(float)
+    rows[rng.random((9, 6)) < 0.3] = 100
+    tg = rng.normal(50, 20, (9, 2))
+    csv = tmp_path / "wifi.csv"
+    csv.write_text(",".join(f"c{i}" for i in range(8)) + "\n" +
+                   "\n".join(",".join(f"{v:.6f}" for v in list(rows[i]) + list(tg[i])) for i in range(9)) + "\n")
+    ref("wifi", csv, 6, 8, tmp_path / "wifi.out")
+    x_ref, t_ref = _read_pair(tmp_path / "wifi.out")
+    w = WiFiDataLoader(True)
+    assert w.load_data(str(csv), 0, 6, 6, 8, True)
+    w.normalize_data()
+    x, t = first_batch(w)
+    assert torch.allclose(x.reshape(x_ref.shape), x_ref, atol=2e-5) and torch.allclose(t.reshape(t_ref.shape), t_ref, atol=2e-5)
+
+    # NormalizationAugmentation
+    img = torch.rand(3, 3, 4, 5)
+    with open(tmp_path / "norm.io", "wb") as f:
+        f.write(struct.pack("<4Q", *img.shape))
+        f.write(img.numpy().tobytes())
+    ref("normalize", tmp_path / "norm.io", tmp_path / "norm.out")
+    (y_ref,) = _read_pair(tmp_path / "norm.out")
+    ours = img.clone()
+    NormalizationAugmentation((0.1, 0.2, 0.3), (0.5, 0.6, 0.7)).apply(ours, None)
+    assert torch.allclose(ours, y_ref, atol=1e-6)
