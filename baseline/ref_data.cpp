@@ -5,6 +5,8 @@
 //   ref_data cifar10 <bin> <out> | cifar100 <bin> <out>
 //   ref_data wifi <csv> <feat_end> <tgt_end> <out> WiFiDataLoader::load_data(+normalize_data) -> first batch
 //   ref_data normalize <io file> <out>             NormalizationAugmentation(mean .1 .2 .3, std .5 .6 .7) on a batch
+//   ref_data hflip|vflip <io file> <out>           Horizontal / VerticalFlipAugmentation(probability 1) on a batch
+//   ref_data accuracy <io file> <unused>           io = predictions, targets -> prints "corrects N accuracy A"
 // <out> = { u64 shape[4], float data[], u64 shape[4], float labels[] } (labels omitted for normalize).
 #include <cstdint>
 #include <cstdio>
@@ -16,6 +18,7 @@
 #include "data_loading/cifar10_data_loader.hpp"
 #include "data_loading/mnist_data_loader.hpp"
 #include "data_loading/wifi_data_loader.hpp"
+#include "utils/utils_extended.hpp"
 
 using namespace tnn;
 
@@ -57,6 +60,35 @@ int main(int argc, char **argv) {
     std::ofstream f(argv[5], std::ios::binary);
     put(f, x);
     put(f, y);
+    return 0;
+  }
+  if (mode == "hflip" || mode == "vflip") {
+    std::ifstream in(argv[2], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> x({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]}), labels({(size_t)s[0], 1, 1, 1});
+    in.read(reinterpret_cast<char *>(x.data()), x.size() * 4);
+    if (mode == "hflip") {
+      HorizontalFlipAugmentation<float> aug(1.0f);
+      aug.apply(x, labels);
+    } else {
+      VerticalFlipAugmentation<float> aug(1.0f);
+      aug.apply(x, labels);
+    }
+    std::ofstream f(argv[3], std::ios::binary);
+    put(f, x);
+    return 0;
+  }
+  if (mode == "accuracy") {
+    std::ifstream in(argv[2], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> p({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(p.data()), p.size() * 4);
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> t({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(t.data()), t.size() * 4);
+    std::printf("corrects %d accuracy %.9g\n", compute_class_corrects(p, t), compute_class_accuracy(p, t));
     return 0;
   }
   if (mode == "normalize") {

@@ -157,6 +157,24 @@ int main(int argc, char **argv) {
     }
     return 0;
   }
+  if (mode == "init") {
+    // ref_snapshot init <model> <unused>: per parameter tensor "param <numel> <min> <max> <mean> <std>" after initialize()
+    std::vector<size_t> shape;
+    size_t classes = 0;
+    auto model = make(argv[2], &shape, &classes);
+    model.set_device(DeviceType::CPU);
+    model.initialize();
+    for (auto *p : model.parameters()) {
+      double mn = 1e30, mx = -1e30, sum = 0, sq = 0;
+      for (size_t i = 0; i < p->size(); ++i) {
+        const double v = p->data()[i];
+        mn = std::min(mn, v); mx = std::max(mx, v); sum += v; sq += v * v;
+      }
+      const double mean = sum / p->size();
+      std::printf("param %zu %.9g %.9g %.9g %.9g\n", p->size(), mn, mx, mean, std::sqrt(std::max(0.0, sq / p->size() - mean * mean)));
+    }
+    return 0;
+  }
   if (mode == "partition") {
     // ref_snapshot partition <model> <stages>: NaivePartitioner ranges, then Sequential::split -> one config per line
     std::vector<size_t> shape;

@@ -441,3 +441,65 @@ def test_dataset_parsers_and_normalisation_match_the_reference(tmp_path):
     ours = img.clone()
     NormalizationAugmentation((0.1, 0.2, 0.3), (0.5, 0.6, 0.7)).apply(ours, None)
     assert torch.allclose(ours, y_ref, atol=1e-6)
+
+
+@pytest.mark.skipif(not os.path.exists(DATA), reason="reference data harness absent (bash baseline/build_ref.sh)")
+def test_flips_and_accuracy_match_the_reference(tmp_path):
+    from dcnn_b200.data import HorizontalFlipAugmentation, VerticalFlipAugmentation
+    from dcnn_b200.train import compute_class_accuracy, compute_class_corrects
+    img = torch.rand(4, 3, 5, 6)
+    with open(tmp_path / "img.io", "wb") as f:
+        f.write(struct.pack("<4Q", *img.shape))
+        f.write(img.numpy().tobytes())
+    for mode, aug in (("hflip", HorizontalFlipAugmentation(1.0)), ("vflip", VerticalFlipAugmentation(1.0))):
+        r = subprocess.run([DATA, mode, str(tmp_path / "img.io"), str(tmp_path / f"{mode}.out")], capture_output=True,
+                           text=True, timeout=120)
+        assert r.returncode == 0, r.stderr[-2000:]
+        (want,) = _read_pair(tmp_path / f"{mode}.out")
+        ours = img.clone()
+        aug.apply(ours, None)
+        assert torch.equal(ours, want), mode
+    g = torch.Generator().manual_seed(2)
+    pred = torch.randn(12, 7, 1, 1, generator=g)
+    pred[3] = pred[3, 0]                                  # a tie across all classes: both sides must pick the same one
+    tgt = torch.zeros(12, 7, 1, 1)
+    for i in range(12):
+        tgt[i, int(pred[i].argmax()) if i % 3 else (i * 2) % 7] = 1.0
+    with open(tmp_path / "acc.io", "wb") as f:
+        for t in (pred, tgt):
+            f.write(struct.pack("<4Q", *t.shape))
+            f.write(t.numpy().tobytes())
+    r = subprocess.run([DATA, "accuracy", str(tmp_path / "acc.io"), "x"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("corrects ")][0].split()
+    assert compute_class_corrects(pred, tgt) == int(line[1])
+    assert abs(compute_class_accuracy(pred, tgt) - float(line[3])) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["mnist_cnn", "resnet9_cifar10"])
+def test_initialisation_has_the_reference_distribution(name):
+    """Parameter by parameter after initialize(): same tensor sizes in the same order, BatchNorm gamma / beta exactly 1 / 0,
+    and for the random tensors the same uniform bound (min / max / standard deviation agree to sampling error; the
+    random streams themselves are different generators)."""
+    r = subprocess.run([BIN, "init", name, "x"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ref = [[float(v) for v in l.split()[1:]] for l in r.stdout.splitlines() if l.startswith("param ")]
+    model = MODEL_ZOO[name]()
+    model.set_seed(3)
+    model.initialize()
+    params = model.parameters()
+    assert [p.numel() for p in params] == [int(r_[0]) for r_ in ref]
+    for p, (numel, mn, mx, mean, std) in zip(params, ref):
+        p = p.double()
+        if std == 0.0:                                    # constant initialisation (BatchNorm affine parameters)
+            assert float(p.min()) == mn == float(p.max()) == mx
+            continue
+        ref_max = max(abs(mn), abs(mx))
+        if numel < 256:                                   # a handful of draws: only the order of magnitude is testable
+            assert 0.3 * ref_max <= float(p.abs().max()) <= 2.0 * ref_max, (numel, float(p.abs().max()), ref_max)
+            continue
+        bound = std * 3 ** 0.5                            # uniform(-b, b) has standard deviation b / sqrt(3)
+        ours_std = float(p.std(unbiased=False))
+        assert abs(ours_std - std) <= (4.0 / numel ** 0.5 + 0.02) * std, (numel, ours_std, std)
+        assert 0.9 * bound <= float(p.abs().max()) <= 1.03 * bound, (numel, float(p.abs().max()), bound)
+        assert abs(float(p.mean())) <= 5.0 * std / numel ** 0.5
