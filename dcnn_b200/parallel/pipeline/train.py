@@ -109,6 +109,84 @@ def train_model(coordinator: Coordinator, train_loader, test_loader, config: Opt
     return history
 
 
+# ------------------------------------------------------------------------------------------------ recovery
+class ResilientBatchRunner:
+    """Runs batches through a coordinator and survives the loss of a stage worker.
+
+    Every ``snapshot_every`` completed batches the stages' parameters are gathered into the coordinator's copy of the
+    model (``collect_current_parameters``).  When a batch fails because a stage died (connection lost, stage error,
+    timeout), ``replacement(stage_index, error)`` is asked for the endpoint of a fresh worker -- start a process, pick a
+    spare, whatever the deployment does; it may return None to give up -- the stage is replaced
+    (``Coordinator.replace_stage``: every stage reloads the last snapshot) and the batches since that snapshot are run
+    again from the replay buffer, so that the sequence of optimizer steps is the one an undisturbed run takes (exactly so
+    with plain SGD; the replaced stage's optimizer moments restart from zero otherwise).  The reference has no
+    recovery: a lost worker ends the run."""
+
+    def __init__(self, coordinator: Coordinator, replacement, snapshot_every: int = 50, max_recoveries: int = 3,
+                 batch_timeout: float = 120.0):
+        self.coordinator, self.replacement = coordinator, replacement
+        self.snapshot_every, self.max_recoveries = max(1, int(snapshot_every)), int(max_recoveries)
+        self.batch_timeout = batch_timeout
+        self.recoveries = 0
+        self._since_snapshot = []          # (microbatch inputs, microbatch labels) of batches after the last snapshot
+        self._have_snapshot = False
+
+    def _lost_stage(self) -> int:
+        c = self.coordinator
+        alive = getattr(c.comm, "peer_alive", None)
+        if alive is not None:
+            for i, name in enumerate(c.stage_names):
+                if not alive(name):
+                    return i
+        for i, name in enumerate(c.stage_names):       # a stage that reported its neighbour gone names itself
+            if any(f"{name}:" in e and "next_stage" in e for e in c.errors[-4:]):
+                return min(i + 1, c.num_stages - 1)
+            if any(f"{name}:" in e and "prev_stage" in e for e in c.errors[-4:]):
+                return max(i - 1, 0)
+        return -1
+
+    def _one(self, xs, ts) -> dict:
+        c = self.coordinator
+        c.async_process_batch(xs, ts, timeout=self.batch_timeout)
+        return c.update_parameters(timeout=self.batch_timeout)
+
+    def snapshot(self) -> bool:
+        ok = self.coordinator.collect_current_parameters()
+        if ok:
+            self._since_snapshot.clear()
+            self._have_snapshot = True
+        return ok
+
+    def run_batch(self, microbatch_inputs, microbatch_labels) -> dict:
+        """One optimisation step; returns ``update_parameters``' result.  Raises if recovery is impossible."""
+        if not self._have_snapshot:
+            if not self.snapshot():
+                raise RuntimeError("cannot take the initial parameter snapshot")
+        xs, ts = list(microbatch_inputs), list(microbatch_labels)
+        while True:
+            try:
+                res = self._one(xs, ts)
+                break
+            except Exception as e:             # PipelineStageLost, ConnectionError, stage ERROR_REPORT, PipelineTimeout
+                idx = self._lost_stage()
+                if idx < 0 or self.recoveries >= self.max_recoveries:
+                    raise
+                endpoint = self.replacement(idx, e)
+                if endpoint is None:
+                    raise
+                self.recoveries += 1
+                print(f"[pipeline] stage {idx} lost ({type(e).__name__}); replacing it and replaying "
+                      f"{len(self._since_snapshot)} batch(es) since the last snapshot")
+                if not self.coordinator.replace_stage(idx, endpoint, timeout=self.batch_timeout):
+                    raise RuntimeError(f"could not bring a replacement for stage {idx} into the pipeline") from e
+                for (px, pt) in self._since_snapshot:
+                    self._one(px, pt)
+        self._since_snapshot.append((xs, ts))
+        if len(self._since_snapshot) >= self.snapshot_every:
+            self.snapshot()
+        return res
+
+
 # ------------------------------------------------------------------------------------------------ SPMD engine driver
 def train_engine_model(engine, train_loader, test_loader, config: Optional[TrainingConfig] = None, replica: int = 0,
                        num_replicas: int = 1, snapshot: bool = False):

@@ -322,3 +322,50 @@ def test_replacing_a_killed_worker_continues_from_the_snapshot_exactly(tmp_path)
         assert abs(a - b) < 1e-4
     for p, q in zip(coord.model.parameters(), ref.parameters()):
         assert torch.allclose(p, q, atol=1e-5, rtol=1e-4)
+
+
+def test_resilient_runner_replaces_a_killed_worker_and_replays(tmp_path):
+    """ResilientBatchRunner: snapshots every 2 batches, a worker is killed after batch 3, the runner obtains a new
+    worker from its callback, reloads the snapshot (state after batch 2), replays batch 3 and continues -- the six losses
+    and the final weights equal an undisturbed single-device run (plain SGD)."""
+    from dcnn_b200.parallel.pipeline.train import ResilientBatchRunner
+    workers = [_start_worker(), _start_worker()]
+    coord = None
+    try:
+        coord = TcpCoordinator(_model(), dnn.SGD(0.05, 0.0), [("127.0.0.1", port) for _, port in workers])
+        coord.seed = 77
+        coord.set_loss_function(dnn.SoftmaxCrossEntropyLoss())
+        coord.set_num_microbatches(2)
+        coord.initialize()
+        assert coord.deploy_stages(timeout=120)
+        coord.start()
+        spawned = []
+
+        def replacement(stage_index, error):
+            proc, port = _start_worker()
+            workers.append((proc, port))
+            spawned.append(stage_index)
+            return Endpoint.tcp("127.0.0.1", port)
+        runner = ResilientBatchRunner(coord, replacement, snapshot_every=2, batch_timeout=60.0)
+        x, t = _data()
+        xs, ts = split_microbatches(x, 2), split_microbatches(t, 2)
+        losses = []
+        for step in range(6):
+            if step == 3:
+                workers[1][0].kill()                     # stage 1 dies between batches 3 and 4
+                workers[1][0].wait(timeout=30)
+            losses.append(runner.run_batch(xs, ts)["loss"])
+        assert spawned == [1] and runner.recoveries == 1
+        assert coord.collect_current_parameters()
+        coord.stop()
+    finally:
+        for p, _ in workers:
+            if p.poll() is None:
+                p.kill()
+        if coord is not None:
+            coord.close()
+    ref, ref_losses = _plain_sgd_reference(6)
+    for a, b in zip(losses, ref_losses):
+        assert abs(a - b) < 1e-4
+    for p, q in zip(coord.model.parameters(), ref.parameters()):
+        assert torch.allclose(p, q, atol=1e-5, rtol=1e-4)
