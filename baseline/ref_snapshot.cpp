@@ -157,6 +157,54 @@ int main(int argc, char **argv) {
     }
     return 0;
   }
+  if (mode == "evalafter") {
+    // ref_snapshot evalafter <prefix> <io> <out> <k>: load a snapshot (fresh BatchNorm running statistics), run k
+    // training-mode forwards of the io input, then write the evaluation-mode forward -> running-statistics convention
+    auto model = Sequential<float>::from_file(argv[2]);
+    model.set_device(DeviceType::CPU);
+    std::ifstream in(argv[3], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> x({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(x.data()), x.size() * 4);
+    const int k = argc > 5 ? std::atoi(argv[5]) : 3;
+    model.set_training(true);
+    for (int i = 0; i < k; ++i) model.forward(x);
+    model.set_training(false);
+    Tensor<float> y = model.forward(x);
+    std::ofstream f(argv[4], std::ios::binary);
+    put_shape(f, y);
+    f.write(reinterpret_cast<const char *>(y.data()), y.size() * 4);
+    return 0;
+  }
+  if (mode == "fwdbwd") {
+    // ref_snapshot fwdbwd <pool_tie|dropout> <io> <out>: tiny single-layer models; writes y then dx for dy = 1
+    std::ifstream in(argv[3], std::ios::binary);
+    uint64_t s[4];
+    in.read(reinterpret_cast<char *>(s), 32);
+    Tensor<float> x({(size_t)s[0], (size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    in.read(reinterpret_cast<char *>(x.data()), x.size() * 4);
+    const std::string which = argv[2];
+    SequentialBuilder<float> b(which);
+    b.input(std::vector<size_t>{(size_t)s[1], (size_t)s[2], (size_t)s[3]});
+    if (which == "pool_tie") b.maxpool2d(2, 2, 2, 2, 0, 0, "mp");
+    else if (which == "pool_overlap_tie") b.maxpool2d(3, 3, 1, 1, 1, 1, "mp");
+    else b.dropout(0.25f, "do");
+    auto model = b.build();
+    model.set_device(DeviceType::CPU);
+    model.initialize();
+    model.set_training(true);
+    Tensor<float> y = model.forward(x);
+    Tensor<float> g(y.shape());
+    g.fill(1.f);
+    Tensor<float> dx = model.backward(g);
+    std::ofstream f(argv[4], std::ios::binary);
+    put_shape(f, y);
+    f.write(reinterpret_cast<const char *>(y.data()), y.size() * 4);
+    put_shape(f, dx);
+    f.write(reinterpret_cast<const char *>(dx.data()), dx.size() * 4);
+    return 0;
+  }
   if (mode == "init") {
     // ref_snapshot init <model> <unused>: per parameter tensor "param <numel> <min> <max> <mean> <std>" after initialize()
     std::vector<size_t> shape;

@@ -504,3 +504,61 @@ def test_initialisation_has_the_reference_distribution(name):
         slack = 4.0 / numel ** 0.5 + 0.03                 # both sides estimate the bound from their own draws
         assert (0.9 - slack) * bound <= float(p.abs().max()) <= (1.0 + slack) * bound, (numel, float(p.abs().max()), bound)
         assert abs(float(p.mean())) <= 5.0 * std / numel ** 0.5
+
+
+def _write_io(path, x):
+    with open(path, "wb") as f:
+        f.write(struct.pack("<4Q", *x.shape))
+        f.write(x.contiguous().numpy().tobytes())
+
+
+@pytest.mark.parametrize("name,shape", [("mnist_cnn", (6, 1, 28, 28)), ("resnet9_cifar10", (4, 3, 32, 32))])
+def test_batchnorm_running_statistics_follow_the_reference_convention(tmp_path, name, shape):
+    """From the same snapshot (fresh running statistics), k training-mode forwards and then an evaluation-mode forward:
+    the evaluation output depends on the momentum convention and on which variance estimate enters running_var."""
+    torch.manual_seed(4)
+    model = MODEL_ZOO[name]()
+    model.set_seed(13)
+    model.initialize()
+    prefix = str(tmp_path / name)
+    model.save_to_file(prefix)
+    x = torch.rand(*shape) * 2 - 0.3
+    _write_io(tmp_path / "x.io", x)
+    for k in (1, 4):
+        out = tmp_path / f"eval{k}.out"
+        _ref("evalafter", prefix, str(tmp_path / "x.io"), str(out), str(k))
+        (y_ref,) = _read_pair(out)
+        ours = nn.Sequential.from_file(prefix, device="CPU")
+        ours.set_training(True)
+        for _ in range(k):
+            ours.forward(x)
+        ours.set_training(False)
+        y = ours.forward(x)
+        assert float((y - y_ref).abs().max()) < 5e-4 * max(1.0, float(y_ref.abs().max())), k
+
+
+def test_max_pool_ties_and_dropout_scaling_match_the_reference(tmp_path):
+    # ties: every window holds equal values -> the gradient must go to the same element on both sides
+    x = torch.ones(2, 3, 6, 6)
+    x[0, 0, :2, :2] = torch.tensor([[1.0, 5.0], [5.0, 5.0]])            # three-way tie that is not at position 0
+    _write_io(tmp_path / "tie.io", x)
+    for which, (k, st, pd) in (("pool_tie", (2, 2, 0)), ("pool_overlap_tie", (3, 1, 1))):
+        _ref("fwdbwd", which, str(tmp_path / "tie.io"), str(tmp_path / f"{which}.out"))
+        y_ref, dx_ref = _read_pair(tmp_path / f"{which}.out")
+        layer = nn.MaxPool2DLayer(k, k, st, st, pd, pd, "mp")
+        y = layer.forward(x)
+        dx = layer.backward(torch.ones_like(y))
+        assert torch.equal(y, y_ref) and torch.equal(dx, dx_ref), which
+    # dropout: which elements drop is random on both sides, the values they take are not
+    ones = torch.ones(4, 8, 16, 16)
+    _write_io(tmp_path / "ones.io", ones)
+    _ref("fwdbwd", "dropout", str(tmp_path / "ones.io"), str(tmp_path / "do.out"))
+    y_ref, dx_ref = _read_pair(tmp_path / "do.out")
+    layer = nn.DropoutLayer(0.25, "do")
+    layer.set_seed(1)
+    y = layer.forward(ones)
+    dx = layer.backward(torch.ones_like(y))
+    for a, b in ((y, y_ref), (dx, dx_ref)):
+        assert sorted(set(a.reshape(-1).tolist())) == sorted(set(b.reshape(-1).tolist())) == [0.0, pytest.approx(1 / 0.75)]
+    assert torch.equal(dx_ref != 0, y_ref != 0) and torch.equal(dx != 0, y != 0)
+    assert abs(float((y != 0).float().mean()) - float((y_ref != 0).float().mean())) < 0.03
