@@ -49,6 +49,7 @@ int main(int argc, char **argv) {
   if (mode == "mnist") { MNISTDataLoader<float> l; return image_batch(l, argv[2], argv[3]); }
   if (mode == "cifar10") { CIFAR10DataLoader<float> l; return image_batch(l, argv[2], argv[3]); }
   if (mode == "cifar100") { CIFAR100DataLoader<float> l; return image_batch(l, argv[2], argv[3]); }
+  if (mode == "cifar100coarse") { CIFAR100DataLoader<float> l(true); return image_batch(l, argv[2], argv[3]); }
   if (mode == "wifi") {
     WiFiDataLoader l(true);
     const size_t fe = std::atoi(argv[3]), te = std::atoi(argv[4]);

@@ -401,7 +401,8 @@ def test_dataset_parsers_and_normalisation_match_the_reference(tmp_path):
     assert x.shape == x_ref.shape and torch.allclose(x, x_ref, atol=1e-7) and torch.equal(t, t_ref)
 
     # CIFAR-10: <label><3072 bytes>;  CIFAR-100: <coarse><fine><3072 bytes>
-    for kind, cls, nlab, classes in (("cifar10", CIFAR10DataLoader, 1, 10), ("cifar100", CIFAR100DataLoader, 2, 100)):
+    for kind, cls, nlab, classes in (("cifar10", CIFAR10DataLoader, 1, 10), ("cifar100", CIFAR100DataLoader, 2, 100),
+                                     ("cifar100coarse", lambda: CIFAR100DataLoader(True), 2, 20)):
         rec = rng.integers(0, 256, (5, nlab + 3072), dtype=np.uint8)
         rec[:, 0] = rng.integers(0, 10 if nlab == 1 else 20, 5)
         if nlab == 2:
