@@ -40,6 +40,16 @@ static Sequential<float> make(const std::string &name, std::vector<size_t> *shap
   if (name == "cifar10_cnn_v1") { *shape = {4, 3, 32, 32}; *classes = 10; return create_cifar10_trainer_v1(); }
   if (name == "resnet9_cifar10") { *shape = {4, 3, 32, 32}; *classes = 10; return create_resnet9_cifar10(); }
   if (name == "resnet18_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_resnet18_tiny_imagenet(); }
+  // architecture-only entries (partition / init modes): the rest of the reference's zoo
+  if (name == "cifar10_cnn_v2") { *shape = {2, 3, 32, 32}; *classes = 10; return create_cifar10_trainer_v2(); }
+  if (name == "resnet18_cifar10") { *shape = {2, 3, 32, 32}; *classes = 10; return create_resnet18_cifar10(); }
+  if (name == "resnet20_cifar10") { *shape = {2, 3, 32, 32}; *classes = 10; return create_resnet20_cifar10(); }
+  if (name == "resnet50_cifar10") { *shape = {2, 3, 32, 32}; *classes = 10; return create_resnet50_cifar10(); }
+  if (name == "resnet9_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_resnet9_tiny_imagenet(); }
+  if (name == "cnn_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_cnn_tiny_imagenet(); }
+  if (name == "resnet34_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_resnet34_tiny_imagenet(); }
+  if (name == "resnet50_tiny_imagenet") { *shape = {2, 3, 64, 64}; *classes = 200; return create_resnet50_tiny_imagenet(); }
+  if (name == "resnet50_imagenet") { *shape = {1, 3, 224, 224}; *classes = 1000; return create_resnet50_imagenet(); }
   if (name == "all_layers") {   // every layer kind the zoo models do not cover: GroupNorm, average pooling with padding,
     *shape = {3, 3, 12, 12};    // strided / asymmetric convolution, the smooth activations, dropout (identity in eval)
     *classes = 6;

@@ -563,3 +563,43 @@ def test_max_pool_ties_and_dropout_scaling_match_the_reference(tmp_path):
         assert sorted(set(a.reshape(-1).tolist())) == sorted(set(b.reshape(-1).tolist())) == [0.0, pytest.approx(1 / 0.75)]
     assert torch.equal(dx_ref != 0, y_ref != 0) and torch.equal(dx != 0, y != 0)
     assert abs(float((y != 0).float().mean()) - float((y_ref != 0).float().mean())) < 0.03
+
+
+ZOO_SHAPES = {"mnist_cnn": [4, 1, 28, 28], "cifar10_cnn_v1": [4, 3, 32, 32], "cifar10_cnn_v2": [2, 3, 32, 32],
+              "resnet9_cifar10": [4, 3, 32, 32], "resnet18_cifar10": [2, 3, 32, 32], "resnet20_cifar10": [2, 3, 32, 32],
+              "resnet50_cifar10": [2, 3, 32, 32], "resnet9_tiny_imagenet": [2, 3, 64, 64], "cnn_tiny_imagenet": [2, 3, 64, 64],
+              "resnet18_tiny_imagenet": [2, 3, 64, 64], "resnet34_tiny_imagenet": [2, 3, 64, 64],
+              "resnet50_tiny_imagenet": [2, 3, 64, 64], "resnet50_imagenet": [1, 3, 224, 224]}
+
+
+@pytest.mark.parametrize("name", sorted(ZOO_SHAPES))
+def test_zoo_model_definitions_equal_the_reference_builders(name):
+    """Every model of nn/example_models.hpp, built by the reference, against this library's zoo entry of the same name:
+    the complete configuration (layer order, names, every hyper-parameter, residual-block contents) and the inferred
+    output shape."""
+    import json
+    r = subprocess.run([BIN, "partition", name, "1"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = r.stdout.splitlines()
+    ref_cfg = [json.loads(l[len("stage "):]) for l in lines if l.startswith("stage ")][0]
+    ref_shape = [int(v) for l in lines if l.startswith("output_shape ") for v in l.split()[1:]]
+    model = MODEL_ZOO[name]()
+
+    def same(x, y, path=""):
+        if isinstance(x, dict):
+            assert isinstance(y, dict) and x.keys() == y.keys(), (path, sorted(x), sorted(y) if isinstance(y, dict) else y)
+            for k in x:
+                same(x[k], y[k], f"{path}/{k}")
+        elif isinstance(x, list):
+            assert isinstance(y, list) and len(x) == len(y), (path, len(x), len(y) if isinstance(y, list) else y)
+            for i, (u, v) in enumerate(zip(x, y)):
+                same(u, v, f"{path}[{i}]")
+        elif isinstance(x, float) or isinstance(y, float):
+            assert abs(float(x) - float(y)) <= 1e-6 * max(abs(float(x)), abs(float(y))), (path, x, y)
+        else:
+            assert x == y, (path, x, y)
+    ours = _normalised_config(model.get_config())
+    ref = _normalised_config(ref_cfg)
+    ours["name"], ref["name"] = ours["name"].replace("_part_0", ""), ref["name"].replace("_part_0", "")
+    same(ours, ref)
+    assert list(model.compute_output_shape(ZOO_SHAPES[name])) == ref_shape
