@@ -603,3 +603,41 @@ def test_zoo_model_definitions_equal_the_reference_builders(name):
     ours["name"], ref["name"] = ours["name"].replace("_part_0", ""), ref["name"].replace("_part_0", "")
     same(ours, ref)
     assert list(model.compute_output_shape(ZOO_SHAPES[name])) == ref_shape
+
+
+@pytest.mark.parametrize("name", ["mnist_cnn", "all_layers", "resnet9_cifar10"])
+def test_native_cpu_backend_reproduces_the_reference_too(tmp_path, monkeypatch, name):
+    """The same reference-written snapshots through this library's own CPU kernels (DCNN_CPU_BACKEND=native: blocked
+    convolution, AVX GEMM, native BatchNorm / pooling) instead of ATen: forward output and one training step's loss."""
+    monkeypatch.setenv("DCNN_CPU_BACKEND", "native")
+    prefix = str(tmp_path / name)
+    _ref("write", name, prefix, "1")
+    x, y_ref, _ = _read_io(prefix + ".io.bin")
+    model = nn.Sequential.from_file(prefix, device="CPU")
+    model.set_training(True)
+    y = model.forward(x)
+    assert float((y - y_ref).abs().max()) < 2e-4 * max(1.0, float(y_ref.abs().max()))
+    # one SGD step on both sides from this snapshot
+    io_path = str(tmp_path / "x.io")
+    _write_io(io_path, x)
+    r = subprocess.run([BIN, "train", prefix, io_path, str(tmp_path / "after"), "2", "sgd", "softmax_ce"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ref_losses = [float(l.split()[1]) for l in r.stdout.splitlines() if l.startswith("loss ")]
+    classes = y.shape[1]
+    t = torch.zeros(x.shape[0], classes, 1, 1)
+    for n in range(x.shape[0]):
+        t[n, (3 * n) % classes] = 1.0
+    opt = nn.SGD(0.05, 0.0)
+    opt.attach(model.parameters(), model.gradients())
+    loss = nn.SoftmaxCrossEntropyLoss()
+    ours = []
+    for _ in range(2):
+        out = model.forward(x)
+        ours.append(float(loss.compute_loss(out, t)))
+        model.backward(loss.compute_gradient(out, t))
+        opt.update()
+        model.clear_gradients()
+    tol = 3e-3 if name == "resnet9_cifar10" else 2e-4
+    assert abs(ours[0] - ref_losses[0]) < 2e-5 * max(1.0, abs(ref_losses[0]))
+    assert abs(ours[1] - ref_losses[1]) < tol * max(1.0, abs(ref_losses[1])), (ours, ref_losses)
