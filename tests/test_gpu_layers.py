@@ -174,3 +174,44 @@ def test_layer_sweep_same_on_cpu_and_gpu(name, make, shape):
         _close(a, b, 2e-3)
     for (k, a), (_, b) in zip(gpu.buffers().items(), cpu.buffers().items()):
         _close(a, b)
+
+
+@pytest.mark.parametrize("name", ["mnist_cnn", "all_layers", "resnet9_cifar10", "resnet18_tiny_imagenet"])
+def test_gpu_forward_and_training_step_against_the_reference_binary(tmp_path, name):
+    """The reference itself as the oracle for the CUDA path: it writes a trained snapshot and its own forward output
+    (baseline/_ref/bin/ref_snapshot, CPU FP32), the snapshot is loaded on cuda:0 and must reproduce that output and the
+    loss sequence of two SGD steps (FP32-exact mode of this file's fixture)."""
+    import subprocess
+    from tests.test_reference_interop import BIN, _read_io, _write_io
+    if not os.path.exists(BIN):
+        pytest.skip("reference subset build absent (bash baseline/build_ref.sh)")
+    prefix = str(tmp_path / name)
+    r = subprocess.run([BIN, "write", name, prefix, "1"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    x, y_ref, _ = _read_io(prefix + ".io.bin")
+    model = dnn.Sequential.from_file(prefix, device="GPU")
+    model.set_training(True)
+    y = model.forward(x.cuda())
+    _close(y, y_ref, 2e-3)
+    io_path = str(tmp_path / "x.io")
+    _write_io(io_path, x)
+    r = subprocess.run([BIN, "train", prefix, io_path, str(tmp_path / "after"), "2", "sgd", "softmax_ce"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ref_losses = [float(l.split()[1]) for l in r.stdout.splitlines() if l.startswith("loss ")]
+    classes = y.shape[1]
+    t = torch.zeros(x.shape[0], classes, 1, 1)
+    for n in range(x.shape[0]):
+        t[n, (3 * n) % classes] = 1.0
+    opt = dnn.SGD(0.05, 0.0)
+    opt.attach(model.parameters(), model.gradients())
+    loss = dnn.SoftmaxCrossEntropyLoss()
+    ours = []
+    for _ in range(2):
+        out = model.forward(x.cuda())
+        ours.append(float(loss.compute_loss(out, t.cuda())))
+        model.backward(loss.compute_gradient(out, t.cuda()))
+        opt.update()
+        model.clear_gradients()
+    assert abs(ours[0] - ref_losses[0]) < 1e-3 * max(1.0, abs(ref_losses[0]))
+    assert abs(ours[1] - ref_losses[1]) < 2e-2 * max(1.0, abs(ref_losses[1])), (ours, ref_losses)
