@@ -167,6 +167,13 @@ int main(int argc, char **argv) {
     }
     return 0;
   }
+  if (mode == "configs") {
+    // ref_snapshot configs x x: optimizer configurations as the coordinator ships them inside a StageConfig
+    std::printf("optimizer %s\n", SGD<float>(0.05f, 0.9f).get_config().to_json().dump().c_str());
+    std::printf("optimizer %s\n", Adam<float>(0.01f, 0.8f, 0.95f, 1e-6f, 1e-3f, false).get_config().to_json().dump().c_str());
+    std::printf("optimizer %s\n", Adam<float>(0.02f, 0.9f, 0.999f, 1e-8f, 1e-2f, true).get_config().to_json().dump().c_str());
+    return 0;
+  }
   if (mode == "evalafter") {
     // ref_snapshot evalafter <prefix> <io> <out> <k>: load a snapshot (fresh BatchNorm running statistics), run k
     // training-mode forwards of the io input, then write the evaluation-mode forward -> running-statistics convention

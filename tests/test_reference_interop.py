@@ -641,3 +641,22 @@ def test_native_cpu_backend_reproduces_the_reference_too(tmp_path, monkeypatch, 
     tol = 3e-3 if name == "resnet9_cifar10" else 2e-4
     assert abs(ours[0] - ref_losses[0]) < 2e-5 * max(1.0, abs(ref_losses[0]))
     assert abs(ours[1] - ref_losses[1]) < tol * max(1.0, abs(ref_losses[1])), (ours, ref_losses)
+
+
+def test_optimizer_configs_have_the_reference_schema():
+    """What a coordinator ships to its workers inside a StageConfig: type, name and parameter keys / values."""
+    import json
+    r = subprocess.run([BIN, "configs", "x", "x"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-2000:]
+    ref = [json.loads(l[len("optimizer "):]) for l in r.stdout.splitlines() if l.startswith("optimizer ")]
+    ours = [nn.SGD(0.05, 0.9).get_config(), nn.Adam(0.01, 0.8, 0.95, 1e-6, 1e-3, False).get_config(),
+            nn.Adam(0.02, 0.9, 0.999, 1e-8, 1e-2, True).get_config()]
+    assert len(ref) == len(ours) == 3
+    for a, b in zip(ours, ref):
+        assert a["type"] == b["type"] and a["name"] == b["name"] and a["parameters"].keys() == b["parameters"].keys()
+        for k, v in a["parameters"].items():
+            w = b["parameters"][k]
+            assert (v == w) if isinstance(v, bool) else abs(v - w) <= 1e-6 * max(abs(v), abs(w)), (k, v, w)
+        # and the factory rebuilds the same optimizer from the reference's JSON
+        again = nn.OptimizerFactory.create_from_config(b)
+        assert again.get_config()["type"] == b["type"]
