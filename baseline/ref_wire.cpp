@@ -4,6 +4,7 @@
 //
 //   ref_wire write <dir>          writes none.frame, bool.frame, string.frame, job.frame (a 2x3x4x5 tensor of i*0.25-3)
 //   ref_wire read <frame file>    parses a frame produced elsewhere and prints its fields, one per line
+//   ref_wire stageconfig <json>   StageConfig::from_json on a configuration produced elsewhere, prints its to_json()
 #include <cstdio>
 #include <fstream>
 #include <iterator>
@@ -12,6 +13,7 @@
 
 #include "pipeline/binary_serializer.hpp"
 #include "pipeline/message.hpp"
+#include "pipeline/stage_config.hpp"
 #include "pipeline/tbuffer.hpp"
 
 using namespace tnn;
@@ -41,6 +43,18 @@ int main(int argc, char **argv) {
     job.data = std::move(t);
     job.micro_batch_id = 7;
     dump(d + "/job.frame", Message("stage_1", CommandType::FORWARD_JOB, std::move(job)), "stage_0");
+    return 0;
+  }
+  if (mode == "stageconfig") {
+    std::ifstream f(argv[2]);
+    nlohmann::json j;
+    f >> j;
+    StageConfig cfg = StageConfig::from_json(j);
+    std::printf("stage_id %s\nnext %s %s\nprev %s %s\nroundtrip %s\n", cfg.stage_id.c_str(),
+                cfg.next_stage_endpoint.get_parameter<std::string>("host").c_str(),
+                cfg.next_stage_endpoint.get_parameter<std::string>("port").c_str(),
+                cfg.prev_stage_endpoint.get_parameter<std::string>("host").c_str(),
+                cfg.prev_stage_endpoint.get_parameter<std::string>("port").c_str(), cfg.to_json().dump().c_str());
     return 0;
   }
   if (mode == "read") {

@@ -660,3 +660,53 @@ def test_optimizer_configs_have_the_reference_schema():
         # and the factory rebuilds the same optimizer from the reference's JSON
         again = nn.OptimizerFactory.create_from_config(b)
         assert again.get_config()["type"] == b["type"]
+
+
+@pytest.mark.skipif(not os.path.exists(WIRE), reason="reference wire harness absent (bash baseline/build_ref.sh)")
+def test_stage_config_of_the_tcp_coordinator_is_parsed_by_the_reference(tmp_path):
+    """The CONFIG_TRANSFER payload a TcpCoordinator sends (model + optimizer JSON, three host:port endpoints) goes
+    through the reference's StageConfig::from_json / Endpoint::from_json, and the reference rebuilds the stage's model
+    from the model_config it carried."""
+    import json
+    from dcnn_b200.parallel.pipeline import Endpoint, StageConfig
+    from dcnn_b200.partitioner import NaivePartitioner
+    model = MODEL_ZOO["resnet9_cifar10"]()
+    parts = NaivePartitioner().get_partitions(model.get_layers(), 2)
+    stage = model.split(parts)[1]
+    cfg = StageConfig("stage_1", stage.get_config(), nn.Adam(0.01).get_config(), Endpoint.tcp("10.0.0.9", 8000),
+                      Endpoint.tcp("10.0.0.1", 8001), Endpoint.tcp("10.0.0.9", 8000), {"type": "softmax_crossentropy"},
+                      False, True)
+    path = tmp_path / "stage.json"
+    path.write_text(cfg.dumps())
+    r = subprocess.run([WIRE, "stageconfig", str(path)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout[-500:] + r.stderr[-2000:]
+    out = dict(l.split(" ", 1) for l in r.stdout.splitlines() if l.split(" ", 1)[0] in ("stage_id", "next", "prev", "roundtrip"))
+    assert out["stage_id"] == "stage_1" and out["next"] == "10.0.0.9 8000" and out["prev"] == "10.0.0.1 8001"
+    back = json.loads(out["roundtrip"])
+    assert back["optimizer_config"]["type"] == "adam" and back["coordinator_endpoint"]["communication_type_"] == "tcp"
+    ours_again = StageConfig.from_json(back)               # and what the reference re-emits parses here
+    assert ours_again.next_stage_endpoint.port == 8000 and ours_again.model_config["name"] == stage.name()
+    # the model_config inside is a snapshot-style config the reference can instantiate: write it as <prefix>.json with
+    # this stage's weights and let the reference load and run it
+    stage.set_seed(3)
+    stage.initialize()
+    prefix = str(tmp_path / "stage_model")
+    stage.save_to_file(prefix)
+    assert json.load(open(prefix + ".json")) == json.loads(json.dumps(back["model_config"]))
+    shape_in = None                                        # the stage's input shape: try the plausible cut points
+    for cand in ([2, 128, 16, 16], [2, 256, 8, 8], [2, 256, 16, 16], [2, 128, 8, 8]):
+        try:
+            stage.compute_output_shape(cand)
+            stage.set_training(True)
+            y = stage.forward(torch.rand(*cand))
+            shape_in = cand
+            break
+        except Exception:
+            continue
+    assert shape_in is not None
+    x = torch.rand(*shape_in)
+    _write_io(tmp_path / "x.io", x)
+    _ref("read", prefix, str(tmp_path / "x.io"), str(tmp_path / "y.out"))
+    (y_ref,) = _read_pair(tmp_path / "y.out")
+    y = stage.forward(x)
+    assert float((y - y_ref).abs().max()) < 2e-4 * max(1.0, float(y_ref.abs().max()))
