@@ -8,7 +8,8 @@ Launch modes:
     counterpart of starting ``network_worker <port> --gpu`` S times plus a coordinator binary in the reference;
   * host:port, exactly like the reference (``PIPELINE_WORKERS=host:8001,host:8002 python examples/<coordinator>.py`` or
     ``--workers host:8001,host:8002``): the stages are ``python examples/network_worker.py <port>`` processes reached
-    over the native TCP transport; ``COORDINATOR_HOST`` is the address they use to call back (default 127.0.0.1)."""
+    over the native TCP transport; ``COORDINATOR_HOST`` is the address they use to call back (default 127.0.0.1).  The reference's ``.env`` keys work too:
+    ``WORKER1_HOST`` / ``WORKER1_PORT``, ``WORKER2_...``, ``COORDINATOR_HOST`` / ``COORDINATOR_PORT`` (``env-example``)."""
 from __future__ import annotations
 
 import os
@@ -33,10 +34,18 @@ def make_coordinator(model, optimizer, loss, num_stages, cfg, partitioner=None, 
             workers = sys.argv[i + 1]
         elif a.startswith("--workers="):
             workers = a.split("=", 1)[1]
+    if not workers and os.environ.get("WORKER1_HOST"):
+        # the reference's .env keys (env-example): WORKER<i>_HOST / WORKER<i>_PORT, COORDINATOR_HOST / COORDINATOR_PORT
+        found, i = [], 1
+        while os.environ.get(f"WORKER{i}_HOST"):
+            found.append(f"{os.environ[f'WORKER{i}_HOST']}:{os.environ.get(f'WORKER{i}_PORT', str(8000 + i))}")
+            i += 1
+        workers = ",".join(found[:num_stages] if num_stages else found)
     if workers:
         from dcnn_b200.parallel.pipeline import TcpCoordinator
         addrs = [w for w in workers.split(",") if w]
         coord = TcpCoordinator(model, optimizer, addrs, os.environ.get("COORDINATOR_HOST", "127.0.0.1"),
+                               listen_port=int(os.environ.get("COORDINATOR_PORT", "0")),
                                stage_devices=["cuda:0" if use_gpu else "cpu"] * len(addrs))
     elif world == 1:
         ngpu = torch.cuda.device_count() if use_gpu else 0

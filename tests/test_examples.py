@@ -86,6 +86,35 @@ def test_host_port_pipeline_launch(tmp_path):
     assert out.count(": shutdown") == 2
 
 
+def test_host_port_pipeline_from_the_reference_env_keys(tmp_path):
+    """WORKER<i>_HOST / WORKER<i>_PORT / COORDINATOR_PORT from a .env file, as in the reference's env-example."""
+    import socket
+    import time
+    ports = []
+    for _ in range(3):
+        s = socket.socket()
+        s.bind(("127.0.0.1", 0))
+        ports.append(s.getsockname()[1])
+        s.close()
+    env = dict(ENV, PYTHONPATH=ROOT, PYTHONUNBUFFERED="1")
+    workers = [subprocess.Popen([sys.executable, os.path.join(ROOT, "examples", "network_worker.py"), str(p), "--host",
+                                 "127.0.0.1"], cwd=str(tmp_path), env=env, stdout=subprocess.PIPE,
+                                stderr=subprocess.STDOUT, text=True) for p in ports[:2]]
+    try:
+        (tmp_path / ".env").write_text(f"WORKER1_HOST=127.0.0.1\nWORKER1_PORT={ports[0]}\nWORKER2_HOST=127.0.0.1\n"
+                                       f"WORKER2_PORT={ports[1]}\nCOORDINATOR_HOST=127.0.0.1\nCOORDINATOR_PORT={ports[2]}\n")
+        time.sleep(1.0)
+        out = _run([sys.executable, os.path.join(ROOT, "examples", "sync_pipeline_coordinator.py")], cwd=str(tmp_path),
+                   timeout=600, PYTHONPATH=ROOT)
+        assert "Deployed 2 pipeline stages" in out and "Stopped all pipeline stages" in out
+        for w in workers:
+            assert w.wait(timeout=60) == 0
+    finally:
+        for w in workers:
+            if w.poll() is None:
+                w.kill()
+
+
 def test_streaming_loader_in_the_stock_training_loop(tmp_path):
     out = _run([sys.executable, os.path.join(ROOT, "examples", "cifar10_resnet9.py")], cwd=str(tmp_path),
                PREFETCH_DEPTH="2", EPOCHS="2")
