@@ -64,6 +64,8 @@ def make_coordinator(model, optimizer, loss, num_stages, cfg, partitioner=None, 
             return None, False
         devs = [f"cuda:{(r - 1)}" if use_gpu else "cpu" for r in stage_ranks]
         coord = DistributedCoordinator(model, optimizer, store, control, 0, stage_ranks, devs)
+    if os.environ.get("COORDINATOR_NUM_THREADS"):          # the reference sizes the coordinator's thread pool with this
+        torch.set_num_threads(max(1, int(os.environ["COORDINATOR_NUM_THREADS"])))
     coord.seed = seed
     coord.set_loss_function(loss)
     if partitioner is not None:
