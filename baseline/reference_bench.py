@@ -10,6 +10,18 @@ BIN = os.path.join(HERE, "_ref", "bin", "ref_bench")
 
 
 def run(args):
+    if getattr(args, "device", "cuda") == "cpu":
+        # BASELINE config 1: the reference's MNIST CNN on the CPU (serial parallel_for in the offline subset build)
+        cpu_bin = os.path.join(HERE, "_ref", "bin", "ref_mnist_cpu")
+        if not os.path.exists(cpu_bin) or getattr(args, "model", "") != "mnist_cnn":
+            print(json.dumps({"impl": "reference", "unavailable": "CPU reference arm exists for --model mnist_cnn only "
+                              "(baseline/build_ref.sh builds it)"}))
+            return 0
+        r = subprocess.run([cpu_bin, str(args.batch), str(args.steps), str(args.warmup)], capture_output=True, text=True)
+        line = [l for l in r.stdout.splitlines() if l.startswith("{")]
+        print(line[-1] if r.returncode == 0 and line else
+              json.dumps({"impl": "reference", "unavailable": "reference CPU harness failed"}))
+        return 0
     if not os.path.exists(BIN):
         print(json.dumps({"impl": "reference", "unavailable": "reference harness not built (baseline/build_ref.sh)"}))
         return 0

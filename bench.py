@@ -120,6 +120,9 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--model", default=os.environ.get("BENCH_MODEL", "resnet50_tiny_imagenet"),
                     help="dcnn_b200.models.MODEL_ZOO key; the headline benchmark is the default (BASELINE.json)")
+    ap.add_argument("--device", default="cuda", choices=["cuda", "cpu"],
+                    help="cpu: BASELINE config 1 (MNIST CNN on the CPU, --model mnist_cnn --batch 64) measured for real "
+                         "on this library's native CPU kernels; the headline benchmark is always cuda")
     ap.add_argument("--microbatches", type=int, default=1)
     return ap.parse_args()
 
@@ -169,7 +172,10 @@ def main():
             raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N > 1")
     # BENCH_DEVICE=cpu: plumbing check of THIS SCRIPT on a machine without a GPU (tests/test_bench_contract.py).  Every
     # number it prints is meaningless and marked as such; the benchmark proper always runs on CUDA.
-    cpu_mode = os.environ.get("BENCH_DEVICE", "cuda") == "cpu"
+    real_cpu = args.device == "cpu"            # a CPU measurement on purpose (BASELINE config 1), not the dry run
+    if real_cpu:
+        os.environ.setdefault("DCNN_CPU_BACKEND", "native")
+    cpu_mode = real_cpu or os.environ.get("BENCH_DEVICE", "cuda") == "cpu"
 
     class _CpuEvent:
         def record(self):
@@ -308,7 +314,7 @@ def main():
     barrier()
     sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else 0,
                            None if cpu_mode else getattr(torch.cuda.get_device_properties(dev), "uuid", None))
-    if rank == 0:
+    if rank == 0 and not cpu_mode:         # no GPU clocks to sample on a CPU run (and the sampler would compete for cores)
         sampler.start()
     _lib.reset_launch_count()
     e0, e1 = new_event(), new_event()
@@ -351,7 +357,8 @@ def main():
     ms_e2e = f0.elapsed_time(f1)
     if rank == 0:
         sampler.stop()
-        sampler.join(timeout=2)
+        if sampler.is_alive():
+            sampler.join(timeout=2)
 
     t = torch.tensor([ms, ms_e2e, final_loss if final_loss == final_loss else -1e30, float(launches)], device=dev,
                      dtype=torch.float64)
@@ -384,7 +391,8 @@ def main():
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": (value / base) if base else None,
             "dtype": "fp32 storage, tf32 tensor-core MMA, fp32 accumulate" if not cpu_mode
-            else "CPU DRY RUN OF THE SCRIPT -- not a measurement", "data": "synthetic", "impl": "ours",
+            else (f"fp32 (CPU, {os.environ.get('DCNN_CPU_BACKEND', 'aten')} kernels, {torch.get_num_threads()} threads)"
+                  if real_cpu else "CPU DRY RUN OF THE SCRIPT -- not a measurement"), "data": "synthetic", "impl": "ours",
             "config": {"model": model_name, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
                        "image": "x".join(map(str, img)), "classes": classes, "parallelism": parallelism,
                        "optimizer": opt_desc, "loss": "LogSoftmaxCrossEntropy",

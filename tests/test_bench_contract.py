@@ -68,3 +68,21 @@ def test_reference_arm_answers_for_unsupported_gpu_counts():
     assert r.returncode == 0
     out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert out["impl"] == "reference" and "unavailable" in out
+
+
+def test_cpu_device_mode_measures_baseline_config_1_on_both_arms():
+    """`bench.py --device cpu --model mnist_cnn`: a real CPU measurement (native kernels), labelled as such, and the
+    reference arm for the same configuration when the reference subset build is present."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--device", "cpu", "--model", "mnist_cnn",
+                        "--batch", "16", "--steps", "3", "--warmup", "3"], capture_output=True, text=True, timeout=600,
+                       cwd=ROOT, env={k: v for k, v in os.environ.items() if k not in ("BENCH_DEVICE", "DCNN_CPU_BACKEND")})
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert KEYS <= set(out) and out["value"] > 0
+    assert "native kernels" in out["dtype"] and "DRY RUN" not in out["dtype"] and out["config"]["model"] == "mnist_cnn"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--device", "cpu",
+                        "--model", "mnist_cnn", "--batch", "16", "--steps", "3", "--warmup", "1"], capture_output=True,
+                       text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0
+    ref = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert ref["impl"] == "reference" and ("unavailable" in ref or ref["value"] > 0)
