@@ -9,8 +9,9 @@ DCNN_TEST_PENDING=1 run t_pending python -m pytest tests/test_gpu_ops.py -m gpu 
     -k "bitmask or n256 or stem_packed or tc3 or batchnorm or narrow or autotuner"
 tail -3 gpurun_out/t_pending.log | cut -c1-300
 DCNN_CONV_2CTA=1 run check_2cta timeout 100 python scripts/check_conv_v3.py --pair; grep -v '^PASS' gpurun_out/check_2cta.log | cut -c1-200
-DCNN_TEST_PENDING=1 run t_layers python -m pytest tests/test_gpu_layers.py -m gpu -q --timeout 240 -p no:cacheprovider
+echo "== t_layers"; DCNN_TEST_PENDING=1 timeout 900 python -m pytest tests/test_gpu_layers.py -m gpu -q --timeout 300 -p no:cacheprovider > gpurun_out/t_layers.log 2>&1; echo "exit $?"
 tail -3 gpurun_out/t_layers.log | cut -c1-300
+run t_dp_first python -m pytest tests/test_gpu_dp.py -m gpu -q --timeout 300 -p no:cacheprovider   # needs >= 2 GPUs: skips on one
 run t_all python -m pytest tests -m gpu -x -q --timeout 300 -p no:cacheprovider
 tail -3 gpurun_out/t_all.log | cut -c1-300
 for cfg in "base" "DCNN_BN_BITMASK=1" "DCNN_WGRAD_N256=1" "DCNN_STEM_TC=1" "DCNN_BN_FINALIZE_NARROW=1" "DCNN_CONV_2CTA=1" "DCNN_AUTOTUNE=1" "DCNN_BN_BITMASK=1 DCNN_WGRAD_N256=1 DCNN_STEM_TC=1 DCNN_BN_FINALIZE_NARROW=1"; do
