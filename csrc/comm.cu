@@ -38,6 +38,7 @@ struct ArParams {
   const float* hyper;                   // optional device {lr, bc1, bc2} (CUDA-graph replay)
   float lr, a, b, eps, bc1, bc2, wd, inv_world;
   int mode;  // 0 SGD, 1 momentum, 2 Adam, 3 AdamW
+  int generic_gather;  // 1: the load-add loop for any replica count (DCNN_AR_GENERIC=1, A/B switch for the hoisted loads)
 };
 
 // Own slice plus the W-1 peers' slices.  All peer loads are issued before the first one is consumed: an NVLink load
@@ -72,7 +73,7 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __gri
     const long long e = p.shard_begin + i * 4;
     // reduce-scatter: sum this 16-byte slice over all replicas (own copy first, peers over NVLink)
     float4 g;
-    switch (p.world) {
+    switch (p.generic_gather ? 0 : p.world) {
       case 2: g = gather_sum<2>(pp, e); break;
       case 4: g = gather_sum<4>(pp, e); break;
       case 8: g = gather_sum<8>(pp, e); break;
@@ -228,6 +229,10 @@ DCNN_API int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* 
   p.block_counter = block_counter; p.rank = rank; p.world = world; p.epoch_ptr = epoch_counter; p.hyper = hyper;
   p.lr = lr; p.a = a; p.b = b; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2; p.wd = wd; p.inv_world = 1.f / (float)world;
   p.mode = mode;
+  {
+    const char* ge = getenv("DCNN_AR_GENERIC");
+    p.generic_gather = (ge != nullptr && atoi(ge) != 0) ? 1 : 0;
+  }
   if (num_blocks <= 0) num_blocks = num_sms();
   epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
   fused_allreduce_update_kernel<<<num_blocks, 512, 0, stream>>>(p);
