@@ -38,7 +38,7 @@ struct ArParams {
   const float* hyper;                   // optional device {lr, bc1, bc2} (CUDA-graph replay)
   float lr, a, b, eps, bc1, bc2, wd, inv_world;
   int mode;  // 0 SGD, 1 momentum, 2 Adam, 3 AdamW
-  int generic_gather;  // 1: the load-add loop for any replica count (DCNN_AR_GENERIC=1, A/B switch for the hoisted loads)
+  int generic_gather;  // 1: the load-add loop (hardware-validated, default); 0: loads-first path for 2 / 4 / 8 replicas (DCNN_AR_HOISTED=1)
 };
 
 // Own slice plus the W-1 peers' slices.  All peer loads are issued before the first one is consumed: an NVLink load
@@ -230,8 +230,9 @@ DCNN_API int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* 
   p.lr = lr; p.a = a; p.b = b; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2; p.wd = wd; p.inv_world = 1.f / (float)world;
   p.mode = mode;
   {
-    const char* ge = getenv("DCNN_AR_GENERIC");
-    p.generic_gather = (ge != nullptr && atoi(ge) != 0) ? 1 : 0;
+    // the loads-first gather was written after the last hardware session: opt-in until tests/test_gpu_dp.py has run with it
+    const char* ge = getenv("DCNN_AR_HOISTED");
+    p.generic_gather = (ge != nullptr && atoi(ge) != 0) ? 0 : 1;
   }
   if (num_blocks <= 0) num_blocks = num_sms();
   epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);

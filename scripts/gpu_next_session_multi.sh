@@ -5,8 +5,10 @@ N=${1:-2}
 mkdir -p gpurun_out
 export PYTHONUNBUFFERED=1
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533"
-# the fused all-reduce kernel changed after its last hardware run (peer loads hoisted): its equivalence tests come first
+# default (validated) all-reduce first, then the opt-in loads-first gather (DCNN_AR_HOISTED=1) through the same tests
 echo "== dp tests"; timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_$N.log | cut -c1-300
+echo "== dp tests, hoisted gather"; DCNN_AR_HOISTED=1 timeout 200 python -m pytest tests/test_gpu_dp.py -m gpu -x -q --timeout 180 -p no:cacheprovider > gpurun_out/t_dp_hoisted_$N.log 2>&1; echo "exit $?"; tail -3 gpurun_out/t_dp_hoisted_$N.log | cut -c1-300
+echo "== allreduce roofline, hoisted gather"; DCNN_AR_HOISTED=1 timeout 200 $TR benchmarks/allreduce_roofline.py > gpurun_out/ar_hoisted_$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/ar_hoisted_$N.log | cut -c1-400
 echo "== allreduce roofline"; timeout 200 $TR benchmarks/allreduce_roofline.py > gpurun_out/ar_$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/ar_$N.log | cut -c1-400
 echo "== dp$N"; timeout 90 $TR bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_dp$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_dp$N.log | cut -c1-300
 echo "== pp$N"; timeout 90 $TR bench.py --gpus $N --steps 10 --warmup 3 --parallelism pp$N --microbatches $((2*N)) > gpurun_out/bench_pp$N.log 2>&1; echo "exit $?"; tail -1 gpurun_out/bench_pp$N.log | cut -c1-300
