@@ -253,7 +253,11 @@ int main(int argc, char **argv) {
     auto stages = model.split(parts);
     for (auto &st : stages) std::printf("stage %s\n", st.get_config().dump().c_str());
     std::vector<size_t> in = shape;
-    std::printf("output_shape");
+    std::printf("forward_complexity");
+    for (uint64_t v : model.forward_complexity(in)) std::printf(" %llu", (unsigned long long)v);
+    std::printf("\nbackward_complexity");
+    for (uint64_t v : model.backward_complexity(in)) std::printf(" %llu", (unsigned long long)v);
+    std::printf("\noutput_shape");
     for (size_t d : model.compute_output_shape(in)) std::printf(" %zu", d);
     std::printf("\n");
     return 0;

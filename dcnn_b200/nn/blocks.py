@@ -163,15 +163,20 @@ class ResidualBlock(Layer):
         return list(s)
 
     def _sum(self, fn, s):
+        """Main path + shortcut path + the element-wise addition over the block's output (forward) / the gradient
+        summation (backward), as the reference counts it (residual_block.hpp:313-359)."""
         total, cur = 0, list(s)
         for l in self.main_path:
             total += getattr(l, fn)(cur)
             cur = l.compute_output_shape(cur)
+        add = 1
+        for d in cur:
+            add *= int(d)
         cur = list(s)
         for l in self.shortcut_path:
             total += getattr(l, fn)(cur)
             cur = l.compute_output_shape(cur)
-        return total
+        return total + add
 
     def forward_flops(self, s):
         return self._sum("forward_flops", s)

@@ -354,6 +354,10 @@ def test_partitions_stage_configs_and_shapes_match_the_reference(name, stages, s
     for a, b in zip(ours, ref_stages):
         assert same(_normalised_config(a.get_config()), _normalised_config(b))
     assert list(model.compute_output_shape(shape)) == ref_shape
+    # per-layer cost models (what a load-balancing partitioner is fed)
+    for key, fn in (("forward_complexity", model.forward_complexity), ("backward_complexity", model.backward_complexity)):
+        ref_cost = [int(v) for l in lines if l.startswith(key + " ") for v in l.split()[1:]]
+        assert [int(v) for v in fn(shape)] == ref_cost, key
 
 
 DATA = os.path.join(ROOT, "baseline", "_ref", "bin", "ref_data")
