@@ -325,7 +325,8 @@ def _normalised_config(o):
 
 
 @pytest.mark.parametrize("name,stages,shape", [("resnet9_cifar10", 3, [4, 3, 32, 32]), ("mnist_cnn", 4, [4, 1, 28, 28]),
-                                               ("resnet18_tiny_imagenet", 5, [2, 3, 64, 64]), ("cifar10_cnn_v1", 2, [4, 3, 32, 32])])
+                                               ("resnet18_tiny_imagenet", 5, [2, 3, 64, 64]), ("cifar10_cnn_v1", 2, [4, 3, 32, 32]),
+                                               ("all_layers", 3, [3, 3, 12, 12])])
 def test_partitions_stage_configs_and_shapes_match_the_reference(name, stages, shape):
     """NaivePartitioner ranges, Sequential::split stage configs (what the coordinator ships to workers) and output-shape
     inference, from the reference's own code."""
@@ -337,7 +338,7 @@ def test_partitions_stage_configs_and_shapes_match_the_reference(name, stages, s
     ref_parts = [tuple(int(v) for v in p.split(":")) for l in lines if l.startswith("partitions ") for p in l.split()[1:]]
     ref_stages = [json.loads(l[len("stage "):]) for l in lines if l.startswith("stage ")]
     ref_shape = [int(v) for l in lines if l.startswith("output_shape ") for v in l.split()[1:]]
-    model = MODEL_ZOO[name]()
+    model = _all_layers() if name == "all_layers" else MODEL_ZOO[name]()
     parts = NaivePartitioner().get_partitions(model.get_layers(), stages)
     assert [(p.start_layer, p.end_layer) for p in parts] == ref_parts
     ours = model.split(parts)
