@@ -393,16 +393,18 @@ def main():
             "dtype": "fp32 storage, tf32 tensor-core MMA, fp32 accumulate" if not cpu_mode
             else (f"fp32 (CPU, {os.environ.get('DCNN_CPU_BACKEND', 'aten')} kernels, {torch.get_num_threads()} threads)"
                   if real_cpu else "CPU DRY RUN OF THE SCRIPT -- not a measurement"), "data": "synthetic", "impl": "ours",
+            # `config` has the same keys (and, for a single device, the same values) on both arms: what is specific to
+            # this implementation's run sits beside it in `run`
             "config": {"model": model_name, "global_batch": gb, "per_gpu_batch": B, "seq_len": None,
                        "image": "x".join(map(str, img)), "classes": classes, "parallelism": parallelism,
                        "optimizer": opt_desc, "loss": "LogSoftmaxCrossEntropy",
-                       "cuda_graph": (step._graph is not None) or
-                                     (engine is not None and getattr(engine, "_graphs", None) is not None),
-                       "microbatches": args.microbatches,
-                       "pipeline_stages": S, "dp_replicas": R, "sync_bn": sync_bn and R > 1,
-                       "pipeline_bubble_fraction": bubble,
+                       "microbatches": args.microbatches, "pipeline_stages": S, "dp_replicas": R,
                        "l2": "per-step working set (activations, >10 GB at batch 256) is far larger than the 126 MB L2; "
                              "inputs rotate over 4 distinct batches"},
+            "run": {"cuda_graph": (step._graph is not None) or
+                                  (engine is not None and getattr(engine, "_graphs", None) is not None),
+                    "sync_bn": sync_bn and R > 1},
+            "pipeline_bubble_fraction": bubble,
             "clocks": sampler.summary(),
             "e2e": {"value": round(e2e, 2), "unit": "images/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},

@@ -59,7 +59,7 @@ def test_two_rank_modes(par, extra):
     assert all(cfg[k] == v for k, v in extra.items())
     assert cfg["global_batch"] == (8 if par == "dp2" else 8)      # dp: 2 x 4; pp: the replica is fed batch x stages
     if par == "pp2":
-        assert 0.0 <= cfg["pipeline_bubble_fraction"] < 1.0
+        assert 0.0 <= out["pipeline_bubble_fraction"] < 1.0
 
 
 def test_reference_arm_answers_for_unsupported_gpu_counts():
