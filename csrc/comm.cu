@@ -38,7 +38,7 @@ struct ArParams {
   const float* hyper;                   // optional device {lr, bc1, bc2} (CUDA-graph replay)
   float lr, a, b, eps, bc1, bc2, wd, inv_world;
   int mode;  // 0 SGD, 1 momentum, 2 Adam, 3 AdamW
-  int generic_gather;  // 1: the load-add loop (hardware-validated, default); 0: loads-first path for 2 / 4 / 8 replicas (DCNN_AR_HOISTED=1)
+  int generic_gather;  // 0 (default): loads-first gather for 2 / 4 / 8 replicas; 1: the load-add loop (other world sizes, DCNN_AR_HOISTED=0)
 };
 
 // Own slice plus the W-1 peers' slices.  All peer loads are issued before the first one is consumed: an NVLink load
@@ -230,15 +230,16 @@ DCNN_API int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* 
   p.lr = lr; p.a = a; p.b = b; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2; p.wd = wd; p.inv_world = 1.f / (float)world;
   p.mode = mode;
   {
-    // the loads-first gather was written after the last hardware session: opt-in until tests/test_gpu_dp.py has run with it
-    const char* ge = getenv("DCNN_AR_HOISTED");
-    p.generic_gather = (ge != nullptr && atoi(ge) != 0) ? 0 : 1;
+    static const bool hoisted = !(getenv("DCNN_AR_HOISTED") != nullptr && atoi(getenv("DCNN_AR_HOISTED")) == 0);
+    p.generic_gather = hoisted ? 0 : 1;
   }
   if (num_blocks <= 0) num_blocks = num_sms();
   epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
   fused_allreduce_update_kernel<<<num_blocks, 512, 0, stream>>>(p);
   DCNN_CHECK_LAUNCH();
-  wait_done_zero_kernel<<<num_sms(), 512, 0, stream>>>(p.done_flags, rank, world, epoch_counter, grad_ptrs[rank], n);
+  // same CTA count as the reduce kernel: a bucket launch on the side stream (32 CTAs) must not fill the SMs that the
+  // backward pass is using with threads that spin on the peers' done flags
+  wait_done_zero_kernel<<<num_blocks, 512, 0, stream>>>(p.done_flags, rank, world, epoch_counter, grad_ptrs[rank], n);
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(3);
   return 0;

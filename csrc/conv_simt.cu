@@ -137,6 +137,29 @@ __global__ void weight_dgrad_layout_kernel(const float* __restrict__ w, float* _
   }
 }
 
+
+// Up to kWtBatch weight tensors in ONE launch: the table {w, wt, K, R, S, C} travels as a kernel parameter (no device
+// table, so the launch is capturable without a host-to-device copy); blockIdx.y selects the entry, blockIdx.x strides
+// over its elements.
+constexpr int kWtBatch = 64;
+struct WtTable { long long e[kWtBatch][6]; };
+__global__ void __launch_bounds__(256) weight_dgrad_layout_batched_kernel(const __grid_constant__ WtTable table) {
+  const long long* e = table.e[blockIdx.y];
+  const float* __restrict__ w = reinterpret_cast<const float*>(e[0]);
+  float* __restrict__ wt = reinterpret_cast<float*>(e[1]);
+  const int K = (int)e[2], R = (int)e[3], S = (int)e[4], C = (int)e[5];
+  const long long total = (long long)K * R * S * C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % K);
+    long long t = i / K;
+    const int s2 = (int)(t % S); t /= S;
+    const int r2 = (int)(t % R);
+    const int c = (int)(t / R);
+    wt[i] = __ldg(w + (((long long)k * R + (R - 1 - r2)) * S + (S - 1 - s2)) * C + c);
+  }
+}
+
 }  // namespace dcnn
 using namespace dcnn;
 
@@ -203,6 +226,21 @@ DCNN_API int dcnn_weight_dgrad_layout(const float* w, float* wt, int K, int R, i
   return 0;
 }
 
+DCNN_API int dcnn_weight_dgrad_layout_batched(const long long* table_host, int count, cudaStream_t stream) {
+  DCNN_REQUIRE(count >= 1, "dcnn_weight_dgrad_layout_batched: bad entry count %d", count);
+  for (int first = 0; first < count; first += kWtBatch) {
+    const int n = count - first < kWtBatch ? count - first : kWtBatch;
+    WtTable t;
+    memset(&t, 0, sizeof(t));
+    memcpy(t.e, table_host + 6 * (size_t)first, sizeof(long long) * 6 * n);
+    dim3 grid(64, (unsigned)n);
+    weight_dgrad_layout_batched_kernel<<<grid, 256, 0, stream>>>(t);
+    DCNN_CHECK_LAUNCH();
+    DCNN_COUNT_LAUNCH(1);
+  }
+  return 0;
+}
+
 namespace dcnn {
 // Packed-tap im2col for small-Cin ("stem") convolutions: P[n,oh,ow,k] = x[n, oh*sh-ph+r, ow*sw-pw+s, c] with
 // k = (r*S+s)*Cin + c for k < R*S*Cin, zero for the padding channels up to Kp (a multiple of 32) and for taps that fall
@@ -212,24 +250,44 @@ namespace dcnn {
 __global__ void __launch_bounds__(256) pack_taps_kernel(const float* __restrict__ x, float* __restrict__ P, int N, int H,
                                                         int W, int Cin, int OH, int OW, int R, int S, int sh, int sw,
                                                         int ph, int pw, int Kp) {
+  // tab[k] = (r << 24) | (s << 16) | c for the packed channel k, -1 for the zero padding up to Kp
+  __shared__ int tab[256];
   const int K = R * S * Cin;
-  const long long total = (long long)N * OH * OW * Kp;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int k = (int)(i % Kp);
-    long long t = i / Kp;
-    const int ow = (int)(t % OW); t /= OW;
-    const int oh = (int)(t % OH);
-    const int n = (int)(t / OH);
-    float v = 0.f;
+  for (int k = threadIdx.x; k < Kp; k += blockDim.x) {
+    int v = -1;
     if (k < K) {
       const int tap = k / Cin, c = k - tap * Cin;
       const int r = tap / S, s2 = tap - r * S;
-      const int ih = oh * sh - ph + r, iw = ow * sw - pw + s2;
-      if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W)
-        v = __ldg(x + (((long long)n * H + ih) * W + iw) * Cin + c);
+      v = (r << 24) | (s2 << 16) | c;
     }
-    P[i] = v;
+    tab[k] = v;
+  }
+  __syncthreads();
+  // a thread packs 4 consecutive k of one pixel (one 16-byte store); Q = Kp/4 threads cover a pixel, so consecutive
+  // threads write whole 4*Kp-byte rows back to back.  Threads beyond the last whole pixel of the block idle.
+  const int Q = Kp >> 2;
+  const int q = threadIdx.x % Q;
+  const int pix_per_block = blockDim.x / Q;
+  const long long pixels = (long long)N * OH * OW;
+  if ((int)threadIdx.x >= pix_per_block * Q) return;
+  for (long long pix = (long long)blockIdx.x * pix_per_block + threadIdx.x / Q; pix < pixels;
+       pix += (long long)gridDim.x * pix_per_block) {
+    const unsigned up = (unsigned)pix;                       // N*OH*OW < 2^32 (checked on the host)
+    const unsigned ow = up % (unsigned)OW, t = up / (unsigned)OW;
+    const unsigned oh = t % (unsigned)OH, n = t / (unsigned)OH;
+    const int ih0 = (int)oh * sh - ph, iw0 = (int)ow * sw - pw;
+    const float* xin = x + (long long)n * H * W * Cin;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e = tab[4 * q + j];
+      v[j] = 0.f;
+      if (e >= 0) {
+        const int ih = ih0 + (e >> 24), iw = iw0 + ((e >> 16) & 255);
+        if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W) v[j] = __ldg(xin + ((long long)ih * W + iw) * Cin + (e & 0xffff));
+      }
+    }
+    *reinterpret_cast<float4*>(P + pix * Kp + 4 * q) = make_float4(v[0], v[1], v[2], v[3]);
   }
 }
 }  // namespace dcnn
@@ -238,9 +296,14 @@ DCNN_API int dcnn_pack_taps(const float* x, float* P, int N, int H, int W, int C
                             int sh, int sw, int ph, int pw, int Kp, cudaStream_t stream) {
   DCNN_REQUIRE(Kp % 32 == 0 && Kp >= R * S * Cin, "dcnn_pack_taps: Kp (%d) must be a multiple of 32 >= R*S*Cin (%d)", Kp,
                R * S * Cin);
-  const long long total = (long long)N * OH * OW * Kp;
-  dcnn::pack_taps_kernel<<<dcnn::ew_grid(total, 256, 4), 256, 0, stream>>>(x, P, N, H, W, Cin, OH, OW, R, S, sh, sw, ph,
-                                                                          pw, Kp);
+  DCNN_REQUIRE(Kp <= 256, "dcnn_pack_taps: Kp (%d) must not exceed 256", Kp);
+  DCNN_REQUIRE((long long)N * OH * OW < (1ll << 32) && R < 128 && S < 256 && Cin < 65536, "dcnn_pack_taps: problem too large");
+  const long long pixels = (long long)N * OH * OW;
+  const int ppb = 256 / (Kp / 4);
+  long long blocks = (pixels + ppb - 1) / ppb;
+  const long long cap = (long long)dcnn::num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  dcnn::pack_taps_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, P, N, H, W, Cin, OH, OW, R, S, sh, sw, ph, pw, Kp);
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(1);
   return 0;

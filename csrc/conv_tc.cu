@@ -1,6 +1,6 @@
 // Implicit-GEMM convolution / GEMM on the 5th-generation tensor cores (sm_100a).
 //
-//   * conv_tc_kernel   : D[pixels, oc] = sum_{tap, c} A[pixel@tap, c] * W[oc, tap, c]      (both operands K-major)
+//   * conv_tc{2,3,5}   : D[pixels, oc] = sum_{tap, c} A[pixel@tap, c] * W[oc, tap, c]      (both operands K-major)
 //       used for conv fprop, conv dgrad (on dY with re-laid-out weights; strided dgrad as parity classes with an
 //       output stride), Dense forward and Dense dgrad.  Replaces cudnnConvolutionForward / BackwardData and
 //       cublasSgemm of the reference (src/nn/layers_impl/cuda/cudnn_conv2d_ops.cu:171-216, dense_ops.cu:24-137).
@@ -45,230 +45,140 @@ struct ConvTcParams {
   int16_t tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_w[kMaxTaps];
 };
 
-template <int BN, int STAGES>
-struct ConvTcSmem {
-  static constexpr int kABytes = kBM * 128;
-  static constexpr int kBBytes = BN * 128;
-  static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kPipeBytes = STAGES * kStageBytes;
-  static constexpr int kOutStride = BN + 4;  // floats; +4 keeps float4 alignment and spreads banks
-  static constexpr int kStagingBytes = kBM * kOutStride * 4;
-  static constexpr int kMainBytes = kPipeBytes > kStagingBytes ? kPipeBytes : kStagingBytes;
-  static constexpr int kTotalBytes = kMainBytes + 1024 /*align*/ + 256 /*barriers*/ + 512 /*row flags*/;
+// =====================================================================================================
+// Epilogue shared by the three kernels below.  Four warps (128 threads, named barriers 1 and 2) turn one accumulator
+// tile of 128 rows x CHUNKS*32 columns into (a) a TMA store (or TMA reduce-add) of the output tile and (b) BatchNorm
+// partial statistics:
+//   epi_begin   the staging buffer is free again (previous TMA stores have read it); row-validity flags of edge tiles
+//   epi_drain   tcgen05.ld -> (+bias) -> 128B-swizzled staging buffer, one [128 rows][32 columns] box per chunk
+//   (caller)    hands the TMEM buffer back to the MMA warp, fence.proxy.async, named barrier
+//   epi_finish  TMA store / reduce-add per chunk (rows and columns outside the tensor are clipped by the TMA unit),
+//               then the shifted single-pass statistics (sum(x-k), sum((x-k)^2), k = the tile's first row) with
+//               conflict-free swizzled reads: thread (column cl, row group rg) sums 32 rows, 4 row groups are merged
+//               through `red`.
+// =====================================================================================================
+struct EpiTile {
+  int n0, oh0, ow0;     // first output pixel of the tile
+  int obn, obh, obw;    // its box (obn * obh * obw == 128 rows, row order n, h, w)
+  int col_base;         // first output channel
+  int stat_tile;        // index of this tile in the partial-statistics buffer
+  int stat_tiles;       // number of statistics tiles (the row counts follow the [stat_tiles][2][Cout] sums)
+  bool write_count;     // this tile records its row count (one n-tile per statistics tile does)
+  bool full;            // no row of the tile is outside [N, OH, OW]
 };
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(kThreads) conv_tc_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                           const __grid_constant__ CUtensorMap tmB,
-                                                           const __grid_constant__ ConvTcParams p) {
-  using S = ConvTcSmem<BN, STAGES>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kMainBytes);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-  uint8_t* row_valid = smem + S::kMainBytes + 256;
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-
-  // tile coordinates: n-tile is the fastest index so CTAs that share an A tile run back to back (L2 reuse)
-  const int n_tile = blockIdx.x % p.n_tiles;
-  const int m_tile = blockIdx.x / p.n_tiles;
-  const int tw = m_tile % p.tiles_w;
-  const int th = (m_tile / p.tiles_w) % p.tiles_h;
-  const int tn = m_tile / (p.tiles_w * p.tiles_h);
-  const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
-
-  const int cchunks = p.Cin / kBK;
-  const int num_kb = p.num_taps * cchunks;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
+__device__ __forceinline__ void epi_begin(const ConvTcParams& p, const EpiTile& t, uint8_t* row_valid, int r,
+                                          bool issuer) {
+  if (issuer) tma_store_wait_read();  // earlier stores no longer read the staging buffer
+  if (p.partials != nullptr && !t.full) {
+    const int w_l = r % t.obw, h_l = (r / t.obw) % t.obh, n_l = r / (t.obw * t.obh);
+    row_valid[r] = ((t.n0 + n_l < p.N) && (t.oh0 + h_l < p.OH) && (t.ow0 + w_l < p.OW)) ? 1 : 0;
   }
-  if (warp == 1) {
-    if (lane == 0) {
-      for (int s = 0; s < STAGES; ++s) {
-        mbar_init(&full_bar[s], 1);
-        mbar_init(&empty_bar[s], 1);
-      }
-      mbar_init(tmem_full_bar, 1);
-      fence_barrier_init();
-    }
-    __syncwarp();
-    tmem_alloc(tmem_slot, BN < 32 ? 32 : BN);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  asm volatile("bar.sync 1, 128;" ::: "memory");
+}
 
-  if (warp == 0) {
-    if (lane == 0) {
-      // ===================== TMA producer =====================
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int t = kb / cchunks;
-        const int c = kb - t * cchunks;
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
-        uint8_t* sA = smem + stage * S::kStageBytes;
-        tma_load_4d(sA, &tmA, &full_bar[stage], c * kBK, ow0 * p.in_mul_w + p.tap_dw[t],
-                    oh0 * p.in_mul_h + p.tap_dh[t], n0);
-        tma_load_2d(sA + S::kABytes, &tmB, &full_bar[stage], p.tap_w[t] * p.Cin + c * kBK, n_tile * BN);
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      // ===================== MMA issuer =====================
-      constexpr uint32_t idesc = make_idesc_tf32(kBM, BN, 0, 0);
-      constexpr uint64_t desc_hi = make_smem_desc_hi(16, 1024);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
-        const uint32_t b_addr = a_addr + S::kABytes;
-#pragma unroll
-        for (int k = 0; k < kBK / 8; ++k) {
-          mma_tf32_ss(tmem_base, make_smem_desc(a_addr + k * 32, desc_hi), make_smem_desc(b_addr + k * 32, desc_hi),
-                      idesc, (kb | k) != 0);
-        }
-        mma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-      mma_commit(tmem_full_bar);
-    }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int q = warp & 3;  // TMEM lane quadrant this warp may access
-    const int r = q * 32 + lane;
-    const int e = threadIdx.x - 64;  // 0..127
-    // row -> output pixel
-    const int w_l = r % p.bw;
-    const int h_l = (r / p.bw) % p.bh;
-    const int n_l = r / (p.bw * p.bh);
-    const bool valid = (n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW);
-    row_valid[r] = valid ? 1 : 0;
-
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    float* staging = reinterpret_cast<float*>(smem);
-    const int col_base = n_tile * BN;
+template <int CHUNKS>
+__device__ __forceinline__ void epi_drain(const ConvTcParams& p, uint32_t tmem_d, uint8_t* staging, int r,
+                                          int col_base) {
 #pragma unroll 1
-    for (int c0 = 0; c0 < BN; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + c0, v);
-      tmem_ld_wait();
-      float* dst = staging + r * S::kOutStride + c0;
+  for (int ch = 0; ch < CHUNKS; ++ch) {
+    if (col_base + ch * 32 >= p.Cout) break;
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
+    tmem_ld_wait();
+    uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        float4 o;
-        o.x = __uint_as_float(v[j + 0]);
-        o.y = __uint_as_float(v[j + 1]);
-        o.z = __uint_as_float(v[j + 2]);
-        o.w = __uint_as_float(v[j + 3]);
-        if (p.bias != nullptr) {
-          const int c = col_base + c0 + j;
-          o.x += (c + 0 < p.Cout) ? __ldg(p.bias + c + 0) : 0.f;
-          o.y += (c + 1 < p.Cout) ? __ldg(p.bias + c + 1) : 0.f;
-          o.z += (c + 2 < p.Cout) ? __ldg(p.bias + c + 2) : 0.f;
-          o.w += (c + 3 < p.Cout) ? __ldg(p.bias + c + 3) : 0.f;
-        }
-        st4(dst + j, o);
-      }
-    }
-    tc_fence_before();
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-
-    // ---- (a) coalesced store: one warp instruction writes one output row segment
-    const int ew = warp - 2;
-    const bool vec_ok = (p.Cout & 3) == 0;
-    for (int i = 0; i < 32; ++i) {
-      const int rr = ew * 32 + i;
-      if (!row_valid[rr]) continue;
-      const int ww = rr % p.bw, hh = (rr / p.bw) % p.bh, nn = rr / (p.bw * p.bh);
-      float* orow = p.out + (long long)(n0 + nn) * p.out_sn + (long long)(oh0 + hh) * p.out_sh +
-                    (long long)(ow0 + ww) * p.out_sw + col_base;
-      const float* srow = staging + rr * S::kOutStride;
-      if (vec_ok) {
-        for (int cj = lane * 4; cj < BN; cj += 128) {
-          if (col_base + cj < p.Cout) {
-            float4 o = ld4(srow + cj);
-            if (p.accumulate) {
-              const float4 old = ld4(orow + cj);
-              o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
-            }
-            st4(orow + cj, o);
-          }
-        }
-      } else {
-        for (int cj = lane; cj < BN; cj += 32) {
-          if (col_base + cj < p.Cout) {
-            float o = srow[cj];
-            if (p.accumulate) o += orow[cj];
-            orow[cj] = o;
-          }
+    for (int j = 0; j < 8; ++j) {
+      float4 o;
+      o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
+      o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
+      if (p.bias != nullptr) {
+        const int c = col_base + ch * 32 + 4 * j;
+        if (c < p.Cout) {  // Cout % 4 == 0 on this path
+          const float4 b = ldg4(p.bias + c);
+          o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
         }
       }
+      *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
     }
-
-    // ---- (b) BatchNorm partial statistics of this tile: per channel (sum, M2 about the tile mean)
-    if (p.partials != nullptr) {
-      int cnt = 0;
-      for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
-      if (e == 0 && n_tile == 0) p.partials[(long long)p.m_tiles * 2 * p.Cout + m_tile] = (float)cnt;
-      for (int j = e; j < BN; j += 128) {
-        const int c = col_base + j;
-        if (c >= p.Cout) continue;
-        float s = 0.f;
-        for (int rr = 0; rr < kBM; ++rr) s += row_valid[rr] ? staging[rr * S::kOutStride + j] : 0.f;
-        const float mean = cnt > 0 ? s / (float)cnt : 0.f;
-        float m2 = 0.f;
-        for (int rr = 0; rr < kBM; ++rr) {
-          const float d = staging[rr * S::kOutStride + j] - mean;
-          m2 += row_valid[rr] ? d * d : 0.f;
-        }
-        p.partials[((long long)m_tile * 2 + 0) * p.Cout + c] = s;
-        p.partials[((long long)m_tile * 2 + 1) * p.Cout + c] = m2;
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
   }
 }
 
+template <int CHUNKS>
+__device__ __forceinline__ void epi_finish(const ConvTcParams& p, const CUtensorMap* tmO, const EpiTile& t,
+                                           uint8_t* staging, float* red, const uint8_t* row_valid, int e) {
+  constexpr int RS = CHUNKS * 32;  // row stride of `red`
+  if (e == 0) {
+    for (int ch = 0; ch < CHUNKS; ++ch) {
+      const int c = t.col_base + ch * 32;
+      if (c >= p.Cout) break;
+      if (p.accumulate) tma_reduce_add_4d(tmO, staging + ch * (kBM * 128), c, t.ow0, t.oh0, t.n0);
+      else tma_store_4d(tmO, staging + ch * (kBM * 128), c, t.ow0, t.oh0, t.n0);
+    }
+    tma_store_commit();
+  }
+  if (p.partials == nullptr) return;
+  const int cl = e & 31, rg = e >> 5;
+  int cnt = kBM;
+  if (!t.full) {
+    cnt = 0;
+    for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
+  }
+  for (int ch = 0; ch < CHUNKS; ++ch) {
+    if (t.col_base + ch * 32 >= p.Cout) break;
+    const uint8_t* src = staging + ch * (kBM * 128);
+    const float kshift = *reinterpret_cast<const float*>(src + ((cl >> 2) << 4) + ((cl & 3) << 2));  // row 0
+    float s = 0.f, qq = 0.f;
+    if (t.full) {
+#pragma unroll 8
+      for (int i = 0; i < 32; ++i) {
+        const int rr = rg * 32 + i;
+        const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) + ((cl & 3) << 2));
+        const float d = x - kshift;
+        s += d;
+        qq = fmaf(d, d, qq);
+      }
+    } else {
+      for (int i = 0; i < 32; ++i) {
+        const int rr = rg * 32 + i;
+        const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) + ((cl & 3) << 2));
+        const float d = row_valid[rr] ? x - kshift : 0.f;
+        s += d;
+        qq = fmaf(d, d, qq);
+      }
+    }
+    red[(0 * 4 + rg) * RS + ch * 32 + cl] = s;
+    red[(1 * 4 + rg) * RS + ch * 32 + cl] = qq;
+  }
+  asm volatile("bar.sync 2, 128;" ::: "memory");
+  for (int j = e; j < RS; j += 128) {
+    const int c = t.col_base + j;
+    if (c < p.Cout) {
+      const int ch = j >> 5, cl2 = j & 31;
+      const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) + ((cl2 & 3) << 2));
+      const float s = red[(0 * 4 + 0) * RS + j] + red[(0 * 4 + 1) * RS + j] + red[(0 * 4 + 2) * RS + j] +
+                      red[(0 * 4 + 3) * RS + j];
+      const float qq = red[(1 * 4 + 0) * RS + j] + red[(1 * 4 + 1) * RS + j] + red[(1 * 4 + 2) * RS + j] +
+                       red[(1 * 4 + 3) * RS + j];
+      const float n = (float)cnt;
+      p.partials[((long long)t.stat_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
+      p.partials[((long long)t.stat_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
+    }
+  }
+  if (e == 0 && t.write_count) p.partials[(long long)t.stat_tiles * 2 * p.Cout + t.stat_tile] = (float)cnt;
+}
 
 // =====================================================================================================
-// conv_tc2: persistent, warp-specialised version of conv_tc_kernel.
+// conv_tc2: persistent, warp-specialised implicit GEMM with 128-pixel tiles.
 //   * one CTA per SM walks a static tile schedule (n-tile fastest); barriers, TMEM allocation and descriptor
 //     prefetch are paid once per CTA instead of once per tile;
 //   * the accumulator is double-buffered in TMEM (2 x BN columns): the MMA warp starts tile i+1 while the four
 //     epilogue warps drain tile i, so short-K layers (1x1 convs) are bounded by the store stream, not by a serial
 //     load -> MMA -> epilogue chain;
-//   * the epilogue stages the tile in 128B-swizzled shared memory and hands it to the TMA unit:
-//     cp.async.bulk.tensor store (or cp.reduce ... .add for the accumulate mode that sums residual-branch
-//     gradients); out-of-range rows/columns of edge tiles are clipped by the TMA unit, there is no per-row
-//     address arithmetic at all;
-//   * BatchNorm partial statistics are computed from the staged tile with conflict-free swizzled reads
-//     (shifted single pass: sum(x-k), sum((x-k)^2) with k = the tile's first row).
+//   * the reduction dimension is padded by the TMA unit: a channel count that is a multiple of 4 but not of 32 gets
+//     ceil(Cin/32) k-blocks per tap and the out-of-range channels of the A box arrive as zeros (whatever the B box
+//     holds there is multiplied by zero);
+//   * epilogue: see above.
 // =====================================================================================================
 template <int BN, int STAGES>
 struct ConvTc2Smem {
@@ -305,7 +215,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.m_tiles * p.n_tiles;
-  const int cchunks = p.Cin / kBK;
+  const int cchunks = (p.Cin + kBK - 1) / kBK;
   const int num_kb = p.num_taps * cchunks;
 
   if (warp == 0 && lane == 0) {
@@ -392,8 +302,6 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
     const int q = warp & 3;          // TMEM lane quadrant
     const int r = q * 32 + lane;     // tile row owned by this thread
     const int e = threadIdx.x - 64;  // 0..127
-    const bool issuer = (e == 0);
-    const int w_l = r % p.bw, h_l = (r / p.bw) % p.bh, n_l = r / (p.bw * p.bh);
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -402,115 +310,27 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
       const int tw = m_tile % p.tiles_w;
       const int th = (m_tile / p.tiles_w) % p.tiles_h;
       const int tn = m_tile / (p.tiles_w * p.tiles_h);
-      const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
-      const int col_base = n_tile * BN;
-      const bool full_tile = (n0 + p.bn <= p.N) && (oh0 + p.bh <= p.OH) && (ow0 + p.bw <= p.OW);
+      EpiTile t;
+      t.n0 = tn * p.bn; t.oh0 = th * p.bh; t.ow0 = tw * p.bw;
+      t.obn = p.bn; t.obh = p.bh; t.obw = p.bw;
+      t.col_base = n_tile * BN;
+      t.stat_tile = m_tile; t.stat_tiles = p.m_tiles; t.write_count = (n_tile == 0);
+      t.full = (t.n0 + p.bn <= p.N) && (t.oh0 + p.bh <= p.OH) && (t.ow0 + p.bw <= p.OW);
 
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
-      if (issuer) tma_store_wait_read();  // the previous tile's stores no longer read the staging buffer
-      if (p.partials != nullptr && !full_tile)
-        row_valid[r] = ((n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW)) ? 1 : 0;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-
-      const uint32_t tmem_d = tmem_base + as * BN + (uint32_t(q * 32) << 16);
-#pragma unroll 1
-      for (int ch = 0; ch < S::kChunks; ++ch) {
-        if (col_base + ch * 32 >= p.Cout) break;
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
-        tmem_ld_wait();
-        uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float4 o;
-          o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
-          o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
-          if (p.bias != nullptr) {
-            const int c = col_base + ch * 32 + 4 * j;
-            if (c < p.Cout) {  // Cout % 4 == 0 on this path
-              const float4 b = ldg4(p.bias + c);
-              o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-            }
-          }
-          *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
-        }
-      }
+      epi_begin(p, t, row_valid, r, e == 0);
+      epi_drain<S::kChunks>(p, tmem_base + as * BN + (uint32_t(q * 32) << 16), staging, r, t.col_base);
       // accumulator fully read: hand the TMEM stage back to the MMA warp
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
       fence_proxy_async();
       asm volatile("bar.sync 1, 128;" ::: "memory");
-
-      if (issuer) {
-        for (int ch = 0; ch < S::kChunks; ++ch) {
-          const int c = col_base + ch * 32;
-          if (c >= p.Cout) break;
-          if (p.accumulate) tma_reduce_add_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
-          else tma_store_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
-        }
-        tma_store_commit();
-      }
-
-      if (p.partials != nullptr) {
-        // shifted single pass over this thread's (column, 32-row group)
-        const int cl = e & 31, rg = e >> 5;
-        int cnt = kBM;
-        if (!full_tile) {
-          cnt = 0;
-          for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
-        }
-        for (int ch = 0; ch < S::kChunks; ++ch) {
-          if (col_base + ch * 32 >= p.Cout) break;
-          const uint8_t* src = staging + ch * (kBM * 128);
-          const float kshift = *reinterpret_cast<const float*>(src + (((cl >> 2) ^ 0) << 4) + ((cl & 3) << 2));  // row 0
-          float s = 0.f, qq = 0.f;
-          if (full_tile) {
-#pragma unroll 8
-            for (int i = 0; i < 32; ++i) {
-              const int rr = rg * 32 + i;
-              const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
-                                                              ((cl & 3) << 2));
-              const float d = x - kshift;
-              s += d;
-              qq = fmaf(d, d, qq);
-            }
-          } else {
-            for (int i = 0; i < 32; ++i) {
-              const int rr = rg * 32 + i;
-              const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
-                                                              ((cl & 3) << 2));
-              const float d = row_valid[rr] ? x - kshift : 0.f;
-              s += d;
-              qq = fmaf(d, d, qq);
-            }
-          }
-          red[(0 * 4 + rg) * BN + ch * 32 + cl] = s;
-          red[(1 * 4 + rg) * BN + ch * 32 + cl] = qq;
-          if (rg == 0) red[(0 * 4 + 0) * BN + ch * 32 + cl] = s;  // (same value; keeps the compiler from hoisting)
-        }
-        asm volatile("bar.sync 2, 128;" ::: "memory");
-        for (int j = e; j < BN; j += 128) {
-          const int c = col_base + j;
-          if (c < p.Cout) {
-            const int ch = j >> 5, cl2 = j & 31;
-            const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) +
-                                                                 ((cl2 & 3) << 2));
-            const float s = red[(0 * 4 + 0) * BN + j] + red[(0 * 4 + 1) * BN + j] + red[(0 * 4 + 2) * BN + j] +
-                            red[(0 * 4 + 3) * BN + j];
-            const float qq = red[(1 * 4 + 0) * BN + j] + red[(1 * 4 + 1) * BN + j] + red[(1 * 4 + 2) * BN + j] +
-                             red[(1 * 4 + 3) * BN + j];
-            const float n = (float)cnt;
-            p.partials[((long long)m_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
-            p.partials[((long long)m_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
-          }
-        }
-        if (e == 0 && n_tile == 0) p.partials[(long long)p.m_tiles * 2 * p.Cout + m_tile] = (float)cnt;
-      }
+      epi_finish<S::kChunks>(p, &tmO, t, staging, red, row_valid, e);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
-    if (issuer) tma_store_wait_all();
+    if (e == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -578,7 +398,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int total_tiles = p.m_tiles * p.n_tiles;
-  const int cchunks = p.Cin / kBK;
+  const int cchunks = (p.Cin + kBK - 1) / kBK;
   const int num_kb = p.num_taps * cchunks;
   constexpr uint32_t kTmemCols = 4 * BN;  // 2 buffers x 2 halves (power of two: 256 or 512)
 
@@ -669,9 +489,6 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
     const int q = warp & 3;
     const int r = q * 32 + lane;     // row inside the half
     const int e = threadIdx.x - 64;  // 0..127
-    const bool issuer = (e == 0);
-    const int w_l = r % pp.obw, h_l = (r / pp.obw) % pp.obh, n_l = r / (pp.obw * pp.obh);
-    const int stat_tiles = 2 * p.m_tiles;
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -680,44 +497,21 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
       const int tw = m_tile % p.tiles_w;
       const int th = (m_tile / p.tiles_w) % p.tiles_h;
       const int tn = m_tile / (p.tiles_w * p.tiles_h);
-      const int col_base = n_tile * BN;
 
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
-        const int n0 = tn * p.bn + half * pp.hdn, oh0 = th * p.bh + half * pp.hdh, ow0 = tw * p.bw + half * pp.hdw;
-        const bool full_tile = (n0 + pp.obn <= p.N) && (oh0 + pp.obh <= p.OH) && (ow0 + pp.obw <= p.OW);
-        const int st = m_tile * 2 + half;  // statistics tile
+        EpiTile t;
+        t.n0 = tn * p.bn + half * pp.hdn; t.oh0 = th * p.bh + half * pp.hdh; t.ow0 = tw * p.bw + half * pp.hdw;
+        t.obn = pp.obn; t.obh = pp.obh; t.obw = pp.obw;
+        t.col_base = n_tile * BN;
+        t.stat_tile = m_tile * 2 + half; t.stat_tiles = 2 * p.m_tiles; t.write_count = (n_tile == 0);
+        t.full = (t.n0 + pp.obn <= p.N) && (t.oh0 + pp.obh <= p.OH) && (t.ow0 + pp.obw <= p.OW);
 
-        if (issuer) tma_store_wait_read();  // earlier stores no longer read the staging buffer
-        if (p.partials != nullptr && !full_tile)
-          row_valid[r] = ((n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW)) ? 1 : 0;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-
-        const uint32_t tmem_d = tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16);
-#pragma unroll 1
-        for (int ch = 0; ch < S::kChunks; ++ch) {
-          if (col_base + ch * 32 >= p.Cout) break;
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
-          tmem_ld_wait();
-          uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float4 o;
-            o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
-            o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
-            if (p.bias != nullptr) {
-              const int c = col_base + ch * 32 + 4 * j;
-              if (c < p.Cout) {
-                const float4 b = ldg4(p.bias + c);
-                o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-              }
-            }
-            *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
-          }
-        }
+        epi_begin(p, t, row_valid, r, e == 0);
+        epi_drain<S::kChunks>(p, tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16), staging, r,
+                              t.col_base);
         if (half == 1) {
           // both halves read: hand the accumulator buffer back to the MMA warp
           tc_fence_before();
@@ -726,74 +520,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
         }
         fence_proxy_async();
         asm volatile("bar.sync 1, 128;" ::: "memory");
-
-        if (issuer) {
-          for (int ch = 0; ch < S::kChunks; ++ch) {
-            const int c = col_base + ch * 32;
-            if (c >= p.Cout) break;
-            if (p.accumulate) tma_reduce_add_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
-            else tma_store_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
-          }
-          tma_store_commit();
-        }
-
-        if (p.partials != nullptr) {
-          const int cl = e & 31, rg = e >> 5;
-          int cnt = kBM;
-          if (!full_tile) {
-            cnt = 0;
-            for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
-          }
-          for (int ch = 0; ch < S::kChunks; ++ch) {
-            if (col_base + ch * 32 >= p.Cout) break;
-            const uint8_t* src = staging + ch * (kBM * 128);
-            const float kshift = *reinterpret_cast<const float*>(src + ((cl >> 2) << 4) + ((cl & 3) << 2));  // row 0
-            float s = 0.f, qq = 0.f;
-            if (full_tile) {
-#pragma unroll 8
-              for (int i = 0; i < 32; ++i) {
-                const int rr = rg * 32 + i;
-                const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
-                                                                ((cl & 3) << 2));
-                const float d = x - kshift;
-                s += d;
-                qq = fmaf(d, d, qq);
-              }
-            } else {
-              for (int i = 0; i < 32; ++i) {
-                const int rr = rg * 32 + i;
-                const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
-                                                                ((cl & 3) << 2));
-                const float d = row_valid[rr] ? x - kshift : 0.f;
-                s += d;
-                qq = fmaf(d, d, qq);
-              }
-            }
-            red[(0 * 4 + rg) * BN + ch * 32 + cl] = s;
-            red[(1 * 4 + rg) * BN + ch * 32 + cl] = qq;
-          }
-          asm volatile("bar.sync 2, 128;" ::: "memory");
-          for (int j = e; j < BN; j += 128) {
-            const int c = col_base + j;
-            if (c < p.Cout) {
-              const int ch = j >> 5, cl2 = j & 31;
-              const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) +
-                                                                   ((cl2 & 3) << 2));
-              const float s = red[(0 * 4 + 0) * BN + j] + red[(0 * 4 + 1) * BN + j] + red[(0 * 4 + 2) * BN + j] +
-                              red[(0 * 4 + 3) * BN + j];
-              const float qq = red[(1 * 4 + 0) * BN + j] + red[(1 * 4 + 1) * BN + j] + red[(1 * 4 + 2) * BN + j] +
-                               red[(1 * 4 + 3) * BN + j];
-              const float n = (float)cnt;
-              p.partials[((long long)st * 2 + 0) * p.Cout + c] = s + n * kshift;
-              p.partials[((long long)st * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
-            }
-          }
-          if (e == 0 && n_tile == 0) p.partials[(long long)stat_tiles * 2 * p.Cout + st] = (float)cnt;
-        }
+        epi_finish<S::kChunks>(p, &tmO, t, staging, red, row_valid, e);
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
-    if (issuer) tma_store_wait_all();
+    if (e == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -817,7 +548,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
 // arrive.expect_tx(bytes of both CTAs) + the peer producer's remote arrive; both producers' TMA loads count their
 // bytes on it.  The leader's MMA thread frees stage s in BOTH CTAs and signals the accumulator to BOTH epilogues
 // with multicast commits.  The epilogue warps of both CTAs (2 x 4) arrive on the leader's tmem_empty[a].
-// Opt-in (DCNN_CONV_2CTA=1): written after the last GPU minutes of its session; not yet run on hardware.
+// Validated on hardware (tests/test_gpu_ops.py::test_conv_tc5_cta_pairs); the autotuner (ops/cuda.py) picks it per
+// shape where it wins, DCNN_CONV_2CTA=1 forces it wherever it applies.
 // =====================================================================================================
 template <int STAGES>
 struct ConvTc5Smem {
@@ -860,7 +592,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
   const int m_pairs = (p.m_tiles + 1) >> 1;
   const int total_tiles = m_pairs * p.n_tiles;   // pair tiles
-  const int cchunks = p.Cin / kBK;
+  const int cchunks = (p.Cin + kBK - 1) / kBK;
   const int num_kb = p.num_taps * cchunks;
 
   if (warp == 0 && lane == 0) {
@@ -950,8 +682,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const int e = threadIdx.x - 64;
-    const bool issuer = (e == 0);
-    const int w_l = r % p.bw, h_l = (r / p.bw) % p.bh, n_l = r / (p.bw * p.bh);
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
@@ -961,45 +691,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       const int tw = m_tile % p.tiles_w;
       const int th = (m_tile / p.tiles_w) % p.tiles_h;
       const int tn = m_tile / (p.tiles_w * p.tiles_h);
-      const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
-      const bool full_tile = (n0 + p.bn <= p.N) && (oh0 + p.bh <= p.OH) && (ow0 + p.bw <= p.OW);
 
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
-        const int col_base = n_tile * BN + half * HC;
-        const bool cols_live = live && col_base < p.Cout;
-        if (issuer) tma_store_wait_read();
-        if (p.partials != nullptr && !full_tile)
-          row_valid[r] = ((n0 + n_l < p.N) && (oh0 + h_l < p.OH) && (ow0 + w_l < p.OW)) ? 1 : 0;
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        EpiTile t;
+        t.n0 = tn * p.bn; t.oh0 = th * p.bh; t.ow0 = tw * p.bw;
+        t.obn = p.bn; t.obh = p.bh; t.obw = p.bw;
+        t.col_base = n_tile * BN + half * HC;
+        t.stat_tile = m_tile; t.stat_tiles = p.m_tiles; t.write_count = (n_tile == 0 && half == 0);
+        t.full = (t.n0 + p.bn <= p.N) && (t.oh0 + p.bh <= p.OH) && (t.ow0 + p.bw <= p.OW);
+        const bool cols_live = live && t.col_base < p.Cout;
 
-        const uint32_t tmem_d = tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16);
-        if (cols_live) {
-#pragma unroll 1
-          for (int ch = 0; ch < S::kChunks; ++ch) {
-            if (col_base + ch * 32 >= p.Cout) break;
-            uint32_t v[32];
-            tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
-            tmem_ld_wait();
-            uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              float4 o;
-              o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
-              o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
-              if (p.bias != nullptr) {
-                const int c = col_base + ch * 32 + 4 * j;
-                if (c < p.Cout) {
-                  const float4 b = ldg4(p.bias + c);
-                  o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
-                }
-              }
-              *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
-            }
-          }
-        }
+        epi_begin(p, t, row_valid, r, e == 0);
+        if (cols_live)
+          epi_drain<S::kChunks>(p, tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16), staging, r, t.col_base);
         if (half == 1) {
           // accumulator fully read by this warp: tell the leader's MMA thread (one arrival per epilogue warp per CTA)
           tc_fence_before();
@@ -1008,63 +715,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         }
         fence_proxy_async();
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (!cols_live) continue;
-
-        if (issuer) {
-          for (int ch = 0; ch < S::kChunks; ++ch) {
-            const int c = col_base + ch * 32;
-            if (c >= p.Cout) break;
-            if (p.accumulate) tma_reduce_add_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
-            else tma_store_4d(&tmO, staging + ch * (kBM * 128), c, ow0, oh0, n0);
-          }
-          tma_store_commit();
-        }
-
-        if (p.partials != nullptr) {
-          const int cl = e & 31, rg = e >> 5;
-          int cnt = kBM;
-          if (!full_tile) {
-            cnt = 0;
-            for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
-          }
-          for (int ch = 0; ch < S::kChunks; ++ch) {
-            if (col_base + ch * 32 >= p.Cout) break;
-            const uint8_t* src = staging + ch * (kBM * 128);
-            const float kshift = *reinterpret_cast<const float*>(src + ((cl >> 2) << 4) + ((cl & 3) << 2));  // row 0
-            float s = 0.f, qq = 0.f;
-            for (int i = 0; i < 32; ++i) {
-              const int rr = rg * 32 + i;
-              const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) +
-                                                              ((cl & 3) << 2));
-              const float d = (full_tile || row_valid[rr]) ? x - kshift : 0.f;
-              s += d;
-              qq = fmaf(d, d, qq);
-            }
-            red[(0 * 4 + rg) * HC + ch * 32 + cl] = s;
-            red[(1 * 4 + rg) * HC + ch * 32 + cl] = qq;
-          }
-          asm volatile("bar.sync 2, 128;" ::: "memory");
-          for (int j = e; j < HC; j += 128) {
-            const int c = col_base + j;
-            if (c < p.Cout) {
-              const int ch = j >> 5, cl2 = j & 31;
-              const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) +
-                                                                   ((cl2 & 3) << 2));
-              const float s = red[(0 * 4 + 0) * HC + j] + red[(0 * 4 + 1) * HC + j] + red[(0 * 4 + 2) * HC + j] +
-                              red[(0 * 4 + 3) * HC + j];
-              const float qq = red[(1 * 4 + 0) * HC + j] + red[(1 * 4 + 1) * HC + j] + red[(1 * 4 + 2) * HC + j] +
-                               red[(1 * 4 + 3) * HC + j];
-              const float n = (float)cnt;
-              p.partials[((long long)m_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
-              p.partials[((long long)m_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
-            }
-          }
-          if (e == 0 && n_tile == 0 && half == 0) p.partials[(long long)p.m_tiles * 2 * p.Cout + m_tile] = (float)cnt;
-        }
+        if (cols_live) epi_finish<S::kChunks>(p, &tmO, t, staging, red, row_valid, e);
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
-    if (issuer) tma_store_wait_all();
+    if (e == 0) tma_store_wait_all();
   }
 
   // both CTAs are done with each other's barriers, shared memory and the paired tensor memory
@@ -1391,8 +1046,7 @@ static bool conv_2cta_applies(int N, int OH, int OW, int mul_h, int mul_w, int C
 // conv_tc3 is used unless it is switched off (DCNN_CONV_V3=0), when the vectorised epilogue applies (Cout % 4 == 0) and the
 // loop space has at least one 256-pixel tile per SM; smaller problems keep the 128-pixel tiles of conv_tc2.
 static bool conv_v3_enabled() {
-  static const bool on = !(getenv("DCNN_CONV_V3") != nullptr && atoi(getenv("DCNN_CONV_V3")) == 0) &&
-                         !(getenv("DCNN_CONV_V1") != nullptr && atoi(getenv("DCNN_CONV_V1")) != 0);
+  static const bool on = !(getenv("DCNN_CONV_V3") != nullptr && atoi(getenv("DCNN_CONV_V3")) == 0);
   return on;
 }
 static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int* bn, int* bh, int* bw) {
@@ -1403,17 +1057,6 @@ static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cou
   if (g_conv_variant == 3) return true;
   const long long m_tiles = (long long)ceil_div(OW, *bw) * ceil_div(OH, *bh) * ceil_div(N, *bn);
   return m_tiles >= num_sms();
-}
-
-template <int BN, int STAGES>
-static int launch_conv(const CUtensorMap& tmA, const CUtensorMap& tmB, const ConvTcParams& p, cudaStream_t stream) {
-  using S = ConvTcSmem<BN, STAGES>;
-  DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, conv_tc_kernel<BN, STAGES>);
-  dim3 grid((unsigned)((long long)p.m_tiles * p.n_tiles));
-  conv_tc_kernel<BN, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmA, tmB, p);
-  DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(1);
-  return 0;
 }
 
 template <int BNW, int STAGES>
@@ -1457,14 +1100,15 @@ DCNN_API int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w
   return dcnn_conv_tc_m_tiles(N, OH, OW, mul_h, mul_w);
 }
 
-// Generic tap-list implicit GEMM (see file header).  x: NHWC [N][H][W][Cin] (Cin % 32 == 0),
-// w: [Cout][Ktot] with K index = tap_w*Cin + c.  Output pixel (n,oh,ow), channel oc is written to
+// Generic tap-list implicit GEMM (see file header).  x: NHWC [N][H][W][Cin] (Cin % 4 == 0: the TMA unit pads each tap's
+// channel run to a multiple of 32 with zeros), Cout % 4 == 0, w: [Cout][Ktot] with K index = tap_w*Cin + c.  Output pixel (n,oh,ow), channel oc is written to
 // out[n*out_sn + oh*out_sh + ow*out_sw + oc].
 DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
                           long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h,
                           int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w,
                           const float* bias, int accumulate, float* partials, cudaStream_t stream) {
-  DCNN_REQUIRE(Cin % kBK == 0, "dcnn_conv_tc: Cin (%d) must be a multiple of 32", Cin);
+  DCNN_REQUIRE(Cin % 4 == 0 && Ktot % 4 == 0, "dcnn_conv_tc: Cin (%d) and Ktot (%d) must be multiples of 4", Cin, Ktot);
+  DCNN_REQUIRE(Cout % 4 == 0, "dcnn_conv_tc: Cout (%d) must be a multiple of 4 (TMA store rows are 16-byte aligned)", Cout);
   DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_conv_tc: bad tap count %d", num_taps);
   DCNN_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0,
                "dcnn_conv_tc: operands must be 16-byte aligned");
@@ -1482,15 +1126,13 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   for (int t = 0; t < num_taps; ++t) {
     p.tap_dh[t] = (int16_t)tap_dh[t]; p.tap_dw[t] = (int16_t)tap_dw[t]; p.tap_w[t] = (int16_t)tap_w[t];
   }
-  const bool vec_ok = (Cout & 3) == 0;
-  DCNN_REQUIRE(!vec_ok || ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (out_sn & 3) == 0 && (out_sh & 3) == 0 &&
-                           (out_sw & 3) == 0),
+  DCNN_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (out_sn & 3) == 0 && (out_sh & 3) == 0 &&
+                   (out_sw & 3) == 0,
                "dcnn_conv_tc: output must be 16-byte aligned with strides multiple of 4");
   CUtensorMap tmA, tmB;
   int rc = make_tmap_nhwc(&tmA, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
   if (rc) return rc;
-  static const bool use_v1 = getenv("DCNN_CONV_V1") != nullptr && atoi(getenv("DCNN_CONV_V1")) != 0;
-  if (vec_ok && conv_2cta_applies(N, OH, OW, in_mul_h, in_mul_w, Cout)) {
+  if (conv_2cta_applies(N, OH, OW, in_mul_h, in_mul_w, Cout)) {
     CUtensorMap tmO5;
     rc = make_tmap_out(&tmO5, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);
     if (rc) return rc;
@@ -1501,7 +1143,7 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   }
   {
     int bn3, bh3, bw3;
-    if (vec_ok && conv_v3_applies(N, OH, OW, in_mul_h, in_mul_w, Cout, &bn3, &bh3, &bw3)) {
+    if (conv_v3_applies(N, OH, OW, in_mul_h, in_mul_w, Cout, &bn3, &bh3, &bw3)) {
       ConvTc3Params q;
       q.b = p;
       q.b.bn = bn3; q.b.bh = bh3; q.b.bw = bw3;
@@ -1530,40 +1172,28 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
       return launch_conv3<128, 3>(tmA3, tmB, tmO3, q, stream);
     }
   }
-  if (vec_ok && !use_v1) {
-    // persistent kernel, TMA-store epilogue
-    CUtensorMap tmO;
-    rc = make_tmap_out(&tmO, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);
-    if (rc) return rc;
-    if (Cout <= 64) {
-      p.n_tiles = 1;
-      rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
-      if (rc) return rc;
-      return launch_conv2<64, 6>(tmA, tmB, tmO, p, stream);
-    }
-    p.n_tiles = ceil_div(Cout, 128);
-    rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
-    if (rc) return rc;
-    return launch_conv2<128, 4>(tmA, tmB, tmO, p, stream);
-  }
+  CUtensorMap tmO;
+  rc = make_tmap_out(&tmO, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);
+  if (rc) return rc;
   if (Cout <= 64) {
-    p.n_tiles = ceil_div(Cout, 64);
+    p.n_tiles = 1;
     rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
     if (rc) return rc;
-    return launch_conv<64, 4>(tmA, tmB, p, stream);
+    return launch_conv2<64, 6>(tmA, tmB, tmO, p, stream);
   }
   p.n_tiles = ceil_div(Cout, 128);
   rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
   if (rc) return rc;
-  return launch_conv<128, 3>(tmA, tmB, p, stream);
+  return launch_conv2<128, 4>(tmA, tmB, tmO, p, stream);
 }
 
 // dW[oc][tap_w*Cin + c] += sum_{n,oh,ow} dY[n,oh,ow,oc] * X[n, oh*mul_h + tap_dh, ow*mul_w + tap_dw, c]
-// dy: NHWC [N][OH][OW][Cout]; x: NHWC [N][H][W][Cin] (Cin % 32 == 0, Cout % 4 == 0).
+// dy: NHWC [N][OH][OW][Cout]; x: NHWC [N][H][W][Cin] (Cin % 4 == 0, Cout % 4 == 0; channel counts that are not
+// multiples of 32 are padded with zeros by the TMA unit, the write-back is guarded).
 DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin,
                            float* dw, int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh,
                            const int* tap_dw, const int* tap_w, cudaStream_t stream) {
-  DCNN_REQUIRE(Cin % 32 == 0, "dcnn_wgrad_tc: Cin (%d) must be a multiple of 32", Cin);
+  DCNN_REQUIRE(Cin % 4 == 0, "dcnn_wgrad_tc: Cin (%d) must be a multiple of 4", Cin);
   DCNN_REQUIRE(Cout % 4 == 0, "dcnn_wgrad_tc: Cout (%d) must be a multiple of 4", Cout);
   DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_wgrad_tc: bad tap count %d", num_taps);
   WgradTcParams p;
@@ -1579,20 +1209,21 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   }
   p.oc_tiles = ceil_div(Cout, 128);
   const bool wide = Cin >= 128;
-  // N = 256 tiles (128 oc x 256 c): 42.7 instead of 32 FLOP per operand byte on the L2-feed-bound mainloop (same
-  // argument as conv_tc3).  Two 96 KB stages.  Opt-in (DCNN_WGRAD_N256=1) until it has had its hardware run.
-  const char* n256_env = getenv("DCNN_WGRAD_N256");
-  const bool n256 = n256_env != nullptr && atoi(n256_env) != 0 && Cin % 256 == 0;
-  const int bnw = n256 ? 256 : (wide ? 128 : 64);
+  // (128 x 256 tiles were tried -- 42.7 instead of 32 FLOP per operand byte, two 96 KB stages -- and measured no faster
+  // than 128 x 128 with three stages on the ResNet-50 step: profiles/05.)
+  const int bnw = wide ? 128 : 64;
   CUtensorMapSwizzle wgrad_swizzle = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
   {
     // MN-major TF32 operands must use the 128B-swizzle-with-32B-atoms layout (TMA: SWIZZLE_128B_ATOM_32B, UMMA
     // layout type 1): rows of 128 B (32 elements along M/N), 32-byte chunks XOR-ed with (row % 4).  LBO = byte distance
     // between 32-element MN chunks (one TMA box), SBO = byte distance between 4-row K groups, one K=8 MMA = 1024 B.
-    uint32_t lbo = kWPix * 128, sbo = 512, a_mn = 1, b_mn = 1, kstep = 1024, layout = 1, swz = 4;
+    uint32_t lbo = kWPix * 128, sbo = 512, a_mn = 1, b_mn = 1, kstep = 1024, layout = 1;
+#ifdef DCNN_DEBUG   // layout experiments without a rebuild (scripts/dbg_wgrad.py): never in release builds
+    uint32_t swz = 4;
     if (const char* dbg = getenv("DCNN_WGRAD_DBG"))
       sscanf(dbg, "%u,%u,%u,%u,%u,%u,%u", &lbo, &sbo, &a_mn, &b_mn, &kstep, &layout, &swz);
     wgrad_swizzle = (CUtensorMapSwizzle)swz;
+#endif
     p.desc_hi_a = make_smem_desc_hi(lbo, sbo, layout);
     p.desc_hi_b = make_smem_desc_hi(lbo, sbo, layout);
     p.idesc = make_idesc_tf32(128, bnw, a_mn, b_mn);
@@ -1613,7 +1244,6 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   if (rc) return rc;
   rc = make_tmap_nhwc(&tmX, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w, wgrad_swizzle);
   if (rc) return rc;
-  if (n256) return launch_wgrad<256, 2>(tmDY, tmX, p, stream);
   if (wide) return launch_wgrad<128, 3>(tmDY, tmX, p, stream);
   return launch_wgrad<64, 4>(tmDY, tmX, p, stream);
 }

@@ -7,6 +7,8 @@
 // reference's Welford kernel, batchnorm_ops.cu:108-155), updates the running statistics (unbiased variance,
 // momentum) and precomputes scale/shift so the apply pass is one FMA per element with ReLU / residual fused.
 // Backward = one reduce pass (ReLU mask folded in) + finalize + one apply pass (dx = g*k1 + x*k2 + k3).
+#include <atomic>
+
 #include "peer.cuh"
 
 namespace dcnn {
@@ -84,6 +86,60 @@ __device__ __forceinline__ Moments merge(Moments a, Moments b) {
   return r;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// One-launch cross-replica exchange for sync-BatchNorm (K27; the reference has neither data parallelism nor a
+// cross-replica BatchNorm).  Every replica owns an exchange area per BatchNorm layer and direction, mapped by all peers:
+//     double data[2 parities][world sources][3][C]  |  u64 flags[ceil(C/8)][kMaxPeers]  |  u64 counter[ceil(C/8)]
+// Warp 0 of a finalize CTA (channel group g = blockIdx.x) PUSHES its three per-channel values into slot [source =
+// this rank] of every replica (plain stores through the NVLink peer mappings), fences, and raises flag [g][rank] in every
+// replica to this call's epoch (st.release.sys).  It then spins on ITS OWN flags [g][*] -- local memory, no NVLink
+// polling -- until every source has reached the epoch, and merges the sources in rank order from local memory, so all
+// replicas compute bit-identical statistics.  The epoch is a device-resident per-(layer, direction, group) call counter
+// kept next to the flags: no host bookkeeping, no separate counter kernel, replayable from a CUDA graph.  Two data
+// parities are enough: a replica can only be one call ahead of the slowest one (it needs that replica's flag of call e
+// to finish call e, and that replica raised it after it had finished reading call e-1).  (This needs a layer's calls
+// to alternate parity per channel group, so one layer must always use the same finalize kernel variant: the host side
+// picks the variant for sync calls from the process-wide switch alone, never from the tile count.)
+struct BnSyncArgs {
+  unsigned char* area[kMaxPeers];  // replica r's exchange area of this layer and direction, as mapped here
+  int rank, world;                 // world <= 1: no exchange
+};
+
+__host__ __device__ inline size_t bn_sync_data_bytes(int world, int C) { return (size_t)2 * world * 3 * C * sizeof(double); }
+
+// Returns this call's local slot: value k of channel c from source r is at ret[(r * 3 + k) * C + c].
+// To be called by all 32 lanes of warp 0; `has` marks the lanes that own channel `c`.
+__device__ __forceinline__ const volatile double* bn_sync_exchange(const BnSyncArgs& s, int lane, int C, int c, bool has,
+                                                                   double v0, double v1, double v2) {
+  const int g = blockIdx.x, G = (C + 7) / 8;   // layout for the finest channel grouping (the narrow kernels')
+  const size_t data_bytes = bn_sync_data_bytes(s.world, C);
+  unsigned char* mine = s.area[s.rank];
+  unsigned long long* my_flags = reinterpret_cast<unsigned long long*>(mine + data_bytes) + (size_t)g * kMaxPeers;
+  unsigned long long* ctr = reinterpret_cast<unsigned long long*>(mine + data_bytes) + (size_t)G * kMaxPeers + g;
+  const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(ctr) + 1;
+  const size_t parity_off = (size_t)(epoch & 1) * s.world * 3 * C;
+  if (has) {
+    for (int r = 0; r < s.world; ++r) {
+      double* d = reinterpret_cast<double*>(s.area[r]) + parity_off + (size_t)s.rank * 3 * C;
+      d[c] = v0;
+      d[C + c] = v1;
+      d[2 * C + c] = v2;
+    }
+  }
+  __threadfence_system();
+  __syncwarp();
+  if (lane < s.world) {
+    st_release_sys(reinterpret_cast<unsigned long long*>(s.area[lane] + data_bytes) + (size_t)g * kMaxPeers + s.rank, epoch);
+    unsigned long long spins = 0;
+    while (ld_acquire_sys(my_flags + lane) < epoch) {
+      if (++spins > (1ull << 31)) __trap();  // a lost replica must not hang the GPU forever
+    }
+  }
+  __syncwarp();
+  if (lane == 0) *ctr = epoch;
+  return reinterpret_cast<const volatile double*>(mine) + parity_off;
+}
+
 // grid: ceil(C/32); block (32 channels, 32 tile lanes).
 // peers: optional cross-replica merge (sync-BN, K27): peer_moments[r] points at replica r's exported
 // (n, mean, m2)[C] triple array (double), readable over NVLink peer mapping; n_peers == 0 => local only.
@@ -94,7 +150,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
                                                            const float* __restrict__ beta, float* __restrict__ mean_out,
                                                            float* __restrict__ invstd_out, float* __restrict__ scale_out,
                                                            float* __restrict__ shift_out,
-                                                           double* __restrict__ export_moments) {
+                                                           const BnSyncArgs sync) {
   __shared__ double s_n[32][33], s_s[32][33], s_q[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   // Per tile we have (n, sum, M2 about the tile mean).  sum(x^2) of the tile = M2 + sum^2/n, so three plain FP64
@@ -118,18 +174,22 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
   s_s[threadIdx.y][threadIdx.x] = as;
   s_q[threadIdx.y][threadIdx.x] = aq;
   __syncthreads();
-  if (threadIdx.y == 0 && c < C) {
-    for (int i = 1; i < 32; ++i) {
-      an += s_n[i][threadIdx.x]; as += s_s[i][threadIdx.x]; aq += s_q[i][threadIdx.x];
+  if (threadIdx.y != 0) return;   // warp 0 finishes
+  const bool has = c < C;
+  for (int i = 1; i < 32; ++i) {
+    an += s_n[i][threadIdx.x]; as += s_s[i][threadIdx.x]; aq += s_q[i][threadIdx.x];
+  }
+  Moments acc{an, an > 0 ? as / an : 0.0, 0.0};
+  acc.m2 = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
+  if (sync.world > 1) {
+    const volatile double* d = bn_sync_exchange(sync, threadIdx.x, C, c, has, acc.n, acc.mean, acc.m2);
+    if (has) {
+      acc = Moments{0, 0, 0};
+      for (int r = 0; r < sync.world; ++r)
+        acc = merge(acc, Moments{d[(r * 3 + 0) * C + c], d[(r * 3 + 1) * C + c], d[(r * 3 + 2) * C + c]});
     }
-    Moments acc{an, an > 0 ? as / an : 0.0, 0.0};
-    acc.m2 = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
-    if (export_moments != nullptr) {
-      export_moments[0 * C + c] = acc.n;
-      export_moments[1 * C + c] = acc.mean;
-      export_moments[2 * C + c] = acc.m2;
-      return;  // the sync variant finishes in bn_finalize_sync_kernel after the peer exchange
-    }
+  }
+  if (has) {
     const double var = acc.n > 0 ? acc.m2 / acc.n : 0.0;  // biased: used to normalise
     const float invstd = (float)(1.0 / sqrt(var + (double)eps));
     const float mean = (float)acc.mean;
@@ -148,7 +208,8 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
 
 // Narrow variants of the two finalize kernels: 8 channels x 128 tile lanes per CTA, i.e. 4x as many CTAs.  The wide
 // kernels put a 4 MB partials array (2048 tiles x 256 channels) on 8 SMs and take ~12 us; the work is the same, only
-// the mapping changes.  32-byte row segments keep every DRAM sector fully used.  Opt-in: DCNN_BN_FINALIZE_NARROW=1.
+// the mapping changes.  32-byte row segments keep every DRAM sector fully used.  Used for >= 256 tiles
+// (DCNN_BN_FINALIZE_NARROW=0 switches them off).
 __global__ void __launch_bounds__(1024) bn_finalize_narrow_kernel(const float* __restrict__ partials, int tiles, int C,
                                                                   float eps, float momentum,
                                                                   float* __restrict__ running_mean,
@@ -159,7 +220,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_narrow_kernel(const float* _
                                                                   float* __restrict__ invstd_out,
                                                                   float* __restrict__ scale_out,
                                                                   float* __restrict__ shift_out,
-                                                                  double* __restrict__ export_moments) {
+                                                                  const BnSyncArgs sync) {
   __shared__ double s_n[128][9], s_s[128][9], s_q[128][9];
   const int c = blockIdx.x * 8 + threadIdx.x;
   double an = 0, as = 0, aq = 0;
@@ -180,18 +241,25 @@ __global__ void __launch_bounds__(1024) bn_finalize_narrow_kernel(const float* _
   s_s[threadIdx.y][threadIdx.x] = as;
   s_q[threadIdx.y][threadIdx.x] = aq;
   __syncthreads();
-  if (threadIdx.y == 0 && c < C) {
+  if (threadIdx.y >= 4) return;   // warp 0 (4 rows of 8 threads) finishes; row 0 owns the channels
+  const bool has = threadIdx.y == 0 && c < C;
+  if (has) {
     for (int i = 1; i < 128; ++i) {
       an += s_n[i][threadIdx.x]; as += s_s[i][threadIdx.x]; aq += s_q[i][threadIdx.x];
     }
-    const double mean_d = an > 0 ? as / an : 0.0;
-    const double m2_d = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
-    if (export_moments != nullptr) {
-      export_moments[0 * C + c] = an;
-      export_moments[1 * C + c] = mean_d;
-      export_moments[2 * C + c] = m2_d;
-      return;
+  }
+  double mean_d = an > 0 ? as / an : 0.0;
+  double m2_d = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
+  if (sync.world > 1) {
+    const volatile double* d = bn_sync_exchange(sync, threadIdx.y * 8 + threadIdx.x, C, c, has, an, mean_d, m2_d);
+    if (has) {
+      Moments acc{0, 0, 0};
+      for (int r = 0; r < sync.world; ++r)
+        acc = merge(acc, Moments{d[(r * 3 + 0) * C + c], d[(r * 3 + 1) * C + c], d[(r * 3 + 2) * C + c]});
+      an = acc.n; mean_d = acc.mean; m2_d = acc.m2;
     }
+  }
+  if (has) {
     const double var = an > 0 ? m2_d / an : 0.0;
     const float invstd = (float)(1.0 / sqrt(var + (double)eps));
     const float mean = (float)mean_d;
@@ -216,7 +284,7 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_narrow_kernel(const floa
                                                                       float* __restrict__ dgamma,
                                                                       float* __restrict__ dbeta, float* __restrict__ k1,
                                                                       float* __restrict__ k2, float* __restrict__ k3,
-                                                                      double* __restrict__ export_sums) {
+                                                                      const BnSyncArgs sync) {
   __shared__ double s_a[128][9], s_b[128][9];
   const int c = blockIdx.x * 8 + threadIdx.x;
   double a = 0, b = 0;
@@ -230,61 +298,30 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_narrow_kernel(const floa
   s_a[threadIdx.y][threadIdx.x] = a;
   s_b[threadIdx.y][threadIdx.x] = b;
   __syncthreads();
-  if (threadIdx.y == 0 && c < C) {
+  if (threadIdx.y >= 4) return;   // warp 0 finishes; row 0 owns the channels
+  const bool has = threadIdx.y == 0 && c < C;
+  if (has) {
     for (int i = 1; i < 128; ++i) { a += s_a[i][threadIdx.x]; b += s_b[i][threadIdx.x]; }
     if (dgamma != nullptr) {
       dgamma[c] += (float)b;
       dbeta[c] += (float)a;
     }
-    if (export_sums != nullptr) {
-      export_sums[0 * C + c] = a;
-      export_sums[1 * C + c] = b;
-      export_sums[2 * C + c] = count;
-      return;
+  }
+  if (sync.world > 1) {
+    const volatile double* d = bn_sync_exchange(sync, threadIdx.y * 8 + threadIdx.x, C, c, has, a, b, count);
+    if (has) {
+      a = b = count = 0;
+      for (int r = 0; r < sync.world; ++r) {
+        a += d[(r * 3 + 0) * C + c]; b += d[(r * 3 + 1) * C + c]; count += d[(r * 3 + 2) * C + c];
+      }
     }
+  }
+  if (has) {
     const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
     const float ma = (float)(a / count), mb = (float)(b / count);
     k1[c] = sc;
     k2[c] = -invstd[c] * mb * sc;
     k3[c] = (mean[c] * invstd[c] * mb - ma) * sc;
-  }
-}
-
-// Cross-replica finish (sync-BN, K27), fused with the rendezvous: block 0 publishes "my moments are exported" to every
-// replica (st.release.sys), every block waits until all replicas have published this epoch (ld.acquire.sys), then each
-// thread merges its channel's (n, mean, M2) from every replica's symmetric buffer over NVLink peer loads.
-__global__ void bn_finalize_sync_kernel(PeerPtrs peer_moments, PeerFlags flags, int rank,
-                                        const unsigned long long* epoch_ptr, int n_peers, int C, float eps,
-                                        float momentum, float* __restrict__ running_mean,
-                                        float* __restrict__ running_var, const float* __restrict__ gamma,
-                                        const float* __restrict__ beta, float* __restrict__ mean_out,
-                                        float* __restrict__ invstd_out, float* __restrict__ scale_out,
-                                        float* __restrict__ shift_out) {
-  if (threadIdx.x == 0) {
-    const unsigned long long epoch = *epoch_ptr;
-    if (blockIdx.x == 0) peer_signal(flags, rank, n_peers, epoch);
-    peer_wait(flags, rank, n_peers, epoch);
-  }
-  __syncthreads();
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  Moments acc{0, 0, 0};
-  for (int r = 0; r < n_peers; ++r) {
-    const volatile double* pm = peer_moments.p[r];  // volatile: never served from a stale L1 line
-    acc = merge(acc, Moments{pm[0 * C + c], pm[1 * C + c], pm[2 * C + c]});
-  }
-  const double var = acc.n > 0 ? acc.m2 / acc.n : 0.0;
-  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
-  const float mean = (float)acc.mean;
-  mean_out[c] = mean;
-  invstd_out[c] = invstd;
-  const float sc = gamma ? gamma[c] * invstd : invstd;
-  scale_out[c] = sc;
-  shift_out[c] = (beta ? beta[c] : 0.f) - mean * sc;
-  if (running_mean != nullptr) {
-    const double unbiased = acc.n > 1 ? acc.m2 / (acc.n - 1) : var;
-    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
-    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
   }
 }
 
@@ -427,7 +464,7 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                                float* __restrict__ k1, float* __restrict__ k2,
                                                                float* __restrict__ k3,
-                                                               double* __restrict__ export_sums) {
+                                                               const BnSyncArgs sync) {
   __shared__ double s_a[32][33], s_b[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   double a = 0, b = 0;
@@ -441,18 +478,23 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
   s_a[threadIdx.y][threadIdx.x] = a;
   s_b[threadIdx.y][threadIdx.x] = b;
   __syncthreads();
-  if (threadIdx.y == 0 && c < C) {
-    for (int i = 1; i < 32; ++i) { a += s_a[i][threadIdx.x]; b += s_b[i][threadIdx.x]; }
-    if (dgamma != nullptr) {  // local contribution; the DP all-reduce sums replicas
-      dgamma[c] += (float)b;
-      dbeta[c] += (float)a;
+  if (threadIdx.y != 0) return;   // warp 0 finishes
+  const bool has = c < C;
+  for (int i = 1; i < 32; ++i) { a += s_a[i][threadIdx.x]; b += s_b[i][threadIdx.x]; }
+  if (has && dgamma != nullptr) {  // local contribution; the DP all-reduce sums replicas
+    dgamma[c] += (float)b;
+    dbeta[c] += (float)a;
+  }
+  if (sync.world > 1) {
+    const volatile double* d = bn_sync_exchange(sync, threadIdx.x, C, c, has, a, b, count);
+    if (has) {
+      a = b = count = 0;
+      for (int r = 0; r < sync.world; ++r) {
+        a += d[(r * 3 + 0) * C + c]; b += d[(r * 3 + 1) * C + c]; count += d[(r * 3 + 2) * C + c];
+      }
     }
-    if (export_sums != nullptr) {
-      export_sums[0 * C + c] = a;
-      export_sums[1 * C + c] = b;
-      export_sums[2 * C + c] = count;
-      return;
-    }
+  }
+  if (has) {
     const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
     const float ma = (float)(a / count), mb = (float)(b / count);
     // dx = (g - ma - xhat*mb) * sc,  xhat = (x - mean)*invstd
@@ -460,31 +502,6 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
     k2[c] = -invstd[c] * mb * sc;
     k3[c] = (mean[c] * invstd[c] * mb - ma) * sc;
   }
-}
-
-__global__ void bn_bwd_finalize_sync_kernel(PeerPtrs peer_sums, PeerFlags flags, int rank,
-                                            const unsigned long long* epoch_ptr, int n_peers, int C,
-                                            const float* __restrict__ mean, const float* __restrict__ invstd,
-                                            const float* __restrict__ gamma, float* __restrict__ k1,
-                                            float* __restrict__ k2, float* __restrict__ k3) {
-  if (threadIdx.x == 0) {
-    const unsigned long long epoch = *epoch_ptr;
-    if (blockIdx.x == 0) peer_signal(flags, rank, n_peers, epoch);
-    peer_wait(flags, rank, n_peers, epoch);
-  }
-  __syncthreads();
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double a = 0, b = 0, n = 0;
-  for (int r = 0; r < n_peers; ++r) {
-    const volatile double* p = peer_sums.p[r];
-    a += p[0 * C + c]; b += p[1 * C + c]; n += p[2 * C + c];
-  }
-  const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
-  const float ma = (float)(a / n), mb = (float)(b / n);
-  k1[c] = sc;
-  k2[c] = -invstd[c] * mb * sc;
-  k3[c] = (mean[c] * invstd[c] * mb - ma) * sc;
 }
 
 // dx = g*k1 + x*k2 + k3 with g = dout masked by (out > 0); optionally also writes the masked g (the gradient
@@ -704,18 +721,18 @@ DCNN_API int dcnn_bn_colstats(const float* x, long long M, int C, float* partial
 
 // read per call (cheap) so that a test can toggle it
 static bool finalize_narrow() {
-  const char* e = getenv("DCNN_BN_FINALIZE_NARROW");
-  return e != nullptr && atoi(e) != 0;
+  const char* e = getenv("DCNN_BN_FINALIZE_NARROW");   // default on (-0.34 ms per ResNet-50 step, profiles/05); 0 = wide only
+  return e == nullptr || atoi(e) != 0;
 }
 
 DCNN_API int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
                               float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
-                              float* scale, float* shift, double* export_moments, cudaStream_t stream) {
+                              float* scale, float* shift, cudaStream_t stream) {
   if (finalize_narrow() && tiles >= 256) {
     dim3 nblock(8, 128);
     bn_finalize_narrow_kernel<<<ceil_div(C, 8), nblock, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
                                                                     running_var, gamma, beta, mean, invstd, scale,
-                                                                    shift, export_moments);
+                                                                    shift, BnSyncArgs{});
     DCNN_CHECK_LAUNCH();
     DCNN_COUNT_LAUNCH(1);
     return 0;
@@ -723,38 +740,77 @@ DCNN_API int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps
   dim3 block(32, 32);
   bn_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
                                                            running_var, gamma, beta, mean, invstd, scale, shift,
-                                                           export_moments);
+                                                           BnSyncArgs{});
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(1);
   return 0;
 }
 
-static int fill_peers(PeerPtrs* pp, PeerFlags* pf, const double* const* ptrs, unsigned long long* const* flag_ptrs,
-                      int n_peers) {
-  DCNN_REQUIRE(n_peers >= 1 && n_peers <= kMaxPeers, "sync-BN: %d replicas out of range (max %d)", n_peers, kMaxPeers);
-  for (int r = 0; r < kMaxPeers; ++r) {
-    pp->p[r] = r < n_peers ? ptrs[r] : nullptr;
-    pf->flags[r] = r < n_peers ? flag_ptrs[r] : nullptr;
-  }
+// ---- one-launch sync-BatchNorm (see bn_sync_exchange): the finalize kernel itself exchanges the per-channel values.
+// areas[r]: replica r's exchange area for this layer and direction as mapped in THIS process (host array of `world`
+// device pointers); each area holds dcnn_bn_sync_area_bytes(world, C) bytes, zero-initialised once.
+DCNN_API long long dcnn_bn_sync_area_bytes(int world, int C) {
+  const long long g = (C + 7) / 8;
+  const long long b = (long long)bn_sync_data_bytes(world, C) + g * kMaxPeers * 8 + g * 8;
+  return (b + 255) / 256 * 256;
+}
+
+static int fill_sync(BnSyncArgs* sa, unsigned char* const* areas, int rank, int world) {
+  DCNN_REQUIRE(world >= 2 && world <= kMaxPeers, "sync-BN: %d replicas out of range (2..%d)", world, kMaxPeers);
+  DCNN_REQUIRE(rank >= 0 && rank < world, "sync-BN: rank %d out of range", rank);
+  for (int r = 0; r < kMaxPeers; ++r) sa->area[r] = r < world ? areas[r] : nullptr;
+  sa->rank = rank;
+  sa->world = world;
   return 0;
 }
 
-// peer_moments[r] / flag_ptrs[r]: replica r's exported-moments buffer and flag array as mapped in THIS process (host
-// arrays of device pointers); epoch_counter: this rank's device-resident rendezvous counter.
-DCNN_API int dcnn_bn_finalize_sync(const double* const* peer_moments, unsigned long long* const* flag_ptrs, int rank,
-                                   unsigned long long* epoch_counter, int n_peers, int C, float eps, float momentum,
-                                   float* running_mean, float* running_var, const float* gamma, const float* beta,
-                                   float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream) {
-  PeerPtrs pp;
-  PeerFlags pf;
-  int rc = fill_peers(&pp, &pf, peer_moments, flag_ptrs, n_peers);
+// A layer must keep one kernel variant for all of its sync calls (parity alternation, see bn_sync_exchange).
+static bool sync_narrow() {
+  static const bool on = finalize_narrow();
+  return on;
+}
+
+DCNN_API int dcnn_bn_finalize_sync1(const float* partials, int tiles, int C, float eps, float momentum,
+                                    float* running_mean, float* running_var, const float* gamma, const float* beta,
+                                    float* mean, float* invstd, float* scale, float* shift,
+                                    unsigned char* const* areas, int rank, int world, cudaStream_t stream) {
+  BnSyncArgs sa;
+  int rc = fill_sync(&sa, areas, rank, world);
   if (rc) return rc;
-  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
-  bn_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(pp, pf, rank, epoch_counter, n_peers, C, eps, momentum,
-                                                               running_mean, running_var, gamma, beta, mean, invstd,
-                                                               scale, shift);
+  if (sync_narrow()) {
+    dim3 nblock(8, 128);
+    bn_finalize_narrow_kernel<<<ceil_div(C, 8), nblock, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
+                                                                    running_var, gamma, beta, mean, invstd, scale,
+                                                                    shift, sa);
+  } else {
+    dim3 block(32, 32);
+    bn_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, eps, momentum, running_mean,
+                                                             running_var, gamma, beta, mean, invstd, scale, shift,
+                                                             sa);
+  }
   DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(2);
+  DCNN_COUNT_LAUNCH(1);
+  return 0;
+}
+
+DCNN_API int dcnn_bn_bwd_finalize_sync1(const float* partials, int tiles, int C, double count, const float* mean,
+                                        const float* invstd, const float* gamma, float* dgamma, float* dbeta,
+                                        float* k1, float* k2, float* k3, unsigned char* const* areas, int rank,
+                                        int world, cudaStream_t stream) {
+  BnSyncArgs sa;
+  int rc = fill_sync(&sa, areas, rank, world);
+  if (rc) return rc;
+  if (sync_narrow()) {
+    dim3 nblock(8, 128);
+    bn_bwd_finalize_narrow_kernel<<<ceil_div(C, 8), nblock, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma,
+                                                                        dgamma, dbeta, k1, k2, k3, sa);
+  } else {
+    dim3 block(32, 32);
+    bn_bwd_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma,
+                                                                 dgamma, dbeta, k1, k2, k3, sa);
+  }
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
   return 0;
 }
 
@@ -821,36 +877,21 @@ DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* 
 
 DCNN_API int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
                                   const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1,
-                                  float* k2, float* k3, double* export_sums, cudaStream_t stream) {
+                                  float* k2, float* k3, cudaStream_t stream) {
   if (finalize_narrow() && tiles >= 256) {
     dim3 nblock(8, 128);
     bn_bwd_finalize_narrow_kernel<<<ceil_div(C, 8), nblock, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma,
-                                                                        dgamma, dbeta, k1, k2, k3, export_sums);
+                                                                        dgamma, dbeta, k1, k2, k3,
+                                                                        BnSyncArgs{});
     DCNN_CHECK_LAUNCH();
     DCNN_COUNT_LAUNCH(1);
     return 0;
   }
   dim3 block(32, 32);
   bn_bwd_finalize_kernel<<<ceil_div(C, 32), block, 0, stream>>>(partials, tiles, C, count, mean, invstd, gamma, dgamma,
-                                                               dbeta, k1, k2, k3, export_sums);
+                                                               dbeta, k1, k2, k3, BnSyncArgs{});
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(1);
-  return 0;
-}
-
-DCNN_API int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, unsigned long long* const* flag_ptrs, int rank,
-                                       unsigned long long* epoch_counter, int n_peers, int C, const float* mean,
-                                       const float* invstd, const float* gamma, float* k1, float* k2, float* k3,
-                                       cudaStream_t stream) {
-  PeerPtrs pp;
-  PeerFlags pf;
-  int rc = fill_peers(&pp, &pf, peer_sums, flag_ptrs, n_peers);
-  if (rc) return rc;
-  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
-  bn_bwd_finalize_sync_kernel<<<ceil_div(C, 128), 128, 0, stream>>>(pp, pf, rank, epoch_counter, n_peers, C, mean,
-                                                                   invstd, gamma, k1, k2, k3);
-  DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(2);
   return 0;
 }
 
@@ -949,7 +990,7 @@ static __device__ __align__(256) float g_bn_noalloc_scratch[kNoAllocScratchFloat
 
 namespace {
 constexpr int kMaxDevices = 64;
-float* g_noalloc_ptr[kMaxDevices] = {};
+std::atomic<float*> g_noalloc_ptr[kMaxDevices];   // zero-initialised; host threads may race to fill a slot (same value)
 }  // namespace
 
 DCNN_API long long dcnn_bn_noalloc_capacity_floats() { return kNoAllocScratchFloats; }
@@ -969,13 +1010,13 @@ DCNN_API int dcnn_bn_batch_stats_noalloc(const float* x, long long M, int C, flo
   int dev = 0;
   DCNN_CHECK_CUDA(cudaGetDevice(&dev));
   DCNN_REQUIRE(dev >= 0 && dev < kMaxDevices, "dcnn_bn_batch_stats_noalloc: device index %d out of range", dev);
-  float* scratch = g_noalloc_ptr[dev];
+  float* scratch = g_noalloc_ptr[dev].load(std::memory_order_relaxed);
   if (scratch == nullptr) {  // once per device, with that device current
     void* p = nullptr;
     DCNN_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bn_noalloc_scratch));
     DCNN_REQUIRE(p != nullptr, "dcnn_bn_batch_stats_noalloc: cudaGetSymbolAddress returned a null address");
     scratch = static_cast<float*>(p);
-    g_noalloc_ptr[dev] = scratch;
+    g_noalloc_ptr[dev].store(scratch, std::memory_order_relaxed);
   }
   if ((C & 3) == 0) {
     dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
@@ -988,7 +1029,7 @@ DCNN_API int dcnn_bn_batch_stats_noalloc(const float* x, long long M, int C, flo
   dim3 fblock(32, 32);
   bn_finalize_kernel<<<ceil_div(C, 32), fblock, 0, stream>>>(scratch, tiles, C, eps, momentum, running_mean,
                                                             running_var, gamma, beta, mean, invstd, scale, shift,
-                                                            nullptr);
+                                                            BnSyncArgs{});
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(2);
   return 0;

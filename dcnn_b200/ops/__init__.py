@@ -58,6 +58,13 @@ def loss_forward_backward(kind, pred, target, param=0.0, want_grad=True):
     return backend_for(pred).loss_forward_backward(kind, pred, target, param, want_grad)
 
 
+def weights_changed():
+    """Tell the CUDA backend that parameters were written behind torch's back (a raw-pointer kernel or a CUDA-graph
+    replay): cached derived layouts of the weights are rebuilt on their next use.  No-op without the CUDA backend."""
+    if _cuda is not None:
+        _cuda.weights_changed()
+
+
 def to_activation_layout(x):
     """Activations on CUDA are physically NHWC (torch channels_last) with a logical NCHW shape."""
     if x.is_cuda and x.dim() == 4:

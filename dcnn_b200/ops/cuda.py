@@ -33,7 +33,7 @@ def _p(t: Optional[torch.Tensor]):
 RECOMPUTE_RELU_MASK = os.environ.get("DCNN_BN_RECOMPUTE_MASK", "1") != "0"
 # DCNN_BN_BITMASK=1: (BN + residual -> ReLU) units keep a 4-bit-per-float4 mask instead of re-reading their output in
 # backward (opt-in until its hardware validation run)
-RELU_BITMASK = os.environ.get("DCNN_BN_BITMASK", "0") == "1"
+RELU_BITMASK = os.environ.get("DCNN_BN_BITMASK", "1") == "1"
 
 
 def tc_enabled() -> bool:
@@ -76,9 +76,11 @@ class CudaStats:
 
 
 # ================================================================================== convolution
-# DCNN_STEM_TC=1: small-Cin convolutions (R*S*Cin <= 64, e.g. the 3x3x3 ResNet stem or a 5x5x1 MNIST conv) are run as
-# packed-tap im2col + a 1x1 tensor-core convolution instead of on CUDA cores (opt-in until validated on hardware).
-STEM_TC = os.environ.get("DCNN_STEM_TC", "0") == "1"
+# Small-Cin convolutions run as packed-tap im2col + a 1x1 tensor-core convolution instead of on CUDA cores: always for
+# channel counts that are not a multiple of 4 (RGB / grey-scale stems: the 3x3x3 ResNet stem is K = 27 -> 32, the 7x7x3
+# ImageNet stem K = 147 -> 160), and for other counts below 32 when all taps fit in 64 packed channels (cheaper than
+# padding every tap to 32).  DCNN_STEM_TC=0 sends them to the CUDA-core kernel.
+STEM_TC = os.environ.get("DCNN_STEM_TC", "1") == "1"
 
 
 def _stem_kp(Cin, R, S):
@@ -86,7 +88,8 @@ def _stem_kp(Cin, R, S):
     if not (STEM_TC and tc_enabled()) or Cin % 32 == 0:
         return 0
     K = R * S * Cin
-    return (K + 31) // 32 * 32 if K <= 64 else 0
+    limit = 64 if Cin % 4 == 0 else 256
+    return (K + 31) // 32 * 32 if K <= limit else 0
 
 
 def _pack_taps(x, R, S, stride, pad, OH, OW, Kp):
@@ -109,7 +112,9 @@ def _packed_weights(w, Kp):
 # DCNN_AUTOTUNE=1: the first time a convolution shape is seen (outside CUDA-graph capture) every structurally possible
 # kernel variant -- conv_tc2 (128-pixel tiles), conv_tc3 (256-pixel tiles), conv_tc5 (CTA pairs, Cout >= 256) -- is timed
 # with CUDA events on that very call's operands and the fastest is used from then on, instead of the built-in size
-# rules.  Opt-in until its first hardware run.
+# rules.  Validated on hardware (-0.18 ms on the 16.5 ms ResNet-50 step, profiles/05); opt-in because the timing run
+# synchronises the host, which a pipeline stage with pre-posted receives must not do outside its warm-up.
+# DCNN_AUTOTUNE_LOG=<file> appends one line per decision.
 AUTOTUNE = os.environ.get("DCNN_AUTOTUNE", "0") == "1"
 _TUNED = {}
 
@@ -122,7 +127,7 @@ def _autotuned(key, cout, fn, tunable=True):
     if v is None:
         if not tunable or torch.cuda.is_current_stream_capturing():
             return fn()
-        best_t = None
+        best_t, times = None, []
         for cand in (2, 3, 5) if cout >= 256 else (2, 3):
             check(lib().dcnn_conv_tc_set_variant(I(cand)), "conv_tc_set_variant")
             try:
@@ -136,9 +141,14 @@ def _autotuned(key, cout, fn, tunable=True):
                 t = e0.elapsed_time(e1)
             finally:
                 check(lib().dcnn_conv_tc_set_variant(I(0)), "conv_tc_set_variant")
+            times.append((cand, round(t / 3 * 1000.0, 1)))
             if best_t is None or t < best_t:
                 best_t, v = t, cand
         _TUNED[key] = v
+        log = os.environ.get("DCNN_AUTOTUNE_LOG", "")
+        if log:
+            with open(log, "a") as f:
+                f.write(f"{key} -> conv_tc{v}  us per launch {times}\n")
     check(lib().dcnn_conv_tc_set_variant(I(v)), "conv_tc_set_variant")
     try:
         return fn()
@@ -169,7 +179,9 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
         return conv2d_forward(_pack_taps(x, R, S, stride, pad, OH, OW, kp), _packed_weights(w, kp), bias, (1, 1),
                               (0, 0), want_stats)
     y = _empty_nhwc(N, Cout, OH, OW, x.device)
-    use_tc = tc_enabled() and Cin % 32 == 0 and R * S <= 49 and \
+    # tensor cores for every channel count that keeps rows 16-byte aligned: the TMA unit pads the reduction dimension
+    # to a multiple of 32 with zeros (C = 1 / 3 stems take the packed-tap route above; anything else is CUDA cores)
+    use_tc = tc_enabled() and Cin % 4 == 0 and Cout % 4 == 0 and R * S <= 49 and \
         ((sh_ == 1 and sw_ == 1) or (tc_strided_enabled() and sh_ <= 8 and sw_ <= 8))
     if use_tc:
         taps = _taps(("f", R, S, ph, pw), lambda: (
@@ -192,12 +204,73 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
     return y, (bn_stats(y) if want_stats else None)
 
 
+# The dgrad operand layout (W[K][R][S][C] -> Wt[C][R][S][K], spatial axes flipped) of EVERY weight tensor that has been
+# through a backward pass is rebuilt by ONE batched launch, the first time a backward pass needs any of them after the
+# weights may have changed.  An entry is valid while (a) torch has not modified the tensor in place (`_version`) and
+# (b) none of this library's kernels that write parameters through raw pointers -- optimizer updates, the fused
+# data-parallel update, CUDA-graph replays of either -- has run since (`weights_changed()` bumps the generation).
+# Before: one launch per convolution per backward pass (52 per ResNet-50 step, 0.29 ms); microbatched and pipelined
+# steps, which run many backward passes per update, reuse the layouts outright.
+class _WtEntry:
+    __slots__ = ("w", "wt", "stamp", "shape", "used")
+
+
+_WT_CACHE = {}
+_WT_GENERATION = [0]
+
+def weights_changed():
+    _WT_GENERATION[0] += 1
+
+
+def clear_weight_layout_cache():
+    _WT_CACHE.clear()
+
+
+def _wt_stamp(w):
+    return (w._version, _WT_GENERATION[0], torch.cuda.is_current_stream_capturing())
+
+
 def _dgrad_weights(w):
     """W[K][R][S][C] -> Wt[C][R][S][K], both spatial axes flipped (K-major over the dY channels)."""
     K, Cc, R, S = w.shape
-    wt = torch.empty(Cc * R * S * K, device=w.device, dtype=torch.float32)
-    check(lib().dcnn_weight_dgrad_layout(_p(w), _p(wt), I(K), I(R), I(S), I(Cc), _stream()), "weight_dgrad_layout")
-    return wt
+    key = (w.data_ptr(), K, Cc, R, S, w.device.index)
+    stamp = _wt_stamp(w)
+    ent = _WT_CACHE.get(key)
+    if ent is not None:
+        ent.used = _WT_GENERATION[0]
+        if ent.stamp == stamp:
+            return ent.wt
+    if ent is None:
+        if len(_WT_CACHE) > 4096:
+            clear_weight_layout_cache()
+        ent = _WtEntry()
+        ent.w, ent.shape, ent.wt, ent.stamp, ent.used = w, (K, R, S, Cc), None, None, _WT_GENERATION[0]
+        _WT_CACHE[key] = ent
+    capturing = stamp[2]
+    # everything on this device that is stale and was needed recently (a model that is no longer trained drops out)
+    # goes into the same launch
+    recent = _WT_GENERATION[0] - 4
+    todo = [e for e in _WT_CACHE.values()
+            if e is ent or (e.w.device == w.device and e.used >= recent and e.stamp != _wt_stamp(e.w))]
+    rows = []
+    for e in todo:
+        # a buffer that belongs to a captured graph's pool is never written by eager launches (and vice versa)
+        if e.wt is None or e.stamp is None or e.stamp[2] != capturing:
+            k_, r_, s_, c_ = e.shape
+            e.wt = torch.empty(c_ * r_ * s_ * k_, device=w.device, dtype=torch.float32)
+        k_, r_, s_, c_ = e.shape
+        rows.append([e.w.data_ptr(), e.wt.data_ptr(), k_, r_, s_, c_])
+    if len(rows) == 1:
+        k_, r_, s_, c_ = ent.shape
+        check(lib().dcnn_weight_dgrad_layout(_p(ent.w), _p(ent.wt), I(k_), I(r_), I(s_), I(c_), _stream()),
+              "weight_dgrad_layout")
+    else:
+        flat = [v for row in rows for v in row]
+        check(lib().dcnn_weight_dgrad_layout_batched((LL * len(flat))(*flat), I(len(rows)), _stream()),
+              "weight_dgrad_layout_batched")
+    for e in todo:
+        e.stamp = _wt_stamp(e.w)
+    return ent.wt
 
 
 def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False):
@@ -211,7 +284,7 @@ def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False
         accumulate = False
     dx = out if out is not None else _empty_nhwc(N, Cin, H, W, dy.device)
     assert dx.is_contiguous(memory_format=CL)
-    use_tc = tc_enabled() and K % 32 == 0 and R * S <= 49 and R - 1 - ph >= -64
+    use_tc = tc_enabled() and K % 4 == 0 and Cin % 4 == 0 and R * S <= 49 and R - 1 - ph >= -64
     if use_tc and sh_ == 1 and sw_ == 1:
         wt = _dgrad_weights(w)
         taps = _taps(("d1", R, S, ph, pw), lambda: (
@@ -273,7 +346,7 @@ def conv2d_backward_weight(dy, x, dw, stride, pad):
         conv2d_backward_weight(dy, _pack_taps(x, R, S, stride, pad, OH, OW, kp), dwp, (1, 1), (0, 0))
         dw.permute(0, 2, 3, 1).reshape(K, R * S * Cin).add_(dwp.reshape(K, kp)[:, :R * S * Cin])
         return
-    use_tc = tc_enabled() and Cin % 32 == 0 and K % 4 == 0 and R * S <= 49 and \
+    use_tc = tc_enabled() and Cin % 4 == 0 and K % 4 == 0 and R * S <= 49 and \
         ((sh_ == 1 and sw_ == 1) or (tc_strided_enabled() and sh_ <= 8 and sw_ <= 8))
     if use_tc:
         taps = _taps(("f", R, S, ph, pw), lambda: (
@@ -311,7 +384,7 @@ def dense_forward(x2d, w2d, bias):
     B, Fin = x2d.shape
     Fout = w2d.shape[0]
     y = torch.empty((B, Fout), device=x2d.device, dtype=torch.float32)
-    if tc_enabled() and Fin % 32 == 0:
+    if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0:
         _conv_tc(x2d, B, 1, 1, Fin, w2d, Fout, Fin, y, 0, Fout, Fout, Fout, 1, 1, 1, 1, _one_tap(), bias, False, None)
     else:
         check(lib().dcnn_conv_fprop_simt(_p(x2d), _p(w2d), _p(bias), _p(y), I(B), I(1), I(1), I(Fin), I(Fout), I(1),
@@ -324,9 +397,8 @@ def dense_backward_data(dy2d, w2d):
     B, Fout = dy2d.shape
     Fin = w2d.shape[1]
     dx = torch.empty((B, Fin), device=dy2d.device, dtype=torch.float32)
-    if tc_enabled() and Fout % 32 == 0:
-        wt = torch.empty(Fin * Fout, device=dy2d.device, dtype=torch.float32)
-        check(lib().dcnn_weight_dgrad_layout(_p(w2d), _p(wt), I(Fout), I(1), I(1), I(Fin), _stream()), "dense wt")
+    if tc_enabled() and Fout % 4 == 0 and Fin % 4 == 0:
+        wt = _dgrad_weights(w2d.view(Fout, Fin, 1, 1))
         _conv_tc(dy2d, B, 1, 1, Fout, wt, Fin, Fout, dx, 0, Fin, Fin, Fin, 1, 1, 1, 1, _one_tap(), None, False, None)
     else:
         check(lib().dcnn_conv_dgrad_simt(_p(dy2d), _p(w2d), _p(dx), I(B), I(1), I(1), I(Fin), I(Fout), I(1), I(1),
@@ -339,7 +411,7 @@ def dense_backward_weight(dy2d, x2d, dw2d):
     x2d = x2d.contiguous()
     B, Fout = dy2d.shape
     Fin = x2d.shape[1]
-    if tc_enabled() and Fin % 32 == 0 and Fout % 4 == 0:
+    if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0:
         n, dh, dw_, wi = _one_tap()
         check(lib().dcnn_wgrad_tc(_p(dy2d), I(B), I(1), I(1), I(Fout), _p(x2d), I(1), I(1), I(Fin), _p(dw2d), I(Fin),
                                   I(1), I(1), I(n), dh, dw_, wi, _stream()), "dense wgrad tc")
@@ -372,7 +444,7 @@ def bn_finalize(stats, eps, momentum, running_mean, running_var, sync=None, gamm
     if sync is None:
         check(lib().dcnn_bn_finalize(_p(stats.partials), I(stats.tiles), I(Cc), F(eps), F(momentum),
                                      _p(running_mean), _p(running_var), _p(gamma), _p(beta), _p(mean), _p(invstd),
-                                     _p(scale), _p(shift), P(0), _stream()), "bn_finalize")
+                                     _p(scale), _p(shift), _stream()), "bn_finalize")
     else:
         sync.finalize_forward(stats, eps, momentum, running_mean, running_var, gamma, beta, mean, invstd, scale, shift)
     return mean, (invstd, scale, shift)
@@ -425,7 +497,7 @@ def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, wa
     k1, k2, k3 = k[:Cc], k[Cc:2 * Cc], k[2 * Cc:]
     if sync is None:
         check(lib().dcnn_bn_bwd_finalize(_p(partials), I(tiles), I(Cc), D(float(M)), _p(mean), _p(invstd), _p(gamma),
-                                         _p(dgamma), _p(dbeta), _p(k1), _p(k2), _p(k3), P(0), _stream()),
+                                         _p(dgamma), _p(dbeta), _p(k1), _p(k2), _p(k3), _stream()),
               "bn_bwd_finalize")
     else:
         sync.finalize_backward(partials, tiles, Cc, M, mean, invstd, gamma, dgamma, dbeta, k1, k2, k3)
@@ -658,6 +730,7 @@ def sgd_update(params, grads, velocities, lr, momentum, zero_grads=False, hyper=
     check(lib().dcnn_multi_tensor_update(I(mode), _p(tb[0]), _p(tb[1]), _p(tb[2]), _p(tb[3]), _p(tb[4]), _p(tb[5]),
                                          _p(tb[6]), I(tb[7]), F(lr), F(momentum), F(0), F(0), F(1), F(1), F(0),
                                          I(1 if zero_grads else 0), _p(hyper), _stream()), "sgd_update")
+    weights_changed()
 
 
 def adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_decay, decoupled, zero_grads=False,
@@ -667,3 +740,4 @@ def adam_update(params, grads, ms, vs, lr, beta1, beta2, eps, bc1, bc2, weight_d
                                          _p(tb[4]), _p(tb[5]), _p(tb[6]), I(tb[7]), F(lr), F(beta1), F(beta2), F(eps),
                                          F(bc1), F(bc2), F(weight_decay), I(1 if zero_grads else 0), _p(hyper),
                                          _stream()), "adam_update")
+    weights_changed()

@@ -171,47 +171,46 @@ class NvlsBuffer:
 
 
 class SyncBN:
-    """Cross-replica BatchNorm statistics for one BN layer (forward moments and backward sums)."""
+    """Cross-replica BatchNorm statistics for one BN layer (forward moments and backward sums).
+
+    CUDA: ONE launch per direction -- the finalize kernel pushes its per-channel values into every replica's exchange
+    area, raises per-channel-group epoch flags and merges all sources from local memory (csrc/norm.cu,
+    ``bn_sync_exchange``); the call counters live on the device, so there is no host-side bookkeeping to keep in step
+    with CUDA-graph replays."""
 
     def __init__(self, dp: "DataParallel", channels: int, offset_bytes: int):
         self.dp, self.C = dp, channels
-        self.off = offset_bytes          # [fwd parity0, fwd parity1, bwd parity0, bwd parity1] x 3*C doubles
-        self.calls_f = self.calls_b = 0
+        self.off = offset_bytes          # [forward area][backward area], each area_bytes(world, C)
+        if dp.device.type == "cuda":
+            a = self.area_bytes(dp.world, channels)
+            self.areas_f = dp.bn_buf.peer_array(offset_bytes)
+            self.areas_b = dp.bn_buf.peer_array(offset_bytes + a)
 
     @staticmethod
-    def bytes_needed(channels: int) -> int:
-        return 4 * 3 * channels * 8
+    def area_bytes(world: int, channels: int) -> int:
+        g = (channels + 7) // 8           # must equal dcnn_bn_sync_area_bytes (checked in DataParallel._setup_sync_bn)
+        b = 2 * world * 3 * channels * 8 + g * 8 * 8 + g * 8
+        return (b + 255) // 256 * 256
 
-    def _slot(self, which: int, parity: int) -> int:
-        return self.off + (which * 2 + parity) * 3 * self.C * 8
+    @classmethod
+    def bytes_needed(cls, world: int, channels: int) -> int:
+        return 2 * cls.area_bytes(world, channels)
 
-    # ---- CUDA: export local moments, then rendezvous + merge inside the finalize kernel
     def finalize_forward(self, stats, eps, momentum, rm, rv, gamma, beta, mean, invstd, scale, shift):
-        from .._lib import F, I, P, check, lib
+        from .._lib import F, I, check, lib
         from ..ops.cuda import _p, _stream
         dp = self.dp
-        off = self._slot(0, self.calls_f & 1)
-        self.calls_f += 1
-        check(lib().dcnn_bn_finalize(_p(stats.partials), I(stats.tiles), I(self.C), F(eps), F(momentum), P(0), P(0),
-                                     _p(gamma), _p(beta), _p(mean), _p(invstd), _p(scale), _p(shift),
-                                     P(dp.bn_buf.ptr + off), _stream()), "bn_finalize(export)")
-        check(lib().dcnn_bn_finalize_sync(dp.bn_buf.peer_array(off), dp.bn_flags, I(dp.rank), P(dp.bn_epoch_ptr),
-                                          I(dp.world), I(self.C), F(eps), F(momentum), _p(rm), _p(rv), _p(gamma),
-                                          _p(beta), _p(mean), _p(invstd), _p(scale), _p(shift), _stream()),
-              "bn_finalize_sync")
+        check(lib().dcnn_bn_finalize_sync1(_p(stats.partials), I(stats.tiles), I(self.C), F(eps), F(momentum), _p(rm),
+                                           _p(rv), _p(gamma), _p(beta), _p(mean), _p(invstd), _p(scale), _p(shift),
+                                           self.areas_f, I(dp.rank), I(dp.world), _stream()), "bn_finalize_sync1")
 
     def finalize_backward(self, partials, tiles, Cc, M, mean, invstd, gamma, dgamma, dbeta, k1, k2, k3):
-        from .._lib import D, I, P, check, lib
+        from .._lib import D, I, check, lib
         from ..ops.cuda import _p, _stream
         dp = self.dp
-        off = self._slot(1, self.calls_b & 1)
-        self.calls_b += 1
-        check(lib().dcnn_bn_bwd_finalize(_p(partials), I(tiles), I(Cc), D(float(M)), _p(mean), _p(invstd), _p(gamma),
-                                         _p(dgamma), _p(dbeta), _p(k1), _p(k2), _p(k3), P(dp.bn_buf.ptr + off),
-                                         _stream()), "bn_bwd_finalize(export)")
-        check(lib().dcnn_bn_bwd_finalize_sync(dp.bn_buf.peer_array(off), dp.bn_flags, I(dp.rank),
-                                              P(dp.bn_epoch_ptr), I(dp.world), I(Cc), _p(mean), _p(invstd),
-                                              _p(gamma), _p(k1), _p(k2), _p(k3), _stream()), "bn_bwd_finalize_sync")
+        check(lib().dcnn_bn_bwd_finalize_sync1(_p(partials), I(tiles), I(Cc), D(float(M)), _p(mean), _p(invstd),
+                                               _p(gamma), _p(dgamma), _p(dbeta), _p(k1), _p(k2), _p(k3), self.areas_b,
+                                               I(dp.rank), I(dp.world), _stream()), "bn_bwd_finalize_sync1")
 
     # ---- CPU / baseline: the same merges with torch.distributed collectives
     def merge_cpu(self, mean, var, n):
@@ -280,6 +279,21 @@ def plan_buckets(unit_params, numels, offsets, n, k, rank, world):
     return buckets
 
 
+def state_layout(n, world, rank, buckets=None):
+    """Slices of the flat parameter space whose optimizer state rank ``rank`` keeps, as ``(flat_begin, flat_end, offset
+    in the rank's state arrays)``: one contiguous shard, or one shard per bucket (``plan_buckets``)."""
+    if buckets is None:
+        shard = n // world
+        return [(rank * shard, (rank + 1) * shard, 0)]
+    out, off = [], 0
+    for bk in buckets:
+        q = bk["n"] // 4
+        sb, se = (q * rank // world) * 4, (q * (rank + 1) // world) * 4
+        out.append((bk["a"] + sb, bk["a"] + se, off))
+        off += se - sb
+    return out
+
+
 class DataParallel:
     def __init__(self, model: Sequential, optimizer: Optimizer, group=None, sync_bn: bool = True,
                  nccl_baseline: bool = False, num_blocks: int = 0):
@@ -301,12 +315,10 @@ class DataParallel:
         self.offsets = offs
         if self.device.type == "cuda":
             # rendezvous state shared by the fused update and sync-BN: symmetric epoch flags + local counters
-            self.ctl = SymmetricBuffer(3 * 64, self.group, self.device)
+            self.ctl = SymmetricBuffer(2 * 64, self.group, self.device)
             self.start_flags = self.ctl.peer_array(0)
             self.done_flags = self.ctl.peer_array(64)
-            self.bn_flags = self.ctl.peer_array(128)
-            self.local = torch.zeros(8, dtype=torch.int64, device=self.device)  # [0] block ctr, [1] epoch, [2] bn epoch
-            self.bn_epoch_ptr = self.local.data_ptr() + 16
+            self.local = torch.zeros(8, dtype=torch.int64, device=self.device)  # [0] block ctr, [1] epoch
         self.buckets = None           # DCNN_DP_BUCKETS=K: K fused all-reduce launches overlapped with backward
         self.final_backward = False   # set by the training step before the last backward pass of an optimisation step
         if self.fused:
@@ -361,15 +373,89 @@ class DataParallel:
         shard = self.n // self.world
         self.shard_begin, self.shard_end = self.rank * shard, (self.rank + 1) * shard
         opt = self.optimizer
-        self.s1 = torch.zeros(shard, device=self.device) if (isinstance(opt, Adam) or getattr(opt, "momentum", 0) > 0) \
-            else None
-        self.s2 = torch.zeros(shard, device=self.device) if isinstance(opt, Adam) else None
+        self._alloc_state(shard)
         opt.params, opt.grads = self.model.parameters(), self.model.gradients()   # for clear_gradients()/introspection
+        # checkpoints: the moments live here, sharded -- the optimizer's state_dict()/load_state_dict() go through us
+        opt.state_dict = self.optimizer_state_dict
+        opt.load_state_dict = self.load_optimizer_state_dict
         if not self.nvls:
             self.grad_ptrs = self.buf.peer_array(4 * self.n)
             self.param_ptrs = self.buf.peer_array(0)
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
+
+    # ------------------------------------------------------------------------------------------------
+    # Sharded optimizer state.  It lives in a symmetric buffer so that ANY rank can assemble the full moments for a
+    # checkpoint by reading its peers' shards over NVLink -- no collective, so a signal handler on one rank can do it.
+    def _alloc_state(self, floats: int):
+        opt = self.optimizer
+        self.n_state = (2 if isinstance(opt, Adam) else (1 if getattr(opt, "momentum", 0) > 0 else 0))
+        self.state_floats = int(floats)
+        self.s1 = self.s2 = None
+        if self.n_state:
+            self.state_buf = SymmetricBuffer(4 * self.n_state * self.state_floats, self.group, self.device)
+            self.s1 = self.state_buf.view(torch.float32, 0, self.state_floats)
+            if self.n_state == 2:
+                self.s2 = self.state_buf.view(torch.float32, 4 * self.state_floats, self.state_floats)
+
+    def _state_layout(self, rank: int):
+        """[(flat_begin, flat_end, offset in that rank's state arrays)] of the slices rank ``rank`` owns."""
+        return state_layout(self.n, self.world, rank, self.buckets)
+
+    def _flat_to_list(self, flat):
+        out = []
+        for p, off, num in zip(self.model.parameters(), self.offsets, self.numels):
+            t = flat[off:off + num]
+            if p.dim() == 4 and not p.is_contiguous():
+                o, c, r, s_ = p.shape
+                t = t.view(o, r, s_, c).permute(0, 3, 1, 2)
+            else:
+                t = t.view(p.shape)
+            out.append(t.clone())
+        return out
+
+    def _list_to_flat(self, tensors):
+        flat = torch.zeros(self.n, device=self.device)
+        for p, off, num, t in zip(self.model.parameters(), self.offsets, self.numels, tensors):
+            t = t.to(self.device, torch.float32)
+            src = t.permute(0, 2, 3, 1).reshape(-1) if (p.dim() == 4 and not p.is_contiguous()) else t.reshape(-1)
+            flat[off:off + num] = src
+        return flat
+
+    def _gather_state(self, which: int):
+        torch.cuda.synchronize(self.device)
+        flat = torch.zeros(self.n, device=self.device)
+        for r in range(self.world):
+            peer = torch.as_tensor(_RawCuda(self.state_buf.peer_ptrs[r] + 4 * which * self.state_floats,
+                                            4 * self.state_floats), device=self.device).view(torch.float32)
+            for b, e, off in self._state_layout(r):
+                flat[b:e] = peer[off:off + e - b]
+        return self._flat_to_list(flat)
+
+    def optimizer_state_dict(self) -> dict:
+        """Same layout as the optimizer's own ``state_dict()`` (per-parameter tensors), assembled from every replica's
+        shard: a checkpoint written under data parallelism resumes on one GPU and the other way round."""
+        opt = self.optimizer
+        if isinstance(opt, Adam):
+            return {"t": opt.t, "m": self._gather_state(0), "v": self._gather_state(1)}
+        return {"velocities": self._gather_state(0) if self.n_state else []}
+
+    def load_optimizer_state_dict(self, state: dict):
+        opt = self.optimizer
+        if isinstance(opt, Adam):
+            opt.t = int(state.get("t", 0))
+            pairs = [(self.s1, state.get("m")), (self.s2, state.get("v"))]
+        else:
+            pairs = [(self.s1, state.get("velocities"))] if self.n_state else []
+        for dst, lst in pairs:
+            if not lst:
+                if dst is not None and lst is not None and len(self.numels):
+                    raise ValueError("checkpoint holds no optimizer moments for a stateful optimizer")
+                continue
+            flat = self._list_to_flat(lst)
+            for b, e, off in self._state_layout(self.rank):
+                dst[off:off + e - b] = flat[b:e]
+        torch.cuda.synchronize(self.device)
 
     # ------------------------------------------------------------------------------------------------
     # Bucketed, overlapped variant (opt-in, DCNN_DP_BUCKETS=K; written after the last GPU minutes of its session, not yet
@@ -391,11 +477,7 @@ class DataParallel:
         for bk in self.buckets:
             bk["grad_ptrs"] = self.buf.peer_array(4 * self.n + 4 * bk["a"])
             bk["param_ptrs"] = self.buf.peer_array(4 * bk["a"])
-        state = max(4, sum(bk["se"] - bk["sb"] for bk in self.buckets))
-        opt = self.optimizer
-        self.s1 = torch.zeros(state, device=self.device) \
-            if (isinstance(opt, Adam) or getattr(opt, "momentum", 0) > 0) else None
-        self.s2 = torch.zeros(state, device=self.device) if isinstance(opt, Adam) else None
+        self._alloc_state(self.n // self.world + 4 * len(self.buckets))
         self.comm_stream = torch.cuda.Stream(device=self.device)
         self._trigger = {bk["first_unit"]: bi for bi, bk in enumerate(self.buckets)}
         self._launched = set()
@@ -451,16 +533,30 @@ class DataParallel:
         self._step_args = None
         self.final_backward = False
 
+    def reset_step_bookkeeping(self):
+        """Forget a step that was recorded but never ran (an aborted CUDA-graph capture).  The rendezvous epochs and the
+        sync-BatchNorm call counters are device-resident, so they did not move; only the bucket bookkeeping is host state."""
+        if self.buckets is not None:
+            self._launched = set()
+            self._step_args = None
+        self.final_backward = False
+
     def _setup_sync_bn(self):
         bns = [l for l in _all_layers(self.model) if isinstance(l, BatchNormLayer)]
         on_gpu = self.device.type == "cuda"
         if on_gpu:
-            total = sum(SyncBN.bytes_needed(l.num_features) for l in bns)
-            self.bn_buf = SymmetricBuffer(total, self.group, self.device)
+            from .._lib import lib
+            l_ = lib()
+            l_.dcnn_bn_sync_area_bytes.restype = C.c_longlong
+            for l in bns:
+                assert SyncBN.area_bytes(self.world, l.num_features) == \
+                    int(l_.dcnn_bn_sync_area_bytes(C.c_int(self.world), C.c_int(l.num_features)))
+            total = sum(SyncBN.bytes_needed(self.world, l.num_features) for l in bns)
+            self.bn_buf = SymmetricBuffer(total, self.group, self.device)     # zero-initialised: epochs start at 0
         off = 0
         for l in bns:
             s = SyncBN(self, l.num_features, off)
-            off += SyncBN.bytes_needed(l.num_features)
+            off += SyncBN.bytes_needed(self.world, l.num_features)
             l.sync = s
             self.sync_objs.append(s)
         if on_gpu:
@@ -484,6 +580,8 @@ class DataParallel:
         opt = optimizer or self.optimizer
         if not self.fused:
             return self._baseline(opt)
+        from .. import ops
+        ops.weights_changed()           # every replica's parameters are rewritten through peer pointers
         if self.buckets is not None:
             return self._finish_buckets()
         from .._lib import F, I, LL, P, check, lib

@@ -15,6 +15,7 @@ from typing import List, Optional
 
 import torch
 
+from . import ops
 from .nn.loss import Loss
 from .nn.optimizers import Optimizer
 from .nn.sequential import Sequential
@@ -165,6 +166,8 @@ class TrainStep:
             self._static = (x.clone(), t.clone())
             g = torch.cuda.CUDAGraph()
             torch.cuda.synchronize()
+            # host-side state that the captured (not executed) step advances: rolled back if the capture fails
+            saved_t = getattr(self.optimizer, "t", None)
             try:
                 with torch.cuda.graph(g):
                     out = self._eager(*self._static)
@@ -173,6 +176,10 @@ class TrainStep:
                 print(f"[dcnn] CUDA graph capture failed ({type(e).__name__}: {e}); continuing without graphs",
                       file=sys.stderr)
                 self.use_cuda_graph, self._static = False, None
+                if saved_t is not None:
+                    self.optimizer.t = saved_t
+                if self.dp is not None:
+                    self.dp.reset_step_bookkeeping()
                 torch.cuda.synchronize()
                 return self._eager(x, t)
             self._graph, self._out = g, out
@@ -184,6 +191,7 @@ class TrainStep:
         self.optimizer.advance()
         self.optimizer.push_hyper()
         self._graph.replay()
+        ops.weights_changed()             # the replayed update wrote the parameters behind torch's back
         return self._out
 
 

@@ -48,17 +48,24 @@ int dcnn_conv_dgrad_simt(const float* dy, const float* w, float* dx, int N, int 
 int dcnn_conv_wgrad_simt(const float* dy, const float* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
                          int sh, int sw, int ph, int pw, cudaStream_t stream);
 int dcnn_weight_dgrad_layout(const float* w, float* wt, int K, int R, int S, int C, cudaStream_t stream);
+/* the same for `count` weight tensors, 64 per launch: table_host[e] = {w, wt, K, R, S, C} as six 64-bit words (host) */
+int dcnn_weight_dgrad_layout_batched(const long long* table_host, int count, cudaStream_t stream);
 
 /* ---- BatchNorm / GroupNorm (batchnorm_ops.cu:108-295, groupnorm_ops.cu:45-252, cudnnConvolutionBackwardBias) ---- */
 int dcnn_bn_stat_tiles(long long M);
 int dcnn_bn_colstats(const float* x, long long M, int C, float* partials, cudaStream_t stream);
 int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
                      float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
-                     float* scale, float* shift, double* export_moments, cudaStream_t stream);
-int dcnn_bn_finalize_sync(const double* const* peer_moments, unsigned long long* const* flag_ptrs, int rank,
-                          unsigned long long* epoch_counter, int n_peers, int C, float eps, float momentum,
-                          float* running_mean, float* running_var, const float* gamma, const float* beta, float* mean,
-                          float* invstd, float* scale, float* shift, cudaStream_t stream);
+                     float* scale, float* shift, cudaStream_t stream);
+/* Sync-BatchNorm in ONE launch (no counterpart in the reference, which has no data parallelism): the finalize kernel
+ * pushes its per-channel values into every replica's exchange area over NVLink peer mappings, raises per-channel-group
+ * epoch flags and merges all replicas' values from local memory.  areas[r] = replica r's area for this layer and
+ * direction as mapped in this process (`world` device pointers, dcnn_bn_sync_area_bytes each, zeroed once). */
+long long dcnn_bn_sync_area_bytes(int world, int C);
+int dcnn_bn_finalize_sync1(const float* partials, int tiles, int C, float eps, float momentum, float* running_mean,
+                           float* running_var, const float* gamma, const float* beta, float* mean, float* invstd,
+                           float* scale, float* shift, unsigned char* const* areas, int rank, int world,
+                           cudaStream_t stream);
 int dcnn_bn_eval_coeffs(const float* rm, const float* rv, const float* gamma, const float* beta, float eps, int C,
                         float* scale, float* shift, cudaStream_t stream);
 int dcnn_bn_apply(const float* x, const float* scale, const float* shift, const float* residual, float* y,
@@ -72,11 +79,11 @@ int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, cons
                        long long M, int C, int relu, float* partials, cudaStream_t stream);
 int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
                          const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1, float* k2,
-                         float* k3, double* export_sums, cudaStream_t stream);
-int dcnn_bn_bwd_finalize_sync(const double* const* peer_sums, unsigned long long* const* flag_ptrs, int rank,
-                              unsigned long long* epoch_counter, int n_peers, int C, const float* mean,
-                              const float* invstd, const float* gamma, float* k1, float* k2, float* k3,
-                              cudaStream_t stream);
+                         float* k3, cudaStream_t stream);
+int dcnn_bn_bwd_finalize_sync1(const float* partials, int tiles, int C, double count, const float* mean,
+                               const float* invstd, const float* gamma, float* dgamma, float* dbeta, float* k1,
+                               float* k2, float* k3, unsigned char* const* areas, int rank, int world,
+                               cudaStream_t stream);
 int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* out, const float* k1, const float* k2,
                       const float* k3, float* dx, float* masked, long long M, int C, int relu, cudaStream_t stream);
 int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, cudaStream_t stream);

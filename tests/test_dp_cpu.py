@@ -117,6 +117,25 @@ def test_bucket_plan_covers_the_buffer_and_shards_evenly():
                     off += bk["se"] - bk["sb"]
 
 
+def test_state_layout_partitions_the_flat_parameter_space():
+    """The sharded optimizer state (one shard per rank, or one per bucket and rank) covers every flat index exactly once
+    and its offsets inside a rank's state arrays are dense -- what checkpoint assembly relies on."""
+    from dcnn_b200.parallel.dp import state_layout
+    for world in (2, 3, 8):
+        n = 4 * world * 37
+        buckets = [{"a": 0, "n": 4 * 11}, {"a": 44, "n": 4 * 50}, {"a": 244, "n": n - 244}]
+        for bk in (None, buckets):
+            seen = [0] * n
+            for r in range(world):
+                off = 0
+                for b, e, o in state_layout(n, world, r, bk):
+                    assert o == off and b % 4 == 0 and e % 4 == 0 and b <= e
+                    off += e - b
+                    for i in range(b, e):
+                        seen[i] += 1
+            assert seen == [1] * n
+
+
 def _fd_receiver(rank, tag, out):
     from dcnn_b200.parallel.dp import recv_fd
     fd = recv_fd(tag, rank + 1, timeout_s=30)

@@ -1,9 +1,6 @@
 """Layer-level device agnosticity (the reference's layer_device_agnosticity_test.cpp): the same layer object type on
 the CPU and on cuda:0 with identical parameters must agree to 1e-3 in FP32-exact mode, including the Conv->MaxPool and
-Conv->Dense mini-pipelines and a residual block.
-
-Written after the last GPU minutes of its session were spent, so it is opt-in until its first hardware run:
-DCNN_TEST_PENDING=1 python -m pytest tests/test_gpu_layers.py -m gpu"""
+Conv->Dense mini-pipelines and a residual block."""
 import os
 
 import pytest
@@ -12,9 +9,7 @@ import torch
 from dcnn_b200 import nn as dnn
 from dcnn_b200.nn.blocks import ResidualBlock
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("DCNN_TEST_PENDING") != "1",
-                                 reason="awaiting first hardware validation (set DCNN_TEST_PENDING=1)")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture(autouse=True)

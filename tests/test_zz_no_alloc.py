@@ -27,7 +27,7 @@ def _regular(lib, x, M, Cc, eps, mom, rm, rv, gamma, beta):
                                C.c_float(mom), C.c_void_p(rm.data_ptr()), C.c_void_p(rv.data_ptr()),
                                C.c_void_p(gamma.data_ptr()), C.c_void_p(beta.data_ptr()),
                                C.c_void_p(out[0].data_ptr()), C.c_void_p(out[1].data_ptr()),
-                               C.c_void_p(out[2].data_ptr()), C.c_void_p(out[3].data_ptr()), C.c_void_p(0),
+                               C.c_void_p(out[2].data_ptr()), C.c_void_p(out[3].data_ptr()),
                                C.c_void_p(0)), "bn_finalize")
     return out
 
@@ -55,7 +55,8 @@ def test_noalloc_bn_stats_matches_regular_entry_point_twice_in_a_row():
     assert cap == 1 << 20
     torch.manual_seed(7)
     # second call is smaller (fewer tiles, fewer channels): it must not see the first call's leftovers
-    for M, Cc in [(8 * 32 * 32, 256), (3 * 7 * 7, 36)]:
+    # ... and the third has a channel count that is not a multiple of 4 (the scalar statistics kernel)
+    for M, Cc in [(8 * 32 * 32, 256), (3 * 7 * 7, 36), (5 * 9 * 9, 10)]:
         x = (torch.randn(M, Cc, device="cuda") * 3 + 5).contiguous()
         gamma = torch.rand(Cc, device="cuda") + 0.5
         beta = torch.randn(Cc, device="cuda")
