@@ -69,7 +69,7 @@ def main():
     m2, opt2, dp2 = build(True)
     nccl_ms = bench(dp2, m2)
     if rank == 0:
-        bw = 900e9
+        bw = 770e9      # measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900
         try:
             peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
                                                 "MEASURED_PEAKS.json")))

@@ -1055,8 +1055,22 @@ static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cou
   *bn = *bh = *bw = 1;
   choose_box(N, OH, OW, 2 * kBM, mul_h, mul_w, bn, bh, bw);
   if (g_conv_variant == 3) return true;
-  const long long m_tiles = (long long)ceil_div(OW, *bw) * ceil_div(OH, *bh) * ceil_div(N, *bn);
-  return m_tiles >= num_sms();
+  // Both kernels are persistent (one CTA per SM, static round-robin) and operand-feed bound, so a launch costs about
+  // ceil(tiles / SMs) waves x (A rows + B rows) per k-step.  256-pixel tiles halve the tile count at 1.5x (N = 128) or
+  // 1.67x (N = 64) the cost per tile: they win unless the smaller tiles fit in the same number of waves.  This
+  // reproduces the choices the autotuner measured on every ResNet-50 layer (profiles/05), e.g. 3x3 256->256 @8x8:
+  // 128 big tiles in one wave (45.7 us) against 256 small ones in two (56.3 us); 3x3 512->512 @4x4: 64 big tiles leave
+  // 84 SMs idle (74.8 us) while 128 small ones use one wave (57.0 us).
+  const int bnt = Cout <= 64 ? 64 : 128;
+  const long long n_tiles = Cout <= 64 ? 1 : ceil_div(Cout, 128);
+  const long long m3 = (long long)ceil_div(OW, *bw) * ceil_div(OH, *bh) * ceil_div(N, *bn);
+  int b2n = 1, b2h = 1, b2w = 1;
+  choose_box(N, OH, OW, kBM, mul_h, mul_w, &b2n, &b2h, &b2w);
+  const long long m2 = (long long)ceil_div(OW, b2w) * ceil_div(OH, b2h) * ceil_div(N, b2n);
+  const long long sms = num_sms();
+  const long long cost3 = ((m3 * n_tiles + sms - 1) / sms) * (2 * kBM + bnt);
+  const long long cost2 = ((m2 * n_tiles + sms - 1) / sms) * (kBM + bnt);
+  return cost3 < cost2;
 }
 
 template <int BNW, int STAGES>

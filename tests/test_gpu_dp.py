@@ -80,13 +80,13 @@ def _worker(rank, world, port, out, kind, baseline, graph=False, steps=3, save_a
     dist.destroy_process_group()
 
 
-def _single(kind, world):
+def _single(kind, world, steps):
     m = _model("cuda:0")
     opt = _make_opt(kind)
     opt.attach(m.parameters(), m.gradients())
     step = TrainStep(m, opt, dnn.SoftmaxCrossEntropyLoss())
     x, t = _data(8 * world)
-    for _ in range(3):
+    for _ in range(steps):
         step(x.cuda(), t.cuda())
     torch.cuda.synchronize()
     return [p.detach().cpu().contiguous() for p in m.parameters()] + [b.cpu() for b in m.buffers().values()]
@@ -99,6 +99,46 @@ def _world():
     return world
 
 
+STEPS = 5          # a whole-step CUDA graph replays from the third call on
+_ENV_KEYS = ("DCNN_AR_HOISTED", "DCNN_DP_BUCKETS", "DCNN_DP_NVLS")
+
+
+def _run(tmp, tag, world, kind, baseline, graph, env, **kw):
+    saved = {k: os.environ.pop(k, None) for k in _ENV_KEYS}
+    os.environ.update(env)
+    try:
+        out = os.path.join(str(tmp), f"dp_{tag}.pt")
+        spawn_bounded(_worker, args=(world, _free_port(), out, kind, baseline, graph, kw.get("steps", STEPS),
+                                     kw.get("save_at"), kw.get("resume_from")), nprocs=world, timeout_s=240)
+        return torch.load(out)
+    finally:
+        for k in _ENV_KEYS:
+            os.environ.pop(k, None)
+            if saved[k] is not None:
+                os.environ[k] = saved[k]
+
+
+@pytest.fixture(scope="module")
+def oracles(tmp_path_factory):
+    """Computed once for the module: the NCCL all-reduce + separate-update baseline on all GPUs and one GPU on the
+    concatenated batch (Adam, STEPS steps)."""
+    world = _world()
+    tmp = tmp_path_factory.mktemp("dp_oracles")
+    return {"world": world, "nccl": _run(tmp, "nccl", world, "adam", True, False, {}),
+            "single": _single("adam", world, STEPS)}
+
+
+def _assert_close(got, others, kind, name):
+    # fused (P2P kernel) vs NCCL baseline: same arithmetic up to summation order.
+    # vs one GPU on the concatenated batch: sync-BN makes the statistics identical up to ordering noise.  Mixed
+    # abs/rel bound: BN betas start at 0 and stay tiny after a few steps, so a pure relative error would just measure noise.
+    atol, rtol = (5e-4, 5e-3) if kind == "sgd" else (5e-3, 5e-2)   # Adam normalises near-zero gradients
+    for oname, other in others:
+        for i, (a, b) in enumerate(zip(got, other)):
+            assert torch.allclose(a, b, rtol=rtol, atol=atol), (name, oname, i, tuple(a.shape),
+                                                                float((a - b).abs().max()))
+
+
 # (name, environment of the fused run, whole-step CUDA graph)
 VARIANTS = [("default", {}, False),
             ("graph", {}, True),
@@ -109,58 +149,30 @@ VARIANTS = [("default", {}, False),
 
 
 @pytest.mark.parametrize("variant", VARIANTS, ids=[v[0] for v in VARIANTS])
-@pytest.mark.parametrize("kind", ["sgd", "adam"])
-def test_fused_allreduce_update_matches_nccl_baseline_and_single_gpu(kind, variant, tmp_path, monkeypatch):
-    world = _world()
+def test_fused_allreduce_update_matches_nccl_baseline_and_single_gpu(variant, oracles, tmp_path):
     name, env, graph = variant
-    if name != "default" and kind == "sgd":
-        pytest.skip("variants are exercised with Adam (the state-carrying case)")
-    res = {}
-    for baseline in (False, True):
-        for k in ("DCNN_AR_HOISTED", "DCNN_DP_BUCKETS", "DCNN_DP_NVLS"):
-            monkeypatch.delenv(k, raising=False)
-        if not baseline:
-            for k, v in env.items():
-                monkeypatch.setenv(k, v)
-        out = str(tmp_path / f"dp_{kind}_{int(baseline)}.pt")
-        steps = 5 if graph else 3           # a graph run replays from its third call on
-        spawn_bounded(_worker, args=(world, _free_port(), out, kind, baseline, graph and not baseline, steps),
-                      nprocs=world, timeout_s=240)
-        res[baseline] = torch.load(out)
-        if graph:
-            break
-    # fused (P2P kernel) vs NCCL baseline: same arithmetic up to summation order.
-    # vs one GPU on the concatenated batch: sync-BN makes the statistics identical up to ordering noise.  Mixed
-    # abs/rel bound: BN betas start at 0 and stay tiny after 3 steps, so a pure relative error would just measure noise.
-    atol, rtol = (5e-4, 5e-3) if kind == "sgd" else (5e-3, 5e-2)   # Adam normalises near-zero gradients
-    others = []
-    if graph:        # graph replay against the same variant run eagerly for the same number of steps
-        out = str(tmp_path / f"dp_{kind}_eager.pt")
-        spawn_bounded(_worker, args=(world, _free_port(), out, kind, False, False, 5), nprocs=world, timeout_s=240)
-        others.append(("eager", torch.load(out)))
-    else:
-        others += [("nccl-baseline", res[True]), ("single-gpu", _single(kind, world))]
-    for oname, other in others:
-        for i, (a, b) in enumerate(zip(res[False], other)):
-            assert torch.allclose(a, b, rtol=rtol, atol=atol), (name, oname, i, tuple(a.shape),
-                                                                float((a - b).abs().max()))
+    got = _run(tmp_path, name, oracles["world"], "adam", False, graph, env)
+    _assert_close(got, [("nccl-baseline", oracles["nccl"]), ("single-gpu", oracles["single"])], "adam", name)
+
+
+def test_fused_sgd_momentum_matches_single_gpu(tmp_path):
+    world = _world()
+    got = _run(tmp_path, "sgd", world, "sgd", False, False, {})
+    _assert_close(got, [("single-gpu", _single("sgd", world, STEPS))], "sgd", "sgd")
 
 
 @pytest.mark.parametrize("buckets", ["0", "3"])
-def test_checkpoint_resume_of_the_sharded_optimizer_state(buckets, tmp_path, monkeypatch):
+def test_checkpoint_resume_of_the_sharded_optimizer_state(buckets, tmp_path):
     """Fused DP keeps Adam's moments sharded over the replicas.  save_training_state on ONE rank assembles them from
     every replica's shard; a fresh job that loads the checkpoint continues exactly like the uninterrupted one."""
     world = _world()
-    monkeypatch.setenv("DCNN_DP_BUCKETS", buckets)
+    env = {"DCNN_DP_BUCKETS": buckets}
     ck = str(tmp_path / "ck")
-    full, resumed = str(tmp_path / "full.pt"), str(tmp_path / "resumed.pt")
-    spawn_bounded(_worker, args=(world, _free_port(), full, "adam", False, False, 4, (2, ck)), nprocs=world, timeout_s=240)
-    spawn_bounded(_worker, args=(world, _free_port(), resumed, "adam", False, False, 2, None, ck), nprocs=world,
-                  timeout_s=240)
+    a = _run(tmp_path, "full", world, "adam", False, False, env, steps=4, save_at=(2, ck))
+    b = _run(tmp_path, "resumed", world, "adam", False, False, env, steps=2, resume_from=ck)
     blob = torch.load(ck + ".train.pt", weights_only=True)
     assert blob["optimizer_state"]["t"] == 2 and len(blob["optimizer_state"]["m"]) > 0
     assert any(float(t.abs().max()) > 0 for t in blob["optimizer_state"]["m"])
-    a, b = torch.load(full), torch.load(resumed)
     for i, (u, v) in enumerate(zip(a, b)):
         # same kernels, same inputs; only the split-K reduction order of wgrad varies run to run
         assert torch.allclose(u, v, rtol=1e-3, atol=1e-4), (i, tuple(u.shape), float((u - v).abs().max()))

@@ -48,7 +48,9 @@ def test_model_forward_backward_matches_cpu(factory, shape, tol, exact, monkeypa
     if exact:
         monkeypatch.setenv("DCNN_DISABLE_TC", "1")
     else:
-        tol = max(tol * 30, 6e-3)
+        # every convolution of both models is on the tensor cores now (the small-channel MNIST layers too: TMA-padded
+        # reduction, packed stem), so both get the same statistical TF32 bound
+        tol = 6e-2
     torch.manual_seed(0)
     cpu = factory()
     cpu.set_seed(1)

@@ -1,8 +1,6 @@
 """SPMD PipelineEngine on real GPUs (>= 2): stages over NCCL per-link communicators == the single-device reference, in
 FP32-exact mode (CUDA-core GEMMs) so the comparison is tight; also with per-op CUDA graphs (DCNN_PIPE_GRAPH=1).
-
-Written after the last GPU minutes of its session: opt-in until its first hardware run (DCNN_TEST_PENDING=1).  Every
-multi-process launch is bounded (spawn_bounded kills ranks that outlive the deadline)."""
+Every multi-process launch is bounded (spawn_bounded kills ranks that outlive the deadline)."""
 import os
 import socket
 
@@ -15,9 +13,7 @@ from dcnn_b200.partitioner import NaivePartitioner
 from dcnn_b200.utils.spawn import spawn_bounded
 from tests.test_pipeline_inprocess import _data, _model, _reference_run
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("DCNN_TEST_PENDING") != "1",
-                                 reason="awaiting first hardware validation (set DCNN_TEST_PENDING=1)")]
+pytestmark = pytest.mark.gpu
 
 
 def _free_port():
