@@ -376,6 +376,7 @@ def main():
     gb = B * R
     value = gb * args.steps / (ms / 1000.0)
     e2e = gb * args.steps / (ms_e2e / 1000.0)
+    out = None
     if rank == 0:
         base = None
         try:
@@ -411,9 +412,58 @@ def main():
             "gpu_launches": int(launches),  # per rank, max over ranks
             "final_loss": final_loss,
         }
-        print(json.dumps(out), flush=True)
+    # ---- BASELINE.json's multi-GPU configuration is pipeline x data parallel with a bubble fraction; the headline value
+    # above is the data-parallel run (the faster arrangement on one NVSwitch box).  With --gpus N > 1 and the default
+    # parallelism, the same N GPUs then run the pipeline arrangement (N = 8: 4 stages x 2 replicas, the named config;
+    # N = 4: 4 stages; N = 2: 2 stages) in a fresh process group of child processes, and its line is attached as
+    # "pipeline" -- throughput, ms/step and bubble fraction measured by the same protocol.  BENCH_PIPELINE=0 skips it.
+    pipe = None
     if world > 1:
         dist.destroy_process_group()
+    if world > 1 and args.parallelism == "auto" and not cpu_mode and os.environ.get("BENCH_PIPELINE", "1") == "1" \
+            and os.environ.get("BENCH_CHILD") != "1":
+        pipe = pipeline_child(args, world, rank)
+    if rank == 0:
+        if pipe is not None:
+            out["pipeline"] = pipe
+            if isinstance(pipe, dict) and pipe.get("pipeline_bubble_fraction") is not None:
+                out["pipeline_bubble_fraction"] = pipe["pipeline_bubble_fraction"]
+        print(json.dumps(out), flush=True)
+
+
+def pipeline_child(args, world, rank):
+    """Every rank starts one child (same GPU) that joins a new process group on MASTER_PORT + 1 and runs this script
+    with --parallelism pp...; rank 0 returns the child's JSON line (or a one-line reason)."""
+    par = {2: "pp2", 4: "pp4", 8: "pp4xdp2"}.get(world)
+    if par is None:
+        return None
+    stages = 4 if world >= 4 else 2
+    mb = int(os.environ.get("BENCH_PIPELINE_MICROBATCHES", 4 * stages))
+    env = dict(os.environ, BENCH_CHILD="1", MASTER_PORT=str(int(os.environ.get("MASTER_PORT", "29500")) + 1),
+               DCNN_PIPE_GRAPH=os.environ.get("DCNN_PIPE_GRAPH", "1"),
+               BENCH_PARTITION=os.environ.get("BENCH_PARTITION", "measured"))
+    for k in list(env):
+        if k.startswith("TORCHELASTIC") or k in ("TORCH_NCCL_ASYNC_ERROR_HANDLING",):
+            env.pop(k)
+    steps = max(5, min(args.steps, 20))
+    cmd = [sys.executable, os.path.abspath(__file__), "--gpus", str(world), "--steps", str(steps), "--warmup", "5",
+           "--parallelism", par, "--microbatches", str(mb), "--batch", str(args.batch), "--model", args.model]
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=float(os.environ.get("BENCH_PIPELINE_TIMEOUT", 240)))
+    except subprocess.TimeoutExpired:
+        return {"unavailable": f"{par} child run exceeded its time limit"} if rank == 0 else None
+    if rank != 0:
+        return None
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    if r.returncode != 0 or not lines:
+        tail = (r.stderr.strip().splitlines() or ["no output"])[-1][:200]
+        return {"unavailable": f"{par} child run failed: {tail}"}
+    d = json.loads(lines[-1])
+    return {k: d.get(k) for k in ("value", "unit", "ms_per_step", "steps", "warmup", "pipeline_bubble_fraction", "e2e",
+                                  "gpu_launches", "final_loss", "run")} | {
+        "parallelism": d["config"]["parallelism"], "microbatches": d["config"]["microbatches"],
+        "pipeline_stages": d["config"]["pipeline_stages"], "dp_replicas": d["config"]["dp_replicas"],
+        "global_batch": d["config"]["global_batch"], "schedule": os.environ.get("SCHEDULE", "semi_async")}
 
 
 def step_launches(step, x, t, _lib):

@@ -54,6 +54,19 @@ def main():
 
     m, opt, dp = build(False)
     fused_ms = bench(dp, m)
+    kernel_us = {}
+    if os.environ.get("AR_PROFILE", "1") == "1":
+        # where the time of one call goes: device time per kernel (CUPTI through torch.profiler), rank 0
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(10):
+                dp.reduce_and_update()
+            torch.cuda.synchronize()
+        for ev in prof.key_averages():
+            t = getattr(ev, "device_time_total", None) or getattr(ev, "cuda_time_total", 0.0)
+            if t and ev.count:
+                kernel_us[ev.key[:60]] = round(t / ev.count, 1)
+        dist.barrier()
     nbytes = dp.bytes_over_nvlink_per_step()
     total_params = dp.n
     del dp, m, opt
@@ -83,7 +96,7 @@ def main():
         floor_ms = nbytes / bw * 1e3
         hbm_ms = 7 * 4 * total_params / world / 6.5e12 * 1e3
         print(json.dumps({"world": world, "params": total_params, "nvlink_bytes_per_dir": nbytes,
-                          "fused_ms": round(fused_ms, 4), "fused_ms_by_ctas": sweep, "nccl_allreduce_plus_update_ms": round(nccl_ms, 4),
+                          "fused_ms": round(fused_ms, 4), "fused_kernel_us": kernel_us, "fused_ms_by_ctas": sweep, "nccl_allreduce_plus_update_ms": round(nccl_ms, 4),
                           "nvlink_floor_ms": round(floor_ms, 4), "hbm_floor_ms": round(hbm_ms, 4),
                           "fraction_of_nvlink_roofline": round(floor_ms / fused_ms, 3),
                           "speedup_vs_nccl_path": round(nccl_ms / fused_ms, 2), "nvlink_GBps_assumed": bw / 1e9}))

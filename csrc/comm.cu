@@ -41,101 +41,124 @@ struct ArParams {
   int generic_gather;  // 0 (default): loads-first gather for 2 / 4 / 8 replicas; 1: the load-add loop (other world sizes, DCNN_AR_HOISTED=0)
 };
 
-// Own slice plus the W-1 peers' slices.  All peer loads are issued before the first one is consumed: an NVLink load
-// takes microseconds, and a load-add-load-add chain would keep only one of them in flight per thread.  The summation
-// order (own, rank+1, rank+2, ...) is the same as the generic loop's, so the result is bit-identical to it.
-template <int W>
-__device__ __forceinline__ float4 gather_sum(const ArParams& p, long long e) {
-  float4 v[W];
-  v[0] = *reinterpret_cast<const float4*>(p.grads[p.rank] + e);
+// One optimizer step on four consecutive elements: gradient g (already averaged), parameter w, state at s (local shard).
+__device__ __forceinline__ float4 ar_update(const ArParams& p, float lr, float bc1, float bc2, float4 g, float4 w,
+                                            long long s) {
+  float gg[4] = {g.x, g.y, g.z, g.w};
+  float ww[4] = {w.x, w.y, w.z, w.w};
+  if (p.mode == 0) {
 #pragma unroll
-  for (int r = 1; r < W; ++r) v[r] = ld_peer4(p.grads[(p.rank + r) & (W - 1)] + e);
-  float4 g = v[0];
+    for (int j = 0; j < 4; ++j) ww[j] -= lr * gg[j];
+  } else if (p.mode == 1) {
+    float4 v = *reinterpret_cast<float4*>(p.s1 + s);
+    float vv[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-  for (int r = 1; r < W; ++r) { g.x += v[r].x; g.y += v[r].y; g.z += v[r].z; g.w += v[r].w; }
-  return g;
+    for (int j = 0; j < 4; ++j) { vv[j] = p.a * vv[j] - lr * gg[j]; ww[j] += vv[j]; }
+    *reinterpret_cast<float4*>(p.s1 + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+  } else {
+    float4 m4 = *reinterpret_cast<float4*>(p.s1 + s), v4 = *reinterpret_cast<float4*>(p.s2 + s);
+    float mm[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mm[j] = p.a * mm[j] + (1.f - p.a) * gg[j];
+      vv[j] = p.b * vv[j] + (1.f - p.b) * gg[j] * gg[j];
+      float upd = lr * (mm[j] / bc1) / (sqrtf(vv[j] / bc2) + p.eps);
+      if (p.wd > 0.f) {
+        if (p.mode == 3) ww[j] -= p.wd * lr * ww[j];
+        else upd += p.wd * lr * ww[j];
+      }
+      ww[j] -= upd;
+    }
+    *reinterpret_cast<float4*>(p.s1 + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+    *reinterpret_cast<float4*>(p.s2 + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+  }
+  return make_float4(ww[0], ww[1], ww[2], ww[3]);
 }
 
+// W = the number of replicas when it is 2, 4 or 8: a thread handles TWO 16-byte slices per iteration and issues all
+// 2 * (W - 1) peer loads before the first one is consumed -- an NVLink load takes microseconds, and a load-add-load-add
+// chain would keep only one of them in flight per thread.  W = 0: any number of replicas, plain load-add loop.  The
+// summation order (own, rank+1, rank+2, ...) is the same in both, so the results are bit-identical.
+// The rendezvous epoch is (*epoch_counter + 1); the last block to finish stores it back, so the counter needs no kernel of
+// its own and the launch replays from a CUDA graph.
+template <int W>
 __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __grid_constant__ ArParams pp) {
-  ArParams p = pp;
-  const unsigned long long epoch = *p.epoch_ptr;
-  if (p.hyper != nullptr) { p.lr = p.hyper[0]; p.bc1 = p.hyper[1]; p.bc2 = p.hyper[2]; }
+  const unsigned long long epoch = *pp.epoch_ptr + 1;
+  float lr = pp.lr, bc1 = pp.bc1, bc2 = pp.bc2;
+  if (pp.hyper != nullptr) { lr = pp.hyper[0]; bc1 = pp.hyper[1]; bc2 = pp.hyper[2]; }
+  const int rank = pp.rank, world = pp.world;
   // every block waits until all replicas have finished producing gradients for this epoch
   if (threadIdx.x == 0) {
-    if (blockIdx.x == 0) peer_signal(p.start_flags, p.rank, p.world, epoch);
-    peer_wait(p.start_flags, p.rank, p.world, epoch);
+    if (blockIdx.x == 0) peer_signal(pp.start_flags, rank, world, epoch);
+    peer_wait(pp.start_flags, rank, world, epoch);
   }
   __syncthreads();
 
-  const long long n4 = (p.shard_end - p.shard_begin) >> 2;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long e = p.shard_begin + i * 4;
-    // reduce-scatter: sum this 16-byte slice over all replicas (own copy first, peers over NVLink)
-    float4 g;
-    switch (p.generic_gather ? 0 : p.world) {
-      case 2: g = gather_sum<2>(pp, e); break;
-      case 4: g = gather_sum<4>(pp, e); break;
-      case 8: g = gather_sum<8>(pp, e); break;
-      default: {
-        g = *reinterpret_cast<const float4*>(pp.grads[p.rank] + e);
-#pragma unroll 1
-        for (int r = 1; r < p.world; ++r) {
-          const int src = (p.rank + r) % p.world;
-          const float4 v = ld_peer4(pp.grads[src] + e);
-          g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
-        }
+  const float* gown = pp.grads[rank];
+  const float* pown = pp.params[rank];
+  const long long n4 = (pp.shard_end - pp.shard_begin) >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const float inv = pp.inv_world;
+  if (W != 0) {
+    constexpr int WW = W > 0 ? W : 1;
+    const float* gpeer[WW];
+#pragma unroll
+    for (int r = 1; r < WW; ++r) gpeer[r] = pp.grads[(rank + r) & (WW - 1)];
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += 2 * stride) {
+      const long long e0 = pp.shard_begin + i * 4;
+      const bool two = i + stride < n4;
+      const long long e1 = two ? e0 + stride * 4 : e0;
+      float4 v0[WW], v1[WW];
+      // reduce-scatter: this 16-byte slice of every replica (own copy first, peers over NVLink)
+#pragma unroll
+      for (int r = 1; r < WW; ++r) { v0[r] = ld_peer4(gpeer[r] + e0); v1[r] = ld_peer4(gpeer[r] + e1); }
+      v0[0] = *reinterpret_cast<const float4*>(gown + e0);
+      v1[0] = *reinterpret_cast<const float4*>(gown + e1);
+      const float4 w0 = *reinterpret_cast<const float4*>(pown + e0), w1 = *reinterpret_cast<const float4*>(pown + e1);
+      float4 g0 = v0[0], g1 = v1[0];
+#pragma unroll
+      for (int r = 1; r < WW; ++r) {
+        g0.x += v0[r].x; g0.y += v0[r].y; g0.z += v0[r].z; g0.w += v0[r].w;
+        g1.x += v1[r].x; g1.y += v1[r].y; g1.z += v1[r].z; g1.w += v1[r].w;
+      }
+      g0.x *= inv; g0.y *= inv; g0.z *= inv; g0.w *= inv;
+      g1.x *= inv; g1.y *= inv; g1.z *= inv; g1.w *= inv;
+      const float4 o0 = ar_update(pp, lr, bc1, bc2, g0, w0, e0 - pp.shard_begin);
+      // all-gather: publish the updated slice to every replica (own copy included)
+#pragma unroll
+      for (int r = 0; r < WW; ++r) *reinterpret_cast<float4*>(pp.params[(rank + r) & (WW - 1)] + e0) = o0;
+      if (two) {
+        const float4 o1 = ar_update(pp, lr, bc1, bc2, g1, w1, e1 - pp.shard_begin);
+#pragma unroll
+        for (int r = 0; r < WW; ++r) *reinterpret_cast<float4*>(pp.params[(rank + r) & (WW - 1)] + e1) = o1;
       }
     }
-    g.x *= p.inv_world; g.y *= p.inv_world; g.z *= p.inv_world; g.w *= p.inv_world;
-    float4 w = *reinterpret_cast<const float4*>(pp.params[p.rank] + e);
-    float gg[4] = {g.x, g.y, g.z, g.w};
-    float ww[4] = {w.x, w.y, w.z, w.w};
-    const long long s = e - p.shard_begin;
-    if (p.mode == 0) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) ww[j] -= p.lr * gg[j];
-    } else if (p.mode == 1) {
-      float4 v = *reinterpret_cast<float4*>(p.s1 + s);
-      float vv[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) { vv[j] = p.a * vv[j] - p.lr * gg[j]; ww[j] += vv[j]; }
-      *reinterpret_cast<float4*>(p.s1 + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-    } else {
-      float4 m4 = *reinterpret_cast<float4*>(p.s1 + s), v4 = *reinterpret_cast<float4*>(p.s2 + s);
-      float mm[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        mm[j] = p.a * mm[j] + (1.f - p.a) * gg[j];
-        vv[j] = p.b * vv[j] + (1.f - p.b) * gg[j] * gg[j];
-        float upd = p.lr * (mm[j] / p.bc1) / (sqrtf(vv[j] / p.bc2) + p.eps);
-        if (p.wd > 0.f) {
-          if (p.mode == 3) ww[j] -= p.wd * p.lr * ww[j];
-          else upd += p.wd * p.lr * ww[j];
-        }
-        ww[j] -= upd;
-      }
-      *reinterpret_cast<float4*>(p.s1 + s) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-      *reinterpret_cast<float4*>(p.s2 + s) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-    }
-    const float4 out = make_float4(ww[0], ww[1], ww[2], ww[3]);
-    // all-gather: publish the updated slice to every replica (own copy included)
+  } else {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += stride) {
+      const long long e = pp.shard_begin + i * 4;
+      float4 g = *reinterpret_cast<const float4*>(gown + e);
 #pragma unroll 1
-    for (int r = 0; r < p.world; ++r) {
-      const int dst = (p.rank + r) % p.world;
-      *reinterpret_cast<float4*>(pp.params[dst] + e) = out;   // pointer tables are read from the parameter bank
+      for (int r = 1; r < world; ++r) {
+        const float4 v = ld_peer4(pp.grads[(rank + r) % world] + e);
+        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+      }
+      g.x *= inv; g.y *= inv; g.z *= inv; g.w *= inv;
+      const float4 w = *reinterpret_cast<const float4*>(pown + e);
+      const float4 out = ar_update(pp, lr, bc1, bc2, g, w, e - pp.shard_begin);
+#pragma unroll 1
+      for (int r = 0; r < world; ++r) *reinterpret_cast<float4*>(pp.params[(rank + r) % world] + e) = out;
     }
   }
-  // this rank may only zero ITS OWN gradient buffer once every peer has read it: that is guaranteed after the
-  // done barrier below, so zeroing is done by dcnn_peer_barrier + the next backward's producers (grads are
-  // overwritten or zero-filled by zero_after_done_kernel).
-  __threadfence_system();
+  // Gradient zeroing: a rank may only zero ITS OWN gradient buffer once every peer has read it, i.e. after the "done"
+  // signals below have arrived from all of them: wait_done_zero_kernel does that.
   __syncthreads();
   if (threadIdx.x == 0) {
-    const unsigned int done = atomicAdd(p.block_counter, 1u);
+    __threadfence_system();   // the block's parameter stores (ordered before this by the barrier) reach the peers first
+    const unsigned int done = atomicAdd(pp.block_counter, 1u);
     if (done == gridDim.x - 1) {
-      *p.block_counter = 0;
-      peer_signal(p.done_flags, p.rank, p.world, epoch);
+      *pp.block_counter = 0;
+      *const_cast<unsigned long long*>(pp.epoch_ptr) = epoch;
+      peer_signal(pp.done_flags, rank, world, epoch);
     }
   }
 }
@@ -234,13 +257,16 @@ DCNN_API int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* 
     p.generic_gather = hoisted ? 0 : 1;
   }
   if (num_blocks <= 0) num_blocks = num_sms();
-  epoch_bump_kernel<<<1, 1, 0, stream>>>(epoch_counter);
-  fused_allreduce_update_kernel<<<num_blocks, 512, 0, stream>>>(p);
+  const int w = p.generic_gather ? 0 : world;
+  if (w == 2) fused_allreduce_update_kernel<2><<<num_blocks, 512, 0, stream>>>(p);
+  else if (w == 4) fused_allreduce_update_kernel<4><<<num_blocks, 512, 0, stream>>>(p);
+  else if (w == 8) fused_allreduce_update_kernel<8><<<num_blocks, 512, 0, stream>>>(p);
+  else fused_allreduce_update_kernel<0><<<num_blocks, 512, 0, stream>>>(p);
   DCNN_CHECK_LAUNCH();
   // same CTA count as the reduce kernel: a bucket launch on the side stream (32 CTAs) must not fill the SMs that the
   // backward pass is using with threads that spin on the peers' done flags
   wait_done_zero_kernel<<<num_blocks, 512, 0, stream>>>(p.done_flags, rank, world, epoch_counter, grad_ptrs[rank], n);
   DCNN_CHECK_LAUNCH();
-  DCNN_COUNT_LAUNCH(3);
+  DCNN_COUNT_LAUNCH(2);
   return 0;
 }

@@ -47,15 +47,18 @@ struct ConvTcParams {
 
 // =====================================================================================================
 // Epilogue shared by the three kernels below.  Four warps (128 threads, named barriers 1 and 2) turn one accumulator
-// tile of 128 rows x CHUNKS*32 columns into (a) a TMA store (or TMA reduce-add) of the output tile and (b) BatchNorm
-// partial statistics:
-//   epi_begin   the staging buffer is free again (previous TMA stores have read it); row-validity flags of edge tiles
-//   epi_drain   tcgen05.ld -> (+bias) -> 128B-swizzled staging buffer, one [128 rows][32 columns] box per chunk
-//   (caller)    hands the TMEM buffer back to the MMA warp, fence.proxy.async, named barrier
-//   epi_finish  TMA store / reduce-add per chunk (rows and columns outside the tensor are clipped by the TMA unit),
-//               then the shifted single-pass statistics (sum(x-k), sum((x-k)^2), k = the tile's first row) with
-//               conflict-free swizzled reads: thread (column cl, row group rg) sums 32 rows, 4 row groups are merged
-//               through `red`.
+// tile of 128 rows x CHUNKS*32 columns into (a) TMA stores (or TMA reduce-adds) of the output tile and (b) BatchNorm
+// partial statistics.  The tile moves through a RING of [128 rows][32 columns] staging buffers, one 32-column chunk
+// at a time, so that the TMA store of a chunk, the statistics pass over it and the TMEM drain of the next chunk overlap:
+//   per chunk   tcgen05.ld -> (+bias) -> 128B-swizzled staging buffer -> fence.proxy.async -> ONE named barrier
+//               -> thread 0: TMA store / reduce-add of that chunk (rows and columns outside the tensor are clipped by
+//                  the TMA unit), its own bulk group
+//               -> all: shifted single-pass statistics of the chunk (sum(x-k), sum((x-k)^2), k = the tile's first row)
+//                  with conflict-free swizzled reads: thread (column cl, row group rg) sums 32 rows
+//   per tile    the TMEM buffer goes back to the MMA warp right after its last tcgen05.ld; the four row groups are merged
+//               through `red` and written as one partial-statistics tile.
+// A staging buffer is reused RING chunks later; thread 0 keeps at most RING-2 bulk groups unfinished before the barrier
+// of a chunk, which frees the buffer of the NEXT chunk (cp.async.bulk.wait_group.read).
 // =====================================================================================================
 struct EpiTile {
   int n0, oh0, ow0;     // first output pixel of the tile
@@ -67,33 +70,44 @@ struct EpiTile {
   bool full;            // no row of the tile is outside [N, OH, OW]
 };
 
-__device__ __forceinline__ void epi_begin(const ConvTcParams& p, const EpiTile& t, uint8_t* row_valid, int r,
-                                          bool issuer) {
-  if (issuer) tma_store_wait_read();  // earlier stores no longer read the staging buffer
-  if (p.partials != nullptr && !t.full) {
+constexpr int kEpiRing = 4;                                  // staging buffers of 16 KB
+constexpr int epi_red_floats(int cols) { return 9 * cols; }  // [2][4 row groups][cols] sums + [cols] shifts
+
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read_n() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+
+template <int CHUNKS, typename Release>
+__device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMap* tmO, const EpiTile& t,
+                                         uint32_t tmem_d, uint8_t* staging, float* red, uint8_t* row_valid, int r, int e,
+                                         uint32_t& ring_pos, Release release) {
+  constexpr int RS = CHUNKS * 32;  // row stride of `red`
+  const bool stats = p.partials != nullptr;
+  if (stats && !t.full) {
     const int w_l = r % t.obw, h_l = (r / t.obw) % t.obh, n_l = r / (t.obw * t.obh);
     row_valid[r] = ((t.n0 + n_l < p.N) && (t.oh0 + h_l < p.OH) && (t.ow0 + w_l < p.OW)) ? 1 : 0;
   }
-  asm volatile("bar.sync 1, 128;" ::: "memory");
-}
-
-template <int CHUNKS>
-__device__ __forceinline__ void epi_drain(const ConvTcParams& p, uint32_t tmem_d, uint8_t* staging, int r,
-                                          int col_base) {
+  const int cl = e & 31, rg = e >> 5;
+  int cnt = kBM, nch = 0;
 #pragma unroll 1
   for (int ch = 0; ch < CHUNKS; ++ch) {
-    if (col_base + ch * 32 >= p.Cout) break;
+    const int c0 = t.col_base + ch * 32;
+    if (c0 >= p.Cout) break;
+    nch = ch + 1;
     uint32_t v[32];
     tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
     tmem_ld_wait();
-    uint8_t* dst = staging + ch * (kBM * 128) + r * 128;
+    if (ch == CHUNKS - 1 || c0 + 32 >= p.Cout) release();   // the accumulator is in registers: TMEM back to the MMA warp
+    uint8_t* buf = staging + (ring_pos % kEpiRing) * (kBM * 128);
+    uint8_t* dst = buf + r * 128;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float4 o;
       o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
       o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
       if (p.bias != nullptr) {
-        const int c = col_base + ch * 32 + 4 * j;
+        const int c = c0 + 4 * j;
         if (c < p.Cout) {  // Cout % 4 == 0 on this path
           const float4 b = ldg4(p.bias + c);
           o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
@@ -101,69 +115,59 @@ __device__ __forceinline__ void epi_drain(const ConvTcParams& p, uint32_t tmem_d
       }
       *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
     }
-  }
-}
-
-template <int CHUNKS>
-__device__ __forceinline__ void epi_finish(const ConvTcParams& p, const CUtensorMap* tmO, const EpiTile& t,
-                                           uint8_t* staging, float* red, const uint8_t* row_valid, int e) {
-  constexpr int RS = CHUNKS * 32;  // row stride of `red`
-  if (e == 0) {
-    for (int ch = 0; ch < CHUNKS; ++ch) {
-      const int c = t.col_base + ch * 32;
-      if (c >= p.Cout) break;
-      if (p.accumulate) tma_reduce_add_4d(tmO, staging + ch * (kBM * 128), c, t.ow0, t.oh0, t.n0);
-      else tma_store_4d(tmO, staging + ch * (kBM * 128), c, t.ow0, t.oh0, t.n0);
+    fence_proxy_async();
+    if (e == 0) tma_store_wait_read_n<kEpiRing - 2>();   // the next chunk's buffer is no longer being read
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (e == 0) {
+      if (p.accumulate) tma_reduce_add_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
+      else tma_store_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
+      tma_store_commit();
     }
-    tma_store_commit();
-  }
-  if (p.partials == nullptr) return;
-  const int cl = e & 31, rg = e >> 5;
-  int cnt = kBM;
-  if (!t.full) {
-    cnt = 0;
-    for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
-  }
-  for (int ch = 0; ch < CHUNKS; ++ch) {
-    if (t.col_base + ch * 32 >= p.Cout) break;
-    const uint8_t* src = staging + ch * (kBM * 128);
-    const float kshift = *reinterpret_cast<const float*>(src + ((cl >> 2) << 4) + ((cl & 3) << 2));  // row 0
-    float s = 0.f, qq = 0.f;
-    if (t.full) {
+    ++ring_pos;
+    if (stats) {
+      if (ch == 0 && !t.full) {
+        cnt = 0;
+        for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
+      }
+      const uint32_t coff = ((cl & 3) << 2);
+      const float kshift = *reinterpret_cast<const float*>(buf + ((cl >> 2) << 4) + coff);  // row 0
+      float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+      if (t.full) {
 #pragma unroll 8
-      for (int i = 0; i < 32; ++i) {
-        const int rr = rg * 32 + i;
-        const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) + ((cl & 3) << 2));
-        const float d = x - kshift;
-        s += d;
-        qq = fmaf(d, d, qq);
+        for (int i = 0; i < 32; i += 2) {
+          const int ra = rg * 32 + i, rb = ra + 1;
+          const float xa = *reinterpret_cast<const float*>(buf + ra * 128 + (((cl >> 2) ^ (ra & 7)) << 4) + coff);
+          const float xb = *reinterpret_cast<const float*>(buf + rb * 128 + (((cl >> 2) ^ (rb & 7)) << 4) + coff);
+          const float da = xa - kshift, db = xb - kshift;
+          s0 += da; q0 = fmaf(da, da, q0);
+          s1 += db; q1 = fmaf(db, db, q1);
+        }
+      } else {
+        for (int i = 0; i < 32; ++i) {
+          const int rr = rg * 32 + i;
+          const float x = *reinterpret_cast<const float*>(buf + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) + coff);
+          const float d = row_valid[rr] ? x - kshift : 0.f;
+          s0 += d;
+          q0 = fmaf(d, d, q0);
+        }
       }
-    } else {
-      for (int i = 0; i < 32; ++i) {
-        const int rr = rg * 32 + i;
-        const float x = *reinterpret_cast<const float*>(src + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) + ((cl & 3) << 2));
-        const float d = row_valid[rr] ? x - kshift : 0.f;
-        s += d;
-        qq = fmaf(d, d, qq);
-      }
+      red[(0 * 4 + rg) * RS + ch * 32 + cl] = s0 + s1;
+      red[(1 * 4 + rg) * RS + ch * 32 + cl] = q0 + q1;
+      if (rg == 0) red[8 * RS + ch * 32 + cl] = kshift;
     }
-    red[(0 * 4 + rg) * RS + ch * 32 + cl] = s;
-    red[(1 * 4 + rg) * RS + ch * 32 + cl] = qq;
   }
+  if (!stats) return;
   asm volatile("bar.sync 2, 128;" ::: "memory");
-  for (int j = e; j < RS; j += 128) {
+  for (int j = e; j < nch * 32; j += 128) {
     const int c = t.col_base + j;
-    if (c < p.Cout) {
-      const int ch = j >> 5, cl2 = j & 31;
-      const float kshift = *reinterpret_cast<const float*>(staging + ch * (kBM * 128) + ((cl2 >> 2) << 4) + ((cl2 & 3) << 2));
-      const float s = red[(0 * 4 + 0) * RS + j] + red[(0 * 4 + 1) * RS + j] + red[(0 * 4 + 2) * RS + j] +
-                      red[(0 * 4 + 3) * RS + j];
-      const float qq = red[(1 * 4 + 0) * RS + j] + red[(1 * 4 + 1) * RS + j] + red[(1 * 4 + 2) * RS + j] +
-                       red[(1 * 4 + 3) * RS + j];
-      const float n = (float)cnt;
-      p.partials[((long long)t.stat_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
-      p.partials[((long long)t.stat_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
-    }
+    const float kshift = red[8 * RS + j];
+    const float s = red[(0 * 4 + 0) * RS + j] + red[(0 * 4 + 1) * RS + j] + red[(0 * 4 + 2) * RS + j] +
+                    red[(0 * 4 + 3) * RS + j];
+    const float qq = red[(1 * 4 + 0) * RS + j] + red[(1 * 4 + 1) * RS + j] + red[(1 * 4 + 2) * RS + j] +
+                     red[(1 * 4 + 3) * RS + j];
+    const float n = (float)cnt;
+    p.partials[((long long)t.stat_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
+    p.partials[((long long)t.stat_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
   }
   if (e == 0 && t.write_count) p.partials[(long long)t.stat_tiles * 2 * p.Cout + t.stat_tile] = (float)cnt;
 }
@@ -187,8 +191,8 @@ struct ConvTc2Smem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kPipeBytes = STAGES * kStageBytes;
   static constexpr int kChunks = BN / 32;
-  static constexpr int kStagingBytes = kChunks * kBM * 128;
-  static constexpr int kRedBytes = 2 * 4 * BN * 4;  // [2][4 row groups][BN]
+  static constexpr int kStagingBytes = kEpiRing * kBM * 128;
+  static constexpr int kRedBytes = epi_red_floats(BN) * 4;
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
@@ -201,8 +205,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
                                                                const __grid_constant__ CUtensorMap tmO,
                                                                const __grid_constant__ ConvTcParams p) {
   using S = ConvTc2Smem<BN, STAGES>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle, computed as an offset so that the compiler keeps the shared address space
+  // (a pointer rebuilt from an integer becomes generic: LD.E / ST.E instead of LDS / STS in the epilogue)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* staging = smem + S::kPipeBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
   uint64_t* empty_bar = full_bar + STAGES;
@@ -303,7 +309,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
     const int r = q * 32 + lane;     // tile row owned by this thread
     const int e = threadIdx.x - 64;  // 0..127
     int as = 0;
-    uint32_t aphase = 0;
+    uint32_t aphase = 0, ring_pos = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
@@ -319,15 +325,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
 
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
-      epi_begin(p, t, row_valid, r, e == 0);
-      epi_drain<S::kChunks>(p, tmem_base + as * BN + (uint32_t(q * 32) << 16), staging, r, t.col_base);
-      // accumulator fully read: hand the TMEM stage back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
-      fence_proxy_async();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      epi_finish<S::kChunks>(p, &tmO, t, staging, red, row_valid, e);
+      uint64_t* rel_bar = &tmem_empty_bar[as];
+      epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + (uint32_t(q * 32) << 16), staging, red, row_valid, r, e,
+                           ring_pos, [&]() {
+                             tc_fence_before();
+                             __syncwarp();
+                             if (lane == 0) mbar_arrive(rel_bar);
+                           });
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     if (e == 0) tma_store_wait_all();
@@ -367,8 +371,8 @@ struct ConvTc3Smem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kPipeBytes = STAGES * kStageBytes;
   static constexpr int kChunks = BN / 32;
-  static constexpr int kStagingBytes = kChunks * kBM * 128;
-  static constexpr int kRedBytes = 2 * 4 * BN * 4;
+  static constexpr int kStagingBytes = kEpiRing * kBM * 128;
+  static constexpr int kRedBytes = epi_red_floats(BN) * 4;
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
@@ -384,8 +388,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
                                                                const __grid_constant__ ConvTc3Params pp) {
   using S = ConvTc3Smem<BN, STAGES>;
   const ConvTcParams& p = pp.b;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle, computed as an offset so that the compiler keeps the shared address space
+  // (a pointer rebuilt from an integer becomes generic: LD.E / ST.E instead of LDS / STS in the epilogue)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* staging = smem + S::kPipeBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
   uint64_t* empty_bar = full_bar + STAGES;
@@ -490,7 +496,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
     const int r = q * 32 + lane;     // row inside the half
     const int e = threadIdx.x - 64;  // 0..127
     int as = 0;
-    uint32_t aphase = 0;
+    uint32_t aphase = 0, ring_pos = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
@@ -509,18 +515,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
         t.stat_tile = m_tile * 2 + half; t.stat_tiles = 2 * p.m_tiles; t.write_count = (n_tile == 0);
         t.full = (t.n0 + pp.obn <= p.N) && (t.oh0 + pp.obh <= p.OH) && (t.ow0 + pp.obw <= p.OW);
 
-        epi_begin(p, t, row_valid, r, e == 0);
-        epi_drain<S::kChunks>(p, tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16), staging, r,
-                              t.col_base);
-        if (half == 1) {
-          // both halves read: hand the accumulator buffer back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
-        }
-        fence_proxy_async();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        epi_finish<S::kChunks>(p, &tmO, t, staging, red, row_valid, e);
+        uint64_t* rel_bar = &tmem_empty_bar[as];
+        epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16), staging, red,
+                             row_valid, r, e, ring_pos, [&]() {
+                               if (half == 1) {   // both halves read: hand the accumulator buffer back to the MMA warp
+                                 tc_fence_before();
+                                 __syncwarp();
+                                 if (lane == 0) mbar_arrive(rel_bar);
+                               }
+                             });
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
@@ -560,8 +563,8 @@ struct ConvTc5Smem {
   static constexpr int kPipeBytes = STAGES * kStageBytes;
   static constexpr int kHalfCols = 128;            // the epilogue drains 128 columns at a time
   static constexpr int kChunks = kHalfCols / 32;
-  static constexpr int kStagingBytes = kChunks * kBM * 128;
-  static constexpr int kRedBytes = 2 * 4 * kHalfCols * 4;
+  static constexpr int kStagingBytes = kEpiRing * kBM * 128;
+  static constexpr int kRedBytes = epi_red_floats(kHalfCols) * 4;
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
@@ -575,8 +578,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
                     const __grid_constant__ CUtensorMap tmO, const __grid_constant__ ConvTcParams p) {
   using S = ConvTc5Smem<STAGES>;
   constexpr int BN = S::kBN, HC = S::kHalfCols;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle, computed as an offset so that the compiler keeps the shared address space
+  // (a pointer rebuilt from an integer becomes generic: LD.E / ST.E instead of LDS / STS in the epilogue)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* staging = smem + S::kPipeBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
   uint64_t* empty_bar = full_bar + STAGES;
@@ -683,7 +688,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const int r = q * 32 + lane;
     const int e = threadIdx.x - 64;
     int as = 0;
-    uint32_t aphase = 0;
+    uint32_t aphase = 0, ring_pos = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = (tile / p.n_tiles) * 2 + (int)cta_rank;
@@ -704,18 +709,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         t.full = (t.n0 + p.bn <= p.N) && (t.oh0 + p.bh <= p.OH) && (t.ow0 + p.bw <= p.OW);
         const bool cols_live = live && t.col_base < p.Cout;
 
-        epi_begin(p, t, row_valid, r, e == 0);
+        // accumulator fully read by this warp: tell the leader's MMA thread (one arrival per epilogue warp per CTA)
+        const uint32_t rel_bar = map_to_cta(smem_u32(&tmem_empty_bar[as]), 0);
+        auto release = [&]() {
+          if (half == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(rel_bar);
+          }
+        };
         if (cols_live)
-          epi_drain<S::kChunks>(p, tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16), staging, r, t.col_base);
-        if (half == 1) {
-          // accumulator fully read by this warp: tell the leader's MMA thread (one arrival per epilogue warp per CTA)
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&tmem_empty_bar[as]), 0));
-        }
-        fence_proxy_async();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (cols_live) epi_finish<S::kChunks>(p, &tmO, t, staging, red, row_valid, e);
+          epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16), staging, red,
+                               row_valid, r, e, ring_pos, release);
+        else
+          release();
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
@@ -766,8 +773,10 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
                                                             const __grid_constant__ CUtensorMap tmX,
                                                             const __grid_constant__ WgradTcParams p) {
   using S = WgradSmem<BNW, STAGES>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle, computed as an offset so that the compiler keeps the shared address space
+  // (a pointer rebuilt from an integer becomes generic: LD.E / ST.E instead of LDS / STS in the epilogue)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kMainBytes);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
@@ -1178,7 +1187,7 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
         q.b.n_tiles = 1;
         rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
         if (rc) return rc;
-        return launch_conv3<64, 4>(tmA3, tmB, tmO3, q, stream);
+        return launch_conv3<64, 3>(tmA3, tmB, tmO3, q, stream);
       }
       q.b.n_tiles = ceil_div(Cout, 128);
       rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
@@ -1268,8 +1277,10 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
 namespace dcnn {
 __global__ void tma_probe_kernel(const __grid_constant__ CUtensorMap tm, int c0, int c1, int c2, int c3, int bytes,
                                  float* out) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle, computed as an offset so that the compiler keeps the shared address space
+  // (a pointer rebuilt from an integer becomes generic: LD.E / ST.E instead of LDS / STS in the epilogue)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   __shared__ uint64_t bar;
   float* f = reinterpret_cast<float*>(smem);
   for (int i = threadIdx.x; i < bytes / 4; i += blockDim.x) f[i] = -12345.f;
@@ -1314,8 +1325,10 @@ __global__ void __launch_bounds__(64, 1) tma_stream_probe_kernel(const __grid_co
                                                                  int stages, int a_rows, int b_rows, int a_row_blocks,
                                                                  int a_col_blocks, int b_row_blocks, int b_col_blocks,
                                                                  int b_shared) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the 128B swizzle, computed as an offset so that the compiler keeps the shared address space
+  // (a pointer rebuilt from an integer becomes generic: LD.E / ST.E instead of LDS / STS in the epilogue)
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   __shared__ uint64_t full_bar[8], empty_bar[8];
   const int stage_bytes = (a_rows + b_rows) * 128;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -89,55 +89,82 @@ __device__ __forceinline__ Moments merge(Moments a, Moments b) {
 // ---------------------------------------------------------------------------------------------------------
 // One-launch cross-replica exchange for sync-BatchNorm (K27; the reference has neither data parallelism nor a
 // cross-replica BatchNorm).  Every replica owns an exchange area per BatchNorm layer and direction, mapped by all peers:
-//     double data[2 parities][world sources][3][C]  |  u64 flags[ceil(C/8)][kMaxPeers]  |  u64 counter[ceil(C/8)]
-// Warp 0 of a finalize CTA (channel group g = blockIdx.x) PUSHES its three per-channel values into slot [source =
-// this rank] of every replica (plain stores through the NVLink peer mappings), fences, and raises flag [g][rank] in every
-// replica to this call's epoch (st.release.sys).  It then spins on ITS OWN flags [g][*] -- local memory, no NVLink
-// polling -- until every source has reached the epoch, and merges the sources in rank order from local memory, so all
-// replicas compute bit-identical statistics.  The epoch is a device-resident per-(layer, direction, group) call counter
-// kept next to the flags: no host bookkeeping, no separate counter kernel, replayable from a CUDA graph.  Two data
-// parities are enough: a replica can only be one call ahead of the slowest one (it needs that replica's flag of call e
-// to finish call e, and that replica raised it after it had finished reading call e-1).  (This needs a layer's calls
-// to alternate parity per channel group, so one layer must always use the same finalize kernel variant: the host side
-// picks the variant for sync calls from the process-wide switch alone, never from the tile count.)
+//     u64 words[2 parities][world sources][6][C]  |  u64 counter[ceil(C/8)]
+// The protocol is flag-in-data ("LL"): each of a channel's three FP64 values travels as two 8-byte words
+// {payload: 32 bits of the value, flag: this call's epoch}.  An aligned 8-byte store is indivisible, so a word whose
+// flag equals the epoch carries valid data -- no fence, no separate flag store and no acknowledgement: the exchange
+// costs ONE one-way NVLink store latency.  (The first version pushed plain data, fenced at system scope and then raised
+// flags with st.release: two NVLink round trips on the critical path of every BatchNorm, 10.7 us per exchange and 1.1 ms
+// of the 16.1 ms two-GPU step; profiles/06.)
+// Warp 0 of a finalize CTA pushes its channels' words into slot [source = this rank] of every replica through the peer
+// mappings, then polls ITS OWN area -- local memory, no NVLink polling -- until every source's words carry the epoch,
+// and merges the sources in rank order, so all replicas compute bit-identical statistics.  The epoch is a
+// device-resident per-(layer, direction, channel group) call counter stored behind the words: no host bookkeeping, no
+// counter kernel, replayable from a CUDA graph.  Two parities are enough: a replica can only be one call ahead of the
+// slowest one (it needs that replica's words of call e to finish call e, and that replica pushed them after it had
+// finished reading call e-1).  This needs a layer's calls to alternate parity per channel group, so one layer must always
+// use the same finalize kernel variant: the host side picks the variant for sync calls from the process-wide switch
+// alone, never from the tile count.
 struct BnSyncArgs {
   unsigned char* area[kMaxPeers];  // replica r's exchange area of this layer and direction, as mapped here
   int rank, world;                 // world <= 1: no exchange
 };
 
-__host__ __device__ inline size_t bn_sync_data_bytes(int world, int C) { return (size_t)2 * world * 3 * C * sizeof(double); }
+__host__ __device__ inline size_t bn_sync_data_bytes(int world, int C) { return (size_t)2 * world * 6 * C * sizeof(unsigned long long); }
 
-// Returns this call's local slot: value k of channel c from source r is at ret[(r * 3 + k) * C + c].
-// To be called by all 32 lanes of warp 0; `has` marks the lanes that own channel `c`.
-__device__ __forceinline__ const volatile double* bn_sync_exchange(const BnSyncArgs& s, int lane, int C, int c, bool has,
-                                                                   double v0, double v1, double v2) {
-  const int g = blockIdx.x, G = (C + 7) / 8;   // layout for the finest channel grouping (the narrow kernels')
+__device__ __forceinline__ void st_relaxed_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Exchanges (v0, v1, v2) of channel c with every replica; take(a, b, c) receives the three values of source 0, 1, ...
+// in rank order.  To be called by all 32 lanes of warp 0; `has` marks the lanes that own a channel.
+template <typename Take>
+__device__ __forceinline__ void bn_sync_exchange(const BnSyncArgs& s, int lane, int C, int c, bool has, double v0,
+                                                 double v1, double v2, Take take) {
+  const int g = blockIdx.x;
   const size_t data_bytes = bn_sync_data_bytes(s.world, C);
   unsigned char* mine = s.area[s.rank];
-  unsigned long long* my_flags = reinterpret_cast<unsigned long long*>(mine + data_bytes) + (size_t)g * kMaxPeers;
-  unsigned long long* ctr = reinterpret_cast<unsigned long long*>(mine + data_bytes) + (size_t)G * kMaxPeers + g;
-  const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long*>(ctr) + 1;
-  const size_t parity_off = (size_t)(epoch & 1) * s.world * 3 * C;
+  unsigned long long* ctr = reinterpret_cast<unsigned long long*>(mine + data_bytes) + g;
+  const unsigned long long call = *reinterpret_cast<volatile unsigned long long*>(ctr) + 1;
+  const unsigned long long flag = (call & 0xffffffffull) << 32;
+  const size_t parity_off = (size_t)(call & 1) * s.world * 6 * C;   // in words
   if (has) {
+    const unsigned long long b0 = (unsigned long long)__double_as_longlong(v0);
+    const unsigned long long b1 = (unsigned long long)__double_as_longlong(v1);
+    const unsigned long long b2 = (unsigned long long)__double_as_longlong(v2);
+    const unsigned long long w[6] = {flag | (b0 & 0xffffffffull), flag | (b0 >> 32), flag | (b1 & 0xffffffffull),
+                                     flag | (b1 >> 32),           flag | (b2 & 0xffffffffull), flag | (b2 >> 32)};
     for (int r = 0; r < s.world; ++r) {
-      double* d = reinterpret_cast<double*>(s.area[r]) + parity_off + (size_t)s.rank * 3 * C;
-      d[c] = v0;
-      d[C + c] = v1;
-      d[2 * C + c] = v2;
+      unsigned long long* d = reinterpret_cast<unsigned long long*>(s.area[r]) + parity_off + (size_t)s.rank * 6 * C + c;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) st_relaxed_sys_u64(d + (size_t)k * C, w[k]);
+    }
+    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(mine) + parity_off + c;
+    for (int r = 0; r < s.world; ++r) {
+      unsigned long long got[6];
+      unsigned long long spins = 0;
+      bool ok;
+      do {
+        ok = true;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          got[k] = ld_relaxed_sys_u64(src + ((size_t)r * 6 + k) * C);
+          ok = ok && ((got[k] & 0xffffffff00000000ull) == flag);
+        }
+        if (!ok && ++spins > (1ull << 28)) __trap();  // a lost replica must not hang the GPU forever
+      } while (!ok);
+      take(__longlong_as_double((long long)((got[0] & 0xffffffffull) | (got[1] << 32))),
+           __longlong_as_double((long long)((got[2] & 0xffffffffull) | (got[3] << 32))),
+           __longlong_as_double((long long)((got[4] & 0xffffffffull) | (got[5] << 32))));
     }
   }
-  __threadfence_system();
   __syncwarp();
-  if (lane < s.world) {
-    st_release_sys(reinterpret_cast<unsigned long long*>(s.area[lane] + data_bytes) + (size_t)g * kMaxPeers + s.rank, epoch);
-    unsigned long long spins = 0;
-    while (ld_acquire_sys(my_flags + lane) < epoch) {
-      if (++spins > (1ull << 31)) __trap();  // a lost replica must not hang the GPU forever
-    }
-  }
-  __syncwarp();
-  if (lane == 0) *ctr = epoch;
-  return reinterpret_cast<const volatile double*>(mine) + parity_off;
+  if (lane == 0) *ctr = call;
 }
 
 // grid: ceil(C/32); block (32 channels, 32 tile lanes).
@@ -150,7 +177,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
                                                            const float* __restrict__ beta, float* __restrict__ mean_out,
                                                            float* __restrict__ invstd_out, float* __restrict__ scale_out,
                                                            float* __restrict__ shift_out,
-                                                           const BnSyncArgs sync) {
+                                                           const __grid_constant__ BnSyncArgs sync) {
   __shared__ double s_n[32][33], s_s[32][33], s_q[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   // Per tile we have (n, sum, M2 about the tile mean).  sum(x^2) of the tile = M2 + sum^2/n, so three plain FP64
@@ -182,12 +209,10 @@ __global__ void __launch_bounds__(1024) bn_finalize_kernel(const float* __restri
   Moments acc{an, an > 0 ? as / an : 0.0, 0.0};
   acc.m2 = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
   if (sync.world > 1) {
-    const volatile double* d = bn_sync_exchange(sync, threadIdx.x, C, c, has, acc.n, acc.mean, acc.m2);
-    if (has) {
-      acc = Moments{0, 0, 0};
-      for (int r = 0; r < sync.world; ++r)
-        acc = merge(acc, Moments{d[(r * 3 + 0) * C + c], d[(r * 3 + 1) * C + c], d[(r * 3 + 2) * C + c]});
-    }
+    const Moments local = acc;
+    acc = Moments{0, 0, 0};
+    bn_sync_exchange(sync, threadIdx.x, C, c, has, local.n, local.mean, local.m2,
+                     [&](double n, double mean, double m2) { acc = merge(acc, Moments{n, mean, m2}); });
   }
   if (has) {
     const double var = acc.n > 0 ? acc.m2 / acc.n : 0.0;  // biased: used to normalise
@@ -220,7 +245,7 @@ __global__ void __launch_bounds__(1024) bn_finalize_narrow_kernel(const float* _
                                                                   float* __restrict__ invstd_out,
                                                                   float* __restrict__ scale_out,
                                                                   float* __restrict__ shift_out,
-                                                                  const BnSyncArgs sync) {
+                                                                  const __grid_constant__ BnSyncArgs sync) {
   __shared__ double s_n[128][9], s_s[128][9], s_q[128][9];
   const int c = blockIdx.x * 8 + threadIdx.x;
   double an = 0, as = 0, aq = 0;
@@ -251,13 +276,10 @@ __global__ void __launch_bounds__(1024) bn_finalize_narrow_kernel(const float* _
   double mean_d = an > 0 ? as / an : 0.0;
   double m2_d = an > 0 ? fmax(aq - as * as / an, 0.0) : 0.0;
   if (sync.world > 1) {
-    const volatile double* d = bn_sync_exchange(sync, threadIdx.y * 8 + threadIdx.x, C, c, has, an, mean_d, m2_d);
-    if (has) {
-      Moments acc{0, 0, 0};
-      for (int r = 0; r < sync.world; ++r)
-        acc = merge(acc, Moments{d[(r * 3 + 0) * C + c], d[(r * 3 + 1) * C + c], d[(r * 3 + 2) * C + c]});
-      an = acc.n; mean_d = acc.mean; m2_d = acc.m2;
-    }
+    Moments acc{0, 0, 0};
+    bn_sync_exchange(sync, threadIdx.y * 8 + threadIdx.x, C, c, has, an, mean_d, m2_d,
+                     [&](double n, double mean, double m2) { acc = merge(acc, Moments{n, mean, m2}); });
+    an = acc.n; mean_d = acc.mean; m2_d = acc.m2;
   }
   if (has) {
     const double var = an > 0 ? m2_d / an : 0.0;
@@ -284,7 +306,7 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_narrow_kernel(const floa
                                                                       float* __restrict__ dgamma,
                                                                       float* __restrict__ dbeta, float* __restrict__ k1,
                                                                       float* __restrict__ k2, float* __restrict__ k3,
-                                                                      const BnSyncArgs sync) {
+                                                                      const __grid_constant__ BnSyncArgs sync) {
   __shared__ double s_a[128][9], s_b[128][9];
   const int c = blockIdx.x * 8 + threadIdx.x;
   double a = 0, b = 0;
@@ -308,13 +330,9 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_narrow_kernel(const floa
     }
   }
   if (sync.world > 1) {
-    const volatile double* d = bn_sync_exchange(sync, threadIdx.y * 8 + threadIdx.x, C, c, has, a, b, count);
-    if (has) {
-      a = b = count = 0;
-      for (int r = 0; r < sync.world; ++r) {
-        a += d[(r * 3 + 0) * C + c]; b += d[(r * 3 + 1) * C + c]; count += d[(r * 3 + 2) * C + c];
-      }
-    }
+    const double la = a, lb = b, lc = count;
+    a = b = count = 0;
+    bn_sync_exchange(sync, threadIdx.y * 8 + threadIdx.x, C, c, has, la, lb, lc, [&](double x, double y, double z) { a += x; b += y; count += z; });
   }
   if (has) {
     const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
@@ -464,7 +482,7 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                                float* __restrict__ k1, float* __restrict__ k2,
                                                                float* __restrict__ k3,
-                                                               const BnSyncArgs sync) {
+                                                               const __grid_constant__ BnSyncArgs sync) {
   __shared__ double s_a[32][33], s_b[32][33];
   const int c = blockIdx.x * 32 + threadIdx.x;
   double a = 0, b = 0;
@@ -486,13 +504,9 @@ __global__ void __launch_bounds__(1024) bn_bwd_finalize_kernel(const float* __re
     dbeta[c] += (float)a;
   }
   if (sync.world > 1) {
-    const volatile double* d = bn_sync_exchange(sync, threadIdx.x, C, c, has, a, b, count);
-    if (has) {
-      a = b = count = 0;
-      for (int r = 0; r < sync.world; ++r) {
-        a += d[(r * 3 + 0) * C + c]; b += d[(r * 3 + 1) * C + c]; count += d[(r * 3 + 2) * C + c];
-      }
-    }
+    const double la = a, lb = b, lc = count;
+    a = b = count = 0;
+    bn_sync_exchange(sync, threadIdx.x, C, c, has, la, lb, lc, [&](double x, double y, double z) { a += x; b += y; count += z; });
   }
   if (has) {
     const float sc = gamma ? gamma[c] * invstd[c] : invstd[c];
@@ -751,7 +765,7 @@ DCNN_API int dcnn_bn_finalize(const float* partials, int tiles, int C, float eps
 // device pointers); each area holds dcnn_bn_sync_area_bytes(world, C) bytes, zero-initialised once.
 DCNN_API long long dcnn_bn_sync_area_bytes(int world, int C) {
   const long long g = (C + 7) / 8;
-  const long long b = (long long)bn_sync_data_bytes(world, C) + g * kMaxPeers * 8 + g * 8;
+  const long long b = (long long)bn_sync_data_bytes(world, C) + g * 8;
   return (b + 255) / 256 * 256;
 }
 

@@ -174,9 +174,9 @@ class SyncBN:
     """Cross-replica BatchNorm statistics for one BN layer (forward moments and backward sums).
 
     CUDA: ONE launch per direction -- the finalize kernel pushes its per-channel values into every replica's exchange
-    area, raises per-channel-group epoch flags and merges all sources from local memory (csrc/norm.cu,
-    ``bn_sync_exchange``); the call counters live on the device, so there is no host-side bookkeeping to keep in step
-    with CUDA-graph replays."""
+    area as flag-in-data words (one NVLink store latency, no fence) and merges all sources from local memory
+    (csrc/norm.cu, ``bn_sync_exchange``); the call counters live on the device, so there is no host-side bookkeeping
+    to keep in step with CUDA-graph replays."""
 
     def __init__(self, dp: "DataParallel", channels: int, offset_bytes: int):
         self.dp, self.C = dp, channels
@@ -189,7 +189,7 @@ class SyncBN:
     @staticmethod
     def area_bytes(world: int, channels: int) -> int:
         g = (channels + 7) // 8           # must equal dcnn_bn_sync_area_bytes (checked in DataParallel._setup_sync_bn)
-        b = 2 * world * 3 * channels * 8 + g * 8 * 8 + g * 8
+        b = 2 * world * 6 * channels * 8 + g * 8
         return (b + 255) // 256 * 256
 
     @classmethod

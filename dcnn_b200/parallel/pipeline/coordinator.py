@@ -209,11 +209,14 @@ class Coordinator:
         fwd = self.comm.dequeue_all_messages_by_type(CommandType.FORWARD_JOB)
         total = 0.0
         grads = {}
+        self.last_correct = 0.0          # correct predictions of this batch (classification losses report them)
         for msg in fwd:
             job = msg.payload
             tgt = microbatch_labels[job.micro_batch_id].to(job.data.device)
-            loss, grad, _ = self.loss_function.forward_backward(job.data, tgt)
+            loss, grad, correct = self.loss_function.forward_backward(job.data, tgt)
             total += float(loss)
+            if correct is not None:
+                self.last_correct += float(correct)
             grads[job.micro_batch_id] = grad
         for i in sorted(grads):
             self.backward(grads[i], i)

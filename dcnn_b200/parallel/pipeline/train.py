@@ -45,12 +45,14 @@ def train_semi_async_epoch(coordinator: Coordinator, train_loader, config: Train
 
 
 def train_sync_epoch(coordinator: Coordinator, train_loader, config: TrainingConfig):
-    """GPipe ordering with the loss on the coordinator (examples/sync_pipeline_coordinator.cpp:99-201)."""
+    """GPipe ordering with the loss on the coordinator (examples/sync_pipeline_coordinator.cpp:99-201).
+    Returns (mean loss, accuracy, seconds) like the semi-async epoch."""
     train_loader.shuffle()
     train_loader.reset()
     coordinator.set_training(True)
     keep = coordinator.loss_on_last_stage
-    total_loss, batches = 0.0, 0
+    total_loss, total_correct, samples, batches = 0.0, 0.0, 0, 0
+    t_epoch = time.perf_counter()
     while True:
         batch = train_loader.get_next_batch()
         if batch is None:
@@ -60,11 +62,37 @@ def train_sync_epoch(coordinator: Coordinator, train_loader, config: TrainingCon
         xs, ts = split_microbatches(data, m), split_microbatches(labels, m)
         coordinator.set_num_microbatches(len(xs))
         total_loss += coordinator.sync_process_batch(xs, ts)
+        total_correct += getattr(coordinator, "last_correct", 0.0)
         coordinator.update_parameters()
         coordinator.set_num_microbatches(m)
+        samples += data.shape[0]
         batches += 1
     coordinator.loss_on_last_stage = keep
-    return total_loss / max(1, batches)
+    return total_loss / max(1, batches), total_correct / max(1, samples), time.perf_counter() - t_epoch
+
+
+def validate_sync_epoch(coordinator: Coordinator, test_loader):
+    """Forward-only pass in EVAL_MODE with the loss on the coordinator (the GPipe arrangement of train_sync_epoch)."""
+    from .protocol import CommandType
+    test_loader.reset()
+    coordinator.set_training(False)
+    total_loss, total_correct, samples, batches = 0.0, 0.0, 0, 0
+    while True:
+        batch = test_loader.get_next_batch()
+        if batch is None:
+            break
+        data, labels = batch
+        coordinator.forward(data, 0)
+        coordinator.join(CommandType.FORWARD_JOB, 1, 120.0)
+        for msg in coordinator.comm.dequeue_all_messages_by_type(CommandType.FORWARD_JOB):
+            out = msg.payload.data
+            loss, _, correct = coordinator.loss_function.forward_backward(out, labels.to(out.device), want_grad=False)
+            total_loss += float(loss)
+            total_correct += float(correct) if correct is not None else 0.0
+        samples += data.shape[0]
+        batches += 1
+    coordinator.set_training(True)
+    return total_loss / max(1, batches), total_correct / max(1, samples)
 
 
 def validate_semi_async_epoch(coordinator: Coordinator, test_loader):
@@ -99,8 +127,7 @@ def train_model(coordinator: Coordinator, train_loader, test_loader, config: Opt
     for epoch in range(config.epochs):
         print(f"Epoch {epoch + 1}/{config.epochs}")
         if schedule == "sync":
-            loss = train_sync_epoch(coordinator, train_loader, config)
-            acc, secs = float("nan"), 0.0
+            loss, acc, secs = train_sync_epoch(coordinator, train_loader, config)
         else:
             loss, acc, secs = train_semi_async_epoch(coordinator, train_loader, config)
         print(f"Epoch {epoch + 1} - loss {loss:.4f}, accuracy {100 * acc:.2f}%, {secs * 1000:.0f} ms")

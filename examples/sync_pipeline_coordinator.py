@@ -8,7 +8,7 @@ from _pipeline_common import make_coordinator
 from dcnn_b200 import nn
 from dcnn_b200.data import create_mnist_data_loaders_dir
 from dcnn_b200.models import create_mnist_trainer
-from dcnn_b200.parallel.pipeline.train import train_model, validate_semi_async_epoch
+from dcnn_b200.parallel.pipeline.train import train_model, validate_sync_epoch
 from dcnn_b200.partitioner import NaivePartitioner
 
 
@@ -24,7 +24,7 @@ def main():
     coord.loss_on_last_stage = False
     train_loader, test_loader = loaders(create_mnist_data_loaders_dir, "./data/mnist", (1, 28, 28), 10, cfg)
     history = train_model(coord, train_loader, test_loader, cfg, schedule="sync")
-    val_loss, val_acc = validate_semi_async_epoch(coord, test_loader) if coord.loss_on_last_stage else (float("nan"), float("nan"))
+    val_loss, val_acc = validate_sync_epoch(coord, test_loader)
     print(f"Validation - Loss: {val_loss:.4f}, Accuracy: {100 * val_acc:.2f}%")
     coord.print_profiling_on_all_stages()
     if coord.save_checkpoint("model_snapshots/" + model.name()):
