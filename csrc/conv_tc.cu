@@ -160,6 +160,7 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
   asm volatile("bar.sync 2, 128;" ::: "memory");
   for (int j = e; j < nch * 32; j += 128) {
     const int c = t.col_base + j;
+    if (c >= p.Cout) continue;   // the last chunk of a channel count that is not a multiple of 32
     const float kshift = red[8 * RS + j];
     const float s = red[(0 * 4 + 0) * RS + j] + red[(0 * 4 + 1) * RS + j] + red[(0 * 4 + 2) * RS + j] +
                     red[(0 * 4 + 3) * RS + j];
