@@ -163,6 +163,123 @@ __global__ void __launch_bounds__(512) fused_allreduce_update_kernel(const __gri
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Push variant of the fused all-reduce + update: the same arithmetic in the same order, but nothing is ever LOADED
+// over NVLink.  (Measured on 2 GPUs, profiles/06: the pull kernel needs 156 us against a 124 us NVLink floor because
+// every gradient element waits for a peer-load round trip, and the peers may only zero their gradients after a second
+// kernel has seen everybody's "done" flag: 51 us more.)
+//   phase A  every rank copies the gradient slice that replica o owns into o's staging buffer (posted NVLink stores)
+//            and zeroes that slice locally -- no peer ever reads another replica's gradients;
+//   barrier  "my slices have arrived" (fence + epoch flags), every CTA waits for all replicas;
+//   phase B  own gradient slice + the R-1 staged slices (all LOCAL loads, summed own, rank+1, rank+2, ... as before)
+//            -> 1/R -> optimizer update of the owned shard -> new parameters stored into every replica (posted NVLink
+//            stores) -> own gradient slice zeroed;
+//   done     fence + epoch flags; block 0 leaves only when every replica has signalled, so the kernel's completion means
+//            this replica's parameters are complete and its staging buffer may be overwritten by the next step.
+// One launch (no counter kernel, no zeroing kernel).  All CTAs must be co-resident (they wait for each other's
+// replicas): the grid is at most one CTA per SM.
+struct ArPushParams {
+  ArParams base;
+  float* stage[kMaxPeers];                 // replica r's staging buffer as mapped here
+  long long sb[kMaxPeers], se[kMaxPeers];  // shard [sb, se) of replica r inside this launch's range (multiples of 4)
+  long long soff[kMaxPeers];               // offset (floats) of this launch's region in replica r's staging buffer
+};
+
+template <int W>
+__global__ void __launch_bounds__(512) fused_allreduce_update_push_kernel(const __grid_constant__ ArPushParams q) {
+  const ArParams& pp = q.base;
+  const unsigned long long epoch = *pp.epoch_ptr + 1;
+  float lr = pp.lr, bc1 = pp.bc1, bc2 = pp.bc2;
+  if (pp.hyper != nullptr) { lr = pp.hyper[0]; bc1 = pp.hyper[1]; bc2 = pp.hyper[2]; }
+  const int rank = pp.rank, world = W > 0 ? W : pp.world;
+  float* gown = pp.grads[rank];
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  // ---- phase A: push the slices the other replicas own, zero them here
+  for (int k = 1; k < world; ++k) {
+    const int o = (rank + k) % world;
+    const long long b = q.sb[o], len = q.se[o] - b, l4 = len >> 2;
+    float* dst = q.stage[o] + q.soff[o] + (long long)(world - k - 1) * len;   // slot of source `rank` at owner o
+    float* src = gown + b;
+    long long i = tid;
+    for (; i + 3 * stride < l4; i += 4 * stride) {
+      float4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const float4*>(src + (i + u * stride) * 4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        *reinterpret_cast<float4*>(dst + (i + u * stride) * 4) = v[u];
+        *reinterpret_cast<float4*>(src + (i + u * stride) * 4) = zero4;
+      }
+    }
+    for (; i < l4; i += stride) {
+      const float4 v = *reinterpret_cast<const float4*>(src + i * 4);
+      *reinterpret_cast<float4*>(dst + i * 4) = v;
+      *reinterpret_cast<float4*>(src + i * 4) = zero4;
+    }
+  }
+  // ---- every replica's slices have arrived
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(pp.block_counter, 1u) == gridDim.x - 1) {
+      *pp.block_counter = 0;
+      peer_signal(pp.start_flags, rank, world, epoch);
+    }
+    peer_wait(pp.start_flags, rank, world, epoch);
+  }
+  __syncthreads();
+
+  // ---- phase B: reduce + update the owned shard, publish the parameters
+  {
+    const long long b = q.sb[rank], len = q.se[rank] - b, l4 = len >> 2;
+    const float* st = q.stage[rank] + q.soff[rank];
+    const float* pown = pp.params[rank];
+    const float inv = pp.inv_world;
+    for (long long i = tid; i < l4; i += stride) {
+      const long long e = b + i * 4;
+      float4 g = *reinterpret_cast<const float4*>(gown + e);
+      if constexpr (W > 0) {
+        float4 v[W];
+#pragma unroll
+        for (int k = 0; k < W - 1; ++k) v[k] = ld_peer4(st + (long long)k * len + i * 4);
+#pragma unroll
+        for (int k = 0; k < W - 1; ++k) { g.x += v[k].x; g.y += v[k].y; g.z += v[k].z; g.w += v[k].w; }
+      } else {
+#pragma unroll 1
+        for (int k = 0; k < world - 1; ++k) {
+          const float4 v = ld_peer4(st + (long long)k * len + i * 4);
+          g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+        }
+      }
+      g.x *= inv; g.y *= inv; g.z *= inv; g.w *= inv;
+      const float4 w = *reinterpret_cast<const float4*>(pown + e);
+      const float4 out = ar_update(pp, lr, bc1, bc2, g, w, i * 4);
+      if constexpr (W > 0) {
+#pragma unroll
+        for (int r = 0; r < W; ++r) *reinterpret_cast<float4*>(pp.params[(rank + r) & (W - 1)] + e) = out;
+      } else {
+#pragma unroll 1
+        for (int r = 0; r < world; ++r) *reinterpret_cast<float4*>(pp.params[(rank + r) % world] + e) = out;
+      }
+      *reinterpret_cast<float4*>(gown + e) = zero4;
+    }
+  }
+  // ---- done
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(pp.block_counter + 1, 1u) == gridDim.x - 1) {
+      pp.block_counter[1] = 0;
+      *const_cast<unsigned long long*>(pp.epoch_ptr) = epoch;
+      peer_signal(pp.done_flags, rank, world, epoch);
+    }
+    if (blockIdx.x == 0) peer_wait(pp.done_flags, rank, world, epoch);
+  }
+}
+
 // Waits for every replica's "done" signal of this epoch, then zeroes the local gradient buffer.
 __global__ void __launch_bounds__(512) wait_done_zero_kernel(PeerFlags done_flags, int rank, int world,
                                                              const unsigned long long* epoch_ptr, float* grads,
@@ -229,6 +346,46 @@ DCNN_API int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, i
   peer_barrier_kernel<<<1, 32, 0, stream>>>(pf, rank, world, epoch_counter);
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(2);
+  return 0;
+}
+
+// Push variant (see fused_allreduce_update_push_kernel).  grad_ptrs / param_ptrs point at the start of this launch's
+// range in every replica; stage_ptrs[r] = replica r's staging buffer; sb/se/soff[r]: replica r's shard inside the range
+// and the offset of this launch's region in r's staging buffer (host arrays of `world` entries); block_counters: two
+// zero-initialised u32.  num_blocks is clamped to one CTA per SM.
+DCNN_API int dcnn_fused_allreduce_update_push(float* const* grad_ptrs, float* const* param_ptrs, float* const* stage_ptrs,
+                                              const long long* sb, const long long* se, const long long* soff,
+                                              float* s1, float* s2, long long n,
+                                              unsigned long long* const* start_flag_ptrs,
+                                              unsigned long long* const* done_flag_ptrs, unsigned int* block_counters,
+                                              int rank, int world, unsigned long long* epoch_counter, int mode, float lr,
+                                              float a, float b, float eps, float bc1, float bc2, float wd,
+                                              const float* hyper, int num_blocks, cudaStream_t stream) {
+  ArPushParams q;
+  memset(&q, 0, sizeof(q));
+  ArParams& p = q.base;
+  DCNN_REQUIRE(world >= 1 && world <= kMaxPeers, "world size %d out of range (max %d)", world, kMaxPeers);
+  for (int r = 0; r < world; ++r) {
+    DCNN_REQUIRE((sb[r] & 3) == 0 && (se[r] & 3) == 0 && (soff[r] & 3) == 0 && sb[r] <= se[r] && se[r] <= n,
+                 "fused all-reduce (push): bad shard of rank %d", r);
+    p.grads[r] = grad_ptrs[r]; p.params[r] = param_ptrs[r]; q.stage[r] = stage_ptrs[r];
+    q.sb[r] = sb[r]; q.se[r] = se[r]; q.soff[r] = soff[r];
+  }
+  int rc = fill_flags(&p.start_flags, start_flag_ptrs, world);
+  if (rc) return rc;
+  rc = fill_flags(&p.done_flags, done_flag_ptrs, world);
+  if (rc) return rc;
+  p.s1 = s1; p.s2 = s2; p.n = n; p.shard_begin = sb[rank]; p.shard_end = se[rank];
+  p.block_counter = block_counters; p.rank = rank; p.world = world; p.epoch_ptr = epoch_counter; p.hyper = hyper;
+  p.lr = lr; p.a = a; p.b = b; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2; p.wd = wd; p.inv_world = 1.f / (float)world;
+  p.mode = mode;
+  if (num_blocks <= 0 || num_blocks > num_sms()) num_blocks = num_sms();   // every CTA must be resident
+  if (world == 2) fused_allreduce_update_push_kernel<2><<<num_blocks, 512, 0, stream>>>(q);
+  else if (world == 4) fused_allreduce_update_push_kernel<4><<<num_blocks, 512, 0, stream>>>(q);
+  else if (world == 8) fused_allreduce_update_push_kernel<8><<<num_blocks, 512, 0, stream>>>(q);
+  else fused_allreduce_update_push_kernel<0><<<num_blocks, 512, 0, stream>>>(q);
+  DCNN_CHECK_LAUNCH();
+  DCNN_COUNT_LAUNCH(1);
   return 0;
 }
 

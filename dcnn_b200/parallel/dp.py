@@ -14,6 +14,7 @@ correctness oracle.  CPU tensors (gloo) take the same baseline route so the logi
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional
 
 import torch
@@ -381,6 +382,11 @@ class DataParallel:
         if not self.nvls:
             self.grad_ptrs = self.buf.peer_array(4 * self.n)
             self.param_ptrs = self.buf.peer_array(0)
+        # push variant of the fused kernel (default; DCNN_AR_PULL=1 keeps the peer-load kernel): every replica owns a
+        # staging buffer that receives the other replicas' slices of its shard
+        self.push = (not self.nvls) and self.world > 1 and os.environ.get("DCNN_AR_PULL", "0") != "1"
+        if self.push:
+            self._setup_push(None)
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
 
@@ -397,6 +403,39 @@ class DataParallel:
             self.s1 = self.state_buf.view(torch.float32, 0, self.state_floats)
             if self.n_state == 2:
                 self.s2 = self.state_buf.view(torch.float32, 4 * self.state_floats, self.state_floats)
+
+    def _setup_push(self, buckets):
+        """Staging buffer and per-launch tables of the push kernel.  A launch (the whole buffer, or one bucket) covers
+        the flat range [a, a+len); replica r owns [sb_r, se_r) of it and receives the other replicas' copies of that
+        slice in its staging buffer at (R-1) x (offset of the slice in r's optimizer-state arrays)."""
+        R = self.world
+        per_rank = [state_layout(self.n, R, r, buckets) for r in range(R)]
+        floats = max((R - 1) * sum(e - b for b, e, _ in lay) for lay in per_rank)
+        if getattr(self, "stage_buf", None) is None or self.stage_buf.nbytes < 4 * floats:
+            self.stage_buf = SymmetricBuffer(4 * max(4, floats), self.group, self.device)
+        self.stage_ptrs = self.stage_buf.peer_array(0)
+        LLA = C.c_longlong * R
+        launches = []
+        n_launch = 1 if buckets is None else len(buckets)
+        for li in range(n_launch):
+            a = 0 if buckets is None else buckets[li]["a"]
+            sb = LLA(*[per_rank[r][li][0] - a for r in range(R)])
+            se = LLA(*[per_rank[r][li][1] - a for r in range(R)])
+            soff = LLA(*[(R - 1) * per_rank[r][li][2] for r in range(R)])
+            launches.append((sb, se, soff))
+        self.push_tables = launches
+        self.push_counters = torch.zeros(2, dtype=torch.int32, device=self.device)
+
+    def _launch_push(self, li, grad_ptrs, param_ptrs, n, s1, s2, args, opt, num_blocks, stream_ptr):
+        from .._lib import F, I, LL, P, check, lib
+        from ..ops.cuda import _p
+        mode, a, b, eps, bc1, bc2, wd = args
+        sb, se, soff = self.push_tables[li]
+        check(lib().dcnn_fused_allreduce_update_push(
+            grad_ptrs, param_ptrs, self.stage_ptrs, sb, se, soff, _p(s1), _p(s2), LL(n), self.start_flags,
+            self.done_flags, P(self.push_counters.data_ptr()), I(self.rank), I(self.world),
+            P(self.local.data_ptr() + 8), I(mode), F(opt.learning_rate), F(a), F(b), F(eps), F(bc1), F(bc2), F(wd),
+            _p(opt.hyper), I(num_blocks), stream_ptr), "dcnn_fused_allreduce_update_push")
 
     def _state_layout(self, rank: int):
         """[(flat_begin, flat_end, offset in that rank's state arrays)] of the slices rank ``rank`` owns."""
@@ -478,6 +517,8 @@ class DataParallel:
             bk["grad_ptrs"] = self.buf.peer_array(4 * self.n + 4 * bk["a"])
             bk["param_ptrs"] = self.buf.peer_array(4 * bk["a"])
         self._alloc_state(self.n // self.world + 4 * len(self.buckets))
+        if self.push:
+            self._setup_push(self.buckets)
         self.comm_stream = torch.cuda.Stream(device=self.device)
         self._trigger = {bk["first_unit"]: bi for bi, bk in enumerate(self.buckets)}
         self._launched = set()
@@ -516,6 +557,12 @@ class DataParallel:
         self.comm_stream.wait_event(ready)
         s1 = self.s1[bk["state_off"]:] if self.s1 is not None else None
         s2 = self.s2[bk["state_off"]:] if self.s2 is not None else None
+        if self.push:
+            with torch.cuda.stream(self.comm_stream):
+                self._launch_push(bi, bk["grad_ptrs"], bk["param_ptrs"], bk["n"], s1, s2, self._step_args, opt,
+                                  self.num_blocks if self.num_blocks > 0 else 32, P(self.comm_stream.cuda_stream))
+            self._launched.add(bi)
+            return
         with torch.cuda.stream(self.comm_stream):
             check(lib().dcnn_fused_allreduce_update(
                 bk["grad_ptrs"], bk["param_ptrs"], _p(s1), _p(s2), LL(bk["n"]), LL(bk["sb"]), LL(bk["se"]),
@@ -606,6 +653,10 @@ class DataParallel:
                 self.done_flags, P(self.local.data_ptr()), I(self.rank), I(self.world), P(self.local.data_ptr() + 8),
                 I(mode), F(opt.learning_rate), F(a), F(b), F(eps), F(bc1), F(bc2), F(wd), _p(opt.hyper),
                 I(self.num_blocks), _stream()), "dcnn_fused_allreduce_update_nvls")
+            return
+        if self.push:
+            self._launch_push(0, self.grad_ptrs, self.param_ptrs, self.n, self.s1, self.s2,
+                              (mode, a, b, eps, bc1, bc2, wd), opt, self.num_blocks, _stream())
             return
         check(lib().dcnn_fused_allreduce_update(
             self.grad_ptrs, self.param_ptrs, _p(self.s1), _p(self.s2), LL(self.n), LL(self.shard_begin),

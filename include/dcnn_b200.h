@@ -161,6 +161,15 @@ int dcnn_ipc_close(void* ptr);
 int dcnn_enable_peer_access(int peer_device);
 int dcnn_peer_barrier(unsigned long long* const* flag_ptrs, int rank, int world, unsigned long long* epoch_counter,
                       cudaStream_t stream);
+/* Push variant: gradient slices are copied into the owners' staging buffers, reduced from local memory, parameters
+ * are stored into every replica -- one launch, no load ever crosses NVLink (no counterpart in the reference). */
+int dcnn_fused_allreduce_update_push(float* const* grad_ptrs, float* const* param_ptrs, float* const* stage_ptrs,
+                                     const long long* sb, const long long* se, const long long* soff, float* s1,
+                                     float* s2, long long n, unsigned long long* const* start_flag_ptrs,
+                                     unsigned long long* const* done_flag_ptrs, unsigned int* block_counters, int rank,
+                                     int world, unsigned long long* epoch_counter, int mode, float lr, float a, float b,
+                                     float eps, float bc1, float bc2, float wd, const float* hyper, int num_blocks,
+                                     cudaStream_t stream);
 int dcnn_fused_allreduce_update(float* const* grad_ptrs, float* const* param_ptrs, float* s1, float* s2, long long n,
                                 long long shard_begin, long long shard_end,
                                 unsigned long long* const* start_flag_ptrs, unsigned long long* const* done_flag_ptrs,
