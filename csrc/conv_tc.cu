@@ -753,6 +753,7 @@ struct WgradTcParams {
   int Cin, Cout, Ktot;
   int num_taps, oc_tiles, c_tiles, splits;
   float* dw;  // [Cout][Ktot]
+  float* scratch;  // deterministic mode: [splits][Cout][Ktot] slabs written with plain stores (else nullptr)
   // operand descriptors are runtime values so that layout experiments do not need a rebuild
   uint64_t desc_hi_a, desc_hi_b;
   uint32_t idesc;
@@ -886,14 +887,25 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
         tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + cc, v);
         tmem_ld_wait();
         if (oc < p.Cout) {
-          float* dst = p.dw + (long long)oc * p.Ktot + (long long)p.tap_w[tap] * p.Cin + c0 + cc;
+          const long long off = (long long)oc * p.Ktot + (long long)p.tap_w[tap] * p.Cin + c0 + cc;
+          if (p.scratch != nullptr) {
+            // deterministic mode: this split's slab, summed over the splits in a fixed order by wgrad_reduce_kernel
+            float* dst = p.scratch + (long long)blockIdx.y * p.Cout * p.Ktot + off;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            if (c0 + cc + j < p.Cin) {
-              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j),
-                           "f"(__uint_as_float(v[j])), "f"(__uint_as_float(v[j + 1])),
-                           "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3]))
-                           : "memory");
+            for (int j = 0; j < 32; j += 4)
+              if (c0 + cc + j < p.Cin)
+                *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                                 __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+          } else {
+            float* dst = p.dw + off;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              if (c0 + cc + j < p.Cin) {
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j),
+                             "f"(__uint_as_float(v[j])), "f"(__uint_as_float(v[j + 1])),
+                             "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3]))
+                             : "memory");
+              }
             }
           }
         }
@@ -906,6 +918,20 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, BNW);
+  }
+}
+
+// dW[i] += sum over the split slabs in index order: the deterministic counterpart of the red.global.add epilogue.
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ scratch, float* __restrict__ dw,
+                                                           int splits, long long total4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    float4 a = *reinterpret_cast<const float4*>(dw + i * 4);
+    for (int s = 0; s < splits; ++s) {
+      const float4 v = *reinterpret_cast<const float4*>(scratch + ((long long)s * total4 + i) * 4);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    *reinterpret_cast<float4*>(dw + i * 4) = a;
   }
 }
 
@@ -1214,28 +1240,60 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
 // dW[oc][tap_w*Cin + c] += sum_{n,oh,ow} dY[n,oh,ow,oc] * X[n, oh*mul_h + tap_dh, ow*mul_w + tap_dw, c]
 // dy: NHWC [N][OH][OW][Cout]; x: NHWC [N][H][W][Cin] (Cin % 4 == 0, Cout % 4 == 0; channel counts that are not
 // multiples of 32 are padded with zeros by the TMA unit, the write-back is guarded).
+static void wgrad_geometry(int N, int OH, int OW, int Cout, int Cin, int in_mul_h, int in_mul_w, int num_taps,
+                           WgradTcParams* p, int* bnw_out) {
+  choose_box(N, OH, OW, kWPix, in_mul_h, in_mul_w, &p->bn, &p->bh, &p->bw);
+  p->tiles_n = ceil_div(N, p->bn); p->tiles_h = ceil_div(OH, p->bh); p->tiles_w = ceil_div(OW, p->bw);
+  p->oc_tiles = ceil_div(Cout, 128);
+  // (128 x 256 tiles were tried -- 42.7 instead of 32 FLOP per operand byte, two 96 KB stages -- and measured no faster
+  // than 128 x 128 with three stages on the ResNet-50 step: profiles/05.)
+  const int bnw = Cin >= 128 ? 128 : 64;
+  p->c_tiles = ceil_div(Cin, bnw);
+  const int pix_tiles = p->tiles_n * p->tiles_h * p->tiles_w;
+  const int base = num_taps * p->oc_tiles * p->c_tiles;
+  int splits = ceil_div(2 * num_sms(), base);
+  if (splits > pix_tiles) splits = pix_tiles;
+  if (splits < 1) splits = 1;
+  // make every split non-empty
+  const int per = ceil_div(pix_tiles, splits);
+  p->splits = ceil_div(pix_tiles, per);
+  *bnw_out = bnw;
+}
+
+// Number of split-K slabs dcnn_wgrad_tc uses for this problem: the deterministic mode's scratch buffer holds
+// splits * Cout * Ktot floats.
+DCNN_API int dcnn_wgrad_tc_splits(int N, int OH, int OW, int Cout, int Cin, int in_mul_h, int in_mul_w, int num_taps) {
+  WgradTcParams p;
+  memset(&p, 0, sizeof(p));
+  int bnw;
+  wgrad_geometry(N, OH, OW, Cout, Cin, in_mul_h, in_mul_w, num_taps, &p, &bnw);
+  return p.splits;
+}
+
+// dW[oc][tap_w*Cin + c] += sum_{n,oh,ow} dY[n,oh,ow,oc] * X[n, oh*mul_h + tap_dh, ow*mul_w + tap_dw, c]
+// dy: NHWC [N][OH][OW][Cout]; x: NHWC [N][H][W][Cin] (Cin % 4 == 0, Cout % 4 == 0; channel counts that are not
+// multiples of 32 are padded with zeros by the TMA unit, the write-back is guarded).
+// scratch == NULL: split-K partial sums are added with red.global.add (fast; the order of the additions, and so the last
+// bits of dW, vary from run to run).  scratch != NULL (dcnn_wgrad_tc_splits * Cout * Ktot floats): every split writes
+// its own slab and a second kernel sums the slabs in index order -- bit-reproducible gradients.
 DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin,
                            float* dw, int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh,
-                           const int* tap_dw, const int* tap_w, cudaStream_t stream) {
+                           const int* tap_dw, const int* tap_w, float* scratch, cudaStream_t stream) {
   DCNN_REQUIRE(Cin % 4 == 0, "dcnn_wgrad_tc: Cin (%d) must be a multiple of 4", Cin);
   DCNN_REQUIRE(Cout % 4 == 0, "dcnn_wgrad_tc: Cout (%d) must be a multiple of 4", Cout);
   DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_wgrad_tc: bad tap count %d", num_taps);
   WgradTcParams p;
   memset(&p, 0, sizeof(p));
   p.N = N; p.OH = OH; p.OW = OW;
-  choose_box(N, OH, OW, kWPix, in_mul_h, in_mul_w, &p.bn, &p.bh, &p.bw);
-  p.tiles_n = ceil_div(N, p.bn); p.tiles_h = ceil_div(OH, p.bh); p.tiles_w = ceil_div(OW, p.bw);
+  int bnw;
+  wgrad_geometry(N, OH, OW, Cout, Cin, in_mul_h, in_mul_w, num_taps, &p, &bnw);
   p.in_mul_h = in_mul_h; p.in_mul_w = in_mul_w;
   p.Cin = Cin; p.Cout = Cout; p.Ktot = Ktot; p.num_taps = num_taps;
   p.dw = dw;
+  p.scratch = scratch;
   for (int t = 0; t < num_taps; ++t) {
     p.tap_dh[t] = (int16_t)tap_dh[t]; p.tap_dw[t] = (int16_t)tap_dw[t]; p.tap_w[t] = (int16_t)tap_w[t];
   }
-  p.oc_tiles = ceil_div(Cout, 128);
-  const bool wide = Cin >= 128;
-  // (128 x 256 tiles were tried -- 42.7 instead of 32 FLOP per operand byte, two 96 KB stages -- and measured no faster
-  // than 128 x 128 with three stages on the ResNet-50 step: profiles/05.)
-  const int bnw = wide ? 128 : 64;
   CUtensorMapSwizzle wgrad_swizzle = CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B;
   {
     // MN-major TF32 operands must use the 128B-swizzle-with-32B-atoms layout (TMA: SWIZZLE_128B_ATOM_32B, UMMA
@@ -1253,23 +1311,20 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
     p.idesc = make_idesc_tf32(128, bnw, a_mn, b_mn);
     p.k_step_bytes = kstep;
   }
-  p.c_tiles = ceil_div(Cin, bnw);
-  const int pix_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
-  const int base = num_taps * p.oc_tiles * p.c_tiles;
-  int splits = ceil_div(2 * num_sms(), base);
-  if (splits > pix_tiles) splits = pix_tiles;
-  if (splits < 1) splits = 1;
-  // make every split non-empty
-  const int per = ceil_div(pix_tiles, splits);
-  splits = ceil_div(pix_tiles, per);
-  p.splits = splits;
   CUtensorMap tmDY, tmX;
   int rc = make_tmap_nhwc(&tmDY, dy, N, OH, OW, Cout, p.bn, p.bh, p.bw, 1, 1, wgrad_swizzle);
   if (rc) return rc;
   rc = make_tmap_nhwc(&tmX, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w, wgrad_swizzle);
   if (rc) return rc;
-  if (wide) return launch_wgrad<128, 3>(tmDY, tmX, p, stream);
-  return launch_wgrad<64, 4>(tmDY, tmX, p, stream);
+  rc = bnw == 128 ? launch_wgrad<128, 3>(tmDY, tmX, p, stream) : launch_wgrad<64, 4>(tmDY, tmX, p, stream);
+  if (rc) return rc;
+  if (scratch != nullptr) {
+    const long long total4 = (long long)Cout * Ktot / 4;   // Ktot % 4 == 0 since Cin % 4 == 0
+    wgrad_reduce_kernel<<<ew_grid(total4, 256), 256, 0, stream>>>(scratch, dw, p.splits, total4);
+    DCNN_CHECK_LAUNCH();
+    DCNN_COUNT_LAUNCH(1);
+  }
+  return 0;
 }
 
 // ---------------------------------------------------------------------------------------------------------

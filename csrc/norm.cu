@@ -401,16 +401,19 @@ __global__ void bn_apply_scalar_kernel(const float* __restrict__ x, const float*
 // RELU: 0 = no mask, 1 = mask from the saved activation output (needed when a residual was added before the ReLU),
 // 2 = mask recomputed as fmaf(x, scale, shift) > 0 -- bit-identical to what bn_apply_kernel evaluated in the forward
 // pass, and one activation-sized read cheaper (`out` then carries scale[C] followed by shift[C]).
-template <int RELU>
+// TX = threads along the channel dimension (4 channels each); the other 256 / TX threads stride over the rows.  Narrow
+// tensors (C = 64: 16 float4 columns) would leave half of a 32-wide row idle, so TX follows C.
+template <int RELU, int TX>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restrict__ dout, const float* __restrict__ x,
                                                             const float* __restrict__ out,
                                                             const float* __restrict__ mean,
                                                             const float* __restrict__ invstd, long long M, int C,
                                                             int rows_per_tile, float* __restrict__ partials) {
-  __shared__ float4 s_a[8][32];
-  __shared__ float4 s_b[8][32];
+  constexpr int TY = 256 / TX;
+  __shared__ float4 s_a[TY][TX];
+  __shared__ float4 s_b[TY][TX];
   const int tile = blockIdx.x;
-  const int c = (blockIdx.y * 32 + threadIdx.x) * 4;
+  const int c = (blockIdx.y * TX + threadIdx.x) * 4;
   const long long r0 = (long long)tile * rows_per_tile, r1 = min(M, r0 + rows_per_tile);
   const bool active = c < C;
   float4 a = make_float4(0, 0, 0, 0), b = a;
@@ -419,7 +422,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
     float4 sc = make_float4(0, 0, 0, 0), sf = sc;
     if (RELU == 2) { sc = ldg4(out + c); sf = ldg4(out + C + c); }
 #pragma unroll 4
-    for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+    for (long long r = r0 + threadIdx.y; r < r1; r += TY) {
       float4 g = ldg4(dout + r * C + c);
       const float4 v = ldg4(x + r * C + c);
       if (RELU == 1) {
@@ -443,7 +446,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
   s_b[threadIdx.y][threadIdx.x] = b;
   __syncthreads();
   if (threadIdx.y == 0 && active) {
-    for (int i = 1; i < 8; ++i) {
+    for (int i = 1; i < TY; ++i) {
       const float4 p = s_a[i][threadIdx.x], q = s_b[i][threadIdx.x];
       a.x += p.x; a.y += p.y; a.z += p.z; a.w += p.w;
       b.x += q.x; b.y += q.y; b.z += q.z; b.w += q.w;
@@ -869,17 +872,51 @@ DCNN_API int dcnn_bn_apply_mask(const float* x, const float* scale, const float*
   return 0;
 }
 
+// Row tiling of the backward reduce.  It has its own rule (the forward statistics kernel and the allocation-free entry
+// point keep stat_rows_per_tile): the tensors it reads are often small (8-70 MB at batch 256), so it wants at least
+// four CTAs per SM even when that means 32-row tiles, and it counts the CTAs along the channel dimension.
+static int bwd_tx(int C) { return C >= 128 ? 32 : (C >= 64 ? 16 : 8); }
+static int bwd_rows_per_tile(long long M, int C, int* tiles) {
+  const int tx = bwd_tx(C), ty = 256 / tx;
+  const long long col_ctas = (C & 3) == 0 ? ceil_div(C, 4 * tx) : ceil_div(C, 32);
+  long long want = ceil_div((long long)num_sms() * 4, col_ctas);
+  if (want < 1) want = 1;
+  long long rows = ceil_div(M, want);
+  if (rows < 32) rows = 32;
+  if (rows > 256) rows = 256;
+  rows = ceil_div(rows, ty) * ty;
+  *tiles = (int)ceil_div(M, rows);
+  return (int)rows;
+}
+
+// Number of row tiles dcnn_bn_bwd_reduce produces for an [M][C] tensor: its partials buffer holds tiles*2*C floats.
+DCNN_API int dcnn_bn_bwd_tiles(long long M, int C) {
+  int tiles;
+  bwd_rows_per_tile(M, C, &tiles);
+  return tiles;
+}
+
+template <int TX>
+static void launch_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean,
+                              const float* invstd, long long M, int C, int relu, int rows, int tiles, float* partials,
+                              cudaStream_t stream) {
+  dim3 grid(tiles, ceil_div(C, 4 * TX)), block(TX, 256 / TX);
+  if (relu == 3) bn_bwd_reduce_kernel<3, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+  else if (relu == 2) bn_bwd_reduce_kernel<2, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+  else if (relu) bn_bwd_reduce_kernel<1, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+  else bn_bwd_reduce_kernel<0, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+}
+
 DCNN_API int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean,
                                 const float* invstd, long long M, int C, int relu, float* partials,
                                 cudaStream_t stream) {
   int tiles;
-  const int rows = stat_rows_per_tile(M, &tiles);
+  const int rows = bwd_rows_per_tile(M, C, &tiles);
   if ((C & 3) == 0) {
-    dim3 grid(tiles, ceil_div(C, 128)), block(32, 8);
-    if (relu == 3) bn_bwd_reduce_kernel<3><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
-    else if (relu == 2) bn_bwd_reduce_kernel<2><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
-    else if (relu) bn_bwd_reduce_kernel<1><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
-    else bn_bwd_reduce_kernel<0><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
+    const int tx = bwd_tx(C);
+    if (tx == 32) launch_bwd_reduce<32>(dout, x, out, mean, invstd, M, C, relu, rows, tiles, partials, stream);
+    else if (tx == 16) launch_bwd_reduce<16>(dout, x, out, mean, invstd, M, C, relu, rows, tiles, partials, stream);
+    else launch_bwd_reduce<8>(dout, x, out, mean, invstd, M, C, relu, rows, tiles, partials, stream);
   } else {
     dim3 grid(tiles, ceil_div(C, 32));
     bn_bwd_reduce_scalar_kernel<<<grid, 32, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials, relu);
@@ -942,10 +979,13 @@ DCNN_API int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* o
   return 0;
 }
 
-DCNN_API int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, cudaStream_t stream) {
+// deterministic != 0: one CTA per column group walks all rows, so every db[c] receives exactly one atomicAdd per call
+// (the sum of two numbers does not depend on the order); otherwise row blocks add their partial sums in arrival order.
+DCNN_API int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, int deterministic, cudaStream_t stream) {
   long long target = (long long)num_sms() * 4;
   long long rows = (M + target - 1) / target;
   if (rows < 64) rows = 64;
+  if (deterministic) rows = M;
   dim3 grid(ceil_div(M, rows), ceil_div(C, 32)), block(32, 8);
   colsum_accum_kernel<<<grid, block, 0, stream>>>(dy, M, C, (int)rows, db);
   DCNN_CHECK_LAUNCH();

@@ -36,6 +36,20 @@ RECOMPUTE_RELU_MASK = os.environ.get("DCNN_BN_RECOMPUTE_MASK", "1") != "0"
 RELU_BITMASK = os.environ.get("DCNN_BN_BITMASK", "1") == "1"
 
 
+# DCNN_DETERMINISTIC=1: bit-reproducible gradients -- the split-K partial sums of the tensor-core weight gradient go to
+# per-split slabs that a second kernel adds in index order (instead of red.global.add), and the bias-gradient column sums
+# use one CTA per column group.  Costs one extra pass over splits x |dW| floats per convolution.
+def deterministic() -> bool:
+    return os.environ.get("DCNN_DETERMINISTIC", "0") == "1"
+
+
+def _wgrad_scratch(N, OH, OW, K, Cin, sh_, sw_, ntaps, ktot, device):
+    if not deterministic():
+        return None
+    splits = lib().dcnn_wgrad_tc_splits(I(N), I(OH), I(OW), I(K), I(Cin), I(sh_), I(sw_), I(ntaps))
+    return torch.empty(splits * K * ktot, device=device, dtype=torch.float32)
+
+
 def tc_enabled() -> bool:
     return os.environ.get("DCNN_DISABLE_TC", "0") != "1"
 
@@ -354,8 +368,10 @@ def conv2d_backward_weight(dy, x, dw, stride, pad):
             [s - pw for r in range(R) for s in range(S)],
             [r * S + s for r in range(R) for s in range(S)]))
         n, dh, dw_, wi = taps
+        scratch = _wgrad_scratch(N, OH, OW, K, Cin, sh_, sw_, n, R * S * Cin, dy.device)
         check(lib().dcnn_wgrad_tc(_p(dy), I(N), I(OH), I(OW), I(K), _p(x), I(H), I(W), I(Cin), _p(dw),
-                                  I(R * S * Cin), I(sh_), I(sw_), I(n), dh, dw_, wi, _stream()), "dcnn_wgrad_tc")
+                                  I(R * S * Cin), I(sh_), I(sw_), I(n), dh, dw_, wi, _p(scratch), _stream()),
+              "dcnn_wgrad_tc")
         return
     check(lib().dcnn_conv_wgrad_simt(_p(dy), _p(x), _p(dw), I(N), I(H), I(W), I(Cin), I(K), I(R), I(S), I(sh_),
                                      I(sw_), I(ph), I(pw), _stream()), "conv_wgrad_simt")
@@ -365,7 +381,8 @@ def bias_grad(dy, db):
     dy = as_nhwc(dy) if dy.dim() == 4 else dy.contiguous()
     Cc = dy.shape[1]
     M = dy.numel() // Cc
-    check(lib().dcnn_colsum_accum(_p(dy), LL(M), I(Cc), _p(db), _stream()), "colsum_accum")
+    check(lib().dcnn_colsum_accum(_p(dy), LL(M), I(Cc), _p(db), I(1 if deterministic() else 0), _stream()),
+          "colsum_accum")
 
 
 # ================================================================================== dense (1x1 conv on [B,1,1,C])
@@ -413,8 +430,9 @@ def dense_backward_weight(dy2d, x2d, dw2d):
     Fin = x2d.shape[1]
     if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0:
         n, dh, dw_, wi = _one_tap()
+        scratch = _wgrad_scratch(B, 1, 1, Fout, Fin, 1, 1, 1, Fin, dy2d.device)
         check(lib().dcnn_wgrad_tc(_p(dy2d), I(B), I(1), I(1), I(Fout), _p(x2d), I(1), I(1), I(Fin), _p(dw2d), I(Fin),
-                                  I(1), I(1), I(n), dh, dw_, wi, _stream()), "dense wgrad tc")
+                                  I(1), I(1), I(n), dh, dw_, wi, _p(scratch), _stream()), "dense wgrad tc")
     else:
         check(lib().dcnn_conv_wgrad_simt(_p(dy2d), _p(x2d), _p(dw2d), I(B), I(1), I(1), I(Fin), I(Fout), I(1), I(1),
                                          I(1), I(1), I(0), I(0), _stream()), "dense wgrad simt")
@@ -489,7 +507,7 @@ def bn_backward(dout, x, out, mean, invstd, gamma, dgamma, dbeta, relu=False, wa
         relu_mode, out = 3, relu_mask          # 4 bits per float4 written by bn_apply(mask_out=...)
     Cc = x.shape[1]
     M = x.numel() // Cc
-    tiles = lib().dcnn_bn_stat_tiles(LL(M))
+    tiles = lib().dcnn_bn_bwd_tiles(LL(M), I(Cc))
     partials = torch.empty(tiles * 2 * Cc, device=x.device, dtype=torch.float32)
     check(lib().dcnn_bn_bwd_reduce(_p(dout), _p(x), _p(out), _p(mean), _p(invstd), LL(M), I(Cc),
                                    I(relu_mode), _p(partials), _stream()), "bn_bwd_reduce")

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Print CPU / memory / NUMA / GPU information (examples/hardware_info_example.cpp, device_manager_example.cpp)."""
+"""Print CPU / memory / NUMA / GPU information and the thread-affinity view (examples/hardware_info_example.cpp)."""
 from _common import sys  # noqa: F401
 
 from dcnn_b200.utils.device import DeviceManager, DeviceType, initializeDefaultDevices

@@ -29,9 +29,12 @@ int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, i
                  long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h, int in_mul_w,
                  int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w, const float* bias,
                  int accumulate, float* partials, cudaStream_t stream);
+/* scratch == NULL: split-K sums by red.global.add (order varies run to run); scratch = dcnn_wgrad_tc_splits * Cout * Ktot
+ * floats: per-split slabs summed in index order by a second kernel (bit-reproducible). */
+int dcnn_wgrad_tc_splits(int N, int OH, int OW, int Cout, int Cin, int in_mul_h, int in_mul_w, int num_taps);
 int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin, float* dw,
                   int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw,
-                  const int* tap_w, cudaStream_t stream);
+                  const int* tap_w, float* scratch, cudaStream_t stream);
 /* measurement tool: persistent CTAs stream TMA operand tiles with no MMA (per-SM / chip-wide ingest rate, effect of a
  * shared B tile); see scripts/tma_ingest_probe.py */
 int dcnn_tma_stream_probe(const float* A, long long a_total_rows, long long a_cols, int a_rows, const float* B,
@@ -75,6 +78,7 @@ int dcnn_bn_apply(const float* x, const float* scale, const float* shift, const 
  * 2 mask recomputed from x (out -> scale[C] | shift[C]), 3 mask bytes. */
 int dcnn_bn_apply_mask(const float* x, const float* scale, const float* shift, const float* residual, float* y,
                        unsigned char* mask, long long M, int C, cudaStream_t stream);
+int dcnn_bn_bwd_tiles(long long M, int C);   /* row tiles of dcnn_bn_bwd_reduce: partials = tiles*2*C floats */
 int dcnn_bn_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean, const float* invstd,
                        long long M, int C, int relu, float* partials, cudaStream_t stream);
 int dcnn_bn_bwd_finalize(const float* partials, int tiles, int C, double count, const float* mean,
@@ -86,7 +90,7 @@ int dcnn_bn_bwd_finalize_sync1(const float* partials, int tiles, int C, double c
                                cudaStream_t stream);
 int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* out, const float* k1, const float* k2,
                       const float* k3, float* dx, float* masked, long long M, int C, int relu, cudaStream_t stream);
-int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, cudaStream_t stream);
+int dcnn_colsum_accum(const float* dy, long long M, int C, float* db, int deterministic, cudaStream_t stream);
 /* Allocation-free variant of dcnn_bn_colstats + dcnn_bn_finalize (no counterpart in the reference).  For callers
  * that may not allocate device memory when they need the statistics (no access to an allocator, or not allowed to
  * take its lock): the per-tile scratch lives in a 4 MiB `static __device__` array inside the library instead of a

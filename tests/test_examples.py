@@ -23,6 +23,7 @@ SIMPLE_EXAMPLES = [
     ("uji_ips_trainer.py", "Validation - Loss"),
     ("sync_pipeline_coordinator.py", "Stopped all pipeline stages"),
     ("hardware_info_example.py", "Available devices"),
+    ("device_manager_example.py", "Memory access test passed"),
     ("tiny_imagenet_visual_check.py", "PNG files"),
     ("device_ptr_example.py", "grow-only"),
     ("cuda_vs_avx2_comparison.py", "native AVX2"),

@@ -62,6 +62,13 @@ def test_trainer_runs_on_the_gpu_and_its_snapshot_loads_in_the_reference(tmp_pat
     assert float((y - y_ref).abs().max()) < 1e-3 * max(1.0, float(y_ref.abs().max()))
 
 
+def test_device_manager_example_exercises_the_gpu(tmp_path):
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "device_manager_example.py")], cwd=str(tmp_path),
+                       env=ENV, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "Successfully allocated 1073741824 bytes on GPU" in r.stdout and "Round trip over flow 'copies': passed" in r.stdout
+
+
 COORDINATORS = ["semi_async_pipeline_coordinator.py", "sync_pipeline_coordinator.py", "coordinator_tiny_imagenet.py"]
 
 

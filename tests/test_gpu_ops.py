@@ -170,6 +170,32 @@ def test_conv_backward_weight(case):
     check_close(db, db_ref, 1e-4, "bias grad")
 
 
+@pytest.mark.parametrize("case", [(8, 64, 16, 16, 128, 3, 1, 1), (4, 256, 8, 8, 64, 1, 1, 0), (6, 20, 9, 9, 12, 3, 2, 1)],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_conv_wgrad_deterministic_mode(case, monkeypatch):
+    """DCNN_DETERMINISTIC=1: split-K slabs summed in index order -- two runs give the same bits (and the right values),
+    also when the call accumulates into an existing gradient; bias gradients likewise."""
+    monkeypatch.setenv("DCNN_DETERMINISTIC", "1")
+    N, C, H, W, OC, k, s, p = case
+    x = torch.randn(N, C, H, W)
+    oh = (H + 2 * p - k) // s + 1
+    dy = torch.randn(N, OC, oh, oh)
+    dw_ref = torch.zeros(OC, C, k, k)
+    ref.conv2d_backward_weight(dy, x, dw_ref, (s, s), (p, p))
+    xg, dyg = cl(x), cl(dy)
+    runs = []
+    for _ in range(3):
+        dw = cl(torch.zeros(OC, C, k, k))
+        ops.conv2d_backward_weight(dyg, xg, dw, (s, s), (p, p))
+        ops.conv2d_backward_weight(dyg, xg, dw, (s, s), (p, p))
+        db = torch.zeros(OC, 1, 1, 1, device=DEV)
+        ops.bias_grad(dyg, db)
+        runs.append((dw.clone(), db.clone()))
+    check_close(runs[0][0], 2 * dw_ref, 4e-3, "deterministic wgrad")
+    for dw, db in runs[1:]:
+        assert torch.equal(dw, runs[0][0]) and torch.equal(db, runs[0][1])
+
+
 def test_conv_fp32_exact_mode(monkeypatch):
     monkeypatch.setenv("DCNN_DISABLE_TC", "1")
     x, w = torch.randn(2, 64, 8, 8), torch.randn(32, 64, 3, 3) / 24
