@@ -268,9 +268,12 @@ DCNN_API int dcnn_nvls_add_device(unsigned long long handle, int device) {
 }
 
 // Every rank: allocate `bytes` of device memory, map it (unicast pointer), bind it to the multicast object at offset 0
-// and map the multicast object (multicast pointer).  The memory is zero-initialised.
-DCNN_API int dcnn_nvls_bind(unsigned long long handle, int device, long long bytes, void** uc_ptr, void** mc_ptr) {
+// and map the multicast object (multicast pointer).  The memory is zero-initialised.  *mem_handle_out is the allocation
+// handle dcnn_nvls_release needs.  Whatever was set up before a failing step is undone.
+DCNN_API int dcnn_nvls_bind(unsigned long long handle, int device, long long bytes, void** uc_ptr, void** mc_ptr,
+                            unsigned long long* mem_handle_out) {
   const DriverApi& d = driver();
+  DCNN_REQUIRE(d.ok, "multicast driver API not available");
   const size_t size = (size_t)bytes;
   CUmemAllocationProp ap;
   memset(&ap, 0, sizeof(ap));
@@ -278,25 +281,64 @@ DCNN_API int dcnn_nvls_bind(unsigned long long handle, int device, long long byt
   ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   ap.location.id = device;
   ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
-  CUmemGenericAllocationHandle mem;
-  DCNN_CHECK_CU(d.MemCreate(&mem, size, &ap, 0));
+  CUmemGenericAllocationHandle mem = 0;
   CUmemAccessDesc acc;
   memset(&acc, 0, sizeof(acc));
   acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   acc.location.id = device;
   acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
   CUdeviceptr uc = 0, mc = 0;
-  DCNN_CHECK_CU(d.MemAddressReserve(&uc, size, 0, 0, 0));
-  DCNN_CHECK_CU(d.MemMap(uc, size, 0, mem, 0));
-  DCNN_CHECK_CU(d.MemSetAccess(uc, size, &acc, 1));
-  DCNN_CHECK_CUDA(cudaMemset((void*)uc, 0, size));
-  DCNN_CHECK_CUDA(cudaDeviceSynchronize());
-  DCNN_CHECK_CU(d.MulticastBindMem((CUmemGenericAllocationHandle)handle, 0, mem, 0, size, 0));
-  DCNN_CHECK_CU(d.MemAddressReserve(&mc, size, 0, 0, 0));
-  DCNN_CHECK_CU(d.MemMap(mc, size, 0, (CUmemGenericAllocationHandle)handle, 0));
-  DCNN_CHECK_CU(d.MemSetAccess(mc, size, &acc, 1));
+  bool uc_mapped = false, mc_mapped = false;
+  CUresult r = d.MemCreate(&mem, size, &ap, 0);
+  const char* what = "cuMemCreate";
+  if (r == CUDA_SUCCESS) { what = "cuMemAddressReserve"; r = d.MemAddressReserve(&uc, size, 0, 0, 0); }
+  if (r == CUDA_SUCCESS) { what = "cuMemMap"; r = d.MemMap(uc, size, 0, mem, 0); uc_mapped = r == CUDA_SUCCESS; }
+  if (r == CUDA_SUCCESS) { what = "cuMemSetAccess"; r = d.MemSetAccess(uc, size, &acc, 1); }
+  if (r == CUDA_SUCCESS) {
+    what = "cudaMemset";
+    if (cudaMemset((void*)uc, 0, size) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) r = CUDA_ERROR_UNKNOWN;
+  }
+  if (r == CUDA_SUCCESS) { what = "cuMulticastBindMem"; r = d.MulticastBindMem((CUmemGenericAllocationHandle)handle, 0, mem, 0, size, 0); }
+  if (r == CUDA_SUCCESS) { what = "cuMemAddressReserve (multicast)"; r = d.MemAddressReserve(&mc, size, 0, 0, 0); }
+  if (r == CUDA_SUCCESS) {
+    what = "cuMemMap (multicast)";
+    r = d.MemMap(mc, size, 0, (CUmemGenericAllocationHandle)handle, 0);
+    mc_mapped = r == CUDA_SUCCESS;
+  }
+  if (r == CUDA_SUCCESS) { what = "cuMemSetAccess (multicast)"; r = d.MemSetAccess(mc, size, &acc, 1); }
+  if (r != CUDA_SUCCESS) {
+    if (mc_mapped) d.MemUnmap(mc, size);
+    if (mc) d.MemAddressFree(mc, size);
+    if (uc_mapped) d.MemUnmap(uc, size);
+    if (uc) d.MemAddressFree(uc, size);
+    if (mem) d.MemRelease(mem);
+    cudaGetLastError();
+    DCNN_REQUIRE(false, "dcnn_nvls_bind: %s failed with CUresult %d", what, (int)r);
+  }
   *uc_ptr = (void*)uc;
   *mc_ptr = (void*)mc;
+  *mem_handle_out = (unsigned long long)mem;
+  return 0;
+}
+
+// Undo dcnn_nvls_bind (and drop this process's reference to the multicast object): unmap and free both address ranges,
+// release the allocation and the object handle.  Every rank calls it once all work on the buffers has finished.
+DCNN_API int dcnn_nvls_release(unsigned long long handle, unsigned long long mem_handle, void* uc_ptr, void* mc_ptr,
+                               long long bytes) {
+  const DriverApi& d = driver();
+  DCNN_REQUIRE(d.ok, "multicast driver API not available");
+  const size_t size = (size_t)bytes;
+  DCNN_CHECK_CUDA(cudaDeviceSynchronize());
+  if (mc_ptr) {
+    DCNN_CHECK_CU(d.MemUnmap((CUdeviceptr)mc_ptr, size));
+    DCNN_CHECK_CU(d.MemAddressFree((CUdeviceptr)mc_ptr, size));
+  }
+  if (uc_ptr) {
+    DCNN_CHECK_CU(d.MemUnmap((CUdeviceptr)uc_ptr, size));
+    DCNN_CHECK_CU(d.MemAddressFree((CUdeviceptr)uc_ptr, size));
+  }
+  if (mem_handle) DCNN_CHECK_CU(d.MemRelease((CUmemGenericAllocationHandle)mem_handle));
+  if (handle) DCNN_CHECK_CU(d.MemRelease((CUmemGenericAllocationHandle)handle));
   return 0;
 }
 

@@ -76,6 +76,22 @@ class SymmetricBuffer:
     def peer_array(self, offset_bytes: int = 0):
         return (C.c_void_p * self.world)(*[p + offset_bytes for p in self.peer_ptrs])
 
+    def close(self):
+        """Collective: every rank closes its mappings of the peers' buffers, then frees its own.  Tensors viewing the
+        buffer must not be used afterwards."""
+        from .._lib import check, lib
+        if self.ptr is None:
+            return
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+        self._bytes = None
+        for r, p in enumerate(self.peer_ptrs):
+            if r != self.rank:
+                check(lib().dcnn_ipc_close(C.c_void_p(p)), "dcnn_ipc_close")
+        dist.barrier(group=self.group)            # nobody frees memory that a peer still has mapped
+        check(lib().dcnn_dev_free(C.c_void_p(self.ptr)), "dcnn_dev_free")
+        self.ptr, self.peer_ptrs = None, []
+
 
 def send_fd_to_ranks(tag: str, ranks, fd: int, timeout_s: float = 60.0):
     """Hand a file descriptor to other local processes: each receiver listens on the abstract-namespace UNIX socket
@@ -158,10 +174,10 @@ class NvlsBuffer:
         self.handle = handle.value
         check(l.dcnn_nvls_add_device(C.c_ulonglong(self.handle), C.c_int(dev)), "dcnn_nvls_add_device")
         dist.barrier(group=group)                      # every device is part of the object before anyone binds
-        uc, mc = C.c_void_p(), C.c_void_p()
+        uc, mc, mem = C.c_void_p(), C.c_void_p(), C.c_ulonglong(0)
         check(l.dcnn_nvls_bind(C.c_ulonglong(self.handle), C.c_int(dev), C.c_longlong(self.nbytes), C.byref(uc),
-                               C.byref(mc)), "dcnn_nvls_bind")
-        self.ptr, self.mc_ptr = uc.value, mc.value
+                               C.byref(mc), C.byref(mem)), "dcnn_nvls_bind")
+        self.ptr, self.mc_ptr, self.mem_handle = uc.value, mc.value, mem.value
         self._bytes = torch.as_tensor(_RawCuda(self.ptr, self.nbytes), device=device)
         torch.cuda.synchronize(device)
         dist.barrier(group=group)                      # all bindings exist before the first multimem access
@@ -169,6 +185,19 @@ class NvlsBuffer:
     def view(self, dtype, offset_bytes: int, numel: int) -> torch.Tensor:
         size = torch.empty((), dtype=dtype).element_size()
         return self._bytes[offset_bytes:offset_bytes + numel * size].view(dtype)
+
+    def close(self):
+        """Collective: unmap both views, release the allocation and the multicast object.  Tensors viewing the buffer
+        must not be used afterwards."""
+        from .._lib import check, lib
+        if self.ptr is None:
+            return
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+        self._bytes = None
+        check(lib().dcnn_nvls_release(C.c_ulonglong(self.handle), C.c_ulonglong(self.mem_handle), C.c_void_p(self.ptr),
+                                      C.c_void_p(self.mc_ptr), C.c_longlong(self.nbytes)), "dcnn_nvls_release")
+        self.ptr = self.mc_ptr = None
 
 
 class SyncBN:
@@ -579,6 +608,29 @@ class DataParallel:
         self._launched = set()
         self._step_args = None
         self.final_backward = False
+
+    def close(self):
+        """Collective: release the symmetric buffers (parameters and gradients move to ordinary tensors first, so the
+        model stays usable on its own)."""
+        if self.device.type != "cuda":
+            return
+        if self.fused:
+            params = [p.detach().clone(memory_format=torch.preserve_format) for p in self.model.parameters()]
+            grads = [g.detach().clone(memory_format=torch.preserve_format) for g in self.model.gradients()]
+            used = 0
+            for l in self.model.layers:
+                used += l.rebind_parameters(params[used:], grads[used:])
+            self.flat_param = self.flat_grad = self.s1 = self.s2 = None
+            from .. import ops
+            ops.weights_changed()
+        for l in _all_layers(self.model):
+            if isinstance(l, BatchNormLayer):
+                l.sync = None
+        for name in ("buf", "stage_buf", "state_buf", "bn_buf", "ctl"):
+            b = getattr(self, name, None)
+            if b is not None:
+                b.close()
+                setattr(self, name, None)
 
     def reset_step_bookkeeping(self):
         """Forget a step that was recorded but never ran (an aborted CUDA-graph capture).  The rendezvous epochs and the

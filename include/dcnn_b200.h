@@ -149,7 +149,10 @@ long long dcnn_nvls_padded_size(int world, long long bytes, int device);
 int dcnn_nvls_create(int world, long long bytes, unsigned long long* handle_out, int* fd_out);   /* rank 0 */
 int dcnn_nvls_import(int fd, unsigned long long* handle_out);                                    /* other ranks */
 int dcnn_nvls_add_device(unsigned long long handle, int device);   /* every rank, before any rank binds */
-int dcnn_nvls_bind(unsigned long long handle, int device, long long bytes, void** uc_ptr, void** mc_ptr);
+int dcnn_nvls_bind(unsigned long long handle, int device, long long bytes, void** uc_ptr, void** mc_ptr,
+                   unsigned long long* mem_handle_out);
+int dcnn_nvls_release(unsigned long long handle, unsigned long long mem_handle, void* uc_ptr, void* mc_ptr,
+                      long long bytes);   /* every rank, after the last use */
 int dcnn_fused_allreduce_update_nvls(const float* mc_grads, float* mc_params, const float* params, float* grads,
                                      float* s1, float* s2, long long n, long long shard_begin, long long shard_end,
                                      unsigned long long* const* start_flag_ptrs,

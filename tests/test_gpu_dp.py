@@ -77,6 +77,13 @@ def _worker(rank, world, port, out, kind, baseline, graph=False, steps=3, save_a
     if rank == 0:
         torch.save([p.detach().cpu().contiguous() for p in m.parameters()] +
                    [b.cpu() for b in m.buffers().values()], out)
+    if resume_from is not None:
+        # teardown of the symmetric buffers (IPC mappings closed, memory freed): the model keeps working on its own
+        before = [p.detach().clone() for p in m.parameters()]
+        dp.close()
+        assert all(torch.equal(a, b) for a, b in zip(before, m.parameters()))
+        y = m.forward(xs)
+        assert torch.isfinite(y).all()
     dist.destroy_process_group()
 
 
