@@ -379,7 +379,20 @@ DCNN_API int dcnn_fused_allreduce_update_push(float* const* grad_ptrs, float* co
   p.block_counter = block_counters; p.rank = rank; p.world = world; p.epoch_ptr = epoch_counter; p.hyper = hyper;
   p.lr = lr; p.a = a; p.b = b; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2; p.wd = wd; p.inv_world = 1.f / (float)world;
   p.mode = mode;
-  if (num_blocks <= 0 || num_blocks > num_sms()) num_blocks = num_sms();   // every CTA must be resident
+  // every CTA must be resident (they wait for each other's replicas): at most what the occupancy calculator allows
+  int per_sm = 1;
+  {
+    auto kern = world == 2 ? fused_allreduce_update_push_kernel<2>
+                           : (world == 4 ? fused_allreduce_update_push_kernel<4>
+                                         : (world == 8 ? fused_allreduce_update_push_kernel<8>
+                                                       : fused_allreduce_update_push_kernel<0>));
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 512, 0) != cudaSuccess || per_sm < 1) {
+      cudaGetLastError();
+      per_sm = 1;
+    }
+  }
+  if (num_blocks <= 0) num_blocks = num_sms();
+  if (num_blocks > per_sm * num_sms()) num_blocks = per_sm * num_sms();
   if (world == 2) fused_allreduce_update_push_kernel<2><<<num_blocks, 512, 0, stream>>>(q);
   else if (world == 4) fused_allreduce_update_push_kernel<4><<<num_blocks, 512, 0, stream>>>(q);
   else if (world == 8) fused_allreduce_update_push_kernel<8><<<num_blocks, 512, 0, stream>>>(q);
