@@ -37,6 +37,7 @@ struct ConvTcParams {
   int Cin, Cout, n_tiles;
   int num_taps;
   int accumulate;
+  int relu;                      // epilogue: out = max(out + bias, 0)  (Conv / Dense followed by ReLU without BatchNorm)
   long long out_sn, out_sh, out_sw;
   float* out;
   const float* bias;
@@ -113,6 +114,7 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
           o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
         }
       }
+      if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
       *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
     }
     fence_proxy_async();
@@ -754,9 +756,10 @@ struct WgradTcParams {
   int num_taps, oc_tiles, c_tiles, splits;
   float* dw;  // [Cout][Ktot]
   float* scratch;  // deterministic mode: [splits][Cout][Ktot] slabs written with plain stores (else nullptr)
+  float* db;       // bias gradient [Cout] (+=), or nullptr: column sums of dY by one extra N = 16 MMA against a tile of ones
   // operand descriptors are runtime values so that layout experiments do not need a rebuild
   uint64_t desc_hi_a, desc_hi_b;
-  uint32_t idesc;
+  uint32_t idesc, idesc_bias;
   uint32_t k_step_bytes;
   int16_t tap_dh[kMaxTaps], tap_dw[kMaxTaps], tap_w[kMaxTaps];
 };
@@ -767,7 +770,9 @@ struct WgradSmem {
   static constexpr int kBBytes = (BNW / 32) * kWPix * 128;  // BNW/32 boxes of [64 pix][32 c]
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kMainBytes = STAGES * kStageBytes;
-  static constexpr int kTotalBytes = kMainBytes + 1024 + 256;
+  static constexpr int kOnesOff = kMainBytes + 1024;   // [8 pixel rows][128 B] of 1.0f, the B operand of the bias-gradient MMA
+  static constexpr int kTotalBytes = kOnesOff + 2048 + 1024 /*align*/;
+  static_assert(kTotalBytes <= 232448, "wgrad shared memory exceeds 227 KB");
 };
 
 template <int BNW, int STAGES>
@@ -799,6 +804,11 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
   const int pt_end = min(pix_tiles, pt_begin + per);
   const int num_kb = max(0, pt_end - pt_begin);
   const int oc0 = oc_tile * 128, c0 = c_tile * BNW;
+  // bias gradient (cudnnConvolutionBackwardBias of the reference, cudnn_conv2d_ops.cu:234-247): db[oc] += sum over the
+  // pixels of dY[pixel, oc] = dY^T x ones -- the CTA of the first tap and first channel tile of each oc tile issues one
+  // extra N = 16 MMA per k-step against a constant tile of ones (zero-filled out-of-image pixels add nothing)
+  const bool bias_cta = p.db != nullptr && tap == 0 && c_tile == 0;
+  constexpr uint32_t kTmemCols = 2 * BNW;   // BNW accumulator columns + 16 for the bias sums, next power of two
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmDY);
@@ -814,8 +824,12 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
       fence_barrier_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, BNW);
+    tmem_alloc(tmem_slot, kTmemCols);
     tmem_relinquish();
+  } else if (warp >= 2 && bias_cta) {
+    float* ones = reinterpret_cast<float*>(smem + S::kOnesOff);
+    for (int i = threadIdx.x - 64; i < 512; i += 128) ones[i] = 1.f;
+    fence_proxy_async();   // generic-proxy writes become visible to the tensor core's reads of shared memory
   }
   tc_fence_before();
   __syncthreads();
@@ -866,6 +880,9 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
             // advancing K by 8 pixel rows == 8 * 128 B == one swizzle atom
             mma_tf32_ss(tmem_base, make_smem_desc(a_addr + k * p.k_step_bytes, p.desc_hi_a),
                         make_smem_desc(b_addr + k * p.k_step_bytes, p.desc_hi_b), idesc, (kb | k) != 0);
+            if (bias_cta)
+              mma_tf32_ss(tmem_base + BNW, make_smem_desc(a_addr + k * p.k_step_bytes, p.desc_hi_a),
+                          make_smem_desc(smem_u32(smem + S::kOnesOff), p.desc_hi_b), p.idesc_bias, (kb | k) != 0);
           }
           mma_commit(&empty_bar[stage]);
           if (++stage == STAGES) {
@@ -881,6 +898,12 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
       const int oc = oc0 + r;
+      if (bias_cta) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + BNW, v);   // column 0 of the 16 (identical) sums
+        tmem_ld_wait();
+        if (oc < p.Cout) atomicAdd(p.db + oc, __uint_as_float(v[0]));
+      }
 #pragma unroll 1
       for (int cc = 0; cc < BNW; cc += 32) {
         uint32_t v[32];
@@ -917,7 +940,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constan
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, BNW);
+    tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -1156,7 +1179,9 @@ DCNN_API int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w
 DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
                           long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h,
                           int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w,
-                          const float* bias, int accumulate, float* partials, cudaStream_t stream) {
+                          const float* bias, int accumulate, int relu, float* partials, cudaStream_t stream) {
+  DCNN_REQUIRE(!(relu && (accumulate || partials != nullptr)),
+               "dcnn_conv_tc: the ReLU epilogue does not combine with accumulation or BatchNorm statistics");
   DCNN_REQUIRE(Cin % 4 == 0 && Ktot % 4 == 0, "dcnn_conv_tc: Cin (%d) and Ktot (%d) must be multiples of 4", Cin, Ktot);
   DCNN_REQUIRE(Cout % 4 == 0, "dcnn_conv_tc: Cout (%d) must be a multiple of 4 (TMA store rows are 16-byte aligned)", Cout);
   DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_conv_tc: bad tap count %d", num_taps);
@@ -1170,7 +1195,7 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   p.m_tiles = p.tiles_n * p.tiles_h * p.tiles_w;
   p.in_mul_h = in_mul_h; p.in_mul_w = in_mul_w;
   p.Cin = Cin; p.Cout = Cout;
-  p.num_taps = num_taps; p.accumulate = accumulate;
+  p.num_taps = num_taps; p.accumulate = accumulate; p.relu = relu;
   p.out_sn = out_sn; p.out_sh = out_sh; p.out_sw = out_sw;
   p.out = out; p.bias = bias; p.partials = partials;
   for (int t = 0; t < num_taps; ++t) {
@@ -1273,13 +1298,18 @@ DCNN_API int dcnn_wgrad_tc_splits(int N, int OH, int OW, int Cout, int Cin, int 
 // dW[oc][tap_w*Cin + c] += sum_{n,oh,ow} dY[n,oh,ow,oc] * X[n, oh*mul_h + tap_dh, ow*mul_w + tap_dw, c]
 // dy: NHWC [N][OH][OW][Cout]; x: NHWC [N][H][W][Cin] (Cin % 4 == 0, Cout % 4 == 0; channel counts that are not
 // multiples of 32 are padded with zeros by the TMA unit, the write-back is guarded).
+// db != NULL: the bias gradient db[oc] += sum over pixels of dY[pixel, oc] is computed by the same launch (one extra
+// N = 16 MMA per k-step in one CTA per oc tile), replacing the separate column-sum pass.
 // scratch == NULL: split-K partial sums are added with red.global.add (fast; the order of the additions, and so the last
 // bits of dW, vary from run to run).  scratch != NULL (dcnn_wgrad_tc_splits * Cout * Ktot floats): every split writes
 // its own slab and a second kernel sums the slabs in index order -- bit-reproducible gradients.
 DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin,
                            float* dw, int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh,
-                           const int* tap_dw, const int* tap_w, float* scratch, cudaStream_t stream) {
+                           const int* tap_dw, const int* tap_w, float* scratch, float* db, cudaStream_t stream) {
   DCNN_REQUIRE(Cin % 4 == 0, "dcnn_wgrad_tc: Cin (%d) must be a multiple of 4", Cin);
+  DCNN_REQUIRE(!(db != nullptr && scratch != nullptr),
+               "dcnn_wgrad_tc: the fused bias gradient adds split sums in arrival order; use dcnn_colsum_accum in the "
+               "deterministic mode");
   DCNN_REQUIRE(Cout % 4 == 0, "dcnn_wgrad_tc: Cout (%d) must be a multiple of 4", Cout);
   DCNN_REQUIRE(num_taps >= 1 && num_taps <= kMaxTaps, "dcnn_wgrad_tc: bad tap count %d", num_taps);
   WgradTcParams p;
@@ -1291,6 +1321,7 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   p.Cin = Cin; p.Cout = Cout; p.Ktot = Ktot; p.num_taps = num_taps;
   p.dw = dw;
   p.scratch = scratch;
+  p.db = db;
   for (int t = 0; t < num_taps; ++t) {
     p.tap_dh[t] = (int16_t)tap_dh[t]; p.tap_dw[t] = (int16_t)tap_dw[t]; p.tap_w[t] = (int16_t)tap_w[t];
   }
@@ -1309,6 +1340,7 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
     p.desc_hi_a = make_smem_desc_hi(lbo, sbo, layout);
     p.desc_hi_b = make_smem_desc_hi(lbo, sbo, layout);
     p.idesc = make_idesc_tf32(128, bnw, a_mn, b_mn);
+    p.idesc_bias = make_idesc_tf32(128, 16, a_mn, b_mn);
     p.k_step_bytes = kstep;
   }
   CUtensorMap tmDY, tmX;

@@ -5,6 +5,7 @@ forward/backward), but ``Sequential`` and ``ResidualBlock`` execute *units*.  A 
 one layer or a fused group:
 
   ConvBNActUnit = Conv2D -> BatchNorm -> [ReLU]
+  GemmReluUnit  = Conv2D | Dense -> ReLU              (ReLU in the GEMM epilogue)
 
 which runs as  conv (BN partial statistics produced by the conv epilogue)  ->  finalize  ->
 one apply pass (scale/shift [+residual] [+ReLU]).  The reference runs the same chain as
@@ -17,7 +18,7 @@ from __future__ import annotations
 from typing import List, Optional
 
 from .. import ops
-from .layers import ActivationLayer, BatchNormLayer, Conv2DLayer, Layer
+from .layers import ActivationLayer, BatchNormLayer, Conv2DLayer, DenseLayer, Layer
 
 
 class SingleUnit:
@@ -77,6 +78,39 @@ class ConvBNActUnit:
         return dx, masked
 
 
+class GemmReluUnit:
+    """Conv2D / Dense -> ReLU without a BatchNorm in between: the ReLU runs in the GEMM epilogue (SURVEY K10 / K22:
+    "epilogue bias(+ReLU)"), so the pre-activation tensor is never written.  The activation layer caches the OUTPUT
+    instead of its input -- for ReLU the mask (out > 0) is the same -- and backward is the two layers' own."""
+
+    def __init__(self, gemm: Layer, act: ActivationLayer):
+        self.gemm, self.act = gemm, act
+        self.layers = [gemm, act]
+
+    @property
+    def name(self):
+        return self.gemm.name + "+" + self.act.name
+
+    def can_fuse_residual(self):
+        return False
+
+    def forward(self, x, mb, residual=None, relu=False):
+        assert residual is None and not relu
+        y = self.gemm.forward(x, mb, relu=True)
+        if self.act.training:
+            self.act._cache[mb] = y
+        return y
+
+    def backward(self, g, mb, want_masked=False, accumulate_into=None):
+        g = self.act.backward(g, mb)
+        if isinstance(self.gemm, Conv2DLayer) and accumulate_into is not None:
+            return self.gemm.backward(g, mb, out=accumulate_into, accumulate=True), None
+        dx = self.gemm.backward(g, mb)
+        if accumulate_into is not None and dx is not None:
+            dx = ops.add(dx, accumulate_into)
+        return dx, None
+
+
 def _is_relu(layer):
     return isinstance(layer, ActivationLayer) and layer.activation.name() == "relu"
 
@@ -93,6 +127,9 @@ def build_units(layers: List[Layer], fuse: bool = True):
             act = layers[i + 2] if i + 2 < n and _is_relu(layers[i + 2]) else None
             units.append(ConvBNActUnit(l, bn, act))
             i += 3 if act is not None else 2
+        elif fuse and isinstance(l, (Conv2DLayer, DenseLayer)) and i + 1 < n and _is_relu(layers[i + 1]):
+            units.append(GemmReluUnit(l, layers[i + 1]))
+            i += 2
         elif fuse and isinstance(l, BatchNormLayer):
             act = layers[i + 1] if i + 1 < n and _is_relu(layers[i + 1]) else None
             units.append(ConvBNActUnit(None, l, act))

@@ -235,11 +235,11 @@ class Conv2DLayer(Layer):
                 self.bias = self._to_dev(self.bias)
                 self.bias_grad = self._to_dev(self.bias_grad)
 
-    def forward(self, x, micro_batch_id=0):
-        y, _ = self.forward_with_stats(x, micro_batch_id, want_stats=False)
+    def forward(self, x, micro_batch_id=0, relu=False):
+        y, _ = self.forward_with_stats(x, micro_batch_id, want_stats=False, relu=relu)
         return y
 
-    def forward_with_stats(self, x, micro_batch_id=0, want_stats=True):
+    def forward_with_stats(self, x, micro_batch_id=0, want_stats=True, relu=False):
         if not self._initialized:
             self.initialize()
         if x.device != self.weights.device:
@@ -249,16 +249,16 @@ class Conv2DLayer(Layer):
             raise ValueError(f"{self.name}: expected {self.in_channels} input channels, got {x.shape[1]}")
         if self.training:
             self._inputs[micro_batch_id] = x
-        return ops.conv2d_forward(x, self.weights, self.bias, self.stride, self.pad, want_stats)
+        return ops.conv2d_forward(x, self.weights, self.bias, self.stride, self.pad, want_stats, relu)
 
     def backward(self, grad, micro_batch_id=0, out=None, accumulate=False):
         x = self._inputs.get(micro_batch_id)
         if x is None:
             raise RuntimeError(f"{self.name}: no cached input for micro-batch {micro_batch_id}")
         grad = ops.to_activation_layout(grad)
-        ops.conv2d_backward_weight(grad, x, self.weight_grad, self.stride, self.pad)
-        if self.use_bias:
-            ops.bias_grad(grad, self.bias_grad)
+        # the bias gradient rides in the weight-gradient launch (K13: the reference calls cudnnConvolutionBackwardBias)
+        ops.conv2d_backward_weight(grad, x, self.weight_grad, self.stride, self.pad,
+                                   self.bias_grad if self.use_bias else None)
         if not self.need_input_grad:
             return None
         return ops.conv2d_backward_data(grad, self.weights, x.shape, self.stride, self.pad,
@@ -346,7 +346,7 @@ class DenseLayer(Layer):
                 self.bias = self.bias.to(self.device)
                 self.bias_grad = self.bias_grad.to(self.device)
 
-    def forward(self, x, micro_batch_id=0):
+    def forward(self, x, micro_batch_id=0, relu=False):
         if not self._initialized:
             self.initialize()
         if x.device != self.weights.device:
@@ -358,16 +358,14 @@ class DenseLayer(Layer):
         if self.training:
             self._inputs[micro_batch_id] = (x2, shape)
         y = ops.dense_forward(x2, self.weights.view(self.output_features, self.input_features),
-                              self.bias)
+                              self.bias, relu)
         return y.reshape(shape[0], self.output_features, 1, 1)
 
     def backward(self, grad, micro_batch_id=0):
         x2, shape = self._inputs[micro_batch_id]
         g2 = grad.reshape(shape[0], self.output_features)
         w2 = self.weights.view(self.output_features, self.input_features)
-        ops.dense_backward_weight(g2, x2, self.weight_grad.view_as(w2))
-        if self.use_bias:
-            ops.bias_grad(g2.reshape(shape[0], self.output_features, 1, 1), self.bias_grad)
+        ops.dense_backward_weight(g2, x2, self.weight_grad.view_as(w2), self.bias_grad if self.use_bias else None)
         if not self.need_input_grad:
             return None
         dx = ops.dense_backward_data(g2, w2)

@@ -34,12 +34,14 @@ def _native():
     return cpu_native if cpu_native.enabled() else None
 
 
-def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
+def conv2d_forward(x, w, bias, stride, pad, want_stats=False, relu=False):
     nat = _native()
     if nat is not None and x.dtype == torch.float32:
         y = nat.conv2d_forward(x, w, bias, stride, pad)
-        return y, (bn_stats(y) if want_stats else None)
-    y = F.conv2d(x, w, None if bias is None else bias.reshape(-1), stride=stride, padding=pad)
+    else:
+        y = F.conv2d(x, w, None if bias is None else bias.reshape(-1), stride=stride, padding=pad)
+    if relu:
+        y = torch.relu_(y)
     return y, (bn_stats(y) if want_stats else None)
 
 
@@ -58,8 +60,10 @@ def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False
     return dx
 
 
-def conv2d_backward_weight(dy, x, dw, stride, pad):
-    """dw += dL/dW  (beta=1 accumulation across microbatches, ref cudnn_conv2d_ops.cu:226)."""
+def conv2d_backward_weight(dy, x, dw, stride, pad, db=None):
+    """dw += dL/dW  (beta=1 accumulation across microbatches, ref cudnn_conv2d_ops.cu:226); db += bias gradient."""
+    if db is not None:
+        bias_grad(dy, db)
     nat = _native()
     if nat is not None and dy.dtype == torch.float32:
         return nat.conv2d_backward_weight(dy, x, dw, stride, pad)
@@ -72,14 +76,15 @@ def bias_grad(dy, db):
     db.add_(dy.sum(dim=(0, 2, 3)).view_as(db))
 
 
-def dense_forward(x2d, w2d, bias):
+def dense_forward(x2d, w2d, bias, relu=False):
     nat = _native()
     if nat is not None and x2d.dtype == torch.float32:
-        return nat.dense_forward(x2d, w2d, bias)
-    y = x2d @ w2d.t()
-    if bias is not None:
-        y = y + bias.view(1, -1)
-    return y
+        y = nat.dense_forward(x2d, w2d, bias)
+    else:
+        y = x2d @ w2d.t()
+        if bias is not None:
+            y = y + bias.view(1, -1)
+    return torch.relu_(y) if relu else y
 
 
 def dense_backward_data(dy2d, w2d):
@@ -89,7 +94,9 @@ def dense_backward_data(dy2d, w2d):
     return dy2d @ w2d
 
 
-def dense_backward_weight(dy2d, x2d, dw2d):
+def dense_backward_weight(dy2d, x2d, dw2d, db=None):
+    if db is not None:
+        db.add_(dy2d.sum(0).view_as(db))
     nat = _native()
     if nat is not None and dy2d.dtype == torch.float32:
         return nat.dense_backward_weight(dy2d, x2d, dw2d)

@@ -171,15 +171,17 @@ def _autotuned(key, cout, fn, tunable=True):
 
 
 def _conv_tc(x, N, H, W, Cin, w, Cout, Ktot, out, out_off, sn, sh, sw, OH, OW, mul_h, mul_w, taps, bias,
-             accumulate, partials):
+             accumulate, partials, relu=False):
     n, dh, dw, wi = taps
     check(lib().dcnn_conv_tc(_p(x), I(N), I(H), I(W), I(Cin), _p(w), I(Cout), I(Ktot),
                              P(out.data_ptr() + 4 * out_off), LL(sn), LL(sh), LL(sw), I(OH), I(OW), I(mul_h),
-                             I(mul_w), I(n), dh, dw, wi, _p(bias), I(1 if accumulate else 0), _p(partials),
-                             _stream()), "dcnn_conv_tc")
+                             I(mul_w), I(n), dh, dw, wi, _p(bias), I(1 if accumulate else 0), I(1 if relu else 0),
+                             _p(partials), _stream()), "dcnn_conv_tc")
 
 
-def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
+def conv2d_forward(x, w, bias, stride, pad, want_stats=False, relu=False):
+    """``relu``: max(., 0) in the epilogue of the tensor-core kernels (Conv -> ReLU without BatchNorm)."""
+    assert not (relu and want_stats)
     x = as_nhwc(x)
     N, Cin, H, W = x.shape
     Cout, _, R, S = w.shape
@@ -191,7 +193,7 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
     kp = _stem_kp(Cin, R, S)
     if kp:
         return conv2d_forward(_pack_taps(x, R, S, stride, pad, OH, OW, kp), _packed_weights(w, kp), bias, (1, 1),
-                              (0, 0), want_stats)
+                              (0, 0), want_stats, relu)
     y = _empty_nhwc(N, Cout, OH, OW, x.device)
     # tensor cores for every channel count that keeps rows 16-byte aligned: the TMA unit pads the reduction dimension
     # to a multiple of 32 with zeros (C = 1 / 3 stems take the packed-tap route above; anything else is CUDA cores)
@@ -210,11 +212,13 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False):
                 partials = torch.empty(tiles * (2 * Cout + 1), device=x.device, dtype=torch.float32)
                 stats = CudaStats(partials, tiles, Cout, N * OH * OW)
             _conv_tc(x, N, H, W, Cin, w, Cout, R * S * Cin, y, 0, OH * OW * Cout, OW * Cout, Cout, OH, OW, sh_, sw_,
-                     taps, bias, False, partials)
+                     taps, bias, False, partials, relu)
             return y, stats
         return _autotuned(("f", N, H, W, Cin, Cout, R, S, sh_, sw_), Cout, run)
     check(lib().dcnn_conv_fprop_simt(_p(x), _p(w), _p(bias), _p(y), I(N), I(H), I(W), I(Cin), I(Cout), I(R), I(S),
                                      I(sh_), I(sw_), I(ph), I(pw), _stream()), "dcnn_conv_fprop_simt")
+    if relu:
+        y = activation_forward(y, "relu", 0.0)
     return y, (bn_stats(y) if want_stats else None)
 
 
@@ -343,7 +347,9 @@ def conv2d_backward_data(dy, w, x_shape, stride, pad, out=None, accumulate=False
     return dx
 
 
-def conv2d_backward_weight(dy, x, dw, stride, pad):
+def conv2d_backward_weight(dy, x, dw, stride, pad, db=None):
+    """dw += dL/dW; with ``db`` also db += column sums of dy -- inside the same launch on the tensor-core path (one extra
+    N = 16 MMA against a tile of ones), by the column-sum kernel otherwise."""
     dy = as_nhwc(dy)
     x = as_nhwc(x)
     N, Cin, H, W = x.shape
@@ -357,7 +363,7 @@ def conv2d_backward_weight(dy, x, dw, stride, pad):
         # the packed activations are rebuilt here rather than kept from the forward pass (134 MB for the ResNet stem at
         # batch 256 against a 30 us kernel)
         dwp = torch.zeros(K, kp, 1, 1, device=dw.device, dtype=torch.float32).contiguous(memory_format=CL)
-        conv2d_backward_weight(dy, _pack_taps(x, R, S, stride, pad, OH, OW, kp), dwp, (1, 1), (0, 0))
+        conv2d_backward_weight(dy, _pack_taps(x, R, S, stride, pad, OH, OW, kp), dwp, (1, 1), (0, 0), db)
         dw.permute(0, 2, 3, 1).reshape(K, R * S * Cin).add_(dwp.reshape(K, kp)[:, :R * S * Cin])
         return
     use_tc = tc_enabled() and Cin % 4 == 0 and K % 4 == 0 and R * S <= 49 and \
@@ -369,10 +375,15 @@ def conv2d_backward_weight(dy, x, dw, stride, pad):
             [r * S + s for r in range(R) for s in range(S)]))
         n, dh, dw_, wi = taps
         scratch = _wgrad_scratch(N, OH, OW, K, Cin, sh_, sw_, n, R * S * Cin, dy.device)
+        fused_db = db if scratch is None else None
         check(lib().dcnn_wgrad_tc(_p(dy), I(N), I(OH), I(OW), I(K), _p(x), I(H), I(W), I(Cin), _p(dw),
-                                  I(R * S * Cin), I(sh_), I(sw_), I(n), dh, dw_, wi, _p(scratch), _stream()),
-              "dcnn_wgrad_tc")
+                                  I(R * S * Cin), I(sh_), I(sw_), I(n), dh, dw_, wi, _p(scratch), _p(fused_db),
+                                  _stream()), "dcnn_wgrad_tc")
+        if db is not None and fused_db is None:
+            bias_grad(dy, db)
         return
+    if db is not None:
+        bias_grad(dy, db)
     check(lib().dcnn_conv_wgrad_simt(_p(dy), _p(x), _p(dw), I(N), I(H), I(W), I(Cin), I(K), I(R), I(S), I(sh_),
                                      I(sw_), I(ph), I(pw), _stream()), "conv_wgrad_simt")
 
@@ -396,16 +407,20 @@ def _one_tap():
     return _ONE_TAP
 
 
-def dense_forward(x2d, w2d, bias):
+def dense_forward(x2d, w2d, bias, relu=False):
     x2d = x2d.contiguous()
     B, Fin = x2d.shape
     Fout = w2d.shape[0]
     y = torch.empty((B, Fout), device=x2d.device, dtype=torch.float32)
     if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0:
-        _conv_tc(x2d, B, 1, 1, Fin, w2d, Fout, Fin, y, 0, Fout, Fout, Fout, 1, 1, 1, 1, _one_tap(), bias, False, None)
+        _conv_tc(x2d, B, 1, 1, Fin, w2d, Fout, Fin, y, 0, Fout, Fout, Fout, 1, 1, 1, 1, _one_tap(), bias, False, None,
+                 relu)
+        return y
     else:
         check(lib().dcnn_conv_fprop_simt(_p(x2d), _p(w2d), _p(bias), _p(y), I(B), I(1), I(1), I(Fin), I(Fout), I(1),
                                          I(1), I(1), I(1), I(0), I(0), _stream()), "dense fprop simt")
+    if relu:
+        y = activation_forward(y.view(B, Fout, 1, 1), "relu", 0.0).view(B, Fout)
     return y
 
 
@@ -423,7 +438,7 @@ def dense_backward_data(dy2d, w2d):
     return dx
 
 
-def dense_backward_weight(dy2d, x2d, dw2d):
+def dense_backward_weight(dy2d, x2d, dw2d, db=None):
     dy2d = dy2d.contiguous()
     x2d = x2d.contiguous()
     B, Fout = dy2d.shape
@@ -431,9 +446,14 @@ def dense_backward_weight(dy2d, x2d, dw2d):
     if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0:
         n, dh, dw_, wi = _one_tap()
         scratch = _wgrad_scratch(B, 1, 1, Fout, Fin, 1, 1, 1, Fin, dy2d.device)
+        fused_db = db if scratch is None else None
         check(lib().dcnn_wgrad_tc(_p(dy2d), I(B), I(1), I(1), I(Fout), _p(x2d), I(1), I(1), I(Fin), _p(dw2d), I(Fin),
-                                  I(1), I(1), I(n), dh, dw_, wi, _p(scratch), _stream()), "dense wgrad tc")
+                                  I(1), I(1), I(n), dh, dw_, wi, _p(scratch), _p(fused_db), _stream()), "dense wgrad tc")
+        if db is not None and fused_db is None:
+            bias_grad(dy2d.view(B, Fout, 1, 1), db)
     else:
+        if db is not None:
+            bias_grad(dy2d.view(B, Fout, 1, 1), db)
         check(lib().dcnn_conv_wgrad_simt(_p(dy2d), _p(x2d), _p(dw2d), I(B), I(1), I(1), I(Fin), I(Fout), I(1), I(1),
                                          I(1), I(1), I(0), I(0), _stream()), "dense wgrad simt")
 

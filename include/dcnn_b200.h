@@ -28,13 +28,13 @@ int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cou
 int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
                  long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h, int in_mul_w,
                  int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w, const float* bias,
-                 int accumulate, float* partials, cudaStream_t stream);
+                 int accumulate, int relu, float* partials, cudaStream_t stream);
 /* scratch == NULL: split-K sums by red.global.add (order varies run to run); scratch = dcnn_wgrad_tc_splits * Cout * Ktot
  * floats: per-split slabs summed in index order by a second kernel (bit-reproducible). */
 int dcnn_wgrad_tc_splits(int N, int OH, int OW, int Cout, int Cin, int in_mul_h, int in_mul_w, int num_taps);
 int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, const float* x, int H, int W, int Cin, float* dw,
                   int Ktot, int in_mul_h, int in_mul_w, int num_taps, const int* tap_dh, const int* tap_dw,
-                  const int* tap_w, float* scratch, cudaStream_t stream);
+                  const int* tap_w, float* scratch, float* db, cudaStream_t stream);   /* db: fused bias gradient or NULL */
 /* measurement tool: persistent CTAs stream TMA operand tiles with no MMA (per-SM / chip-wide ingest rate, effect of a
  * shared B tile); see scripts/tma_ingest_probe.py */
 int dcnn_tma_stream_probe(const float* A, long long a_total_rows, long long a_cols, int a_rows, const float* B,

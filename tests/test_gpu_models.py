@@ -4,7 +4,8 @@ import torch
 
 import dcnn_b200 as dc
 from dcnn_b200 import nn as dnn
-from dcnn_b200.models import create_mnist_trainer, create_resnet9_cifar10, create_resnet50_tiny_imagenet
+from dcnn_b200.models import (create_cifar10_trainer_v1, create_mnist_trainer, create_resnet9_cifar10,
+                               create_resnet50_tiny_imagenet)
 
 pytestmark = pytest.mark.gpu
 
@@ -42,6 +43,7 @@ def _grad_err(gpu_grads, cpu_grads):
 @pytest.mark.parametrize("exact", [True, False], ids=["fp32exact", "tf32"])
 @pytest.mark.parametrize("factory,shape,tol", [
     (create_mnist_trainer, (8, 1, 28, 28), 2e-4),
+    (create_cifar10_trainer_v1, (8, 3, 32, 32), 2e-4),      # Conv -> ReLU without BatchNorm: ReLU in the GEMM epilogue
     (create_resnet9_cifar10, (8, 3, 32, 32), 2e-3),
 ])
 def test_model_forward_backward_matches_cpu(factory, shape, tol, exact, monkeypatch):

@@ -196,6 +196,44 @@ def test_conv_wgrad_deterministic_mode(case, monkeypatch):
         assert torch.equal(dw, runs[0][0]) and torch.equal(db, runs[0][1])
 
 
+@pytest.mark.parametrize("case", [(4, 64, 16, 16, 128, 3, 1, 1, True), (2, 16, 9, 9, 48, 5, 1, 0, True),
+                                  (2, 3, 32, 32, 64, 3, 1, 1, False), (3, 6, 8, 8, 10, 3, 1, 1, True)],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_conv_relu_epilogue_and_fused_bias_gradient(case):
+    """Conv -> ReLU with the ReLU in the GEMM epilogue, and the bias gradient computed inside the weight-gradient launch
+    (tensor-core paths, packed stem and the CUDA-core fallback) against the CPU oracle."""
+    N, C, H, W, OC, k, s, p, bias = case
+    x = torch.randn(N, C, H, W)
+    w = torch.randn(OC, C, k, k) / (C * k * k) ** 0.5
+    b = torch.randn(OC, 1, 1, 1) if bias else None
+    y_ref, _ = ref.conv2d_forward(x, w, b, (s, s), (p, p), False)
+    y, _ = ops.conv2d_forward(cl(x), cl(w), None if b is None else b.to(DEV), (s, s), (p, p), False, True)
+    check_close(y, torch.relu(y_ref), 4e-3, "conv + relu epilogue")
+    assert float(y.min()) >= 0.0
+    dy = torch.randn_like(y_ref)
+    dw_ref, db_ref = torch.zeros(OC, C, k, k), torch.zeros(OC, 1, 1, 1)
+    ref.conv2d_backward_weight(dy, x, dw_ref, (s, s), (p, p), db_ref)
+    dw, db = cl(torch.zeros(OC, C, k, k)), torch.zeros(OC, 1, 1, 1, device=DEV)
+    ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p), db)
+    ops.conv2d_backward_weight(cl(dy), cl(x), dw, (s, s), (p, p), db)       # both accumulate
+    check_close(dw, 2 * dw_ref, 4e-3, "wgrad with fused bias gradient")
+    check_close(db, 2 * db_ref, 4e-3, "fused bias gradient")
+
+
+@pytest.mark.parametrize("B,Fin,Fout", [(256, 2048, 200), (33, 96, 48), (64, 512, 10)])
+def test_dense_relu_epilogue_and_fused_bias_gradient(B, Fin, Fout):
+    x, w, b = torch.randn(B, Fin), torch.randn(Fout, Fin) / Fin ** 0.5, torch.randn(Fout, 1, 1, 1)
+    y = ops.dense_forward(x.to(DEV), w.to(DEV), b.to(DEV), True)
+    check_close(y, torch.relu(ref.dense_forward(x, w, b)), 4e-3, "dense + relu epilogue")
+    dy = torch.randn(B, Fout)
+    dw_ref, db_ref = torch.zeros(Fout, Fin), torch.zeros(Fout, 1, 1, 1)
+    ref.dense_backward_weight(dy, x, dw_ref, db_ref)
+    dw, db = torch.zeros(Fout, Fin, device=DEV), torch.zeros(Fout, 1, 1, 1, device=DEV)
+    ops.dense_backward_weight(dy.to(DEV), x.to(DEV), dw, db)
+    check_close(dw, dw_ref, 4e-3, "dense wgrad")
+    check_close(db, db_ref, 4e-3, "dense fused bias gradient")
+
+
 def test_conv_fp32_exact_mode(monkeypatch):
     monkeypatch.setenv("DCNN_DISABLE_TC", "1")
     x, w = torch.randn(2, 64, 8, 8), torch.randn(32, 64, 3, 3) / 24
