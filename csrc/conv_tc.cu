@@ -1276,12 +1276,24 @@ static void wgrad_geometry(int N, int OH, int OW, int Cout, int Cin, int in_mul_
   p->c_tiles = ceil_div(Cin, bnw);
   const int pix_tiles = p->tiles_n * p->tiles_h * p->tiles_w;
   const int base = num_taps * p->oc_tiles * p->c_tiles;
-  int splits = ceil_div(2 * num_sms(), base);
-  if (splits > pix_tiles) splits = pix_tiles;
-  if (splits < 1) splits = 1;
-  // make every split non-empty
-  const int per = ceil_div(pix_tiles, splits);
-  p->splits = ceil_div(pix_tiles, per);
+  // Split-K factor.  One CTA fits per SM (its pipeline stages fill shared memory), so a launch runs in
+  // ceil(CTAs / SMs) waves and each wave costs the k-iterations of one CTA plus its prologue and red.add epilogue
+  // (about four k-iterations).  Pick the factor that minimises waves x (k-iterations + 4); fewer splits on a tie (less
+  // atomic traffic).  (Round 1 aimed for two CTAs per SM regardless: 5 splits x 64 CTAs = 2.2 waves for the 1x1
+  // 2048->512 layer at 4x4 where 2 splits run in one.)
+  const long long sms = num_sms();
+  int best = 1;
+  long long best_cost = -1;
+  const int max_splits = pix_tiles < 512 ? pix_tiles : 512;
+  for (int sp = 1; sp <= max_splits; ++sp) {
+    const int per = ceil_div(pix_tiles, sp);
+    const int eff = ceil_div(pix_tiles, per);   // every split non-empty
+    if (eff != sp) continue;
+    const long long waves = ((long long)base * eff + sms - 1) / sms;
+    const long long cost = waves * (per + 4);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = eff; }
+  }
+  p->splits = best;
   *bnw_out = bnw;
 }
 

@@ -208,7 +208,9 @@ def test_conv_relu_epilogue_and_fused_bias_gradient(case):
     b = torch.randn(OC, 1, 1, 1) if bias else None
     y_ref, _ = ref.conv2d_forward(x, w, b, (s, s), (p, p), False)
     y, _ = ops.conv2d_forward(cl(x), cl(w), None if b is None else b.to(DEV), (s, s), (p, p), False, True)
-    check_close(y, torch.relu(y_ref), 4e-3, "conv + relu epilogue")
+    # after the ReLU a channel's largest value can be several times smaller than before it, so the per-channel bound
+    # (relative to that maximum) needs more room for the same TF32 noise
+    check_close(y, torch.relu(y_ref), 8e-3, "conv + relu epilogue")
     assert float(y.min()) >= 0.0
     dy = torch.randn_like(y_ref)
     dw_ref, db_ref = torch.zeros(OC, C, k, k), torch.zeros(OC, 1, 1, 1)
@@ -224,7 +226,7 @@ def test_conv_relu_epilogue_and_fused_bias_gradient(case):
 def test_dense_relu_epilogue_and_fused_bias_gradient(B, Fin, Fout):
     x, w, b = torch.randn(B, Fin), torch.randn(Fout, Fin) / Fin ** 0.5, torch.randn(Fout, 1, 1, 1)
     y = ops.dense_forward(x.to(DEV), w.to(DEV), b.to(DEV), True)
-    check_close(y, torch.relu(ref.dense_forward(x, w, b)), 4e-3, "dense + relu epilogue")
+    check_close(y, torch.relu(ref.dense_forward(x, w, b)), 8e-3, "dense + relu epilogue")
     dy = torch.randn(B, Fout)
     dw_ref, db_ref = torch.zeros(Fout, Fin), torch.zeros(Fout, 1, 1, 1)
     ref.dense_backward_weight(dy, x, dw_ref, db_ref)
