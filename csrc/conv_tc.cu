@@ -550,9 +550,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
 // per k-step for a 128x256 output slice -- half the TMA traffic per MAC of conv_tc2 and 2/3 of conv_tc3's -- with the
 // epilogue of tile i still overlapping the mainloop of tile i+1.
 //
-// Protocol (after the DeepGEMM / CUTLASS 2-SM pattern): full[s] lives in the leader, count 2 = the leader producer's
-// arrive.expect_tx(bytes of both CTAs) + the peer producer's remote arrive; both producers' TMA loads count their
-// bytes on it.  The leader's MMA thread frees stage s in BOTH CTAs and signals the accumulator to BOTH epilogues
+// Protocol (after the DeepGEMM / CUTLASS 2-SM pattern): full[s] lives in the leader, count 1 = the leader producer's
+// arrive.expect_tx(bytes of both CTAs); both producers' TMA loads count their bytes on it.  The leader's MMA thread frees stage s in BOTH CTAs and signals the accumulator to BOTH epilogues
 // with multicast commits.  The epilogue warps of both CTAs (2 x 4) arrive on the leader's tmem_empty[a].
 // Validated on hardware (tests/test_gpu_ops.py::test_conv_tc5_cta_pairs); the autotuner (ops/cuda.py) picks it per
 // shape where it wins, DCNN_CONV_2CTA=1 forces it wherever it applies.
@@ -611,7 +610,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < STAGES; ++s) {
-        mbar_init(&full_bar[s], 2);    // (used in the leader) leader producer + peer producer
+        mbar_init(&full_bar[s], 1);    // (used in the leader) the leader producer's arrive.expect_tx for both CTAs' bytes
         mbar_init(&empty_bar[s], 1);   // one multicast commit
       }
       for (int a = 0; a < 2; ++a) {
@@ -650,8 +649,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           tma_load_4d_pair(sA, &tmA, leader_full, c * kBK, iw0 + p.tap_dw[t], ih0 + p.tap_dh[t], n0);
           tma_load_2d_pair(sA + S::kABytes, &tmB, leader_full, p.tap_w[t] * p.Cin + c * kBK,
                            n_tile * BN + (int)cta_rank * (BN / 2));
+          // Only the leader arrives (expecting the bytes of BOTH CTAs); the peer's loads just count their bytes on the
+          // leader's barrier.  A transaction count that runs ahead of the expect_tx is fine -- the phase cannot
+          // complete before the leader's arrival -- and the peer cannot run a whole phase ahead because it waits for its
+          // own empty barrier, which the leader's MMA commit releases.  (The first version had the peer arrive remotely
+          // with release semantics: a MEMBAR + ERRBAR in the peer's producer loop on every k-block, which starved its TMA
+          // stream -- tensor pipe 28 % against conv_tc3's 62 % on the same layer, profiles/05.)
           if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * S::kStageBytes);
-          else mbar_arrive_cluster(leader_full);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -1086,50 +1090,64 @@ static int launch_conv5(const CUtensorMap& tmA, const CUtensorMap& tmB, const CU
   return 0;
 }
 
-// conv_tc5 (CTA pairs, 256 x 256 tiles): opt-in with DCNN_CONV_2CTA=1, for Cout >= 256 (Cout % 4 == 0) when there is at
-// least one pair tile per CTA pair.  Uses conv_tc2's 128-pixel boxes, so the statistics-tile count is unchanged.
-// Per-thread override of the variant choice, used by the autotuner (ops/cuda.py): 0 = the rules below, 2 = conv_tc2,
-// 3 = conv_tc3 wherever it is structurally possible, 5 = conv_tc5 wherever it is structurally possible.
+// ---------------------------------------------------------------------------------------------------------
+// Which kernel runs a problem.  All three are persistent (one CTA, or CTA pair, per SM, static round-robin) and bound by
+// the L2 -> SM operand feed once K is deep, so a launch costs about  waves x k-blocks x (time of one k-block), with the
+// k-block times measured on B200 (profiles/05 section 3 and section 5):
+//     conv_tc2  128 px x 128 ch per CTA   256 operand rows   0.39 us     (N = 64: 192 rows)
+//     conv_tc3  256 px x 128 ch per CTA   384 rows           0.53 us     (N = 64: 320 rows)
+//     conv_tc5  128 px x 256 ch per CTA   256 rows           0.45 us     (a CTA pair shares one 256 x 256 tile)
+// conv_tc5 does twice conv_tc2's work per k-block for 1.15x its time, but its cross-CTA handshakes and its two-pass
+// epilogue only pay off when the mainloop is long: it needs Cout >= 256 and at least 16 k-blocks.
+// Per-thread override, used by the autotuner (ops/cuda.py) and the tests: 0 = this rule, 2 / 3 / 5 = that kernel wherever
+// it is structurally possible.  DCNN_CONV_2CTA=1 forces conv_tc5 wherever it applies, DCNN_CONV_2CTA=0 and DCNN_CONV_V3=0
+// take the respective kernel out of the rule.
 static thread_local int g_conv_variant = 0;
 
-static bool conv_2cta_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout) {
-  if (g_conv_variant != 0) return g_conv_variant == 5 && (Cout & 3) == 0 && Cout >= 256;
-  const char* e = getenv("DCNN_CONV_2CTA");
-  if (e == nullptr || atoi(e) == 0 || (Cout & 3) != 0 || Cout < 256) return false;
-  int bn = 1, bh = 1, bw = 1;
-  choose_box(N, OH, OW, kBM, mul_h, mul_w, &bn, &bh, &bw);
-  const long long m_tiles = (long long)ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
-  return ((m_tiles + 1) / 2) * ceil_div(Cout, 256) >= num_sms() / 2;
-}
-
-// conv_tc3 is used unless it is switched off (DCNN_CONV_V3=0), when the vectorised epilogue applies (Cout % 4 == 0) and the
-// loop space has at least one 256-pixel tile per SM; smaller problems keep the 128-pixel tiles of conv_tc2.
 static bool conv_v3_enabled() {
   static const bool on = !(getenv("DCNN_CONV_V3") != nullptr && atoi(getenv("DCNN_CONV_V3")) == 0);
   return on;
 }
-static bool conv_v3_applies(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int* bn, int* bh, int* bw) {
-  if (g_conv_variant != 0 && g_conv_variant != 3) return false;
-  if ((g_conv_variant == 0 && !conv_v3_enabled()) || (Cout & 3) != 0) return false;
-  *bn = *bh = *bw = 1;
-  choose_box(N, OH, OW, 2 * kBM, mul_h, mul_w, bn, bh, bw);
-  if (g_conv_variant == 3) return true;
-  // Both kernels are persistent (one CTA per SM, static round-robin) and operand-feed bound, so a launch costs about
-  // ceil(tiles / SMs) waves x (A rows + B rows) per k-step.  256-pixel tiles halve the tile count at 1.5x (N = 128) or
-  // 1.67x (N = 64) the cost per tile: they win unless the smaller tiles fit in the same number of waves.  This
-  // reproduces the choices the autotuner measured on every ResNet-50 layer (profiles/05), e.g. 3x3 256->256 @8x8:
-  // 128 big tiles in one wave (45.7 us) against 256 small ones in two (56.3 us); 3x3 512->512 @4x4: 64 big tiles leave
-  // 84 SMs idle (74.8 us) while 128 small ones use one wave (57.0 us).
-  const int bnt = Cout <= 64 ? 64 : 128;
-  const long long n_tiles = Cout <= 64 ? 1 : ceil_div(Cout, 128);
-  const long long m3 = (long long)ceil_div(OW, *bw) * ceil_div(OH, *bh) * ceil_div(N, *bn);
+static int conv_2cta_mode() {   // -1: not set, 0: off, 1: forced
+  static const int m = getenv("DCNN_CONV_2CTA") == nullptr ? -1 : (atoi(getenv("DCNN_CONV_2CTA")) != 0 ? 1 : 0);
+  return m;
+}
+
+struct ConvChoice {
+  int variant;           // 2, 3 or 5
+  int bn3, bh3, bw3;     // conv_tc3's 256-pixel load box (valid when variant == 3)
+};
+
+static ConvChoice choose_conv_variant(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int num_kb) {
+  ConvChoice c;
+  c.variant = 2;
+  c.bn3 = c.bh3 = c.bw3 = 1;
+  choose_box(N, OH, OW, 2 * kBM, mul_h, mul_w, &c.bn3, &c.bh3, &c.bw3);
+  const bool can5 = Cout >= 256;
+  if (g_conv_variant == 2) return c;
+  if (g_conv_variant == 3) { c.variant = 3; return c; }
+  if (g_conv_variant == 5) { c.variant = can5 ? 5 : 2; return c; }
+  if (conv_2cta_mode() == 1 && can5) { c.variant = 5; return c; }
   int b2n = 1, b2h = 1, b2w = 1;
   choose_box(N, OH, OW, kBM, mul_h, mul_w, &b2n, &b2h, &b2w);
   const long long m2 = (long long)ceil_div(OW, b2w) * ceil_div(OH, b2h) * ceil_div(N, b2n);
+  const long long m3 = (long long)ceil_div(OW, c.bw3) * ceil_div(OH, c.bh3) * ceil_div(N, c.bn3);
   const long long sms = num_sms();
-  const long long cost3 = ((m3 * n_tiles + sms - 1) / sms) * (2 * kBM + bnt);
-  const long long cost2 = ((m2 * n_tiles + sms - 1) / sms) * (kBM + bnt);
-  return cost3 < cost2;
+  const bool narrow = Cout <= 64;
+  const long long n_tiles = narrow ? 1 : ceil_div(Cout, 128);
+  // k-block times in units of 0.01 us
+  const long long t2 = narrow ? 29 : 39, t3 = narrow ? 44 : 53, t5 = 45;
+  long long best = ((m2 * n_tiles + sms - 1) / sms) * t2;
+  if (conv_v3_enabled()) {
+    const long long cost3 = ((m3 * n_tiles + sms - 1) / sms) * t3;
+    if (cost3 < best) { best = cost3; c.variant = 3; }
+  }
+  if (can5 && num_kb >= 16 && conv_2cta_mode() != 0) {
+    const long long pairs = sms / 2;
+    const long long cost5 = ((((m2 + 1) / 2) * ceil_div(Cout, 256) + pairs - 1) / pairs) * t5;
+    if (cost5 < best) { best = cost5; c.variant = 5; }
+  }
+  return c;
 }
 
 template <int BNW, int STAGES>
@@ -1163,13 +1181,11 @@ DCNN_API int dcnn_conv_tc_set_variant(int variant) {
 }
 
 // Number of BatchNorm partial-statistics tiles dcnn_conv_tc will emit for this problem (the partials buffer holds
-// tiles*(2*Cout+1) floats).  Equals dcnn_conv_tc_m_tiles unless the 256-pixel kernel is selected, which emits two
-// 128-row statistics tiles per M tile.
-DCNN_API int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout) {
-  int bn, bh, bw;
-  if (conv_2cta_applies(N, OH, OW, mul_h, mul_w, Cout)) return dcnn_conv_tc_m_tiles(N, OH, OW, mul_h, mul_w);
-  if (conv_v3_applies(N, OH, OW, mul_h, mul_w, Cout, &bn, &bh, &bw))
-    return 2 * ceil_div(OW, bw) * ceil_div(OH, bh) * ceil_div(N, bn);
+// tiles*(2*Cout+1) floats); num_kb = taps * ceil(Cin / 32).  Equals dcnn_conv_tc_m_tiles unless the 256-pixel kernel is
+// selected, which emits two 128-row statistics tiles per M tile.
+DCNN_API int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int num_kb) {
+  const ConvChoice c = choose_conv_variant(N, OH, OW, mul_h, mul_w, Cout, num_kb);
+  if (c.variant == 3) return 2 * ceil_div(OW, c.bw3) * ceil_div(OH, c.bh3) * ceil_div(N, c.bn3);
   return dcnn_conv_tc_m_tiles(N, OH, OW, mul_h, mul_w);
 }
 
@@ -1207,7 +1223,8 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   CUtensorMap tmA, tmB;
   int rc = make_tmap_nhwc(&tmA, x, N, H, W, Cin, p.bn, p.bh, p.bw, in_mul_h, in_mul_w);
   if (rc) return rc;
-  if (conv_2cta_applies(N, OH, OW, in_mul_h, in_mul_w, Cout)) {
+  const ConvChoice choice = choose_conv_variant(N, OH, OW, in_mul_h, in_mul_w, Cout, num_taps * ceil_div(Cin, kBK));
+  if (choice.variant == 5) {
     CUtensorMap tmO5;
     rc = make_tmap_out(&tmO5, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);
     if (rc) return rc;
@@ -1216,36 +1233,34 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
     if (rc) return rc;
     return launch_conv5<4>(tmA, tmB, tmO5, p, stream);
   }
-  {
-    int bn3, bh3, bw3;
-    if (conv_v3_applies(N, OH, OW, in_mul_h, in_mul_w, Cout, &bn3, &bh3, &bw3)) {
-      ConvTc3Params q;
-      q.b = p;
-      q.b.bn = bn3; q.b.bh = bh3; q.b.bw = bw3;
-      q.b.tiles_n = ceil_div(N, bn3); q.b.tiles_h = ceil_div(OH, bh3); q.b.tiles_w = ceil_div(OW, bw3);
-      q.b.m_tiles = q.b.tiles_n * q.b.tiles_h * q.b.tiles_w;
-      // the second 128 rows of the box (row order n, h, w) start half-way along its slowest dimension of extent >= 2
-      q.obn = bn3; q.obh = bh3; q.obw = bw3;
-      q.hdn = q.hdh = q.hdw = 0;
-      if (bn3 >= 2) { q.obn = bn3 / 2; q.hdn = bn3 / 2; }
-      else if (bh3 >= 2) { q.obh = bh3 / 2; q.hdh = bh3 / 2; }
-      else { q.obw = bw3 / 2; q.hdw = bw3 / 2; }
-      CUtensorMap tmA3, tmO3;
-      rc = make_tmap_nhwc(&tmA3, x, N, H, W, Cin, bn3, bh3, bw3, in_mul_h, in_mul_w);
+  if (choice.variant == 3) {
+    const int bn3 = choice.bn3, bh3 = choice.bh3, bw3 = choice.bw3;
+    ConvTc3Params q;
+    q.b = p;
+    q.b.bn = bn3; q.b.bh = bh3; q.b.bw = bw3;
+    q.b.tiles_n = ceil_div(N, bn3); q.b.tiles_h = ceil_div(OH, bh3); q.b.tiles_w = ceil_div(OW, bw3);
+    q.b.m_tiles = q.b.tiles_n * q.b.tiles_h * q.b.tiles_w;
+    // the second 128 rows of the box (row order n, h, w) start half-way along its slowest dimension of extent >= 2
+    q.obn = bn3; q.obh = bh3; q.obw = bw3;
+    q.hdn = q.hdh = q.hdw = 0;
+    if (bn3 >= 2) { q.obn = bn3 / 2; q.hdn = bn3 / 2; }
+    else if (bh3 >= 2) { q.obh = bh3 / 2; q.hdh = bh3 / 2; }
+    else { q.obw = bw3 / 2; q.hdw = bw3 / 2; }
+    CUtensorMap tmA3, tmO3;
+    rc = make_tmap_nhwc(&tmA3, x, N, H, W, Cin, bn3, bh3, bw3, in_mul_h, in_mul_w);
+    if (rc) return rc;
+    rc = make_tmap_out(&tmO3, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, q.obn, q.obh, q.obw);
+    if (rc) return rc;
+    if (Cout <= 64) {
+      q.b.n_tiles = 1;
+      rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
       if (rc) return rc;
-      rc = make_tmap_out(&tmO3, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, q.obn, q.obh, q.obw);
-      if (rc) return rc;
-      if (Cout <= 64) {
-        q.b.n_tiles = 1;
-        rc = make_tmap_2d(&tmB, w, Cout, Ktot, 64);
-        if (rc) return rc;
-        return launch_conv3<64, 3>(tmA3, tmB, tmO3, q, stream);
-      }
-      q.b.n_tiles = ceil_div(Cout, 128);
-      rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
-      if (rc) return rc;
-      return launch_conv3<128, 3>(tmA3, tmB, tmO3, q, stream);
+      return launch_conv3<64, 3>(tmA3, tmB, tmO3, q, stream);
     }
+    q.b.n_tiles = ceil_div(Cout, 128);
+    rc = make_tmap_2d(&tmB, w, Cout, Ktot, 128);
+    if (rc) return rc;
+    return launch_conv3<128, 3>(tmA3, tmB, tmO3, q, stream);
   }
   CUtensorMap tmO;
   rc = make_tmap_out(&tmO, out, N, OH, OW, Cout, out_sn, out_sh, out_sw, p.bn, p.bh, p.bw);

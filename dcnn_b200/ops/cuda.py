@@ -208,7 +208,8 @@ def conv2d_forward(x, w, bias, stride, pad, want_stats=False, relu=False):
             stats = None
             partials = None
             if want_stats:      # the statistics-tile count depends on the kernel variant in force
-                tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_), I(Cout))
+                tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(OH), I(OW), I(sh_), I(sw_), I(Cout),
+                                                      I(R * S * ((Cin + 31) // 32)))
                 partials = torch.empty(tiles * (2 * Cout + 1), device=x.device, dtype=torch.float32)
                 stats = CudaStats(partials, tiles, Cout, N * OH * OW)
             _conv_tc(x, N, H, W, Cin, w, Cout, R * S * Cin, y, 0, OH * OW * Cout, OW * Cout, Cout, OH, OW, sh_, sw_,

@@ -24,7 +24,7 @@ int dcnn_conv_tc_m_tiles(int N, int OH, int OW, int mul_h, int mul_w);
 /* statistics tiles dcnn_conv_tc emits for this problem (== m_tiles unless the 256-pixel kernel is selected; DCNN_CONV_V3=0 disables it) */
 /* autotuner hook: force conv_tc2 (2), conv_tc3 (3) or conv_tc5 (5) for this thread's next calls; 0 = built-in rules */
 int dcnn_conv_tc_set_variant(int variant);
-int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout);
+int dcnn_conv_tc_stat_tiles(int N, int OH, int OW, int mul_h, int mul_w, int Cout, int num_kb);
 int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const float* w, int Cout, int Ktot, float* out,
                  long long out_sn, long long out_sh, long long out_sw, int OH, int OW, int in_mul_h, int in_mul_w,
                  int num_taps, const int* tap_dh, const int* tap_dw, const int* tap_w, const float* bias,

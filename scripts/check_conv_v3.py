@@ -60,7 +60,7 @@ cases = PAIR_CASES if "--pair" in sys.argv else [(64, 64, 32, 32, 128, 3, 1, 1, 
          (64, 128, 32, 32, 128, 3, 1, 1, False)]
 for (N, Ci, H, W, Co, k, s, p, bias) in cases:
     oh, ow = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
-    tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(oh), I(ow), I(s), I(s), I(Co))
+    tiles = lib().dcnn_conv_tc_stat_tiles(I(N), I(oh), I(ow), I(s), I(s), I(Co), I(k * k * ((Ci + 31) // 32)))
     base = lib().dcnn_conv_tc_m_tiles(I(N), I(oh), I(ow), I(s), I(s))
     tag = f"[{N}x{Ci}x{H}x{W} -> {Co} k{k} s{s}] stat tiles {tiles} (v2 would use {base})"
     print(tag, flush=True)
