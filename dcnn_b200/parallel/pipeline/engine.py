@@ -38,13 +38,23 @@ import os as _os
 _PIPE_DEBUG = _os.environ.get("DCNN_PIPE_DEBUG", "0") == "1"
 
 
-def build_schedule(kind: str, stage: int, num_stages: int, num_microbatches: int) -> List[Tuple[str, int]]:
+def build_schedule(kind: str, stage: int, num_stages: int, num_microbatches: int,
+                   warmup_factor: Optional[int] = None) -> List[Tuple[str, int]]:
+    """``sync``: all forwards, then all backwards (GPipe).  ``semi_async``: 1F1B -- ``warm`` forwards, then forward /
+    backward alternate, then the remaining backwards.  The textbook warm-up, S-1-stage forwards, leaves no slack between
+    neighbouring stages: in the steady state every activation / gradient hand-off (NCCL send + receive, 8-33 MB) lands on
+    the critical path (measured on 8 GPUs, pp4 x dp2: step 36.9 ms against 29.9 ms for the ideal 1F1B of the same busy
+    time).  ``warmup_factor`` = 2 (default, DCNN_PIPE_WARMUP_FACTOR) gives every stage two microbatches of lead over its
+    successor instead of one, so a transfer has a whole forward or backward of compute to hide behind; the price is
+    activation memory for up to 2(S-1)+1 microbatches on the first stage."""
     m = num_microbatches
     if kind == "sync":
         return [("F", i) for i in range(m)] + [("B", i) for i in range(m)]
     if kind != "semi_async":
         raise ValueError(f"unknown schedule '{kind}' (sync | semi_async)")
-    warm = min(num_stages - 1 - stage, m)
+    if warmup_factor is None:
+        warmup_factor = int(_os.environ.get("DCNN_PIPE_WARMUP_FACTOR", "2") or 2)
+    warm = min(max(1, warmup_factor) * (num_stages - 1 - stage), m)
     ops = [("F", i) for i in range(warm)]
     for i in range(m - warm):
         ops.append(("F", warm + i))

@@ -23,15 +23,22 @@ def _free_port():
 
 def test_schedules():
     assert build_schedule("sync", 0, 2, 3) == [("F", 0), ("F", 1), ("F", 2), ("B", 0), ("B", 1), ("B", 2)]
-    # last stage alternates immediately; first stage warms up with S-1 forwards (1F1B)
-    assert build_schedule("semi_async", 2, 3, 4) == [("F", 0), ("B", 0), ("F", 1), ("B", 1), ("F", 2), ("B", 2),
-                                                     ("F", 3), ("B", 3)]
-    assert build_schedule("semi_async", 0, 3, 4) == [("F", 0), ("F", 1), ("F", 2), ("B", 0), ("F", 3), ("B", 1),
-                                                     ("B", 2), ("B", 3)]
-    for st in range(4):
-        ops = build_schedule("semi_async", st, 4, 2)
-        assert sorted(ops) == sorted([("F", 0), ("F", 1), ("B", 0), ("B", 1)])
-        assert all(ops.index(("F", i)) < ops.index(("B", i)) for i in range(2))
+    # last stage alternates immediately; with the textbook warm-up the first stage runs S-1 forwards ahead (1F1B)
+    assert build_schedule("semi_async", 2, 3, 4, 1) == [("F", 0), ("B", 0), ("F", 1), ("B", 1), ("F", 2), ("B", 2),
+                                                        ("F", 3), ("B", 3)]
+    assert build_schedule("semi_async", 0, 3, 4, 1) == [("F", 0), ("F", 1), ("F", 2), ("B", 0), ("F", 3), ("B", 1),
+                                                        ("B", 2), ("B", 3)]
+    # default: two microbatches of lead per stage of distance to the end, so transfers hide behind compute
+    assert build_schedule("semi_async", 1, 3, 6) == [("F", 0), ("F", 1), ("F", 2), ("B", 0), ("F", 3), ("B", 1),
+                                                     ("F", 4), ("B", 2), ("F", 5), ("B", 3), ("B", 4), ("B", 5)]
+    assert build_schedule("semi_async", 0, 3, 6)[:5] == [("F", 0), ("F", 1), ("F", 2), ("F", 3), ("F", 4)]
+    for factor in (1, 2, 3):
+        for st in range(4):
+            for m in (2, 5):
+                ops = build_schedule("semi_async", st, 4, m, factor)
+                assert sorted(ops) == sorted([("F", i) for i in range(m)] + [("B", i) for i in range(m)])
+                assert all(ops.index(("F", i)) < ops.index(("B", i)) for i in range(m))
+                assert [o for o in ops if o[0] == "B"] == [("B", i) for i in range(m)]
 
 
 def _proc(rank, world, port, out, stages, reps, micro, schedule):
