@@ -391,8 +391,9 @@ DCNN_API int dcnn_fused_allreduce_update_push(float* const* grad_ptrs, float* co
       per_sm = 1;
     }
   }
-  // default: two CTAs per SM when they fit (0.199 -> 0.183 ms at R = 2: more posted stores in flight per SM)
-  if (num_blocks <= 0) num_blocks = (per_sm >= 2 ? 2 : 1) * num_sms();
+  // default: two CTAs per SM for up to four replicas when they fit (0.199 -> 0.183 ms at R = 2: more posted stores in
+  // flight per SM); at R = 8 one CTA per SM measured the same or better (0.347 vs 0.359-0.374 ms)
+  if (num_blocks <= 0) num_blocks = (per_sm >= 2 && world <= 4 ? 2 : 1) * num_sms();
   if (num_blocks > per_sm * num_sms()) num_blocks = per_sm * num_sms();
   if (world == 2) fused_allreduce_update_push_kernel<2><<<num_blocks, 512, 0, stream>>>(q);
   else if (world == 4) fused_allreduce_update_push_kernel<4><<<num_blocks, 512, 0, stream>>>(q);
