@@ -38,7 +38,6 @@ struct ConvTcParams {
   int num_taps;
   int accumulate;
   int relu;                      // epilogue: out = max(out + bias, 0)  (Conv / Dense followed by ReLU without BatchNorm)
-  int lsu_store;                 // epilogue: 1 = coalesced st.global / red.global from the staging tile, 0 = TMA store
   long long out_sn, out_sh, out_sw;
   float* out;
   const float* bias;
@@ -86,16 +85,9 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
                                          uint32_t& ring_pos, Release release) {
   constexpr int RS = CHUNKS * 32;  // row stride of `red`
   const bool stats = p.partials != nullptr;
-  long long* row_off = reinterpret_cast<long long*>(row_valid + 128);   // [128] element offsets of the rows, -1 = outside
-  if (p.lsu_store) asm volatile("bar.sync 1, 128;" ::: "memory");   // the previous tile's stores have read row_off
-  if ((stats && !t.full) || p.lsu_store) {
+  if (stats && !t.full) {
     const int w_l = r % t.obw, h_l = (r / t.obw) % t.obh, n_l = r / (t.obw * t.obh);
-    const bool ok = (t.n0 + n_l < p.N) && (t.oh0 + h_l < p.OH) && (t.ow0 + w_l < p.OW);
-    row_valid[r] = ok ? 1 : 0;
-    if (p.lsu_store)
-      row_off[r] = ok ? (long long)(t.n0 + n_l) * p.out_sn + (long long)(t.oh0 + h_l) * p.out_sh +
-                            (long long)(t.ow0 + w_l) * p.out_sw
-                      : -1ll;
+    row_valid[r] = ((t.n0 + n_l < p.N) && (t.oh0 + h_l < p.OH) && (t.ow0 + w_l < p.OW)) ? 1 : 0;
   }
   const int cl = e & 31, rg = e >> 5;
   int cnt = kBM, nch = 0;
@@ -125,35 +117,16 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
       if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
       *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
     }
-    if (p.lsu_store) {
-      // SM-issued stores: the TMA unit keeps its queue for the operand loads of the mainloop (a TMA store issued here
-      // waits behind up to three stages of queued loads).  Thread e writes the 16-byte pieces e, e+128, ... of the
-      // [128 rows][128 B] chunk: eight consecutive threads cover one 128-byte row segment.
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int piece = k * 128 + e, row = piece >> 3, c16 = piece & 7;
-        const long long off = row_off[row];
-        const int c = c0 + c16 * 4;
-        if (off >= 0 && c < p.Cout) {
-          const float4 v = *reinterpret_cast<const float4*>(buf + row * 128 + ((c16 ^ (row & 7)) << 4));
-          float* dstg = p.out + off + c;
-          if (p.accumulate)
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dstg), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
-                         : "memory");
-          else
-            *reinterpret_cast<float4*>(dstg) = v;
-        }
-      }
-    } else {
-      fence_proxy_async();
-      if (e == 0) tma_store_wait_read_n<kEpiRing - 2>();   // the next chunk's buffer is no longer being read
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (e == 0) {
-        if (p.accumulate) tma_reduce_add_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
-        else tma_store_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
-        tma_store_commit();
-      }
+    // (Writing the chunk with coalesced st.global / red.global from the SMs instead -- on the theory that a TMA store
+    // queues behind the mainloop's TMA loads -- was measured and is slower: 15.33 vs 14.23 ms per ResNet-50 step,
+    // 1x1 64->256 @32x32 158 vs 97 us; profiles/05 section 7.  The TMA store stays.)
+    fence_proxy_async();
+    if (e == 0) tma_store_wait_read_n<kEpiRing - 2>();   // the next chunk's buffer is no longer being read
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (e == 0) {
+      if (p.accumulate) tma_reduce_add_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
+      else tma_store_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
+      tma_store_commit();
     }
     ++ring_pos;
     if (stats) {
@@ -229,7 +202,7 @@ struct ConvTc2Smem {
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
-  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*row offsets*/ + 1024 /*align*/;
+  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*align*/;
 };
 
 template <int BN, int STAGES>
@@ -409,7 +382,7 @@ struct ConvTc3Smem {
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
-  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*row offsets*/ + 1024 /*align*/;
+  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*align*/;
   static_assert(kTotalBytes <= 232448, "conv_tc3 shared memory exceeds 227 KB");
   static_assert(4 * BN <= 512, "conv_tc3 accumulators exceed TMEM");
 };
@@ -600,7 +573,7 @@ struct ConvTc5Smem {
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
-  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*row offsets*/ + 1024 /*align*/;
+  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*align*/;
   static_assert(kTotalBytes <= 232448, "conv_tc5 shared memory exceeds 227 KB");
 };
 
@@ -1242,10 +1215,6 @@ DCNN_API int dcnn_conv_tc(const float* x, int N, int H, int W, int Cin, const fl
   p.in_mul_h = in_mul_h; p.in_mul_w = in_mul_w;
   p.Cin = Cin; p.Cout = Cout;
   p.num_taps = num_taps; p.accumulate = accumulate; p.relu = relu;
-  {
-    static const int lsu = getenv("DCNN_EPI_STORE") != nullptr && strcmp(getenv("DCNN_EPI_STORE"), "lsu") == 0 ? 1 : 0;
-    p.lsu_store = lsu;
-  }
   p.out_sn = out_sn; p.out_sh = out_sh; p.out_sw = out_sw;
   p.out = out; p.bias = bias; p.partials = partials;
   for (int t = 0; t < num_taps; ++t) {

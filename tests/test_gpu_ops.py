@@ -322,10 +322,11 @@ def test_groupnorm(N, C, H, W, G):
 
 
 # ----------------------------------------------------------------------------------------- pooling / act / misc
+@pytest.mark.parametrize("H", [13, 12])
 @pytest.mark.parametrize("C", [64, 6])
 @pytest.mark.parametrize("k,s,p", [(2, 2, 0), (3, 2, 1), (3, 3, 0), (3, 1, 1)])
-def test_maxpool(C, k, s, p):
-    x = torch.randn(3, C, 13, 13)
+def test_maxpool(C, k, s, p, H):
+    x = torch.randn(3, C, H, H + 3)
     y_ref, idx_ref = ref.maxpool_forward(x, (k, k), (s, s), (p, p))
     y, idx = ops.maxpool_forward(cl(x), (k, k), (s, s), (p, p))
     check_close(y, y_ref, 1e-7, "maxpool fwd")
