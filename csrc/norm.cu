@@ -412,8 +412,10 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
   constexpr int TY = 256 / TX;
   __shared__ float4 s_a[TY][TX];
   __shared__ float4 s_b[TY][TX];
-  const int tile = blockIdx.x;
-  const int c = (blockIdx.y * TX + threadIdx.x) * 4;
+  // column chunk fastest: CTAs that are resident together read neighbouring 4*TX-channel pieces of the SAME rows, so
+  // between them they consume whole rows (whole DRAM pages) instead of a 512-byte piece of every row each
+  const int tile = blockIdx.y;
+  const int c = (blockIdx.x * TX + threadIdx.x) * 4;
   const long long r0 = (long long)tile * rows_per_tile, r1 = min(M, r0 + rows_per_tile);
   const bool active = c < C;
   float4 a = make_float4(0, 0, 0, 0), b = a;
@@ -884,6 +886,7 @@ static int bwd_rows_per_tile(long long M, int C, int* tiles) {
   long long rows = ceil_div(M, want);
   if (rows < 32) rows = 32;
   if (rows > 256) rows = 256;
+  if (ceil_div(M, rows) > 65535) rows = ceil_div(M, 65535);   // the row tiles are the grid's y dimension
   rows = ceil_div(rows, ty) * ty;
   *tiles = (int)ceil_div(M, rows);
   return (int)rows;
@@ -900,7 +903,7 @@ template <int TX>
 static void launch_bwd_reduce(const float* dout, const float* x, const float* out, const float* mean,
                               const float* invstd, long long M, int C, int relu, int rows, int tiles, float* partials,
                               cudaStream_t stream) {
-  dim3 grid(tiles, ceil_div(C, 4 * TX)), block(TX, 256 / TX);
+  dim3 grid(ceil_div(C, 4 * TX), tiles), block(TX, 256 / TX);
   if (relu == 3) bn_bwd_reduce_kernel<3, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
   else if (relu == 2) bn_bwd_reduce_kernel<2, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
   else if (relu) bn_bwd_reduce_kernel<1, TX><<<grid, block, 0, stream>>>(dout, x, out, mean, invstd, M, C, rows, partials);
