@@ -27,7 +27,8 @@ using namespace tc;
 constexpr int kMaxTaps = 49;
 constexpr int kBM = 128;       // output pixels per tile == TMEM lanes
 constexpr int kBK = 32;        // fp32 per k-block == 128 bytes == one swizzle row
-constexpr int kThreads = 192;  // warp0: TMA, warp1: MMA + TMEM alloc, warps 2-5: epilogue
+constexpr int kThreads = 320;   // conv kernels: warp0 TMA, warp1 MMA + TMEM alloc, warps 2-5 and 6-9: two epilogue groups
+constexpr int kWgradThreads = 192;  // wgrad: warp0 TMA, warp1 MMA + TMEM alloc, warps 2-5 epilogue
 
 struct ConvTcParams {
   int N, OH, OW;                 // loop-space extents
@@ -47,10 +48,15 @@ struct ConvTcParams {
 };
 
 // =====================================================================================================
-// Epilogue shared by the three kernels below.  Four warps (128 threads, named barriers 1 and 2) turn one accumulator
+// Epilogue shared by the three kernels below.  TWO groups of four warps (128 threads each; group g uses named barriers
+// 1+2g and 2+2g, staging buffers 2g and 2g+1, and takes the 32-column chunks g, g+2, ... of a tile) turn one accumulator
 // tile of 128 rows x CHUNKS*32 columns into (a) TMA stores (or TMA reduce-adds) of the output tile and (b) BatchNorm
-// partial statistics.  The tile moves through a RING of [128 rows][32 columns] staging buffers, one 32-column chunk
-// at a time, so that the TMA store of a chunk, the statistics pass over it and the TMEM drain of the next chunk overlap:
+// partial statistics.  With one group every SM sub-partition ran a single epilogue warp, so nothing hid its LDS / FADD
+// latencies (ncu, 1x1 64->256 @32x32: 1600 cycles per chunk for ~450 instructions, tensor pipe 9 %); a tcgen05.ld may
+// only touch the 32 TMEM lanes of its warp's quadrant (warp % 4), which warps 6-9 cover again.  The two groups never
+// synchronise with each other: each merges the statistics of its own chunks.  Within a group a chunk moves through
+// that group's two staging buffers, so that the TMA store of a chunk, the statistics pass over it and the TMEM drain of
+// the group's next chunk overlap:
 //   per chunk   tcgen05.ld -> (+bias) -> 128B-swizzled staging buffer -> fence.proxy.async -> ONE named barrier
 //               -> thread 0: TMA store / reduce-add of that chunk (rows and columns outside the tensor are clipped by
 //                  the TMA unit), its own bulk group
@@ -58,8 +64,8 @@ struct ConvTcParams {
 //                  with conflict-free swizzled reads: thread (column cl, row group rg) sums 32 rows
 //   per tile    the TMEM buffer goes back to the MMA warp right after its last tcgen05.ld; the four row groups are merged
 //               through `red` and written as one partial-statistics tile.
-// A staging buffer is reused RING chunks later; thread 0 keeps at most RING-2 bulk groups unfinished before the barrier
-// of a chunk, which frees the buffer of the NEXT chunk (cp.async.bulk.wait_group.read).
+// A staging buffer is reused two chunks of the group later; the group's thread 0 lets no bulk group stay unfinished
+// before the barrier of a chunk, which frees the buffer of the group's NEXT chunk (cp.async.bulk.wait_group.read 0).
 // =====================================================================================================
 struct EpiTile {
   int n0, oh0, ow0;     // first output pixel of the tile
@@ -71,7 +77,8 @@ struct EpiTile {
   bool full;            // no row of the tile is outside [N, OH, OW]
 };
 
-constexpr int kEpiRing = 4;                                  // staging buffers of 16 KB
+constexpr int kEpiRing = 4;                                  // staging buffers of 16 KB: two per epilogue group
+constexpr int kEpiGroups = 2;
 constexpr int epi_red_floats(int cols) { return 9 * cols; }  // [2][4 row groups][cols] sums + [cols] shifts
 
 template <int N>
@@ -79,10 +86,13 @@ __device__ __forceinline__ void tma_store_wait_read_n() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 
+// g: epilogue group (0 / 1); e: thread index inside the group (0..127); r: accumulator row = TMEM lane of this thread;
+// row_valid: this group's 128 row flags; ring_pos: this group's chunk counter.  release() is called by every thread of
+// the group once the group's last tcgen05.ld of the tile has completed.
 template <int CHUNKS, typename Release>
 __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMap* tmO, const EpiTile& t,
-                                         uint32_t tmem_d, uint8_t* staging, float* red, uint8_t* row_valid, int r, int e,
-                                         uint32_t& ring_pos, Release release) {
+                                         uint32_t tmem_d, uint8_t* staging, float* red, uint8_t* row_valid, int g, int r,
+                                         int e, uint32_t& ring_pos, Release release) {
   constexpr int RS = CHUNKS * 32;  // row stride of `red`
   const bool stats = p.partials != nullptr;
   if (stats && !t.full) {
@@ -90,17 +100,22 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
     row_valid[r] = ((t.n0 + n_l < p.N) && (t.oh0 + h_l < p.OH) && (t.ow0 + w_l < p.OW)) ? 1 : 0;
   }
   const int cl = e & 31, rg = e >> 5;
-  int cnt = kBM, nch = 0;
+  const int bar_a = 1 + 2 * g, bar_b = 2 + 2 * g;
+  int cnt = kBM;
+  bool any = false, released = false;
 #pragma unroll 1
-  for (int ch = 0; ch < CHUNKS; ++ch) {
+  for (int ch = g; ch < CHUNKS; ch += kEpiGroups) {
     const int c0 = t.col_base + ch * 32;
     if (c0 >= p.Cout) break;
-    nch = ch + 1;
+    any = true;
     uint32_t v[32];
     tmem_ld_32x32b_x32(tmem_d + ch * 32, v);
     tmem_ld_wait();
-    if (ch == CHUNKS - 1 || c0 + 32 >= p.Cout) release();   // the accumulator is in registers: TMEM back to the MMA warp
-    uint8_t* buf = staging + (ring_pos % kEpiRing) * (kBM * 128);
+    if (ch + kEpiGroups >= CHUNKS || c0 + 32 * kEpiGroups >= p.Cout) {   // the group's last chunk of this tile
+      release();                                                         // accumulator in registers: TMEM back to the MMA warp
+      released = true;
+    }
+    uint8_t* buf = staging + (g * 2 + (ring_pos & 1)) * (kBM * 128);
     uint8_t* dst = buf + r * 128;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -121,8 +136,8 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
     // queues behind the mainloop's TMA loads -- was measured and is slower: 15.33 vs 14.23 ms per ResNet-50 step,
     // 1x1 64->256 @32x32 158 vs 97 us; profiles/05 section 7.  The TMA store stays.)
     fence_proxy_async();
-    if (e == 0) tma_store_wait_read_n<kEpiRing - 2>();   // the next chunk's buffer is no longer being read
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (e == 0) tma_store_wait_read_n<0>();   // the group's other buffer (its next chunk's) is no longer being read
+    asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
     if (e == 0) {
       if (p.accumulate) tma_reduce_add_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
       else tma_store_4d(tmO, buf, c0, t.ow0, t.oh0, t.n0);
@@ -130,7 +145,7 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
     }
     ++ring_pos;
     if (stats) {
-      if (ch == 0 && !t.full) {
+      if (ch == g && !t.full) {   // the group's first chunk of the tile
         cnt = 0;
         for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
       }
@@ -161,11 +176,13 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
       if (rg == 0) red[8 * RS + ch * 32 + cl] = kshift;
     }
   }
-  if (!stats) return;
-  asm volatile("bar.sync 2, 128;" ::: "memory");
-  for (int j = e; j < nch * 32; j += 128) {
+  if (!released) release();   // a group without a chunk in this tile (narrow last n-tile) still hands the TMEM buffer back
+  if (!stats || !any) return;
+  asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");
+  // merge the four row groups of this group's chunks (columns of the chunks g, g+2, ...)
+  for (int j = e; j < RS; j += 128) {
     const int c = t.col_base + j;
-    if (c >= p.Cout) continue;   // the last chunk of a channel count that is not a multiple of 32
+    if (((j >> 5) % kEpiGroups) != g || c >= p.Cout) continue;   // the other group's chunk, or beyond the last channel
     const float kshift = red[8 * RS + j];
     const float s = red[(0 * 4 + 0) * RS + j] + red[(0 * 4 + 1) * RS + j] + red[(0 * 4 + 2) * RS + j] +
                     red[(0 * 4 + 3) * RS + j];
@@ -175,7 +192,7 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
     p.partials[((long long)t.stat_tile * 2 + 0) * p.Cout + c] = s + n * kshift;
     p.partials[((long long)t.stat_tile * 2 + 1) * p.Cout + c] = cnt > 0 ? fmaxf(qq - s * s / n, 0.f) : 0.f;
   }
-  if (e == 0 && t.write_count) p.partials[(long long)t.stat_tiles * 2 * p.Cout + t.stat_tile] = (float)cnt;
+  if (e == 0 && g == 0 && t.write_count) p.partials[(long long)t.stat_tiles * 2 * p.Cout + t.stat_tile] = (float)cnt;
 }
 
 // =====================================================================================================
@@ -202,7 +219,7 @@ struct ConvTc2Smem {
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
-  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*align*/;
+  static constexpr int kTotalBytes = kFlagOff + 256 /*row flags of both epilogue groups*/ + 1024 /*align*/;
 };
 
 template <int BN, int STAGES>
@@ -243,7 +260,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
-        mbar_init(&tmem_empty_bar[a], 4);  // one arrival per epilogue warp
+        mbar_init(&tmem_empty_bar[a], 8);  // one arrival per epilogue warp (two groups of four)
       }
       fence_barrier_init();
     }
@@ -313,7 +330,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
     // ===================== epilogue (warps 2..5) =====================
     const int q = warp & 3;          // TMEM lane quadrant
     const int r = q * 32 + lane;     // tile row owned by this thread
-    const int e = threadIdx.x - 64;  // 0..127
+    const int g = (warp - 2) >> 2;   // epilogue group: warps 2-5 / 6-9
+    const int e = (threadIdx.x - 64) & 127;  // thread index inside the group
     int as = 0;
     uint32_t aphase = 0, ring_pos = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -332,8 +350,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
       uint64_t* rel_bar = &tmem_empty_bar[as];
-      epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + (uint32_t(q * 32) << 16), staging, red, row_valid, r, e,
-                           ring_pos, [&]() {
+      epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + (uint32_t(q * 32) << 16), staging, red, row_valid + g * 128, g,
+                           r, e, ring_pos, [&]() {
                              tc_fence_before();
                              __syncwarp();
                              if (lane == 0) mbar_arrive(rel_bar);
@@ -382,7 +400,7 @@ struct ConvTc3Smem {
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
-  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*align*/;
+  static constexpr int kTotalBytes = kFlagOff + 256 /*row flags of both epilogue groups*/ + 1024 /*align*/;
   static_assert(kTotalBytes <= 232448, "conv_tc3 shared memory exceeds 227 KB");
   static_assert(4 * BN <= 512, "conv_tc3 accumulators exceed TMEM");
 };
@@ -427,7 +445,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tmem_full_bar[a], 1);
-        mbar_init(&tmem_empty_bar[a], 4);  // one arrival per epilogue warp
+        mbar_init(&tmem_empty_bar[a], 8);  // one arrival per epilogue warp (two groups of four)
       }
       fence_barrier_init();
     }
@@ -500,7 +518,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
     // ===================== epilogue (warps 2..5), one 128-row half at a time =====================
     const int q = warp & 3;
     const int r = q * 32 + lane;     // row inside the half
-    const int e = threadIdx.x - 64;  // 0..127
+    const int g = (warp - 2) >> 2;   // epilogue group: warps 2-5 / 6-9
+    const int e = (threadIdx.x - 64) & 127;  // thread index inside the group
     int as = 0;
     uint32_t aphase = 0, ring_pos = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -523,7 +542,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
 
         uint64_t* rel_bar = &tmem_empty_bar[as];
         epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16), staging, red,
-                             row_valid, r, e, ring_pos, [&]() {
+                             row_valid + g * 128, g, r, e, ring_pos, [&]() {
                                if (half == 1) {   // both halves read: hand the accumulator buffer back to the MMA warp
                                  tc_fence_before();
                                  __syncwarp();
@@ -573,7 +592,7 @@ struct ConvTc5Smem {
   static constexpr int kBarOff = kPipeBytes + kStagingBytes;
   static constexpr int kRedOff = kBarOff + 256;
   static constexpr int kFlagOff = kRedOff + kRedBytes;
-  static constexpr int kTotalBytes = kFlagOff + 128 /*row flags*/ + 1024 /*align*/;
+  static constexpr int kTotalBytes = kFlagOff + 256 /*row flags of both epilogue groups*/ + 1024 /*align*/;
   static_assert(kTotalBytes <= 232448, "conv_tc5 shared memory exceeds 227 KB");
 };
 
@@ -618,7 +637,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(&tmem_full_bar[a], 1);   // one multicast commit
-        mbar_init(&tmem_empty_bar[a], 8);  // (used in the leader) 4 epilogue warps of each CTA
+        mbar_init(&tmem_empty_bar[a], 16);  // (used in the leader) 8 epilogue warps of each CTA
       }
       fence_barrier_init();
     }
@@ -696,7 +715,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     // ===================== epilogue (warps 2..5 of both CTAs): own 128 pixels, 256 channels in two halves ==========
     const int q = warp & 3;
     const int r = q * 32 + lane;
-    const int e = threadIdx.x - 64;
+    const int g = (warp - 2) >> 2;   // epilogue group: warps 2-5 / 6-9
+    const int e = (threadIdx.x - 64) & 127;
     int as = 0;
     uint32_t aphase = 0, ring_pos = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
@@ -730,7 +750,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         };
         if (cols_live)
           epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16), staging, red,
-                               row_valid, r, e, ring_pos, release);
+                               row_valid + g * 128, g, r, e, ring_pos, release);
         else
           release();
       }
@@ -783,7 +803,7 @@ struct WgradSmem {
 };
 
 template <int BNW, int STAGES>
-__global__ void __launch_bounds__(kThreads) wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY,
+__global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY,
                                                             const __grid_constant__ CUtensorMap tmX,
                                                             const __grid_constant__ WgradTcParams p) {
   using S = WgradSmem<BNW, STAGES>;
@@ -1158,7 +1178,7 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
   using S = WgradSmem<BNW, STAGES>;
   DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, wgrad_tc_kernel<BNW, STAGES>);
   dim3 grid((unsigned)(p.num_taps * p.oc_tiles * p.c_tiles), (unsigned)p.splits);
-  wgrad_tc_kernel<BNW, STAGES><<<grid, kThreads, S::kTotalBytes, stream>>>(tmDY, tmX, p);
+  wgrad_tc_kernel<BNW, STAGES><<<grid, kWgradThreads, S::kTotalBytes, stream>>>(tmDY, tmX, p);
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(1);
   return 0;
