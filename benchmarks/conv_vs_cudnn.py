@@ -46,6 +46,8 @@ def main():
               (128, 128, 16, 3, 1, 1), (512, 256, 16, 1, 1, 0), (256, 256, 16, 3, 2, 1), (256, 1024, 8, 1, 1, 0),
               (1024, 256, 8, 1, 1, 0), (256, 256, 8, 3, 1, 1), (1024, 512, 8, 1, 1, 0), (512, 512, 8, 3, 2, 1),
               (512, 2048, 4, 1, 1, 0), (2048, 512, 4, 1, 1, 0), (512, 512, 4, 3, 1, 1)]
+    if os.environ.get("BENCH_SHAPES"):      # comma-separated indices into the list above
+        shapes = [shapes[int(i)] for i in os.environ["BENCH_SHAPES"].split(",")]
     print(f"batch {N}; times in us (ours / cuDNN), ratio > 1 means ours is faster")
     print(f"{'shape':32s} {'fprop':>17s} {'dgrad':>17s} {'wgrad':>17s}")
     tot = [0.0, 0.0]

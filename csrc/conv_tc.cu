@@ -781,6 +781,7 @@ struct WgradTcParams {
   int in_mul_h, in_mul_w;
   int Cin, Cout, Ktot;
   int num_taps, oc_tiles, c_tiles, splits;
+  int pair;   // 1: two taps per CTA (Cout <= 64, stride 1, same-size output): see dcnn_wgrad_tc
   float* dw;  // [Cout][Ktot]
   float* scratch;  // deterministic mode: [splits][Cout][Ktot] slabs written with plain stores (else nullptr)
   float* db;       // bias gradient [Cout] (+=), or nullptr: column sums of dY by one extra N = 16 MMA against a tile of ones
@@ -869,6 +870,16 @@ __global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_co
         int stage = 0;
         uint32_t phase = 0;
         const int dh = p.tap_dh[tap], dw_ = p.tap_dw[tap];
+        // Only boxes that hold real channels are loaded (a box wholly beyond Cout / Cin would be zero-filled by the TMA
+        // unit -- measured: at no cost in time, so this saves nothing but the fill); the accumulator rows / columns of
+        // a skipped box hold garbage that the guarded write-back never stores.
+        const int na = min(4, (p.Cout - oc0 + 31) >> 5);
+        const int nb = min(BNW / 32, (p.Cin - c0 + 31) >> 5);
+        // pair mode: rows 0-63 of the tile are dY shifted by -tap(2*tap), rows 64-127 dY shifted by -tap(2*tap+1), and
+        // X is loaded unshifted, once for both taps
+        const int t1 = 2 * tap + 1;
+        const int na_pair = na * (t1 < p.num_taps ? 2 : 1);
+        const uint32_t stage_tx = uint32_t((p.pair ? na_pair : na) + nb) * (kWPix * 128);
         for (int kb = 0; kb < num_kb; ++kb) {
           const int pt = pt_begin + kb;
           const int tw = pt % p.tiles_w;
@@ -876,16 +887,30 @@ __global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_co
           const int tn = pt / (p.tiles_w * p.tiles_h);
           const int n0 = tn * p.bn, oh0 = th * p.bh, ow0 = tw * p.bw;
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
+          mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
           uint8_t* sA = smem + stage * S::kStageBytes;
           uint8_t* sB = sA + S::kABytes;
+          if (p.pair) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            tma_load_4d(sA + i * kWPix * 128, &tmDY, &full_bar[stage], oc0 + i * 32, ow0, oh0, n0);
+            for (int i = 0; i < 4; ++i) {
+              const int t = 2 * tap + (i >> 1);
+              if (t < p.num_taps && (i & 1) < na)
+                tma_load_4d(sA + i * kWPix * 128, &tmDY, &full_bar[stage], (i & 1) * 32, ow0 - p.tap_dw[t],
+                            oh0 - p.tap_dh[t], n0);
+            }
 #pragma unroll
-          for (int j = 0; j < BNW / 32; ++j)
-            tma_load_4d(sB + j * kWPix * 128, &tmX, &full_bar[stage], c0 + j * 32, ow0 * p.in_mul_w + dw_,
-                        oh0 * p.in_mul_h + dh, n0);
+            for (int j = 0; j < BNW / 32; ++j)
+              if (j < nb) tma_load_4d(sB + j * kWPix * 128, &tmX, &full_bar[stage], c0 + j * 32, ow0, oh0, n0);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (i < na) tma_load_4d(sA + i * kWPix * 128, &tmDY, &full_bar[stage], oc0 + i * 32, ow0, oh0, n0);
+#pragma unroll
+            for (int j = 0; j < BNW / 32; ++j)
+              if (j < nb)
+                tma_load_4d(sB + j * kWPix * 128, &tmX, &full_bar[stage], c0 + j * 32, ow0 * p.in_mul_w + dw_,
+                            oh0 * p.in_mul_h + dh, n0);
+          }
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -924,7 +949,9 @@ __global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_co
       const int r = q * 32 + lane;  // output row = oc
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
-      const int oc = oc0 + r;
+      // pair mode: row r is output channel r % 64 of tap 2*tap + r / 64
+      const int etap = p.pair ? 2 * tap + (r >> 6) : tap;
+      const int oc = p.pair ? (etap < p.num_taps ? (r & 63) : p.Cout) : oc0 + r;
       if (bias_cta) {
         uint32_t v[32];
         tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + BNW, v);   // column 0 of the 16 (identical) sums
@@ -937,7 +964,7 @@ __global__ void __launch_bounds__(kWgradThreads) wgrad_tc_kernel(const __grid_co
         tmem_ld_32x32b_x32(tmem_base + (uint32_t(q * 32) << 16) + cc, v);
         tmem_ld_wait();
         if (oc < p.Cout) {
-          const long long off = (long long)oc * p.Ktot + (long long)p.tap_w[tap] * p.Cin + c0 + cc;
+          const long long off = (long long)oc * p.Ktot + (long long)p.tap_w[etap] * p.Cin + c0 + cc;
           if (p.scratch != nullptr) {
             // deterministic mode: this split's slab, summed over the splits in a fixed order by wgrad_reduce_kernel
             float* dst = p.scratch + (long long)blockIdx.y * p.Cout * p.Ktot + off;
@@ -1177,7 +1204,8 @@ template <int BNW, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradTcParams& p, cudaStream_t stream) {
   using S = WgradSmem<BNW, STAGES>;
   DCNN_SET_MAX_SMEM_ONCE(S::kTotalBytes, wgrad_tc_kernel<BNW, STAGES>);
-  dim3 grid((unsigned)(p.num_taps * p.oc_tiles * p.c_tiles), (unsigned)p.splits);
+  const int tap_groups = p.pair ? (p.num_taps + 1) / 2 : p.num_taps;
+  dim3 grid((unsigned)(tap_groups * p.oc_tiles * p.c_tiles), (unsigned)p.splits);
   wgrad_tc_kernel<BNW, STAGES><<<grid, kWgradThreads, S::kTotalBytes, stream>>>(tmDY, tmX, p);
   DCNN_CHECK_LAUNCH();
   DCNN_COUNT_LAUNCH(1);
@@ -1366,7 +1394,16 @@ DCNN_API int dcnn_wgrad_tc(const float* dy, int N, int OH, int OW, int Cout, con
   memset(&p, 0, sizeof(p));
   p.N = N; p.OH = OH; p.OW = OW;
   int bnw;
-  wgrad_geometry(N, OH, OW, Cout, Cin, in_mul_h, in_mul_w, num_taps, &p, &bnw);
+  // Two taps per CTA when the 128-row tile would be half empty (Cout <= 64): with a same-size stride-1 output,
+  //   dW[oc][tap][c] = sum over x positions of dY[pos - tap][oc] * X[pos][c]   (dY zero outside the image),
+  // so rows 0-63 / 64-127 of the A tile hold dY shifted by two different taps and one unshifted X tile serves both: half
+  // the CTAs and MMAs, and 48 KB instead of 64 KB of operand traffic per k-block and tap pair (3x3 64->64 at 32x32,
+  // batch 256: 166 -> 98 us, the ResNet-50 step 13.58 -> 13.38 ms; profiles/05 section 8).  Not with the fused bias
+  // gradient (its column sums need unshifted dY) nor in the deterministic mode (dcnn_wgrad_tc_splits sizes the scratch
+  // from the unpaired geometry).
+  p.pair = (Cout <= 64 && num_taps >= 2 && in_mul_h == 1 && in_mul_w == 1 && OH == H && OW == W && db == nullptr &&
+            scratch == nullptr) ? 1 : 0;
+  wgrad_geometry(N, OH, OW, Cout, Cin, in_mul_h, in_mul_w, p.pair ? (num_taps + 1) / 2 : num_taps, &p, &bnw);
   p.in_mul_h = in_mul_h; p.in_mul_w = in_mul_w;
   p.Cin = Cin; p.Cout = Cout; p.Ktot = Ktot; p.num_taps = num_taps;
   p.dw = dw;

@@ -110,6 +110,9 @@ CONV_CASES = [
     (3, 20, 9, 9, 12, 1, 1, 0, False),
     (2, 36, 12, 12, 40, 3, 2, 1, False),
     (2, 6, 8, 8, 10, 3, 1, 1, True),         # neither multiple of 4: CUDA-core kernels
+    (3, 32, 13, 13, 32, 3, 1, 1, False),     # wgrad with two taps per CTA (Cout <= 64, stride 1, same-size output):
+    (2, 40, 10, 10, 48, 5, 1, 2, False),     #   odd image sizes, 25 taps (an unpaired last tap), channels % 32 != 0,
+    (2, 256, 8, 8, 64, 3, 1, 1, False),      #   several input-channel tiles
 ]
 
 
