@@ -337,7 +337,7 @@ def main():
     # ---- end-to-end arm: public API, pinned-host -> device copy of every batch + loss read-back every step
     h2d = host_x[0].numel() * 4 + host_t[0].numel() * 4
     d2h = 8
-    out_host = pin(torch.zeros(2, dtype=torch.float32))
+    out_host = [pin(torch.zeros(2, dtype=torch.float32)) for _ in range(2)]
     # The batches come through the library's PrefetchLoader, the front end train_classification_model puts on every
     # loader (dcnn_b200/train.py): a worker thread stages each batch in pinned memory and issues its host-to-device copy
     # on a side stream, so the copy of batch i+1 overlaps the kernels of step i.  One "epoch" of exactly `steps` batches
@@ -364,18 +364,25 @@ def main():
     def e2e_epoch(n):
         from dcnn_b200.data import PrefetchLoader
         feed = PrefetchLoader(_HostBatches(n), B, depth=2, device=None if cpu_mode else dev)
-        done, last = 0, (None, None)
+        done, last, landed = 0, (None, None), [None, None]
         while True:
             b = feed.get_next_batch()
             if b is None:
                 break
             loss, correct = step(b[0], b[1])
-            if loss is not None:
-                out_host[0].copy_(loss, non_blocking=True)
-                out_host[1].copy_(correct, non_blocking=True)
+            slot = done & 1
+            if loss is not None:                       # every step's loss and correct count are read back ...
+                out_host[slot][0].copy_(loss, non_blocking=True)
+                if correct is not None:
+                    out_host[slot][1].copy_(correct, non_blocking=True)
             if not cpu_mode:
-                torch.cuda.current_stream().synchronize()     # the step's result is on the host before the next step
+                landed[slot] = new_event()
+                landed[slot].record()
+                if landed[slot ^ 1] is not None:        # ... and the host waits for the PREVIOUS step's pair once this
+                    landed[slot ^ 1].synchronize()      # step is submitted, so the device never waits for the host
             done, last = done + 1, (loss, correct)
+        if not cpu_mode:
+            torch.cuda.current_stream().synchronize()
         feed.close()
         assert done == n, (done, n)
         return last
@@ -443,7 +450,7 @@ def main():
             "e2e": {"value": round(e2e, 2), "unit": "images/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "path": "dcnn_b200.data.PrefetchLoader (pinned staging, H2D on a side stream one batch ahead) -> "
-                            "train step -> loss/correct D2H + stream synchronize every step"},
+                            "train step -> loss/correct D2H every step, host waits for step i-1's pair after submitting step i"},
             "gpu_launches": int(launches),  # per rank, max over ranks
             "final_loss": final_loss,
         }
