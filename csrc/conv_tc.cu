@@ -61,7 +61,7 @@ struct ConvTcParams {
 //               -> thread 0: TMA store / reduce-add of that chunk (rows and columns outside the tensor are clipped by
 //                  the TMA unit), its own bulk group
 //               -> all: shifted single-pass statistics of the chunk (sum(x-k), sum((x-k)^2), k = the tile's first row)
-//                  with conflict-free swizzled reads: thread (column cl, row group rg) sums 32 rows
+//                  with conflict-free swizzled 64-bit reads: thread (column pair, 16-row group), two-wide FP32 math
 //   per tile    the TMEM buffer goes back to the MMA warp right after its last tcgen05.ld; the four row groups are merged
 //               through `red` and written as one partial-statistics tile.
 // A staging buffer is reused two chunks of the group later; the group's thread 0 lets no bulk group stay unfinished
@@ -89,7 +89,10 @@ __device__ __forceinline__ void tma_store_wait_read_n() {
 // g: epilogue group (0 / 1); e: thread index inside the group (0..127); r: accumulator row = TMEM lane of this thread;
 // row_valid: this group's 128 row flags; ring_pos: this group's chunk counter.  release() is called by every thread of
 // the group once the group's last tcgen05.ld of the tile has completed.
-template <int CHUNKS, typename Release>
+// POST: the launch has a bias and / or a ReLU to apply (kept out of the instruction stream of the common case -- a
+// ResNet convolution has neither -- where the predicated-off loads, adds and maxes were ~140 of the ~300 issue slots
+// per chunk of an issue-bound warp).
+template <int CHUNKS, bool POST, typename Release>
 __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMap* tmO, const EpiTile& t,
                                          uint32_t tmem_d, uint8_t* staging, float* red, uint8_t* row_valid, int g, int r,
                                          int e, uint32_t& ring_pos, Release release) {
@@ -99,7 +102,7 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
     const int w_l = r % t.obw, h_l = (r / t.obw) % t.obh, n_l = r / (t.obw * t.obh);
     row_valid[r] = ((t.n0 + n_l < p.N) && (t.oh0 + h_l < p.OH) && (t.ow0 + w_l < p.OW)) ? 1 : 0;
   }
-  const int cl = e & 31, rg = e >> 5;
+  const int rg = e >> 5;
   const int bar_a = 1 + 2 * g, bar_b = 2 + 2 * g;
   int cnt = kBM;
   bool any = false, released = false;
@@ -122,14 +125,16 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
       float4 o;
       o.x = __uint_as_float(v[4 * j + 0]); o.y = __uint_as_float(v[4 * j + 1]);
       o.z = __uint_as_float(v[4 * j + 2]); o.w = __uint_as_float(v[4 * j + 3]);
-      if (p.bias != nullptr) {
-        const int c = c0 + 4 * j;
-        if (c < p.Cout) {  // Cout % 4 == 0 on this path
-          const float4 b = ldg4(p.bias + c);
-          o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+      if constexpr (POST) {
+        if (p.bias != nullptr) {
+          const int c = c0 + 4 * j;
+          if (c < p.Cout) {  // Cout % 4 == 0 on this path
+            const float4 b = ldg4(p.bias + c);
+            o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+          }
         }
+        if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
       }
-      if (p.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
       *reinterpret_cast<float4*>(dst + ((j ^ (r & 7)) << 4)) = o;
     }
     // (Writing the chunk with coalesced st.global / red.global from the SMs instead -- on the theory that a TMA store
@@ -149,31 +154,46 @@ __device__ __forceinline__ void epi_tile(const ConvTcParams& p, const CUtensorMa
         cnt = 0;
         for (int rr = 0; rr < kBM; ++rr) cnt += row_valid[rr];
       }
-      const uint32_t coff = ((cl & 3) << 2);
-      const float kshift = *reinterpret_cast<const float*>(buf + ((cl >> 2) << 4) + coff);  // row 0
-      float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+      // thread (column pair cp, 16-row group hr): 16 LDS.64 and packed two-wide FP32 arithmetic (add / fma .f32x2,
+      // SASS FADD2 / FFMA2) -- a third of the issue slots of one column x 32 rows with scalar operations
+      const int cp = e & 15, hr = e >> 4;
+      const uint32_t cq = cp >> 1, coff = (cp & 1) << 3;
+      const uint8_t* rows = buf + hr * 16 * 128;
+      const float2 k2 = *reinterpret_cast<const float2*>(buf + (cq << 4) + coff);   // row 0 of the chunk: the shifts
+      float2 sum, sq;
       if (t.full) {
-#pragma unroll 8
-        for (int i = 0; i < 32; i += 2) {
-          const int ra = rg * 32 + i, rb = ra + 1;
-          const float xa = *reinterpret_cast<const float*>(buf + ra * 128 + (((cl >> 2) ^ (ra & 7)) << 4) + coff);
-          const float xb = *reinterpret_cast<const float*>(buf + rb * 128 + (((cl >> 2) ^ (rb & 7)) << 4) + coff);
-          const float da = xa - kshift, db = xb - kshift;
-          s0 += da; q0 = fmaf(da, da, q0);
-          s1 += db; q1 = fmaf(db, db, q1);
+        const uint64_t nk = f32x2_pack(-k2.x, -k2.y);
+        uint64_t sa = 0, sb = 0, qa = 0, qb = 0;   // the all-zero pattern is {0.f, 0.f}
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+          const uint64_t xa = *reinterpret_cast<const uint64_t*>(rows + i * 128 + ((cq ^ (i & 7)) << 4) + coff);
+          const uint64_t xb =
+              *reinterpret_cast<const uint64_t*>(rows + (i + 1) * 128 + ((cq ^ ((i + 1) & 7)) << 4) + coff);
+          const uint64_t da = f32x2_add(xa, nk), db = f32x2_add(xb, nk);
+          sa = f32x2_add(sa, da); qa = f32x2_fma(da, da, qa);
+          sb = f32x2_add(sb, db); qb = f32x2_fma(db, db, qb);
         }
+        sum = f32x2_unpack(f32x2_add(sa, sb));
+        sq = f32x2_unpack(f32x2_add(qa, qb));
       } else {
-        for (int i = 0; i < 32; ++i) {
-          const int rr = rg * 32 + i;
-          const float x = *reinterpret_cast<const float*>(buf + rr * 128 + (((cl >> 2) ^ (rr & 7)) << 4) + coff);
-          const float d = row_valid[rr] ? x - kshift : 0.f;
-          s0 += d;
-          q0 = fmaf(d, d, q0);
+        sum = make_float2(0.f, 0.f);
+        sq = make_float2(0.f, 0.f);
+        for (int i = 0; i < 16; ++i) {
+          const float2 x = *reinterpret_cast<const float2*>(rows + i * 128 + ((cq ^ (i & 7)) << 4) + coff);
+          const bool ok = row_valid[hr * 16 + i] != 0;
+          const float d0 = ok ? x.x - k2.x : 0.f, d1 = ok ? x.y - k2.y : 0.f;
+          sum.x += d0; sq.x = fmaf(d0, d0, sq.x);
+          sum.y += d1; sq.y = fmaf(d1, d1, sq.y);
         }
       }
-      red[(0 * 4 + rg) * RS + ch * 32 + cl] = s0 + s1;
-      red[(1 * 4 + rg) * RS + ch * 32 + cl] = q0 + q1;
-      if (rg == 0) red[8 * RS + ch * 32 + cl] = kshift;
+      // lanes 16-31 hold the second 16 rows of the warp's 32 for the same column pairs
+      sum.x += __shfl_xor_sync(0xffffffffu, sum.x, 16); sum.y += __shfl_xor_sync(0xffffffffu, sum.y, 16);
+      sq.x += __shfl_xor_sync(0xffffffffu, sq.x, 16); sq.y += __shfl_xor_sync(0xffffffffu, sq.y, 16);
+      if ((e & 16) == 0) {
+        *reinterpret_cast<float2*>(&red[(0 * 4 + rg) * RS + ch * 32 + 2 * cp]) = sum;
+        *reinterpret_cast<float2*>(&red[(1 * 4 + rg) * RS + ch * 32 + 2 * cp]) = sq;
+        if (rg == 0) *reinterpret_cast<float2*>(&red[8 * RS + ch * 32 + 2 * cp]) = k2;
+      }
     }
   }
   if (!released) release();   // a group without a chunk in this tile (narrow last n-tile) still hands the TMEM buffer back
@@ -334,6 +354,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
     const int e = (threadIdx.x - 64) & 127;  // thread index inside the group
     int as = 0;
     uint32_t aphase = 0, ring_pos = 0;
+    const bool post = p.bias != nullptr || p.relu != 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
@@ -350,12 +371,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc2_kernel(const __grid_cons
       mbar_wait(&tmem_full_bar[as], aphase);
       tc_fence_after();
       uint64_t* rel_bar = &tmem_empty_bar[as];
-      epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + (uint32_t(q * 32) << 16), staging, red, row_valid + g * 128, g,
-                           r, e, ring_pos, [&]() {
-                             tc_fence_before();
-                             __syncwarp();
-                             if (lane == 0) mbar_arrive(rel_bar);
-                           });
+      auto release = [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(rel_bar);
+      };
+      const uint32_t tmem_d = tmem_base + as * BN + (uint32_t(q * 32) << 16);
+      if (post)
+        epi_tile<S::kChunks, true>(p, &tmO, t, tmem_d, staging, red, row_valid + g * 128, g, r, e, ring_pos, release);
+      else
+        epi_tile<S::kChunks, false>(p, &tmO, t, tmem_d, staging, red, row_valid + g * 128, g, r, e, ring_pos, release);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     if (e == 0) tma_store_wait_all();
@@ -522,6 +547,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
     const int e = (threadIdx.x - 64) & 127;  // thread index inside the group
     int as = 0;
     uint32_t aphase = 0, ring_pos = 0;
+    const bool post = p.bias != nullptr || p.relu != 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = tile / p.n_tiles;
@@ -541,14 +567,18 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc3_kernel(const __grid_cons
         t.full = (t.n0 + pp.obn <= p.N) && (t.oh0 + pp.obh <= p.OH) && (t.ow0 + pp.obw <= p.OW);
 
         uint64_t* rel_bar = &tmem_empty_bar[as];
-        epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16), staging, red,
-                             row_valid + g * 128, g, r, e, ring_pos, [&]() {
-                               if (half == 1) {   // both halves read: hand the accumulator buffer back to the MMA warp
-                                 tc_fence_before();
-                                 __syncwarp();
-                                 if (lane == 0) mbar_arrive(rel_bar);
-                               }
-                             });
+        auto release = [&]() {
+          if (half == 1) {   // both halves read: hand the accumulator buffer back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(rel_bar);
+          }
+        };
+        const uint32_t tmem_d = tmem_base + as * (2 * BN) + half * BN + (uint32_t(q * 32) << 16);
+        if (post)
+          epi_tile<S::kChunks, true>(p, &tmO, t, tmem_d, staging, red, row_valid + g * 128, g, r, e, ring_pos, release);
+        else
+          epi_tile<S::kChunks, false>(p, &tmO, t, tmem_d, staging, red, row_valid + g * 128, g, r, e, ring_pos, release);
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
@@ -719,6 +749,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const int e = (threadIdx.x - 64) & 127;
     int as = 0;
     uint32_t aphase = 0, ring_pos = 0;
+    const bool post = p.bias != nullptr || p.relu != 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const int n_tile = tile % p.n_tiles;
       const int m_tile = (tile / p.n_tiles) * 2 + (int)cta_rank;
@@ -748,11 +779,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             if (lane == 0) mbar_arrive_cluster(rel_bar);
           }
         };
-        if (cols_live)
-          epi_tile<S::kChunks>(p, &tmO, t, tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16), staging, red,
-                               row_valid + g * 128, g, r, e, ring_pos, release);
-        else
+        const uint32_t tmem_d = tmem_base + as * BN + half * HC + (uint32_t(q * 32) << 16);
+        if (!cols_live)
           release();
+        else if (post)
+          epi_tile<S::kChunks, true>(p, &tmO, t, tmem_d, staging, red, row_valid + g * 128, g, r, e, ring_pos, release);
+        else
+          epi_tile<S::kChunks, false>(p, &tmO, t, tmem_d, staging, red, row_valid + g * 128, g, r, e, ring_pos, release);
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
