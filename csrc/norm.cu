@@ -358,28 +358,51 @@ __global__ void bn_eval_coeffs_kernel(const float* __restrict__ rm, const float*
 // y = x*scale[c] + shift[c] (+ residual) (ReLU).  float4 over channels; C % 4 == 0.
 // `mask` (optional, RELU only): one byte per float4, bit j set iff lane j of the float4 passed the ReLU -- 1/16 of
 // the tensor instead of the whole output when BatchNorm backward needs the mask of a (BN + residual -> ReLU) unit.
+// Element-wise BatchNorm passes: float4 items per thread and loop iteration, and the channel of item i.
+constexpr int kEwUnroll = 4;
+__device__ __forceinline__ int ew_channel(long long i, int C4) {
+  return i <= 0xffffffffll ? (int)((unsigned)i % (unsigned)C4) : (int)(i % C4);
+}
+static inline int ew_grid_unrolled(long long total4) {
+  return ew_grid((total4 + kEwUnroll - 1) / kEwUnroll, 256);
+}
+
 template <bool RES, bool RELU>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, const float* __restrict__ scale,
                                                        const float* __restrict__ shift, const float* __restrict__ res,
                                                        float* __restrict__ y, long long total4, int C4,
                                                        uint8_t* __restrict__ mask = nullptr) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C4) * 4;
-    const float4 v = ldcs4(x + i * 4);
-    const float4 sc = ldg4(scale + c), sf = ldg4(shift + c);
-    float4 o;
-    o.x = fmaf(v.x, sc.x, sf.x); o.y = fmaf(v.y, sc.y, sf.y); o.z = fmaf(v.z, sc.z, sf.z); o.w = fmaf(v.w, sc.w, sf.w);
-    if (RES) {
-      const float4 r = ldcs4(res + i * 4);
-      o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+  // kEwUnroll float4 per thread and iteration, all loads issued before the first use: one load in flight per thread
+  // left these passes latency-bound at ~5.0 of the 6.55 TB/s copy peak (ncu: 57 % of the warp slots, 32 % issue).
+  // The channel index uses 32-bit arithmetic (the 64-bit remainder was a ~50-instruction call per element).
+  const long long stride = (long long)gridDim.x * (256 * kEwUnroll);
+  for (long long base = blockIdx.x * (long long)(256 * kEwUnroll) + threadIdx.x; base < total4; base += stride) {
+    float4 v[kEwUnroll], r[kEwUnroll];
+#pragma unroll
+    for (int k = 0; k < kEwUnroll; ++k) {
+      const long long i = base + k * 256;
+      if (i < total4) {
+        v[k] = ldcs4(x + i * 4);
+        if (RES) r[k] = ldcs4(res + i * 4);
+      }
     }
-    if (RELU) {
-      if (mask != nullptr)
-        mask[i] = (uint8_t)((o.x > 0.f ? 1 : 0) | (o.y > 0.f ? 2 : 0) | (o.z > 0.f ? 4 : 0) | (o.w > 0.f ? 8 : 0));
-      o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+#pragma unroll
+    for (int k = 0; k < kEwUnroll; ++k) {
+      const long long i = base + k * 256;
+      if (i >= total4) break;
+      const int c = ew_channel(i, C4) * 4;
+      const float4 sc = ldg4(scale + c), sf = ldg4(shift + c);
+      float4 o;
+      o.x = fmaf(v[k].x, sc.x, sf.x); o.y = fmaf(v[k].y, sc.y, sf.y);
+      o.z = fmaf(v[k].z, sc.z, sf.z); o.w = fmaf(v[k].w, sc.w, sf.w);
+      if (RES) { o.x += r[k].x; o.y += r[k].y; o.z += r[k].z; o.w += r[k].w; }
+      if (RELU) {
+        if (mask != nullptr)
+          mask[i] = (uint8_t)((o.x > 0.f ? 1 : 0) | (o.y > 0.f ? 2 : 0) | (o.z > 0.f ? 4 : 0) | (o.w > 0.f ? 8 : 0));
+        o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+      }
+      st4(y + i * 4, o);
     }
-    st4(y + i * 4, o);
   }
 }
 
@@ -531,30 +554,47 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restri
                                                            const float* __restrict__ k2, const float* __restrict__ k3,
                                                            float* __restrict__ dx, float* __restrict__ masked,
                                                            long long total4, int C4) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C4) * 4;
-    float4 g = ldcs4(dout + i * 4);
-    const float4 v = ldcs4(x + i * 4);
-    if (RELU == 1) {
-      const float4 o = ldcs4(out + i * 4);
-      g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
-      g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
-    } else if (RELU == 2) {
-      const float4 sc = ldg4(out + c), sf = ldg4(out + C4 * 4 + c);
-      g.x = fmaf(v.x, sc.x, sf.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, sc.y, sf.y) > 0.f ? g.y : 0.f;
-      g.z = fmaf(v.z, sc.z, sf.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, sc.w, sf.w) > 0.f ? g.w : 0.f;
-    } else if (RELU == 3) {
-      const unsigned mk = reinterpret_cast<const uint8_t*>(out)[i];
-      g.x = (mk & 1u) ? g.x : 0.f; g.y = (mk & 2u) ? g.y : 0.f;
-      g.z = (mk & 4u) ? g.z : 0.f; g.w = (mk & 8u) ? g.w : 0.f;
+  // same shape as bn_apply_kernel: kEwUnroll float4 per thread and iteration, loads first
+  const long long stride = (long long)gridDim.x * (256 * kEwUnroll);
+  for (long long base = blockIdx.x * (long long)(256 * kEwUnroll) + threadIdx.x; base < total4; base += stride) {
+    float4 gg[kEwUnroll], vv[kEwUnroll], oo[kEwUnroll];
+    unsigned mk[kEwUnroll];
+#pragma unroll
+    for (int k = 0; k < kEwUnroll; ++k) {
+      const long long i = base + k * 256;
+      if (i < total4) {
+        gg[k] = ldcs4(dout + i * 4);
+        vv[k] = ldcs4(x + i * 4);
+        if (RELU == 1) oo[k] = ldcs4(out + i * 4);
+        if (RELU == 3) mk[k] = reinterpret_cast<const uint8_t*>(out)[i];
+      }
     }
-    const float4 a = ldg4(k1 + c), b = ldg4(k2 + c), d = ldg4(k3 + c);
-    float4 r;
-    r.x = fmaf(g.x, a.x, fmaf(v.x, b.x, d.x)); r.y = fmaf(g.y, a.y, fmaf(v.y, b.y, d.y));
-    r.z = fmaf(g.z, a.z, fmaf(v.z, b.z, d.z)); r.w = fmaf(g.w, a.w, fmaf(v.w, b.w, d.w));
-    st4(dx + i * 4, r);
-    if (MASKED) st4(masked + i * 4, g);
+#pragma unroll
+    for (int k = 0; k < kEwUnroll; ++k) {
+      const long long i = base + k * 256;
+      if (i >= total4) break;
+      const int c = ew_channel(i, C4) * 4;
+      float4 g = gg[k];
+      const float4 v = vv[k];
+      if (RELU == 1) {
+        const float4 o = oo[k];
+        g.x = o.x > 0.f ? g.x : 0.f; g.y = o.y > 0.f ? g.y : 0.f;
+        g.z = o.z > 0.f ? g.z : 0.f; g.w = o.w > 0.f ? g.w : 0.f;
+      } else if (RELU == 2) {
+        const float4 sc = ldg4(out + c), sf = ldg4(out + C4 * 4 + c);
+        g.x = fmaf(v.x, sc.x, sf.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, sc.y, sf.y) > 0.f ? g.y : 0.f;
+        g.z = fmaf(v.z, sc.z, sf.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, sc.w, sf.w) > 0.f ? g.w : 0.f;
+      } else if (RELU == 3) {
+        g.x = (mk[k] & 1u) ? g.x : 0.f; g.y = (mk[k] & 2u) ? g.y : 0.f;
+        g.z = (mk[k] & 4u) ? g.z : 0.f; g.w = (mk[k] & 8u) ? g.w : 0.f;
+      }
+      const float4 a = ldg4(k1 + c), b = ldg4(k2 + c), d = ldg4(k3 + c);
+      float4 r;
+      r.x = fmaf(g.x, a.x, fmaf(v.x, b.x, d.x)); r.y = fmaf(g.y, a.y, fmaf(v.y, b.y, d.y));
+      r.z = fmaf(g.z, a.z, fmaf(v.z, b.z, d.z)); r.w = fmaf(g.w, a.w, fmaf(v.w, b.w, d.w));
+      st4(dx + i * 4, r);
+      if (MASKED) st4(masked + i * 4, g);
+    }
   }
 }
 
@@ -846,7 +886,7 @@ DCNN_API int dcnn_bn_apply(const float* x, const float* scale, const float* shif
   const long long total = M * C;
   if ((C & 3) == 0) {
     const long long t4 = total / 4;
-    const int grid = ew_grid(t4, 256);
+    const int grid = ew_grid_unrolled(t4);
     const int C4 = C / 4;
     if (residual && relu) bn_apply_kernel<true, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C4);
     else if (residual) bn_apply_kernel<true, false><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C4);
@@ -866,7 +906,7 @@ DCNN_API int dcnn_bn_apply_mask(const float* x, const float* scale, const float*
                                 float* y, unsigned char* mask, long long M, int C, cudaStream_t stream) {
   DCNN_REQUIRE((C & 3) == 0, "dcnn_bn_apply_mask: C (%d) must be a multiple of 4", C);
   const long long t4 = M * C / 4;
-  const int grid = ew_grid(t4, 256);
+  const int grid = ew_grid_unrolled(t4);
   if (residual) bn_apply_kernel<true, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C / 4, mask);
   else bn_apply_kernel<false, true><<<grid, 256, 0, stream>>>(x, scale, shift, residual, y, t4, C / 4, mask);
   DCNN_CHECK_LAUNCH();
@@ -955,7 +995,7 @@ DCNN_API int dcnn_bn_bwd_apply(const float* dout, const float* x, const float* o
   const long long total = M * C;
   if ((C & 3) == 0) {
     const long long t4 = total / 4;
-    const int grid = ew_grid(t4, 256);
+    const int grid = ew_grid_unrolled(t4);
     const int C4 = C / 4;
     if (relu == 3 && masked)
       bn_bwd_apply_kernel<3, true><<<grid, 256, 0, stream>>>(dout, x, out, k1, k2, k3, dx, masked, t4, C4);
