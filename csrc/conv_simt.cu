@@ -139,24 +139,50 @@ __global__ void weight_dgrad_layout_kernel(const float* __restrict__ w, float* _
 
 
 // Up to kWtBatch weight tensors in ONE launch: the table {w, wt, K, R, S, C} travels as a kernel parameter (no device
-// table, so the launch is capturable without a host-to-device copy); blockIdx.y selects the entry, blockIdx.x strides
-// over its elements.
+// table, so the launch is capturable without a host-to-device copy); the CTAs stride over the 32 x 32 tiles of all entries.
 constexpr int kWtBatch = 64;
-struct WtTable { long long e[kWtBatch][6]; };
+struct WtTable {
+  long long e[kWtBatch][6];
+  int tile_end[kWtBatch];   // running total of 32 x 32 tiles up to and including entry i
+  int count;
+};
 __global__ void __launch_bounds__(256) weight_dgrad_layout_batched_kernel(const __grid_constant__ WtTable table) {
-  const long long* e = table.e[blockIdx.y];
-  const float* __restrict__ w = reinterpret_cast<const float*>(e[0]);
-  float* __restrict__ wt = reinterpret_cast<float*>(e[1]);
-  const int K = (int)e[2], R = (int)e[3], S = (int)e[4], C = (int)e[5];
-  const long long total = (long long)K * R * S * C;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int k = (int)(i % K);
-    long long t = i / K;
-    const int s2 = (int)(t % S); t /= S;
-    const int r2 = (int)(t % R);
-    const int c = (int)(t / R);
-    wt[i] = __ldg(w + (((long long)k * R + (R - 1 - r2)) * S + (S - 1 - s2)) * C + c);
+  // per tap a [K][C] -> [C][K] transpose (taps mirrored) through a 32 x 32 shared-memory tile: reads coalesced along c,
+  // writes coalesced along k, and the index arithmetic is per tile instead of four 64-bit divisions per element (the
+  // element-wise version ran at 1.5 TB/s: 128 us for the 94 MB of ResNet-50 weights)
+  // The tiles of all entries form one list that the CTAs stride over (an entry per blockIdx.y with a fixed number of
+  // CTAs left the three 2.4M-element weights of the last stage to 64 CTAs each: 119 us, latency-bound).
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int total_tiles = table.tile_end[table.count - 1];
+  for (int g = blockIdx.x; g < total_tiles; g += gridDim.x) {
+    int lo = 0, hi = table.count - 1;   // first entry whose running total exceeds g
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (table.tile_end[mid] > g) hi = mid; else lo = mid + 1;
+    }
+    const long long* e = table.e[lo];
+    const float* __restrict__ w = reinterpret_cast<const float*>(e[0]);
+    float* __restrict__ wt = reinterpret_cast<float*>(e[1]);
+    const int K = (int)e[2], R = (int)e[3], S = (int)e[4], C = (int)e[5];
+    const int kt = (K + 31) >> 5, ct = (C + 31) >> 5;
+    const int t = g - (lo > 0 ? table.tile_end[lo - 1] : 0);
+    const int cb = t % ct;
+    const int u = t / ct;
+    const int kb = u % kt, tap = u / kt;
+    const int r = tap / S, s2 = tap % S;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = kb * 32 + ty + 8 * j, c = cb * 32 + tx;
+      tile[ty + 8 * j][tx] = (k < K && c < C) ? __ldg(w + (((long long)k * R + r) * S + s2) * C + c) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = cb * 32 + ty + 8 * j, k = kb * 32 + tx;
+      if (c < C && k < K) wt[(((long long)c * R + (R - 1 - r)) * S + (S - 1 - s2)) * K + k] = tile[tx][ty + 8 * j];
+    }
+    __syncthreads();
   }
 }
 
@@ -233,8 +259,16 @@ DCNN_API int dcnn_weight_dgrad_layout_batched(const long long* table_host, int c
     WtTable t;
     memset(&t, 0, sizeof(t));
     memcpy(t.e, table_host + 6 * (size_t)first, sizeof(long long) * 6 * n);
-    dim3 grid(64, (unsigned)n);
-    weight_dgrad_layout_batched_kernel<<<grid, 256, 0, stream>>>(t);
+    long long total = 0;
+    for (int i = 0; i < n; ++i) {
+      const long long K = t.e[i][2], R = t.e[i][3], S = t.e[i][4], C = t.e[i][5];
+      total += R * S * ((K + 31) / 32) * ((C + 31) / 32);
+      DCNN_REQUIRE(total < (1ll << 31), "dcnn_weight_dgrad_layout_batched: too many tiles (%lld)", total);
+      t.tile_end[i] = (int)total;
+    }
+    t.count = n;
+    const long long cap = 8ll * num_sms();
+    weight_dgrad_layout_batched_kernel<<<(unsigned)(total < cap ? total : cap), 256, 0, stream>>>(t);
     DCNN_CHECK_LAUNCH();
     DCNN_COUNT_LAUNCH(1);
   }
