@@ -34,7 +34,11 @@ def main():
     dev = "cuda" if cuda else "cpu"
     shapes = [(64, 128, 2097152 if cuda else 65536), (262144, 256, 64), (262144, 64, 256), (65536, 512, 128),
               (16384, 1024, 256), (4096, 2048, 512), (256, 200, 2048)]
-    print(f"{'M':>8} {'N':>6} {'K':>8} | {'fwd ms':>9} {'TFLOP/s':>8} | {'wgrad ms':>9} {'TFLOP/s':>8}")
+    # the library GEMM of the same precision class next to ours (the reference's Dense layer is cuBLAS SGEMM,
+    # src/math/cuda/gemm.cu:28): torch.matmul = cuBLAS / cuBLASLt with TF32 allowed, y = x w^T and dw = dy^T x
+    torch.backends.cuda.matmul.allow_tf32 = True
+    print(f"{'M':>8} {'N':>6} {'K':>8} | {'fwd ms':>9} {'TFLOP/s':>8} {'cuBLAS ms':>10} {'ratio':>6} | "
+          f"{'wgrad ms':>9} {'TFLOP/s':>8} {'cuBLAS ms':>10} {'ratio':>6}")
     for M, N, K in shapes:
         x = torch.randn(M, K, device=dev)
         w = torch.randn(N, K, device=dev) / K ** 0.5
@@ -42,8 +46,13 @@ def main():
         dw = torch.zeros(N, K, device=dev)
         t_f = timed(lambda: ops.dense_forward(x, w, None), 10, cuda)
         t_w = timed(lambda: ops.dense_backward_weight(dy, x, dw), 10, cuda)
+        c_f = timed(lambda: torch.matmul(x, w.t()), 10, cuda)
+        c_w = timed(lambda: dw.addmm_(dy.t(), x), 10, cuda)
         fl = 2.0 * M * N * K
-        print(f"{M:>8} {N:>6} {K:>8} | {t_f:>9.3f} {fl / t_f / 1e9:>8.1f} | {t_w:>9.3f} {fl / t_w / 1e9:>8.1f}")
+        print(f"{M:>8} {N:>6} {K:>8} | {t_f:>9.3f} {fl / t_f / 1e9:>8.1f} {c_f:>10.3f} {c_f / t_f:>5.2f}x | "
+              f"{t_w:>9.3f} {fl / t_w / 1e9:>8.1f} {c_w:>10.3f} {c_w / t_w:>5.2f}x")
+    print("ratio = library time / ours (> 1: ours is faster); back-to-back launches, operands larger than L2 except the "
+          "last shape")
 
 
 if __name__ == "__main__":
