@@ -431,10 +431,29 @@ def _one_tap():
     return _ONE_TAP
 
 
+def _reduction_bound(B, Fout, Fin):
+    """A product with a handful of output tiles and a very long reduction (the reference's gemm_benchmark shape,
+    64 x 128 x 2M): the forward kernel has no split-K, so it would run on as many SMs as there are output tiles."""
+    return (B + 127) // 128 * ((Fout + 127) // 128) <= 8 and Fin >= 32768 and B % 4 == 0
+
+
+def _dense_forward_split_k(x2d, w2d, bias, relu):
+    """y = x w^T through the weight-gradient kernel, whose reduction dimension is split over the whole machine:
+    dW'[B][Fout] = (x^T)^T (w^T) with the Fin reduction rows as its 'pixels' (two transposed copies, then one launch)."""
+    B, Fout = x2d.shape[0], w2d.shape[0]
+    y = torch.zeros((B, Fout), device=x2d.device, dtype=torch.float32)
+    dense_backward_weight(x2d.t().contiguous(), w2d.t().contiguous(), y)
+    if bias is not None:
+        y += bias.reshape(1, Fout)
+    return torch.relu_(y) if relu else y
+
+
 def dense_forward(x2d, w2d, bias, relu=False):
     x2d = x2d.contiguous()
     B, Fin = x2d.shape
     Fout = w2d.shape[0]
+    if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0 and _reduction_bound(B, Fout, Fin):
+        return _dense_forward_split_k(x2d, w2d.reshape(Fout, Fin), bias, relu)
     y = torch.empty((B, Fout), device=x2d.device, dtype=torch.float32)
     if tc_enabled() and Fin % 4 == 0 and Fout % 4 == 0:
         _conv_tc(x2d, B, 1, 1, Fin, w2d, Fout, Fin, y, 0, Fout, Fout, Fout, 1, 1, 1, 1, _one_tap(), bias, False, None,

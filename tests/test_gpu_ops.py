@@ -263,6 +263,17 @@ def test_dense(B, Fin, Fout):
     check_close(dw, dw_ref, tol, "dense wgrad")
 
 
+def test_dense_forward_with_few_output_tiles_and_a_long_reduction():
+    """One output tile and a 65536-long reduction: routed through the split-K weight-gradient kernel
+    (ops/cuda.py::_dense_forward_split_k) instead of a forward launch that would occupy one SM."""
+    M, N, K = 8, 12, 65536
+    x, w, b = torch.randn(M, K), torch.randn(N, K) / K ** 0.5, torch.randn(N)
+    y = ops.dense_forward(x.to(DEV), w.to(DEV), b.to(DEV), True)
+    want = torch.relu(x @ w.t() + b)
+    assert y.shape == want.shape
+    assert float((y.cpu() - want).abs().max() / want.abs().max()) < 4e-3
+
+
 # ----------------------------------------------------------------------------------------- batch norm
 @pytest.mark.parametrize("N,C,H,W", [(8, 64, 16, 16), (4, 256, 8, 8), (3, 6, 5, 5), (16, 2048, 2, 2)])
 @pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True)])
