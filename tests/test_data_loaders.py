@@ -227,3 +227,44 @@ def test_prefetch_loader_surfaces_producer_errors():
     with _pytest.raises(RuntimeError, match="disk on fire"):
         while pf.get_next_batch() is not None:
             pass
+
+
+def test_prefetch_loader_is_reusable_over_epochs_of_different_length():
+    """bench.py's end-to-end arm keeps ONE PrefetchLoader for its warm-up epoch and its timed epoch (so that the pinned
+    staging ring and the side-stream buffers exist before the timed region): an epoch abandoned half-way, then epochs of
+    different lengths, must each deliver exactly their own batches, in order."""
+    from dcnn_b200.data import PrefetchLoader
+
+    class Counted:
+        def __init__(self):
+            self.n, self.i = 0, 0
+
+        def size(self):
+            return self.n * 4
+
+        def reset(self):
+            self.i = 0
+
+        def get_batch(self, batch_size):
+            if self.i >= self.n:
+                return None
+            self.i += 1
+            return torch.full((batch_size, 2), float(self.i)), torch.full((batch_size, 1), float(-self.i))
+
+    src = Counted()
+    pf = PrefetchLoader(src, 4, depth=2)
+    src.n = 6
+    pf.reset()
+    assert float(pf.get_next_batch()[0][0, 0]) == 1.0          # ... and abandon the epoch with batches still queued
+    for n in (3, 1, 5):
+        src.n = n
+        pf.reset()
+        seen = []
+        while True:
+            b = pf.get_next_batch()
+            if b is None:
+                break
+            assert float(b[1][0, 0]) == -float(b[0][0, 0])
+            seen.append(int(b[0][0, 0]))
+        assert seen == list(range(1, n + 1)), seen
+    pf.close()
