@@ -338,8 +338,9 @@ def main():
     h2d = host_x[0].numel() * 4 + host_t[0].numel() * 4
     d2h = 8
     out_host = [pin(torch.zeros(2, dtype=torch.float32)) for _ in range(2)]
-    # The batches come through the library's PrefetchLoader, the front end train_classification_model puts on every
-    # loader (dcnn_b200/train.py): a worker thread stages each batch in pinned memory and issues its host-to-device copy
+    # The batches come through the library's PrefetchLoader, the streaming front end of the training loops
+    # (PREFETCH_DEPTH=k in train_classification_model, dcnn_b200/train.py): a worker thread stages each batch in pinned
+    # memory and issues its host-to-device copy
     # on a side stream, so the copy of batch i+1 overlaps the kernels of step i.  One "epoch" of exactly `steps` batches
     # is produced inside the timed region (the loader is started after the first event), nothing is copied ahead of it.
     class _HostBatches:
