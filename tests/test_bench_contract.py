@@ -13,7 +13,17 @@ KEYS = {"metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "
         "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "impl"}
 
 
-def _bench(args, nproc=1, port=29700, timeout=600):
+def _free_port():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _bench(args, nproc=1, port=None, timeout=600):
+    port = port or _free_port()      # fixed ports collided with other multi-process tests under pytest-xdist
     cmd = [sys.executable]
     if nproc > 1:
         cmd += ["-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
@@ -53,7 +63,7 @@ def test_headline_defaults_name_the_baseline_config():
                                        ("pp2", {"dp_replicas": 1, "pipeline_stages": 2})])
 def test_two_rank_modes(par, extra):
     out = _bench(["--gpus", "2", "--steps", "2", "--warmup", "1", "--batch", "4", "--model", "mnist_cnn",
-                  "--parallelism", par], nproc=2, port=29701 if par == "dp2" else 29702)
+                  "--parallelism", par], nproc=2)
     cfg = out["config"]
     assert out["n_gpus"] == 2 and cfg["parallelism"] == par
     assert all(cfg[k] == v for k, v in extra.items())
